@@ -1,0 +1,159 @@
+/* b200jpeg.h -- C ABI of the B200-native baseline-JPEG codec (libb200jpeg.so).
+ *
+ * This is the drop-in boundary below nvImageCodec's plugin interface.  Every entry point takes plain pointers and sizes
+ * (no C++/torch types).  The nvImageCodec extension module (libb200jpeg_ext.so, exporting nvimgcodecExtensionModuleEntry,
+ * reference include/nvimgcodec.h:1356-1364) is a thin adapter that forwards the plugin callbacks
+ *     nvimgcodecDecoderDesc_t::create/destroy/canDecode/decode   (reference include/nvimgcodec.h:1150-1209)
+ *     nvimgcodecEncoderDesc_t::create/destroy/canEncode/encode   (reference include/nvimgcodec.h:1087-1145)
+ * to the functions below; the reference implementation they replace is extensions/libjpeg_turbo/
+ * libjpeg_turbo_decoder.cpp:118-173 (canDecode), :324-490 (decode/decodeBatch) and, for encode, the libjpeg-turbo
+ * jpeg_compress path (the reference ships no CPU JPEG encoder plugin; extensions/nvjpeg/cuda_encoder.cpp:284-396 is the
+ * interface precedent).
+ *
+ * All compute is CUDA on sm_100a.  There is no CPU fallback: every call that needs the device fails with
+ * B200JPEG_STATUS_CUDA_ERROR / ARCH_MISMATCH when it is missing.
+ */
+#ifndef B200JPEG_H
+#define B200JPEG_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200JPEG_API __attribute__((visibility("default")))
+#else
+#define B200JPEG_API
+#endif
+
+typedef struct b200jpegDecoder* b200jpegDecoder_t;
+typedef struct b200jpegEncoder* b200jpegEncoder_t;
+
+typedef enum
+{
+    B200JPEG_STATUS_SUCCESS = 0,
+    B200JPEG_STATUS_INVALID_PARAMETER = 1,
+    B200JPEG_STATUS_BAD_JPEG = 2,         /* marker syntax broken / truncated header */
+    B200JPEG_STATUS_UNSUPPORTED = 3,      /* valid JPEG outside this codec's scope (progressive, arithmetic, 12-bit, CMYK, 4:1:1 ...) */
+    B200JPEG_STATUS_CORRUPT_STREAM = 4,   /* entropy-coded data inconsistent with the header (detected on the GPU) */
+    B200JPEG_STATUS_CUDA_ERROR = 5,
+    B200JPEG_STATUS_ARCH_MISMATCH = 6,    /* device is not sm_100 */
+    B200JPEG_STATUS_ALLOC_FAILED = 7,
+    B200JPEG_STATUS_BUFFER_TOO_SMALL = 8, /* encoder output capacity */
+    B200JPEG_STATUS_INTERNAL_ERROR = 9
+} b200jpegStatus_t;
+
+/* Output sample formats; the numeric values equal nvimgcodecSampleFormat_t (reference include/nvimgcodec.h:384-392). */
+typedef enum
+{
+    B200JPEG_FMT_P_UNCHANGED = 1, /* planar RGB, also for gray streams (what libjpeg_turbo_ext produces) */
+    B200JPEG_FMT_I_UNCHANGED = 2, /* interleaved RGB */
+    B200JPEG_FMT_P_RGB = 3,
+    B200JPEG_FMT_I_RGB = 4,
+    B200JPEG_FMT_P_BGR = 5,
+    B200JPEG_FMT_I_BGR = 6,
+    B200JPEG_FMT_P_Y = 7
+} b200jpegFormat_t;
+
+/* Chroma subsampling; numeric values equal nvimgcodecChromaSubsampling_t (reference include/nvimgcodec.h:360-372). */
+typedef enum
+{
+    B200JPEG_CSS_444 = 0,
+    B200JPEG_CSS_422 = 2,
+    B200JPEG_CSS_420 = 3,
+    B200JPEG_CSS_440 = 4,
+    B200JPEG_CSS_GRAY = 7
+} b200jpegSubsampling_t;
+
+/* What the header parse found (the plugin's canDecode decides on this; mirrors what the reference learns from
+ * jpeg_read_header, external/libjpeg-turbo/jdmarker.c get_sof:242 / get_sos:308 / get_dri:569). */
+typedef struct
+{
+    int32_t width, height;
+    int32_t num_components;       /* 1 or 3 */
+    int32_t h_samp[3], v_samp[3];
+    int32_t subsampling;          /* b200jpegSubsampling_t, -1 if not one of them */
+    int32_t sof_marker;           /* 0xC0 .. 0xCF */
+    int32_t restart_interval;     /* MCUs, 0 = none */
+    int32_t precision;
+    int32_t supported;            /* 1 if b200jpeg_decode_batch can decode it */
+    uint64_t scan_offset, scan_bytes; /* entropy-coded segment inside the file */
+} b200jpegStreamInfo_t;
+
+/* One output image of a decode batch: device (or host) pixel buffer description, same meaning as the
+ * nvimgcodecImageInfo_t fields buffer / plane_info[].row_stride / sample_format (reference include/nvimgcodec.h:474-497).
+ * Planar formats: plane p starts at buffer + p * row_stride * height (reference extensions/nvjpeg/cuda_decoder.cpp:532-538). */
+typedef struct
+{
+    void* buffer;
+    int64_t row_stride;  /* bytes */
+    int32_t format;      /* b200jpegFormat_t */
+    int32_t on_host;     /* 0: buffer is device memory (plugin case); 1: host memory, the library stages + copies back */
+} b200jpegOutput_t;
+
+/* ---- library ---- */
+B200JPEG_API const char* b200jpeg_version(void);
+B200JPEG_API const char* b200jpeg_status_string(int status);
+
+/* ---- stream probe (host only, no CUDA) ---- */
+B200JPEG_API int b200jpeg_parse_header(const uint8_t* data, size_t size, b200jpegStreamInfo_t* info);
+
+/* ---- decoder ----
+ * options: the reference's option string, "name=value" tokens separated by spaces, optional "b200jpeg_decoder:" or ":"
+ * prefix (reference extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:250-276): fancy_upsampling=0|1 (default 1),
+ * subseq_bytes=N, sync_rounds=N. */
+B200JPEG_API int b200jpeg_decoder_create(b200jpegDecoder_t* decoder, int device_id, const char* options);
+B200JPEG_API int b200jpeg_decoder_destroy(b200jpegDecoder_t decoder);
+
+/* Decode a batch.  data[i]/sizes[i]: whole JPEG files in host memory.  outputs[i]: where the pixels go.
+ * user_stream: CUDA stream (cudaStream_t as void*) the outputs are ordered on -- on return the work has been enqueued and
+ * synchronised enough that statuses[i] is final (B200JPEG_STATUS_*) and device outputs are complete.
+ * Replaces DecoderImpl::decodeBatch (reference extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:444-490). */
+B200JPEG_API int b200jpeg_decode_batch(b200jpegDecoder_t decoder, int batch_size, const uint8_t* const* data, const size_t* sizes,
+    const b200jpegOutput_t* outputs, void* user_stream, int32_t* statuses);
+
+/* Two-phase variant used to time the device work with inputs already resident in HBM:
+ * prepare = parse + table building + H2D of bitstreams/descriptors; run = every kernel of the decode, nothing else. */
+B200JPEG_API int b200jpeg_decode_prepare(b200jpegDecoder_t decoder, int batch_size, const uint8_t* const* data, const size_t* sizes,
+    const b200jpegOutput_t* outputs, int32_t* statuses);
+B200JPEG_API int b200jpeg_decode_run(b200jpegDecoder_t decoder, void* user_stream, int32_t* statuses);
+
+/* Counters of the last run: [0] kernels launched, [1] Huffman sync rounds, [2] entropy-coded bytes, [3] decoded blocks,
+ * [4] subsequences, [5] device scratch bytes, [6] re-run count (non-converged sync), [7] reserved */
+B200JPEG_API int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats8);
+
+/* Debug/verification taps on the last prepared+run batch (device -> host copies of intermediates):
+ *   what = 0: quantised coefficients of image i in MCU scan order, int16[blocks*64] (natural order inside a block)
+ *   what = 1: component plane c of image i after dequant+IDCT (MCU-padded), uint8
+ *   what = 2: unstuffed entropy-coded bytes of image i
+ * returns bytes written or <0 */
+B200JPEG_API int64_t b200jpeg_debug_fetch(b200jpegDecoder_t decoder, int what, int image, int component, void* host_dst, size_t capacity);
+
+/* ---- encoder (baseline, standard Huffman tables, JFIF header; mirrors libjpeg-turbo jpeg_compress with
+ * jpeg_set_quality(q, TRUE), JDCT_ISLOW, optimize_coding=FALSE) ---- */
+typedef struct
+{
+    const void* buffer;  /* interleaved RGB (format I_RGB) or gray (P_Y) uint8 */
+    int64_t row_stride;
+    int32_t width, height;
+    int32_t format;      /* B200JPEG_FMT_I_RGB | B200JPEG_FMT_P_RGB | B200JPEG_FMT_P_Y */
+    int32_t on_host;
+    int32_t subsampling; /* b200jpegSubsampling_t of the produced stream */
+    int32_t quality;     /* 1..100 */
+    int32_t restart_interval;
+} b200jpegEncodeInput_t;
+
+B200JPEG_API int b200jpeg_encoder_create(b200jpegEncoder_t* encoder, int device_id, const char* options);
+B200JPEG_API int b200jpeg_encoder_destroy(b200jpegEncoder_t encoder);
+/* out[i] (host memory, capacity out_capacity[i]) receives a complete JFIF file; out_sizes[i] its length. */
+B200JPEG_API int b200jpeg_encode_batch(b200jpegEncoder_t encoder, int batch_size, const b200jpegEncodeInput_t* inputs, uint8_t* const* out,
+    const size_t* out_capacity, size_t* out_sizes, void* user_stream, int32_t* statuses);
+B200JPEG_API int b200jpeg_encoder_get_stats(b200jpegEncoder_t encoder, uint64_t* stats8);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200JPEG_H */

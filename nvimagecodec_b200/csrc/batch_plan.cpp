@@ -1,0 +1,195 @@
+// batch_plan.cpp -- see batch_plan.h
+#include "batch_plan.h"
+#include <cstring>
+
+namespace b200jpeg {
+
+namespace {
+inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
+inline uint32_t cdiv(uint64_t a, uint64_t b) { return uint32_t((a + b - 1) / b); }
+} // namespace
+
+// canonical code assignment as in jpeg_make_d_derived_tbl (external/libjpeg-turbo/jdhuff.c:143-285)
+void build_dev_table(const HuffSpec& spec, DevHuffTable& t)
+{
+    std::memset(&t, 0, sizeof(t));
+    std::memcpy(t.vals, spec.vals, 256);
+    int code = 0, p = 0;
+    for (int l = 1; l <= 16; ++l) {
+        const int n = spec.bits[l];
+        if (n) {
+            t.valoffset[l] = p - code;
+            for (int i = 0; i < n; ++i, ++p, ++code) {
+                if (l <= kLutBits && code < (1 << l)) {
+                    const int first = code << (kLutBits - l);
+                    const int cnt = 1 << (kLutBits - l);
+                    for (int j = 0; j < cnt; ++j)
+                        t.lut[first + j] = uint16_t((l << 8) | spec.vals[p & 255]);
+                }
+            }
+            t.maxcode[l] = code - 1;
+        } else {
+            t.maxcode[l] = -1;
+        }
+        code <<= 1;
+    }
+    t.maxcode[0] = -1;
+    t.maxcode[17] = 0x7FFFFFFF;
+}
+
+int resolve_format(int f, int ncomp)
+{
+    (void)ncomp;
+    switch (f) {
+    // *_UNCHANGED is 3-channel RGB in the reference plugin even for gray streams
+    // (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:336-345,400-412)
+    case 1: return 3; // P_UNCHANGED -> planar RGB
+    case 2: return 4; // I_UNCHANGED -> interleaved RGB
+    case 3: case 4: case 5: case 6: case 7: return f;
+    default: return 0;
+    }
+}
+
+void plan_begin(BatchPlan& plan, const PlanOptions& opt)
+{
+    plan = BatchPlan();
+    plan.subseq_bits = opt.subseq_bytes * 8;
+    plan.map_unstuff.push_back(0);
+    plan.map_subseq.push_back(0);
+    plan.map_idct.push_back(0);
+    plan.map_color.push_back(0);
+}
+
+static int intern_huff(BatchPlan& plan, std::vector<HuffSpec>& seen, const HuffSpec& s)
+{
+    for (size_t i = 0; i < seen.size(); ++i)
+        if (!std::memcmp(seen[i].bits, s.bits, 17) && !std::memcmp(seen[i].vals, s.vals, 256))
+            return int(i);
+    seen.push_back(s);
+    plan.huff.emplace_back();
+    build_dev_table(s, plan.huff.back());
+    return int(seen.size() - 1);
+}
+
+static int intern_quant(BatchPlan& plan, const uint16_t* q)
+{
+    const size_t n = plan.quant.size() / 64;
+    for (size_t i = 0; i < n; ++i)
+        if (!std::memcmp(&plan.quant[i * 64], q, 128))
+            return int(i);
+    plan.quant.insert(plan.quant.end(), q, q + 64);
+    return int(n);
+}
+
+// one spec list per plan; kept in a side table keyed by the plan address (plans are built single-threaded)
+static thread_local std::vector<HuffSpec> g_seen;
+
+void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out, const PlanOptions& opt)
+{
+    if (plan.images.empty())
+        g_seen.clear();
+    ImageDesc im;
+    std::memset(&im, 0, sizeof(im));
+    im.width = pj.width;
+    im.height = pj.height;
+    im.ncomp = pj.ncomp;
+    im.out_fmt = resolve_format(out.format, pj.ncomp);
+    im.ncomp_out = (im.out_fmt == 7) ? 1 : pj.ncomp;
+    im.hmax = im.vmax = 1;
+    for (int c = 0; c < pj.ncomp; ++c) {
+        im.hs[c] = pj.ncomp == 1 ? 1 : pj.hs[c]; // a single-component scan is never interleaved (jdinput.c:166-186)
+        im.vs[c] = pj.ncomp == 1 ? 1 : pj.vs[c];
+        if (im.hs[c] > im.hmax) im.hmax = im.hs[c];
+        if (im.vs[c] > im.vmax) im.vmax = im.vs[c];
+    }
+    for (int c = pj.ncomp; c < 3; ++c)
+        im.hs[c] = im.vs[c] = 1;
+    im.mcus_x = (pj.width + 8 * im.hmax - 1) / (8 * im.hmax);
+    im.mcus_y = (pj.height + 8 * im.vmax - 1) / (8 * im.vmax);
+    int j = 0;
+    for (int c = 0; c < pj.ncomp; ++c) {
+        im.blk_first[c] = j;
+        for (int k = 0; k < im.hs[c] * im.vs[c]; ++k)
+            im.blk_comp[j++] = uint8_t(c);
+        im.wib[c] = im.mcus_x * im.hs[c];
+        im.hib[c] = im.mcus_y * im.vs[c];
+        im.ds_w[c] = (pj.width * im.hs[c] + im.hmax - 1) / im.hmax;
+        im.ds_h[c] = (pj.height * im.vs[c] + im.vmax - 1) / im.vmax;
+        im.qt[c] = intern_quant(plan, pj.quant[pj.tq[c]]);
+        im.dc_tab[c] = intern_huff(plan, g_seen, pj.dc[pj.td[c]]);
+        im.ac_tab[c] = intern_huff(plan, g_seen, pj.ac[pj.ta[c]]);
+    }
+    im.bpm = j;
+    im.mcu_slots = j * 64;
+    const uint32_t mcus = uint32_t(im.mcus_x) * uint32_t(im.mcus_y);
+    im.total_slots = mcus * uint32_t(im.mcu_slots);
+    im.restart_interval = pj.restart_interval;
+    if (pj.restart_interval > 0 && uint32_t(pj.restart_interval) < mcus) {
+        im.num_segments = int(cdiv(mcus, pj.restart_interval));
+        im.seg_slots = uint32_t(pj.restart_interval) * uint32_t(im.mcu_slots);
+    } else {
+        im.num_segments = 1;
+        im.seg_slots = im.total_slots;
+        im.restart_interval = 0;
+    }
+    im.seg_first = plan.total_segs;
+    plan.total_segs += uint32_t(im.num_segments) + 1;
+
+    im.raw_off = plan.raw_bytes;
+    im.raw_len = uint32_t(pj.scan_bytes);
+    plan.raw_bytes = align_up(plan.raw_bytes + im.raw_len + 1, 16);
+    im.clean_off = plan.clean_bytes;
+    plan.clean_bytes = align_up(plan.clean_bytes + im.raw_len + 16, 16);
+
+    im.chunk_first = plan.total_chunks;
+    im.chunk_count = cdiv(im.raw_len, kChunkBytes);
+    if (im.chunk_count == 0) im.chunk_count = 1;
+    plan.total_chunks += im.chunk_count;
+    plan.map_unstuff.push_back(plan.total_chunks);
+
+    im.subseq_count = cdiv(uint64_t(im.raw_len) * 8, plan.subseq_bits);
+    if (im.subseq_count == 0) im.subseq_count = 1;
+    im.subseq_cta_count = cdiv(im.subseq_count, kSubseqCta);
+    im.subseq_first = plan.total_subseq;
+    im.subseq_cta_first = plan.map_subseq.back();
+    plan.total_subseq += im.subseq_cta_count * kSubseqCta;
+    plan.map_subseq.push_back(im.subseq_cta_first + im.subseq_cta_count);
+
+    im.coef_off = plan.coef_elems;
+    plan.coef_elems = align_up(plan.coef_elems + im.total_slots, 64);
+    uint64_t blocks_out = 0;
+    for (int c = 0; c < pj.ncomp; ++c) {
+        im.plane_pitch[c] = im.wib[c] * 8;
+        im.plane_off[c] = plan.plane_bytes;
+        plan.plane_bytes = align_up(plan.plane_bytes + uint64_t(im.plane_pitch[c]) * im.hib[c] * 8 + 16, 128);
+        if (c < im.ncomp_out)
+            blocks_out += uint64_t(im.wib[c]) * im.hib[c];
+    }
+    im.idct_cta_first = plan.map_idct.back();
+    im.idct_cta_count = cdiv(blocks_out, kIdctCta);
+    plan.map_idct.push_back(im.idct_cta_first + im.idct_cta_count);
+    const uint64_t units = uint64_t(cdiv(pj.width, 16)) * pj.height;
+    im.color_cta_first = plan.map_color.back();
+    im.color_cta_count = cdiv(units, kColorCta);
+    plan.map_color.push_back(im.color_cta_first + im.color_cta_count);
+
+    im.out = static_cast<uint8_t*>(out.buffer);
+    im.out_stride = out.row_stride;
+    im.fancy = opt.fancy_upsampling ? 1 : 0;
+
+    plan.total_blocks += uint64_t(mcus) * im.bpm;
+    plan.total_pixels += uint64_t(pj.width) * pj.height;
+    const int planes = (im.out_fmt == 7) ? 1 : 3;
+    plan.out_bytes += uint64_t(pj.width) * pj.height * planes;
+    plan.images.push_back(im);
+}
+
+void plan_finish(BatchPlan& plan)
+{
+    plan.raw_bytes = align_up(plan.raw_bytes + 64, 256);
+    plan.clean_bytes = align_up(plan.clean_bytes + 64, 256);
+    plan.coef_elems = align_up(plan.coef_elems + 64, 128);
+    plan.plane_bytes = align_up(plan.plane_bytes + 64, 256);
+}
+
+} // namespace b200jpeg

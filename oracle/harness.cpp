@@ -236,9 +236,10 @@ REFH_API int refh_decode(void* hd, int n, const unsigned char** data, const size
             break;
         }
         nvimgcodecImageInfo_t csinfo{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), 0};
-        int unchanged_channels = 3;
-        if (nvimgcodecCodeStreamGetImageInfo(cs[i], &csinfo) == NVIMGCODEC_STATUS_SUCCESS)
-            unchanged_channels = csinfo.num_planes;
+        // *_UNCHANGED means 3-channel RGB in the reference plugin even for gray streams
+        // (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:336-345,400-412), so the buffer always has 3 channels
+        const int unchanged_channels = 3;
+        nvimgcodecCodeStreamGetImageInfo(cs[i], &csinfo);
         nvimgcodecImageInfo_t info;
         fill_image_info(info, widths[i], heights[i], sample_formats[i], row_strides[i], buffer_kind, buffers[i], cuda_stream,
             unchanged_channels);

@@ -1,0 +1,53 @@
+"""tests/emu/emu.py -- TEST INFRASTRUCTURE: build + ctypes binding of the CPU emulation of the b200jpeg kernels."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+SO = os.path.join(HERE, "libb200jpeg_emu.so")
+CSRC = os.path.join(ROOT, "nvimagecodec_b200", "csrc")
+_lib = None
+
+
+def build(force=False):
+    srcs = [os.path.join(HERE, "emu_decode.cpp"), os.path.join(CSRC, "batch_plan.cpp"), os.path.join(CSRC, "jpeg_parse.cpp")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("jpeg_math.cuh", "device_types.h", "batch_plan.h", "jpeg_parse.h", "host_shim.h")]
+    if force or not os.path.exists(SO) or any(os.path.getmtime(d) > os.path.getmtime(SO) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fwrapv", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", SO] + srcs)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(SO)
+        L.emu_decode_batch.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p),
+                                       C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_void_p)]
+        _lib = L
+    return _lib
+
+
+def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=64, jacobi=True, want_coef=False, slots=None):
+    """dims: list of (w, h).  Returns (outputs, statuses, rounds, coefs)"""
+    n = len(datas)
+    fmts = fmt if isinstance(fmt, (list, tuple)) else [fmt] * n
+    outs, strides = [], []
+    for (w, h), f in zip(dims, fmts):
+        if f in (4, 6, 2):
+            outs.append(np.zeros((h, w, 3), np.uint8)); strides.append(3 * w)
+        elif f == 7:
+            outs.append(np.zeros((1, h, w), np.uint8)); strides.append(w)
+        else:
+            outs.append(np.zeros((3, h, w), np.uint8)); strides.append(w)
+    coefs = [np.zeros(s, np.int16) for s in slots] if want_coef else None
+    st = (C.c_int * n)()
+    rounds = C.c_int(0)
+    lib().emu_decode_batch(n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
+                           (C.c_void_p * n)(*[o.ctypes.data for o in outs]), (C.c_int64 * n)(*strides), (C.c_int * n)(*fmts),
+                           int(fancy), subseq_bytes, max_rounds, int(jacobi), st, C.byref(rounds),
+                           (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None)
+    return outs, list(st), rounds.value, coefs
