@@ -4,10 +4,18 @@ themselves are produced by libjpeg-turbo (PIL's bundled copy in bench.py, oracle
 import numpy as np
 
 
+try:
+    import cv2 as _cv2
+except Exception:  # pragma: no cover
+    _cv2 = None
+
+
 def _lowpass(rng, h, w, cell):
     """cheap band-limited noise: bilinear upsampling of a coarse random grid"""
     gh, gw = max(2, h // cell + 2), max(2, w // cell + 2)
     g = rng.standard_normal((gh, gw)).astype(np.float32)
+    if _cv2 is not None and h * w > 65536:
+        return _cv2.resize(g, (w, h), interpolation=_cv2.INTER_LINEAR)
     ys = np.linspace(0, gh - 1.001, h, dtype=np.float32)
     xs = np.linspace(0, gw - 1.001, w, dtype=np.float32)
     y0 = ys.astype(np.int32)

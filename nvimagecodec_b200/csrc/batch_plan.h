@@ -10,10 +10,6 @@
 
 namespace b200jpeg {
 
-constexpr int kIdctCta = 128;
-constexpr int kColorCta = 256;
-constexpr int kDcCta = 512;
-
 struct OutputSpec
 {
     void* buffer = nullptr; // device pointer the colour kernel writes to

@@ -1,0 +1,469 @@
+// decode_kernels.cu -- sm_100a kernels of the b200jpeg decode path and their launcher.
+//
+// Pipeline for one batch (all kernels are descriptor-driven: one launch covers every image of the batch, a CTA finds its
+// image with a binary search over a per-kernel prefix map):
+//   U1 k_unstuff_count   count kept bytes / RSTn markers per 4 KB chunk of entropy-coded data
+//   U2 k_unstuff_scan    per image: exclusive scan of the chunk counts, unstuffed length, segment table init
+//   U3 k_unstuff_write   compact: drop FF00 stuffing, FF fill, RSTn markers; record restart-segment starts
+//   H1 k_huff_sync x R   self-synchronising subsequence decode (no output), Jacobi rounds until nothing changes
+//   H2 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute write position per subsequence
+//   H3 k_huff_write      final decode pass: de-zigzagged int16 coefficients, MCU scan order
+//   D1 k_dc_scan         per image: DC prediction = segmented (restart interval) prefix sum per component
+//   I1 k_idct            dequantise + islow IDCT, one 8x8 block per thread, writes component planes
+//   C1 k_color           upsample (fancy / box) + YCbCr->RGB, 16 pixels per thread, 128-bit stores
+// The per-thread arithmetic lives in jpeg_math.cuh (shared with the CPU emulation used by the tests).
+#include <cuda_runtime.h>
+#include "decode_kernels.h"
+#include "jpeg_math.cuh"
+
+namespace b200jpeg {
+
+__device__ __forceinline__ int find_image(const uint32_t* __restrict__ map, int n, uint32_t cta)
+{
+    int lo = 0, hi = n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (map[mid] <= cta)
+            lo = mid;
+        else
+            hi = mid - 1;
+    }
+    return lo;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Unstuffing
+// ------------------------------------------------------------------------------------------------------------------
+struct ByteClass
+{
+    uint32_t keep;   // bit i: byte i is entropy-coded data
+    uint32_t marker; // bit i: byte i is the FF of an RSTn marker
+    uint32_t bad;    // any other marker
+};
+
+// Classify the 16 bytes at [base, base+16) of an image's raw scan data.
+__device__ __forceinline__ ByteClass classify16(const uint8_t* __restrict__ raw, uint32_t raw_len, uint32_t base, uint32_t w[4], uint32_t& next)
+{
+    if (base + 16 <= raw_len) {
+        const uint4 v = *reinterpret_cast<const uint4*>(raw + base);
+        w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+    } else {
+        w[0] = w[1] = w[2] = w[3] = 0;
+        for (uint32_t i = 0; base + i < raw_len && i < 16; ++i)
+            w[i >> 2] |= uint32_t(raw[base + i]) << (8 * (i & 3));
+    }
+    uint32_t prev = (base > 0 && base <= raw_len) ? raw[base - 1] : 0;
+    next = (base + 16 < raw_len) ? raw[base + 16] : 0;
+    ByteClass c{0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t cur = (w[i >> 2] >> (8 * (i & 3))) & 255u;
+        const uint32_t nx = (i < 15) ? ((w[(i + 1) >> 2] >> (8 * ((i + 1) & 3))) & 255u) : next;
+        const bool in = base + i < raw_len;
+        const bool has_next = base + i + 1 < raw_len;
+        bool remove = false;
+        if (cur == 0x00 && prev == 0xFF)
+            remove = true;
+        else if (cur == 0xFF && nx == 0xFF)
+            remove = true;
+        else if (cur == 0xFF && nx >= 0xD0 && nx <= 0xD7) {
+            remove = true;
+            if (in)
+                c.marker |= 1u << i;
+        } else if (cur >= 0xD0 && cur <= 0xD7 && prev == 0xFF)
+            remove = true;
+        else if (cur == 0xFF && nx != 0 && has_next)
+            c.bad = 1;
+        if (in && !remove)
+            c.keep |= 1u << i;
+        prev = cur;
+    }
+    return c;
+}
+
+__global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_count(BatchDev b)
+{
+    const int img = find_image(b.cta_map_unstuff, b.num_images, blockIdx.x);
+    const ImageDesc& im = b.images[img];
+    const uint32_t chunk = blockIdx.x - b.cta_map_unstuff[img];
+    const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
+    uint32_t w[4], next;
+    ByteClass c{0, 0, 0};
+    if (base < im.raw_len)
+        c = classify16(b.raw + im.raw_off, im.raw_len, base, w, next);
+    uint32_t kept = __popc(c.keep), markers = __popc(c.marker);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        kept += __shfl_down_sync(0xFFFFFFFFu, kept, o);
+        markers += __shfl_down_sync(0xFFFFFFFFu, markers, o);
+    }
+    __shared__ uint32_t s_k[kUnstuffThreads / 32], s_m[kUnstuffThreads / 32];
+    if ((threadIdx.x & 31) == 0) {
+        s_k[threadIdx.x >> 5] = kept;
+        s_m[threadIdx.x >> 5] = markers;
+    }
+    if (c.bad)
+        atomicOr(&b.states[img].error, kErrBadMarker);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t k = 0, m = 0;
+#pragma unroll
+        for (int i = 0; i < kUnstuffThreads / 32; ++i) {
+            k += s_k[i];
+            m += s_m[i];
+        }
+        b.chunk_counts[im.chunk_first + chunk] = uint64_t(k) | (uint64_t(m) << 32);
+    }
+}
+
+// one warp per image
+__global__ void __launch_bounds__(32) k_unstuff_scan(BatchDev b)
+{
+    const int img = blockIdx.x;
+    const ImageDesc& im = b.images[img];
+    const uint32_t lane = threadIdx.x;
+    uint64_t carry = 0;
+    for (uint32_t c0 = 0; c0 < im.chunk_count; c0 += 32) {
+        const uint32_t c = c0 + lane;
+        const uint64_t v = c < im.chunk_count ? b.chunk_counts[im.chunk_first + c] : 0;
+        uint64_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= uint32_t(o))
+                inc += t;
+        }
+        if (c < im.chunk_count)
+            b.chunk_counts[im.chunk_first + c] = carry + inc - v;
+        carry += __shfl_sync(0xFFFFFFFFu, inc, 31);
+    }
+    const uint32_t clean_len = uint32_t(carry), markers = uint32_t(carry >> 32);
+    uint32_t* S = b.seg_start + im.seg_first;
+    for (uint32_t g = lane; g <= uint32_t(im.num_segments); g += 32)
+        S[g] = g == 0 ? 0u : clean_len; // U3 overwrites [1 .. markers]
+    if (lane == 0) {
+        b.states[img].clean_len = clean_len;
+        b.states[img].marker_count = markers;
+        if (markers != uint32_t(im.num_segments - 1))
+            atomicOr(&b.states[img].error, kErrBadMarker);
+    }
+}
+
+__global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
+{
+    const int img = find_image(b.cta_map_unstuff, b.num_images, blockIdx.x);
+    const ImageDesc& im = b.images[img];
+    const uint32_t chunk = blockIdx.x - b.cta_map_unstuff[img];
+    const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
+    uint32_t w[4] = {0, 0, 0, 0}, next = 0;
+    ByteClass c{0, 0, 0};
+    if (base < im.raw_len)
+        c = classify16(b.raw + im.raw_off, im.raw_len, base, w, next);
+    // block exclusive scan of (kept | markers << 16)
+    const uint32_t mine = uint32_t(__popc(c.keep)) | (uint32_t(__popc(c.marker)) << 16);
+    uint32_t inc = mine;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= uint32_t(o))
+            inc += t;
+    }
+    __shared__ uint32_t s_w[kUnstuffThreads / 32];
+    if (lane == 31)
+        s_w[warp] = inc;
+    __syncthreads();
+    uint32_t wpre = 0;
+#pragma unroll
+    for (int i = 0; i < kUnstuffThreads / 32; ++i)
+        if (i < int(warp))
+            wpre += s_w[i];
+    const uint32_t excl = wpre + inc - mine;
+    const uint64_t cb = b.chunk_counts[im.chunk_first + chunk];
+    uint32_t pos = uint32_t(cb) + (excl & 0xFFFFu);
+    uint32_t ord = uint32_t(cb >> 32) + (excl >> 16);
+    uint8_t* dst = b.clean + im.clean_off;
+    uint32_t* S = b.seg_start + im.seg_first;
+    uint32_t bad = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t cur = (w[i >> 2] >> (8 * (i & 3))) & 255u;
+        if (c.keep & (1u << i))
+            dst[pos++] = uint8_t(cur);
+        if (c.marker & (1u << i)) {
+            const uint32_t nx = (i < 15) ? ((w[(i + 1) >> 2] >> (8 * ((i + 1) & 3))) & 255u) : next;
+            if (ord + 1 < uint32_t(im.num_segments)) {
+                S[ord + 1] = pos;
+                if (nx != 0xD0u + (ord & 7u))
+                    bad = 1;
+            } else
+                bad = 1;
+            ++ord;
+        }
+    }
+    if (bad)
+        atomicOr(&b.states[img].error, kErrBadMarker);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Huffman: synchronisation rounds, slot scan, write pass
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
+{
+    const int img = find_image(b.cta_map_subseq, b.num_images, blockIdx.x);
+    const ImageDesc& im = b.images[img];
+    const uint32_t k = (blockIdx.x - b.cta_map_subseq[img]) * kSubseqCta + threadIdx.x;
+    const uint32_t t = im.subseq_first + k;
+    const uint32_t clean_len = b.states[img].clean_len;
+    const bool idle = uint64_t(k) * uint32_t(b.subseq_bits) >= uint64_t(clean_len) * 8u;
+    SubseqState s;
+    unsigned long long E;
+    if (round == 0) {
+        if (idle) {
+            b.sub_exit[t] = b.sub_entry[t] = (unsigned long long)clean_len * 8u;
+            b.sub_rec[t] = 0;
+            return;
+        }
+        s.p = k * uint32_t(b.subseq_bits);
+        s.slot = 0;
+        s.n = 0;
+        s.abs = (k == 0);
+        E = s.p;
+    } else {
+        if (idle || k == 0)
+            return;
+        E = b.sub_exit[t - 1];
+        if (E == b.sub_entry[t])
+            return;
+        s.p = uint32_t(E);
+        s.slot = uint32_t(E >> 32);
+        s.n = 0;
+        s.abs = false;
+    }
+    decode_subsequence<false>(b, im, &b.states[img], k, clean_len, s);
+    b.sub_exit[t] = (unsigned long long)s.p | ((unsigned long long)s.slot << 32);
+    b.sub_entry[t] = E;
+    b.sub_rec[t] = (s.n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
+    if (round > 0)
+        atomicAdd(&b.redo_counter[round], 1u);
+}
+
+// segmented-scan combine: a = earlier prefix, x = later element; bit31 = "absolute" flag
+__device__ __forceinline__ uint32_t seg_combine(uint32_t a, uint32_t x) { return (x & 0x80000000u) ? x : a + x; }
+
+constexpr int kScanThreads = 256;
+__global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
+{
+    const int img = blockIdx.x;
+    const ImageDesc& im = b.images[img];
+    const uint32_t count = im.subseq_cta_count * kSubseqCta;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ uint32_t s_w[kScanThreads / 32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0)
+        s_carry = 0x80000000u;
+    __syncthreads();
+    for (uint32_t c0 = 0; c0 < count; c0 += kScanThreads) {
+        const uint32_t c = c0 + threadIdx.x;
+        uint32_t v = c < count ? b.sub_rec[im.subseq_first + c] : 0u;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, v, o);
+            if (lane >= uint32_t(o))
+                v = seg_combine(tprev, v);
+        }
+        if (lane == 31)
+            s_w[warp] = v;
+        __syncthreads();
+        uint32_t pre = s_carry;
+        for (int i = 0; i < int(warp); ++i)
+            pre = seg_combine(pre, s_w[i]);
+        v = seg_combine(pre, v);
+        if (c < count)
+            b.sub_abs[im.subseq_first + c] = v;
+        __syncthreads();
+        if (threadIdx.x == kScanThreads - 1)
+            s_carry = v;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
+{
+    const int img = find_image(b.cta_map_subseq, b.num_images, blockIdx.x);
+    const ImageDesc& im = b.images[img];
+    const uint32_t k = (blockIdx.x - b.cta_map_subseq[img]) * kSubseqCta + threadIdx.x;
+    const uint32_t t = im.subseq_first + k;
+    const uint32_t clean_len = b.states[img].clean_len;
+    if (uint64_t(k) * uint32_t(b.subseq_bits) >= uint64_t(clean_len) * 8u)
+        return;
+    SubseqState s;
+    if (k == 0) {
+        s.p = 0;
+        s.slot = 0;
+        s.n = 0;
+    } else {
+        const unsigned long long E = b.sub_exit[t - 1];
+        if (E != b.sub_entry[t])
+            atomicOr(&b.states[img].error, kErrNotConverged);
+        s.p = uint32_t(E);
+        s.slot = uint32_t(E >> 32);
+        s.n = b.sub_abs[t - 1] & 0x7FFFFFFFu;
+    }
+    s.abs = true;
+    decode_subsequence<true>(b, im, &b.states[img], k, clean_len, s);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// DC prediction: per image, segmented (restart interval) inclusive scan of per-MCU DC-difference sums per component.
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
+{
+    const int img = blockIdx.x;
+    const ImageDesc& im = b.images[img];
+    const uint32_t mcus = uint32_t(im.mcus_x) * uint32_t(im.mcus_y);
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int NW = kDcCta / 32;
+    __shared__ int s_v[NW][3];
+    __shared__ int s_f[NW];
+    __shared__ int s_carry[3];
+    if (threadIdx.x < 3)
+        s_carry[threadIdx.x] = 0;
+    __syncthreads();
+    int16_t* coef = b.coef + im.coef_off;
+    const uint32_t ri = im.restart_interval ? uint32_t(im.restart_interval) : 0xFFFFFFFFu;
+    for (uint32_t m0 = 0; m0 < mcus; m0 += kDcCta) {
+        const uint32_t m = m0 + threadIdx.x;
+        int d[kMaxBlocksPerMcu];
+        int v0 = 0, v1 = 0, v2 = 0;
+        int flag = 0;
+        if (m < mcus) {
+            for (int j = 0; j < im.bpm; ++j) {
+                d[j] = coef[(uint64_t(m) * im.bpm + j) * 64];
+                const int c = im.blk_comp[j];
+                if (c == 0) v0 += d[j];
+                else if (c == 1) v1 += d[j];
+                else v2 += d[j];
+            }
+            flag = (m % ri == 0) ? 1 : 0;
+        }
+        const int own0 = v0, own1 = v1, own2 = v2;
+        // warp inclusive segmented scan
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t0 = __shfl_up_sync(0xFFFFFFFFu, v0, o), t1 = __shfl_up_sync(0xFFFFFFFFu, v1, o),
+                      t2 = __shfl_up_sync(0xFFFFFFFFu, v2, o), tf = __shfl_up_sync(0xFFFFFFFFu, flag, o);
+            if (lane >= uint32_t(o)) {
+                if (!flag) {
+                    v0 += t0;
+                    v1 += t1;
+                    v2 += t2;
+                }
+                flag |= tf;
+            }
+        }
+        if (lane == 31) {
+            s_v[warp][0] = v0;
+            s_v[warp][1] = v1;
+            s_v[warp][2] = v2;
+            s_f[warp] = flag;
+        }
+        __syncthreads();
+        // prefix over preceding warps (and the carry of earlier iterations)
+        int p0 = s_carry[0], p1 = s_carry[1], p2 = s_carry[2];
+        for (int i = 0; i < int(warp); ++i) {
+            if (s_f[i]) {
+                p0 = s_v[i][0];
+                p1 = s_v[i][1];
+                p2 = s_v[i][2];
+            } else {
+                p0 += s_v[i][0];
+                p1 += s_v[i][1];
+                p2 += s_v[i][2];
+            }
+        }
+        if (!flag) {
+            v0 += p0;
+            v1 += p1;
+            v2 += p2;
+        }
+        // v = inclusive DC totals through this MCU; predictor at MCU start = v - own
+        if (m < mcus) {
+            int pred[3] = {v0 - own0, v1 - own1, v2 - own2};
+            for (int j = 0; j < im.bpm; ++j) {
+                const int c = im.blk_comp[j];
+                pred[c] += d[j];
+                coef[(uint64_t(m) * im.bpm + j) * 64] = int16_t(pred[c]);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == kDcCta - 1) {
+            s_carry[0] = v0;
+            s_carry[1] = v1;
+            s_carry[2] = v2;
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// IDCT and colour
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
+{
+    const int img = find_image(b.cta_map_idct, b.num_images, blockIdx.x);
+    const ImageDesc& im = b.images[img];
+    idct_thread(b, im, (blockIdx.x - b.cta_map_idct[img]) * kIdctCta + threadIdx.x);
+}
+
+__global__ void __launch_bounds__(kColorCta) k_color(BatchDev b)
+{
+    const int img = find_image(b.cta_map_color, b.num_images, blockIdx.x);
+    const ImageDesc& im = b.images[img];
+    color_thread(b, im, (blockIdx.x - b.cta_map_color[img]) * kColorCta + threadIdx.x);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Launcher
+// ------------------------------------------------------------------------------------------------------------------
+int launch_unstuff(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
+{
+    k_unstuff_count<<<d.unstuff_ctas, kUnstuffThreads, 0, st>>>(b);
+    k_unstuff_scan<<<d.num_images, 32, 0, st>>>(b);
+    k_unstuff_write<<<d.unstuff_ctas, kUnstuffThreads, 0, st>>>(b);
+    return 3;
+}
+
+int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int first_round, int num_rounds)
+{
+    for (int r = first_round; r < first_round + num_rounds; ++r)
+        k_huff_sync<<<d.subseq_ctas, kSubseqCta, 0, st>>>(b, r);
+    return num_rounds;
+}
+
+int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
+{
+    k_subseq_scan<<<d.num_images, kScanThreads, 0, st>>>(b);
+    k_huff_write<<<d.subseq_ctas, kSubseqCta, 0, st>>>(b);
+    return 2;
+}
+
+int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
+{
+    k_dc_scan<<<d.num_images, kDcCta, 0, st>>>(b);
+    return 1;
+}
+
+int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
+{
+    k_idct<<<d.idct_ctas, kIdctCta, 0, st>>>(b);
+    return 1;
+}
+
+int launch_color(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
+{
+    k_color<<<d.color_ctas, kColorCta, 0, st>>>(b);
+    return 1;
+}
+
+} // namespace b200jpeg

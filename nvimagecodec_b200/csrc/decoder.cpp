@@ -1,0 +1,471 @@
+// decoder.cpp -- host side of the b200jpeg batch decoder: header parsing, batch planning, pinned staging, H2D, kernel
+// launches on the decoder's own stream, status read-back.  Mirrors the role of DecoderImpl::decodeBatch in the reference
+// (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:444-490) with the plumbing pattern of the reference's batched GPU
+// plugin (extensions/nvjpeg/hw_decoder.cpp:492-680): gather bitstreams, one batched launch sequence, sync, report.
+#include "decoder.h"
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+#include "../../include/b200jpeg.h"
+
+namespace b200jpeg {
+
+namespace {
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+#define B2J_CUDA(call)                                                                                         \
+    do {                                                                                                       \
+        cudaError_t e__ = (call);                                                                              \
+        if (e__ != cudaSuccess) {                                                                              \
+            std::fprintf(stderr, "b200jpeg: CUDA error %s at %s:%d\n", cudaGetErrorString(e__), __FILE__, __LINE__); \
+            return B200JPEG_STATUS_CUDA_ERROR;                                                                 \
+        }                                                                                                      \
+    } while (0)
+} // namespace
+
+DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
+{
+    DecoderOptions o;
+    if (!options)
+        return o;
+    std::string s(options);
+    size_t pos = 0;
+    while (pos < s.size()) {
+        while (pos < s.size() && s[pos] == ' ')
+            ++pos;
+        size_t end = s.find(' ', pos);
+        if (end == std::string::npos)
+            end = s.size();
+        std::string tok = s.substr(pos, end - pos);
+        pos = end;
+        if (tok.empty())
+            continue;
+        std::string module, name = tok, value;
+        const size_t colon = tok.find(':');
+        if (colon != std::string::npos) {
+            module = tok.substr(0, colon);
+            name = tok.substr(colon + 1);
+        }
+        const size_t eq = name.find('=');
+        if (eq == std::string::npos)
+            continue;
+        value = name.substr(eq + 1);
+        name = name.substr(0, eq);
+        if (!module.empty() && module != plugin_id)
+            continue;
+        if (name == "fancy_upsampling")
+            o.fancy_upsampling = std::atoi(value.c_str()) != 0;
+        else if (name == "subseq_bytes") {
+            int v = std::atoi(value.c_str());
+            if (v >= 32 && v <= 4096 && (v % 4) == 0)
+                o.subseq_bytes = v;
+        } else if (name == "sync_rounds")
+            o.sync_rounds = std::max(0, std::atoi(value.c_str()));
+        else if (name == "copy_threads")
+            o.copy_threads = std::max(1, std::atoi(value.c_str()));
+        else if (name == "profile")
+            o.profile = std::atoi(value.c_str()) != 0;
+    }
+    return o;
+}
+
+Decoder::Decoder(int device_id, const DecoderOptions& opt) : device_(device_id), opt_(opt) {}
+
+Decoder::~Decoder()
+{
+    if (device_ >= 0)
+        cudaSetDevice(device_);
+    DevBuf* dbufs[] = {&d_raw_, &d_clean_, &d_coef_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
+        &d_rec_, &d_abs_, &d_redo_, &d_out_};
+    for (DevBuf* b : dbufs)
+        if (b->p)
+            cudaFree(b->p);
+    DevBuf* hbufs[] = {&h_raw_, &h_meta_, &h_states_};
+    for (DevBuf* b : hbufs)
+        if (b->p)
+            cudaFreeHost(b->p);
+    if (ev_in_)
+        cudaEventDestroy(ev_in_);
+    for (cudaEvent_t e : ev_stage_)
+        if (e)
+            cudaEventDestroy(e);
+    if (stream_)
+        cudaStreamDestroy(stream_);
+}
+
+int Decoder::init()
+{
+    int count = 0;
+    B2J_CUDA(cudaGetDeviceCount(&count));
+    if (device_ < 0 || device_ >= count)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    B2J_CUDA(cudaSetDevice(device_));
+    cudaDeviceProp prop;
+    B2J_CUDA(cudaGetDeviceProperties(&prop, device_));
+    if (prop.major != 10) {
+        std::fprintf(stderr, "b200jpeg: device %d is sm_%d%d; this library only carries sm_100a code\n", device_, prop.major, prop.minor);
+        return B200JPEG_STATUS_ARCH_MISMATCH;
+    }
+    B2J_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+    B2J_CUDA(cudaEventCreateWithFlags(&ev_in_, cudaEventDisableTiming));
+    if (opt_.profile)
+        for (cudaEvent_t& e : ev_stage_)
+            B2J_CUDA(cudaEventCreate(&e));
+    adaptive_rounds_ = opt_.sync_rounds > 0 ? opt_.sync_rounds : 8;
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+int Decoder::ensure(DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap)
+        return 0;
+    if (b.p) {
+        B2J_CUDA(cudaStreamSynchronize(stream_));
+        B2J_CUDA(cudaFree(b.p));
+        scratch_bytes_ -= b.cap;
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    const size_t want = align_up(bytes + bytes / 8, 1 << 20);
+    if (cudaMalloc(&b.p, want) != cudaSuccess) {
+        cudaGetLastError();
+        return B200JPEG_STATUS_ALLOC_FAILED;
+    }
+    b.cap = want;
+    scratch_bytes_ += want;
+    return 0;
+}
+
+int Decoder::ensure_pinned(DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap)
+        return 0;
+    if (b.p) {
+        B2J_CUDA(cudaStreamSynchronize(stream_));
+        B2J_CUDA(cudaFreeHost(b.p));
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    const size_t want = align_up(bytes + bytes / 8, 1 << 20);
+    if (cudaHostAlloc(&b.p, want, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return B200JPEG_STATUS_ALLOC_FAILED;
+    }
+    b.cap = want;
+    return 0;
+}
+
+int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses)
+{
+    ready_ = false;
+    if (n < 0 || (n > 0 && (!data || !sizes || !outs || !statuses)))
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    B2J_CUDA(cudaSetDevice(device_));
+    batch_size_ = n;
+    parsed_.resize(n);
+    pre_status_.assign(n, B200JPEG_STATUS_SUCCESS);
+    planned_to_batch_.clear();
+    host_outs_.clear();
+
+    PlanOptions popt;
+    popt.subseq_bytes = opt_.subseq_bytes;
+    popt.fancy_upsampling = opt_.fancy_upsampling;
+    plan_begin(plan_, popt);
+    size_t dev_out_bytes = 0;
+    std::vector<size_t> out_offsets;
+    for (int i = 0; i < n; ++i) {
+        const ParseResult r = parse_jpeg(data[i], sizes[i], parsed_[i]);
+        if (r != PARSE_OK) {
+            pre_status_[i] = B200JPEG_STATUS_BAD_JPEG;
+            continue;
+        }
+        if (!is_supported(parsed_[i]) || !resolve_format(outs[i].format, parsed_[i].ncomp)) {
+            pre_status_[i] = B200JPEG_STATUS_UNSUPPORTED;
+            continue;
+        }
+        if (!outs[i].buffer) {
+            pre_status_[i] = B200JPEG_STATUS_INVALID_PARAMETER;
+            continue;
+        }
+        OutputSpec os;
+        os.buffer = outs[i].buffer;
+        os.row_stride = outs[i].row_stride;
+        os.format = outs[i].format;
+        if (outs[i].on_host) {
+            const int fmt = resolve_format(outs[i].format, parsed_[i].ncomp);
+            const bool interleaved = (fmt == 4 || fmt == 6);
+            HostOutput ho;
+            ho.image = int(plan_.images.size());
+            ho.host = outs[i].buffer;
+            ho.host_stride = outs[i].row_stride;
+            ho.row_bytes = size_t(parsed_[i].width) * (interleaved ? 3 : 1);
+            ho.rows = size_t(parsed_[i].height) * (interleaved ? 1 : (fmt == 7 ? 1 : 3));
+            ho.dev_off = dev_out_bytes;
+            const size_t pitch = align_up(ho.row_bytes, 16);
+            dev_out_bytes += align_up(pitch * ho.rows, 256);
+            host_outs_.push_back(ho);
+            os.buffer = nullptr; // patched below once d_out_ is allocated
+            os.row_stride = int64_t(pitch);
+        }
+        plan_add_image(plan_, parsed_[i], os, popt);
+        planned_to_batch_.push_back(i);
+    }
+    plan_finish(plan_);
+    for (int i = 0; i < n; ++i)
+        statuses[i] = pre_status_[i];
+    const int m = int(plan_.images.size());
+    if (m == 0) {
+        ready_ = true;
+        return B200JPEG_STATUS_SUCCESS;
+    }
+
+    // ---- scratch ----
+    int rc = 0;
+    if ((rc = ensure(d_raw_, plan_.raw_bytes)) || (rc = ensure(d_clean_, plan_.clean_bytes)) ||
+        (rc = ensure(d_coef_, plan_.coef_elems * sizeof(int16_t))) || (rc = ensure(d_planes_, plan_.plane_bytes)) ||
+        (rc = ensure(d_states_, sizeof(ImageState) * m)) || (rc = ensure(d_seg_, sizeof(uint32_t) * (plan_.total_segs + 1))) ||
+        (rc = ensure(d_chunks_, sizeof(uint64_t) * plan_.total_chunks)) || (rc = ensure(d_exit_, 8 * size_t(plan_.total_subseq))) ||
+        (rc = ensure(d_entry_, 8 * size_t(plan_.total_subseq))) || (rc = ensure(d_rec_, 4 * size_t(plan_.total_subseq))) ||
+        (rc = ensure(d_abs_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_redo_, 4 * kMaxSyncRounds)) ||
+        (dev_out_bytes && (rc = ensure(d_out_, dev_out_bytes))))
+        return rc;
+    for (const HostOutput& ho : host_outs_)
+        plan_.images[ho.image].out = static_cast<uint8_t*>(d_out_.p) + ho.dev_off;
+
+    // ---- metadata block: descriptors, tables, CTA maps -> one pinned buffer, one H2D ----
+    const size_t off_img = 0;
+    const size_t off_huff = align_up(off_img + sizeof(ImageDesc) * m, 256);
+    const size_t off_quant = align_up(off_huff + sizeof(DevHuffTable) * plan_.huff.size(), 256);
+    const size_t off_m0 = align_up(off_quant + plan_.quant.size() * sizeof(uint16_t), 256);
+    const size_t map_bytes = align_up(sizeof(uint32_t) * (m + 1), 256);
+    const size_t meta_bytes = off_m0 + 4 * map_bytes;
+    if ((rc = ensure(d_meta_, meta_bytes)) || (rc = ensure_pinned(h_meta_, meta_bytes)) ||
+        (rc = ensure_pinned(h_raw_, plan_.raw_bytes)) ||
+        (rc = ensure_pinned(h_states_, sizeof(ImageState) * m + 4 * kMaxSyncRounds)))
+        return rc;
+    uint8_t* hm = static_cast<uint8_t*>(h_meta_.p);
+    std::memcpy(hm + off_img, plan_.images.data(), sizeof(ImageDesc) * m);
+    std::memcpy(hm + off_huff, plan_.huff.data(), sizeof(DevHuffTable) * plan_.huff.size());
+    std::memcpy(hm + off_quant, plan_.quant.data(), plan_.quant.size() * sizeof(uint16_t));
+    std::memcpy(hm + off_m0 + 0 * map_bytes, plan_.map_unstuff.data(), sizeof(uint32_t) * (m + 1));
+    std::memcpy(hm + off_m0 + 1 * map_bytes, plan_.map_subseq.data(), sizeof(uint32_t) * (m + 1));
+    std::memcpy(hm + off_m0 + 2 * map_bytes, plan_.map_idct.data(), sizeof(uint32_t) * (m + 1));
+    std::memcpy(hm + off_m0 + 3 * map_bytes, plan_.map_color.data(), sizeof(uint32_t) * (m + 1));
+
+    // ---- entropy-coded bytes -> pinned staging (parallel memcpy) ----
+    uint8_t* hr = static_cast<uint8_t*>(h_raw_.p);
+    auto copy_range = [&](int lo, int hi) {
+        for (int i = lo; i < hi; ++i) {
+            const ImageDesc& im = plan_.images[i];
+            const int bi = planned_to_batch_[i];
+            std::memcpy(hr + im.raw_off, data[bi] + parsed_[bi].scan_offset, im.raw_len);
+        }
+    };
+    const int nthreads = std::min(opt_.copy_threads, std::max(1, int(plan_.raw_bytes >> 20)));
+    if (nthreads <= 1) {
+        copy_range(0, m);
+    } else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; ++t)
+            th.emplace_back(copy_range, m * t / nthreads, m * (t + 1) / nthreads);
+        for (auto& x : th)
+            x.join();
+    }
+    B2J_CUDA(cudaMemcpyAsync(d_meta_.p, h_meta_.p, meta_bytes, cudaMemcpyHostToDevice, stream_));
+    B2J_CUDA(cudaMemcpyAsync(d_raw_.p, h_raw_.p, plan_.raw_bytes, cudaMemcpyHostToDevice, stream_));
+
+    uint8_t* dm = static_cast<uint8_t*>(d_meta_.p);
+    dev_ = BatchDev{};
+    dev_.images = reinterpret_cast<const ImageDesc*>(dm + off_img);
+    dev_.states = static_cast<ImageState*>(d_states_.p);
+    dev_.num_images = m;
+    dev_.raw = static_cast<const uint8_t*>(d_raw_.p);
+    dev_.clean = static_cast<uint8_t*>(d_clean_.p);
+    dev_.huff = reinterpret_cast<const DevHuffTable*>(dm + off_huff);
+    dev_.quant = reinterpret_cast<const uint16_t*>(dm + off_quant);
+    dev_.seg_start = static_cast<uint32_t*>(d_seg_.p);
+    dev_.chunk_counts = static_cast<uint64_t*>(d_chunks_.p);
+    dev_.sub_exit = static_cast<unsigned long long*>(d_exit_.p);
+    dev_.sub_entry = static_cast<unsigned long long*>(d_entry_.p);
+    dev_.sub_rec = static_cast<uint32_t*>(d_rec_.p);
+    dev_.sub_abs = static_cast<uint32_t*>(d_abs_.p);
+    dev_.redo_counter = static_cast<uint32_t*>(d_redo_.p);
+    dev_.coef = static_cast<int16_t*>(d_coef_.p);
+    dev_.planes = static_cast<uint8_t*>(d_planes_.p);
+    dev_.cta_map_unstuff = reinterpret_cast<const uint32_t*>(dm + off_m0 + 0 * map_bytes);
+    dev_.cta_map_subseq = reinterpret_cast<const uint32_t*>(dm + off_m0 + 1 * map_bytes);
+    dev_.cta_map_idct = reinterpret_cast<const uint32_t*>(dm + off_m0 + 2 * map_bytes);
+    dev_.cta_map_color = reinterpret_cast<const uint32_t*>(dm + off_m0 + 3 * map_bytes);
+    dev_.cta_map_dc = nullptr;
+    dev_.subseq_bits = plan_.subseq_bits;
+    dims_.num_images = m;
+    dims_.unstuff_ctas = plan_.map_unstuff.back();
+    dims_.subseq_ctas = plan_.map_subseq.back();
+    dims_.idct_ctas = plan_.map_idct.back();
+    dims_.color_ctas = plan_.map_color.back();
+    ready_ = true;
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+int Decoder::launch_all(int first_round, int rounds, bool redo)
+{
+    const int m = dims_.num_images;
+    const bool prof = opt_.profile;
+    auto mark = [&](int i) {
+        if (prof)
+            cudaEventRecord(ev_stage_[i], stream_);
+    };
+    mark(kStageUnstuff);
+    if (!redo) {
+        B2J_CUDA(cudaMemsetAsync(d_states_.p, 0, sizeof(ImageState) * m, stream_));
+        B2J_CUDA(cudaMemsetAsync(d_redo_.p, 0, 4 * kMaxSyncRounds, stream_));
+        B2J_CUDA(cudaMemsetAsync(d_clean_.p, 0, plan_.clean_bytes, stream_));
+        stat_launches_ += launch_unstuff(dev_, dims_, stream_);
+    }
+    mark(kStageSync);
+    stat_launches_ += launch_huff_sync(dev_, dims_, stream_, first_round, rounds);
+    mark(kStageWrite);
+    B2J_CUDA(cudaMemsetAsync(d_coef_.p, 0, plan_.coef_elems * sizeof(int16_t), stream_));
+    stat_launches_ += launch_huff_write(dev_, dims_, stream_);
+    mark(kStageDc);
+    stat_launches_ += launch_dc(dev_, dims_, stream_);
+    mark(kStageIdct);
+    stat_launches_ += launch_idct(dev_, dims_, stream_);
+    mark(kStageColor);
+    stat_launches_ += launch_color(dev_, dims_, stream_);
+    mark(kNumStages);
+    stage_valid_ = prof;
+    B2J_CUDA(cudaGetLastError());
+    B2J_CUDA(cudaMemcpyAsync(h_states_.p, d_states_.p, sizeof(ImageState) * m, cudaMemcpyDeviceToHost, stream_));
+    B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(h_states_.p) + sizeof(ImageState) * m, d_redo_.p, 4 * kMaxSyncRounds,
+        cudaMemcpyDeviceToHost, stream_));
+    return 0;
+}
+
+int Decoder::run(cudaStream_t user_stream, int32_t* statuses)
+{
+    if (!ready_)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    B2J_CUDA(cudaSetDevice(device_));
+    for (int i = 0; i < batch_size_; ++i)
+        statuses[i] = pre_status_[i];
+    const int m = dims_.num_images;
+    if (m == 0)
+        return B200JPEG_STATUS_SUCCESS;
+    // order after whatever the caller still has in flight on the stream that owns the output buffers
+    B2J_CUDA(cudaEventRecord(ev_in_, user_stream));
+    B2J_CUDA(cudaStreamWaitEvent(stream_, ev_in_, 0));
+    stat_launches_ = 0;
+    stat_reruns_ = 0;
+    int first = 0, rounds = std::min(adaptive_rounds_, kMaxSyncRounds);
+    int total_rounds = 0;
+    ImageState* hs = static_cast<ImageState*>(h_states_.p);
+    const uint32_t* redo = reinterpret_cast<const uint32_t*>(static_cast<uint8_t*>(h_states_.p) + sizeof(ImageState) * m);
+    bool redo_pass = false;
+    while (true) {
+        int rc = launch_all(first, rounds, redo_pass);
+        if (rc)
+            return rc;
+        B2J_CUDA(cudaStreamSynchronize(stream_));
+        total_rounds = first + rounds;
+        bool not_converged = false;
+        for (int i = 0; i < m; ++i)
+            if (hs[i].error & kErrNotConverged)
+                not_converged = true;
+        if (!not_converged || total_rounds + 8 > kMaxSyncRounds)
+            break;
+        // rare: more Jacobi rounds are needed. Clear the flags, keep the unstuffed data, continue the rounds.
+        for (int i = 0; i < m; ++i) {
+            hs[i].error &= ~kErrNotConverged;
+            hs[i].done_slots = 0;
+        }
+        B2J_CUDA(cudaMemcpyAsync(d_states_.p, hs, sizeof(ImageState) * m, cudaMemcpyHostToDevice, stream_));
+        first = total_rounds;
+        rounds = 8;
+        redo_pass = true;
+        ++stat_reruns_;
+    }
+    stat_rounds_ = total_rounds;
+    if (opt_.sync_rounds == 0) {
+        // adapt: first round (>=1) in which no subsequence had to be re-decoded, plus one round of margin
+        int needed = total_rounds;
+        for (int r = 1; r < total_rounds; ++r)
+            if (redo[r] == 0) {
+                needed = r;
+                break;
+            }
+        adaptive_rounds_ = std::max(adaptive_rounds_ - 1, std::min(needed + 2, kMaxSyncRounds));
+    }
+    // host-memory outputs: copy back
+    for (const HostOutput& ho : host_outs_) {
+        const size_t pitch = align_up(ho.row_bytes, 16);
+        B2J_CUDA(cudaMemcpy2DAsync(ho.host, size_t(ho.host_stride), static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch, ho.row_bytes,
+            ho.rows, cudaMemcpyDeviceToHost, stream_));
+    }
+    if (!host_outs_.empty())
+        B2J_CUDA(cudaStreamSynchronize(stream_));
+    for (int i = 0; i < m; ++i) {
+        const int bi = planned_to_batch_[i];
+        if (hs[i].error || hs[i].done_slots != plan_.images[i].total_slots)
+            statuses[bi] = B200JPEG_STATUS_CORRUPT_STREAM;
+    }
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+void Decoder::get_stats(uint64_t* s) const
+{
+    s[0] = stat_launches_;
+    s[1] = stat_rounds_;
+    s[2] = 0;
+    for (const ImageDesc& im : plan_.images)
+        s[2] += im.raw_len;
+    s[3] = plan_.total_blocks;
+    s[4] = plan_.total_subseq;
+    s[5] = scratch_bytes_;
+    s[6] = stat_reruns_;
+    s[7] = plan_.out_bytes;
+}
+
+int Decoder::get_stage_times(float* ms, int n)
+{
+    if (!opt_.profile || !stage_valid_)
+        return -1;
+    for (int i = 0; i < n && i < kNumStages; ++i)
+        if (cudaEventElapsedTime(&ms[i], ev_stage_[i], ev_stage_[i + 1]) != cudaSuccess)
+            return -1;
+    return kNumStages;
+}
+
+int64_t Decoder::debug_fetch(int what, int image, int comp, void* dst, size_t cap)
+{
+    int planned = -1;
+    for (size_t i = 0; i < planned_to_batch_.size(); ++i)
+        if (planned_to_batch_[i] == image)
+            planned = int(i);
+    if (planned < 0 || !dst)
+        return -1;
+    const ImageDesc& im = plan_.images[planned];
+    const void* src = nullptr;
+    size_t bytes = 0;
+    if (what == 0) {
+        src = static_cast<int16_t*>(d_coef_.p) + im.coef_off;
+        bytes = size_t(im.total_slots) * 2;
+    } else if (what == 1) {
+        if (comp < 0 || comp >= im.ncomp)
+            return -1;
+        src = static_cast<uint8_t*>(d_planes_.p) + im.plane_off[comp];
+        bytes = size_t(im.plane_pitch[comp]) * im.hib[comp] * 8;
+    } else if (what == 2) {
+        src = static_cast<uint8_t*>(d_clean_.p) + im.clean_off;
+        bytes = static_cast<ImageState*>(h_states_.p)[planned].clean_len;
+    } else
+        return -1;
+    if (bytes > cap)
+        return -2;
+    if (cudaSetDevice(device_) != cudaSuccess || cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost) != cudaSuccess)
+        return -3;
+    return int64_t(bytes);
+}
+
+} // namespace b200jpeg

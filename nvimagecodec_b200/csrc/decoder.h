@@ -1,0 +1,95 @@
+// decoder.h -- batch decoder object behind b200jpeg_decode_* (host scheduling, staging, launches).
+#pragma once
+#include <cuda_runtime_api.h>
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+#include "batch_plan.h"
+#include "decode_kernels.h"
+
+namespace b200jpeg {
+
+struct DecoderOptions
+{
+    bool fancy_upsampling = true; // reference default (libjpeg_turbo_decoder.cpp:250-276)
+    int subseq_bytes = 256;
+    int sync_rounds = 0; // 0 = automatic
+    int copy_threads = 4;
+    bool profile = false; // record CUDA events between the kernel stages (b200jpeg_decoder_get_stage_times)
+};
+
+// Parse "name=value" tokens; tokens may be prefixed "b200jpeg_decoder:" or ":"; tokens addressed to another plugin are
+// ignored (same grammar as the reference, extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:250-276).
+DecoderOptions parse_decoder_options(const char* options, const char* plugin_id);
+
+struct DevBuf
+{
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct HostOutput // an output the caller wants in host memory
+{
+    int image = -1;      // planned image index
+    void* host = nullptr;
+    int64_t host_stride = 0;
+    size_t dev_off = 0;
+    size_t row_bytes = 0;
+    size_t rows = 0;
+};
+
+class Decoder
+{
+  public:
+    Decoder(int device_id, const DecoderOptions& opt);
+    ~Decoder();
+    int init(); // b200jpegStatus_t
+
+    struct OutputDesc
+    {
+        void* buffer;
+        int64_t row_stride;
+        int format;
+        int on_host;
+    };
+
+    int prepare(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses);
+    int run(cudaStream_t user_stream, int32_t* statuses);
+    void get_stats(uint64_t* s8) const;
+    int get_stage_times(float* ms, int n); // per Stage, last run
+    int64_t debug_fetch(int what, int image, int comp, void* dst, size_t cap);
+    int device() const { return device_; }
+
+  private:
+    int ensure(DevBuf& b, size_t bytes);
+    int ensure_pinned(DevBuf& b, size_t bytes);
+    int launch_all(int first_round, int rounds, bool redo);
+
+    int device_;
+    DecoderOptions opt_;
+    cudaStream_t stream_ = nullptr;
+    cudaEvent_t ev_in_ = nullptr;
+    cudaEvent_t ev_stage_[kNumStages + 1] = {};
+    bool stage_valid_ = false;
+    bool ready_ = false;
+
+    BatchPlan plan_;
+    std::vector<ParsedJpeg> parsed_;
+    std::vector<int> planned_to_batch_; // planned image -> index in the caller's batch
+    std::vector<int32_t> pre_status_;   // per batch entry status decided at prepare time
+    int batch_size_ = 0;
+    std::vector<HostOutput> host_outs_;
+
+    DevBuf d_raw_, d_clean_, d_coef_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_redo_,
+        d_out_;
+    DevBuf h_raw_, h_meta_, h_states_;
+    BatchDev dev_{};
+    LaunchDims dims_{};
+    size_t scratch_bytes_ = 0;
+
+    uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_reruns_ = 0;
+    int adaptive_rounds_ = 0;
+};
+
+} // namespace b200jpeg

@@ -15,6 +15,9 @@ constexpr int kSubseqCta = 128;       // threads per CTA in the subsequence kern
 constexpr int kUnstuffThreads = 256;  // threads per CTA in the unstuffing kernels
 constexpr int kUnstuffBytesPerThread = 16;
 constexpr int kChunkBytes = kUnstuffThreads * kUnstuffBytesPerThread; // raw bytes per unstuff CTA
+constexpr int kIdctCta = 128;        // threads per CTA, one 8x8 block per thread
+constexpr int kColorCta = 256;       // threads per CTA, 16 pixels per thread
+constexpr int kDcCta = 512;          // threads per CTA, one MCU per thread per iteration
 constexpr int kMaxBlocksPerMcu = 6;   // luma up to 2x2 + Cb + Cr
 
 // Decode table derived from one DHT table (reference: d_derived_tbl, external/libjpeg-turbo/jdhuff.h:27-51 and

@@ -1,0 +1,190 @@
+"""Python host mirror of the reference's `nvimgcodec.Decoder` for the JPEG path (reference python/decoder.cpp:31-58 ctor,
+:148-252 batch decode, :283-326 defaults; python/image.cpp for Image).  Same names and argument meaning:
+
+    dec = Decoder(device_id=0, options=":fancy_upsampling=0")
+    img = dec.decode(jpeg_bytes)              # -> Image or None
+    imgs = dec.decode([bytes, bytes, ...])    # -> list of Image / None
+
+Outputs are device-resident interleaved RGB uint8 (H, W, 3) exactly as the reference's Python layer allocates them
+(python/decoder.cpp:148-225: STRIDED_DEVICE, I_RGB).  PyTorch is used only to own device memory and streams.
+All decode work happens in libb200jpeg.so (CUDA, sm_100a); a missing library or GPU raises."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _capi
+
+
+class Image:
+    """Device image, mirrors nvimgcodec.Image (python/image.cpp:434-481): shape/width/height/dtype,
+    __cuda_array_interface__, cpu(), cuda(), plus torch() for zero-copy hand-off."""
+
+    def __init__(self, tensor):
+        self._t = tensor
+
+    @property
+    def shape(self):
+        return tuple(self._t.shape)
+
+    @property
+    def height(self):
+        return self._t.shape[0]
+
+    @property
+    def width(self):
+        return self._t.shape[1]
+
+    @property
+    def ndim(self):
+        return self._t.dim()
+
+    @property
+    def dtype(self):
+        return np.uint8
+
+    @property
+    def __cuda_array_interface__(self):
+        return self._t.__cuda_array_interface__
+
+    def __dlpack__(self, stream=None):
+        return self._t.__dlpack__(stream=stream)
+
+    def __dlpack_device__(self):
+        return self._t.__dlpack_device__()
+
+    def torch(self):
+        return self._t
+
+    def cuda(self):
+        return self
+
+    def cpu(self):
+        return self._t.cpu().numpy()
+
+
+_FORMATS = {"rgb": _capi.FMT_I_RGB, "bgr": _capi.FMT_I_BGR, "gray": _capi.FMT_P_Y, "planar_rgb": _capi.FMT_P_RGB,
+            "planar_bgr": _capi.FMT_P_BGR}
+
+
+class Decoder:
+    def __init__(self, device_id=0, max_num_cpu_threads=0, backend_kinds=None, options=":fancy_upsampling=0"):
+        if not torch.cuda.is_available():
+            raise RuntimeError("b200jpeg needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.device_id = torch.cuda.current_device() if device_id is None or device_id < 0 else device_id
+        self._h = C.c_void_p()
+        rc = _capi.lib().b200jpeg_decoder_create(C.byref(self._h), self.device_id, options.encode())
+        if rc != 0:
+            raise RuntimeError("b200jpeg_decoder_create: %s" % _capi.status_string(rc))
+        self.last_statuses = []
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _capi.lib().b200jpeg_decoder_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- low level: caller-provided buffers -------------------------------------------------------------------
+    def _outputs(self, buffers, strides, formats, on_host):
+        n = len(buffers)
+        outs = (_capi.Output * n)()
+        for i in range(n):
+            outs[i].buffer = buffers[i]
+            outs[i].row_stride = strides[i]
+            outs[i].format = formats[i]
+            outs[i].on_host = int(on_host)
+        return outs
+
+    def decode_into(self, datas, buffers, strides, formats, on_host=False, cuda_stream=0):
+        """decode a batch into raw pointers (device pointers, or host pointers with on_host=True) -> status list"""
+        n = len(datas)
+        st = (C.c_int32 * n)()
+        rc = _capi.lib().b200jpeg_decode_batch(self._h, n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
+                                               self._outputs(buffers, strides, formats, on_host), C.c_void_p(cuda_stream), st)
+        if rc != 0:
+            raise RuntimeError("b200jpeg_decode_batch: %s" % _capi.status_string(rc))
+        self.last_statuses = list(st)
+        return self.last_statuses
+
+    def prepare(self, datas, buffers, strides, formats, on_host=False):
+        n = len(datas)
+        st = (C.c_int32 * n)()
+        self._keep = (datas, (C.c_char_p * n)(*datas))
+        rc = _capi.lib().b200jpeg_decode_prepare(self._h, n, self._keep[1], (C.c_size_t * n)(*[len(d) for d in datas]),
+                                                 self._outputs(buffers, strides, formats, on_host), st)
+        if rc != 0:
+            raise RuntimeError("b200jpeg_decode_prepare: %s" % _capi.status_string(rc))
+        self._n = n
+        return list(st)
+
+    def run(self, cuda_stream=0):
+        st = (C.c_int32 * self._n)()
+        rc = _capi.lib().b200jpeg_decode_run(self._h, C.c_void_p(cuda_stream), st)
+        if rc != 0:
+            raise RuntimeError("b200jpeg_decode_run: %s" % _capi.status_string(rc))
+        self.last_statuses = list(st)
+        return self.last_statuses
+
+    def stats(self):
+        s = (C.c_uint64 * 8)()
+        _capi.lib().b200jpeg_decoder_get_stats(self._h, s)
+        keys = ("launches", "sync_rounds", "scan_bytes", "blocks", "subsequences", "scratch_bytes", "reruns", "out_bytes")
+        return dict(zip(keys, [int(v) for v in s]))
+
+    STAGES = ("unstuff", "huff_sync", "huff_write", "dc_scan", "idct", "color")
+
+    def stage_times(self):
+        """per-stage device ms of the last run (needs option profile=1) or None"""
+        ms = (C.c_float * 6)()
+        if _capi.lib().b200jpeg_decoder_get_stage_times(self._h, ms, 6) < 0:
+            return None
+        return dict(zip(self.STAGES, [float(v) for v in ms]))
+
+    def debug_fetch(self, what, image, component, nbytes, dtype=np.uint8):
+        buf = np.zeros(nbytes, np.uint8)
+        got = _capi.lib().b200jpeg_debug_fetch(self._h, what, image, component, buf.ctypes.data, nbytes)
+        if got < 0:
+            raise RuntimeError("b200jpeg_debug_fetch failed: %d" % got)
+        return buf[:got].view(dtype)
+
+    # ---- reference-style API ----------------------------------------------------------------------------------
+    def decode(self, data, params=None, cuda_stream=0, color="rgb"):
+        single = isinstance(data, (bytes, bytearray, memoryview, np.ndarray))
+        datas = [data] if single else list(data)
+        datas = [d.tobytes() if isinstance(d, np.ndarray) else bytes(d) for d in datas]
+        fmt = _FORMATS[color]
+        dev = torch.device("cuda", self.device_id)
+        tensors, bufs, strides, ok = [], [], [], []
+        for d in datas:
+            try:
+                info = _capi.parse_header(d)
+            except ValueError:
+                tensors.append(None)
+                continue
+            if fmt in (_capi.FMT_I_RGB, _capi.FMT_I_BGR):
+                t = torch.empty((info.height, info.width, 3), dtype=torch.uint8, device=dev)
+                stride = info.width * 3
+            elif fmt == _capi.FMT_P_Y:
+                t = torch.empty((info.height, info.width, 1), dtype=torch.uint8, device=dev)
+                stride = info.width
+            else:
+                t = torch.empty((3, info.height, info.width), dtype=torch.uint8, device=dev)
+                stride = info.width
+            tensors.append(t)
+        live = [i for i, t in enumerate(tensors) if t is not None]
+        if live:
+            torch.cuda.current_stream(dev).synchronize() if cuda_stream == 0 else None
+            st = self.decode_into([datas[i] for i in live], [tensors[i].data_ptr() for i in live],
+                                  [tensors[i].shape[1] * tensors[i].shape[2] if tensors[i].dim() == 3 and fmt in (
+                                      _capi.FMT_I_RGB, _capi.FMT_I_BGR, _capi.FMT_P_Y) else tensors[i].shape[2] for i in live],
+                                  [fmt] * len(live), False, cuda_stream)
+            for i, s in zip(live, st):
+                if s != 0:
+                    tensors[i] = None
+        imgs = [Image(t) if t is not None else None for t in tensors]
+        return imgs[0] if single else imgs

@@ -1,0 +1,198 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the compiled reference (oracle/_ref) and the
+plain-C port, bit-exact on RGB bytes, DCT coefficients and intermediate planes."""
+import numpy as np
+import pytest
+
+import util
+from util import make_jpeg, port, ref
+
+pytestmark = pytest.mark.gpu
+
+FMT_REF = {4: ref.I_RGB, 6: ref.I_BGR, 3: ref.P_RGB, 5: ref.P_BGR, 7: ref.P_Y}
+
+
+@pytest.fixture(scope="module")
+def torch_mod():
+    import torch
+    return torch
+
+
+@pytest.fixture(scope="module")
+def refdec():
+    s = ref.Session.shared()
+    return {1: s.decoder(options=":fancy_upsampling=1"), 0: s.decoder(options=":fancy_upsampling=0")}
+
+
+def gpu_decode(torch, datas, fmt=4, options=":fancy_upsampling=1", pad_stride=0, want_decoder=False):
+    from nvimagecodec_b200.decoder import Decoder
+    dec = Decoder(0, options=options)
+    outs, ptrs, strides = [], [], []
+    for d in datas:
+        i = port.info(d)
+        w, h = i["width"], i["height"]
+        if fmt in (4, 6):
+            stride = w * 3 + pad_stride
+            t = torch.zeros((h, stride), dtype=torch.uint8, device="cuda")
+        elif fmt == 7:
+            stride = w + pad_stride
+            t = torch.zeros((h, stride), dtype=torch.uint8, device="cuda")
+        else:
+            stride = w + pad_stride
+            t = torch.zeros((3 * h, stride), dtype=torch.uint8, device="cuda")
+        outs.append(t)
+        ptrs.append(t.data_ptr())
+        strides.append(stride)
+    st = dec.decode_into(datas, ptrs, strides, [fmt] * len(datas))
+    torch.cuda.synchronize()
+    res = []
+    for d, t in zip(datas, outs):
+        i = port.info(d)
+        w, h = i["width"], i["height"]
+        a = t.cpu().numpy()
+        if fmt in (4, 6):
+            res.append(a[:, :w * 3].reshape(h, w, 3))
+        elif fmt == 7:
+            res.append(a[:, :w].reshape(1, h, w))
+        else:
+            res.append(a[:, :w].reshape(3, h, w))
+    if want_decoder:
+        return res, st, dec
+    dec.close()
+    return res, st
+
+
+def diagnose(dec, datas, idx):
+    """stage-wise comparison for image idx of the last batch -> string"""
+    d = datas[idx]
+    info = port.info(d)
+    msgs = []
+    hdr = __import__("nvimagecodec_b200").parse_header(d)
+    scan = d[hdr.scan_offset:hdr.scan_offset + hdr.scan_bytes]
+    clean_ref, marks = util.unstuff_reference(scan)
+    clean = dec.debug_fetch(2, idx, 0, len(scan) + 64).tobytes()
+    msgs.append("clean stream: %s (len %d vs %d)" % ("OK" if clean == clean_ref else "MISMATCH", len(clean), len(clean_ref)))
+    want = util.mcu_order_coefficients(d)
+    got = dec.debug_fetch(0, idx, 0, want.size * 2, np.int16)
+    if got.size == want.size:
+        bad = np.nonzero(got != want)[0]
+        msgs.append("coefficients: %d mismatches%s" % (bad.size, "" if not bad.size else " first at slot %d (block %d)" % (bad[0], bad[0] // 64)))
+    else:
+        msgs.append("coefficients: size %d vs %d" % (got.size, want.size))
+    for c in range(info["ncomp"]):
+        wp = port.plane(d, c)
+        gp = dec.debug_fetch(1, idx, c, wp.size).reshape(wp.shape)
+        msgs.append("plane %d: %d mismatches" % (c, int((gp != wp).sum())))
+    return "; ".join(msgs)
+
+
+CASES = [
+    # w, h, samp, quality, restart_interval, gray
+    (227, 149, (2, 2), 75, 0, False),
+    (64, 48, (1, 1), 90, 0, False),
+    (131, 77, (2, 1), 85, 0, False),
+    (131, 77, (1, 2), 85, 0, False),
+    (333, 211, (2, 2), 90, 5, False),
+    (17, 9, (2, 2), 90, 0, False),
+    (3, 5, (2, 2), 90, 0, False),
+    (2, 2, (2, 1), 90, 0, False),
+    (1, 1, (1, 1), 90, 0, False),
+    (640, 426, (2, 2), 75, 0, False),
+    (100, 100, (1, 1), 95, 7, False),
+    (500, 375, (2, 2), 75, 1, False),
+    (800, 600, (2, 1), 90, 50, False),
+    (201, 99, (1, 1), 85, 0, True),
+    (1920, 1080, (2, 2), 90, 0, False),
+    (1280, 720, (2, 2), 50, 0, False),
+]
+
+
+@pytest.mark.parametrize("fancy", [1, 0])
+def test_mixed_batch_rgb_bit_exact(torch_mod, refdec, fancy):
+    datas = [make_jpeg(1000 + i, w, h, samp, q, restart_interval=ri, gray=g) for i, (w, h, samp, q, ri, g) in enumerate(CASES)]
+    got, st, dec = gpu_decode(torch_mod, datas, 4, ":fancy_upsampling=%d" % fancy, want_decoder=True)
+    want, rst, _ = refdec[fancy].decode_host(datas)
+    assert all(s == ref.STATUS_SUCCESS for s in rst)
+    problems = []
+    for i, (g, w) in enumerate(zip(got, want)):
+        if st[i] != 0 or not np.array_equal(g, w):
+            problems.append("case %d %s status %d diff %d | %s" % (i, CASES[i], st[i], int((g != w).sum()), diagnose(dec, datas, i)))
+    print(dec.stats())
+    dec.close()
+    assert not problems, "\n".join(problems)
+
+
+@pytest.mark.parametrize("fmt", [6, 3, 5, 7])
+def test_output_formats(torch_mod, refdec, fmt):
+    datas = [make_jpeg(2000 + i, w, h, samp, q, restart_interval=ri, gray=g) for i, (w, h, samp, q, ri, g) in enumerate(CASES[:14])]
+    got, st = gpu_decode(torch_mod, datas, fmt, pad_stride=13)
+    want, rst, _ = refdec[1].decode_host(datas, fmt=FMT_REF[fmt])
+    for i, (g, w) in enumerate(zip(got, want)):
+        assert st[i] == 0, (i, st[i])
+        assert np.array_equal(g, w), (i, CASES[i], fmt)
+
+
+def test_coefficients_bit_exact(torch_mod):
+    datas = [make_jpeg(3000 + i, w, h, samp, q, restart_interval=ri, gray=g) for i, (w, h, samp, q, ri, g) in enumerate(CASES[:14])]
+    got, st, dec = gpu_decode(torch_mod, datas, 4, want_decoder=True)
+    for i, d in enumerate(datas):
+        want = util.mcu_order_coefficients(d)
+        g = dec.debug_fetch(0, i, 0, want.size * 2, np.int16)
+        assert np.array_equal(g, want), (i, CASES[i])
+    dec.close()
+
+
+def test_subsequence_sizes_and_rounds(torch_mod, refdec):
+    datas = [make_jpeg(4000 + i, 640, 480, (2, 2), 90) for i in range(4)] + [make_jpeg(4100, 1920, 1080, (2, 2), 90)]
+    want, _, _ = refdec[1].decode_host(datas)
+    for opts in (":fancy_upsampling=1 :subseq_bytes=64", ":fancy_upsampling=1 :subseq_bytes=128 :sync_rounds=2",
+                 ":fancy_upsampling=1 :subseq_bytes=1024", "b200jpeg_decoder:subseq_bytes=512 other_plugin:subseq_bytes=32"):
+        got, st = gpu_decode(torch_mod, datas, 4, opts)
+        for i, (g, w) in enumerate(zip(got, want)):
+            assert st[i] == 0 and np.array_equal(g, w), (opts, i)
+
+
+def test_bad_and_unsupported_streams(torch_mod):
+    good = make_jpeg(5000, 320, 240)
+    prog = make_jpeg(5001, 320, 240, progressive=True)
+    arith = make_jpeg(5002, 320, 240, arith=True)
+    truncated = good[:len(good) // 2]
+    garbage = b"not a jpeg at all"
+    datas = [good, prog, arith, truncated, garbage, good]
+    from nvimagecodec_b200.decoder import Decoder
+    dec = Decoder(0, options=":fancy_upsampling=1")
+    outs = [torch_mod.zeros((240, 960), dtype=torch_mod.uint8, device="cuda") for _ in datas]
+    st = dec.decode_into(datas, [o.data_ptr() for o in outs], [960] * len(datas), [4] * len(datas))
+    assert st[0] == 0 and st[5] == 0
+    assert st[1] == 3 and st[2] == 3      # UNSUPPORTED -> the framework falls back to the CPU decoder
+    assert st[3] == 4                      # CORRUPT_STREAM (entropy data ends early)
+    assert st[4] == 2                      # BAD_JPEG
+    assert torch_mod.equal(outs[0], outs[5])
+    dec.close()
+
+
+def test_host_output_buffers(torch_mod, refdec):
+    datas = [make_jpeg(6000 + i, 400 + 3 * i, 300 + i, (2, 2), 80) for i in range(5)]
+    from nvimagecodec_b200.decoder import Decoder
+    dec = Decoder(0, options=":fancy_upsampling=1")
+    outs = [np.zeros((300 + i, (400 + 3 * i) * 3), np.uint8) for i in range(5)]
+    st = dec.decode_into(datas, [o.ctypes.data for o in outs], [o.shape[1] for o in outs], [4] * 5, on_host=True)
+    want, _, _ = refdec[1].decode_host(datas)
+    for i in range(5):
+        assert st[i] == 0
+        assert np.array_equal(outs[i].reshape(want[i].shape), want[i])
+    dec.close()
+
+
+def test_python_mirror_api(torch_mod, refdec):
+    from nvimagecodec_b200 import Decoder
+    datas = [make_jpeg(7000 + i, 320, 200 + i) for i in range(3)]
+    dec = Decoder(device_id=0)  # reference Python default: ":fancy_upsampling=0"
+    imgs = dec.decode(datas)
+    want, _, _ = refdec[0].decode_host(datas)
+    for im, w in zip(imgs, want):
+        assert im is not None and im.shape == w.shape
+        assert np.array_equal(im.cpu(), w)
+        assert im.__cuda_array_interface__["shape"] == w.shape
+    one = dec.decode(datas[0])
+    assert np.array_equal(one.cpu(), want[0])
+    assert dec.decode(b"garbage") is None
