@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the b200jpeg decode path (BASELINE.json: decoded Mpixel/s & images/s, batched JPEG
+1080p 4:2:0).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--batch 64]
+
+One step = one pass of the hot path over one batch: 64 synthetic 1920x1080 4:2:0 q90 baseline JPEGs (no restart
+markers) -> interleaved RGB uint8 (BASELINE.json configs[0]/[1] shape: the configuration the metric is quoted on).
+  value : whole-job Mpixel/s with the compressed bytes already resident in HBM (b200jpeg_decode_run only: every kernel)
+  e2e   : the same metric through the C ABI call a plugin user makes, HOST jpeg bytes in -> HOST pixels out
+          (b200jpeg_decode_batch with on_host outputs: parse, pinned staging, H2D, kernels, D2H inside the timed region)
+  roofline     : dominant kernel stage, algorithmic bytes / CUDA-event time vs the measured HBM peak
+  cpu_baseline : the reference's own CPU path (libjpeg_turbo_ext through nvimgcodecDecoderDecode, oracle/_ref build)
+N>1: one process per GPU (torchrun), the batch is replicated per rank (weak scaling), no collective on the data path.
+"""
+import argparse
+import io
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, QUALITY = 1920, 1080, 90
+
+
+def _encode_one(seed):
+    from PIL import Image
+    from nvimagecodec_b200.corpus import synth_image
+    b = io.BytesIO()
+    Image.fromarray(synth_image(seed, W, H)).save(b, "JPEG", quality=QUALITY, subsampling="4:2:0", optimize=False)
+    return b.getvalue()
+
+
+def make_corpus(n):
+    """n seeded synthetic 1080p JPEGs; encoded by PIL's bundled libjpeg-turbo (byte-identical to the reference's
+    libjpeg-turbo 3.0.3 jpeg_compress with the same parameters -- checked in tests/test_oracle.py)"""
+    from concurrent.futures import ProcessPoolExecutor
+    import multiprocessing as mp
+    workers = max(1, min(16, (os.cpu_count() or 1)))
+    with ProcessPoolExecutor(max_workers=workers, mp_context=mp.get_context("spawn")) as ex:
+        return list(ex.map(_encode_one, [1000 + i for i in range(n)]))
+
+
+class ClockSampler:
+    FIELDS = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.samples = []
+        self.stop = False
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.thread.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons}
+
+
+def hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def reference_decode_all(datas, reps, threads=0):
+    """reference CPU path: nvimgcodecDecoderDecode -> libjpeg_turbo_ext on the thread-pool executor, host RGB out"""
+    from oracle import ref
+    sess = ref.Session.shared()
+    dec = sess.decoder(device_id=ref.DEVICE_CPU_ONLY, backends=ref.BACKEND_CPU_ONLY, num_threads=threads, options=":fancy_upsampling=1")
+    outs, st, secs = dec.decode_host(datas, fmt=ref.I_RGB, reps=reps, dims=[(W, H)] * len(datas))
+    assert all(s == ref.STATUS_SUCCESS for s in st)
+    return outs, secs
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    n = args.batch
+    datas = make_corpus(n)
+    cores = os.cpu_count() or 1
+    sample = min(n, max(8, cores * 2)) if cores < 32 else n  # bounded sample of the same workload per step
+    sub = datas[:sample]
+    _, warm = reference_decode_all(sub, max(1, min(args.warmup, 2)))
+    _, secs = reference_decode_all(sub, args.steps)
+    total = float(sum(secs))
+    mpix = sample * W * H / 1e6
+    value = mpix * args.steps / total
+    line = {
+        "impl": "reference", "metric": "decoded_mpixel_per_s", "value": value, "unit": "Mpixel/s", "images_per_s": sample * args.steps / total,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C1: %dx 1920x1080 4:2:0 q90 baseline JPEG, no restart markers -> interleaved RGB u8" % n,
+                   "reference_path": "nvimgcodecDecoderDecode -> libjpeg_turbo_ext (libjpeg-turbo 3.0.3, WITH_SIMD=0: no nasm in image) "
+                                     "on the default thread-pool executor, host buffers"},
+        "cpu_baseline": {"value": value, "unit": "Mpixel/s", "cores": cores, "kind": "reference",
+                         "sample": "%d of the %d images per step, %d steps, all %d host threads" % (sample, n, args.steps, cores)},
+        "e2e": {"value": value, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--options", default=":fancy_upsampling=1 :profile=1")
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    datas = make_corpus(args.batch)  # before CUDA init (spawned workers)
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the b200jpeg path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from nvimagecodec_b200.decoder import Decoder
+
+    n = args.batch
+    dec = Decoder(local_rank, options=args.options)
+    outs = [torch.empty((H, W * 3), dtype=torch.uint8, device=dev) for _ in range(n)]
+    ptrs = [o.data_ptr() for o in outs]
+    strides = [W * 3] * n
+    fmts = [4] * n
+    stream = torch.cuda.current_stream(dev).cuda_stream
+
+    # ---- parity gate + CPU baseline (rank 0): the same bytes through the reference's CPU path ----
+    st = dec.decode_into(datas, ptrs, strides, fmts, False, stream)
+    assert all(s == 0 for s in st), st
+    cpu_baseline = None
+    if rank == 0 and not args.skip_cpu_baseline:
+        cores = os.cpu_count() or 1
+        reps = 3 if cores >= 16 else 1
+        want, secs = reference_decode_all(datas, reps)
+        for i in range(n):
+            got = outs[i].cpu().numpy().reshape(H, W, 3)
+            if not np.array_equal(got, want[i]):
+                raise SystemExit("PARITY FAILURE on image %d: GPU output differs from the reference decoder" % i)
+        best = min(secs)
+        cpu_baseline = {"value": n * W * H / 1e6 / best, "unit": "Mpixel/s", "cores": cores, "kind": "reference",
+                        "images_per_s": n / best,
+                        "sample": "all %d images of the batch, best of %d passes, nvimgcodec default executor with %d threads, "
+                                  "libjpeg-turbo 3.0.3 WITH_SIMD=0" % (n, reps, cores)}
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- value: device-resident inputs, kernels only ----
+    st = dec.prepare(datas, ptrs, strides, fmts, False)
+    assert all(s == 0 for s in st)
+    for _ in range(args.warmup):
+        dec.run(stream)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage_acc = {}
+    launches = 0
+    with ClockSampler(local_rank) as clocks:
+        e0.record()
+        for _ in range(args.steps):
+            st = dec.run(stream)
+            launches += dec.stats()["launches"]
+            for k, v in (dec.stage_times() or {}).items():
+                stage_acc[k] = stage_acc.get(k, 0.0) + v
+        e1.record()
+        barrier()
+    assert all(s == 0 for s in st)
+    ms_total = e0.elapsed_time(e1)
+    stats = dec.stats()
+
+    # ---- e2e: host JPEG bytes -> host RGB through the C ABI ----
+    houts = [torch.empty((H, W * 3), dtype=torch.uint8).pin_memory() for _ in range(n)]
+    hptrs = [o.data_ptr() for o in houts]
+    for _ in range(2):
+        dec.decode_into(datas, hptrs, strides, fmts, True, stream)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        st = dec.decode_into(datas, hptrs, strides, fmts, True, stream)
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    assert all(s == 0 for s in st)
+    if rank == 0:
+        assert torch.equal(houts[0], outs[0].cpu()), "host-output path differs from device-output path"
+
+    # ---- reduce over ranks (max time) ----
+    t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    mpix_step = n * W * H / 1e6 * world
+    ms_step = ms_total / args.steps
+    value = mpix_step / (ms_step / 1e3)
+    peak, peak_kind = hbm_peak()
+    # algorithmic bytes per stage for this batch: compressed bytes S, coefficients 128 B/block,
+    # planes 64 B/block, output bytes
+    S, blocks, out_b = stats["scan_bytes"], stats["blocks"], stats["out_bytes"]
+    alg = {"unstuff": 2 * S, "huff_sync": S, "huff_write": S + 128 * blocks, "dc_scan": 4 * blocks, "idct": 128 * blocks + 64 * blocks,
+           "color": 64 * blocks + out_b}
+    stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
+    dom = max(stage_ms, key=stage_ms.get) if stage_ms else None
+    roof = None
+    if dom:
+        achieved = alg[dom] / (stage_ms[dom] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "algorithmic_bytes": alg[dom], "ms": stage_ms[dom],
+                "pipeline": {"algorithmic_bytes": S + out_b, "achieved": (S + out_b) / (ms_step * 1e-3) / 1e9,
+                             "frac": (S + out_b) / (ms_step * 1e-3) / 1e9 / peak},
+                "stage_ms": stage_ms, "stage_frac": {k: alg[k] / (v * 1e-3) / 1e9 / peak for k, v in stage_ms.items() if v > 0},
+                "huffman_gbit_per_s": S * 8 / ((stage_ms.get("huff_sync", 0) + stage_ms.get("huff_write", 0)) * 1e-3) / 1e9}
+    line = {
+        "metric": "decoded_mpixel_per_s", "value": value, "unit": "Mpixel/s", "images_per_s": n * world / (ms_step / 1e3),
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C1: %dx 1920x1080 4:2:0 q90 baseline JPEG (%.0f KB avg), no restart markers -> interleaved RGB u8, "
+                               "fancy upsampling, per GPU" % (n, S / n / 1e3),
+                   "l2": "working set per step %.0f MB (coefficients+planes+output) > 126 MB L2, no explicit flush" %
+                         ((192 * blocks + out_b) / 1e6),
+                   "options": args.options, "sync_rounds": stats["sync_rounds"], "subsequences": stats["subsequences"],
+                   "parity": "bit-exact vs reference libjpeg_turbo_ext on all %d images before timing" % n},
+        "clocks": clocks.summary(),
+        "e2e": {"value": mpix_step / (e2e_ms / args.steps / 1e3), "unit": "Mpixel/s", "images_per_s": n * world / (e2e_ms / args.steps / 1e3),
+                "ms_per_step": e2e_ms / args.steps, "h2d_bytes_per_step": int(S), "d2h_bytes_per_step": int(out_b), "timing": "wall clock around "
+                "b200jpeg_decode_batch (synchronous), pinned host output buffers"},
+        "gpu_launches": int(launches),
+        "roofline": roof,
+        "cpu_baseline": cpu_baseline,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -377,7 +377,7 @@ int Decoder::run(cudaStream_t user_stream, int32_t* statuses)
             break;
         // rare: more Jacobi rounds are needed. Clear the flags, keep the unstuffed data, continue the rounds.
         for (int i = 0; i < m; ++i) {
-            hs[i].error &= ~kErrNotConverged;
+            hs[i].error &= kErrBadMarker; // everything else came from decoding with unsynchronised entry states
             hs[i].done_slots = 0;
         }
         B2J_CUDA(cudaMemcpyAsync(d_states_.p, hs, sizeof(ImageState) * m, cudaMemcpyHostToDevice, stream_));

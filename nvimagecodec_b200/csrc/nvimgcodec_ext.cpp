@@ -1,0 +1,329 @@
+// nvimgcodec_ext.cpp -- nvImageCodec extension module "b200jpeg_extension".
+//
+// Exports nvimgcodecExtensionModuleEntry (reference include/nvimgcodec.h:1356-1364) and registers
+//   * decoder  id "b200jpeg_decoder", codec "jpeg", backend NVIMGCODEC_BACKEND_KIND_GPU_ONLY, priority 50
+//   * encoder  id "b200jpeg_encoder", codec "jpeg", backend NVIMGCODEC_BACKEND_KIND_GPU_ONLY, priority 50
+// through the unchanged plugin ABI, so nvimgcodecDecoderDecode / nvimgcodecEncoderEncode, the registry's priority and
+// fallback logic (src/codec.cpp:119-124, src/decoder_worker.cpp:63-93,252-307) and the Python bindings pick them up as a
+// drop-in for the JPEG path.  Structure follows the reference's own plugins (extensions/libjpeg_turbo/libjpeg_turbo_ext.cpp:
+// 28-100 for registration, libjpeg_turbo_decoder.cpp:118-173 for the canDecode matrix, nvjpeg/hw_decoder.cpp:492-680 for
+// batched GPU plumbing, nvjpeg/cuda_encoder.cpp:284-396 for encode) -- the arithmetic is ours (libb200jpeg, CUDA sm_100a).
+// Anything outside the codec's scope is declined in canDecode/canEncode so the framework falls back to the next decoder
+// (libjpeg_turbo_ext, priority 300); there is no CPU fallback in here.
+#include <nvimgcodec.h>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+#include "../../include/b200jpeg.h"
+
+#ifndef NVIMGCODEC_VER
+#include "nvimgcodec_version.h"
+#endif
+
+namespace {
+
+constexpr float kPriority = 50.0f; // ahead of nvjpeg HW (100) / nvjpeg CUDA (200) / libjpeg_turbo (300) / opencv (400)
+const char* kDecoderId = "b200jpeg_decoder";
+const char* kEncoderId = "b200jpeg_encoder";
+
+void log_msg(const nvimgcodecFrameworkDesc_t* fw, nvimgcodecDebugMessageSeverity_t sev, const char* id, const std::string& msg)
+{
+    if (!fw || !fw->log)
+        return;
+    nvimgcodecDebugMessageData_t data{NVIMGCODEC_STRUCTURE_TYPE_DEBUG_MESSAGE_DATA, sizeof(nvimgcodecDebugMessageData_t), nullptr,
+        msg.c_str(), 0, nullptr, id, NVIMGCODEC_VER};
+    fw->log(fw->instance, sev, NVIMGCODEC_DEBUG_MESSAGE_CATEGORY_GENERAL, &data);
+}
+
+// Bytes of a code stream: zero-copy map when the io stream supports it, else read into `storage`
+// (idiom of extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:373-400).
+const uint8_t* stream_bytes(nvimgcodecIoStreamDesc_t* io, std::vector<uint8_t>& storage, size_t& size)
+{
+    size = 0;
+    if (!io || io->size(io->instance, &size) != NVIMGCODEC_STATUS_SUCCESS || size == 0)
+        return nullptr;
+    void* ptr = nullptr;
+    if (io->map && io->map(io->instance, &ptr, 0, size) == NVIMGCODEC_STATUS_SUCCESS && ptr)
+        return static_cast<const uint8_t*>(ptr);
+    storage.resize(size);
+    size_t got = 0;
+    if (io->seek(io->instance, 0, SEEK_SET) != NVIMGCODEC_STATUS_SUCCESS)
+        return nullptr;
+    if (io->read(io->instance, &got, storage.data(), size) != NVIMGCODEC_STATUS_SUCCESS || got != size)
+        return nullptr;
+    return storage.data();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Decoder
+// ---------------------------------------------------------------------------------------------------------------
+struct DecoderState
+{
+    const nvimgcodecFrameworkDesc_t* fw = nullptr;
+    const nvimgcodecExecutionParams_t* exec = nullptr;
+    b200jpegDecoder_t dec = nullptr;
+};
+
+nvimgcodecProcessingStatus_t check_target(const nvimgcodecImageInfo_t& info, const b200jpegStreamInfo_t& si,
+    const nvimgcodecDecodeParams_t* params)
+{
+    nvimgcodecProcessingStatus_t st = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+    const uint32_t planes = info.num_planes;
+    const uint32_t ch0 = info.plane_info[0].num_channels;
+    switch (info.sample_format) {
+    case NVIMGCODEC_SAMPLEFORMAT_I_RGB:
+    case NVIMGCODEC_SAMPLEFORMAT_I_BGR:
+    case NVIMGCODEC_SAMPLEFORMAT_I_UNCHANGED:
+        if (planes != 1)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_PLANES_UNSUPPORTED;
+        if (ch0 != 3)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_CHANNELS_UNSUPPORTED;
+        break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_RGB:
+    case NVIMGCODEC_SAMPLEFORMAT_P_BGR:
+    case NVIMGCODEC_SAMPLEFORMAT_P_UNCHANGED:
+        if (planes != 3)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_PLANES_UNSUPPORTED;
+        if (ch0 != 1)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_CHANNELS_UNSUPPORTED;
+        break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_Y:
+        if (planes != 1)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_PLANES_UNSUPPORTED;
+        if (ch0 != 1)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_CHANNELS_UNSUPPORTED;
+        break;
+    default: // P_YUV, unknown
+        st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_FORMAT_UNSUPPORTED;
+        break;
+    }
+    if (info.plane_info[0].sample_type != NVIMGCODEC_SAMPLE_DATA_TYPE_UINT8)
+        st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_TYPE_UNSUPPORTED;
+    if (params->enable_roi && info.region.ndim > 0)
+        st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED;
+    if (params->apply_exif_orientation && (info.orientation.flip_x || info.orientation.flip_y || info.orientation.rotated != 0))
+        st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
+    if (int(info.plane_info[0].width) != si.width || int(info.plane_info[0].height) != si.height)
+        st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED; // a cropped / resized target is not ours
+    if (info.buffer_kind != NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_DEVICE)
+        st |= NVIMGCODEC_PROCESSING_STATUS_BACKEND_UNSUPPORTED;
+    return st;
+}
+
+nvimgcodecStatus_t dec_can_decode(nvimgcodecDecoder_t decoder, nvimgcodecProcessingStatus_t* status, nvimgcodecCodeStreamDesc_t** css,
+    nvimgcodecImageDesc_t** imgs, int n, const nvimgcodecDecodeParams_t* params)
+{
+    if (!decoder || !status || !css || !imgs || !params)
+        return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    try {
+        std::vector<uint8_t> storage;
+        for (int i = 0; i < n; ++i) {
+            status[i] = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+            nvimgcodecJpegImageInfo_t jinfo{NVIMGCODEC_STRUCTURE_TYPE_JPEG_IMAGE_INFO, sizeof(nvimgcodecJpegImageInfo_t), nullptr};
+            nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), &jinfo};
+            css[i]->getImageInfo(css[i]->instance, &cs_info);
+            if (std::strcmp(cs_info.codec_name, "jpeg") != 0) {
+                status[i] = NVIMGCODEC_PROCESSING_STATUS_CODEC_UNSUPPORTED;
+                continue;
+            }
+            size_t size = 0;
+            const uint8_t* data = stream_bytes(css[i]->io_stream, storage, size);
+            b200jpegStreamInfo_t si;
+            if (!data || b200jpeg_parse_header(data, size, &si) != B200JPEG_STATUS_SUCCESS) {
+                status[i] = NVIMGCODEC_PROCESSING_STATUS_FAIL;
+                continue;
+            }
+            if (!si.supported) {
+                // progressive / arithmetic / lossless => ENCODING_UNSUPPORTED, everything else (CMYK, 4:1:1, 12-bit,
+                // multi-scan ...) => CODESTREAM_UNSUPPORTED; both send the sample to the next decoder
+                status[i] = (si.sof_marker != 0xC0 && si.sof_marker != 0xC1) ? NVIMGCODEC_PROCESSING_STATUS_ENCODING_UNSUPPORTED
+                                                                             : NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED;
+                continue;
+            }
+            nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+            imgs[i]->getImageInfo(imgs[i]->instance, &info);
+            status[i] = check_target(info, si, params);
+        }
+    } catch (...) {
+        return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+    }
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, nvimgcodecCodeStreamDesc_t** css, nvimgcodecImageDesc_t** imgs, int n,
+    const nvimgcodecDecodeParams_t* params)
+{
+    auto* st = reinterpret_cast<DecoderState*>(decoder);
+    if (!st || !css || !imgs || n < 0)
+        return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    std::vector<char> reported(n, 0);
+    auto report = [&](int i, nvimgcodecProcessingStatus_t s) {
+        if (!reported[i]) { // imageReady exactly once per sample (src/processing_results.cpp:104-115)
+            reported[i] = 1;
+            imgs[i]->imageReady(imgs[i]->instance, s);
+        }
+    };
+    try {
+        std::vector<std::vector<uint8_t>> storage(n);
+        std::vector<const uint8_t*> data(n, nullptr);
+        std::vector<size_t> sizes(n, 0);
+        std::vector<b200jpegOutput_t> outs(n);
+        cudaStream_t user_stream = nullptr;
+        for (int i = 0; i < n; ++i) {
+            data[i] = stream_bytes(css[i]->io_stream, storage[i], sizes[i]);
+            nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+            imgs[i]->getImageInfo(imgs[i]->instance, &info);
+            outs[i].buffer = info.buffer;
+            outs[i].row_stride = int64_t(info.plane_info[0].row_stride);
+            outs[i].format = int32_t(info.sample_format);
+            outs[i].on_host = info.buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST ? 1 : 0;
+            if (i == 0)
+                user_stream = info.cuda_stream;
+            if (!data[i]) {
+                static const uint8_t empty[2] = {0, 0};
+                data[i] = empty;
+                sizes[i] = 0;
+            }
+        }
+        std::vector<int32_t> res(n, B200JPEG_STATUS_INTERNAL_ERROR);
+        const int rc = b200jpeg_decode_batch(st->dec, n, data.data(), sizes.data(), outs.data(), user_stream, res.data());
+        // b200jpeg_decode_batch returns with the device work complete, so every user stream may consume the outputs
+        for (int i = 0; i < n; ++i) {
+            nvimgcodecProcessingStatus_t ps = NVIMGCODEC_PROCESSING_STATUS_FAIL;
+            if (rc == B200JPEG_STATUS_SUCCESS) {
+                switch (res[i]) {
+                case B200JPEG_STATUS_SUCCESS: ps = NVIMGCODEC_PROCESSING_STATUS_SUCCESS; break;
+                case B200JPEG_STATUS_UNSUPPORTED: ps = NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED; break;
+                case B200JPEG_STATUS_BAD_JPEG:
+                case B200JPEG_STATUS_CORRUPT_STREAM: ps = NVIMGCODEC_PROCESSING_STATUS_IMAGE_CORRUPTED; break;
+                default: ps = NVIMGCODEC_PROCESSING_STATUS_FAIL; break;
+                }
+            }
+            if (css[i]->io_stream && css[i]->io_stream->unmap && storage[i].empty() && sizes[i])
+                css[i]->io_stream->unmap(css[i]->io_stream->instance, const_cast<uint8_t*>(data[i]), sizes[i]);
+            report(i, ps);
+        }
+        if (rc != B200JPEG_STATUS_SUCCESS) {
+            log_msg(st->fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR, kDecoderId, std::string("decode batch failed: ") + b200jpeg_status_string(rc));
+            return rc == B200JPEG_STATUS_CUDA_ERROR ? NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR : NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+        }
+    } catch (...) {
+        for (int i = 0; i < n; ++i)
+            report(i, NVIMGCODEC_PROCESSING_STATUS_FAIL);
+        return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+    }
+    (void)params;
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t dec_destroy(nvimgcodecDecoder_t decoder)
+{
+    auto* st = reinterpret_cast<DecoderState*>(decoder);
+    if (!st)
+        return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    if (st->dec)
+        b200jpeg_decoder_destroy(st->dec);
+    delete st;
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+struct Extension;
+nvimgcodecStatus_t dec_create(void* instance, nvimgcodecDecoder_t* decoder, const nvimgcodecExecutionParams_t* exec, const char* options);
+
+// ---------------------------------------------------------------------------------------------------------------
+// Extension object: owns the descriptors (the framework keeps pointers to them, src/image_decoder_factory.cpp:26-29)
+// ---------------------------------------------------------------------------------------------------------------
+struct Extension
+{
+    const nvimgcodecFrameworkDesc_t* fw;
+    nvimgcodecDecoderDesc_t dec_desc;
+    bool dec_registered = false;
+
+    explicit Extension(const nvimgcodecFrameworkDesc_t* f) : fw(f)
+    {
+        dec_desc = nvimgcodecDecoderDesc_t{NVIMGCODEC_STRUCTURE_TYPE_DECODER_DESC, sizeof(nvimgcodecDecoderDesc_t), nullptr, this, kDecoderId,
+            "jpeg", NVIMGCODEC_BACKEND_KIND_GPU_ONLY, dec_create, dec_destroy, dec_can_decode, dec_decode};
+        if (fw->registerDecoder(fw->instance, &dec_desc, kPriority) == NVIMGCODEC_STATUS_SUCCESS)
+            dec_registered = true;
+    }
+    ~Extension()
+    {
+        if (dec_registered)
+            fw->unregisterDecoder(fw->instance, &dec_desc);
+    }
+};
+
+nvimgcodecStatus_t dec_create(void* instance, nvimgcodecDecoder_t* decoder, const nvimgcodecExecutionParams_t* exec, const char* options)
+{
+    auto* ext = reinterpret_cast<Extension*>(instance);
+    if (!ext || !decoder || !exec)
+        return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    if (exec->device_id == NVIMGCODEC_DEVICE_CPU_ONLY)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER; // like extensions/nvjpeg/cuda_decoder.cpp:272-273
+    auto st = std::make_unique<DecoderState>();
+    st->fw = ext->fw;
+    st->exec = exec;
+    const int rc = b200jpeg_decoder_create(&st->dec, exec->device_id, options ? options : "");
+    if (rc != B200JPEG_STATUS_SUCCESS) {
+        log_msg(ext->fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_WARNING, kDecoderId, std::string("decoder unavailable: ") + b200jpeg_status_string(rc));
+        return rc == B200JPEG_STATUS_ARCH_MISMATCH ? NVIMGCODEC_STATUS_EXTENSION_ARCH_MISMATCH : NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR;
+    }
+    *decoder = reinterpret_cast<nvimgcodecDecoder_t>(st.release());
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t ext_create(void* instance, nvimgcodecExtension_t* extension, const nvimgcodecFrameworkDesc_t* framework)
+{
+    (void)instance;
+    if (!extension || !framework)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER;
+    try {
+        *extension = reinterpret_cast<nvimgcodecExtension_t>(new Extension(framework));
+    } catch (...) {
+        return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+    }
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t ext_destroy(nvimgcodecExtension_t extension)
+{
+    if (!extension)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER;
+    delete reinterpret_cast<Extension*>(extension);
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+// clang-format off
+const nvimgcodecExtensionDesc_t kExtensionDesc = {
+    NVIMGCODEC_STRUCTURE_TYPE_EXTENSION_DESC,
+    sizeof(nvimgcodecExtensionDesc_t),
+    nullptr,
+    nullptr,
+    "b200jpeg_extension",
+    NVIMGCODEC_VER,
+    NVIMGCODEC_EXT_API_VER,
+    ext_create,
+    ext_destroy
+};
+// clang-format on
+
+} // namespace
+
+extern "C" {
+
+// static-registration seam used by tests (nvimgcodecExtensionCreate, src/nvimgcodec_capi.cpp:224-243)
+__attribute__((visibility("default"))) nvimgcodecStatus_t get_b200jpeg_extension_desc(nvimgcodecExtensionDesc_t* ext_desc)
+{
+    if (!ext_desc || ext_desc->struct_type != NVIMGCODEC_STRUCTURE_TYPE_EXTENSION_DESC)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER;
+    *ext_desc = kExtensionDesc;
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+__attribute__((visibility("default"))) nvimgcodecStatus_t nvimgcodecExtensionModuleEntry(nvimgcodecExtensionDesc_t* ext_desc)
+{
+    return get_b200jpeg_extension_desc(ext_desc);
+}
+
+} // extern "C"

@@ -1,0 +1,83 @@
+"""CPU tests of the kernel logic: the per-thread bodies of the CUDA kernels (jpeg_math.cuh) + the batch planner run in a
+CPU emulation (tests/emu) and must match the oracle bit-for-bit, including the self-synchronising Huffman decode with
+Jacobi rounds, restart segments, every sampling mode and output format."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import util
+from util import GOLDEN, make_jpeg, port, ref
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu"))
+import emu  # noqa: E402
+
+pytestmark = pytest.mark.skipif(not util.have_ref(), reason="corpus needs oracle/_ref's libjpeg-turbo encoder")
+
+CASES = [(227, 149, (2, 2), 75, 0, False), (64, 48, (1, 1), 90, 0, False), (131, 77, (2, 1), 85, 0, False), (131, 77, (1, 2), 85, 0, False),
+         (333, 211, (2, 2), 90, 5, False), (17, 9, (2, 2), 90, 0, False), (3, 5, (2, 2), 90, 0, False), (2, 2, (2, 1), 90, 0, False),
+         (1, 1, (1, 1), 90, 0, False), (640, 426, (2, 2), 75, 0, False), (100, 100, (1, 1), 95, 7, False), (500, 375, (2, 2), 75, 1, False),
+         (400, 300, (2, 1), 90, 50, False), (201, 99, (1, 1), 85, 0, True)]
+
+
+def corpus():
+    return [make_jpeg(1000 + i, w, h, samp, q, restart_interval=ri, gray=g) for i, (w, h, samp, q, ri, g) in enumerate(CASES)]
+
+
+@pytest.mark.parametrize("fancy", [1, 0])
+@pytest.mark.parametrize("subseq", [32, 128, 512])
+def test_emulated_pipeline_bit_exact(fancy, subseq):
+    datas = corpus()
+    dims = [(c[0], c[1]) for c in CASES]
+    outs, st, rounds, _ = emu.decode_batch(datas, dims, 4, fancy, subseq)
+    assert st == [0] * len(datas)
+    for d, o in zip(datas, outs):
+        assert np.array_equal(o, port.decode(d, port.FMT_I_RGB, fancy))
+    assert rounds < 64
+
+
+def test_emulated_coefficients_match_reference():
+    datas = corpus()
+    dims = [(c[0], c[1]) for c in CASES]
+    slots = [util.mcu_order_coefficients(d).size for d in datas]
+    _, st, _, coefs = emu.decode_batch(datas, dims, 4, 1, 128, want_coef=True, slots=slots)
+    for d, c in zip(datas, coefs):
+        assert np.array_equal(c, util.mcu_order_coefficients(d))
+
+
+@pytest.mark.parametrize("fmt,pfmt", [(3, port.FMT_P_RGB), (5, port.FMT_P_BGR), (6, port.FMT_I_BGR), (7, port.FMT_Y)])
+def test_emulated_output_formats(fmt, pfmt):
+    datas = corpus()
+    dims = [(c[0], c[1]) for c in CASES]
+    outs, st, _, _ = emu.decode_batch(datas, dims, fmt)
+    for d, o in zip(datas, outs):
+        assert np.array_equal(np.squeeze(o), np.squeeze(port.decode(d, pfmt, True)))
+
+
+def test_emulated_jacobi_and_gauss_seidel_agree_and_1080p_converges():
+    d = make_jpeg(1000, 1920, 1080, (2, 2), 90)
+    want = port.decode(d, port.FMT_I_RGB, True)
+    for jac in (True, False):
+        outs, st, rounds, _ = emu.decode_batch([d], [(1920, 1080)], 4, 1, 256, jacobi=jac)
+        assert st == [0] and np.array_equal(outs[0], want)
+        assert rounds <= (12 if jac else 3)
+
+
+def test_emulated_corrupt_and_unsupported():
+    good = make_jpeg(5000, 320, 240)
+    prog = make_jpeg(5001, 320, 240, progressive=True)
+    truncated = good[:len(good) // 2]
+    bad_rst = bytearray(make_jpeg(5002, 320, 240, restart_interval=4))
+    i = bad_rst.find(b"\xff\xd1")
+    bad_rst[i + 1] = 0xD5  # wrong restart marker number
+    datas = [good, prog, truncated, b"nope", bytes(bad_rst)]
+    outs, st, _, _ = emu.decode_batch(datas, [(320, 240)] * 5, 4)
+    assert st == [0, 3, 4, 2, 4]
+
+
+def test_golden_fixtures_through_emulation():
+    for name in ("testorig.jpg", "testorig_420_islow.jpg", "testorig_440_islow.jpg", "testorig_gray_islow.jpg"):
+        d = open(os.path.join(GOLDEN, name), "rb").read()
+        outs, st, _, _ = emu.decode_batch([d], [(227, 149)], 4)
+        assert st == [0] and np.array_equal(outs[0], port.decode(d, port.FMT_I_RGB, True)), name

@@ -1,0 +1,95 @@
+"""CPU tests: pin the oracle.  (a) plain-C port vs libjpeg-turbo's own golden MD5s and the committed fixtures,
+(b) port vs the compiled reference (when oracle/_ref is present) on a seeded corpus incl. coefficients."""
+import hashlib
+import io
+import json
+import os
+
+import numpy as np
+import pytest
+
+import util
+from util import GOLDEN, make_jpeg, port, ref, synth_image
+
+G = json.load(open(os.path.join(GOLDEN, "golden.json")))
+
+
+def _fixture(name):
+    return open(os.path.join(GOLDEN, name), "rb").read()
+
+
+def test_port_reproduces_libjpeg_turbo_known_answers():
+    md5 = G["ljt_md5"]
+    j440, j420, jgray = _fixture("testorig_440_islow.jpg"), _fixture("testorig_420_islow.jpg"), _fixture("testorig_gray_islow.jpg")
+    assert hashlib.md5(j440).hexdigest() == md5["MD5_JPEG_440_ISLOW"]
+    assert hashlib.md5(j420).hexdigest() == md5["MD5_JPEG_420_ISLOW"]
+    assert hashlib.md5(jgray).hexdigest() == md5["MD5_JPEG_GRAY_ISLOW"]
+    rgb = port.decode(j440, port.FMT_I_RGB, True)
+    assert hashlib.md5(b"P6\n227 149\n255\n" + rgb.tobytes()).hexdigest() == md5["MD5_PPM_440_ISLOW"]
+    y = port.decode(jgray, port.FMT_Y, True)
+    assert hashlib.md5(b"P5\n227 149\n255\n" + y.tobytes()).hexdigest() == md5["MD5_PPM_GRAY_ISLOW"]
+    rgb = port.decode(jgray, port.FMT_I_RGB, True)
+    assert hashlib.md5(b"P6\n227 149\n255\n" + rgb.tobytes()).hexdigest() == md5["MD5_PPM_GRAY_ISLOW_RGB"]
+
+
+def test_port_matches_reference_plugin_fixture_hashes():
+    for name, want in G["decoded_md5"].items():
+        rgb = port.decode(_fixture(name), port.FMT_I_RGB, True)
+        assert hashlib.md5(b"P6\n227 149\n255\n" + rgb.tobytes()).hexdigest() == want["ppm_rgb"], name
+
+
+@pytest.mark.skipif(not util.have_ref(), reason="oracle/_ref not built")
+def test_synthetic_golden_hashes_and_port_vs_reference():
+    d1 = ref.Session.shared().decoder(options=":fancy_upsampling=1")
+    d0 = ref.Session.shared().decoder(options=":fancy_upsampling=0")
+    for e in G["synthetic_sha256"]:
+        data = make_jpeg(e["seed"], e["w"], e["h"], tuple(e["samp"]), e["quality"], restart_interval=e["restart_interval"], gray=e["gray"])
+        assert hashlib.sha256(data).hexdigest() == e["jpeg_sha256"], "corpus generator / libjpeg-turbo encoder drifted"
+        for fancy, dec in ((1, d1), (0, d0)):
+            rgb, st, _ = dec.decode_host([data])
+            assert st == [ref.STATUS_SUCCESS]
+            assert hashlib.sha256(rgb[0].tobytes()).hexdigest() == e["rgb_sha256_fancy%d" % fancy]
+            assert np.array_equal(port.decode(data, port.FMT_I_RGB, fancy), rgb[0])
+        ncomp = 1 if e["gray"] else 3
+        for c in range(ncomp):
+            pc = port.coefficients(data, c)
+            assert np.array_equal(pc, ref.ljt_coefficients(data, c, pc.shape[1], pc.shape[0]))
+
+
+@pytest.mark.skipif(not util.have_ref(), reason="oracle/_ref not built")
+def test_port_output_formats_vs_reference():
+    d1 = ref.Session.shared().decoder(options=":fancy_upsampling=1")
+    color = make_jpeg(77, 120, 90, (2, 2), 90)
+    gray = make_jpeg(78, 99, 55, gray=True)
+    for pf, rf in ((port.FMT_P_RGB, ref.P_RGB), (port.FMT_I_BGR, ref.I_BGR), (port.FMT_P_BGR, ref.P_BGR), (port.FMT_Y, ref.P_Y)):
+        for data in (color, gray):
+            o, st, _ = d1.decode_host([data], fmt=rf)
+            assert st == [ref.STATUS_SUCCESS]
+            assert np.array_equal(np.squeeze(o[0]), np.squeeze(port.decode(data, pf, True)))
+
+
+@pytest.mark.skipif(not util.have_ref(), reason="oracle/_ref not built")
+def test_pil_encoder_is_byte_identical_to_reference_libjpeg_turbo():
+    """bench.py builds its corpus with PIL's bundled libjpeg-turbo; it must be the same bitstream the reference's makes"""
+    from PIL import Image
+    img = synth_image(5, 320, 240)
+    for ss, samp in (("4:2:0", (2, 2)), ("4:2:2", (2, 1)), ("4:4:4", (1, 1))):
+        b = io.BytesIO()
+        Image.fromarray(img).save(b, "JPEG", quality=90, subsampling=ss, optimize=False)
+        assert b.getvalue() == ref.ljt_encode(img, 90, samp)
+
+
+def test_idct_stage_helper_matches_full_decode():
+    data = _fixture("testorig_420_islow.jpg")
+    coef = port.coefficients(data, 0)
+    plane = port.plane(data, 0)
+    import ctypes as C
+    # luma quant table of quality 75 (jcparam.c std table scaled by 50%)
+    base = [16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55, 14, 13, 16, 24, 40, 57, 69, 56, 14, 17, 22, 29, 51, 87, 80, 62, 18, 22,
+            37, 56, 68, 109, 103, 77, 24, 35, 55, 64, 81, 104, 113, 92, 49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100, 103, 99]
+    q = np.array([max(1, min(255, (b * 50 + 50) // 100)) for b in base], np.uint16)
+    out = np.zeros((8, 8), np.uint8)
+    for by, bx in ((0, 0), (3, 5), (10, 20)):
+        blk = np.ascontiguousarray(coef[by, bx])
+        port.lib().jo_idct_islow(blk.ctypes.data, q.ctypes.data, out.ctypes.data, 8)
+        assert np.array_equal(out, plane[by * 8:by * 8 + 8, bx * 8:bx * 8 + 8])
