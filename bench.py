@@ -250,7 +250,7 @@ def main():
     # algorithmic bytes per stage for this batch: compressed bytes S, coefficients 128 B/block,
     # planes 64 B/block, output bytes
     S, blocks, out_b = stats["scan_bytes"], stats["blocks"], stats["out_bytes"]
-    alg = {"unstuff": 2 * S, "huff_sync": S, "huff_write": S + 128 * blocks, "dc_scan": 4 * blocks, "idct": 128 * blocks + 64 * blocks,
+    alg = {"unstuff": 2 * S, "huff_sync": 2 * S, "huff_write": S + 130 * blocks, "dc_scan": 4 * blocks, "idct": 130 * blocks + 64 * blocks,
            "color": 64 * blocks + out_b}
     stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
     dom = max(stage_ms, key=stage_ms.get) if stage_ms else None
@@ -271,7 +271,7 @@ def main():
                                "fancy upsampling, per GPU" % (n, S / n / 1e3),
                    "l2": "working set per step %.0f MB (coefficients+planes+output) > 126 MB L2, no explicit flush" %
                          ((192 * blocks + out_b) / 1e6),
-                   "options": args.options, "sync_rounds": stats["sync_rounds"], "subsequences": stats["subsequences"],
+                   "options": args.options, "sync_rounds": stats["sync_rounds"], "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"],
                    "parity": "bit-exact vs reference libjpeg_turbo_ext on all %d images before timing" % n},
         "clocks": clocks.summary(),
         "e2e": {"value": mpix_step / (e2e_ms / args.steps / 1e3), "unit": "Mpixel/s", "images_per_s": n * world / (e2e_ms / args.steps / 1e3),

@@ -104,7 +104,7 @@ B200JPEG_API int b200jpeg_parse_header(const uint8_t* data, size_t size, b200jpe
 /* ---- decoder ----
  * options: the reference's option string, "name=value" tokens separated by spaces, optional "b200jpeg_decoder:" or ":"
  * prefix (reference extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:250-276): fancy_upsampling=0|1 (default 1),
- * subseq_bytes=N, sync_rounds=N, profile=0|1. */
+ * subseq_bytes=N (bytes of unstuffed stream per Huffman decoding thread, default 128), profile=0|1. */
 B200JPEG_API int b200jpeg_decoder_create(b200jpegDecoder_t* decoder, int device_id, const char* options);
 B200JPEG_API int b200jpeg_decoder_destroy(b200jpegDecoder_t decoder);
 
@@ -121,13 +121,14 @@ B200JPEG_API int b200jpeg_decode_prepare(b200jpegDecoder_t decoder, int batch_si
     const b200jpegOutput_t* outputs, int32_t* statuses);
 B200JPEG_API int b200jpeg_decode_run(b200jpegDecoder_t decoder, void* user_stream, int32_t* statuses);
 
-/* Counters of the last run: [0] kernels launched, [1] Huffman sync rounds, [2] entropy-coded bytes, [3] decoded blocks,
- * [4] subsequences, [5] device scratch bytes, [6] re-run count (non-converged sync), [7] reserved */
+/* Counters of the last run: [0] kernels launched, [1] Huffman sync rounds (2 full rounds + work-list rounds), [2] entropy-coded
+ * bytes, [3] decoded blocks, [4] subsequences, [5] device scratch bytes, [6] subsequences re-decoded in the work-list rounds,
+ * [7] output bytes */
 B200JPEG_API int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats8);
 
 /* Per-stage device times (ms) of the last run, measured with CUDA events on the decoder's own stream; needs the option
- * "profile=1".  Stages: 0 unstuff (3 kernels + memsets), 1 Huffman sync rounds, 2 slot scan + Huffman write (+ coefficient
- * memset), 3 DC prediction, 4 dequant+IDCT, 5 upsample+colour.  Returns the number of stages or -1. */
+ * "profile=1".  Stages: 0 unstuff (3 kernels + memsets), 1 Huffman sync rounds, 2 slot scan + Huffman write,
+ * 3 DC prediction, 4 dequant+IDCT, 5 upsample+colour.  Returns the number of stages or -1. */
 B200JPEG_API int b200jpeg_decoder_get_stage_times(b200jpegDecoder_t decoder, float* ms, int n);
 
 /* Debug/verification taps on the last prepared+run batch (device -> host copies of intermediates):

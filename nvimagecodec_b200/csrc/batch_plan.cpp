@@ -9,11 +9,13 @@ inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 inline uint32_t cdiv(uint64_t a, uint64_t b) { return uint32_t((a + b - 1) / b); }
 } // namespace
 
-// canonical code assignment as in jpeg_make_d_derived_tbl (external/libjpeg-turbo/jdhuff.c:143-285)
-void build_dev_table(const HuffSpec& spec, DevHuffTable& t)
+// canonical code assignment as in jpeg_make_d_derived_tbl (external/libjpeg-turbo/jdhuff.c:143-285); the first-level
+// table holds pre-digested entries (device_types.h huff_entry)
+void build_dev_table(const HuffSpec& spec, bool is_dc, DevHuffTable& t)
 {
     std::memset(&t, 0, sizeof(t));
     std::memcpy(t.vals, spec.vals, 256);
+    t.is_dc = is_dc ? 1 : 0;
     int code = 0, p = 0;
     for (int l = 1; l <= 16; ++l) {
         const int n = spec.bits[l];
@@ -23,8 +25,9 @@ void build_dev_table(const HuffSpec& spec, DevHuffTable& t)
                 if (l <= kLutBits && code < (1 << l)) {
                     const int first = code << (kLutBits - l);
                     const int cnt = 1 << (kLutBits - l);
+                    const uint16_t e = uint16_t(huff_entry(l, spec.vals[p & 255], is_dc));
                     for (int j = 0; j < cnt; ++j)
-                        t.lut[first + j] = uint16_t((l << 8) | spec.vals[p & 255]);
+                        t.lut[first + j] = e;
                 }
             }
             t.maxcode[l] = code - 1;
@@ -60,14 +63,20 @@ void plan_begin(BatchPlan& plan, const PlanOptions& opt)
     plan.map_color.push_back(0);
 }
 
-static int intern_huff(BatchPlan& plan, std::vector<HuffSpec>& seen, const HuffSpec& s)
+struct SeenTable
+{
+    HuffSpec spec;
+    bool is_dc;
+};
+
+static int intern_huff(BatchPlan& plan, std::vector<SeenTable>& seen, const HuffSpec& s, bool is_dc)
 {
     for (size_t i = 0; i < seen.size(); ++i)
-        if (!std::memcmp(seen[i].bits, s.bits, 17) && !std::memcmp(seen[i].vals, s.vals, 256))
+        if (seen[i].is_dc == is_dc && !std::memcmp(seen[i].spec.bits, s.bits, 17) && !std::memcmp(seen[i].spec.vals, s.vals, 256))
             return int(i);
-    seen.push_back(s);
+    seen.push_back(SeenTable{s, is_dc});
     plan.huff.emplace_back();
-    build_dev_table(s, plan.huff.back());
+    build_dev_table(s, is_dc, plan.huff.back());
     return int(seen.size() - 1);
 }
 
@@ -82,7 +91,7 @@ static int intern_quant(BatchPlan& plan, const uint16_t* q)
 }
 
 // one spec list per plan; kept in a side table keyed by the plan address (plans are built single-threaded)
-static thread_local std::vector<HuffSpec> g_seen;
+static thread_local std::vector<SeenTable> g_seen;
 
 void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out, const PlanOptions& opt)
 {
@@ -107,6 +116,7 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     im.mcus_x = (pj.width + 8 * im.hmax - 1) / (8 * im.hmax);
     im.mcus_y = (pj.height + 8 * im.vmax - 1) / (8 * im.vmax);
     int j = 0;
+    int dc_tab[3] = {0, 0, 0}, ac_tab[3] = {0, 0, 0};
     for (int c = 0; c < pj.ncomp; ++c) {
         im.blk_first[c] = j;
         for (int k = 0; k < im.hs[c] * im.vs[c]; ++k)
@@ -116,20 +126,34 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
         im.ds_w[c] = (pj.width * im.hs[c] + im.hmax - 1) / im.hmax;
         im.ds_h[c] = (pj.height * im.vs[c] + im.vmax - 1) / im.vmax;
         im.qt[c] = intern_quant(plan, pj.quant[pj.tq[c]]);
-        im.dc_tab[c] = intern_huff(plan, g_seen, pj.dc[pj.td[c]]);
-        im.ac_tab[c] = intern_huff(plan, g_seen, pj.ac[pj.ta[c]]);
+        dc_tab[c] = intern_huff(plan, g_seen, pj.dc[pj.td[c]], true);
+        ac_tab[c] = intern_huff(plan, g_seen, pj.ac[pj.ta[c]], false);
     }
     im.bpm = j;
-    im.mcu_slots = j * 64;
+    // table selectors: distinct pool tables get shared-memory slots in order of first use
+    im.ntabs = 0;
+    auto slot_of = [&](int pool_idx) {
+        for (int s = 0; s < im.ntabs; ++s)
+            if (im.tab_pool[s] == pool_idx)
+                return s;
+        im.tab_pool[im.ntabs] = pool_idx;
+        return im.ntabs++;
+    };
+    for (int b = 0; b < im.bpm; ++b) {
+        const int c = im.blk_comp[b];
+        im.tabsel_g[b] = TabSel{uint32_t(dc_tab[c]) * kHuffTableU16, uint32_t(ac_tab[c]) * kHuffTableU16, uint32_t(dc_tab[c]), uint32_t(ac_tab[c])};
+        im.tabsel_s[b] = TabSel{uint32_t(slot_of(dc_tab[c])) * kLutSize, uint32_t(slot_of(ac_tab[c])) * kLutSize, uint32_t(dc_tab[c]),
+            uint32_t(ac_tab[c])};
+    }
     const uint32_t mcus = uint32_t(im.mcus_x) * uint32_t(im.mcus_y);
-    im.total_slots = mcus * uint32_t(im.mcu_slots);
+    im.total_blocks = mcus * uint32_t(im.bpm);
     im.restart_interval = pj.restart_interval;
     if (pj.restart_interval > 0 && uint32_t(pj.restart_interval) < mcus) {
         im.num_segments = int(cdiv(mcus, pj.restart_interval));
-        im.seg_slots = uint32_t(pj.restart_interval) * uint32_t(im.mcu_slots);
+        im.seg_blocks = uint32_t(pj.restart_interval) * uint32_t(im.bpm);
     } else {
         im.num_segments = 1;
-        im.seg_slots = im.total_slots;
+        im.seg_blocks = im.total_blocks;
         im.restart_interval = 0;
     }
     im.seg_first = plan.total_segs;
@@ -156,7 +180,7 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     plan.map_subseq.push_back(im.subseq_cta_first + im.subseq_cta_count);
 
     im.coef_off = plan.coef_elems;
-    plan.coef_elems = align_up(plan.coef_elems + im.total_slots, 64);
+    plan.coef_elems = align_up(plan.coef_elems + uint64_t(im.total_blocks) * 64, 64);
     uint64_t blocks_out = 0;
     for (int c = 0; c < pj.ncomp; ++c) {
         im.plane_pitch[c] = im.wib[c] * 8;
@@ -168,9 +192,11 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     im.idct_cta_first = plan.map_idct.back();
     im.idct_cta_count = cdiv(blocks_out, kIdctCta);
     plan.map_idct.push_back(im.idct_cta_first + im.idct_cta_count);
-    const uint64_t units = uint64_t(cdiv(pj.width, 16)) * pj.height;
+    const int vy = pj.ncomp == 1 ? 1 : im.vmax / im.vs[1];
+    im.color_rows = vy == 2 ? im.ds_h[1] + 1 : pj.height; // row pairs (2q+1, 2q+2), q = -1 .. ds_h-1, when chroma is v-subsampled
+    im.color_xtiles = int(cdiv(pj.width, kColorTilePx));
     im.color_cta_first = plan.map_color.back();
-    im.color_cta_count = cdiv(units, kColorCta);
+    im.color_cta_count = cdiv(uint64_t(im.color_rows) * im.color_xtiles, kColorCta / 32);
     plan.map_color.push_back(im.color_cta_first + im.color_cta_count);
 
     im.out = static_cast<uint8_t*>(out.buffer);

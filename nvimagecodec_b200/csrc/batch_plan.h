@@ -36,7 +36,7 @@ struct BatchPlan
     int max_sync_depth = 0;
 };
 
-void build_dev_table(const HuffSpec& spec, DevHuffTable& out);
+void build_dev_table(const HuffSpec& spec, bool is_dc, DevHuffTable& out);
 
 // Resolve UNCHANGED formats; returns 0 if (format, ncomp) is not something this codec writes.
 int resolve_format(int requested, int ncomp);

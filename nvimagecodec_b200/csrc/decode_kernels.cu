@@ -5,16 +5,25 @@
 //   U1 k_unstuff_count   count kept bytes / RSTn markers per 4 KB chunk of entropy-coded data
 //   U2 k_unstuff_scan    per image: exclusive scan of the chunk counts, unstuffed length, segment table init
 //   U3 k_unstuff_write   compact: drop FF00 stuffing, FF fill, RSTn markers; record restart-segment starts
-//   H1 k_huff_sync x R   self-synchronising subsequence decode (no output), Jacobi rounds until nothing changes
-//   H2 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute write position per subsequence
-//   H3 k_huff_write      final decode pass: de-zigzagged int16 coefficients, MCU scan order
-//   D1 k_dc_scan         per image: DC prediction = segmented (restart interval) prefix sum per component
-//   I1 k_idct            dequantise + islow IDCT, one 8x8 block per thread, writes component planes
-//   C1 k_color           upsample (fancy / box) + YCbCr->RGB, 16 pixels per thread, 128-bit stores
-// The per-thread arithmetic lives in jpeg_math.cuh (shared with the CPU emulation used by the tests).
+//   H1 k_huff_sync x 2   self-synchronising subsequence decode (no output): round 0 from a guessed state, round 1 from the
+//                        predecessor's exit state; subsequences whose exit state changed feed a work list
+//   H2 k_huff_sync_tail  cooperative kernel: Jacobi rounds over the (compacted) work list until it is empty
+//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute write position per subsequence
+//   H4 k_huff_write      final decode pass: a CTA zeroes the coefficient range it owns, then stores de-zigzagged int16 AC
+//                        coefficients and the per-block DC differences
+//   D1 k_dc_scan         per image: DC prediction = segmented (restart interval) prefix sum per component over dc[]
+//   I1 k_idct            dequantise + islow IDCT, one 8x8 block per thread (coefficients staged through shared memory so
+//                        that global loads are full 128-byte lines), writes component planes
+//   C1 k_color           upsample (fancy / box) + YCbCr->RGB; a warp produces 512 pixels x (1|2) rows, staged in shared
+//                        memory and written with fully coalesced 128-byte store instructions at any alignment
+// The per-thread arithmetic lives in huffman.cuh / jpeg_math.cuh (shared with the CPU emulation used by the tests).
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include "decode_kernels.h"
+#include "huffman.cuh"
 #include "jpeg_math.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace b200jpeg {
 
@@ -208,44 +217,133 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
 // ------------------------------------------------------------------------------------------------------------------
 // Huffman: synchronisation rounds, slot scan, write pass
 // ------------------------------------------------------------------------------------------------------------------
+
+// Stage the image's distinct Huffman LUTs and its per-block table selectors in shared memory.
+__device__ __forceinline__ void stage_tables(const BatchDev& b, const ImageDesc& im, uint16_t* s_lut, TabSel* s_tabsel)
+{
+    static_assert(kLutSize * 2 == kSubseqCta * 16, "one uint4 per thread copies one LUT");
+    for (int s = 0; s < im.ntabs; ++s) {
+        const uint4* src = reinterpret_cast<const uint4*>(b.huff[im.tab_pool[s]].lut);
+        reinterpret_cast<uint4*>(s_lut + s * kLutSize)[threadIdx.x] = src[threadIdx.x];
+    }
+    if (threadIdx.x < kMaxBlocksPerMcu)
+        s_tabsel[threadIdx.x] = im.tabsel_s[threadIdx.x];
+    __syncthreads();
+}
+
+__device__ __forceinline__ HuffEnv make_env(const BatchDev& b, const ImageDesc& im, uint32_t clean_len, const uint16_t* lut, const TabSel* tabsel)
+{
+    HuffEnv env;
+    env.words = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
+    env.lut = lut;
+    env.tabsel = tabsel;
+    env.pool = b.huff;
+    env.seg = b.seg_start + im.seg_first;
+    env.num_segments = im.num_segments;
+    env.seg_blocks = im.seg_blocks;
+    env.total_blocks = im.total_blocks;
+    env.clean_bits = clean_len * 8u;
+    env.bpm = im.bpm;
+    return env;
+}
+
+// Decode subsequence k of an image from entry state E in synchronisation mode and publish the result.
+// Returns true if the exit state differs from the one recorded before.
+__device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& env, uint32_t t, uint32_t k, unsigned long long E, bool exact)
+{
+    HuffState s;
+    s.p = uint32_t(E);
+    const uint32_t slot = uint32_t(E >> 32);
+    s.z = slot & 63u;
+    s.blk = slot >> 6;
+    s.nblk = 0;
+    s.abs = exact;
+    const uint32_t z_entry = s.z;
+    decode_span<false>(env, s, (k + 1u) * uint32_t(b.subseq_bits), false, 0, nullptr, nullptr);
+    const unsigned long long X = pack_state(s.p, s.blk * 64u + s.z);
+    const bool changed = (X != __ldcg(b.sub_exit + t));
+    b.sub_exit[t] = X;
+    b.sub_entry[t] = E;
+    // slots consumed: absolute (from the image start) once a known state was passed, else relative to the entry
+    const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
+    b.sub_rec[t] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
+    return changed;
+}
+
 __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
 {
+    __shared__ __align__(16) uint16_t s_lut[kMaxTabSlots * kLutSize];
+    __shared__ TabSel s_tabsel[kMaxBlocksPerMcu];
     const int img = find_image(b.cta_map_subseq, b.num_images, blockIdx.x);
     const ImageDesc& im = b.images[img];
+    stage_tables(b, im, s_lut, s_tabsel);
     const uint32_t k = (blockIdx.x - b.cta_map_subseq[img]) * kSubseqCta + threadIdx.x;
     const uint32_t t = im.subseq_first + k;
     const uint32_t clean_len = b.states[img].clean_len;
-    const bool idle = uint64_t(k) * uint32_t(b.subseq_bits) >= uint64_t(clean_len) * 8u;
-    SubseqState s;
-    unsigned long long E;
+    const uint32_t clean_bits = clean_len * 8u;
+    const bool idle = uint64_t(k) * uint32_t(b.subseq_bits) >= uint64_t(clean_bits);
+    const HuffEnv env = make_env(b, im, clean_len, s_lut, s_tabsel);
     if (round == 0) {
         if (idle) {
-            b.sub_exit[t] = b.sub_entry[t] = (unsigned long long)clean_len * 8u;
+            b.sub_exit[t] = b.sub_entry[t] = pack_state(clean_bits, 0);
             b.sub_rec[t] = 0;
             return;
         }
-        s.p = k * uint32_t(b.subseq_bits);
-        s.slot = 0;
-        s.n = 0;
-        s.abs = (k == 0);
-        E = s.p;
+        b.sub_exit[t] = ~0ull;
+        sync_decode(b, env, t, k, pack_state(k * uint32_t(b.subseq_bits), 0), k == 0);
     } else {
         if (idle || k == 0)
             return;
-        E = b.sub_exit[t - 1];
+        const unsigned long long E = b.sub_exit[t - 1];
         if (E == b.sub_entry[t])
             return;
-        s.p = uint32_t(E);
-        s.slot = uint32_t(E >> 32);
-        s.n = 0;
-        s.abs = false;
+        const bool changed = sync_decode(b, env, t, k, E, false);
+        const bool next_live = uint64_t(k + 1) * uint32_t(b.subseq_bits) < uint64_t(clean_bits);
+        if (changed && next_live) {
+            const uint32_t i = atomicAdd(&b.sync->count[0], 1u);
+            b.worklist[0][i] = t + 1;
+        }
     }
-    decode_subsequence<false>(b, im, &b.states[img], k, clean_len, s);
-    b.sub_exit[t] = (unsigned long long)s.p | ((unsigned long long)s.slot << 32);
-    b.sub_entry[t] = E;
-    b.sub_rec[t] = (s.n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
-    if (round > 0)
-        atomicAdd(&b.redo_counter[round], 1u);
+}
+
+// Jacobi rounds over the work list until no subsequence changes any more.  Cooperative launch: every CTA is resident,
+// grid.sync() separates the rounds.  Round r reads list r & 1 (length count[r % 3]) and appends to list (r + 1) & 1
+// (length count[(r + 1) % 3]); count[(r + 2) % 3] is cleared for the round after.
+__global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b)
+{
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t redone = 0;
+    int r = 0;
+    for (; r < kMaxTailRounds; ++r) {
+        const uint32_t n = __ldcg(&b.sync->count[r % 3]);
+        if (n == 0)
+            break;
+        if (tid == 0)
+            b.sync->count[(r + 2) % 3] = 0;
+        const uint32_t* in = b.worklist[r & 1];
+        uint32_t* out = b.worklist[(r + 1) & 1];
+        for (uint32_t i = tid; i < n; i += nthreads) {
+            const uint32_t t = __ldcg(in + i);
+            const int img = find_image(b.cta_map_subseq, b.num_images, t / kSubseqCta);
+            const ImageDesc& im = b.images[img];
+            const uint32_t k = t - im.subseq_first;
+            const unsigned long long E = __ldcg(b.sub_exit + t - 1); // written by other SMs in earlier rounds: bypass L1
+            if (E == __ldcg(b.sub_entry + t))
+                continue;
+            const uint32_t clean_len = b.states[img].clean_len;
+            const HuffEnv env = make_env(b, im, clean_len, reinterpret_cast<const uint16_t*>(b.huff), im.tabsel_g);
+            const bool changed = sync_decode(b, env, t, k, E, false);
+            ++redone;
+            if (changed && uint64_t(k + 1) * uint32_t(b.subseq_bits) < uint64_t(clean_len) * 8u)
+                out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
+        }
+        grid.sync();
+    }
+    if (redone)
+        atomicAdd(&b.sync->redone, redone);
+    if (tid == 0)
+        b.sync->rounds = uint32_t(r);
 }
 
 // segmented-scan combine: a = earlier prefix, x = later element; bit31 = "absolute" flag
@@ -263,9 +361,13 @@ __global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
     if (threadIdx.x == 0)
         s_carry = 0x80000000u;
     __syncthreads();
+    bool bad = false;
     for (uint32_t c0 = 0; c0 < count; c0 += kScanThreads) {
         const uint32_t c = c0 + threadIdx.x;
         uint32_t v = c < count ? b.sub_rec[im.subseq_first + c] : 0u;
+        if (c > 0 && c < count && b.sub_entry[im.subseq_first + c] != b.sub_exit[im.subseq_first + c - 1] &&
+            uint64_t(c) * uint32_t(b.subseq_bits) < uint64_t(b.states[img].clean_len) * 8u)
+            bad = true; // the chain of entry/exit states is not consistent: synchronisation did not finish
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, v, o);
@@ -286,36 +388,72 @@ __global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
             s_carry = v;
         __syncthreads();
     }
+    if (bad)
+        atomicOr(&b.states[img].error, kErrNotConverged);
 }
 
 __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
 {
+    __shared__ __align__(16) uint16_t s_lut[kMaxTabSlots * kLutSize];
+    __shared__ TabSel s_tabsel[kMaxBlocksPerMcu];
     const int img = find_image(b.cta_map_subseq, b.num_images, blockIdx.x);
     const ImageDesc& im = b.images[img];
-    const uint32_t k = (blockIdx.x - b.cta_map_subseq[img]) * kSubseqCta + threadIdx.x;
+    stage_tables(b, im, s_lut, s_tabsel);
+    const uint32_t cta = blockIdx.x - b.cta_map_subseq[img];
+    const uint32_t k0 = cta * kSubseqCta, k = k0 + threadIdx.x;
     const uint32_t t = im.subseq_first + k;
     const uint32_t clean_len = b.states[img].clean_len;
-    if (uint64_t(k) * uint32_t(b.subseq_bits) >= uint64_t(clean_len) * 8u)
+    const uint32_t clean_bits = clean_len * 8u;
+    const uint32_t S = uint32_t(b.subseq_bits);
+
+    // blocks this CTA owns: those that *start* inside its subsequences
+    const uint32_t n_first = k0 == 0 ? 0u : (b.sub_abs[im.subseq_first + k0 - 1] & 0x7FFFFFFFu);
+    const bool last_cta = cta + 1 == im.subseq_cta_count;
+    const uint32_t n_next = b.sub_abs[im.subseq_first + k0 + kSubseqCta - 1] & 0x7FFFFFFFu;
+    const uint32_t first_block = (n_first + 63u) >> 6;
+    uint32_t end_block = last_cta ? im.total_blocks : (n_next + 63u) >> 6;
+    if (end_block > im.total_blocks)
+        end_block = im.total_blocks;
+    int16_t* coef = b.coef + im.coef_off;
+    int16_t* dc = b.dc + im.coef_off / 64;
+    if (end_block > first_block) { // zero the owned coefficient range: the scattered stores below then hit lines in L2
+        uint4* z4 = reinterpret_cast<uint4*>(coef + uint64_t(first_block) * 64);
+        const uint32_t n16 = (end_block - first_block) * 8u;
+        for (uint32_t i = threadIdx.x; i < n16; i += kSubseqCta)
+            z4[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    if (uint64_t(k) * S >= uint64_t(clean_bits))
         return;
-    SubseqState s;
+    HuffState s;
     if (k == 0) {
         s.p = 0;
-        s.slot = 0;
-        s.n = 0;
+        s.z = 0;
+        s.blk = 0;
+        s.nblk = 0;
     } else {
         const unsigned long long E = b.sub_exit[t - 1];
-        if (E != b.sub_entry[t])
-            atomicOr(&b.states[img].error, kErrNotConverged);
+        const uint32_t slot = uint32_t(E >> 32);
         s.p = uint32_t(E);
-        s.slot = uint32_t(E >> 32);
-        s.n = b.sub_abs[t - 1] & 0x7FFFFFFFu;
+        s.z = slot & 63u;
+        s.blk = slot >> 6;
+        s.nblk = (b.sub_abs[t - 1] & 0x7FFFFFFFu) >> 6;
     }
     s.abs = true;
-    decode_subsequence<true>(b, im, &b.states[img], k, clean_len, s);
+    const bool extend = (threadIdx.x == kSubseqCta - 1) || (uint64_t(k + 1) * S >= uint64_t(clean_bits));
+    const HuffEnv env = make_env(b, im, clean_len, s_lut, s_tabsel);
+    const uint32_t end = (k + 1u) * S;
+    uint32_t err = 0;
+    if (!(extend && s.p >= end && s.z == 0))
+        err = decode_span<true>(env, s, end, extend, first_block, coef, dc);
+    if (s.nblk == im.total_blocks && s.z == 0 && extend)
+        b.states[img].done_blocks = s.nblk;
+    if (err)
+        atomicOr(&b.states[img].error, err);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// DC prediction: per image, segmented (restart interval) inclusive scan of per-MCU DC-difference sums per component.
+// DC prediction: per image, segmented (restart interval) inclusive scan of the DC differences per component.
 // ------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
 {
@@ -330,7 +468,7 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
     if (threadIdx.x < 3)
         s_carry[threadIdx.x] = 0;
     __syncthreads();
-    int16_t* coef = b.coef + im.coef_off;
+    int16_t* dc = b.dc + im.coef_off / 64;
     const uint32_t ri = im.restart_interval ? uint32_t(im.restart_interval) : 0xFFFFFFFFu;
     for (uint32_t m0 = 0; m0 < mcus; m0 += kDcCta) {
         const uint32_t m = m0 + threadIdx.x;
@@ -339,7 +477,7 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
         int flag = 0;
         if (m < mcus) {
             for (int j = 0; j < im.bpm; ++j) {
-                d[j] = coef[(uint64_t(m) * im.bpm + j) * 64];
+                d[j] = dc[uint64_t(m) * im.bpm + j];
                 const int c = im.blk_comp[j];
                 if (c == 0) v0 += d[j];
                 else if (c == 1) v1 += d[j];
@@ -393,7 +531,7 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
             for (int j = 0; j < im.bpm; ++j) {
                 const int c = im.blk_comp[j];
                 pred[c] += d[j];
-                coef[(uint64_t(m) * im.bpm + j) * 64] = int16_t(pred[c]);
+                dc[uint64_t(m) * im.bpm + j] = int16_t(pred[c]);
             }
         }
         __syncthreads();
@@ -407,20 +545,187 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// IDCT and colour
+// IDCT: one block per thread.  A warp first copies its 32 blocks' coefficients (32 x 128 bytes, scattered over the MCU
+// order) into shared memory with 128-byte-coalesced loads, then each lane reads its own block back (row pitch 144 bytes:
+// conflict free for 16-byte accesses).
 // ------------------------------------------------------------------------------------------------------------------
+constexpr int kIdctPitch = 144;
 __global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
 {
+    __shared__ __align__(16) uint8_t s_blk[kIdctCta * kIdctPitch];
+    __shared__ uint16_t s_q[3 * 64];
     const int img = find_image(b.cta_map_idct, b.num_images, blockIdx.x);
     const ImageDesc& im = b.images[img];
-    idct_thread(b, im, (blockIdx.x - b.cta_map_idct[img]) * kIdctCta + threadIdx.x);
+    for (int i = threadIdx.x; i < im.ncomp_out * 64; i += kIdctCta)
+        s_q[i] = b.quant[im.qt[i >> 6] * 64 + (i & 63)];
+    const uint32_t u = (blockIdx.x - b.cta_map_idct[img]) * kIdctCta + threadIdx.x;
+    const IdctBlockRef ref = idct_locate(im, u);
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t* wbuf = s_blk + warp * 32 * kIdctPitch;
+    const int16_t* coef = b.coef + im.coef_off;
+    const uint32_t my_src = ref.comp >= 0 ? ref.src_blk : 0xFFFFFFFFu;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int bw = i * 4 + int(lane >> 3); // block of the warp this lane helps to load
+        const uint32_t src = __shfl_sync(0xFFFFFFFFu, my_src, bw);
+        if (src != 0xFFFFFFFFu) {
+            const uint4 v = reinterpret_cast<const uint4*>(coef + uint64_t(src) * 64)[lane & 7];
+            *reinterpret_cast<uint4*>(wbuf + bw * kIdctPitch + (lane & 7) * 16) = v;
+        }
+    }
+    __syncthreads();
+    if (ref.comp < 0)
+        return;
+    alignas(16) int16_t blk[64];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        reinterpret_cast<uint4*>(blk)[i] = *reinterpret_cast<const uint4*>(wbuf + lane * kIdctPitch + i * 16);
+    const int dcval = b.dc[im.coef_off / 64 + ref.src_blk];
+    uint32_t out[16];
+    idct_block(blk, dcval, s_q + ref.comp * 64, out);
+    uint8_t* dst = b.planes + ref.dst;
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+        *reinterpret_cast<uint2*>(dst + r * ref.pitch) = make_uint2(out[2 * r], out[2 * r + 1]);
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Colour: a warp tile is 512 pixels x VY rows.  Each lane converts 16 pixels per row, the warp's rows are assembled in
+// shared memory and written out with one 4-byte word per lane per store instruction (128 contiguous bytes per
+// instruction) whatever the alignment of the destination row.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int kRowWords = kColorTilePx * 3 / 4; // interleaved RGB row of a tile in 32-bit words
+
+// copy nbytes from shared memory (word aligned, one spare word readable past the end) to dst (any alignment)
+__device__ __forceinline__ void warp_store_row(uint8_t* dst, const uint32_t* s_row, int nbytes, uint32_t lane)
+{
+    const uint32_t m = uint32_t(reinterpret_cast<uintptr_t>(dst) & 3u);
+    const uint8_t* sb = reinterpret_cast<const uint8_t*>(s_row);
+    if (m == 0) {
+        const int nw = nbytes >> 2;
+        uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+        for (int w = int(lane); w < nw; w += 32)
+            d32[w] = s_row[w];
+        const int done = nw << 2;
+        if (int(lane) < nbytes - done)
+            dst[done + lane] = sb[done + lane];
+    } else {
+        int head = int(4u - m);
+        if (head > nbytes)
+            head = nbytes;
+        if (int(lane) < head)
+            dst[lane] = sb[lane];
+        const int nw = (nbytes - head) >> 2;
+        uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
+        const uint32_t sh = uint32_t(head) * 8u;
+        for (int w = int(lane); w < nw; w += 32)
+            d32[w] = __funnelshift_r(s_row[w], s_row[w + 1], sh);
+        const int done = head + (nw << 2);
+        if (int(lane) < nbytes - done)
+            dst[done + lane] = sb[done + lane];
+    }
+}
+
+template <int HX, int VY>
+__device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& im, uint32_t tile, uint32_t* s_warp, uint32_t lane)
+{
+    const int q = int(tile / uint32_t(im.color_xtiles)) - (VY == 2 ? 1 : 0);
+    const int xt = int(tile % uint32_t(im.color_xtiles));
+    const int xbase = xt * kColorTilePx;
+    const int x0 = xbase + int(lane) * 16;
+    uint32_t px[VY * 16];
+    int yrow[VY];
+    if (x0 < im.width) {
+        color_unit<HX, VY>(b, im, q, x0, px, yrow);
+    } else {
+#pragma unroll
+        for (int r = 0; r < VY; ++r)
+            yrow[r] = -1;
+        // rows of this tile must be known by every lane: recompute validity below from lane 0
+    }
+    // row validity is a property of the tile, take it from lane 0 (always inside the image)
+    int yr[VY];
+#pragma unroll
+    for (int r = 0; r < VY; ++r)
+        yr[r] = __shfl_sync(0xFFFFFFFFu, yrow[r], 0);
+    const int tile_px = im.width - xbase < kColorTilePx ? im.width - xbase : kColorTilePx;
+    const int fmt = im.out_fmt;
+    if (fmt == 4 || fmt == 6) { // interleaved
+#pragma unroll
+        for (int r = 0; r < VY; ++r) {
+            uint32_t* s_row = s_warp + r * (kRowWords + 4);
+            if (x0 < im.width) {
+                uint32_t w[12];
+#pragma unroll
+                for (int g = 0; g < 4; ++g) { // 4 pixels -> 3 words
+                    const uint32_t a = px[r * 16 + 4 * g], c = px[r * 16 + 4 * g + 1], d = px[r * 16 + 4 * g + 2], e = px[r * 16 + 4 * g + 3];
+                    w[3 * g] = (a & 0xFFFFFFu) | (c << 24);
+                    w[3 * g + 1] = ((c >> 8) & 0xFFFFu) | (d << 16);
+                    w[3 * g + 2] = ((d >> 16) & 0xFFu) | (e << 8);
+                }
+                uint4* s4 = reinterpret_cast<uint4*>(s_row + lane * 12);
+                s4[0] = make_uint4(w[0], w[1], w[2], w[3]);
+                s4[1] = make_uint4(w[4], w[5], w[6], w[7]);
+                s4[2] = make_uint4(w[8], w[9], w[10], w[11]);
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < VY; ++r)
+            if (yr[r] >= 0)
+                warp_store_row(im.out + int64_t(yr[r]) * im.out_stride + int64_t(xbase) * 3, s_warp + r * (kRowWords + 4), tile_px * 3, lane);
+    } else { // planar: P_RGB / P_BGR three planes, P_Y one
+        const int nplanes = fmt == 7 ? 1 : 3;
+        constexpr int kPlaneWords = kColorTilePx / 4 + 4;
+#pragma unroll
+        for (int r = 0; r < VY; ++r) {
+            if (x0 < im.width) {
+                for (int pl = 0; pl < nplanes; ++pl) {
+                    uint32_t w[4];
+#pragma unroll
+                    for (int g = 0; g < 4; ++g)
+                        w[g] = ((px[r * 16 + 4 * g] >> (8 * pl)) & 255u) | (((px[r * 16 + 4 * g + 1] >> (8 * pl)) & 255u) << 8) |
+                               (((px[r * 16 + 4 * g + 2] >> (8 * pl)) & 255u) << 16) | (((px[r * 16 + 4 * g + 3] >> (8 * pl)) & 255u) << 24);
+                    *reinterpret_cast<uint4*>(s_warp + (r * 3 + pl) * kPlaneWords + lane * 4) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < VY; ++r)
+            if (yr[r] >= 0)
+                for (int pl = 0; pl < nplanes; ++pl)
+                    warp_store_row(im.out + (int64_t(pl) * im.height + yr[r]) * im.out_stride + xbase, s_warp + (r * 3 + pl) * kPlaneWords,
+                        tile_px, lane);
+    }
+    __syncwarp();
+}
+
+constexpr int kColorWarpWords = 800; // >= 2 * (kRowWords + 4) and >= 6 * (kColorTilePx / 4 + 4)
+static_assert(kColorWarpWords >= 6 * (kColorTilePx / 4 + 4) && kColorWarpWords >= 2 * (kRowWords + 4), "staging must fit");
 
 __global__ void __launch_bounds__(kColorCta) k_color(BatchDev b)
 {
+    __shared__ __align__(16) uint32_t s_stage[(kColorCta / 32) * kColorWarpWords];
     const int img = find_image(b.cta_map_color, b.num_images, blockIdx.x);
     const ImageDesc& im = b.images[img];
-    color_thread(b, im, (blockIdx.x - b.cta_map_color[img]) * kColorCta + threadIdx.x);
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tile = (blockIdx.x - b.cta_map_color[img]) * (kColorCta / 32) + warp;
+    if (tile >= uint32_t(im.color_rows) * uint32_t(im.color_xtiles))
+        return;
+    uint32_t* s_warp = s_stage + warp * kColorWarpWords;
+    const int hx = color_hx(im), vy = color_vy(im);
+    if (vy == 2) {
+        if (hx == 2)
+            color_tile<2, 2>(b, im, tile, s_warp, lane);
+        else
+            color_tile<1, 2>(b, im, tile, s_warp, lane);
+    } else {
+        if (hx == 2)
+            color_tile<2, 1>(b, im, tile, s_warp, lane);
+        else
+            color_tile<1, 1>(b, im, tile, s_warp, lane);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -434,11 +739,27 @@ int launch_unstuff(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
     return 3;
 }
 
-int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int first_round, int num_rounds)
+int tail_grid_size(int device)
 {
-    for (int r = first_round; r < first_round + num_rounds; ++r)
-        k_huff_sync<<<d.subseq_ctas, kSubseqCta, 0, st>>>(b, r);
-    return num_rounds;
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_huff_sync_tail, kSubseqCta, 0) != cudaSuccess || per_sm < 1)
+        return 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms < 1)
+        return 0;
+    if (per_sm > 4)
+        per_sm = 4;
+    return per_sm * sms;
+}
+
+int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid)
+{
+    k_huff_sync<<<d.subseq_ctas, kSubseqCta, 0, st>>>(b, 0);
+    k_huff_sync<<<d.subseq_ctas, kSubseqCta, 0, st>>>(b, 1);
+    BatchDev bb = b;
+    void* args[] = {&bb};
+    if (cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_huff_sync_tail), dim3(tail_grid), dim3(kSubseqCta), args, 0, st) != cudaSuccess)
+        return -1;
+    return 3;
 }
 
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st)

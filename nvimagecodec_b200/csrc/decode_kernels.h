@@ -13,7 +13,9 @@ struct LaunchDims
 
 // each returns the number of kernels it launched
 int launch_unstuff(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
-int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int first_round, int num_rounds);
+// rounds 0 and 1 over every subsequence, then the cooperative tail kernel (grid size from tail_grid_size); -1 on launch failure
+int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid);
+int tail_grid_size(int device); // CTAs of k_huff_sync_tail that are co-resident on the device (0 on error)
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
@@ -21,6 +23,5 @@ int launch_color(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 
 enum Stage { kStageUnstuff = 0, kStageSync, kStageWrite, kStageDc, kStageIdct, kStageColor, kNumStages };
 
-constexpr int kMaxSyncRounds = 256; // size of the redo counter array
 
 } // namespace b200jpeg

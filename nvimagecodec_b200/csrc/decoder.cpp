@@ -60,9 +60,7 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
             int v = std::atoi(value.c_str());
             if (v >= 32 && v <= 4096 && (v % 4) == 0)
                 o.subseq_bytes = v;
-        } else if (name == "sync_rounds")
-            o.sync_rounds = std::max(0, std::atoi(value.c_str()));
-        else if (name == "copy_threads")
+        } else if (name == "copy_threads")
             o.copy_threads = std::max(1, std::atoi(value.c_str()));
         else if (name == "profile")
             o.profile = std::atoi(value.c_str()) != 0;
@@ -76,8 +74,8 @@ Decoder::~Decoder()
 {
     if (device_ >= 0)
         cudaSetDevice(device_);
-    DevBuf* dbufs[] = {&d_raw_, &d_clean_, &d_coef_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
-        &d_rec_, &d_abs_, &d_redo_, &d_out_};
+    DevBuf* dbufs[] = {&d_raw_, &d_clean_, &d_coef_, &d_dc_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
+        &d_rec_, &d_abs_, &d_wl0_, &d_wl1_, &d_sync_, &d_out_};
     for (DevBuf* b : dbufs)
         if (b->p)
             cudaFree(b->p);
@@ -112,7 +110,9 @@ int Decoder::init()
     if (opt_.profile)
         for (cudaEvent_t& e : ev_stage_)
             B2J_CUDA(cudaEventCreate(&e));
-    adaptive_rounds_ = opt_.sync_rounds > 0 ? opt_.sync_rounds : 8;
+    tail_grid_ = tail_grid_size(device_);
+    if (tail_grid_ <= 0)
+        return B200JPEG_STATUS_CUDA_ERROR;
     return B200JPEG_STATUS_SUCCESS;
 }
 
@@ -223,11 +223,13 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     // ---- scratch ----
     int rc = 0;
     if ((rc = ensure(d_raw_, plan_.raw_bytes)) || (rc = ensure(d_clean_, plan_.clean_bytes)) ||
-        (rc = ensure(d_coef_, plan_.coef_elems * sizeof(int16_t))) || (rc = ensure(d_planes_, plan_.plane_bytes)) ||
+        (rc = ensure(d_coef_, plan_.coef_elems * sizeof(int16_t))) || (rc = ensure(d_dc_, plan_.coef_elems / 64 * sizeof(int16_t) + 64)) ||
+        (rc = ensure(d_planes_, plan_.plane_bytes)) ||
         (rc = ensure(d_states_, sizeof(ImageState) * m)) || (rc = ensure(d_seg_, sizeof(uint32_t) * (plan_.total_segs + 1))) ||
         (rc = ensure(d_chunks_, sizeof(uint64_t) * plan_.total_chunks)) || (rc = ensure(d_exit_, 8 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_entry_, 8 * size_t(plan_.total_subseq))) || (rc = ensure(d_rec_, 4 * size_t(plan_.total_subseq))) ||
-        (rc = ensure(d_abs_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_redo_, 4 * kMaxSyncRounds)) ||
+        (rc = ensure(d_abs_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_wl0_, 4 * size_t(plan_.total_subseq))) ||
+        (rc = ensure(d_wl1_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_sync_, sizeof(SyncCounters))) ||
         (dev_out_bytes && (rc = ensure(d_out_, dev_out_bytes))))
         return rc;
     for (const HostOutput& ho : host_outs_)
@@ -242,7 +244,7 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     const size_t meta_bytes = off_m0 + 4 * map_bytes;
     if ((rc = ensure(d_meta_, meta_bytes)) || (rc = ensure_pinned(h_meta_, meta_bytes)) ||
         (rc = ensure_pinned(h_raw_, plan_.raw_bytes)) ||
-        (rc = ensure_pinned(h_states_, sizeof(ImageState) * m + 4 * kMaxSyncRounds)))
+        (rc = ensure_pinned(h_states_, sizeof(ImageState) * m + sizeof(SyncCounters))))
         return rc;
     uint8_t* hm = static_cast<uint8_t*>(h_meta_.p);
     std::memcpy(hm + off_img, plan_.images.data(), sizeof(ImageDesc) * m);
@@ -290,15 +292,18 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     dev_.sub_entry = static_cast<unsigned long long*>(d_entry_.p);
     dev_.sub_rec = static_cast<uint32_t*>(d_rec_.p);
     dev_.sub_abs = static_cast<uint32_t*>(d_abs_.p);
-    dev_.redo_counter = static_cast<uint32_t*>(d_redo_.p);
+    dev_.worklist[0] = static_cast<uint32_t*>(d_wl0_.p);
+    dev_.worklist[1] = static_cast<uint32_t*>(d_wl1_.p);
+    dev_.sync = static_cast<SyncCounters*>(d_sync_.p);
     dev_.coef = static_cast<int16_t*>(d_coef_.p);
+    dev_.dc = static_cast<int16_t*>(d_dc_.p);
     dev_.planes = static_cast<uint8_t*>(d_planes_.p);
     dev_.cta_map_unstuff = reinterpret_cast<const uint32_t*>(dm + off_m0 + 0 * map_bytes);
     dev_.cta_map_subseq = reinterpret_cast<const uint32_t*>(dm + off_m0 + 1 * map_bytes);
     dev_.cta_map_idct = reinterpret_cast<const uint32_t*>(dm + off_m0 + 2 * map_bytes);
     dev_.cta_map_color = reinterpret_cast<const uint32_t*>(dm + off_m0 + 3 * map_bytes);
-    dev_.cta_map_dc = nullptr;
     dev_.subseq_bits = plan_.subseq_bits;
+    dev_.total_subseq = plan_.total_subseq;
     dims_.num_images = m;
     dims_.unstuff_ctas = plan_.map_unstuff.back();
     dims_.subseq_ctas = plan_.map_subseq.back();
@@ -308,7 +313,7 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     return B200JPEG_STATUS_SUCCESS;
 }
 
-int Decoder::launch_all(int first_round, int rounds, bool redo)
+int Decoder::launch_all()
 {
     const int m = dims_.num_images;
     const bool prof = opt_.profile;
@@ -317,16 +322,17 @@ int Decoder::launch_all(int first_round, int rounds, bool redo)
             cudaEventRecord(ev_stage_[i], stream_);
     };
     mark(kStageUnstuff);
-    if (!redo) {
-        B2J_CUDA(cudaMemsetAsync(d_states_.p, 0, sizeof(ImageState) * m, stream_));
-        B2J_CUDA(cudaMemsetAsync(d_redo_.p, 0, 4 * kMaxSyncRounds, stream_));
-        B2J_CUDA(cudaMemsetAsync(d_clean_.p, 0, plan_.clean_bytes, stream_));
-        stat_launches_ += launch_unstuff(dev_, dims_, stream_);
-    }
+    B2J_CUDA(cudaMemsetAsync(d_states_.p, 0, sizeof(ImageState) * m, stream_));
+    B2J_CUDA(cudaMemsetAsync(d_sync_.p, 0, sizeof(SyncCounters), stream_));
+    stat_launches_ += launch_unstuff(dev_, dims_, stream_);
     mark(kStageSync);
-    stat_launches_ += launch_huff_sync(dev_, dims_, stream_, first_round, rounds);
+    const int ns = launch_huff_sync(dev_, dims_, stream_, tail_grid_);
+    if (ns < 0) {
+        std::fprintf(stderr, "b200jpeg: cooperative launch failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+        return B200JPEG_STATUS_CUDA_ERROR;
+    }
+    stat_launches_ += ns;
     mark(kStageWrite);
-    B2J_CUDA(cudaMemsetAsync(d_coef_.p, 0, plan_.coef_elems * sizeof(int16_t), stream_));
     stat_launches_ += launch_huff_write(dev_, dims_, stream_);
     mark(kStageDc);
     stat_launches_ += launch_dc(dev_, dims_, stream_);
@@ -338,7 +344,7 @@ int Decoder::launch_all(int first_round, int rounds, bool redo)
     stage_valid_ = prof;
     B2J_CUDA(cudaGetLastError());
     B2J_CUDA(cudaMemcpyAsync(h_states_.p, d_states_.p, sizeof(ImageState) * m, cudaMemcpyDeviceToHost, stream_));
-    B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(h_states_.p) + sizeof(ImageState) * m, d_redo_.p, 4 * kMaxSyncRounds,
+    B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(h_states_.p) + sizeof(ImageState) * m, d_sync_.p, sizeof(SyncCounters),
         cudaMemcpyDeviceToHost, stream_));
     return 0;
 }
@@ -357,57 +363,23 @@ int Decoder::run(cudaStream_t user_stream, int32_t* statuses)
     B2J_CUDA(cudaEventRecord(ev_in_, user_stream));
     B2J_CUDA(cudaStreamWaitEvent(stream_, ev_in_, 0));
     stat_launches_ = 0;
-    stat_reruns_ = 0;
-    int first = 0, rounds = std::min(adaptive_rounds_, kMaxSyncRounds);
-    int total_rounds = 0;
-    ImageState* hs = static_cast<ImageState*>(h_states_.p);
-    const uint32_t* redo = reinterpret_cast<const uint32_t*>(static_cast<uint8_t*>(h_states_.p) + sizeof(ImageState) * m);
-    bool redo_pass = false;
-    while (true) {
-        int rc = launch_all(first, rounds, redo_pass);
-        if (rc)
-            return rc;
-        B2J_CUDA(cudaStreamSynchronize(stream_));
-        total_rounds = first + rounds;
-        bool not_converged = false;
-        for (int i = 0; i < m; ++i)
-            if (hs[i].error & kErrNotConverged)
-                not_converged = true;
-        if (!not_converged || total_rounds + 8 > kMaxSyncRounds)
-            break;
-        // rare: more Jacobi rounds are needed. Clear the flags, keep the unstuffed data, continue the rounds.
-        for (int i = 0; i < m; ++i) {
-            hs[i].error &= kErrBadMarker; // everything else came from decoding with unsynchronised entry states
-            hs[i].done_slots = 0;
-        }
-        B2J_CUDA(cudaMemcpyAsync(d_states_.p, hs, sizeof(ImageState) * m, cudaMemcpyHostToDevice, stream_));
-        first = total_rounds;
-        rounds = 8;
-        redo_pass = true;
-        ++stat_reruns_;
-    }
-    stat_rounds_ = total_rounds;
-    if (opt_.sync_rounds == 0) {
-        // adapt: first round (>=1) in which no subsequence had to be re-decoded, plus one round of margin
-        int needed = total_rounds;
-        for (int r = 1; r < total_rounds; ++r)
-            if (redo[r] == 0) {
-                needed = r;
-                break;
-            }
-        adaptive_rounds_ = std::max(adaptive_rounds_ - 1, std::min(needed + 2, kMaxSyncRounds));
-    }
+    const int rc = launch_all();
+    if (rc)
+        return rc;
     // host-memory outputs: copy back
     for (const HostOutput& ho : host_outs_) {
         const size_t pitch = align_up(ho.row_bytes, 16);
         B2J_CUDA(cudaMemcpy2DAsync(ho.host, size_t(ho.host_stride), static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch, ho.row_bytes,
             ho.rows, cudaMemcpyDeviceToHost, stream_));
     }
-    if (!host_outs_.empty())
-        B2J_CUDA(cudaStreamSynchronize(stream_));
+    B2J_CUDA(cudaStreamSynchronize(stream_));
+    const ImageState* hs = static_cast<const ImageState*>(h_states_.p);
+    const SyncCounters* sc = reinterpret_cast<const SyncCounters*>(static_cast<const uint8_t*>(h_states_.p) + sizeof(ImageState) * m);
+    stat_rounds_ = 2 + sc->rounds;
+    stat_redone_ = sc->redone;
     for (int i = 0; i < m; ++i) {
         const int bi = planned_to_batch_[i];
-        if (hs[i].error || hs[i].done_slots != plan_.images[i].total_slots)
+        if (hs[i].error || hs[i].done_blocks != plan_.images[i].total_blocks)
             statuses[bi] = B200JPEG_STATUS_CORRUPT_STREAM;
     }
     return B200JPEG_STATUS_SUCCESS;
@@ -423,7 +395,7 @@ void Decoder::get_stats(uint64_t* s) const
     s[3] = plan_.total_blocks;
     s[4] = plan_.total_subseq;
     s[5] = scratch_bytes_;
-    s[6] = stat_reruns_;
+    s[6] = stat_redone_;
     s[7] = plan_.out_bytes;
 }
 
@@ -448,9 +420,21 @@ int64_t Decoder::debug_fetch(int what, int image, int comp, void* dst, size_t ca
     const ImageDesc& im = plan_.images[planned];
     const void* src = nullptr;
     size_t bytes = 0;
-    if (what == 0) {
-        src = static_cast<int16_t*>(d_coef_.p) + im.coef_off;
-        bytes = size_t(im.total_slots) * 2;
+    if (what == 0) { // coefficients: AC from the coefficient array, DC (after prediction) from the DC array
+        const size_t nb = im.total_blocks;
+        bytes = nb * 128;
+        if (bytes > cap)
+            return -2;
+        if (cudaSetDevice(device_) != cudaSuccess ||
+            cudaMemcpy(dst, static_cast<int16_t*>(d_coef_.p) + im.coef_off, bytes, cudaMemcpyDeviceToHost) != cudaSuccess)
+            return -3;
+        std::vector<int16_t> dcv(nb);
+        if (cudaMemcpy(dcv.data(), static_cast<int16_t*>(d_dc_.p) + im.coef_off / 64, nb * 2, cudaMemcpyDeviceToHost) != cudaSuccess)
+            return -3;
+        int16_t* o = static_cast<int16_t*>(dst);
+        for (size_t i = 0; i < nb; ++i)
+            o[i * 64] = dcv[i];
+        return int64_t(bytes);
     } else if (what == 1) {
         if (comp < 0 || comp >= im.ncomp)
             return -1;

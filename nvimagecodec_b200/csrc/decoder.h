@@ -13,8 +13,7 @@ namespace b200jpeg {
 struct DecoderOptions
 {
     bool fancy_upsampling = true; // reference default (libjpeg_turbo_decoder.cpp:250-276)
-    int subseq_bytes = 256;
-    int sync_rounds = 0; // 0 = automatic
+    int subseq_bytes = 128;
     int copy_threads = 4;
     bool profile = false; // record CUDA events between the kernel stages (b200jpeg_decoder_get_stage_times)
 };
@@ -64,7 +63,7 @@ class Decoder
   private:
     int ensure(DevBuf& b, size_t bytes);
     int ensure_pinned(DevBuf& b, size_t bytes);
-    int launch_all(int first_round, int rounds, bool redo);
+    int launch_all();
 
     int device_;
     DecoderOptions opt_;
@@ -81,15 +80,15 @@ class Decoder
     int batch_size_ = 0;
     std::vector<HostOutput> host_outs_;
 
-    DevBuf d_raw_, d_clean_, d_coef_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_redo_,
-        d_out_;
+    DevBuf d_raw_, d_clean_, d_coef_, d_dc_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_wl0_,
+        d_wl1_, d_sync_, d_out_;
     DevBuf h_raw_, h_meta_, h_states_;
     BatchDev dev_{};
     LaunchDims dims_{};
     size_t scratch_bytes_ = 0;
 
-    uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_reruns_ = 0;
-    int adaptive_rounds_ = 0;
+    uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_redone_ = 0;
+    int tail_grid_ = 0;
 };
 
 } // namespace b200jpeg

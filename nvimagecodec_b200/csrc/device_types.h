@@ -10,24 +10,52 @@
 
 namespace b200jpeg {
 
-constexpr int kLutBits = 10;          // first-level Huffman lookup width
-constexpr int kSubseqCta = 128;       // threads per CTA in the subsequence kernels (one subsequence per thread)
+constexpr int kLutBits = 11;          // first-level Huffman lookup width
+constexpr int kLutSize = 1 << kLutBits;
+constexpr int kSubseqCta = 256;       // threads per CTA in the subsequence kernels (one subsequence per thread)
 constexpr int kUnstuffThreads = 256;  // threads per CTA in the unstuffing kernels
 constexpr int kUnstuffBytesPerThread = 16;
 constexpr int kChunkBytes = kUnstuffThreads * kUnstuffBytesPerThread; // raw bytes per unstuff CTA
 constexpr int kIdctCta = 128;        // threads per CTA, one 8x8 block per thread
-constexpr int kColorCta = 256;       // threads per CTA, 16 pixels per thread
+constexpr int kColorCta = 128;       // threads per CTA: 4 warps, each warp one tile of 512 pixels x (1|2) rows
+constexpr int kColorTilePx = 512;    // pixels per warp tile (16 per lane)
 constexpr int kDcCta = 512;          // threads per CTA, one MCU per thread per iteration
 constexpr int kMaxBlocksPerMcu = 6;   // luma up to 2x2 + Cb + Cr
+constexpr int kMaxTabSlots = 6;       // distinct Huffman tables one image can reference (3 components x DC/AC)
 
 // Decode table derived from one DHT table (reference: d_derived_tbl, external/libjpeg-turbo/jdhuff.h:27-51 and
-// jpeg_make_d_derived_tbl, jdhuff.c:143-285; we use a 10-bit first level instead of 8 -- same symbols come out).
+// jpeg_make_d_derived_tbl, jdhuff.c:143-285).  We use an 11-bit first level instead of 8 and store pre-digested entries
+//   entry = code_length | size << 5 | zadv << 9
+// size = number of value bits that follow the code; zadv = how far the zigzag position advances (DC: 1; AC run/size:
+// run + 1; ZRL: 16; EOB: 64).  entry == 0: the code is longer than kLutBits (or invalid) -> maxcode walk.
+// The same symbols come out as with the reference's tables.
 struct DevHuffTable
 {
-    uint16_t lut[1 << kLutBits]; // (code length << 8) | symbol ; 0 => code longer than kLutBits (or invalid)
-    int32_t maxcode[18];         // largest code of each length, -1 if none
-    int32_t valoffset[18];       // vals[] index = code + valoffset[len]
+    uint16_t lut[kLutSize];
+    int32_t maxcode[18];   // largest code of each length, -1 if none
+    int32_t valoffset[18]; // vals[] index = code + valoffset[len]
     uint8_t vals[256];
+    int32_t is_dc;
+    int32_t pad_[3];       // sizeof == 4512, a multiple of 16
+};
+constexpr uint32_t kHuffTableU16 = sizeof(DevHuffTable) / 2; // stride of the table pool in uint16 units
+
+B2J_HD uint32_t huff_entry(int len, int sym, bool is_dc)
+{
+    const int s = sym & 15;
+    int zadv = 1;
+    if (!is_dc) {
+        const int r = sym >> 4;
+        zadv = s ? r + 1 : (r == 15 ? 16 : 64);
+    }
+    return uint32_t(len) | (uint32_t(s) << 5) | (uint32_t(zadv) << 9);
+}
+
+// Table selector of one block position inside the MCU: offsets (uint16 units from the LUT base the kernel uses) and pool
+// indices (for the long-code walk) of the DC and AC tables of that block's component.
+struct alignas(16) TabSel
+{
+    uint32_t dc_off, ac_off, dc_idx, ac_idx;
 };
 
 // Per-image descriptor, built on the host, read-only on the device.
@@ -40,17 +68,22 @@ struct ImageDesc
     int32_t hmax, vmax;
     int32_t mcus_x, mcus_y;
     int32_t bpm;          // blocks per MCU
-    int32_t mcu_slots;    // bpm * 64
     int32_t restart_interval; // MCUs per restart segment (0 => single segment)
     int32_t num_segments;
-    uint32_t seg_slots;   // coefficient slots per full segment (restart_interval * mcu_slots, or total)
-    uint32_t total_slots; // mcus * mcu_slots
+    uint32_t seg_blocks;   // blocks per full segment (restart_interval * bpm, or total)
+    uint32_t total_blocks; // mcus * bpm
     int32_t wib[3], hib[3];   // MCU-padded block grid per component
     int32_t ds_w[3], ds_h[3]; // downsampled_width / height (jdinput.c:130-135)
     int32_t blk_first[3];     // first block-in-MCU index of each component
     uint8_t blk_comp[8];      // component of block j in the MCU
     int32_t qt[3];            // quant table pool index per component
-    int32_t dc_tab[3], ac_tab[3]; // Huffman table pool index per component
+
+    // Huffman tables: per block-in-MCU selectors, relative to the global pool (tail kernel) and to the per-CTA shared
+    // memory copy (main kernels); tab_pool lists the distinct pool tables to stage, slot s -> shared offset s * kLutSize
+    TabSel tabsel_g[kMaxBlocksPerMcu];
+    TabSel tabsel_s[kMaxBlocksPerMcu];
+    int32_t ntabs;
+    int32_t tab_pool[kMaxTabSlots];
 
     // entropy-coded bytes
     uint64_t raw_off;     // byte offset in the batch raw buffer (16-byte aligned)
@@ -62,12 +95,13 @@ struct ImageDesc
     uint32_t seg_first;   // index into the segment-start pool; entries [seg_first, seg_first + num_segments]
 
     // intermediates
-    uint64_t coef_off;        // int16 units, blocks in MCU scan order
+    uint64_t coef_off;        // int16 units, blocks in MCU scan order (coef_off / 64 = first block in the DC array)
     uint64_t plane_off[3];    // bytes
     int32_t plane_pitch[3];
     uint32_t idct_cta_first, idct_cta_count;
     uint32_t color_cta_first, color_cta_count;
-    uint32_t dc_cta;          // unused for now
+    int32_t color_rows;       // row groups the colour kernel walks (height, or ds_h + 1 row pairs when vmax == 2)
+    int32_t color_xtiles;     // warp tiles per row group
 
     // output
     uint8_t* out;
@@ -82,18 +116,25 @@ struct ImageState
     uint32_t clean_len;     // unstuffed bytes
     uint32_t marker_count;  // RSTn markers seen
     uint32_t error;         // bit flags, see kErr*
-    uint32_t done_slots;    // set by the thread that completes the last block (== total_slots when the scan is complete)
+    uint32_t done_blocks;   // set by the thread that completes the last block (== total_blocks when the scan is complete)
 };
 
 constexpr uint32_t kErrBadMarker = 1;     // unexpected marker inside entropy-coded data / wrong RSTn order / count
 constexpr uint32_t kErrBadCode = 2;       // invalid Huffman code on the synchronised path
-constexpr uint32_t kErrNotConverged = 4;  // subsequence synchronisation incomplete (host re-runs more rounds)
+constexpr uint32_t kErrNotConverged = 4;  // subsequence synchronisation incomplete
 constexpr uint32_t kErrOverrun = 8;       // decode ran past the end of a segment / image
 
-// Subsequence record after a sync round.
-struct SubseqRec
+// State of the Huffman decoder between two symbols, packed in 64 bits: bit position | (block-in-MCU * 64 + zigzag index) << 32
+B2J_HD unsigned long long pack_state(uint32_t p, uint32_t slot) { return (unsigned long long)p | ((unsigned long long)slot << 32); }
+
+constexpr int kMaxTailRounds = 512;
+
+struct SyncCounters // device-side bookkeeping of the synchronisation rounds
 {
-    uint32_t n_abs; // bit31: value is absolute (relative to image start), else relative to the entry; low 31 bits: slots
+    uint32_t count[3];    // work-list lengths (rotating: round r reads [r % 3], appends to [(r + 1) % 3])
+    uint32_t rounds;      // tail rounds executed
+    uint32_t redone;      // subsequences re-decoded in tail rounds
+    uint32_t pad_[3];
 };
 
 struct BatchDev // pointers handed to every kernel
@@ -107,19 +148,21 @@ struct BatchDev // pointers handed to every kernel
     const uint16_t* quant; // pool of 64-entry natural-order tables
     uint32_t* seg_start;   // pool
     uint64_t* chunk_counts; // per unstuff chunk: kept bytes | markers << 32  (then exclusive-scanned in place)
-    unsigned long long* sub_exit;   // per subsequence: p | slot << 32
-    unsigned long long* sub_entry;  // entry used by the last decode of that subsequence
-    uint32_t* sub_rec;      // SubseqRec
-    uint32_t* sub_abs;      // scanned absolute exit slot
-    uint32_t* redo_counter; // [round]
-    int16_t* coef;
+    unsigned long long* sub_exit;   // per subsequence: decoder state after its last symbol
+    unsigned long long* sub_entry;  // state the last decode of that subsequence started from
+    uint32_t* sub_rec;      // coefficient slots consumed by that decode; bit31: absolute (a restart boundary was crossed)
+    uint32_t* sub_abs;      // inclusive scan of sub_rec: absolute slot count at the subsequence's exit
+    uint32_t* worklist[2];  // subsequences whose entry changed (global subsequence indices)
+    SyncCounters* sync;
+    int16_t* coef;          // AC coefficients, natural order, 64 per block (slot 0 unused: the DC lives in dc[])
+    int16_t* dc;            // per block: DC difference after the write pass, DC value after the DC scan
     uint8_t* planes;
     const uint32_t* cta_map_unstuff; // prefix arrays: first CTA of each image (+ total at [num_images])
     const uint32_t* cta_map_subseq;
     const uint32_t* cta_map_idct;
     const uint32_t* cta_map_color;
-    const uint32_t* cta_map_dc;
     int32_t subseq_bits;   // bits per subsequence
+    uint32_t total_subseq;
 };
 
 } // namespace b200jpeg

@@ -1,12 +1,12 @@
-// jpeg_math.cuh -- the arithmetic of the b200jpeg decode path as host+device inline functions.
-// Each function is the per-thread body of one kernel in decode_kernels.cu; compiled with g++ (B2J_HD = inline) the same
-// bodies run in the CPU emulation used by the "not gpu" tests (tests/emu), so the logic is checked without a GPU.
+// jpeg_math.cuh -- sample-domain arithmetic of the b200jpeg decode path as host+device inline functions: dequantisation
+// + integer "islow" IDCT of one block, and chroma upsampling + YCbCr->RGB of one 16-pixel unit.  The CUDA kernels in
+// decode_kernels.cu wrap these bodies with the memory staging; compiled with g++ (B2J_HD = inline) the same bodies run
+// in the CPU emulation used by the "not gpu" tests (tests/emu).
 //
 // Reference arithmetic restated here ("ljt/" = external/libjpeg-turbo in the reference tree):
-//   Huffman decode      ljt/jdhuff.c decode_mcu_slow:552-660, HUFF_EXTEND:483-488, jpeg_huff_decode:398-450
 //   dequant + IDCT      ljt/jidctint.c:173-410 (_jpeg_idct_islow), range limit ljt/jdmaster.c:386-407
-//   upsampling          ljt/jdsample.c h2v1_fancy:276 h1v2_fancy:316 h2v2_fancy:362 h2v1:205 h2v2:233,
-//                       edge rows ljt/jdmainct.c:217-250
+//   upsampling          ljt/jdsample.c h2v1_fancy:276 h1v2_fancy:316 h2v2_fancy:362 h2v1:205 h2v2:233, selector :414-535,
+//                       edge rows ljt/jdmainct.c:217-250; merged (non-fancy) path ljt/jdmrgext.c:24-184
 //   colour              ljt/jdcolor.c:215-251, ljt/jdcolext.c:30-76
 #pragma once
 #include "device_types.h"
@@ -16,250 +16,22 @@
 
 namespace b200jpeg {
 
-#if defined(__CUDA_ARCH__)
-#define B2J_ZZ(i) c_zigzag[i]
-static __constant__ uint8_t c_zigzag[80] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6,
-    7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55,
-    62, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};
-#else
-#if defined(__CUDACC__)
-static __constant__ uint8_t c_zigzag[80] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6,
-    7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55,
-    62, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};
-#endif
-static const uint8_t h_zigzag[80] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6,
-    7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55,
-    62, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};
-#define B2J_ZZ(i) h_zigzag[i]
-#endif
-
-B2J_HD uint32_t bswap32(uint32_t v)
-{
-#if defined(__CUDA_ARCH__)
-    return __byte_perm(v, 0, 0x0123);
-#else
-    return __builtin_bswap32(v);
-#endif
-}
-
 // ------------------------------------------------------------------------------------------------------------------
-// Bit window over the unstuffed stream: 32 valid bits starting at absolute bit position p (MSB first).
-// ------------------------------------------------------------------------------------------------------------------
-struct BitWindow
-{
-    const uint32_t* words;
-    uint32_t idx;
-    uint32_t w0, w1;
-};
-
-B2J_HD void bw_init(BitWindow& bw, const uint32_t* words)
-{
-    bw.words = words;
-    bw.idx = 0xFFFFFFF0u;
-    bw.w0 = bw.w1 = 0;
-}
-
-B2J_HD uint32_t bw_peek(BitWindow& bw, uint32_t p)
-{
-    const uint32_t i = p >> 5;
-    if (i != bw.idx) {
-        if (i == bw.idx + 1) {
-            bw.w0 = bw.w1;
-            bw.w1 = bswap32(bw.words[i + 1]);
-        } else {
-            bw.w0 = bswap32(bw.words[i]);
-            bw.w1 = bswap32(bw.words[i + 1]);
-        }
-        bw.idx = i;
-    }
-    const uint32_t sh = p & 31;
-#if defined(__CUDA_ARCH__)
-    return __funnelshift_l(bw.w1, bw.w0, sh);
-#else
-    return sh ? (bw.w0 << sh) | (bw.w1 >> (32 - sh)) : bw.w0;
-#endif
-}
-
-// One Huffman symbol from the top bits of win. Returns symbol, sets len (1..16). ok=false on an invalid code.
-B2J_HD int huff_symbol(const DevHuffTable* t, uint32_t win, int& len, bool& ok)
-{
-    const uint32_t e = t->lut[win >> (32 - kLutBits)];
-    if (e) {
-        len = int(e >> 8);
-        return int(e & 255);
-    }
-    for (int l = kLutBits + 1; l <= 16; ++l) {
-        const int code = int(win >> (32 - l));
-        if (code <= t->maxcode[l]) {
-            len = l;
-            return t->vals[(code + t->valoffset[l]) & 255];
-        }
-    }
-    ok = false;
-    len = 16;
-    return 0;
-}
-
-B2J_HD int huff_extend(int x, int s) { return x < (1 << (s - 1)) ? x - (1 << s) + 1 : x; }
-
-struct SubseqState
-{
-    uint32_t p;    // bit position of the next symbol (relative to the image's unstuffed stream)
-    uint32_t slot; // coefficient slot inside the current MCU: block_in_mcu * 64 + zigzag index
-    uint32_t n;    // slots consumed: absolute (from image start) if abs, else relative to the entry of this decode
-    bool abs;
-};
-
-// ------------------------------------------------------------------------------------------------------------------
-// Decode every symbol that starts inside subsequence k of image `im`, beginning in state `s`.
-// WRITE=false: synchronisation pass (nothing is stored).  WRITE=true: final pass, s.abs must be true; coefficients are
-// written de-zigzagged into the image's coefficient area (DC still as the difference).
-// Restart segments: segment g covers unstuffed bytes [S[g], S[g+1]); crossing into a new segment makes the state exact.
-// ------------------------------------------------------------------------------------------------------------------
-template <bool WRITE>
-B2J_HD void decode_subsequence(const BatchDev& b, const ImageDesc& im, ImageState* st, uint32_t k, uint32_t clean_len, SubseqState& s)
-{
-    const uint32_t clean_bits = clean_len * 8u;
-    uint32_t end = (k + 1) * uint32_t(b.subseq_bits);
-    if (end > clean_bits)
-        end = clean_bits;
-    const uint32_t* S = b.seg_start + im.seg_first;
-    const int nseg = im.num_segments;
-
-    // locate the segment containing p
-    int g = 0;
-    if (nseg > 1) {
-        int lo = 0, hi = nseg - 1;
-        const uint32_t pb = s.p >> 3;
-        while (lo < hi) {
-            const int mid = (lo + hi + 1) >> 1;
-            if (S[mid] <= pb)
-                lo = mid;
-            else
-                hi = mid - 1;
-        }
-        g = lo;
-    }
-    if (!s.abs && s.p == S[g] * 8u) { // exactly at a segment start: the state is known
-        s.abs = true;
-        s.n = uint32_t(g) * im.seg_slots;
-        s.slot = 0;
-    }
-    bool last = (g == nseg - 1);
-    uint32_t B = last ? clean_bits : S[g + 1] * 8u;
-    uint32_t seg_end = last ? im.total_slots : uint32_t(g + 1) * im.seg_slots;
-
-    BitWindow bw;
-    bw_init(bw, reinterpret_cast<const uint32_t*>(b.clean + im.clean_off));
-    int16_t* coef = WRITE ? b.coef + im.coef_off : nullptr;
-    uint32_t err = 0;
-
-    while (true) {
-        bool advance = false;
-        if (s.abs && s.n >= seg_end) { // segment complete: the rest of its bytes is padding
-            if (last) {
-                if (WRITE)
-                    st->done_slots = s.n;
-                break;
-            }
-            advance = true;
-        } else if (s.p >= B) {
-            if (last)
-                break;
-            if (WRITE)
-                err |= kErrOverrun; // segment data ended before its blocks were complete
-            advance = true;
-        }
-        if (!advance) {
-            if (s.p >= end)
-                break;
-            const uint32_t win = bw_peek(bw, s.p);
-            const uint32_t blk = s.slot >> 6;
-            uint32_t z = s.slot & 63;
-            const int comp = im.blk_comp[blk];
-            const DevHuffTable* t = b.huff + (z == 0 ? im.dc_tab[comp] : im.ac_tab[comp]);
-            int len;
-            bool ok = true;
-            const int sym = huff_symbol(t, win, len, ok);
-            const int sz = sym & 15;
-            const uint32_t total = uint32_t(len + sz);
-            if (s.p + total > B) { // symbol would cross the segment end: it was padding, not data
-                if (last) {
-                    if (WRITE)
-                        err |= kErrOverrun;
-                    s.p = B;
-                    break;
-                }
-                advance = true;
-            } else {
-                if (WRITE && !ok)
-                    err |= kErrBadCode;
-                int val = 0;
-                if (sz)
-                    val = huff_extend(int((win << len) >> (32 - sz)), sz);
-                uint32_t adv;
-                if (z == 0) {
-                    if (WRITE)
-                        coef[(s.n & ~63u)] = int16_t(val);
-                    adv = 1;
-                } else {
-                    const int r = sym >> 4;
-                    if (sz) {
-                        z += r;
-                        if (z > 63) {
-                            z = 63;
-                            if (WRITE)
-                                err |= kErrBadCode;
-                        }
-                        if (WRITE)
-                            coef[(s.n & ~63u) + B2J_ZZ(z)] = int16_t(val);
-                        adv = z + 1 - (s.slot & 63);
-                    } else if (r == 15) {
-                        adv = 16;
-                        if ((s.slot & 63) + 16 > 64)
-                            adv = 64 - (s.slot & 63);
-                    } else {
-                        adv = 64 - (s.slot & 63); // EOB
-                    }
-                }
-                s.slot += adv;
-                s.n += adv;
-                if (s.slot >= uint32_t(im.mcu_slots))
-                    s.slot = 0;
-                s.p += total;
-            }
-        }
-        if (advance) {
-            ++g;
-            s.p = S[g] * 8u;
-            s.slot = 0;
-            s.abs = true;
-            s.n = uint32_t(g) * im.seg_slots;
-            last = (g == nseg - 1);
-            B = last ? clean_bits : S[g + 1] * 8u;
-            seg_end = last ? im.total_slots : uint32_t(g + 1) * im.seg_slots;
-        }
-    }
-    if (WRITE && err) {
-#if defined(__CUDA_ARCH__)
-        atomicOr(&st->error, err);
-#else
-        st->error |= err;
-#endif
-    }
-}
-
-// ------------------------------------------------------------------------------------------------------------------
-// Dequantise + 8x8 inverse DCT ("islow") of one block: in[64] natural-order coefficients, q[64] natural-order quant
-// values, out = 8 rows of 8 samples packed little-endian in two uint32 each.  int32 arithmetic: exact for every stream
-// an 8-bit encoder can produce (the reference's JLONG is wider only for corrupt input).
+// Dequantise + 8x8 inverse DCT ("islow") of one block: in[64] natural-order coefficients (in[0] ignored, the DC value is
+// passed separately), q[64] natural-order quant values, out = 8 rows of 8 samples packed little-endian in two uint32
+// each.  int32 arithmetic: exact for every stream an 8-bit encoder can produce (the reference's JLONG is wider only for
+// corrupt input).
 // ------------------------------------------------------------------------------------------------------------------
 B2J_HD int idct_descale(int x, int n) { return (x + (1 << (n - 1))) >> n; }
 
+// range_limit[(x) & RANGE_MASK] of the reference (ljt/jdmaster.c:386-407): a clamp of x + 128 to [0, 255] for
+// x in [-512, 511], and the table's wrap-around outside of that
 B2J_HD uint32_t idct_range_limit(int v)
 {
-    const int i = v & 1023;
-    return uint32_t(i < 128 ? i + 128 : (i < 512 ? 255 : (i < 896 ? 0 : i - 896)));
+    int t = int(uint32_t(v) << 22) >> 22; // sign-extend the low 10 bits: wraps exactly like the & 1023 table index
+    t += 128;
+    t = t < 0 ? 0 : (t > 255 ? 255 : t);
+    return uint32_t(t);
 }
 
 B2J_HD void idct_1d(int i0, int i1, int i2, int i3, int i4, int i5, int i6, int i7, int* o)
@@ -302,13 +74,14 @@ B2J_HD void idct_1d(int i0, int i1, int i2, int i3, int i4, int i5, int i6, int 
     o[4] = tmp13 - tmp0;
 }
 
-B2J_HD void idct_block(const int16_t* in, const uint16_t* q, uint32_t* out /*[16]*/)
+B2J_HD void idct_block(const int16_t* in, int dcval, const uint16_t* q, uint32_t* out /*[16]*/)
 {
     int ws[64];
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         int o[8];
-        idct_1d(in[c] * q[c], in[8 + c] * q[8 + c], in[16 + c] * q[16 + c], in[24 + c] * q[24 + c], in[32 + c] * q[32 + c],
+        const int i0 = (c == 0 ? dcval : int(in[c])) * q[c];
+        idct_1d(i0, in[8 + c] * q[8 + c], in[16 + c] * q[16 + c], in[24 + c] * q[24 + c], in[32 + c] * q[32 + c],
             in[40 + c] * q[40 + c], in[48 + c] * q[48 + c], in[56 + c] * q[56 + c], o);
 #pragma unroll
         for (int r = 0; r < 8; ++r)
@@ -329,10 +102,22 @@ B2J_HD void idct_block(const int16_t* in, const uint16_t* q, uint32_t* out /*[16
     }
 }
 
-// Body of the IDCT kernel: thread u of image im handles one block, enumerated in plane order (component, block row,
-// block column) so that neighbouring threads write neighbouring 8-byte row pieces.
-B2J_HD void idct_thread(const BatchDev& b, const ImageDesc& im, uint32_t u)
+// Where block u (plane order: component, block row, block column) of image im comes from and goes to.
+struct IdctBlockRef
 {
+    int comp;          // -1: no such block
+    uint32_t src_blk;  // block index in MCU scan order (relative to the image)
+    uint64_t dst;      // byte offset of the block's top-left sample in the planes buffer
+    int pitch;
+};
+
+B2J_HD IdctBlockRef idct_locate(const ImageDesc& im, uint32_t u)
+{
+    IdctBlockRef r;
+    r.comp = -1;
+    r.src_blk = 0;
+    r.dst = 0;
+    r.pitch = 0;
     int c = 0;
     uint32_t rem = u;
     for (; c < im.ncomp_out; ++c) {
@@ -342,74 +127,29 @@ B2J_HD void idct_thread(const BatchDev& b, const ImageDesc& im, uint32_t u)
         rem -= nb;
     }
     if (c >= im.ncomp_out)
-        return;
+        return r;
     const int bx = int(rem % uint32_t(im.wib[c])), by = int(rem / uint32_t(im.wib[c]));
     const int mcu = (by / im.vs[c]) * im.mcus_x + (bx / im.hs[c]);
     const int j = im.blk_first[c] + (by % im.vs[c]) * im.hs[c] + (bx % im.hs[c]);
-    const int16_t* in = b.coef + im.coef_off + (uint64_t(mcu) * im.bpm + j) * 64;
-    const uint16_t* q = b.quant + im.qt[c] * 64;
-    alignas(16) int16_t blk[64];
-    const uint4* in4 = reinterpret_cast<const uint4*>(in);
-    uint4* blk4 = reinterpret_cast<uint4*>(blk);
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-        blk4[i] = in4[i];
-    uint32_t out[16];
-    idct_block(blk, q, out);
-    uint8_t* dst = b.planes + im.plane_off[c] + uint64_t(by) * 8 * im.plane_pitch[c] + bx * 8;
-#pragma unroll
-    for (int r = 0; r < 8; ++r)
-        *reinterpret_cast<uint2*>(dst + r * im.plane_pitch[c]) = make_uint2(out[2 * r], out[2 * r + 1]);
+    r.comp = c;
+    r.src_blk = uint32_t(mcu) * uint32_t(im.bpm) + uint32_t(j);
+    r.pitch = im.plane_pitch[c];
+    r.dst = im.plane_off[c] + uint64_t(by) * 8 * uint64_t(r.pitch) + uint64_t(bx) * 8;
+    return r;
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// Upsampling + colour conversion.
+// Upsampling + colour conversion of one unit: 16 horizontally adjacent pixels of one output row (VY == 1) or of the
+// output row pair (2q+1, 2q+2) (VY == 2; this pairing needs only chroma rows q and q+1).
 // ------------------------------------------------------------------------------------------------------------------
-B2J_HD int upsampled_sample(const BatchDev& b, const ImageDesc& im, int c, int x, int y)
+B2J_HD int clamp_u8(int v)
 {
-    const uint8_t* P = b.planes + im.plane_off[c];
-    const int pitch = im.plane_pitch[c];
-    const int hx = im.hmax / im.hs[c], vy = im.vmax / im.vs[c];
-    if (hx == 1 && vy == 1)
-        return P[uint64_t(y) * pitch + x];
-    const bool fancy = im.fancy != 0;
-    if (vy == 1) { // h2v1
-        const uint8_t* in = P + uint64_t(y) * pitch;
-        const int cx = x >> 1;
-        if (!(fancy && im.ds_w[c] > 2))
-            return in[cx];
-        if (!(x & 1))
-            return cx == 0 ? in[0] : (in[cx] * 3 + in[cx - 1] + 1) >> 2;
-        return cx == im.ds_w[c] - 1 ? in[cx] : (in[cx] * 3 + in[cx + 1] + 2) >> 2;
-    }
-    const int r = y >> 1;
-    int far_row = (y & 1) ? r + 1 : r - 1;
-    if (far_row < 0)
-        far_row = 0;
-    if (far_row > im.ds_h[c] - 1)
-        far_row = im.ds_h[c] - 1;
-    const uint8_t* n0 = P + uint64_t(r) * pitch;
-    const uint8_t* n1 = P + uint64_t(far_row) * pitch;
-    if (hx == 1) { // h1v2
-        if (!fancy)
-            return n0[x];
-        return (n0[x] * 3 + n1[x] + ((y & 1) ? 2 : 1)) >> 2;
-    }
-    const int cx = x >> 1; // h2v2
-    if (!(fancy && im.ds_w[c] > 2))
-        return n0[cx];
-    const int cs = n0[cx] * 3 + n1[cx];
-    if (!(x & 1)) {
-        if (cx == 0)
-            return (cs * 4 + 8) >> 4;
-        return (cs * 3 + (n0[cx - 1] * 3 + n1[cx - 1]) + 8) >> 4;
-    }
-    if (cx == im.ds_w[c] - 1)
-        return (cs * 4 + 7) >> 4;
-    return (cs * 3 + (n0[cx + 1] * 3 + n1[cx + 1]) + 7) >> 4;
+#if defined(__CUDA_ARCH__)
+    return __vimin_s32_relu(v, 255);
+#else
+    return v < 0 ? 0 : (v > 255 ? 255 : v);
+#endif
 }
-
-B2J_HD int clamp_u8(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
 
 B2J_HD void ycc_to_rgb(int y, int cb, int cr, int& r, int& g, int& bl)
 {
@@ -419,79 +159,184 @@ B2J_HD void ycc_to_rgb(int y, int cb, int cr, int& r, int& g, int& bl)
     g = clamp_u8(y + ((-22554 * xcb - 46802 * xcr + 32768) >> 16));
 }
 
-constexpr int kColorPixelsPerThread = 16;
-
-// Body of the colour kernel: thread u of image im produces 16 consecutive pixels of one output row.
-B2J_HD void color_thread(const BatchDev& b, const ImageDesc& im, uint32_t u)
+B2J_HD void load16(const uint8_t* p, int* v) // p is 8-byte aligned
 {
-    const uint32_t units_per_row = (uint32_t(im.width) + kColorPixelsPerThread - 1) / kColorPixelsPerThread;
-    const int y = int(u / units_per_row);
-    if (y >= im.height)
-        return;
-    const int x0 = int(u % units_per_row) * kColorPixelsPerThread;
-    const int npx = im.width - x0 < kColorPixelsPerThread ? im.width - x0 : kColorPixelsPerThread;
-    const int fmt = im.out_fmt;
-    uint8_t c0[kColorPixelsPerThread], c1[kColorPixelsPerThread], c2[kColorPixelsPerThread];
-    const bool want_rgb = (fmt != 7);
-    const bool bgr = (fmt == 5 || fmt == 6);
-#pragma unroll 4
-    for (int i = 0; i < kColorPixelsPerThread; ++i) {
-        int r = 0, g = 0, bl = 0;
-        if (i < npx) {
-            const int yy = upsampled_sample(b, im, 0, x0 + i, y);
-            if (!want_rgb || im.ncomp == 1)
-                r = g = bl = yy;
-            else
-                ycc_to_rgb(yy, upsampled_sample(b, im, 1, x0 + i, y), upsampled_sample(b, im, 2, x0 + i, y), r, g, bl);
-        }
-        c0[i] = uint8_t(bgr ? bl : r);
-        c1[i] = uint8_t(g);
-        c2[i] = uint8_t(bgr ? r : bl);
-    }
-    if (fmt == 4 || fmt == 6) { // interleaved
-        uint8_t* dst = im.out + int64_t(y) * im.out_stride + int64_t(x0) * 3;
-        if (npx == kColorPixelsPerThread && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-            uint32_t w[12];
+    const uint2 a = *reinterpret_cast<const uint2*>(p), c = *reinterpret_cast<const uint2*>(p + 8);
+    const uint32_t w[4] = {a.x, a.y, c.x, c.y};
 #pragma unroll
-            for (int k = 0; k < 12; ++k) {
-                uint32_t v = 0;
+    for (int i = 0; i < 16; ++i)
+        v[i] = int((w[i >> 2] >> (8 * (i & 3))) & 255u);
+}
+
+// chroma samples [c0 - 1, c0 + N] of a plane row with the column index clamped to [0, dsw - 1]; v[0] is column c0 - 1
+template <int N>
+B2J_HD void load_chroma_row(const uint8_t* row, int c0, int dsw, int* v /*[N + 2]*/)
+{
+    if (c0 >= 1 && c0 + N <= dsw - 1) {
+        v[0] = row[c0 - 1];
+        v[N + 1] = row[c0 + N];
+        if constexpr (N == 8) {
+            const uint2 a = *reinterpret_cast<const uint2*>(row + c0);
 #pragma unroll
-                for (int bb = 0; bb < 4; ++bb) {
-                    const int idx = k * 4 + bb, px = idx / 3, ch = idx % 3;
-                    const uint32_t s = ch == 0 ? c0[px] : (ch == 1 ? c1[px] : c2[px]);
-                    v |= s << (8 * bb);
-                }
-                w[k] = v;
+            for (int i = 0; i < 4; ++i) {
+                v[1 + i] = int((a.x >> (8 * i)) & 255u);
+                v[5 + i] = int((a.y >> (8 * i)) & 255u);
             }
-            uint4* d4 = reinterpret_cast<uint4*>(dst);
-            d4[0] = make_uint4(w[0], w[1], w[2], w[3]);
-            d4[1] = make_uint4(w[4], w[5], w[6], w[7]);
-            d4[2] = make_uint4(w[8], w[9], w[10], w[11]);
         } else {
-            for (int i = 0; i < npx; ++i) {
-                dst[3 * i] = c0[i];
-                dst[3 * i + 1] = c1[i];
-                dst[3 * i + 2] = c2[i];
+            load16(row + c0, v + 1);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < N + 2; ++i) {
+            int c = c0 - 1 + i;
+            c = c < 0 ? 0 : (c > dsw - 1 ? dsw - 1 : c);
+            v[i] = row[c];
+        }
+    }
+}
+
+// Full-resolution chroma of the unit for one component: up[r][i], r < VY, i < 16.
+template <int HX, int VY>
+B2J_HD void upsample_unit(const uint8_t* P, int pitch, int dsw, int dsh, bool fancy, int q, int x0, int up[][16])
+{
+    constexpr int NC = 16 / HX;
+    const int c0 = x0 / HX;
+    if constexpr (VY == 1) {
+        const uint8_t* row = P + uint64_t(q) * pitch;
+        if constexpr (HX == 1) {
+            load16(row + c0, up[0]);
+        } else {
+            int a[NC + 2];
+            load_chroma_row<NC>(row, c0, dsw, a);
+            const bool f = fancy && dsw > 2;
+#pragma unroll
+            for (int i = 0; i < NC; ++i) {
+                up[0][2 * i] = f ? (3 * a[i + 1] + a[i] + 1) >> 2 : a[i + 1];
+                up[0][2 * i + 1] = f ? (3 * a[i + 1] + a[i + 2] + 2) >> 2 : a[i + 1];
             }
         }
-    } else { // planar (P_RGB / P_BGR: 3 planes; P_Y: 1 plane)
-        const int nplanes = want_rgb ? 3 : 1;
-        for (int pl = 0; pl < nplanes; ++pl) {
-            uint8_t* dst = im.out + (int64_t(pl) * im.height + y) * im.out_stride + x0;
-            const uint8_t* src = pl == 0 ? c0 : (pl == 1 ? c1 : c2);
-            if (npx == kColorPixelsPerThread && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-                uint32_t w[4];
+    } else {
+        int ra = q < 0 ? 0 : (q > dsh - 1 ? dsh - 1 : q), rb = q + 1 > dsh - 1 ? dsh - 1 : q + 1;
+        const uint8_t* rowa = P + uint64_t(ra) * pitch;
+        const uint8_t* rowb = P + uint64_t(rb) * pitch;
+        if constexpr (HX == 1) {
+            int a[16], bb[16];
+            load16(rowa + c0, a);
+            load16(rowb + c0, bb);
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    w[k] = uint32_t(src[4 * k]) | (uint32_t(src[4 * k + 1]) << 8) | (uint32_t(src[4 * k + 2]) << 16) |
-                           (uint32_t(src[4 * k + 3]) << 24);
-                *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+            for (int i = 0; i < 16; ++i) {
+                up[0][i] = fancy ? (3 * a[i] + bb[i] + 2) >> 2 : a[i];
+                up[1][i] = fancy ? (3 * bb[i] + a[i] + 1) >> 2 : bb[i];
+            }
+        } else {
+            int a[NC + 2], bb[NC + 2];
+            load_chroma_row<NC>(rowa, c0, dsw, a);
+            load_chroma_row<NC>(rowb, c0, dsw, bb);
+            const bool f = fancy && dsw > 2;
+            if (f) {
+                int ca[NC + 2], cb[NC + 2];
+#pragma unroll
+                for (int i = 0; i < NC + 2; ++i) {
+                    ca[i] = 3 * a[i] + bb[i];
+                    cb[i] = 3 * bb[i] + a[i];
+                }
+#pragma unroll
+                for (int i = 0; i < NC; ++i) {
+                    up[0][2 * i] = (3 * ca[i + 1] + ca[i] + 8) >> 4;
+                    up[0][2 * i + 1] = (3 * ca[i + 1] + ca[i + 2] + 7) >> 4;
+                    up[1][2 * i] = (3 * cb[i + 1] + cb[i] + 8) >> 4;
+                    up[1][2 * i + 1] = (3 * cb[i + 1] + cb[i + 2] + 7) >> 4;
+                }
             } else {
-                for (int i = 0; i < npx; ++i)
-                    dst[i] = src[i];
+#pragma unroll
+                for (int i = 0; i < NC; ++i) {
+                    up[0][2 * i] = up[0][2 * i + 1] = a[i + 1];
+                    up[1][2 * i] = up[1][2 * i + 1] = bb[i + 1];
+                }
             }
         }
     }
 }
+
+// px[r * 16 + i] = c0 | c1 << 8 | c2 << 16 of pixel x0 + i of output row yrow[r]; channel order already swapped for BGR
+// outputs, Y replicated for gray streams; Y-only output (P_Y) has just c0.  yrow[r] < 0 marks a row outside the image.
+template <int HX, int VY>
+B2J_HD void color_unit(const BatchDev& b, const ImageDesc& im, int q, int x0, uint32_t* px, int* yrow)
+{
+    if constexpr (VY == 2) {
+        yrow[0] = 2 * q + 1;
+        yrow[1] = 2 * q + 2;
+    } else {
+        yrow[0] = q;
+    }
+#pragma unroll
+    for (int r = 0; r < VY; ++r)
+        if (yrow[r] < 0 || yrow[r] >= im.height)
+            yrow[r] = -1;
+    int yv[VY][16];
+#pragma unroll
+    for (int r = 0; r < VY; ++r) {
+        if (yrow[r] >= 0)
+            load16(b.planes + im.plane_off[0] + uint64_t(yrow[r]) * im.plane_pitch[0] + x0, yv[r]);
+        else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                yv[r][i] = 0;
+        }
+    }
+    const int fmt = im.out_fmt;
+    if (im.ncomp == 1 || fmt == 7) {
+#pragma unroll
+        for (int r = 0; r < VY; ++r)
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                px[r * 16 + i] = uint32_t(yv[r][i]) * 0x010101u;
+        return;
+    }
+    int cbv[VY][16], crv[VY][16];
+    upsample_unit<HX, VY>(b.planes + im.plane_off[1], im.plane_pitch[1], im.ds_w[1], im.ds_h[1], im.fancy != 0, q, x0, cbv);
+    upsample_unit<HX, VY>(b.planes + im.plane_off[2], im.plane_pitch[2], im.ds_w[2], im.ds_h[2], im.fancy != 0, q, x0, crv);
+    const bool bgr = (fmt == 5 || fmt == 6);
+#pragma unroll
+    for (int r = 0; r < VY; ++r)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            int rr, gg, bl;
+            ycc_to_rgb(yv[r][i], cbv[r][i], crv[r][i], rr, gg, bl);
+            px[r * 16 + i] = bgr ? (uint32_t(bl) | (uint32_t(gg) << 8) | (uint32_t(rr) << 16))
+                                 : (uint32_t(rr) | (uint32_t(gg) << 8) | (uint32_t(bl) << 16));
+        }
+}
+
+// Plain store of a unit (used by the CPU emulation; the CUDA kernel stages through shared memory instead).
+template <int VY>
+B2J_HD void store_unit_simple(const ImageDesc& im, int x0, const uint32_t* px, const int* yrow)
+{
+    const int fmt = im.out_fmt;
+    const int npx = im.width - x0 < 16 ? im.width - x0 : 16;
+    for (int r = 0; r < VY; ++r) {
+        if (yrow[r] < 0)
+            continue;
+        if (fmt == 4 || fmt == 6) {
+            uint8_t* dst = im.out + int64_t(yrow[r]) * im.out_stride + int64_t(x0) * 3;
+            for (int i = 0; i < npx; ++i) {
+                dst[3 * i] = uint8_t(px[r * 16 + i]);
+                dst[3 * i + 1] = uint8_t(px[r * 16 + i] >> 8);
+                dst[3 * i + 2] = uint8_t(px[r * 16 + i] >> 16);
+            }
+        } else {
+            const int nplanes = fmt == 7 ? 1 : 3;
+            for (int pl = 0; pl < nplanes; ++pl) {
+                uint8_t* dst = im.out + (int64_t(pl) * im.height + yrow[r]) * im.out_stride + x0;
+                for (int i = 0; i < npx; ++i)
+                    dst[i] = uint8_t(px[r * 16 + i] >> (8 * pl));
+            }
+        }
+    }
+}
+
+// sampling class of an image for the colour kernel: chroma horizontal / vertical expansion
+B2J_HD int color_hx(const ImageDesc& im) { return im.ncomp == 1 ? 1 : im.hmax / im.hs[1]; }
+B2J_HD int color_vy(const ImageDesc& im) { return im.ncomp == 1 ? 1 : im.vmax / im.vs[1]; }
 
 } // namespace b200jpeg

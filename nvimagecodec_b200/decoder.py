@@ -133,7 +133,7 @@ class Decoder:
     def stats(self):
         s = (C.c_uint64 * 8)()
         _capi.lib().b200jpeg_decoder_get_stats(self._h, s)
-        keys = ("launches", "sync_rounds", "scan_bytes", "blocks", "subsequences", "scratch_bytes", "reruns", "out_bytes")
+        keys = ("launches", "sync_rounds", "scan_bytes", "blocks", "subsequences", "scratch_bytes", "tail_redone", "out_bytes")
         return dict(zip(keys, [int(v) for v in s]))
 
     STAGES = ("unstuff", "huff_sync", "huff_write", "dc_scan", "idct", "color")

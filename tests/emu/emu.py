@@ -14,9 +14,9 @@ _lib = None
 
 def build(force=False):
     srcs = [os.path.join(HERE, "emu_decode.cpp"), os.path.join(CSRC, "batch_plan.cpp"), os.path.join(CSRC, "jpeg_parse.cpp")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("jpeg_math.cuh", "device_types.h", "batch_plan.h", "jpeg_parse.h", "host_shim.h")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("jpeg_math.cuh", "huffman.cuh", "device_types.h", "batch_plan.h", "jpeg_parse.h", "host_shim.h")]
     if force or not os.path.exists(SO) or any(os.path.getmtime(d) > os.path.getmtime(SO) for d in deps):
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fwrapv", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", SO] + srcs)
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fwrapv", "-fno-strict-aliasing", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", SO] + srcs)
 
 
 def lib():
@@ -26,7 +26,7 @@ def lib():
         L = C.CDLL(SO)
         L.emu_decode_batch.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p),
                                        C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int,
-                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_void_p)]
+                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -46,8 +46,10 @@ def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=64
     coefs = [np.zeros(s, np.int16) for s in slots] if want_coef else None
     st = (C.c_int * n)()
     rounds = C.c_int(0)
+    stats = (C.c_uint64 * 8)()
     lib().emu_decode_batch(n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
                            (C.c_void_p * n)(*[o.ctypes.data for o in outs]), (C.c_int64 * n)(*strides), (C.c_int * n)(*fmts),
                            int(fancy), subseq_bytes, max_rounds, int(jacobi), st, C.byref(rounds),
-                           (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None)
+                           (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None, stats)
+    decode_batch.last_stats = {"rounds": int(stats[0]), "redone": int(stats[1]), "subsequences": int(stats[2])}
     return outs, list(st), rounds.value, coefs

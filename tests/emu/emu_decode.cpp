@@ -8,13 +8,14 @@
 #include <cstring>
 #include <vector>
 #include "../../nvimagecodec_b200/csrc/batch_plan.h"
+#include "../../nvimagecodec_b200/csrc/huffman.cuh"
 #include "../../nvimagecodec_b200/csrc/jpeg_math.cuh"
 
 using namespace b200jpeg;
 
 extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t* sizes, uint8_t* const* outs, const int64_t* strides,
     const int* formats, int fancy, int subseq_bytes, int max_rounds, int jacobi, int* statuses, int* rounds_used,
-    int16_t* const* coef_out /* optional per image, MCU order */)
+    int16_t* const* coef_out /* optional per image, MCU order */, unsigned long long* stats /* optional [8] */)
 {
     PlanOptions opt;
     opt.subseq_bytes = subseq_bytes;
@@ -44,8 +45,8 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     plan_finish(plan);
     const int m = int(plan.images.size());
     std::vector<uint8_t> raw(plan.raw_bytes, 0), clean(plan.clean_bytes, 0), planes(plan.plane_bytes, 0);
-    std::vector<int16_t> coef(plan.coef_elems, 0);
-    std::vector<uint32_t> seg(plan.total_segs + 1, 0), rec(plan.total_subseq, 0), sabs(plan.total_subseq, 0), redo(64, 0);
+    std::vector<int16_t> coef(plan.coef_elems, 0x5A5A), dcv(plan.coef_elems / 64 + 64, 0x5A5A); // poisoned: the kernels must zero what they own
+    std::vector<uint32_t> seg(plan.total_segs + 1, 0), rec(plan.total_subseq, 0), sabs(plan.total_subseq, 0);
     std::vector<unsigned long long> ex(plan.total_subseq, 0), en(plan.total_subseq, 0);
     std::vector<ImageState> states(m);
     std::memset(states.data(), 0, sizeof(ImageState) * m);
@@ -63,11 +64,55 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     b.sub_entry = en.data();
     b.sub_rec = rec.data();
     b.sub_abs = sabs.data();
-    b.redo_counter = redo.data();
     b.coef = coef.data();
+    b.dc = dcv.data();
     b.planes = planes.data();
     b.subseq_bits = plan.subseq_bits;
+    b.total_subseq = plan.total_subseq;
+    const uint32_t S = uint32_t(plan.subseq_bits);
 
+    auto make_env = [&](int i, bool shared_layout, std::vector<uint16_t>& s_lut) {
+        const ImageDesc& im = plan.images[i];
+        HuffEnv env;
+        env.words = reinterpret_cast<const uint32_t*>(clean.data() + im.clean_off);
+        if (shared_layout) { // what stage_tables() builds in shared memory
+            s_lut.assign(size_t(kMaxTabSlots) * kLutSize, 0);
+            for (int s = 0; s < im.ntabs; ++s)
+                std::memcpy(&s_lut[size_t(s) * kLutSize], plan.huff[im.tab_pool[s]].lut, kLutSize * 2);
+            env.lut = s_lut.data();
+            env.tabsel = im.tabsel_s;
+        } else {
+            env.lut = reinterpret_cast<const uint16_t*>(plan.huff.data());
+            env.tabsel = im.tabsel_g;
+        }
+        env.pool = plan.huff.data();
+        env.seg = seg.data() + im.seg_first;
+        env.num_segments = im.num_segments;
+        env.seg_blocks = im.seg_blocks;
+        env.total_blocks = im.total_blocks;
+        env.clean_bits = states[i].clean_len * 8u;
+        env.bpm = im.bpm;
+        return env;
+    };
+    // sync_decode of decode_kernels.cu
+    auto sync_decode = [&](const HuffEnv& env, uint32_t t, uint32_t k, unsigned long long E, bool exact) {
+        HuffState s;
+        s.p = uint32_t(E);
+        const uint32_t slot = uint32_t(E >> 32);
+        s.z = slot & 63u;
+        s.blk = slot >> 6;
+        s.nblk = 0;
+        s.abs = exact;
+        const uint32_t z_entry = s.z;
+        decode_span<false>(env, s, (k + 1u) * S, false, 0, nullptr, nullptr);
+        const unsigned long long X = pack_state(s.p, s.blk * 64u + s.z);
+        const bool changed = X != ex[t];
+        ex[t] = X;
+        en[t] = E;
+        const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
+        rec[t] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
+        return changed;
+    };
     // ---- unstuffing + restart marker removal (what k_unstuff_count/scan/write compute) ----
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
@@ -100,79 +145,124 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         if (int(markers) != im.num_segments - 1) states[i].error |= kErrBadMarker;
     }
 
-    // ---- synchronisation rounds ----
-    int rounds = 0;
-    for (int round = 0; round < max_rounds; ++round) {
-        std::vector<unsigned long long> snap;
-        if (jacobi) snap = ex;
-        uint32_t redone = 0;
+    // ---- synchronisation: round 0 (guessed state), round 1 (predecessor's exit), then work-list rounds ----
+    (void)jacobi;
+    std::vector<uint32_t> wl, wl_next;
+    unsigned long long redone = 0;
+    for (int round = 0; round < 2; ++round) {
+        const std::vector<unsigned long long> snap = ex; // worst-case race: every thread sees its predecessor's old exit
         for (int i = 0; i < m; ++i) {
             const ImageDesc& im = plan.images[i];
-            const uint32_t clean_len = states[i].clean_len;
+            std::vector<uint16_t> s_lut;
+            const HuffEnv env = make_env(i, true, s_lut);
+            const uint32_t clean_bits = states[i].clean_len * 8u;
             for (uint32_t k = 0; k < im.subseq_cta_count * kSubseqCta; ++k) {
                 const uint32_t t = im.subseq_first + k;
-                const bool idle = uint64_t(k) * plan.subseq_bits >= uint64_t(clean_len) * 8;
-                SubseqState s;
-                unsigned long long E;
+                const bool idle = uint64_t(k) * S >= uint64_t(clean_bits);
                 if (round == 0) {
                     if (idle) {
-                        ex[t] = en[t] = (unsigned long long)clean_len * 8;
+                        ex[t] = en[t] = pack_state(clean_bits, 0);
                         rec[t] = 0;
                         continue;
                     }
-                    s.p = k * plan.subseq_bits;
-                    s.slot = 0;
-                    s.n = 0;
-                    s.abs = (k == 0);
-                    E = s.p;
+                    ex[t] = ~0ull;
+                    sync_decode(env, t, k, pack_state(k * S, 0), k == 0);
                 } else {
-                    if (idle || k == 0) continue;
-                    E = jacobi ? snap[t - 1] : ex[t - 1];
-                    if (E == en[t]) continue;
-                    s.p = uint32_t(E);
-                    s.slot = uint32_t(E >> 32);
-                    s.n = 0;
-                    s.abs = false;
-                    ++redone;
+                    if (idle || k == 0)
+                        continue;
+                    const unsigned long long E = snap[t - 1];
+                    if (E == en[t])
+                        continue;
+                    const bool changed = sync_decode(env, t, k, E, false);
+                    if (changed && uint64_t(k + 1) * S < uint64_t(clean_bits))
+                        wl.push_back(t + 1);
                 }
-                decode_subsequence<false>(b, im, &states[i], k, clean_len, s);
-                ex[t] = (unsigned long long)s.p | ((unsigned long long)s.slot << 32);
-                en[t] = E;
-                rec[t] = (s.n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0);
             }
         }
-        rounds = round + 1;
-        if (round > 0 && redone == 0) break;
+    }
+    int rounds = 2;
+    while (!wl.empty() && rounds < max_rounds) {
+        const std::vector<unsigned long long> snap = ex;
+        wl_next.clear();
+        for (uint32_t t : wl) {
+            int i = 0;
+            while (i + 1 < m && plan.images[i + 1].subseq_first <= t)
+                ++i;
+            const ImageDesc& im = plan.images[i];
+            const uint32_t k = t - im.subseq_first;
+            const unsigned long long E = snap[t - 1];
+            if (E == en[t])
+                continue;
+            std::vector<uint16_t> unused;
+            const HuffEnv env = make_env(i, false, unused); // the tail kernel reads the tables from the global pool
+            const bool changed = sync_decode(env, t, k, E, false);
+            ++redone;
+            if (changed && uint64_t(k + 1) * S < uint64_t(states[i].clean_len) * 8u)
+                wl_next.push_back(t + 1);
+        }
+        wl.swap(wl_next);
+        ++rounds;
     }
     if (rounds_used) *rounds_used = rounds;
-
-    // ---- segmented scan of slot counts (k_subseq_scan) ----
-    for (int i = 0; i < m; ++i) {
-        const ImageDesc& im = plan.images[i];
-        uint32_t A = 0;
-        for (uint32_t k = 0; k < im.subseq_cta_count * kSubseqCta; ++k) {
-            const uint32_t r = rec[im.subseq_first + k];
-            A = (r & 0x80000000u) ? (r & 0x7FFFFFFFu) : A + r;
-            sabs[im.subseq_first + k] = A | 0x80000000u;
-        }
+    if (stats) {
+        stats[0] = uint64_t(rounds);
+        stats[1] = redone;
+        stats[2] = plan.total_subseq;
     }
-    // ---- write pass (k_huff_write) ----
+
+    // ---- segmented scan of slot counts + consistency check (k_subseq_scan) ----
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
-        const uint32_t clean_len = states[i].clean_len;
+        uint32_t A = 0x80000000u;
         for (uint32_t k = 0; k < im.subseq_cta_count * kSubseqCta; ++k) {
             const uint32_t t = im.subseq_first + k;
-            if (uint64_t(k) * plan.subseq_bits >= uint64_t(clean_len) * 8) continue;
-            SubseqState s;
-            if (k == 0) {
-                s.p = 0; s.slot = 0; s.n = 0;
-            } else {
-                const unsigned long long E = ex[t - 1];
-                if (E != en[t]) states[i].error |= kErrNotConverged;
-                s.p = uint32_t(E); s.slot = uint32_t(E >> 32); s.n = sabs[t - 1] & 0x7FFFFFFFu;
+            if (k > 0 && en[t] != ex[t - 1] && uint64_t(k) * S < uint64_t(states[i].clean_len) * 8u)
+                states[i].error |= kErrNotConverged;
+            const uint32_t r = rec[t];
+            A = (r & 0x80000000u) ? r : A + r;
+            sabs[t] = A;
+        }
+    }
+    // ---- write pass (k_huff_write): CTA by CTA, zero the owned range first ----
+    for (int i = 0; i < m; ++i) {
+        const ImageDesc& im = plan.images[i];
+        std::vector<uint16_t> s_lut;
+        const HuffEnv env = make_env(i, true, s_lut);
+        const uint32_t clean_bits = states[i].clean_len * 8u;
+        int16_t* cf = coef.data() + im.coef_off;
+        int16_t* dcp = dcv.data() + im.coef_off / 64;
+        // CTAs in reverse order: a later CTA zeroing after an earlier CTA stored would lose data if ownership were wrong
+        for (int cta = int(im.subseq_cta_count) - 1; cta >= 0; --cta) {
+            const uint32_t k0 = uint32_t(cta) * kSubseqCta;
+            const uint32_t n_first = k0 == 0 ? 0u : (sabs[im.subseq_first + k0 - 1] & 0x7FFFFFFFu);
+            const bool last_cta = uint32_t(cta) + 1 == im.subseq_cta_count;
+            const uint32_t n_next = sabs[im.subseq_first + k0 + kSubseqCta - 1] & 0x7FFFFFFFu;
+            const uint32_t first_block = (n_first + 63u) >> 6;
+            uint32_t end_block = last_cta ? im.total_blocks : (n_next + 63u) >> 6;
+            if (end_block > im.total_blocks) end_block = im.total_blocks;
+            for (uint32_t bb = first_block; bb < end_block; ++bb)
+                std::memset(cf + uint64_t(bb) * 64, 0, 128);
+            for (uint32_t ti = 0; ti < uint32_t(kSubseqCta); ++ti) {
+                const uint32_t k = k0 + ti, t = im.subseq_first + k;
+                if (uint64_t(k) * S >= uint64_t(clean_bits)) continue;
+                HuffState s;
+                if (k == 0) {
+                    s.p = 0; s.z = 0; s.blk = 0; s.nblk = 0;
+                } else {
+                    const unsigned long long E = ex[t - 1];
+                    const uint32_t slot = uint32_t(E >> 32);
+                    s.p = uint32_t(E); s.z = slot & 63u; s.blk = slot >> 6;
+                    s.nblk = (sabs[t - 1] & 0x7FFFFFFFu) >> 6;
+                }
+                s.abs = true;
+                const bool extend = (ti == uint32_t(kSubseqCta) - 1) || (uint64_t(k + 1) * S >= uint64_t(clean_bits));
+                const uint32_t end = (k + 1u) * S;
+                uint32_t err = 0;
+                if (!(extend && s.p >= end && s.z == 0))
+                    err = decode_span<true>(env, s, end, extend, first_block, cf, dcp);
+                if (s.nblk == im.total_blocks && s.z == 0 && extend) states[i].done_blocks = s.nblk;
+                states[i].error |= err;
             }
-            s.abs = true;
-            decode_subsequence<true>(b, im, &states[i], k, clean_len, s);
         }
     }
     // ---- DC prediction (k_dc_scan) ----
@@ -180,23 +270,50 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         const ImageDesc& im = plan.images[i];
         int pred[3] = {0, 0, 0};
         const uint32_t mcus = uint32_t(im.mcus_x) * im.mcus_y;
+        int16_t* dcp = dcv.data() + im.coef_off / 64;
         for (uint32_t mc = 0; mc < mcus; ++mc) {
             if (im.restart_interval && mc % im.restart_interval == 0) pred[0] = pred[1] = pred[2] = 0;
             for (int j = 0; j < im.bpm; ++j) {
-                int16_t* d = coef.data() + im.coef_off + (uint64_t(mc) * im.bpm + j) * 64;
+                int16_t* d = dcp + uint64_t(mc) * im.bpm + j;
                 pred[im.blk_comp[j]] += *d;
                 *d = int16_t(pred[im.blk_comp[j]]);
             }
         }
-        if (coef_out && coef_out[idx[i]]) std::memcpy(coef_out[idx[i]], coef.data() + im.coef_off, size_t(im.total_slots) * 2);
+        if (coef_out && coef_out[idx[i]]) {
+            int16_t* o = coef_out[idx[i]];
+            std::memcpy(o, coef.data() + im.coef_off, size_t(im.total_blocks) * 128);
+            for (uint32_t bb = 0; bb < im.total_blocks; ++bb) o[uint64_t(bb) * 64] = dcp[bb];
+        }
     }
     // ---- IDCT + colour ----
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
-        for (uint32_t u = 0; u < im.idct_cta_count * kIdctCta; ++u) idct_thread(b, im, u);
-        for (uint32_t u = 0; u < im.color_cta_count * kColorCta; ++u) color_thread(b, im, u);
+        for (uint32_t u = 0; u < im.idct_cta_count * kIdctCta; ++u) {
+            const IdctBlockRef ref = idct_locate(im, u);
+            if (ref.comp < 0) continue;
+            uint32_t out[16];
+            idct_block(coef.data() + im.coef_off + uint64_t(ref.src_blk) * 64, dcv[im.coef_off / 64 + ref.src_blk],
+                plan.quant.data() + im.qt[ref.comp] * 64, out);
+            for (int r = 0; r < 8; ++r) std::memcpy(planes.data() + ref.dst + uint64_t(r) * ref.pitch, &out[2 * r], 8);
+        }
+        const int hx = color_hx(im), vy = color_vy(im);
+        const uint32_t tiles = uint32_t(im.color_rows) * uint32_t(im.color_xtiles);
+        for (uint32_t tile = 0; tile < tiles; ++tile) {
+            const int q = int(tile / uint32_t(im.color_xtiles)) - (vy == 2 ? 1 : 0);
+            const int xbase = int(tile % uint32_t(im.color_xtiles)) * kColorTilePx;
+            for (int lane = 0; lane < 32; ++lane) {
+                const int x0 = xbase + lane * 16;
+                if (x0 >= im.width) continue;
+                uint32_t px[32];
+                int yrow[2] = {-1, -1};
+                if (vy == 2 && hx == 2) { color_unit<2, 2>(b, im, q, x0, px, yrow); store_unit_simple<2>(im, x0, px, yrow); }
+                else if (vy == 2) { color_unit<1, 2>(b, im, q, x0, px, yrow); store_unit_simple<2>(im, x0, px, yrow); }
+                else if (hx == 2) { color_unit<2, 1>(b, im, q, x0, px, yrow); store_unit_simple<1>(im, x0, px, yrow); }
+                else { color_unit<1, 1>(b, im, q, x0, px, yrow); store_unit_simple<1>(im, x0, px, yrow); }
+            }
+        }
         if (states[i].error) statuses[idx[i]] = 4;
-        else if (states[i].done_slots != im.total_slots) statuses[idx[i]] = 4;
+        else if (states[i].done_blocks != im.total_blocks) statuses[idx[i]] = 4;
     }
     return 0;
 }

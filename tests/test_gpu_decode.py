@@ -144,7 +144,7 @@ def test_coefficients_bit_exact(torch_mod):
 def test_subsequence_sizes_and_rounds(torch_mod, refdec):
     datas = [make_jpeg(4000 + i, 640, 480, (2, 2), 90) for i in range(4)] + [make_jpeg(4100, 1920, 1080, (2, 2), 90)]
     want, _, _ = refdec[1].decode_host(datas)
-    for opts in (":fancy_upsampling=1 :subseq_bytes=64", ":fancy_upsampling=1 :subseq_bytes=128 :sync_rounds=2",
+    for opts in (":fancy_upsampling=1 :subseq_bytes=64", ":fancy_upsampling=1 :subseq_bytes=32",
                  ":fancy_upsampling=1 :subseq_bytes=1024", "b200jpeg_decoder:subseq_bytes=512 other_plugin:subseq_bytes=32"):
         got, st = gpu_decode(torch_mod, datas, 4, opts)
         for i, (g, w) in enumerate(zip(got, want)):
