@@ -38,6 +38,46 @@ void build_dev_table(const HuffSpec& spec, bool is_dc, DevHuffTable& t)
     }
     t.maxcode[0] = -1;
     t.maxcode[17] = 0x7FFFFFFF;
+    // second level: group the codes longer than kLutBits by their kLutBits-bit prefix; a prefix whose longest code has
+    // kLutBits + n bits gets 2^n entries indexed by the n bits after the prefix
+    int maxlen[kLutSize];
+    std::memset(maxlen, 0, sizeof(maxlen));
+    code = 0;
+    for (int l = 1; l <= 16; ++l) {
+        for (int i = 0; i < spec.bits[l]; ++i, ++code)
+            if (l > kLutBits && (code >> (l - kLutBits)) < kLutSize && l > maxlen[code >> (l - kLutBits)])
+                maxlen[code >> (l - kLutBits)] = l;
+        code <<= 1;
+    }
+    int used = 0, off_of[kLutSize];
+    for (int pre = 0; pre < kLutSize; ++pre) {
+        off_of[pre] = -1;
+        if (!maxlen[pre] || t.lut[pre])
+            continue; // (a first-level entry there would mean the table is not prefix free: leave it to the walk)
+        const int n = maxlen[pre] - kLutBits, size = 1 << n;
+        if (used + size > kLut2Size)
+            continue; // does not fit: entry stays 0, the kernel walks maxcode[]
+        off_of[pre] = used;
+        t.lut[pre] = uint16_t((n << 5) | ((used / 2) << 8));
+        used += size;
+    }
+    code = 0;
+    p = 0;
+    for (int l = 1; l <= 16; ++l) {
+        for (int i = 0; i < spec.bits[l]; ++i, ++p, ++code) {
+            if (l <= kLutBits || (code >> (l - kLutBits)) >= kLutSize)
+                continue;
+            const int pre = code >> (l - kLutBits);
+            if (off_of[pre] < 0)
+                continue;
+            const int n = maxlen[pre] - kLutBits, sub = code & ((1 << (l - kLutBits)) - 1);
+            const int first = sub << (kLutBits + n - l), cnt = 1 << (kLutBits + n - l);
+            const uint16_t e = uint16_t(huff_entry(l, spec.vals[p & 255], is_dc));
+            for (int j = 0; j < cnt; ++j)
+                t.lut[kLutSize + off_of[pre] + first + j] = e;
+        }
+        code <<= 1;
+    }
 }
 
 int resolve_format(int f, int ncomp)
@@ -142,7 +182,7 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     for (int b = 0; b < im.bpm; ++b) {
         const int c = im.blk_comp[b];
         im.tabsel_g[b] = TabSel{uint32_t(dc_tab[c]) * kHuffTableU16, uint32_t(ac_tab[c]) * kHuffTableU16, uint32_t(dc_tab[c]), uint32_t(ac_tab[c])};
-        im.tabsel_s[b] = TabSel{uint32_t(slot_of(dc_tab[c])) * kLutSize, uint32_t(slot_of(ac_tab[c])) * kLutSize, uint32_t(dc_tab[c]),
+        im.tabsel_s[b] = TabSel{uint32_t(slot_of(dc_tab[c])) * kLutEntries, uint32_t(slot_of(ac_tab[c])) * kLutEntries, uint32_t(dc_tab[c]),
             uint32_t(ac_tab[c])};
     }
     const uint32_t mcus = uint32_t(im.mcus_x) * uint32_t(im.mcus_y);

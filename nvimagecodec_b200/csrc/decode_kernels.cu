@@ -17,13 +17,9 @@
 //   C1 k_color           upsample (fancy / box) + YCbCr->RGB; a warp produces 512 pixels x (1|2) rows, staged in shared
 //                        memory and written with fully coalesced 128-byte store instructions at any alignment
 // The per-thread arithmetic lives in huffman.cuh / jpeg_math.cuh (shared with the CPU emulation used by the tests).
-#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include "decode_kernels.h"
-#include "huffman.cuh"
 #include "jpeg_math.cuh"
-
-namespace cg = cooperative_groups;
 
 namespace b200jpeg {
 
@@ -212,244 +208,6 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
     }
     if (bad)
         atomicOr(&b.states[img].error, kErrBadMarker);
-}
-
-// ------------------------------------------------------------------------------------------------------------------
-// Huffman: synchronisation rounds, slot scan, write pass
-// ------------------------------------------------------------------------------------------------------------------
-
-// Stage the image's distinct Huffman LUTs and its per-block table selectors in shared memory.
-__device__ __forceinline__ void stage_tables(const BatchDev& b, const ImageDesc& im, uint16_t* s_lut, TabSel* s_tabsel)
-{
-    static_assert(kLutSize * 2 == kSubseqCta * 16, "one uint4 per thread copies one LUT");
-    for (int s = 0; s < im.ntabs; ++s) {
-        const uint4* src = reinterpret_cast<const uint4*>(b.huff[im.tab_pool[s]].lut);
-        reinterpret_cast<uint4*>(s_lut + s * kLutSize)[threadIdx.x] = src[threadIdx.x];
-    }
-    if (threadIdx.x < kMaxBlocksPerMcu)
-        s_tabsel[threadIdx.x] = im.tabsel_s[threadIdx.x];
-    __syncthreads();
-}
-
-__device__ __forceinline__ HuffEnv make_env(const BatchDev& b, const ImageDesc& im, uint32_t clean_len, const uint16_t* lut, const TabSel* tabsel)
-{
-    HuffEnv env;
-    env.words = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
-    env.lut = lut;
-    env.tabsel = tabsel;
-    env.pool = b.huff;
-    env.seg = b.seg_start + im.seg_first;
-    env.num_segments = im.num_segments;
-    env.seg_blocks = im.seg_blocks;
-    env.total_blocks = im.total_blocks;
-    env.clean_bits = clean_len * 8u;
-    env.bpm = im.bpm;
-    return env;
-}
-
-// Decode subsequence k of an image from entry state E in synchronisation mode and publish the result.
-// Returns true if the exit state differs from the one recorded before.
-__device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& env, uint32_t t, uint32_t k, unsigned long long E, bool exact)
-{
-    HuffState s;
-    s.p = uint32_t(E);
-    const uint32_t slot = uint32_t(E >> 32);
-    s.z = slot & 63u;
-    s.blk = slot >> 6;
-    s.nblk = 0;
-    s.abs = exact;
-    const uint32_t z_entry = s.z;
-    decode_span<false>(env, s, (k + 1u) * uint32_t(b.subseq_bits), false, 0, nullptr, nullptr);
-    const unsigned long long X = pack_state(s.p, s.blk * 64u + s.z);
-    const bool changed = (X != __ldcg(b.sub_exit + t));
-    b.sub_exit[t] = X;
-    b.sub_entry[t] = E;
-    // slots consumed: absolute (from the image start) once a known state was passed, else relative to the entry
-    const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
-    b.sub_rec[t] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
-    return changed;
-}
-
-__global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
-{
-    __shared__ __align__(16) uint16_t s_lut[kMaxTabSlots * kLutSize];
-    __shared__ TabSel s_tabsel[kMaxBlocksPerMcu];
-    const int img = find_image(b.cta_map_subseq, b.num_images, blockIdx.x);
-    const ImageDesc& im = b.images[img];
-    stage_tables(b, im, s_lut, s_tabsel);
-    const uint32_t k = (blockIdx.x - b.cta_map_subseq[img]) * kSubseqCta + threadIdx.x;
-    const uint32_t t = im.subseq_first + k;
-    const uint32_t clean_len = b.states[img].clean_len;
-    const uint32_t clean_bits = clean_len * 8u;
-    const bool idle = uint64_t(k) * uint32_t(b.subseq_bits) >= uint64_t(clean_bits);
-    const HuffEnv env = make_env(b, im, clean_len, s_lut, s_tabsel);
-    if (round == 0) {
-        if (idle) {
-            b.sub_exit[t] = b.sub_entry[t] = pack_state(clean_bits, 0);
-            b.sub_rec[t] = 0;
-            return;
-        }
-        b.sub_exit[t] = ~0ull;
-        sync_decode(b, env, t, k, pack_state(k * uint32_t(b.subseq_bits), 0), k == 0);
-    } else {
-        if (idle || k == 0)
-            return;
-        const unsigned long long E = b.sub_exit[t - 1];
-        if (E == b.sub_entry[t])
-            return;
-        const bool changed = sync_decode(b, env, t, k, E, false);
-        const bool next_live = uint64_t(k + 1) * uint32_t(b.subseq_bits) < uint64_t(clean_bits);
-        if (changed && next_live) {
-            const uint32_t i = atomicAdd(&b.sync->count[0], 1u);
-            b.worklist[0][i] = t + 1;
-        }
-    }
-}
-
-// Jacobi rounds over the work list until no subsequence changes any more.  Cooperative launch: every CTA is resident,
-// grid.sync() separates the rounds.  Round r reads list r & 1 (length count[r % 3]) and appends to list (r + 1) & 1
-// (length count[(r + 1) % 3]); count[(r + 2) % 3] is cleared for the round after.
-__global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b)
-{
-    cg::grid_group grid = cg::this_grid();
-    const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t redone = 0;
-    int r = 0;
-    for (; r < kMaxTailRounds; ++r) {
-        const uint32_t n = __ldcg(&b.sync->count[r % 3]);
-        if (n == 0)
-            break;
-        if (tid == 0)
-            b.sync->count[(r + 2) % 3] = 0;
-        const uint32_t* in = b.worklist[r & 1];
-        uint32_t* out = b.worklist[(r + 1) & 1];
-        for (uint32_t i = tid; i < n; i += nthreads) {
-            const uint32_t t = __ldcg(in + i);
-            const int img = find_image(b.cta_map_subseq, b.num_images, t / kSubseqCta);
-            const ImageDesc& im = b.images[img];
-            const uint32_t k = t - im.subseq_first;
-            const unsigned long long E = __ldcg(b.sub_exit + t - 1); // written by other SMs in earlier rounds: bypass L1
-            if (E == __ldcg(b.sub_entry + t))
-                continue;
-            const uint32_t clean_len = b.states[img].clean_len;
-            const HuffEnv env = make_env(b, im, clean_len, reinterpret_cast<const uint16_t*>(b.huff), im.tabsel_g);
-            const bool changed = sync_decode(b, env, t, k, E, false);
-            ++redone;
-            if (changed && uint64_t(k + 1) * uint32_t(b.subseq_bits) < uint64_t(clean_len) * 8u)
-                out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
-        }
-        grid.sync();
-    }
-    if (redone)
-        atomicAdd(&b.sync->redone, redone);
-    if (tid == 0)
-        b.sync->rounds = uint32_t(r);
-}
-
-// segmented-scan combine: a = earlier prefix, x = later element; bit31 = "absolute" flag
-__device__ __forceinline__ uint32_t seg_combine(uint32_t a, uint32_t x) { return (x & 0x80000000u) ? x : a + x; }
-
-constexpr int kScanThreads = 256;
-__global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
-{
-    const int img = blockIdx.x;
-    const ImageDesc& im = b.images[img];
-    const uint32_t count = im.subseq_cta_count * kSubseqCta;
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    __shared__ uint32_t s_w[kScanThreads / 32];
-    __shared__ uint32_t s_carry;
-    if (threadIdx.x == 0)
-        s_carry = 0x80000000u;
-    __syncthreads();
-    bool bad = false;
-    for (uint32_t c0 = 0; c0 < count; c0 += kScanThreads) {
-        const uint32_t c = c0 + threadIdx.x;
-        uint32_t v = c < count ? b.sub_rec[im.subseq_first + c] : 0u;
-        if (c > 0 && c < count && b.sub_entry[im.subseq_first + c] != b.sub_exit[im.subseq_first + c - 1] &&
-            uint64_t(c) * uint32_t(b.subseq_bits) < uint64_t(b.states[img].clean_len) * 8u)
-            bad = true; // the chain of entry/exit states is not consistent: synchronisation did not finish
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, v, o);
-            if (lane >= uint32_t(o))
-                v = seg_combine(tprev, v);
-        }
-        if (lane == 31)
-            s_w[warp] = v;
-        __syncthreads();
-        uint32_t pre = s_carry;
-        for (int i = 0; i < int(warp); ++i)
-            pre = seg_combine(pre, s_w[i]);
-        v = seg_combine(pre, v);
-        if (c < count)
-            b.sub_abs[im.subseq_first + c] = v;
-        __syncthreads();
-        if (threadIdx.x == kScanThreads - 1)
-            s_carry = v;
-        __syncthreads();
-    }
-    if (bad)
-        atomicOr(&b.states[img].error, kErrNotConverged);
-}
-
-__global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
-{
-    __shared__ __align__(16) uint16_t s_lut[kMaxTabSlots * kLutSize];
-    __shared__ TabSel s_tabsel[kMaxBlocksPerMcu];
-    const int img = find_image(b.cta_map_subseq, b.num_images, blockIdx.x);
-    const ImageDesc& im = b.images[img];
-    stage_tables(b, im, s_lut, s_tabsel);
-    const uint32_t cta = blockIdx.x - b.cta_map_subseq[img];
-    const uint32_t k0 = cta * kSubseqCta, k = k0 + threadIdx.x;
-    const uint32_t t = im.subseq_first + k;
-    const uint32_t clean_len = b.states[img].clean_len;
-    const uint32_t clean_bits = clean_len * 8u;
-    const uint32_t S = uint32_t(b.subseq_bits);
-
-    // blocks this CTA owns: those that *start* inside its subsequences
-    const uint32_t n_first = k0 == 0 ? 0u : (b.sub_abs[im.subseq_first + k0 - 1] & 0x7FFFFFFFu);
-    const bool last_cta = cta + 1 == im.subseq_cta_count;
-    const uint32_t n_next = b.sub_abs[im.subseq_first + k0 + kSubseqCta - 1] & 0x7FFFFFFFu;
-    const uint32_t first_block = (n_first + 63u) >> 6;
-    uint32_t end_block = last_cta ? im.total_blocks : (n_next + 63u) >> 6;
-    if (end_block > im.total_blocks)
-        end_block = im.total_blocks;
-    int16_t* coef = b.coef + im.coef_off;
-    int16_t* dc = b.dc + im.coef_off / 64;
-    if (end_block > first_block) { // zero the owned coefficient range: the scattered stores below then hit lines in L2
-        uint4* z4 = reinterpret_cast<uint4*>(coef + uint64_t(first_block) * 64);
-        const uint32_t n16 = (end_block - first_block) * 8u;
-        for (uint32_t i = threadIdx.x; i < n16; i += kSubseqCta)
-            z4[i] = make_uint4(0, 0, 0, 0);
-    }
-    __syncthreads();
-    if (uint64_t(k) * S >= uint64_t(clean_bits))
-        return;
-    HuffState s;
-    if (k == 0) {
-        s.p = 0;
-        s.z = 0;
-        s.blk = 0;
-        s.nblk = 0;
-    } else {
-        const unsigned long long E = b.sub_exit[t - 1];
-        const uint32_t slot = uint32_t(E >> 32);
-        s.p = uint32_t(E);
-        s.z = slot & 63u;
-        s.blk = slot >> 6;
-        s.nblk = (b.sub_abs[t - 1] & 0x7FFFFFFFu) >> 6;
-    }
-    s.abs = true;
-    const bool extend = (threadIdx.x == kSubseqCta - 1) || (uint64_t(k + 1) * S >= uint64_t(clean_bits));
-    const HuffEnv env = make_env(b, im, clean_len, s_lut, s_tabsel);
-    const uint32_t end = (k + 1u) * S;
-    uint32_t err = 0;
-    if (!(extend && s.p >= end && s.z == 0))
-        err = decode_span<true>(env, s, end, extend, first_block, coef, dc);
-    if (s.nblk == im.total_blocks && s.z == 0 && extend)
-        b.states[img].done_blocks = s.nblk;
-    if (err)
-        atomicOr(&b.states[img].error, err);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -737,36 +495,6 @@ int launch_unstuff(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
     k_unstuff_scan<<<d.num_images, 32, 0, st>>>(b);
     k_unstuff_write<<<d.unstuff_ctas, kUnstuffThreads, 0, st>>>(b);
     return 3;
-}
-
-int tail_grid_size(int device)
-{
-    int per_sm = 0, sms = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_huff_sync_tail, kSubseqCta, 0) != cudaSuccess || per_sm < 1)
-        return 0;
-    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms < 1)
-        return 0;
-    if (per_sm > 4)
-        per_sm = 4;
-    return per_sm * sms;
-}
-
-int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid)
-{
-    k_huff_sync<<<d.subseq_ctas, kSubseqCta, 0, st>>>(b, 0);
-    k_huff_sync<<<d.subseq_ctas, kSubseqCta, 0, st>>>(b, 1);
-    BatchDev bb = b;
-    void* args[] = {&bb};
-    if (cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_huff_sync_tail), dim3(tail_grid), dim3(kSubseqCta), args, 0, st) != cudaSuccess)
-        return -1;
-    return 3;
-}
-
-int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
-{
-    k_subseq_scan<<<d.num_images, kScanThreads, 0, st>>>(b);
-    k_huff_write<<<d.subseq_ctas, kSubseqCta, 0, st>>>(b);
-    return 2;
 }
 
 int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st)

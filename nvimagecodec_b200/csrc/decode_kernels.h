@@ -15,7 +15,8 @@ struct LaunchDims
 int launch_unstuff(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 // rounds 0 and 1 over every subsequence, then the cooperative tail kernel (grid size from tail_grid_size); -1 on launch failure
 int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid);
-int tail_grid_size(int device); // CTAs of k_huff_sync_tail that are co-resident on the device (0 on error)
+// set the dynamic shared memory limits for b.lut_slots / b.stream_words and size the cooperative tail grid; -1 on error
+int huff_configure(const BatchDev& b, int device, int* tail_grid);
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st);

@@ -62,6 +62,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
                 o.subseq_bytes = v;
         } else if (name == "copy_threads")
             o.copy_threads = std::max(1, std::atoi(value.c_str()));
+        else if (name == "stage_stream")
+            o.stage_stream = std::atoi(value.c_str()) != 0;
         else if (name == "profile")
             o.profile = std::atoi(value.c_str()) != 0;
     }
@@ -110,9 +112,6 @@ int Decoder::init()
     if (opt_.profile)
         for (cudaEvent_t& e : ev_stage_)
             B2J_CUDA(cudaEventCreate(&e));
-    tail_grid_ = tail_grid_size(device_);
-    if (tail_grid_ <= 0)
-        return B200JPEG_STATUS_CUDA_ERROR;
     return B200JPEG_STATUS_SUCCESS;
 }
 
@@ -303,6 +302,22 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     dev_.cta_map_idct = reinterpret_cast<const uint32_t*>(dm + off_m0 + 2 * map_bytes);
     dev_.cta_map_color = reinterpret_cast<const uint32_t*>(dm + off_m0 + 3 * map_bytes);
     dev_.subseq_bits = plan_.subseq_bits;
+    dev_.num_tables = int(plan_.huff.size());
+    dev_.lut_slots = 1;
+    for (const ImageDesc& im : plan_.images)
+        dev_.lut_slots = std::max(dev_.lut_slots, im.ntabs);
+    // stream staging in shared memory: per thread its subsequence plus the words a symbol may run over, an odd count
+    dev_.stream_words = 0;
+    if (opt_.stage_stream && opt_.subseq_bytes <= 256)
+        dev_.stream_words = (plan_.subseq_bits / 32 + 5) | 1;
+    if (dev_.lut_slots != cfg_lut_slots_ || dev_.stream_words != cfg_stream_words_) {
+        if (huff_configure(dev_, device_, &tail_grid_) != 0 || tail_grid_ <= 0) {
+            std::fprintf(stderr, "b200jpeg: cannot configure the Huffman kernels: %s\n", cudaGetErrorString(cudaGetLastError()));
+            return B200JPEG_STATUS_CUDA_ERROR;
+        }
+        cfg_lut_slots_ = dev_.lut_slots;
+        cfg_stream_words_ = dev_.stream_words;
+    }
     dev_.total_subseq = plan_.total_subseq;
     dims_.num_images = m;
     dims_.unstuff_ctas = plan_.map_unstuff.back();

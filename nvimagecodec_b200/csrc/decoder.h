@@ -15,6 +15,7 @@ struct DecoderOptions
     bool fancy_upsampling = true; // reference default (libjpeg_turbo_decoder.cpp:250-276)
     int subseq_bytes = 128;
     int copy_threads = 4;
+    bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)
     bool profile = false; // record CUDA events between the kernel stages (b200jpeg_decoder_get_stage_times)
 };
 
@@ -88,7 +89,7 @@ class Decoder
     size_t scratch_bytes_ = 0;
 
     uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_redone_ = 0;
-    int tail_grid_ = 0;
+    int tail_grid_ = 0, cfg_lut_slots_ = -1, cfg_stream_words_ = -1;
 };
 
 } // namespace b200jpeg

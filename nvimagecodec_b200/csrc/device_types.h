@@ -12,6 +12,8 @@ namespace b200jpeg {
 
 constexpr int kLutBits = 11;          // first-level Huffman lookup width
 constexpr int kLutSize = 1 << kLutBits;
+constexpr int kLut2Size = 512;        // second-level entries (codes longer than kLutBits)
+constexpr int kLutEntries = kLutSize + kLut2Size;
 constexpr int kSubseqCta = 256;       // threads per CTA in the subsequence kernels (one subsequence per thread)
 constexpr int kUnstuffThreads = 256;  // threads per CTA in the unstuffing kernels
 constexpr int kUnstuffBytesPerThread = 16;
@@ -27,16 +29,18 @@ constexpr int kMaxTabSlots = 6;       // distinct Huffman tables one image can r
 // jpeg_make_d_derived_tbl, jdhuff.c:143-285).  We use an 11-bit first level instead of 8 and store pre-digested entries
 //   entry = code_length | size << 5 | zadv << 9
 // size = number of value bits that follow the code; zadv = how far the zigzag position advances (DC: 1; AC run/size:
-// run + 1; ZRL: 16; EOB: 64).  entry == 0: the code is longer than kLutBits (or invalid) -> maxcode walk.
+// run + 1; ZRL: 16; EOB: 64).  Codes longer than kLutBits: the first-level entry of their 11-bit prefix has code_length 0
+// and holds n << 5 | (offset / 2) << 8; the entry of the code is lut[kLutSize + offset + next n bits] (same format, full
+// length).  entry == 0: invalid code, or a table too irregular for kLut2Size second-level entries -> maxcode walk.
 // The same symbols come out as with the reference's tables.
 struct DevHuffTable
 {
-    uint16_t lut[kLutSize];
+    uint16_t lut[kLutEntries];
     int32_t maxcode[18];   // largest code of each length, -1 if none
     int32_t valoffset[18]; // vals[] index = code + valoffset[len]
     uint8_t vals[256];
     int32_t is_dc;
-    int32_t pad_[3];       // sizeof == 4512, a multiple of 16
+    int32_t pad_[3];       // sizeof == 5536, a multiple of 16
 };
 constexpr uint32_t kHuffTableU16 = sizeof(DevHuffTable) / 2; // stride of the table pool in uint16 units
 
@@ -79,7 +83,7 @@ struct ImageDesc
     int32_t qt[3];            // quant table pool index per component
 
     // Huffman tables: per block-in-MCU selectors, relative to the global pool (tail kernel) and to the per-CTA shared
-    // memory copy (main kernels); tab_pool lists the distinct pool tables to stage, slot s -> shared offset s * kLutSize
+    // memory copy (main kernels); tab_pool lists the distinct pool tables to stage, slot s -> shared offset s * kLutEntries
     TabSel tabsel_g[kMaxBlocksPerMcu];
     TabSel tabsel_s[kMaxBlocksPerMcu];
     int32_t ntabs;
@@ -163,6 +167,9 @@ struct BatchDev // pointers handed to every kernel
     const uint32_t* cta_map_color;
     int32_t subseq_bits;   // bits per subsequence
     uint32_t total_subseq;
+    int32_t num_tables;    // Huffman tables in the pool
+    int32_t lut_slots;     // LUT slots the decoding kernels reserve in shared memory (>= every image's ntabs)
+    int32_t stream_words;  // 32-bit words of staged stream per thread (odd, >= subseq_bits / 32 + 4); 0 = read the stream from global memory
 };
 
 } // namespace b200jpeg

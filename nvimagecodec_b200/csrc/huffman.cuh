@@ -64,7 +64,8 @@ B2J_HD uint32_t huff_long_code(const DevHuffTable* t, uint32_t win, bool& ok)
 // Everything a decoding thread needs to know about its image; the pointers may be shared or global memory.
 struct HuffEnv
 {
-    const uint32_t* words;   // unstuffed stream of the image (4-byte aligned, readable 16 bytes past the end)
+    const uint32_t* words;   // unstuffed stream of the image (4-byte aligned, readable 16 bytes past the end); with
+                             // PRESWAPPED the words were byte-swapped to big-endian bit order when they were staged
     const uint16_t* lut;     // LUT base the TabSel offsets refer to
     const TabSel* tabsel;    // [bpm]
     const DevHuffTable* pool; // global table pool (long-code walk)
@@ -91,7 +92,7 @@ struct HuffState
 //                per block, absolute block index), the DC *difference* into dc[block].  With extend = true the thread
 //                keeps going past `end` until the block it is in is complete (the last subsequence of a CTA finishes
 //                the block that straddles into the next CTA's range).  Returns error flags.
-template <bool WRITE>
+template <bool WRITE, bool PRESWAPPED = false>
 B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool extend, uint32_t first_block, int16_t* coef, int16_t* dc)
 {
     if (end > env.clean_bits)
@@ -128,15 +129,29 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool
         const uint32_t seg_end = last ? env.total_blocks : uint32_t(g + 1) * env.seg_blocks; // used when s.abs
         TabSel ts = env.tabsel[blk];
         uint32_t widx = p >> 5;
-        uint32_t w0 = bswap32(env.words[widx]), w1 = bswap32(env.words[widx + 1]), w2 = bswap32(env.words[widx + 2]);
+        uint32_t w0 = env.words[widx], w1 = env.words[widx + 1], w2 = env.words[widx + 2];
+        if (!PRESWAPPED) {
+            w0 = bswap32(w0);
+            w1 = bswap32(w1);
+            w2 = bswap32(w2);
+        }
         bool cross = false;
         while (p < lim) {
             const uint32_t win = funnel_left(w0, w1, p & 31u);
             const uint32_t base = z ? ts.ac_off : ts.dc_off;
             uint32_t e = env.lut[base + (win >> (32 - kLutBits))];
-            if (e == 0) {
+            if ((e & 31u) == 0) { // code longer than kLutBits
                 bool ok = true;
-                e = huff_long_code(env.pool + (z ? ts.ac_idx : ts.dc_idx), win, ok);
+                if (e) {
+                    const uint32_t n = (e >> 5) & 7u;
+                    e = env.lut[base + uint32_t(kLutSize) + (e >> 8) * 2u + ((win >> (32 - kLutBits - n)) & ((1u << n) - 1u))];
+                    if (e == 0) { // unused code space below that prefix
+                        ok = false;
+                        e = 16u | (1u << 9);
+                    }
+                } else {
+                    e = huff_long_code(env.pool + (z ? ts.ac_idx : ts.dc_idx), win, ok);
+                }
                 if (WRITE && !ok)
                     err |= kErrBadCode;
             }
@@ -173,7 +188,7 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool
                 ++widx;
                 w0 = w1;
                 w1 = w2;
-                w2 = bswap32(env.words[widx + 2]);
+                w2 = PRESWAPPED ? env.words[widx + 2] : bswap32(env.words[widx + 2]);
             }
             if (z >= 64u) { // block complete
                 z = 0;

@@ -1,0 +1,403 @@
+// huffman_kernels.cu -- sm_100a kernels of the entropy-decode stage of b200jpeg.
+//
+//   H1 k_huff_sync x 2   self-synchronising subsequence decode (no output): round 0 from a guessed state, round 1 from the
+//                        predecessor's exit state; subsequences whose exit state changed feed a work list
+//   H2 k_huff_sync_tail  cooperative kernel: Jacobi rounds over the (compacted) work list until it is empty
+//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute write position per subsequence
+//   H4 k_huff_write      final decode pass: a CTA zeroes the coefficient range it owns, then stores de-zigzagged int16 AC
+//                        coefficients and the per-block DC differences
+// Shared memory layout of the decoding kernels (dynamic): [LUTs: lut_slots x 5 KB][TabSel x 8][stream staging].
+// The unstuffed stream of the CTA's subsequences is staged (byte-swapped to bit order) with coalesced loads; thread t
+// owns the words [t * W, (t + 1) * W) where W = stream_words is odd, so threads at the same position of their
+// subsequence hit different banks; the last W - S/32 words of a region duplicate the start of the next one.
+// The per-thread decode loop lives in huffman.cuh (shared with the CPU emulation used by the tests).
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+#include "decode_kernels.h"
+#include "huffman.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace b200jpeg {
+
+__device__ __forceinline__ int find_image_h(const uint32_t* __restrict__ map, int n, uint32_t cta)
+{
+    int lo = 0, hi = n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (map[mid] <= cta)
+            lo = mid;
+        else
+            hi = mid - 1;
+    }
+    return lo;
+}
+
+struct HuffSmem
+{
+    uint16_t* lut;
+    TabSel* tabsel;
+    uint32_t* stream;
+};
+
+__device__ __forceinline__ HuffSmem carve_smem(const BatchDev& b, unsigned char* base, int tabsel_entries)
+{
+    HuffSmem s;
+    s.lut = reinterpret_cast<uint16_t*>(base);
+    s.tabsel = reinterpret_cast<TabSel*>(base + size_t(b.lut_slots) * kLutEntries * 2);
+    s.stream = reinterpret_cast<uint32_t*>(s.tabsel + tabsel_entries);
+    return s;
+}
+
+// Stage the image's distinct Huffman LUTs, its per-block table selectors and (if enabled) the stream of the CTA's
+// subsequences in shared memory.
+__device__ __forceinline__ void stage_cta(const BatchDev& b, const ImageDesc& im, const HuffSmem& sm, uint32_t k0)
+{
+    for (int s = 0; s < im.ntabs; ++s) {
+        const uint4* src = reinterpret_cast<const uint4*>(b.huff[im.tab_pool[s]].lut);
+        for (int i = threadIdx.x; i < kLutEntries / 8; i += kSubseqCta)
+            reinterpret_cast<uint4*>(sm.lut + s * kLutEntries)[i] = src[i];
+    }
+    if (threadIdx.x < kMaxBlocksPerMcu)
+        sm.tabsel[threadIdx.x] = im.tabsel_s[threadIdx.x];
+    if (b.stream_words) {
+        const uint32_t spw = uint32_t(b.subseq_bits) >> 5, W = uint32_t(b.stream_words), extra = W - spw;
+        const uint32_t* words = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
+        const uint32_t first = k0 * spw, max_words = (im.raw_len + 16u) >> 2; // words of this image that exist
+        const uint32_t total = kSubseqCta * spw + extra;
+        for (uint32_t g = threadIdx.x; g < total; g += kSubseqCta) {
+            const uint32_t a = first + g;
+            const uint32_t v = a < max_words ? __byte_perm(words[a], 0, 0x0123) : 0u;
+            const uint32_t t = g / spw, j = g - t * spw;
+            if (t < kSubseqCta)
+                sm.stream[t * W + j] = v;
+            if (j < extra && t > 0)
+                sm.stream[(t - 1) * W + spw + j] = v;
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ HuffEnv make_env(const BatchDev& b, const ImageDesc& im, uint32_t clean_len, const uint32_t* words,
+    const uint16_t* lut, const TabSel* tabsel)
+{
+    HuffEnv env;
+    env.words = words;
+    env.lut = lut;
+    env.tabsel = tabsel;
+    env.pool = b.huff;
+    env.seg = b.seg_start + im.seg_first;
+    env.num_segments = im.num_segments;
+    env.seg_blocks = im.seg_blocks;
+    env.total_blocks = im.total_blocks;
+    env.clean_bits = clean_len * 8u;
+    env.bpm = im.bpm;
+    return env;
+}
+
+// Decode subsequence k of an image from entry state E in synchronisation mode and publish the result.
+// Returns true if the exit state differs from the one recorded before.
+template <bool PRESWAPPED>
+__device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& env, uint32_t t, uint32_t k, unsigned long long E, bool exact)
+{
+    HuffState s;
+    s.p = uint32_t(E);
+    const uint32_t slot = uint32_t(E >> 32);
+    s.z = slot & 63u;
+    s.blk = slot >> 6;
+    s.nblk = 0;
+    s.abs = exact;
+    const uint32_t z_entry = s.z;
+    decode_span<false, PRESWAPPED>(env, s, (k + 1u) * uint32_t(b.subseq_bits), false, 0, nullptr, nullptr);
+    const unsigned long long X = pack_state(s.p, s.blk * 64u + s.z);
+    const bool changed = (X != __ldcg(b.sub_exit + t));
+    b.sub_exit[t] = X;
+    b.sub_entry[t] = E;
+    // slots consumed: absolute (from the image start) once a known state was passed, else relative to the entry
+    const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
+    b.sub_rec[t] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
+    return changed;
+}
+
+extern __shared__ __align__(16) unsigned char g_dyn_smem[];
+
+__global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
+{
+    const int img = find_image_h(b.cta_map_subseq, b.num_images, blockIdx.x);
+    const ImageDesc& im = b.images[img];
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, 8);
+    const uint32_t k0 = (blockIdx.x - b.cta_map_subseq[img]) * kSubseqCta;
+    stage_cta(b, im, sm, k0);
+    const uint32_t k = k0 + threadIdx.x;
+    const uint32_t t = im.subseq_first + k;
+    const uint32_t clean_len = b.states[img].clean_len;
+    const uint32_t clean_bits = clean_len * 8u;
+    const uint32_t S = uint32_t(b.subseq_bits);
+    const bool idle = uint64_t(k) * S >= uint64_t(clean_bits);
+    const bool staged = b.stream_words != 0;
+    const uint32_t* words = staged ? sm.stream + threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5)
+                                   : reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
+    const HuffEnv env = make_env(b, im, clean_len, words, sm.lut, sm.tabsel);
+    if (round == 0) {
+        if (idle) {
+            b.sub_exit[t] = b.sub_entry[t] = pack_state(clean_bits, 0);
+            b.sub_rec[t] = 0;
+            return;
+        }
+        b.sub_exit[t] = ~0ull;
+        const unsigned long long E = pack_state(k * S, 0);
+        if (staged)
+            sync_decode<true>(b, env, t, k, E, k == 0);
+        else
+            sync_decode<false>(b, env, t, k, E, k == 0);
+    } else {
+        if (idle || k == 0)
+            return;
+        const unsigned long long E = b.sub_exit[t - 1];
+        if (E == b.sub_entry[t])
+            return;
+        const bool changed = staged ? sync_decode<true>(b, env, t, k, E, false) : sync_decode<false>(b, env, t, k, E, false);
+        const bool next_live = uint64_t(k + 1) * S < uint64_t(clean_bits);
+        if (changed && next_live) {
+            const uint32_t i = atomicAdd(&b.sync->count[0], 1u);
+            b.worklist[0][i] = t + 1;
+        }
+    }
+}
+
+// Jacobi rounds over the work list until no subsequence changes any more.  Cooperative launch: every CTA is resident,
+// grid.sync() separates the rounds.  Round r reads list r & 1 (length count[r % 3]) and appends to list (r + 1) & 1
+// (length count[(r + 1) % 3]); count[(r + 2) % 3] is cleared for the round after.
+// These rounds are latency bound (a chain of n unsynchronised subsequences takes n rounds, each as long as one thread
+// needs for one subsequence), so everything the decode loop touches is staged in shared memory first: the whole LUT pool
+// (when it has at most lut_slots tables), and per thread its image's table selectors and its subsequence's words.
+__global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b)
+{
+    cg::grid_group grid = cg::this_grid();
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kSubseqCta * 8);
+    const bool pool_staged = b.num_tables <= b.lut_slots;
+    if (pool_staged) {
+        for (int s = 0; s < b.num_tables; ++s)
+            for (int i = threadIdx.x; i < kLutEntries / 8; i += kSubseqCta)
+                reinterpret_cast<uint4*>(sm.lut + s * kLutEntries)[i] = reinterpret_cast<const uint4*>(b.huff[s].lut)[i];
+    }
+    __syncthreads();
+    const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t S = uint32_t(b.subseq_bits), spw = S >> 5, W = uint32_t(b.stream_words);
+    TabSel* my_tabsel = sm.tabsel + threadIdx.x * 8;
+    uint32_t* my_words = sm.stream + threadIdx.x * W;
+    uint32_t redone = 0;
+    int r = 0;
+    for (; r < kMaxTailRounds; ++r) {
+        const uint32_t n = __ldcg(&b.sync->count[r % 3]);
+        if (n == 0)
+            break;
+        if (tid == 0)
+            b.sync->count[(r + 2) % 3] = 0;
+        const uint32_t* in = b.worklist[r & 1];
+        uint32_t* out = b.worklist[(r + 1) & 1];
+        for (uint32_t i = tid; i < n; i += nthreads) {
+            const uint32_t t = __ldcg(in + i);
+            const int img = find_image_h(b.cta_map_subseq, b.num_images, t / kSubseqCta);
+            const ImageDesc& im = b.images[img];
+            const uint32_t k = t - im.subseq_first;
+            const unsigned long long E = __ldcg(b.sub_exit + t - 1); // written by other SMs in earlier rounds: bypass L1
+            if (E == __ldcg(b.sub_entry + t))
+                continue;
+            const uint32_t clean_len = b.states[img].clean_len;
+            const uint32_t* gwords = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
+            const uint16_t* lut = reinterpret_cast<const uint16_t*>(b.huff);
+            const TabSel* tabsel = im.tabsel_g;
+            if (pool_staged) { // selectors relative to the staged pool: table i sits at i * kLutEntries
+                for (int j = 0; j < im.bpm; ++j) {
+                    const TabSel g = im.tabsel_g[j];
+                    my_tabsel[j] = TabSel{g.dc_idx * kLutEntries, g.ac_idx * kLutEntries, g.dc_idx, g.ac_idx};
+                }
+                lut = sm.lut;
+                tabsel = my_tabsel;
+            }
+            bool changed;
+            if (W) {
+                const uint32_t first = k * spw, max_words = (im.raw_len + 16u) >> 2;
+                for (uint32_t j = 0; j < W; ++j)
+                    my_words[j] = first + j < max_words ? __byte_perm(gwords[first + j], 0, 0x0123) : 0u;
+                const HuffEnv env = make_env(b, im, clean_len, my_words - first, lut, tabsel);
+                changed = sync_decode<true>(b, env, t, k, E, false);
+            } else {
+                const HuffEnv env = make_env(b, im, clean_len, gwords, lut, tabsel);
+                changed = sync_decode<false>(b, env, t, k, E, false);
+            }
+            ++redone;
+            if (changed && uint64_t(k + 1) * S < uint64_t(clean_len) * 8u)
+                out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
+        }
+        grid.sync();
+    }
+    if (redone)
+        atomicAdd(&b.sync->redone, redone);
+    if (tid == 0)
+        b.sync->rounds = uint32_t(r);
+}
+
+// segmented-scan combine: a = earlier prefix, x = later element; bit31 = "absolute" flag
+__device__ __forceinline__ uint32_t seg_combine(uint32_t a, uint32_t x) { return (x & 0x80000000u) ? x : a + x; }
+
+constexpr int kScanThreads = 256;
+__global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
+{
+    const int img = blockIdx.x;
+    const ImageDesc& im = b.images[img];
+    const uint32_t count = im.subseq_cta_count * kSubseqCta;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ uint32_t s_w[kScanThreads / 32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0)
+        s_carry = 0x80000000u;
+    __syncthreads();
+    bool bad = false;
+    for (uint32_t c0 = 0; c0 < count; c0 += kScanThreads) {
+        const uint32_t c = c0 + threadIdx.x;
+        uint32_t v = c < count ? b.sub_rec[im.subseq_first + c] : 0u;
+        if (c > 0 && c < count && b.sub_entry[im.subseq_first + c] != b.sub_exit[im.subseq_first + c - 1] &&
+            uint64_t(c) * uint32_t(b.subseq_bits) < uint64_t(b.states[img].clean_len) * 8u)
+            bad = true; // the chain of entry/exit states is not consistent: synchronisation did not finish
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, v, o);
+            if (lane >= uint32_t(o))
+                v = seg_combine(tprev, v);
+        }
+        if (lane == 31)
+            s_w[warp] = v;
+        __syncthreads();
+        uint32_t pre = s_carry;
+        for (int i = 0; i < int(warp); ++i)
+            pre = seg_combine(pre, s_w[i]);
+        v = seg_combine(pre, v);
+        if (c < count)
+            b.sub_abs[im.subseq_first + c] = v;
+        __syncthreads();
+        if (threadIdx.x == kScanThreads - 1)
+            s_carry = v;
+        __syncthreads();
+    }
+    if (bad)
+        atomicOr(&b.states[img].error, kErrNotConverged);
+}
+
+__global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
+{
+    const int img = find_image_h(b.cta_map_subseq, b.num_images, blockIdx.x);
+    const ImageDesc& im = b.images[img];
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, 8);
+    const uint32_t cta = blockIdx.x - b.cta_map_subseq[img];
+    const uint32_t k0 = cta * kSubseqCta, k = k0 + threadIdx.x;
+    stage_cta(b, im, sm, k0);
+    const uint32_t t = im.subseq_first + k;
+    const uint32_t clean_len = b.states[img].clean_len;
+    const uint32_t clean_bits = clean_len * 8u;
+    const uint32_t S = uint32_t(b.subseq_bits);
+
+    // blocks this CTA owns: those that *start* inside its subsequences
+    const uint32_t n_first = k0 == 0 ? 0u : (b.sub_abs[im.subseq_first + k0 - 1] & 0x7FFFFFFFu);
+    const bool last_cta = cta + 1 == im.subseq_cta_count;
+    const uint32_t n_next = b.sub_abs[im.subseq_first + k0 + kSubseqCta - 1] & 0x7FFFFFFFu;
+    const uint32_t first_block = (n_first + 63u) >> 6;
+    uint32_t end_block = last_cta ? im.total_blocks : (n_next + 63u) >> 6;
+    if (end_block > im.total_blocks)
+        end_block = im.total_blocks;
+    int16_t* coef = b.coef + im.coef_off;
+    int16_t* dc = b.dc + im.coef_off / 64;
+    if (end_block > first_block) { // zero the owned coefficient range: the scattered stores below then hit lines in L2
+        uint4* z4 = reinterpret_cast<uint4*>(coef + uint64_t(first_block) * 64);
+        const uint32_t n16 = (end_block - first_block) * 8u;
+        for (uint32_t i = threadIdx.x; i < n16; i += kSubseqCta)
+            z4[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    if (uint64_t(k) * S >= uint64_t(clean_bits))
+        return;
+    HuffState s;
+    if (k == 0) {
+        s.p = 0;
+        s.z = 0;
+        s.blk = 0;
+        s.nblk = 0;
+    } else {
+        const unsigned long long E = b.sub_exit[t - 1];
+        const uint32_t slot = uint32_t(E >> 32);
+        s.p = uint32_t(E);
+        s.z = slot & 63u;
+        s.blk = slot >> 6;
+        s.nblk = (b.sub_abs[t - 1] & 0x7FFFFFFFu) >> 6;
+    }
+    s.abs = true;
+    const bool extend = (threadIdx.x == kSubseqCta - 1) || (uint64_t(k + 1) * S >= uint64_t(clean_bits));
+    const uint32_t* gwords = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
+    const uint32_t end = (k + 1u) * S;
+    uint32_t err = 0;
+    if (b.stream_words) {
+        const HuffEnv env = make_env(b, im, clean_len, sm.stream + threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5), sm.lut, sm.tabsel);
+        err = decode_span<true, true>(env, s, end, false, first_block, coef, dc);
+        if (extend) { // finish the block that straddles into the next CTA's subsequences, reading the stream from global memory
+            const HuffEnv env_g = make_env(b, im, clean_len, gwords, sm.lut, sm.tabsel);
+            err |= decode_span<true, false>(env_g, s, end, true, first_block, coef, dc);
+        }
+    } else {
+        const HuffEnv env = make_env(b, im, clean_len, gwords, sm.lut, sm.tabsel);
+        err = decode_span<true, false>(env, s, end, extend, first_block, coef, dc);
+    }
+    if (s.nblk == im.total_blocks && s.z == 0 && extend)
+        b.states[img].done_blocks = s.nblk;
+    if (err)
+        atomicOr(&b.states[img].error, err);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Launchers
+// ------------------------------------------------------------------------------------------------------------------
+static size_t main_smem_bytes(const BatchDev& b) { return size_t(b.lut_slots) * kLutEntries * 2 + 8 * sizeof(TabSel) + size_t(kSubseqCta) * b.stream_words * 4; }
+static size_t tail_smem_bytes(const BatchDev& b)
+{
+    return size_t(b.lut_slots) * kLutEntries * 2 + size_t(kSubseqCta) * 8 * sizeof(TabSel) + size_t(kSubseqCta) * b.stream_words * 4;
+}
+
+int huff_configure(const BatchDev& b, int device, int* tail_grid)
+{
+    const size_t ms = main_smem_bytes(b), ts = tail_smem_bytes(b);
+    if (cudaFuncSetAttribute(k_huff_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ms)) != cudaSuccess ||
+        cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ms)) != cudaSuccess ||
+        cudaFuncSetAttribute(k_huff_sync_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ts)) != cudaSuccess)
+        return -1;
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_huff_sync_tail, kSubseqCta, ts) != cudaSuccess || per_sm < 1)
+        return -1;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms < 1)
+        return -1;
+    if (per_sm > 2)
+        per_sm = 2;
+    *tail_grid = per_sm * sms;
+    return 0;
+}
+
+int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid)
+{
+    const size_t ms = main_smem_bytes(b);
+    k_huff_sync<<<d.subseq_ctas, kSubseqCta, ms, st>>>(b, 0);
+    k_huff_sync<<<d.subseq_ctas, kSubseqCta, ms, st>>>(b, 1);
+    BatchDev bb = b;
+    void* args[] = {&bb};
+    if (cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_huff_sync_tail), dim3(tail_grid), dim3(kSubseqCta), args, tail_smem_bytes(b), st) !=
+        cudaSuccess)
+        return -1;
+    return 3;
+}
+
+int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
+{
+    k_subseq_scan<<<d.num_images, kScanThreads, 0, st>>>(b);
+    k_huff_write<<<d.subseq_ctas, kSubseqCta, main_smem_bytes(b), st>>>(b);
+    return 2;
+}
+
+} // namespace b200jpeg

@@ -76,9 +76,9 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         HuffEnv env;
         env.words = reinterpret_cast<const uint32_t*>(clean.data() + im.clean_off);
         if (shared_layout) { // what stage_tables() builds in shared memory
-            s_lut.assign(size_t(kMaxTabSlots) * kLutSize, 0);
+            s_lut.assign(size_t(kMaxTabSlots) * kLutEntries, 0);
             for (int s = 0; s < im.ntabs; ++s)
-                std::memcpy(&s_lut[size_t(s) * kLutSize], plan.huff[im.tab_pool[s]].lut, kLutSize * 2);
+                std::memcpy(&s_lut[size_t(s) * kLutEntries], plan.huff[im.tab_pool[s]].lut, kLutEntries * 2);
             env.lut = s_lut.data();
             env.tabsel = im.tabsel_s;
         } else {
