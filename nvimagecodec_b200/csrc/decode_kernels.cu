@@ -341,149 +341,28 @@ __global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
     const int dcval = b.dc[im.coef_off / 64 + ref.src_blk];
     uint32_t out[16];
     idct_block(blk, dcval, s_q + ref.comp * 64, out);
+    // Horizontally subsampled planes: the colour kernel reads column ds_w as the right neighbour of the last real column
+    // ds_w - 1 (the reference's edge rule is "the neighbour of the last column is the column itself", jdsample.c:276-411),
+    // so when both sit in this block (ds_w % 8 != 0) column ds_w gets a copy of column ds_w - 1.
+    const int dsw = im.ds_w[ref.comp];
+    if (im.hs[ref.comp] < im.hmax && (dsw & 7) != 0) {
+        const int bx = int((ref.dst - im.plane_off[ref.comp]) % uint64_t(ref.pitch)) >> 3;
+        if (bx == (dsw >> 3)) {
+            const int e = dsw & 7; // 1..7: copy sample e-1 to sample e in every row
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const unsigned long long v = (unsigned long long)out[2 * r] | ((unsigned long long)out[2 * r + 1] << 32);
+                const unsigned long long src = (v >> (8 * (e - 1))) & 0xFFull;
+                const unsigned long long w = (v & ~(0xFFull << (8 * e))) | (src << (8 * e));
+                out[2 * r] = uint32_t(w);
+                out[2 * r + 1] = uint32_t(w >> 32);
+            }
+        }
+    }
     uint8_t* dst = b.planes + ref.dst;
 #pragma unroll
     for (int r = 0; r < 8; ++r)
         *reinterpret_cast<uint2*>(dst + r * ref.pitch) = make_uint2(out[2 * r], out[2 * r + 1]);
-}
-
-// ------------------------------------------------------------------------------------------------------------------
-// Colour: a warp tile is 512 pixels x VY rows.  Each lane converts 16 pixels per row, the warp's rows are assembled in
-// shared memory and written out with one 4-byte word per lane per store instruction (128 contiguous bytes per
-// instruction) whatever the alignment of the destination row.
-// ------------------------------------------------------------------------------------------------------------------
-constexpr int kRowWords = kColorTilePx * 3 / 4; // interleaved RGB row of a tile in 32-bit words
-
-// copy nbytes from shared memory (word aligned, one spare word readable past the end) to dst (any alignment)
-__device__ __forceinline__ void warp_store_row(uint8_t* dst, const uint32_t* s_row, int nbytes, uint32_t lane)
-{
-    const uint32_t m = uint32_t(reinterpret_cast<uintptr_t>(dst) & 3u);
-    const uint8_t* sb = reinterpret_cast<const uint8_t*>(s_row);
-    if (m == 0) {
-        const int nw = nbytes >> 2;
-        uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
-        for (int w = int(lane); w < nw; w += 32)
-            d32[w] = s_row[w];
-        const int done = nw << 2;
-        if (int(lane) < nbytes - done)
-            dst[done + lane] = sb[done + lane];
-    } else {
-        int head = int(4u - m);
-        if (head > nbytes)
-            head = nbytes;
-        if (int(lane) < head)
-            dst[lane] = sb[lane];
-        const int nw = (nbytes - head) >> 2;
-        uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
-        const uint32_t sh = uint32_t(head) * 8u;
-        for (int w = int(lane); w < nw; w += 32)
-            d32[w] = __funnelshift_r(s_row[w], s_row[w + 1], sh);
-        const int done = head + (nw << 2);
-        if (int(lane) < nbytes - done)
-            dst[done + lane] = sb[done + lane];
-    }
-}
-
-template <int HX, int VY>
-__device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& im, uint32_t tile, uint32_t* s_warp, uint32_t lane)
-{
-    const int q = int(tile / uint32_t(im.color_xtiles)) - (VY == 2 ? 1 : 0);
-    const int xt = int(tile % uint32_t(im.color_xtiles));
-    const int xbase = xt * kColorTilePx;
-    const int x0 = xbase + int(lane) * 16;
-    uint32_t px[VY * 16];
-    int yrow[VY];
-    if (x0 < im.width) {
-        color_unit<HX, VY>(b, im, q, x0, px, yrow);
-    } else {
-#pragma unroll
-        for (int r = 0; r < VY; ++r)
-            yrow[r] = -1;
-        // rows of this tile must be known by every lane: recompute validity below from lane 0
-    }
-    // row validity is a property of the tile, take it from lane 0 (always inside the image)
-    int yr[VY];
-#pragma unroll
-    for (int r = 0; r < VY; ++r)
-        yr[r] = __shfl_sync(0xFFFFFFFFu, yrow[r], 0);
-    const int tile_px = im.width - xbase < kColorTilePx ? im.width - xbase : kColorTilePx;
-    const int fmt = im.out_fmt;
-    if (fmt == 4 || fmt == 6) { // interleaved
-#pragma unroll
-        for (int r = 0; r < VY; ++r) {
-            uint32_t* s_row = s_warp + r * (kRowWords + 4);
-            if (x0 < im.width) {
-                uint32_t w[12];
-#pragma unroll
-                for (int g = 0; g < 4; ++g) { // 4 pixels -> 3 words
-                    const uint32_t a = px[r * 16 + 4 * g], c = px[r * 16 + 4 * g + 1], d = px[r * 16 + 4 * g + 2], e = px[r * 16 + 4 * g + 3];
-                    w[3 * g] = (a & 0xFFFFFFu) | (c << 24);
-                    w[3 * g + 1] = ((c >> 8) & 0xFFFFu) | (d << 16);
-                    w[3 * g + 2] = ((d >> 16) & 0xFFu) | (e << 8);
-                }
-                uint4* s4 = reinterpret_cast<uint4*>(s_row + lane * 12);
-                s4[0] = make_uint4(w[0], w[1], w[2], w[3]);
-                s4[1] = make_uint4(w[4], w[5], w[6], w[7]);
-                s4[2] = make_uint4(w[8], w[9], w[10], w[11]);
-            }
-        }
-        __syncwarp();
-#pragma unroll
-        for (int r = 0; r < VY; ++r)
-            if (yr[r] >= 0)
-                warp_store_row(im.out + int64_t(yr[r]) * im.out_stride + int64_t(xbase) * 3, s_warp + r * (kRowWords + 4), tile_px * 3, lane);
-    } else { // planar: P_RGB / P_BGR three planes, P_Y one
-        const int nplanes = fmt == 7 ? 1 : 3;
-        constexpr int kPlaneWords = kColorTilePx / 4 + 4;
-#pragma unroll
-        for (int r = 0; r < VY; ++r) {
-            if (x0 < im.width) {
-                for (int pl = 0; pl < nplanes; ++pl) {
-                    uint32_t w[4];
-#pragma unroll
-                    for (int g = 0; g < 4; ++g)
-                        w[g] = ((px[r * 16 + 4 * g] >> (8 * pl)) & 255u) | (((px[r * 16 + 4 * g + 1] >> (8 * pl)) & 255u) << 8) |
-                               (((px[r * 16 + 4 * g + 2] >> (8 * pl)) & 255u) << 16) | (((px[r * 16 + 4 * g + 3] >> (8 * pl)) & 255u) << 24);
-                    *reinterpret_cast<uint4*>(s_warp + (r * 3 + pl) * kPlaneWords + lane * 4) = make_uint4(w[0], w[1], w[2], w[3]);
-                }
-            }
-        }
-        __syncwarp();
-#pragma unroll
-        for (int r = 0; r < VY; ++r)
-            if (yr[r] >= 0)
-                for (int pl = 0; pl < nplanes; ++pl)
-                    warp_store_row(im.out + (int64_t(pl) * im.height + yr[r]) * im.out_stride + xbase, s_warp + (r * 3 + pl) * kPlaneWords,
-                        tile_px, lane);
-    }
-    __syncwarp();
-}
-
-constexpr int kColorWarpWords = 800; // >= 2 * (kRowWords + 4) and >= 6 * (kColorTilePx / 4 + 4)
-static_assert(kColorWarpWords >= 6 * (kColorTilePx / 4 + 4) && kColorWarpWords >= 2 * (kRowWords + 4), "staging must fit");
-
-__global__ void __launch_bounds__(kColorCta) k_color(BatchDev b)
-{
-    __shared__ __align__(16) uint32_t s_stage[(kColorCta / 32) * kColorWarpWords];
-    const int img = find_image(b.cta_map_color, b.num_images, blockIdx.x);
-    const ImageDesc& im = b.images[img];
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t tile = (blockIdx.x - b.cta_map_color[img]) * (kColorCta / 32) + warp;
-    if (tile >= uint32_t(im.color_rows) * uint32_t(im.color_xtiles))
-        return;
-    uint32_t* s_warp = s_stage + warp * kColorWarpWords;
-    const int hx = color_hx(im), vy = color_vy(im);
-    if (vy == 2) {
-        if (hx == 2)
-            color_tile<2, 2>(b, im, tile, s_warp, lane);
-        else
-            color_tile<1, 2>(b, im, tile, s_warp, lane);
-    } else {
-        if (hx == 2)
-            color_tile<2, 1>(b, im, tile, s_warp, lane);
-        else
-            color_tile<1, 1>(b, im, tile, s_warp, lane);
-    }
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -506,12 +385,6 @@ int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
 int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
 {
     k_idct<<<d.idct_ctas, kIdctCta, 0, st>>>(b);
-    return 1;
-}
-
-int launch_color(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
-{
-    k_color<<<d.color_ctas, kColorCta, 0, st>>>(b);
     return 1;
 }
 
