@@ -46,7 +46,12 @@ struct ByteClass
     uint32_t bad;    // any other marker
 };
 
-// Classify the 16 bytes at [base, base+16) of an image's raw scan data.
+// byte mask (0xFF / 0x00 per byte) -> 4 bits
+__device__ __forceinline__ uint32_t mask4(uint32_t m) { return ((m & 0x01010101u) * 0x01020408u) >> 24; }
+
+// Classify the 16 bytes at [base, base+16) of an image's raw scan data, four bytes per SIMD-in-register step.
+//   removed: 00 after FF (stuffing), FF before FF (fill), FF Dn and the Dn after FF (restart marker); anything else after
+//   an FF is a marker that must not occur inside entropy-coded data.
 __device__ __forceinline__ ByteClass classify16(const uint8_t* __restrict__ raw, uint32_t raw_len, uint32_t base, uint32_t w[4], uint32_t& next)
 {
     if (base + 16 <= raw_len) {
@@ -57,32 +62,28 @@ __device__ __forceinline__ ByteClass classify16(const uint8_t* __restrict__ raw,
         for (uint32_t i = 0; base + i < raw_len && i < 16; ++i)
             w[i >> 2] |= uint32_t(raw[base + i]) << (8 * (i & 3));
     }
-    uint32_t prev = (base > 0 && base <= raw_len) ? raw[base - 1] : 0;
+    const uint32_t prev = (base > 0 && base <= raw_len) ? raw[base - 1] : 0;
     next = (base + 16 < raw_len) ? raw[base + 16] : 0;
-    ByteClass c{0, 0, 0};
+    uint32_t remove = 0, marker = 0, bad = 0;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        const uint32_t cur = (w[i >> 2] >> (8 * (i & 3))) & 255u;
-        const uint32_t nx = (i < 15) ? ((w[(i + 1) >> 2] >> (8 * ((i + 1) & 3))) & 255u) : next;
-        const bool in = base + i < raw_len;
-        const bool has_next = base + i + 1 < raw_len;
-        bool remove = false;
-        if (cur == 0x00 && prev == 0xFF)
-            remove = true;
-        else if (cur == 0xFF && nx == 0xFF)
-            remove = true;
-        else if (cur == 0xFF && nx >= 0xD0 && nx <= 0xD7) {
-            remove = true;
-            if (in)
-                c.marker |= 1u << i;
-        } else if (cur >= 0xD0 && cur <= 0xD7 && prev == 0xFF)
-            remove = true;
-        else if (cur == 0xFF && nx != 0 && has_next)
-            c.bad = 1;
-        if (in && !remove)
-            c.keep |= 1u << i;
-        prev = cur;
+    for (int j = 0; j < 4; ++j) {
+        const uint32_t cur = w[j];
+        const uint32_t pw = (cur << 8) | (j ? (w[j > 0 ? j - 1 : 0] >> 24) : prev);
+        const uint32_t nw = (cur >> 8) | ((j < 3 ? w[j < 3 ? j + 1 : 3] : next) << 24);
+        const uint32_t ff = __vcmpeq4(cur, 0xFFFFFFFFu), zz = __vcmpeq4(cur, 0u), rst = __vcmpeq4(cur & 0xF8F8F8F8u, 0xD0D0D0D0u);
+        const uint32_t pff = __vcmpeq4(pw, 0xFFFFFFFFu);
+        const uint32_t nff = __vcmpeq4(nw, 0xFFFFFFFFu), nz = __vcmpeq4(nw, 0u), nrst = __vcmpeq4(nw & 0xF8F8F8F8u, 0xD0D0D0D0u);
+        remove |= mask4((zz & pff) | (ff & (nff | nrst)) | (rst & pff)) << (4 * j);
+        marker |= mask4(ff & nrst) << (4 * j);
+        bad |= mask4(ff & ~(nz | nff | nrst)) << (4 * j);
     }
+    const uint32_t n_in = raw_len - base < 16u ? raw_len - base : 16u;
+    const uint32_t in_mask = (1u << n_in) - 1u;
+    ByteClass c;
+    c.keep = ~remove & in_mask;
+    c.marker = marker & in_mask;
+    const uint32_t n_succ = raw_len - base - 1u < 16u ? raw_len - base - 1u : 16u; // bytes that have a successor inside the data
+    c.bad = (bad & ((1u << n_succ) - 1u)) ? 1u : 0u;
     return c;
 }
 
@@ -185,29 +186,61 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
             wpre += s_w[i];
     const uint32_t excl = wpre + inc - mine;
     const uint64_t cb = b.chunk_counts[im.chunk_first + chunk];
-    uint32_t pos = uint32_t(cb) + (excl & 0xFFFFu);
+    // kept bytes are compacted into shared memory first, then copied out with aligned 4-byte stores
+    __shared__ __align__(16) uint32_t s_out[kChunkBytes / 4 + 4];
+    __shared__ uint32_t s_total;
+    uint8_t* sb = reinterpret_cast<uint8_t*>(s_out);
+    uint32_t lpos = excl & 0xFFFFu;                    // position inside the chunk's output
+    const uint32_t gbase = uint32_t(cb);               // position of the chunk's output in the image's clean stream
     uint32_t ord = uint32_t(cb >> 32) + (excl >> 16);
-    uint8_t* dst = b.clean + im.clean_off;
     uint32_t* S = b.seg_start + im.seg_first;
     uint32_t bad = 0;
+    if (c.keep == 0xFFFFu && (lpos & 3u) == 0) {
+        uint32_t* s32 = s_out + (lpos >> 2);
+        s32[0] = w[0];
+        s32[1] = w[1];
+        s32[2] = w[2];
+        s32[3] = w[3];
+        lpos += 16;
+    } else {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        const uint32_t cur = (w[i >> 2] >> (8 * (i & 3))) & 255u;
-        if (c.keep & (1u << i))
-            dst[pos++] = uint8_t(cur);
-        if (c.marker & (1u << i)) {
-            const uint32_t nx = (i < 15) ? ((w[(i + 1) >> 2] >> (8 * ((i + 1) & 3))) & 255u) : next;
-            if (ord + 1 < uint32_t(im.num_segments)) {
-                S[ord + 1] = pos;
-                if (nx != 0xD0u + (ord & 7u))
+        for (int i = 0; i < 16; ++i) {
+            const uint32_t cur = (w[i >> 2] >> (8 * (i & 3))) & 255u;
+            if (c.keep & (1u << i))
+                sb[lpos++] = uint8_t(cur);
+            if (c.marker & (1u << i)) {
+                const uint32_t nx = (i < 15) ? ((w[(i + 1) >> 2] >> (8 * ((i + 1) & 3))) & 255u) : next;
+                if (ord + 1 < uint32_t(im.num_segments)) {
+                    S[ord + 1] = gbase + lpos;
+                    if (nx != 0xD0u + (ord & 7u))
+                        bad = 1;
+                } else
                     bad = 1;
-            } else
-                bad = 1;
-            ++ord;
+                ++ord;
+            }
         }
     }
+    if (threadIdx.x == kUnstuffThreads - 1)
+        s_total = lpos;
     if (bad)
         atomicOr(&b.states[img].error, kErrBadMarker);
+    __syncthreads();
+    const uint32_t K = s_total;
+    uint8_t* d = b.clean + im.clean_off + gbase;
+    const uint32_t m = uint32_t(reinterpret_cast<uintptr_t>(d) & 3u);
+    uint32_t head = m ? 4u - m : 0u;
+    if (head > K)
+        head = K;
+    if (threadIdx.x < head)
+        d[threadIdx.x] = sb[threadIdx.x];
+    const uint32_t nw = (K - head) >> 2;
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(d + head);
+    const uint32_t sh = head * 8u;
+    for (uint32_t i = threadIdx.x; i < nw; i += kUnstuffThreads)
+        d32[i] = head ? __funnelshift_r(s_out[i], s_out[i + 1], sh) : s_out[i];
+    const uint32_t done = head + (nw << 2);
+    if (threadIdx.x < K - done)
+        d[done + threadIdx.x] = sb[done + threadIdx.x];
 }
 
 // ------------------------------------------------------------------------------------------------------------------
