@@ -141,7 +141,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=64)
-    ap.add_argument("--options", default=":fancy_upsampling=1 :profile=1")
+    ap.add_argument("--options", default=":fancy_upsampling=1")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -203,20 +203,30 @@ def main():
         dec.run(stream)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stage_acc = {}
     launches = 0
     with ClockSampler(local_rank) as clocks:
         e0.record()
         for _ in range(args.steps):
             st = dec.run(stream)
             launches += dec.stats()["launches"]
-            for k, v in (dec.stage_times() or {}).items():
-                stage_acc[k] = stage_acc.get(k, 0.0) + v
         e1.record()
         barrier()
     assert all(s == 0 for s in st)
     ms_total = e0.elapsed_time(e1)
     stats = dec.stats()
+
+    # ---- per-stage device times: same batch, same steps, single stream with CUDA events between the stages ----
+    stage_acc = {}
+    decp = Decoder(local_rank, options=args.options + " :profile=1")
+    st = decp.prepare(datas, ptrs, strides, fmts, False)
+    for _ in range(args.warmup):
+        decp.run(stream)
+    for _ in range(args.steps):
+        decp.run(stream)
+        for k, v in (decp.stage_times() or {}).items():
+            stage_acc[k] = stage_acc.get(k, 0.0) + v
+    decp.close()
+    barrier()
 
     # ---- e2e: host JPEG bytes -> host RGB through the C ABI ----
     houts = [torch.empty((H, W * 3), dtype=torch.uint8).pin_memory() for _ in range(n)]

@@ -126,10 +126,18 @@ int b200jpeg_decode_run(b200jpegDecoder_t decoder, void* user_stream, int32_t* s
 int b200jpeg_decode_batch(b200jpegDecoder_t decoder, int n, const uint8_t* const* data, const size_t* sizes,
     const b200jpegOutput_t* outputs, void* user_stream, int32_t* statuses)
 {
-    const int rc = b200jpeg_decode_prepare(decoder, n, data, sizes, outputs, statuses);
-    if (rc != B200JPEG_STATUS_SUCCESS)
-        return rc;
-    return b200jpeg_decode_run(decoder, user_stream, statuses);
+    if (!decoder || n < 0)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    try {
+        std::vector<Decoder::OutputDesc> outs(n);
+        for (int i = 0; i < n; ++i)
+            outs[i] = Decoder::OutputDesc{outputs[i].buffer, outputs[i].row_stride, outputs[i].format, outputs[i].on_host};
+        return decoder->impl->decode(n, data, sizes, outs.data(), static_cast<cudaStream_t>(user_stream), statuses);
+    } catch (const std::bad_alloc&) {
+        return B200JPEG_STATUS_ALLOC_FAILED;
+    } catch (...) {
+        return B200JPEG_STATUS_INTERNAL_ERROR;
+    }
 }
 
 int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats8)

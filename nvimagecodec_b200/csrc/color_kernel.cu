@@ -308,10 +308,11 @@ constexpr int kColorWarpWords = 2 * 3 * kPlaneStride > 2 * kRowStride ? 2 * 3 * 
 __global__ void __launch_bounds__(kColorCta) k_color(BatchDev b)
 {
     __shared__ __align__(16) uint32_t s_stage[(kColorCta / 32) * kColorWarpWords];
-    const int img = find_image_c(b.cta_map_color, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.base_color;
+    const int img = find_image_c(b.cta_map_color, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t tile = (blockIdx.x - b.cta_map_color[img]) * (kColorCta / 32) + warp;
+    const uint32_t tile = (cta_abs - b.cta_map_color[img]) * (kColorCta / 32) + warp;
     if (tile >= uint32_t(im.color_rows) * uint32_t(im.color_xtiles))
         return;
     uint32_t* s_warp = s_stage + warp * kColorWarpWords;

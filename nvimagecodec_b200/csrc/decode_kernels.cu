@@ -89,9 +89,10 @@ __device__ __forceinline__ ByteClass classify16(const uint8_t* __restrict__ raw,
 
 __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_count(BatchDev b)
 {
-    const int img = find_image(b.cta_map_unstuff, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.base_unstuff;
+    const int img = find_image(b.cta_map_unstuff, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
-    const uint32_t chunk = blockIdx.x - b.cta_map_unstuff[img];
+    const uint32_t chunk = cta_abs - b.cta_map_unstuff[img];
     const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
     uint32_t w[4], next;
     ByteClass c{0, 0, 0};
@@ -157,9 +158,10 @@ __global__ void __launch_bounds__(32) k_unstuff_scan(BatchDev b)
 
 __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
 {
-    const int img = find_image(b.cta_map_unstuff, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.base_unstuff;
+    const int img = find_image(b.cta_map_unstuff, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
-    const uint32_t chunk = blockIdx.x - b.cta_map_unstuff[img];
+    const uint32_t chunk = cta_abs - b.cta_map_unstuff[img];
     const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
     uint32_t w[4] = {0, 0, 0, 0}, next = 0;
     ByteClass c{0, 0, 0};
@@ -345,11 +347,12 @@ __global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
 {
     __shared__ __align__(16) uint8_t s_blk[kIdctCta * kIdctPitch];
     __shared__ uint16_t s_q[3 * 64];
-    const int img = find_image(b.cta_map_idct, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.base_idct;
+    const int img = find_image(b.cta_map_idct, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     for (int i = threadIdx.x; i < im.ncomp_out * 64; i += kIdctCta)
         s_q[i] = b.quant[im.qt[i >> 6] * 64 + (i & 63)];
-    const uint32_t u = (blockIdx.x - b.cta_map_idct[img]) * kIdctCta + threadIdx.x;
+    const uint32_t u = (cta_abs - b.cta_map_idct[img]) * kIdctCta + threadIdx.x;
     const IdctBlockRef ref = idct_locate(im, u);
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint8_t* wbuf = s_blk + warp * 32 * kIdctPitch;

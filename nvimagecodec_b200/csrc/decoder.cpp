@@ -62,6 +62,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
                 o.subseq_bytes = v;
         } else if (name == "copy_threads")
             o.copy_threads = std::max(1, std::atoi(value.c_str()));
+        else if (name == "groups")
+            o.groups = std::max(1, std::atoi(value.c_str()));
         else if (name == "stage_stream")
             o.stage_stream = std::atoi(value.c_str()) != 0;
         else if (name == "profile")
@@ -90,8 +92,11 @@ Decoder::~Decoder()
     for (cudaEvent_t e : ev_stage_)
         if (e)
             cudaEventDestroy(e);
-    if (stream_)
-        cudaStreamDestroy(stream_);
+    if (ev_meta_)
+        cudaEventDestroy(ev_meta_);
+    for (cudaStream_t st : streams_)
+        if (st)
+            cudaStreamDestroy(st);
 }
 
 int Decoder::init()
@@ -107,8 +112,11 @@ int Decoder::init()
         std::fprintf(stderr, "b200jpeg: device %d is sm_%d%d; this library only carries sm_100a code\n", device_, prop.major, prop.minor);
         return B200JPEG_STATUS_ARCH_MISMATCH;
     }
-    B2J_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+    for (cudaStream_t& st : streams_)
+        B2J_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     B2J_CUDA(cudaEventCreateWithFlags(&ev_in_, cudaEventDisableTiming));
+    B2J_CUDA(cudaEventCreateWithFlags(&ev_meta_, cudaEventDisableTiming));
+    B2J_CUDA(cudaDeviceGetAttribute(&sm_count_, cudaDevAttrMultiProcessorCount, device_));
     if (opt_.profile)
         for (cudaEvent_t& e : ev_stage_)
             B2J_CUDA(cudaEventCreate(&e));
@@ -120,7 +128,8 @@ int Decoder::ensure(DevBuf& b, size_t bytes)
     if (bytes <= b.cap)
         return 0;
     if (b.p) {
-        B2J_CUDA(cudaStreamSynchronize(stream_));
+        for (cudaStream_t st : streams_)
+            B2J_CUDA(cudaStreamSynchronize(st));
         B2J_CUDA(cudaFree(b.p));
         scratch_bytes_ -= b.cap;
         b.p = nullptr;
@@ -141,7 +150,8 @@ int Decoder::ensure_pinned(DevBuf& b, size_t bytes)
     if (bytes <= b.cap)
         return 0;
     if (b.p) {
-        B2J_CUDA(cudaStreamSynchronize(stream_));
+        for (cudaStream_t st : streams_)
+            B2J_CUDA(cudaStreamSynchronize(st));
         B2J_CUDA(cudaFreeHost(b.p));
         b.p = nullptr;
         b.cap = 0;
@@ -155,9 +165,11 @@ int Decoder::ensure_pinned(DevBuf& b, size_t bytes)
     return 0;
 }
 
-int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses)
+int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses)
 {
     ready_ = false;
+    groups_.clear();
+    data_ = data;
     if (n < 0 || (n > 0 && (!data || !sizes || !outs || !statuses)))
         return B200JPEG_STATUS_INVALID_PARAMETER;
     B2J_CUDA(cudaSetDevice(device_));
@@ -228,7 +240,7 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
         (rc = ensure(d_chunks_, sizeof(uint64_t) * plan_.total_chunks)) || (rc = ensure(d_exit_, 8 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_entry_, 8 * size_t(plan_.total_subseq))) || (rc = ensure(d_rec_, 4 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_abs_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_wl0_, 4 * size_t(plan_.total_subseq))) ||
-        (rc = ensure(d_wl1_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_sync_, sizeof(SyncCounters))) ||
+        (rc = ensure(d_wl1_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_sync_, sizeof(SyncCounters) * kMaxGroups)) ||
         (dev_out_bytes && (rc = ensure(d_out_, dev_out_bytes))))
         return rc;
     for (const HostOutput& ho : host_outs_)
@@ -243,7 +255,7 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     const size_t meta_bytes = off_m0 + 4 * map_bytes;
     if ((rc = ensure(d_meta_, meta_bytes)) || (rc = ensure_pinned(h_meta_, meta_bytes)) ||
         (rc = ensure_pinned(h_raw_, plan_.raw_bytes)) ||
-        (rc = ensure_pinned(h_states_, sizeof(ImageState) * m + sizeof(SyncCounters))))
+        (rc = ensure_pinned(h_states_, sizeof(ImageState) * m + sizeof(SyncCounters) * kMaxGroups)))
         return rc;
     uint8_t* hm = static_cast<uint8_t*>(h_meta_.p);
     std::memcpy(hm + off_img, plan_.images.data(), sizeof(ImageDesc) * m);
@@ -254,27 +266,8 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     std::memcpy(hm + off_m0 + 2 * map_bytes, plan_.map_idct.data(), sizeof(uint32_t) * (m + 1));
     std::memcpy(hm + off_m0 + 3 * map_bytes, plan_.map_color.data(), sizeof(uint32_t) * (m + 1));
 
-    // ---- entropy-coded bytes -> pinned staging (parallel memcpy) ----
-    uint8_t* hr = static_cast<uint8_t*>(h_raw_.p);
-    auto copy_range = [&](int lo, int hi) {
-        for (int i = lo; i < hi; ++i) {
-            const ImageDesc& im = plan_.images[i];
-            const int bi = planned_to_batch_[i];
-            std::memcpy(hr + im.raw_off, data[bi] + parsed_[bi].scan_offset, im.raw_len);
-        }
-    };
-    const int nthreads = std::min(opt_.copy_threads, std::max(1, int(plan_.raw_bytes >> 20)));
-    if (nthreads <= 1) {
-        copy_range(0, m);
-    } else {
-        std::vector<std::thread> th;
-        for (int t = 0; t < nthreads; ++t)
-            th.emplace_back(copy_range, m * t / nthreads, m * (t + 1) / nthreads);
-        for (auto& x : th)
-            x.join();
-    }
-    B2J_CUDA(cudaMemcpyAsync(d_meta_.p, h_meta_.p, meta_bytes, cudaMemcpyHostToDevice, stream_));
-    B2J_CUDA(cudaMemcpyAsync(d_raw_.p, h_raw_.p, plan_.raw_bytes, cudaMemcpyHostToDevice, stream_));
+    B2J_CUDA(cudaMemcpyAsync(d_meta_.p, h_meta_.p, meta_bytes, cudaMemcpyHostToDevice, streams_[0]));
+    B2J_CUDA(cudaEventRecord(ev_meta_, streams_[0]));
 
     uint8_t* dm = static_cast<uint8_t*>(d_meta_.p);
     dev_ = BatchDev{};
@@ -311,7 +304,7 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     if (opt_.stage_stream && opt_.subseq_bytes <= 256)
         dev_.stream_words = (plan_.subseq_bits / 32 + 5) | 1;
     if (dev_.lut_slots != cfg_lut_slots_ || dev_.stream_words != cfg_stream_words_) {
-        if (huff_configure(dev_, device_, &tail_grid_) != 0 || tail_grid_ <= 0) {
+        if (huff_configure(dev_, device_, &tail_capacity_) != 0 || tail_capacity_ <= 0) {
             std::fprintf(stderr, "b200jpeg: cannot configure the Huffman kernels: %s\n", cudaGetErrorString(cudaGetLastError()));
             return B200JPEG_STATUS_CUDA_ERROR;
         }
@@ -319,85 +312,207 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
         cfg_stream_words_ = dev_.stream_words;
     }
     dev_.total_subseq = plan_.total_subseq;
-    dims_.num_images = m;
-    dims_.unstuff_ctas = plan_.map_unstuff.back();
-    dims_.subseq_ctas = plan_.map_subseq.back();
-    dims_.idct_ctas = plan_.map_idct.back();
-    dims_.color_ctas = plan_.map_color.back();
+    // ---- groups of consecutive images, balanced by entropy-coded bytes; each group runs on its own stream ----
+    int G = opt_.profile ? 1 : std::max(1, std::min(opt_.groups, kMaxGroups));
+    G = std::min(G, m);
+    int per_group = std::max(1, std::min(tail_capacity_ / G, sm_count_));
+    int first = 0;
+    for (int g = 0; g < G; ++g) {
+        int last = first;
+        if (g == G - 1) {
+            last = m;
+        } else {
+            const uint64_t target = plan_.raw_bytes * uint64_t(g + 1) / uint64_t(G);
+            while (last < m - (G - 1 - g) && (last == first || plan_.images[last].raw_off + plan_.images[last].raw_len / 2 <= target))
+                ++last;
+        }
+        Group gr;
+        gr.first = first;
+        gr.count = last - first;
+        gr.tail_grid = per_group;
+        gr.dev = dev_;
+        gr.dev.images = dev_.images + first;
+        gr.dev.states = dev_.states + first;
+        gr.dev.num_images = gr.count;
+        gr.dev.cta_map_unstuff = dev_.cta_map_unstuff + first;
+        gr.dev.cta_map_subseq = dev_.cta_map_subseq + first;
+        gr.dev.cta_map_idct = dev_.cta_map_idct + first;
+        gr.dev.cta_map_color = dev_.cta_map_color + first;
+        gr.dev.base_unstuff = plan_.map_unstuff[first];
+        gr.dev.base_subseq = plan_.map_subseq[first];
+        gr.dev.base_idct = plan_.map_idct[first];
+        gr.dev.base_color = plan_.map_color[first];
+        gr.dev.worklist[0] = dev_.worklist[0] + plan_.images[first].subseq_first;
+        gr.dev.worklist[1] = dev_.worklist[1] + plan_.images[first].subseq_first;
+        gr.dev.sync = dev_.sync + g;
+        gr.dims.num_images = gr.count;
+        gr.dims.unstuff_ctas = plan_.map_unstuff[last] - plan_.map_unstuff[first];
+        gr.dims.subseq_ctas = plan_.map_subseq[last] - plan_.map_subseq[first];
+        gr.dims.idct_ctas = plan_.map_idct[last] - plan_.map_idct[first];
+        gr.dims.color_ctas = plan_.map_color[last] - plan_.map_color[first];
+        gr.raw_lo = plan_.images[first].raw_off;
+        gr.raw_hi = last < m ? plan_.images[last].raw_off : plan_.raw_bytes;
+        groups_.push_back(gr);
+        first = last;
+    }
+    for (size_t i = 0; i < host_outs_.size(); ++i)
+        for (Group& gr : groups_)
+            if (host_outs_[i].image >= gr.first && host_outs_[i].image < gr.first + gr.count)
+                gr.host_outs.push_back(int(i));
     ready_ = true;
     return B200JPEG_STATUS_SUCCESS;
 }
 
-int Decoder::launch_all()
+// entropy-coded bytes of one group -> pinned staging -> device (asynchronous on the group's stream)
+int Decoder::stage_group(int g)
 {
-    const int m = dims_.num_images;
-    const bool prof = opt_.profile;
+    Group& gr = groups_[g];
+    uint8_t* hr = static_cast<uint8_t*>(h_raw_.p);
+    auto copy_range = [&](int lo, int hi) {
+        for (int i = lo; i < hi; ++i) {
+            const ImageDesc& im = plan_.images[i];
+            const int bi = planned_to_batch_[i];
+            std::memcpy(hr + im.raw_off, data_[bi] + parsed_[bi].scan_offset, im.raw_len);
+        }
+    };
+    const size_t bytes = gr.raw_hi - gr.raw_lo;
+    const int nthreads = std::min(std::min(opt_.copy_threads, gr.count), std::max(1, int(bytes >> 20)));
+    if (nthreads <= 1) {
+        copy_range(gr.first, gr.first + gr.count);
+    } else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; ++t)
+            th.emplace_back(copy_range, gr.first + gr.count * t / nthreads, gr.first + gr.count * (t + 1) / nthreads);
+        for (auto& x : th)
+            x.join();
+    }
+    B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(d_raw_.p) + gr.raw_lo, hr + gr.raw_lo, bytes, cudaMemcpyHostToDevice, streams_[g]));
+    return 0;
+}
+
+int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses)
+{
+    const int rc = plan_batch(n, data, sizes, outs, statuses);
+    if (rc)
+        return rc;
+    for (size_t g = 0; g < groups_.size(); ++g)
+        if (const int r = stage_group(int(g)))
+            return r;
+    for (size_t g = 0; g < groups_.size(); ++g)
+        B2J_CUDA(cudaStreamSynchronize(streams_[g])); // the caller's bytes are not needed any more
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+// every kernel of one group on the group's stream, then its statuses (and host outputs) back to the host
+int Decoder::launch_group(int g)
+{
+    Group& gr = groups_[g];
+    cudaStream_t st = streams_[g];
+    const int m0 = gr.first, mc = gr.count;
+    const bool prof = opt_.profile && groups_.size() == 1;
     auto mark = [&](int i) {
         if (prof)
-            cudaEventRecord(ev_stage_[i], stream_);
+            cudaEventRecord(ev_stage_[i], st);
     };
+    if (g != 0)
+        B2J_CUDA(cudaStreamWaitEvent(st, ev_meta_, 0)); // descriptors / tables went up on stream 0
+    B2J_CUDA(cudaStreamWaitEvent(st, ev_in_, 0));       // and whatever the caller had in flight on the output buffers
     mark(kStageUnstuff);
-    B2J_CUDA(cudaMemsetAsync(d_states_.p, 0, sizeof(ImageState) * m, stream_));
-    B2J_CUDA(cudaMemsetAsync(d_sync_.p, 0, sizeof(SyncCounters), stream_));
-    stat_launches_ += launch_unstuff(dev_, dims_, stream_);
+    B2J_CUDA(cudaMemsetAsync(static_cast<ImageState*>(d_states_.p) + m0, 0, sizeof(ImageState) * mc, st));
+    B2J_CUDA(cudaMemsetAsync(gr.dev.sync, 0, sizeof(SyncCounters), st));
+    stat_launches_ += launch_unstuff(gr.dev, gr.dims, st);
     mark(kStageSync);
-    const int ns = launch_huff_sync(dev_, dims_, stream_, tail_grid_);
+    const int ns = launch_huff_sync(gr.dev, gr.dims, st, gr.tail_grid);
     if (ns < 0) {
         std::fprintf(stderr, "b200jpeg: cooperative launch failed: %s\n", cudaGetErrorString(cudaGetLastError()));
         return B200JPEG_STATUS_CUDA_ERROR;
     }
     stat_launches_ += ns;
     mark(kStageWrite);
-    stat_launches_ += launch_huff_write(dev_, dims_, stream_);
+    stat_launches_ += launch_huff_write(gr.dev, gr.dims, st);
     mark(kStageDc);
-    stat_launches_ += launch_dc(dev_, dims_, stream_);
+    stat_launches_ += launch_dc(gr.dev, gr.dims, st);
     mark(kStageIdct);
-    stat_launches_ += launch_idct(dev_, dims_, stream_);
+    stat_launches_ += launch_idct(gr.dev, gr.dims, st);
     mark(kStageColor);
-    stat_launches_ += launch_color(dev_, dims_, stream_);
+    stat_launches_ += launch_color(gr.dev, gr.dims, st);
     mark(kNumStages);
     stage_valid_ = prof;
     B2J_CUDA(cudaGetLastError());
-    B2J_CUDA(cudaMemcpyAsync(h_states_.p, d_states_.p, sizeof(ImageState) * m, cudaMemcpyDeviceToHost, stream_));
-    B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(h_states_.p) + sizeof(ImageState) * m, d_sync_.p, sizeof(SyncCounters),
-        cudaMemcpyDeviceToHost, stream_));
+    const int m = int(plan_.images.size());
+    B2J_CUDA(cudaMemcpyAsync(static_cast<ImageState*>(h_states_.p) + m0, static_cast<ImageState*>(d_states_.p) + m0, sizeof(ImageState) * mc,
+        cudaMemcpyDeviceToHost, st));
+    B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(h_states_.p) + sizeof(ImageState) * m + sizeof(SyncCounters) * g, gr.dev.sync,
+        sizeof(SyncCounters), cudaMemcpyDeviceToHost, st));
+    for (int idx : gr.host_outs) { // host-memory outputs: copy back
+        const HostOutput& ho = host_outs_[idx];
+        const size_t pitch = align_up(ho.row_bytes, 16);
+        B2J_CUDA(cudaMemcpy2DAsync(ho.host, size_t(ho.host_stride), static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch, ho.row_bytes,
+            ho.rows, cudaMemcpyDeviceToHost, st));
+    }
     return 0;
 }
 
-int Decoder::run(cudaStream_t user_stream, int32_t* statuses)
+int Decoder::begin_run(cudaStream_t user_stream, int32_t* statuses)
 {
     if (!ready_)
         return B200JPEG_STATUS_INVALID_PARAMETER;
     B2J_CUDA(cudaSetDevice(device_));
     for (int i = 0; i < batch_size_; ++i)
         statuses[i] = pre_status_[i];
-    const int m = dims_.num_images;
+    stat_launches_ = 0;
+    if (!groups_.empty())
+        B2J_CUDA(cudaEventRecord(ev_in_, user_stream));
+    return 0;
+}
+
+int Decoder::finish(int32_t* statuses)
+{
+    const int m = int(plan_.images.size());
+    for (size_t g = 0; g < groups_.size(); ++g)
+        B2J_CUDA(cudaStreamSynchronize(streams_[g]));
     if (m == 0)
         return B200JPEG_STATUS_SUCCESS;
-    // order after whatever the caller still has in flight on the stream that owns the output buffers
-    B2J_CUDA(cudaEventRecord(ev_in_, user_stream));
-    B2J_CUDA(cudaStreamWaitEvent(stream_, ev_in_, 0));
-    stat_launches_ = 0;
-    const int rc = launch_all();
-    if (rc)
-        return rc;
-    // host-memory outputs: copy back
-    for (const HostOutput& ho : host_outs_) {
-        const size_t pitch = align_up(ho.row_bytes, 16);
-        B2J_CUDA(cudaMemcpy2DAsync(ho.host, size_t(ho.host_stride), static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch, ho.row_bytes,
-            ho.rows, cudaMemcpyDeviceToHost, stream_));
-    }
-    B2J_CUDA(cudaStreamSynchronize(stream_));
     const ImageState* hs = static_cast<const ImageState*>(h_states_.p);
     const SyncCounters* sc = reinterpret_cast<const SyncCounters*>(static_cast<const uint8_t*>(h_states_.p) + sizeof(ImageState) * m);
-    stat_rounds_ = 2 + sc->rounds;
-    stat_redone_ = sc->redone;
+    stat_rounds_ = 0;
+    stat_redone_ = 0;
+    for (size_t g = 0; g < groups_.size(); ++g) {
+        stat_rounds_ = std::max<uint64_t>(stat_rounds_, 2 + sc[g].rounds);
+        stat_redone_ += sc[g].redone;
+    }
     for (int i = 0; i < m; ++i) {
         const int bi = planned_to_batch_[i];
         if (hs[i].error || hs[i].done_blocks != plan_.images[i].total_blocks)
             statuses[bi] = B200JPEG_STATUS_CORRUPT_STREAM;
     }
     return B200JPEG_STATUS_SUCCESS;
+}
+
+// device work only: the entropy-coded bytes are already in device memory (prepare)
+int Decoder::run(cudaStream_t user_stream, int32_t* statuses)
+{
+    if (const int rc = begin_run(user_stream, statuses))
+        return rc;
+    for (size_t g = 0; g < groups_.size(); ++g)
+        if (const int rc = launch_group(int(g)))
+            return rc;
+    return finish(statuses);
+}
+
+// whole decode, pipelined over the groups: while group g is on the GPU the host stages group g+1
+int Decoder::decode(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, cudaStream_t user_stream, int32_t* statuses)
+{
+    int rc = plan_batch(n, data, sizes, outs, statuses);
+    if (rc)
+        return rc;
+    if ((rc = begin_run(user_stream, statuses)))
+        return rc;
+    for (size_t g = 0; g < groups_.size(); ++g) {
+        if ((rc = stage_group(int(g))) || (rc = launch_group(int(g))))
+            return rc;
+    }
+    return finish(statuses);
 }
 
 void Decoder::get_stats(uint64_t* s) const

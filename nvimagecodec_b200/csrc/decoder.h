@@ -15,6 +15,7 @@ struct DecoderOptions
     bool fancy_upsampling = true; // reference default (libjpeg_turbo_decoder.cpp:250-276)
     int subseq_bytes = 128;
     int copy_threads = 4;
+    int groups = 4;           // the batch is cut into this many groups of images that run on separate streams (pipelining)
     bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)
     bool profile = false; // record CUDA events between the kernel stages (b200jpeg_decoder_get_stage_times)
 };
@@ -39,6 +40,17 @@ struct HostOutput // an output the caller wants in host memory
     size_t rows = 0;
 };
 
+constexpr int kMaxGroups = 8;
+
+struct Group // consecutive planned images that are launched together on one stream
+{
+    int first = 0, count = 0, tail_grid = 0;
+    BatchDev dev{};
+    LaunchDims dims{};
+    size_t raw_lo = 0, raw_hi = 0;
+    std::vector<int> host_outs; // indices into host_outs_
+};
+
 class Decoder
 {
   public:
@@ -54,8 +66,11 @@ class Decoder
         int on_host;
     };
 
+    // two-phase: prepare = parse + plan + H2D of the bitstreams; run = all device work of the prepared batch
     int prepare(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses);
     int run(cudaStream_t user_stream, int32_t* statuses);
+    // one-shot, pipelined over the groups (host staging of group g+1 overlaps the device work of group g)
+    int decode(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, cudaStream_t user_stream, int32_t* statuses);
     void get_stats(uint64_t* s8) const;
     int get_stage_times(float* ms, int n); // per Stage, last run
     int64_t debug_fetch(int what, int image, int comp, void* dst, size_t cap);
@@ -64,12 +79,16 @@ class Decoder
   private:
     int ensure(DevBuf& b, size_t bytes);
     int ensure_pinned(DevBuf& b, size_t bytes);
-    int launch_all();
+    int plan_batch(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses);
+    int stage_group(int g);
+    int launch_group(int g);
+    int begin_run(cudaStream_t user_stream, int32_t* statuses);
+    int finish(int32_t* statuses);
 
     int device_;
     DecoderOptions opt_;
-    cudaStream_t stream_ = nullptr;
-    cudaEvent_t ev_in_ = nullptr;
+    cudaStream_t streams_[kMaxGroups] = {};
+    cudaEvent_t ev_in_ = nullptr, ev_meta_ = nullptr;
     cudaEvent_t ev_stage_[kNumStages + 1] = {};
     bool stage_valid_ = false;
     bool ready_ = false;
@@ -86,10 +105,12 @@ class Decoder
     DevBuf h_raw_, h_meta_, h_states_;
     BatchDev dev_{};
     LaunchDims dims_{};
+    std::vector<Group> groups_;
+    const uint8_t* const* data_ = nullptr; // caller's bitstreams during decode()/prepare()
     size_t scratch_bytes_ = 0;
 
     uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_redone_ = 0;
-    int tail_grid_ = 0, cfg_lut_slots_ = -1, cfg_stream_words_ = -1;
+    int tail_capacity_ = 0, sm_count_ = 0, cfg_lut_slots_ = -1, cfg_stream_words_ = -1;
 };
 
 } // namespace b200jpeg

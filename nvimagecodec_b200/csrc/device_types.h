@@ -165,6 +165,9 @@ struct BatchDev // pointers handed to every kernel
     const uint32_t* cta_map_subseq;
     const uint32_t* cta_map_idct;
     const uint32_t* cta_map_color;
+    // a launch may cover only a group of consecutive images: images / states / the CTA maps then point at the group's first
+    // image (map values stay absolute) and the kernels add these bases to blockIdx.x
+    uint32_t base_unstuff, base_subseq, base_idct, base_color;
     int32_t subseq_bits;   // bits per subsequence
     uint32_t total_subseq;
     int32_t num_tables;    // Huffman tables in the pool

@@ -123,10 +123,11 @@ extern __shared__ __align__(16) unsigned char g_dyn_smem[];
 
 __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
 {
-    const int img = find_image_h(b.cta_map_subseq, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.base_subseq;
+    const int img = find_image_h(b.cta_map_subseq, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     const HuffSmem sm = carve_smem(b, g_dyn_smem, 8);
-    const uint32_t k0 = (blockIdx.x - b.cta_map_subseq[img]) * kSubseqCta;
+    const uint32_t k0 = (cta_abs - b.cta_map_subseq[img]) * kSubseqCta;
     stage_cta(b, im, sm, k0);
     const uint32_t k = k0 + threadIdx.x;
     const uint32_t t = im.subseq_first + k;
@@ -287,10 +288,11 @@ __global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
 
 __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
 {
-    const int img = find_image_h(b.cta_map_subseq, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.base_subseq;
+    const int img = find_image_h(b.cta_map_subseq, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     const HuffSmem sm = carve_smem(b, g_dyn_smem, 8);
-    const uint32_t cta = blockIdx.x - b.cta_map_subseq[img];
+    const uint32_t cta = cta_abs - b.cta_map_subseq[img];
     const uint32_t k0 = cta * kSubseqCta, k = k0 + threadIdx.x;
     stage_cta(b, im, sm, k0);
     const uint32_t t = im.subseq_first + k;
@@ -374,9 +376,7 @@ int huff_configure(const BatchDev& b, int device, int* tail_grid)
         return -1;
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms < 1)
         return -1;
-    if (per_sm > 2)
-        per_sm = 2;
-    *tail_grid = per_sm * sms;
+    *tail_grid = per_sm * sms; // co-resident CTAs of the tail kernel on an otherwise empty device
     return 0;
 }
 
