@@ -41,6 +41,7 @@ def main():
     assert hashlib.md5(files["testorig_gray_islow.jpg"]).hexdigest() == LJT_MD5["MD5_JPEG_GRAY_ISLOW"]
     for name, data in files.items():
         open(os.path.join(HERE, name), "wb").write(data)
+    open(os.path.join(HERE, "testorig.ppm"), "wb").write(raw)  # source image of the encoder known answers
     dec = ref.Session.shared().decoder(options=":fancy_upsampling=1")
     golden = {"ljt_md5": LJT_MD5, "decoded_md5": {}, "synthetic_sha256": []}
     for name, data in files.items():
