@@ -1,29 +1,337 @@
-// encoder.cpp -- placeholder until the encode kernels land: every image reports B200JPEG_STATUS_UNSUPPORTED (there is no
-// CPU fallback in this library).
+// encoder.cpp -- host side of the b200jpeg batch encoder: per-image planning (geometry, quality -> reciprocal tables,
+// JFIF header bytes), pinned staging of host pixels, the kernel sequence of encode_kernels.cu on the encoder's own stream,
+// and the read-back of the entropy-coded bytes behind the host-written headers.
+// Interface precedent in the reference: extensions/nvjpeg/cuda_encoder.cpp:284-396 (batched GPU encoder plugin); the
+// arithmetic mirrors libjpeg-turbo's jpeg_compress (see enc_math.cuh / enc_plan.cpp for the per-function citations).
 #include "encoder.h"
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "enc_plan.h"
+#include "encode_kernels.h"
 
 namespace b200jpeg {
 
+namespace {
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+#define B2J_CUDA(call)                                                                                              \
+    do {                                                                                                            \
+        cudaError_t e__ = (call);                                                                                   \
+        if (e__ != cudaSuccess) {                                                                                   \
+            std::fprintf(stderr, "b200jpeg: CUDA error %s at %s:%d\n", cudaGetErrorString(e__), __FILE__, __LINE__); \
+            return B200JPEG_STATUS_CUDA_ERROR;                                                                      \
+        }                                                                                                           \
+    } while (0)
+
+struct Buf
+{
+    void* p = nullptr;
+    size_t cap = 0;
+};
+} // namespace
+
 struct Encoder::Impl
 {
-    int device;
+    int device = 0;
+    bool profile = false;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_in = nullptr;
+    cudaEvent_t ev[8] = {};
+    Buf d_pixels, d_meta, d_dyn, d_coef, d_dc, d_acbits, d_blk_off, d_seg_bits, d_seg_off, d_img_bytes, d_stream, d_chunks, d_out;
+    Buf h_pixels, h_meta, h_dyn, h_sizes, h_out;
+    uint64_t stats[8] = {};
+    float stage_ms[4] = {};
+
+    int ensure(Buf& b, size_t bytes, bool pinned)
+    {
+        if (bytes <= b.cap)
+            return 0;
+        if (b.p) {
+            B2J_CUDA(cudaStreamSynchronize(stream));
+            B2J_CUDA(pinned ? cudaFreeHost(b.p) : cudaFree(b.p));
+            b.p = nullptr;
+            b.cap = 0;
+        }
+        const size_t want = align_up(bytes + bytes / 8 + 256, 1 << 16);
+        const cudaError_t e = pinned ? cudaHostAlloc(&b.p, want, cudaHostAllocDefault) : cudaMalloc(&b.p, want);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return B200JPEG_STATUS_ALLOC_FAILED;
+        }
+        b.cap = want;
+        return 0;
+    }
 };
 
-Encoder::Encoder(int device_id, const char*) : impl_(new Impl{device_id}) {}
-Encoder::~Encoder() { delete impl_; }
-int Encoder::init() { return B200JPEG_STATUS_SUCCESS; }
-int Encoder::encode(int n, const b200jpegEncodeInput_t*, uint8_t* const*, const size_t*, size_t* out_sizes, cudaStream_t, int32_t* statuses)
+Encoder::Encoder(int device_id, const char* options) : impl_(new Impl)
 {
-    for (int i = 0; i < n; ++i) {
-        statuses[i] = B200JPEG_STATUS_UNSUPPORTED;
-        out_sizes[i] = 0;
+    impl_->device = device_id;
+    if (options && std::string(options).find("profile=1") != std::string::npos)
+        impl_->profile = true;
+}
+
+Encoder::~Encoder()
+{
+    Impl& s = *impl_;
+    cudaSetDevice(s.device);
+    Buf* dev[] = {&s.d_pixels, &s.d_meta, &s.d_dyn, &s.d_coef, &s.d_dc, &s.d_acbits, &s.d_blk_off, &s.d_seg_bits, &s.d_seg_off, &s.d_img_bytes,
+        &s.d_stream, &s.d_chunks, &s.d_out};
+    for (Buf* b : dev)
+        if (b->p)
+            cudaFree(b->p);
+    Buf* host[] = {&s.h_pixels, &s.h_meta, &s.h_dyn, &s.h_sizes, &s.h_out};
+    for (Buf* b : host)
+        if (b->p)
+            cudaFreeHost(b->p);
+    for (cudaEvent_t e : s.ev)
+        if (e)
+            cudaEventDestroy(e);
+    if (s.ev_in)
+        cudaEventDestroy(s.ev_in);
+    if (s.stream)
+        cudaStreamDestroy(s.stream);
+    delete impl_;
+}
+
+int Encoder::init()
+{
+    Impl& s = *impl_;
+    int count = 0;
+    B2J_CUDA(cudaGetDeviceCount(&count));
+    if (s.device < 0 || s.device >= count)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    B2J_CUDA(cudaSetDevice(s.device));
+    cudaDeviceProp prop;
+    B2J_CUDA(cudaGetDeviceProperties(&prop, s.device));
+    if (prop.major != 10) {
+        std::fprintf(stderr, "b200jpeg: device %d is sm_%d%d; this library only carries sm_100a code\n", s.device, prop.major, prop.minor);
+        return B200JPEG_STATUS_ARCH_MISMATCH;
     }
+    B2J_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    B2J_CUDA(cudaEventCreateWithFlags(&s.ev_in, cudaEventDisableTiming));
+    for (cudaEvent_t& e : s.ev)
+        B2J_CUDA(cudaEventCreate(&e));
     return B200JPEG_STATUS_SUCCESS;
 }
+
+int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out, const size_t* out_capacity, size_t* out_sizes,
+    cudaStream_t user_stream, int32_t* statuses)
+{
+    Impl& s = *impl_;
+    B2J_CUDA(cudaSetDevice(s.device));
+    std::memset(s.stats, 0, sizeof(s.stats));
+    std::vector<EncImageDesc> images;
+    std::vector<int> batch_index;
+    std::vector<EncQuantTable> quant;
+    std::vector<std::vector<uint8_t>> headers;
+    std::vector<uint32_t> map_dct(1, 0), map_emit(1, 0), seg_map(1, 0);
+    std::vector<size_t> host_pix_off; // staging offset of host inputs (SIZE_MAX for device inputs)
+    size_t host_pix_bytes = 0;
+    uint64_t total_blocks = 0, in_bytes = 0;
+    for (int i = 0; i < n; ++i) {
+        out_sizes[i] = 0;
+        statuses[i] = B200JPEG_STATUS_SUCCESS;
+        EncImageDesc im;
+        if (!in[i].buffer || !out[i] || in[i].quality < 1 || in[i].quality > 100) {
+            statuses[i] = B200JPEG_STATUS_INVALID_PARAMETER;
+            continue;
+        }
+        if (!enc_plan_image(in[i].width, in[i].height, in[i].format, in[i].subsampling, in[i].restart_interval, im)) {
+            statuses[i] = B200JPEG_STATUS_UNSUPPORTED;
+            continue;
+        }
+        const int64_t min_stride = int64_t(im.width) * (im.in_fmt == B200JPEG_FMT_I_RGB ? 3 : 1);
+        if (in[i].row_stride < min_stride) {
+            statuses[i] = B200JPEG_STATUS_INVALID_PARAMETER;
+            continue;
+        }
+        im.pixels = static_cast<const uint8_t*>(in[i].buffer);
+        im.stride = in[i].row_stride;
+        const size_t planes = im.in_fmt == B200JPEG_FMT_P_RGB ? 3 : 1;
+        const size_t bytes = size_t(im.stride) * im.height * planes;
+        in_bytes += size_t(min_stride) * im.height * planes;
+        if (in[i].on_host) {
+            host_pix_off.push_back(host_pix_bytes);
+            host_pix_bytes += align_up(bytes, 256);
+        } else {
+            host_pix_off.push_back(SIZE_MAX);
+        }
+        im.qt = int32_t(quant.size());
+        quant.emplace_back();
+        enc_build_quant(in[i].quality, 0, quant.back());
+        quant.emplace_back();
+        enc_build_quant(in[i].quality, 1, quant.back());
+        headers.emplace_back();
+        enc_write_headers(im, quant[im.qt], quant[im.qt + 1], headers.back());
+        im.dct_cta_first = map_dct.back();
+        im.emit_cta_first = map_emit.back();
+        im.blk_first = total_blocks;
+        im.seg_first = seg_map.back();
+        map_dct.push_back(map_dct.back() + uint32_t(im.tiles_per_row) * uint32_t(im.mcus_y));
+        map_emit.push_back(map_emit.back() + (im.total_blocks + kEncCta - 1) / kEncCta);
+        seg_map.push_back(seg_map.back() + im.num_segments);
+        total_blocks += im.total_blocks;
+        images.push_back(im);
+        batch_index.push_back(i);
+    }
+    const int m = int(images.size());
+    if (m == 0)
+        return B200JPEG_STATUS_SUCCESS;
+    const uint32_t total_segs = seg_map.back();
+
+    // ---- scratch ----
+    int rc = 0;
+    const size_t off_img = 0;
+    const size_t off_quant = align_up(off_img + sizeof(EncImageDesc) * m, 256);
+    const size_t off_huff = align_up(off_quant + sizeof(EncQuantTable) * quant.size(), 256);
+    const size_t map_bytes = align_up(sizeof(uint32_t) * (m + 1), 256);
+    const size_t off_maps = align_up(off_huff + sizeof(EncHuffTables), 256);
+    const size_t meta_bytes = off_maps + 3 * map_bytes;
+    const size_t dyn_bytes = align_up(sizeof(EncImageDyn) * m, 256) + map_bytes;
+    if ((rc = s.ensure(s.d_meta, meta_bytes, false)) || (rc = s.ensure(s.h_meta, meta_bytes, true)) || (rc = s.ensure(s.d_dyn, dyn_bytes, false)) ||
+        (rc = s.ensure(s.h_dyn, dyn_bytes, true)) || (rc = s.ensure(s.d_coef, total_blocks * 128, false)) ||
+        (rc = s.ensure(s.d_dc, total_blocks * 2, false)) || (rc = s.ensure(s.d_acbits, total_blocks * 2, false)) ||
+        (rc = s.ensure(s.d_blk_off, total_blocks * 4, false)) || (rc = s.ensure(s.d_seg_bits, size_t(total_segs) * 4, false)) ||
+        (rc = s.ensure(s.d_seg_off, size_t(total_segs) * 4, false)) || (rc = s.ensure(s.d_img_bytes, size_t(m) * 8, false)) ||
+        (rc = s.ensure(s.h_sizes, size_t(m) * 8, true)) || (host_pix_bytes && ((rc = s.ensure(s.d_pixels, host_pix_bytes, false)) ||
+                                                               (rc = s.ensure(s.h_pixels, host_pix_bytes, true)))))
+        return rc;
+
+    // ---- host pixels -> pinned staging -> device ----
+    B2J_CUDA(cudaEventRecord(s.ev_in, user_stream));
+    B2J_CUDA(cudaStreamWaitEvent(s.stream, s.ev_in, 0));
+    if (s.profile)
+        cudaEventRecord(s.ev[0], s.stream);
+    if (host_pix_bytes) {
+        for (int k = 0; k < m; ++k) {
+            if (host_pix_off[k] == SIZE_MAX)
+                continue;
+            EncImageDesc& im = images[k];
+            const size_t planes = im.in_fmt == B200JPEG_FMT_P_RGB ? 3 : 1;
+            const size_t bytes = size_t(im.stride) * im.height * planes;
+            std::memcpy(static_cast<uint8_t*>(s.h_pixels.p) + host_pix_off[k], im.pixels, bytes);
+            im.pixels = static_cast<const uint8_t*>(s.d_pixels.p) + host_pix_off[k];
+        }
+        B2J_CUDA(cudaMemcpyAsync(s.d_pixels.p, s.h_pixels.p, host_pix_bytes, cudaMemcpyHostToDevice, s.stream));
+    }
+    uint8_t* hm = static_cast<uint8_t*>(s.h_meta.p);
+    std::memcpy(hm + off_img, images.data(), sizeof(EncImageDesc) * m);
+    std::memcpy(hm + off_quant, quant.data(), sizeof(EncQuantTable) * quant.size());
+    enc_build_huff(*reinterpret_cast<EncHuffTables*>(hm + off_huff));
+    std::memcpy(hm + off_maps, map_dct.data(), sizeof(uint32_t) * (m + 1));
+    std::memcpy(hm + off_maps + map_bytes, map_emit.data(), sizeof(uint32_t) * (m + 1));
+    std::memcpy(hm + off_maps + 2 * map_bytes, seg_map.data(), sizeof(uint32_t) * (m + 1));
+    B2J_CUDA(cudaMemcpyAsync(s.d_meta.p, s.h_meta.p, meta_bytes, cudaMemcpyHostToDevice, s.stream));
+
+    uint8_t* dm = static_cast<uint8_t*>(s.d_meta.p);
+    EncBatchDev b{};
+    b.images = reinterpret_cast<const EncImageDesc*>(dm + off_img);
+    b.dyn = static_cast<const EncImageDyn*>(s.d_dyn.p);
+    b.num_images = m;
+    b.quant = reinterpret_cast<const EncQuantTable*>(dm + off_quant);
+    b.huff = reinterpret_cast<const EncHuffTables*>(dm + off_huff);
+    b.coef = static_cast<int16_t*>(s.d_coef.p);
+    b.dc = static_cast<int16_t*>(s.d_dc.p);
+    b.acbits = static_cast<uint16_t*>(s.d_acbits.p);
+    b.blk_off = static_cast<uint32_t*>(s.d_blk_off.p);
+    b.seg_bits = static_cast<uint32_t*>(s.d_seg_bits.p);
+    b.seg_byte_off = static_cast<uint32_t*>(s.d_seg_off.p);
+    b.img_stream_bytes = static_cast<uint32_t*>(s.d_img_bytes.p);
+    b.img_out_bytes = static_cast<uint32_t*>(s.d_img_bytes.p) + m;
+    b.cta_map_dct = reinterpret_cast<const uint32_t*>(dm + off_maps);
+    b.cta_map_emit = reinterpret_cast<const uint32_t*>(dm + off_maps + map_bytes);
+    b.seg_map = reinterpret_cast<const uint32_t*>(dm + off_maps + 2 * map_bytes);
+    b.cta_map_stuff = reinterpret_cast<const uint32_t*>(static_cast<uint8_t*>(s.d_dyn.p) + align_up(sizeof(EncImageDyn) * m, 256));
+
+    EncLaunchDims d;
+    d.num_images = m;
+    d.dct_ctas = map_dct.back();
+    d.emit_ctas = map_emit.back();
+    d.total_segments = total_segs;
+    uint64_t launches = 0;
+    launches += launch_enc_dct(b, d, s.stream);
+    if (s.profile)
+        cudaEventRecord(s.ev[1], s.stream);
+    launches += launch_enc_scan(b, d, s.stream);
+    B2J_CUDA(cudaGetLastError());
+    uint32_t* hsizes = static_cast<uint32_t*>(s.h_sizes.p);
+    B2J_CUDA(cudaMemcpyAsync(hsizes, b.img_stream_bytes, sizeof(uint32_t) * m, cudaMemcpyDeviceToHost, s.stream));
+    B2J_CUDA(cudaStreamSynchronize(s.stream)); // the stream lengths decide the layout of everything that follows
+
+    // ---- second half: layout of the streams, Huffman emit, stuffing ----
+    EncImageDyn* dyn = static_cast<EncImageDyn*>(s.h_dyn.p);
+    uint32_t* map_stuff = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(s.h_dyn.p) + align_up(sizeof(EncImageDyn) * m, 256));
+    uint64_t stream_bytes = 0, out_bytes = 0;
+    uint32_t chunks = 0;
+    for (int k = 0; k < m; ++k) {
+        dyn[k].stream_off = stream_bytes;
+        dyn[k].stream_bytes = hsizes[k];
+        dyn[k].chunk_first = chunks;
+        dyn[k].out_off = out_bytes;
+        map_stuff[k] = chunks;
+        stream_bytes += align_up(size_t(hsizes[k]) + 16, 256);
+        out_bytes += align_up(2 * size_t(hsizes[k]) + 2 * size_t(images[k].num_segments) + 16, 256);
+        chunks += (hsizes[k] + kEncStuffChunk - 1) / kEncStuffChunk;
+    }
+    map_stuff[m] = chunks;
+    if ((rc = s.ensure(s.d_stream, stream_bytes, false)) || (rc = s.ensure(s.d_out, out_bytes, false)) ||
+        (rc = s.ensure(s.d_chunks, size_t(chunks) * 4 + 4, false)))
+        return rc;
+    b.stream = static_cast<uint8_t*>(s.d_stream.p);
+    b.out = static_cast<uint8_t*>(s.d_out.p);
+    b.chunk_out = static_cast<uint32_t*>(s.d_chunks.p);
+    d.stuff_ctas = chunks;
+    B2J_CUDA(cudaMemcpyAsync(s.d_dyn.p, s.h_dyn.p, dyn_bytes, cudaMemcpyHostToDevice, s.stream));
+    if (s.profile)
+        cudaEventRecord(s.ev[2], s.stream);
+    launches += launch_enc_emit(b, d, s.stream);
+    if (s.profile)
+        cudaEventRecord(s.ev[3], s.stream);
+    launches += launch_enc_stuff(b, d, s.stream);
+    if (s.profile)
+        cudaEventRecord(s.ev[4], s.stream);
+    B2J_CUDA(cudaGetLastError());
+    B2J_CUDA(cudaMemcpyAsync(hsizes + m, b.img_out_bytes, sizeof(uint32_t) * m, cudaMemcpyDeviceToHost, s.stream));
+    B2J_CUDA(cudaStreamSynchronize(s.stream));
+
+    // ---- headers (host) + entropy-coded bytes (device -> caller's buffer) + EOI ----
+    uint64_t total_out = 0;
+    for (int k = 0; k < m; ++k) {
+        const int bi = batch_index[k];
+        const size_t hdr = headers[k].size(), body = hsizes[m + k], need = hdr + body + 2;
+        if (need > out_capacity[bi]) {
+            statuses[bi] = B200JPEG_STATUS_BUFFER_TOO_SMALL;
+            out_sizes[bi] = need;
+            continue;
+        }
+        std::memcpy(out[bi], headers[k].data(), hdr);
+        B2J_CUDA(cudaMemcpyAsync(out[bi] + hdr, static_cast<uint8_t*>(s.d_out.p) + dyn[k].out_off, body, cudaMemcpyDeviceToHost, s.stream));
+        out[bi][hdr + body] = 0xFF;
+        out[bi][hdr + body + 1] = 0xD9;
+        out_sizes[bi] = need;
+        total_out += need;
+    }
+    B2J_CUDA(cudaStreamSynchronize(s.stream));
+    if (s.profile)
+        for (int i = 0; i < 4; ++i)
+            cudaEventElapsedTime(&s.stage_ms[i], s.ev[i], s.ev[i + 1]);
+    s.stats[0] = launches;
+    s.stats[1] = total_blocks;
+    s.stats[2] = in_bytes;
+    s.stats[3] = total_out;
+    s.stats[4] = stream_bytes;
+    s.stats[5] = uint64_t(s.stage_ms[0] * 1e3f);
+    s.stats[6] = uint64_t((s.stage_ms[1] + s.stage_ms[2]) * 1e3f);
+    s.stats[7] = uint64_t(s.stage_ms[3] * 1e3f);
+    return B200JPEG_STATUS_SUCCESS;
+}
+
 void Encoder::get_stats(uint64_t* s8) const
 {
     for (int i = 0; i < 8; ++i)
-        s8[i] = 0;
+        s8[i] = impl_->stats[i];
 }
 
 } // namespace b200jpeg

@@ -11,6 +11,7 @@
 // Anything outside the codec's scope is declined in canDecode/canEncode so the framework falls back to the next decoder
 // (libjpeg_turbo_ext, priority 300); there is no CPU fallback in here.
 #include <nvimgcodec.h>
+#include <algorithm>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -228,6 +229,188 @@ nvimgcodecStatus_t dec_destroy(nvimgcodecDecoder_t decoder)
     return NVIMGCODEC_STATUS_SUCCESS;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Encoder (interface precedent: extensions/nvjpeg/cuda_encoder.cpp:54-147 canEncode, :284-396 encode)
+// ---------------------------------------------------------------------------------------------------------------
+struct EncoderState
+{
+    const nvimgcodecFrameworkDesc_t* fw = nullptr;
+    const nvimgcodecExecutionParams_t* exec = nullptr;
+    b200jpegEncoder_t enc = nullptr;
+};
+
+// what the caller wants written: baseline only, standard Huffman tables only
+bool wants_out_of_scope_jpeg(const nvimgcodecImageInfo_t& cs_info, const nvimgcodecEncodeParams_t* params)
+{
+    for (auto* p = static_cast<const nvimgcodecJpegImageInfo_t*>(cs_info.struct_next); p; p = static_cast<const nvimgcodecJpegImageInfo_t*>(p->struct_next))
+        if (p->struct_type == NVIMGCODEC_STRUCTURE_TYPE_JPEG_IMAGE_INFO && p->encoding != NVIMGCODEC_JPEG_ENCODING_BASELINE_DCT &&
+            p->encoding != NVIMGCODEC_JPEG_ENCODING_UNKNOWN)
+            return true;
+    for (auto* p = static_cast<const nvimgcodecJpegEncodeParams_t*>(params->struct_next); p; p = static_cast<const nvimgcodecJpegEncodeParams_t*>(p->struct_next))
+        if (p->struct_type == NVIMGCODEC_STRUCTURE_TYPE_JPEG_ENCODE_PARAMS && p->optimized_huffman)
+            return true;
+    return false;
+}
+
+nvimgcodecProcessingStatus_t check_source(const nvimgcodecImageInfo_t& info, const nvimgcodecImageInfo_t& out_info)
+{
+    nvimgcodecProcessingStatus_t st = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+    const bool gray = info.sample_format == NVIMGCODEC_SAMPLEFORMAT_P_Y;
+    switch (info.sample_format) {
+    case NVIMGCODEC_SAMPLEFORMAT_I_RGB:
+        if (info.num_planes != 1 || info.plane_info[0].num_channels != 3)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_CHANNELS_UNSUPPORTED;
+        break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_RGB:
+        if (info.num_planes != 3 || info.plane_info[0].num_channels != 1)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_PLANES_UNSUPPORTED;
+        break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_Y:
+        if (info.num_planes != 1 || info.plane_info[0].num_channels != 1)
+            st |= NVIMGCODEC_PROCESSING_STATUS_NUM_CHANNELS_UNSUPPORTED;
+        break;
+    default:
+        st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_FORMAT_UNSUPPORTED;
+        break;
+    }
+    for (uint32_t p = 0; p < info.num_planes; ++p)
+        if (info.plane_info[p].sample_type != NVIMGCODEC_SAMPLE_DATA_TYPE_UINT8)
+            st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_TYPE_UNSUPPORTED;
+    switch (out_info.chroma_subsampling) {
+    case NVIMGCODEC_SAMPLING_444:
+    case NVIMGCODEC_SAMPLING_422:
+    case NVIMGCODEC_SAMPLING_420:
+    case NVIMGCODEC_SAMPLING_440:
+        if (gray)
+            st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLING_UNSUPPORTED;
+        break;
+    case NVIMGCODEC_SAMPLING_GRAY:
+        if (!gray)
+            st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLING_UNSUPPORTED; // RGB -> gray conversion is not offered
+        break;
+    default:
+        st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLING_UNSUPPORTED;
+        break;
+    }
+    if (info.color_spec != NVIMGCODEC_COLORSPEC_UNCHANGED && info.color_spec != NVIMGCODEC_COLORSPEC_SRGB &&
+        !(gray && (info.color_spec == NVIMGCODEC_COLORSPEC_GRAY || info.color_spec == NVIMGCODEC_COLORSPEC_SYCC)))
+        st |= NVIMGCODEC_PROCESSING_STATUS_COLOR_SPEC_UNSUPPORTED;
+    if (info.buffer_kind != NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_DEVICE && info.buffer_kind != NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST)
+        st |= NVIMGCODEC_PROCESSING_STATUS_BACKEND_UNSUPPORTED;
+    return st;
+}
+
+nvimgcodecStatus_t enc_can_encode(nvimgcodecEncoder_t encoder, nvimgcodecProcessingStatus_t* status, nvimgcodecImageDesc_t** imgs,
+    nvimgcodecCodeStreamDesc_t** css, int n, const nvimgcodecEncodeParams_t* params)
+{
+    if (!encoder || !status || !css || !imgs || !params)
+        return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    try {
+        for (int i = 0; i < n; ++i) {
+            nvimgcodecJpegImageInfo_t jinfo{NVIMGCODEC_STRUCTURE_TYPE_JPEG_IMAGE_INFO, sizeof(nvimgcodecJpegImageInfo_t), nullptr};
+            jinfo.encoding = NVIMGCODEC_JPEG_ENCODING_UNKNOWN;
+            nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), &jinfo};
+            css[i]->getImageInfo(css[i]->instance, &cs_info);
+            if (std::strcmp(cs_info.codec_name, "jpeg") != 0) {
+                status[i] = NVIMGCODEC_PROCESSING_STATUS_CODEC_UNSUPPORTED;
+                continue;
+            }
+            if (wants_out_of_scope_jpeg(cs_info, params)) {
+                status[i] = NVIMGCODEC_PROCESSING_STATUS_ENCODING_UNSUPPORTED;
+                continue;
+            }
+            nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+            imgs[i]->getImageInfo(imgs[i]->instance, &info);
+            status[i] = check_source(info, cs_info);
+        }
+    } catch (...) {
+        return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+    }
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t enc_encode(nvimgcodecEncoder_t encoder, nvimgcodecImageDesc_t** imgs, nvimgcodecCodeStreamDesc_t** css, int n,
+    const nvimgcodecEncodeParams_t* params)
+{
+    auto* st = reinterpret_cast<EncoderState*>(encoder);
+    if (!st || !css || !imgs || !params || n < 0)
+        return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    std::vector<char> reported(n, 0);
+    auto report = [&](int i, nvimgcodecProcessingStatus_t s) {
+        if (!reported[i]) {
+            reported[i] = 1;
+            imgs[i]->imageReady(imgs[i]->instance, s);
+        }
+    };
+    try {
+        std::vector<b200jpegEncodeInput_t> in(n);
+        std::vector<std::vector<uint8_t>> bufs(n);
+        std::vector<uint8_t*> outs(n);
+        std::vector<size_t> caps(n), sizes(n, 0);
+        std::vector<int32_t> res(n, B200JPEG_STATUS_INTERNAL_ERROR);
+        cudaStream_t user_stream = nullptr;
+        const int quality = std::max(1, std::min(100, int(params->quality + 0.5f)));
+        for (int i = 0; i < n; ++i) {
+            nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+            imgs[i]->getImageInfo(imgs[i]->instance, &info);
+            nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+            css[i]->getImageInfo(css[i]->instance, &cs_info);
+            in[i].buffer = info.buffer;
+            in[i].row_stride = int64_t(info.plane_info[0].row_stride);
+            in[i].width = int32_t(info.plane_info[0].width);
+            in[i].height = int32_t(info.plane_info[0].height);
+            in[i].format = int32_t(info.sample_format);
+            in[i].on_host = info.buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST ? 1 : 0;
+            in[i].subsampling = int32_t(cs_info.chroma_subsampling);
+            in[i].quality = quality;
+            in[i].restart_interval = 0;
+            if (i == 0)
+                user_stream = info.cuda_stream;
+            caps[i] = size_t(in[i].width) * in[i].height * (in[i].format == B200JPEG_FMT_P_Y ? 1 : 3) * 2 + 4096;
+            bufs[i].resize(caps[i]);
+            outs[i] = bufs[i].data();
+        }
+        const int rc = b200jpeg_encode_batch(st->enc, n, in.data(), outs.data(), caps.data(), sizes.data(), user_stream, res.data());
+        for (int i = 0; i < n; ++i) {
+            if (rc != B200JPEG_STATUS_SUCCESS || res[i] != B200JPEG_STATUS_SUCCESS) {
+                report(i, NVIMGCODEC_PROCESSING_STATUS_FAIL);
+                continue;
+            }
+            // hand the file to the code stream (idiom of extensions/nvjpeg/cuda_encoder.cpp:383-388)
+            nvimgcodecIoStreamDesc_t* io = css[i]->io_stream;
+            size_t written = 0;
+            io->reserve(io->instance, sizes[i]);
+            io->seek(io->instance, 0, SEEK_SET);
+            io->write(io->instance, &written, outs[i], sizes[i]);
+            io->flush(io->instance);
+            report(i, written == sizes[i] ? NVIMGCODEC_PROCESSING_STATUS_SUCCESS : NVIMGCODEC_PROCESSING_STATUS_FAIL);
+        }
+        if (rc != B200JPEG_STATUS_SUCCESS) {
+            log_msg(st->fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR, kEncoderId, std::string("encode batch failed: ") + b200jpeg_status_string(rc));
+            return rc == B200JPEG_STATUS_CUDA_ERROR ? NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR : NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+        }
+    } catch (...) {
+        for (int i = 0; i < n; ++i)
+            report(i, NVIMGCODEC_PROCESSING_STATUS_FAIL);
+        return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+    }
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t enc_destroy(nvimgcodecEncoder_t encoder)
+{
+    auto* st = reinterpret_cast<EncoderState*>(encoder);
+    if (!st)
+        return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    if (st->enc)
+        b200jpeg_encoder_destroy(st->enc);
+    delete st;
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t enc_create(void* instance, nvimgcodecEncoder_t* encoder, const nvimgcodecExecutionParams_t* exec, const char* options);
+
 struct Extension;
 nvimgcodecStatus_t dec_create(void* instance, nvimgcodecDecoder_t* decoder, const nvimgcodecExecutionParams_t* exec, const char* options);
 
@@ -238,7 +421,8 @@ struct Extension
 {
     const nvimgcodecFrameworkDesc_t* fw;
     nvimgcodecDecoderDesc_t dec_desc;
-    bool dec_registered = false;
+    nvimgcodecEncoderDesc_t enc_desc;
+    bool dec_registered = false, enc_registered = false;
 
     explicit Extension(const nvimgcodecFrameworkDesc_t* f) : fw(f)
     {
@@ -246,9 +430,15 @@ struct Extension
             "jpeg", NVIMGCODEC_BACKEND_KIND_GPU_ONLY, dec_create, dec_destroy, dec_can_decode, dec_decode};
         if (fw->registerDecoder(fw->instance, &dec_desc, kPriority) == NVIMGCODEC_STATUS_SUCCESS)
             dec_registered = true;
+        enc_desc = nvimgcodecEncoderDesc_t{NVIMGCODEC_STRUCTURE_TYPE_ENCODER_DESC, sizeof(nvimgcodecEncoderDesc_t), nullptr, this, kEncoderId,
+            "jpeg", NVIMGCODEC_BACKEND_KIND_GPU_ONLY, enc_create, enc_destroy, enc_can_encode, enc_encode};
+        if (fw->registerEncoder(fw->instance, &enc_desc, kPriority) == NVIMGCODEC_STATUS_SUCCESS)
+            enc_registered = true;
     }
     ~Extension()
     {
+        if (enc_registered)
+            fw->unregisterEncoder(fw->instance, &enc_desc);
         if (dec_registered)
             fw->unregisterDecoder(fw->instance, &dec_desc);
     }
@@ -270,6 +460,25 @@ nvimgcodecStatus_t dec_create(void* instance, nvimgcodecDecoder_t* decoder, cons
         return rc == B200JPEG_STATUS_ARCH_MISMATCH ? NVIMGCODEC_STATUS_EXTENSION_ARCH_MISMATCH : NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR;
     }
     *decoder = reinterpret_cast<nvimgcodecDecoder_t>(st.release());
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t enc_create(void* instance, nvimgcodecEncoder_t* encoder, const nvimgcodecExecutionParams_t* exec, const char* options)
+{
+    auto* ext = reinterpret_cast<Extension*>(instance);
+    if (!ext || !encoder || !exec)
+        return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    if (exec->device_id == NVIMGCODEC_DEVICE_CPU_ONLY)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER; // like extensions/nvjpeg/cuda_encoder.cpp:203-204
+    auto st = std::make_unique<EncoderState>();
+    st->fw = ext->fw;
+    st->exec = exec;
+    const int rc = b200jpeg_encoder_create(&st->enc, exec->device_id, options ? options : "");
+    if (rc != B200JPEG_STATUS_SUCCESS) {
+        log_msg(ext->fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_WARNING, kEncoderId, std::string("encoder unavailable: ") + b200jpeg_status_string(rc));
+        return rc == B200JPEG_STATUS_ARCH_MISMATCH ? NVIMGCODEC_STATUS_EXTENSION_ARCH_MISMATCH : NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR;
+    }
+    *encoder = reinterpret_cast<nvimgcodecEncoder_t>(st.release());
     return NVIMGCODEC_STATUS_SUCCESS;
 }
 

@@ -13,8 +13,10 @@ _lib = None
 
 
 def build(force=False):
-    srcs = [os.path.join(HERE, "emu_decode.cpp"), os.path.join(CSRC, "batch_plan.cpp"), os.path.join(CSRC, "jpeg_parse.cpp")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("jpeg_math.cuh", "huffman.cuh", "device_types.h", "batch_plan.h", "jpeg_parse.h", "host_shim.h")]
+    srcs = [os.path.join(HERE, "emu_decode.cpp"), os.path.join(HERE, "emu_encode.cpp"), os.path.join(CSRC, "batch_plan.cpp"),
+            os.path.join(CSRC, "jpeg_parse.cpp"), os.path.join(CSRC, "enc_plan.cpp")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("jpeg_math.cuh", "huffman.cuh", "device_types.h", "batch_plan.h", "jpeg_parse.h", "host_shim.h", "enc_math.cuh", "enc_types.h",
+                                                      "enc_plan.h")]
     if force or not os.path.exists(SO) or any(os.path.getmtime(d) > os.path.getmtime(SO) for d in deps):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-fwrapv", "-fno-strict-aliasing", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", SO] + srcs)
 
@@ -27,8 +29,27 @@ def lib():
         L.emu_decode_batch.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p),
                                        C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+        L.emu_encode.restype = C.c_long
+        L.emu_encode.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
         _lib = L
     return _lib
+
+
+def encode(pixels, quality=90, subsampling=3, restart_interval=0, planar=False):
+    """pixels: (H,W,3) RGB, (3,H,W) planar RGB with planar=True, or (H,W) gray uint8 -> JPEG bytes (emulated kernels)"""
+    a = np.ascontiguousarray(pixels, dtype=np.uint8)
+    if a.ndim == 2:
+        h, w = a.shape; fmt = 7; stride = w; subsampling = 7
+    elif planar:
+        _, h, w = a.shape; fmt = 3; stride = w
+    else:
+        h, w = a.shape[:2]; fmt = 4; stride = 3 * w
+    cap = h * w * 6 + 65536
+    out = np.empty(cap, np.uint8)
+    n = lib().emu_encode(a.ctypes.data, w, h, fmt, stride, subsampling, quality, restart_interval, out.ctypes.data, cap)
+    if n < 0:
+        raise RuntimeError("emu_encode rc=%d" % n)
+    return out[:n].tobytes()
 
 
 def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=64, jacobi=True, want_coef=False, slots=None):
