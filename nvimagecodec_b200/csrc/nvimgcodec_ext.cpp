@@ -308,9 +308,9 @@ nvimgcodecStatus_t enc_can_encode(nvimgcodecEncoder_t encoder, nvimgcodecProcess
         return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
     try {
         for (int i = 0; i < n; ++i) {
-            nvimgcodecJpegImageInfo_t jinfo{NVIMGCODEC_STRUCTURE_TYPE_JPEG_IMAGE_INFO, sizeof(nvimgcodecJpegImageInfo_t), nullptr};
-            jinfo.encoding = NVIMGCODEC_JPEG_ENCODING_UNKNOWN;
-            nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), &jinfo};
+            // an output code stream has no parser: ask without a chained structure and look at the chain that comes back
+            // (src/code_stream.cpp:75-98; same idiom as extensions/nvjpeg/cuda_encoder.cpp:64-83)
+            nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
             css[i]->getImageInfo(css[i]->instance, &cs_info);
             if (std::strcmp(cs_info.codec_name, "jpeg") != 0) {
                 status[i] = NVIMGCODEC_PROCESSING_STATUS_CODEC_UNSUPPORTED;

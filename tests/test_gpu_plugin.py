@@ -38,15 +38,19 @@ def test_decode_through_reference_framework(sess):
     dec.close()
 
 
-def test_gpu_only_backend_selects_b200jpeg_and_declines_progressive(sess):
+def test_gpu_only_backend_selects_b200jpeg(sess):
+    """backends=[GPU_ONLY]: libjpeg_turbo_ext (CPU_ONLY) is filtered out by the framework (src/decoder_worker.cpp:63-93), so a
+    successful decode can only have come from our plugin"""
     import torch
-    good, prog = make_jpeg(410, 320, 240), make_jpeg(411, 320, 240, progressive=True)
-    dec = sess.decoder(device_id=0, backends=ref.BACKEND_GPU_ONLY, options=":fancy_upsampling=1")  # only our plugin is GPU_ONLY here
+    datas = [make_jpeg(410 + i, 320, 240, samp) for i, samp in enumerate([(2, 2), (1, 1)])]
+    dec = sess.decoder(device_id=0, backends=ref.BACKEND_GPU_ONLY, options=":fancy_upsampling=1")
     outs = [torch.zeros((240, 960), dtype=torch.uint8, device="cuda") for _ in range(2)]
-    st, _ = dec.decode_raw([good, prog], [o.data_ptr() for o in outs], [(320, 240)] * 2, [ref.I_RGB] * 2, [960] * 2, ref.BUFFER_DEVICE)
     torch.cuda.synchronize()
-    assert st[0] == ref.STATUS_SUCCESS and st[1] != ref.STATUS_SUCCESS
-    assert np.array_equal(outs[0].cpu().numpy().reshape(240, 320, 3), port.decode(good, port.FMT_I_RGB, True))
+    st, _ = dec.decode_raw(datas, [o.data_ptr() for o in outs], [(320, 240)] * 2, [ref.I_RGB] * 2, [960] * 2, ref.BUFFER_DEVICE)
+    torch.cuda.synchronize()
+    assert st == [ref.STATUS_SUCCESS] * 2
+    for d, o in zip(datas, outs):
+        assert np.array_equal(o.cpu().numpy().reshape(240, 320, 3), port.decode(d, port.FMT_I_RGB, True))
     dec.close()
 
 
