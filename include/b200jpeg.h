@@ -132,7 +132,8 @@ B200JPEG_API int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t*
 B200JPEG_API int b200jpeg_decoder_get_stage_times(b200jpegDecoder_t decoder, float* ms, int n);
 
 /* Debug/verification taps on the last prepared+run batch (device -> host copies of intermediates):
- *   what = 0: quantised coefficients of image i in MCU scan order, int16[blocks*64] (natural order inside a block)
+ *   what = 0: quantised coefficients of image i in MCU scan order, int16[blocks*64] (natural order inside a block);
+ *             needs the decoder option "dump_coef=1" (the product path keeps coefficients as compact records only)
  *   what = 1: component plane c of image i after dequant+IDCT (MCU-padded), uint8
  *   what = 2: unstuffed entropy-coded bytes of image i
  * returns bytes written or <0 */

@@ -1,5 +1,6 @@
 // batch_plan.cpp -- see batch_plan.h
 #include "batch_plan.h"
+#include <algorithm>
 #include <cstring>
 
 namespace b200jpeg {
@@ -219,6 +220,10 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     plan.total_subseq += im.subseq_cta_count * kSubseqCta;
     plan.map_subseq.push_back(im.subseq_cta_first + im.subseq_cta_count);
 
+    // coefficient records: one per AC symbol; reserve for 2 bits per symbol plus the per-subsequence rounding
+    im.rec_off = plan.rec_elems;
+    im.rec_cap = uint32_t(std::min<uint64_t>(uint64_t(im.raw_len) * 4 + uint64_t(im.subseq_cta_count) * kSubseqCta * kRecAlign + 64, 0xFFFFFF00ull));
+    plan.rec_elems = align_up(plan.rec_elems + im.rec_cap, 64);
     im.coef_off = plan.coef_elems;
     plan.coef_elems = align_up(plan.coef_elems + uint64_t(im.total_blocks) * 64, 64);
     uint64_t blocks_out = 0;
@@ -255,6 +260,7 @@ void plan_finish(BatchPlan& plan)
     plan.raw_bytes = align_up(plan.raw_bytes + 64, 256);
     plan.clean_bytes = align_up(plan.clean_bytes + 64, 256);
     plan.coef_elems = align_up(plan.coef_elems + 64, 128);
+    plan.rec_elems = align_up(plan.rec_elems + 64, 128);
     plan.plane_bytes = align_up(plan.plane_bytes + 64, 256);
 }
 

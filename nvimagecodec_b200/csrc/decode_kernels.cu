@@ -9,11 +9,11 @@
 //                        predecessor's exit state; subsequences whose exit state changed feed a work list
 //   H2 k_huff_sync_tail  cooperative kernel: Jacobi rounds over the (compacted) work list until it is empty
 //   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute write position per subsequence
-//   H4 k_huff_write      final decode pass: a CTA zeroes the coefficient range it owns, then stores de-zigzagged int16 AC
-//                        coefficients and the per-block DC differences
+//   H4 k_huff_write      final decode pass: every AC symbol becomes a 16-bit coefficient record (8-byte stores from a
+//                        register queue), every DC symbol stores the block's DC difference and first record index
 //   D1 k_dc_scan         per image: DC prediction = segmented (restart interval) prefix sum per component over dc[]
-//   I1 k_idct            dequantise + islow IDCT, one 8x8 block per thread (coefficients staged through shared memory so
-//                        that global loads are full 128-byte lines), writes component planes
+//   I1 k_idct            coefficient records -> dense block in shared memory, dequantise + islow IDCT, one 8x8 block per
+//                        thread, writes component planes
 //   C1 k_color           upsample (fancy / box) + YCbCr->RGB; a warp produces 512 pixels x (1|2) rows, staged in shared
 //                        memory and written with fully coalesced 128-byte store instructions at any alignment
 // The per-thread arithmetic lives in huffman.cuh / jpeg_math.cuh (shared with the CPU emulation used by the tests).
@@ -338,15 +338,17 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// IDCT: one block per thread.  A warp first copies its 32 blocks' coefficients (32 x 128 bytes, scattered over the MCU
-// order) into shared memory with 128-byte-coalesced loads, then each lane reads its own block back (row pitch 144 bytes:
-// conflict free for 16-byte accesses).
+// IDCT: one block per thread.  Each thread expands its block's coefficient records (sequential uint16 reads from the
+// record stream the Huffman write pass produced) into its own dense 8x8 slot in shared memory (row pitch 144 bytes:
+// conflict free for 16-byte accesses) and reads the slot back as the IDCT input.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kIdctPitch = 144;
+__constant__ uint8_t c_zz_next[kRecZigzagNextSize] = B2J_ZIGZAG_NEXT_INIT;
 __global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
 {
     __shared__ __align__(16) uint8_t s_blk[kIdctCta * kIdctPitch];
     __shared__ uint16_t s_q[3 * 64];
+    __shared__ uint8_t s_zz[kRecZigzagNextSize + 3];
     const uint32_t cta_abs = blockIdx.x + b.base_idct;
     const int img = find_image(b.cta_map_idct, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
@@ -354,26 +356,28 @@ __global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
         s_q[i] = b.quant[im.qt[i >> 6] * 64 + (i & 63)];
     const uint32_t u = (cta_abs - b.cta_map_idct[img]) * kIdctCta + threadIdx.x;
     const IdctBlockRef ref = idct_locate(im, u);
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint8_t* wbuf = s_blk + warp * 32 * kIdctPitch;
-    const int16_t* coef = b.coef + im.coef_off;
-    const uint32_t my_src = ref.comp >= 0 ? ref.src_blk : 0xFFFFFFFFu;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int bw = i * 4 + int(lane >> 3); // block of the warp this lane helps to load
-        const uint32_t src = __shfl_sync(0xFFFFFFFFu, my_src, bw);
-        if (src != 0xFFFFFFFFu) {
-            const uint4 v = reinterpret_cast<const uint4*>(coef + uint64_t(src) * 64)[lane & 7];
-            *reinterpret_cast<uint4*>(wbuf + bw * kIdctPitch + (lane & 7) * 16) = v;
-        }
-    }
+    if (threadIdx.x < kRecZigzagNextSize)
+        s_zz[threadIdx.x] = c_zz_next[threadIdx.x];
     __syncthreads();
     if (ref.comp < 0)
         return;
+    // the thread's own slot: zero it, scatter the block's coefficient records into it, read it back as a dense block
+    uint8_t* slot = s_blk + threadIdx.x * kIdctPitch;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        reinterpret_cast<uint4*>(slot)[i] = make_uint4(0, 0, 0, 0);
+    if (records_to_block(b.rec + im.rec_off, b.blk_rec[im.coef_off / 64 + ref.src_blk], b.states[img].rec_total, s_zz,
+            reinterpret_cast<int16_t*>(slot)))
+        atomicOr(&b.states[img].error, kErrBadCode);
     alignas(16) int16_t blk[64];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
-        reinterpret_cast<uint4*>(blk)[i] = *reinterpret_cast<const uint4*>(wbuf + lane * kIdctPitch + i * 16);
+        reinterpret_cast<uint4*>(blk)[i] = reinterpret_cast<const uint4*>(slot)[i];
+    if (b.dump_coef) { // debug tap: the dense coefficients as the reference holds them (DC slot unused)
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            reinterpret_cast<uint4*>(b.coef + im.coef_off + uint64_t(ref.src_blk) * 64)[i] = reinterpret_cast<const uint4*>(blk)[i];
+    }
     const int dcval = b.dc[im.coef_off / 64 + ref.src_blk];
     uint32_t out[16];
     idct_block(blk, dcval, s_q + ref.comp * 64, out);

@@ -66,6 +66,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
             o.groups = std::max(1, std::atoi(value.c_str()));
         else if (name == "stage_stream")
             o.stage_stream = std::atoi(value.c_str()) != 0;
+        else if (name == "dump_coef")
+            o.dump_coef = std::atoi(value.c_str()) != 0;
         else if (name == "profile")
             o.profile = std::atoi(value.c_str()) != 0;
     }
@@ -78,7 +80,7 @@ Decoder::~Decoder()
 {
     if (device_ >= 0)
         cudaSetDevice(device_);
-    DevBuf* dbufs[] = {&d_raw_, &d_clean_, &d_coef_, &d_dc_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
+    DevBuf* dbufs[] = {&d_records_, &d_blkrec_, &d_nrec_, &d_recoff_, &d_raw_, &d_clean_, &d_coef_, &d_dc_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
         &d_rec_, &d_abs_, &d_wl0_, &d_wl1_, &d_sync_, &d_out_};
     for (DevBuf* b : dbufs)
         if (b->p)
@@ -234,7 +236,10 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     // ---- scratch ----
     int rc = 0;
     if ((rc = ensure(d_raw_, plan_.raw_bytes)) || (rc = ensure(d_clean_, plan_.clean_bytes)) ||
-        (rc = ensure(d_coef_, plan_.coef_elems * sizeof(int16_t))) || (rc = ensure(d_dc_, plan_.coef_elems / 64 * sizeof(int16_t) + 64)) ||
+        (opt_.dump_coef && (rc = ensure(d_coef_, plan_.coef_elems * sizeof(int16_t)))) ||
+        (rc = ensure(d_dc_, plan_.coef_elems / 64 * sizeof(int16_t) + 64)) || (rc = ensure(d_records_, plan_.rec_elems * sizeof(uint16_t))) ||
+        (rc = ensure(d_blkrec_, plan_.coef_elems / 64 * sizeof(uint32_t) + 64)) || (rc = ensure(d_nrec_, 4 * size_t(plan_.total_subseq))) ||
+        (rc = ensure(d_recoff_, 4 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_planes_, plan_.plane_bytes)) ||
         (rc = ensure(d_states_, sizeof(ImageState) * m)) || (rc = ensure(d_seg_, sizeof(uint32_t) * (plan_.total_segs + 1))) ||
         (rc = ensure(d_chunks_, sizeof(uint64_t) * plan_.total_chunks)) || (rc = ensure(d_exit_, 8 * size_t(plan_.total_subseq))) ||
@@ -288,6 +293,11 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.worklist[1] = static_cast<uint32_t*>(d_wl1_.p);
     dev_.sync = static_cast<SyncCounters*>(d_sync_.p);
     dev_.coef = static_cast<int16_t*>(d_coef_.p);
+    dev_.dump_coef = opt_.dump_coef ? 1 : 0;
+    dev_.rec = static_cast<uint16_t*>(d_records_.p);
+    dev_.blk_rec = static_cast<uint32_t*>(d_blkrec_.p);
+    dev_.sub_nrec = static_cast<uint32_t*>(d_nrec_.p);
+    dev_.sub_rec_off = static_cast<uint32_t*>(d_recoff_.p);
     dev_.dc = static_cast<int16_t*>(d_dc_.p);
     dev_.planes = static_cast<uint8_t*>(d_planes_.p);
     dev_.cta_map_unstuff = reinterpret_cast<const uint32_t*>(dm + off_m0 + 0 * map_bytes);
@@ -302,7 +312,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     // stream staging in shared memory: per thread its subsequence plus the words a symbol may run over, an odd count
     dev_.stream_words = 0;
     if (opt_.stage_stream && opt_.subseq_bytes <= 256)
-        dev_.stream_words = (plan_.subseq_bits / 32 + 5) | 1;
+        dev_.stream_words = (plan_.subseq_bits / 32 + 3) | 1; // a symbol starting in the last word reads two words past it
     if (dev_.lut_slots != cfg_lut_slots_ || dev_.stream_words != cfg_stream_words_) {
         if (huff_configure(dev_, device_, &tail_capacity_) != 0 || tail_capacity_ <= 0) {
             std::fprintf(stderr, "b200jpeg: cannot configure the Huffman kernels: %s\n", cudaGetErrorString(cudaGetLastError()));
@@ -551,6 +561,8 @@ int64_t Decoder::debug_fetch(int what, int image, int comp, void* dst, size_t ca
     const void* src = nullptr;
     size_t bytes = 0;
     if (what == 0) { // coefficients: AC from the coefficient array, DC (after prediction) from the DC array
+        if (!opt_.dump_coef)
+            return -4; // needs the decoder option dump_coef=1
         const size_t nb = im.total_blocks;
         bytes = nb * 128;
         if (bytes > cap)

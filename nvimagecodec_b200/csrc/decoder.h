@@ -17,6 +17,7 @@ struct DecoderOptions
     int copy_threads = 4;
     int groups = 4;           // the batch is cut into this many groups of images that run on separate streams (pipelining)
     bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)
+    bool dump_coef = false; // debug: keep dense DCT coefficients for b200jpeg_debug_fetch(what = 0)
     bool profile = false; // record CUDA events between the kernel stages (b200jpeg_decoder_get_stage_times)
 };
 
@@ -100,7 +101,7 @@ class Decoder
     int batch_size_ = 0;
     std::vector<HostOutput> host_outs_;
 
-    DevBuf d_raw_, d_clean_, d_coef_, d_dc_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_wl0_,
+    DevBuf d_records_, d_blkrec_, d_nrec_, d_recoff_, d_raw_, d_clean_, d_coef_, d_dc_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_wl0_,
         d_wl1_, d_sync_, d_out_;
     DevBuf h_raw_, h_meta_, h_states_;
     BatchDev dev_{};

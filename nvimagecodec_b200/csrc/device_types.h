@@ -27,9 +27,9 @@ constexpr int kMaxTabSlots = 6;       // distinct Huffman tables one image can r
 
 // Decode table derived from one DHT table (reference: d_derived_tbl, external/libjpeg-turbo/jdhuff.h:27-51 and
 // jpeg_make_d_derived_tbl, jdhuff.c:143-285).  We use an 11-bit first level instead of 8 and store pre-digested entries
-//   entry = code_length | size << 5 | zadv << 9
-// size = number of value bits that follow the code; zadv = how far the zigzag position advances (DC: 1; AC run/size:
-// run + 1; ZRL: 16; EOB: 64).  Codes longer than kLutBits: the first-level entry of their 11-bit prefix has code_length 0
+//   entry = (code_length + size) | size << 5 | zadv << 9
+// size = number of value bits that follow the code (so the low 5 bits are the total number of bits the symbol takes:
+// at most 16 + 15); zadv = how far the zigzag position advances (DC: 1; AC run/size: run + 1; ZRL: 16; EOB: 64).  Codes longer than kLutBits: the first-level entry of their 11-bit prefix has code_length 0
 // and holds n << 5 | (offset / 2) << 8; the entry of the code is lut[kLutSize + offset + next n bits] (same format, full
 // length).  entry == 0: invalid code, or a table too irregular for kLut2Size second-level entries -> maxcode walk.
 // The same symbols come out as with the reference's tables.
@@ -52,7 +52,7 @@ B2J_HD uint32_t huff_entry(int len, int sym, bool is_dc)
         const int r = sym >> 4;
         zadv = s ? r + 1 : (r == 15 ? 16 : 64);
     }
-    return uint32_t(len) | (uint32_t(s) << 5) | (uint32_t(zadv) << 9);
+    return uint32_t(len + s) | (uint32_t(s) << 5) | (uint32_t(zadv) << 9);
 }
 
 // Table selector of one block position inside the MCU: offsets (uint16 units from the LUT base the kernel uses) and pool
@@ -99,7 +99,9 @@ struct ImageDesc
     uint32_t seg_first;   // index into the segment-start pool; entries [seg_first, seg_first + num_segments]
 
     // intermediates
-    uint64_t coef_off;        // int16 units, blocks in MCU scan order (coef_off / 64 = first block in the DC array)
+    uint64_t rec_off;         // first coefficient record of this image in the record buffer (uint16 units, multiple of 8)
+    uint32_t rec_cap;         // records reserved for the image
+    uint64_t coef_off;        // int16 units, blocks in MCU scan order (coef_off / 64 = first block in the DC / block-record arrays)
     uint64_t plane_off[3];    // bytes
     int32_t plane_pitch[3];
     uint32_t idct_cta_first, idct_cta_count;
@@ -121,12 +123,24 @@ struct ImageState
     uint32_t marker_count;  // RSTn markers seen
     uint32_t error;         // bit flags, see kErr*
     uint32_t done_blocks;   // set by the thread that completes the last block (== total_blocks when the scan is complete)
+    uint32_t rec_total;     // coefficient records of the image (after the subsequence scan)
+    uint32_t pad_[3];
 };
 
 constexpr uint32_t kErrBadMarker = 1;     // unexpected marker inside entropy-coded data / wrong RSTn order / count
 constexpr uint32_t kErrBadCode = 2;       // invalid Huffman code on the synchronised path
 constexpr uint32_t kErrNotConverged = 4;  // subsequence synchronisation incomplete
 constexpr uint32_t kErrOverrun = 8;       // decode ran past the end of a segment / image
+constexpr uint32_t kErrRecords = 16;      // more coefficient records than reserved (a stream averaging < 2 bits per AC symbol)
+
+// Coefficient records: what the Huffman write pass hands to the IDCT kernel, one uint16 per AC symbol in stream order
+//   run << 12 | (value & 0xFFF)   a coefficient `value` (never 0) after `run` zeros
+//   kRecZrl                       sixteen zeros
+//   kRecEnd                       end of block (the EOB symbol)
+//   kRecPad                       filler at the end of a subsequence's record range, skipped by the reader
+// A block whose last coefficient sits at zigzag position 63 has no kRecEnd: the reader stops at position 64.
+constexpr uint32_t kRecZrl = 0xF000u, kRecEnd = 0x0000u, kRecPad = 0x0800u;
+constexpr uint32_t kRecAlign = 4;         // records per 8-byte store: every subsequence's range is a multiple of this
 
 // State of the Huffman decoder between two symbols, packed in 64 bits: bit position | (block-in-MCU * 64 + zigzag index) << 32
 B2J_HD unsigned long long pack_state(uint32_t p, uint32_t slot) { return (unsigned long long)p | ((unsigned long long)slot << 32); }
@@ -158,7 +172,12 @@ struct BatchDev // pointers handed to every kernel
     uint32_t* sub_abs;      // inclusive scan of sub_rec: absolute slot count at the subsequence's exit
     uint32_t* worklist[2];  // subsequences whose entry changed (global subsequence indices)
     SyncCounters* sync;
-    int16_t* coef;          // AC coefficients, natural order, 64 per block (slot 0 unused: the DC lives in dc[])
+    uint32_t* sub_nrec;     // per subsequence: AC symbols (= coefficient records) its last decode produced
+    uint32_t* sub_rec_off;  // exclusive scan of sub_nrec rounded up to kRecAlign: first record of the subsequence in the image
+    uint16_t* rec;          // coefficient records of all images (ImageDesc::rec_off)
+    uint32_t* blk_rec;      // per block: index of its first record inside the image's records
+    int32_t dump_coef;      // debug: the IDCT kernel also writes the dense coefficients it reconstructed to coef[]
+    int16_t* coef;          // debug tap (dump_coef): AC coefficients, natural order, 64 per block (slot 0 unused: the DC lives in dc[])
     int16_t* dc;            // per block: DC difference after the write pass, DC value after the DC scan
     uint8_t* planes;
     const uint32_t* cta_map_unstuff; // prefix arrays: first CTA of each image (+ total at [num_images])
@@ -172,7 +191,7 @@ struct BatchDev // pointers handed to every kernel
     uint32_t total_subseq;
     int32_t num_tables;    // Huffman tables in the pool
     int32_t lut_slots;     // LUT slots the decoding kernels reserve in shared memory (>= every image's ntabs)
-    int32_t stream_words;  // 32-bit words of staged stream per thread (odd, >= subseq_bits / 32 + 4); 0 = read the stream from global memory
+    int32_t stream_words;  // 32-bit words of staged stream per thread (odd, >= subseq_bits / 32 + 3); 0 = read the stream from global memory
 };
 
 } // namespace b200jpeg

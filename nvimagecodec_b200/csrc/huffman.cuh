@@ -10,6 +10,9 @@
 // (decode_kernels.cu); Huffman streams self-synchronise, so the repair converges after a few rounds.
 #pragma once
 #include "device_types.h"
+#if !defined(__CUDACC__)
+#include "host_shim.h"
+#endif
 
 namespace b200jpeg {
 
@@ -39,14 +42,17 @@ B2J_HD uint32_t bswap32(uint32_t v)
 #endif
 }
 
-B2J_HD uint32_t funnel_left(uint32_t hi, uint32_t lo, uint32_t sh) // top 32 bits of (hi:lo) << sh, sh in [0, 31]
+B2J_HD uint32_t funnel_left(uint32_t hi, uint32_t lo, uint32_t sh) // top 32 bits of (hi:lo) << (sh mod 32)
 {
 #if defined(__CUDA_ARCH__)
-    return __funnelshift_l(lo, hi, sh);
+    return __funnelshift_l(lo, hi, sh); // the hardware shift wraps at 32: callers pass the bit position itself
 #else
+    sh &= 31u;
     return sh ? (hi << sh) | (lo >> (32 - sh)) : hi;
 #endif
 }
+
+
 
 // Long-code walk (code length > kLutBits), ljt/jdhuff.c jpeg_huff_decode:398-450.  Returns a LUT-format entry; an
 // invalid code comes back as length 16, size 0, zadv 1 with ok = false.
@@ -61,11 +67,30 @@ B2J_HD uint32_t huff_long_code(const DevHuffTable* t, uint32_t win, bool& ok)
     return 16u | (1u << 9);
 }
 
+// Entry of a code longer than kLutBits (first-level entry e0 with a zero length field): second-level table, or the
+// maxcode walk when the table was too irregular for it.  Invalid codes come back as "16 bits, no value, advance 1".
+B2J_HD uint32_t huff_long_entry(const uint16_t* lut, uint32_t base, uint32_t e0, const DevHuffTable* tab, uint32_t win, bool& ok)
+{
+    if (e0) {
+        const uint32_t n = (e0 >> 5) & 7u;
+        const uint32_t e = lut[base + uint32_t(kLutSize) + (e0 >> 8) * 2u + ((win >> (32 - kLutBits - n)) & ((1u << n) - 1u))];
+        if (e)
+            return e;
+        ok = false; // unused code space below that prefix
+        return 16u | (1u << 9);
+    }
+    return huff_long_code(tab, win, ok);
+}
+
+struct HuffEnv;
+B2J_HD uint32_t staged_word(const HuffEnv& env, uint32_t wi);
+
 // Everything a decoding thread needs to know about its image; the pointers may be shared or global memory.
 struct HuffEnv
 {
     const uint32_t* words;   // unstuffed stream of the image (4-byte aligned, readable 16 bytes past the end); with
                              // PRESWAPPED the words were byte-swapped to big-endian bit order when they were staged
+    uint32_t words_s;        // device, PRESWAPPED only: shared-window address of words[0] (the fast loop reads with ld.shared)
     const uint16_t* lut;     // LUT base the TabSel offsets refer to
     const TabSel* tabsel;    // [bpm]
     const DevHuffTable* pool; // global table pool (long-code walk)
@@ -77,29 +102,79 @@ struct HuffEnv
     int32_t bpm;
 };
 
+B2J_HD uint32_t staged_word(const HuffEnv& env, uint32_t wi) // word wi of the staged (byte-swapped) stream
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(env.words_s + wi * 4u));
+    return v;
+#else
+    return env.words[wi];
+#endif
+}
+
 struct HuffState
 {
     uint32_t p;      // bit position of the next symbol
     uint32_t z;      // zigzag index inside the current block (0 = the DC symbol is next)
     uint32_t blk;    // block inside the MCU
     uint32_t nblk;   // blocks completed: absolute block index of the current block if abs, else relative to the entry
+    uint32_t nrec;   // symbols decoded = records the write pass emits for the same span
     bool abs;
 };
 
+// Where the write pass puts what it decodes (all pointers are per image).  Every symbol pushes exactly one record (a DC
+// symbol pushes padding) so the loop has no data-dependent branch around the queue; records go out eight bytes at a time
+// from a 64-bit register queue: the stores of a warp's lanes hit 32 different lines whatever we do, so there should be few.
+struct RecOut
+{
+    uint16_t* rec;      // the image's records
+    uint32_t* blk_rec;  // per block: index of its first record
+    int16_t* dc;        // per block: DC difference
+    uint32_t cursor;    // next record index; starts at the subsequence's offset (a multiple of kRecAlign)
+    uint32_t limit;     // end of the subsequence's range: records past it are dropped (only a corrupt stream gets there)
+    uint32_t qlo, qhi;  // the last records, oldest in the low half of qlo
+
+    B2J_HD void push(uint32_t r)
+    {
+        qlo = (qlo >> 16) | (qhi << 16);
+        qhi = (qhi >> 16) | (r << 16);
+        ++cursor;
+        if ((cursor & (kRecAlign - 1u)) == 0 && cursor <= limit)
+            *reinterpret_cast<uint2*>(rec + cursor - kRecAlign) = make_uint2(qlo, qhi);
+    }
+    B2J_HD void finish() // fill the range with padding records
+    {
+        while (cursor < limit)
+            push(kRecPad);
+    }
+};
+
+// value bits -> coefficient (HUFF_EXTEND, ljt/jdhuff.c:483-488) and the record of the symbol, without branches.
+// t = stream window shifted so that the first value bit is bit 31; sz = number of value bits; zadv from the table entry.
+B2J_HD uint32_t make_record(uint32_t t, uint32_t sz, uint32_t zadv, bool is_ac, int& val)
+{
+    const uint32_t bits = sz ? t >> (32u - sz) : 0u;
+    const int neg = ~(int(t) >> 31); // all ones when the first value bit is 0: a negative coefficient
+    val = int(bits) + (neg & (1 - (1 << sz)));
+    uint32_t r = (((zadv - 1u) << 12) | (uint32_t(val) & 0xFFFu)) & 0xFFFFu; // ZRL (sz 0, zadv 16) comes out as kRecZrl
+    r = zadv == 64u ? kRecEnd : r;
+    return is_ac ? r : kRecPad;
+}
+
 // Decode every symbol that starts in [s.p, end) (segment changes included), beginning in state s.
-// WRITE = false: synchronisation pass, nothing is stored.
-// WRITE = true : s.abs must hold.  Coefficients of blocks >= first_block are stored: AC de-zigzagged into coef (64 int16
-//                per block, absolute block index), the DC *difference* into dc[block].  With extend = true the thread
-//                keeps going past `end` until the block it is in is complete (the last subsequence of a CTA finishes
-//                the block that straddles into the next CTA's range).  Returns error flags.
+// WRITE = false: synchronisation pass, nothing is stored; s.nrec counts the symbols.
+// WRITE = true : s.abs must hold.  Every symbol becomes a record in `out` (AC: coefficient / ZRL / end of block, DC:
+//                padding); a DC symbol also stores the DC difference of its block and the index of the block's first
+//                coefficient record.  Returns error flags.
 template <bool WRITE, bool PRESWAPPED = false>
-B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool extend, uint32_t first_block, int16_t* coef, int16_t* dc)
+B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecOut* out)
 {
     if (end > env.clean_bits)
         end = env.clean_bits;
     uint32_t err = 0;
-    if (WRITE && (s.nblk >= env.total_blocks || (extend && s.p >= end && s.z == 0)))
-        return 0; // nothing left to decode (trailing bytes after the last block / the block ended with the subsequence)
+    if (WRITE && s.nblk >= env.total_blocks)
+        return 0; // trailing bytes after the last block
     const int nseg = env.num_segments;
     int g = 0;
     if (nseg > 1) { // locate the segment containing p
@@ -120,14 +195,56 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool
             s.blk = 0;
         }
     }
-    uint32_t p = s.p, z = s.z, blk = s.blk, nblk = s.nblk;
-    bool stop = false;
-    while (!stop) {
+    uint32_t p = s.p, z = s.z, blk = s.blk, nblk = s.nblk, nrec = s.nrec;
+    for (;;) {
         const bool last = (g == nseg - 1);
         const uint32_t B = last ? env.clean_bits : env.seg[g + 1] * 8u; // end of this segment's bits
-        const uint32_t lim = extend ? B : (end < B ? end : B);
+        const uint32_t lim = end < B ? end : B;
         const uint32_t seg_end = last ? env.total_blocks : uint32_t(g + 1) * env.seg_blocks; // used when s.abs
         TabSel ts = env.tabsel[blk];
+        bool cross = false;
+        if (PRESWAPPED && p < lim && lim + 32u <= B && (!WRITE || nblk + (lim - p) / 2u + 16u < seg_end)) {
+            // Well inside a segment (the common case): no symbol can run over the segment end (and, writing, the blocks
+            // of the segment cannot run out: a block takes at least two bits), so the loop carries nothing but the
+            // decoder state.  Both stream words are fetched per symbol (shared memory): cheaper than keeping a sliding
+            // window up to date in a loop whose lanes all diverge.
+            do {
+                const uint32_t wi = p >> 5;
+                const uint32_t win = funnel_left(staged_word(env, wi), staged_word(env, wi + 1), p);
+                const uint32_t base = z ? ts.ac_off : ts.dc_off;
+                uint32_t e = env.lut[base + (win >> (32 - kLutBits))];
+                if ((e & 31u) == 0) {
+                    bool ok = true;
+                    e = huff_long_entry(env.lut, base, e, env.pool + (z ? ts.ac_idx : ts.dc_idx), win, ok);
+                    if (WRITE && !ok)
+                        err |= kErrBadCode;
+                }
+                const uint32_t tot = e & 31u, zadv = e >> 9;
+                if (WRITE) {
+                    const uint32_t sz = (e >> 5) & 15u;
+                    int val;
+                    const uint32_t r = make_record(win << (tot - sz), sz, zadv, z != 0, val);
+                    out->push(r);
+                    if (z == 0) {
+                        out->dc[nblk] = int16_t(val);
+                        out->blk_rec[nblk] = out->cursor;
+                    }
+                } else {
+                    ++nrec;
+                }
+                p += tot;
+                z += zadv;
+                if (z >= 64u) {
+                    z = 0;
+                    ++nblk;
+                    ++blk;
+                    if (blk == uint32_t(env.bpm))
+                        blk = 0;
+                    ts = env.tabsel[blk];
+                }
+            } while (p < lim);
+            break; // p >= end, still inside the segment
+        }
         uint32_t widx = p >> 5;
         uint32_t w0 = env.words[widx], w1 = env.words[widx + 1], w2 = env.words[widx + 2];
         if (!PRESWAPPED) {
@@ -135,52 +252,32 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool
             w1 = bswap32(w1);
             w2 = bswap32(w2);
         }
-        bool cross = false;
         while (p < lim) {
-            const uint32_t win = funnel_left(w0, w1, p & 31u);
+            const uint32_t win = funnel_left(w0, w1, p);
             const uint32_t base = z ? ts.ac_off : ts.dc_off;
             uint32_t e = env.lut[base + (win >> (32 - kLutBits))];
             if ((e & 31u) == 0) { // code longer than kLutBits
                 bool ok = true;
-                if (e) {
-                    const uint32_t n = (e >> 5) & 7u;
-                    e = env.lut[base + uint32_t(kLutSize) + (e >> 8) * 2u + ((win >> (32 - kLutBits - n)) & ((1u << n) - 1u))];
-                    if (e == 0) { // unused code space below that prefix
-                        ok = false;
-                        e = 16u | (1u << 9);
-                    }
-                } else {
-                    e = huff_long_code(env.pool + (z ? ts.ac_idx : ts.dc_idx), win, ok);
-                }
+                e = huff_long_entry(env.lut, base, e, env.pool + (z ? ts.ac_idx : ts.dc_idx), win, ok);
                 if (WRITE && !ok)
                     err |= kErrBadCode;
             }
-            const uint32_t len = e & 31u, sz = (e >> 5) & 15u, zadv = e >> 9;
-            const uint32_t newp = p + len + sz;
+            const uint32_t tot = e & 31u, sz = (e >> 5) & 15u, zadv = e >> 9;
+            const uint32_t newp = p + tot;
             if (newp > B) { // the "symbol" runs over the segment end: it was padding
                 cross = true;
                 break;
             }
             if (WRITE) {
-                int val = 0;
-                if (sz) {
-                    const uint32_t bits = (win << len) >> (32u - sz);
-                    val = int(bits);
-                    if (!(bits >> (sz - 1u)))
-                        val -= (1 << sz) - 1; // HUFF_EXTEND
+                int val;
+                const uint32_t r = make_record(win << (tot - sz), sz, zadv, z != 0, val);
+                out->push(r);
+                if (z == 0) {
+                    out->dc[nblk] = int16_t(val);
+                    out->blk_rec[nblk] = out->cursor;
                 }
-                if (nblk - first_block < env.total_blocks - first_block) { // first_block <= nblk < total_blocks
-                    if (z == 0)
-                        dc[nblk] = int16_t(val);
-                    else if (sz) {
-                        uint32_t zt = z + zadv - 1u;
-                        if (zt > 63u) {
-                            zt = 63u;
-                            err |= kErrBadCode;
-                        }
-                        coef[uint64_t(nblk) * 64u + B2J_ZZ(zt)] = int16_t(val);
-                    }
-                }
+            } else {
+                ++nrec;
             }
             z += zadv;
             p = newp;
@@ -201,14 +298,8 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool
                     cross = true;
                     break;
                 }
-                if (extend && p >= end) {
-                    stop = true;
-                    break;
-                }
             }
         }
-        if (stop)
-            break;
         if (cross || p >= B) {
             if (last) {
                 if (cross) {
@@ -226,8 +317,8 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool
             blk = 0;
             nblk = uint32_t(g) * env.seg_blocks;
             s.abs = true;
-            if (extend && p >= end)
-                break; // the straddling block ended with its segment
+            if (p >= end)
+                break;
         } else {
             break; // p >= end
         }
@@ -236,6 +327,7 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, bool
     s.z = z;
     s.blk = blk;
     s.nblk = nblk;
+    s.nrec = nrec;
     return err;
 }
 

@@ -3,9 +3,10 @@
 //   H1 k_huff_sync x 2   self-synchronising subsequence decode (no output): round 0 from a guessed state, round 1 from the
 //                        predecessor's exit state; subsequences whose exit state changed feed a work list
 //   H2 k_huff_sync_tail  cooperative kernel: Jacobi rounds over the (compacted) work list until it is empty
-//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute write position per subsequence
-//   H4 k_huff_write      final decode pass: a CTA zeroes the coefficient range it owns, then stores de-zigzagged int16 AC
-//                        coefficients and the per-block DC differences
+//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute block position per subsequence,
+//                        scan of record counts -> record offset per subsequence
+//   H4 k_huff_write      final decode pass: every AC symbol becomes a 16-bit coefficient record (8-byte stores from a
+//                        register queue), every DC symbol stores the block's DC difference and first record index
 // Shared memory layout of the decoding kernels (dynamic): [LUTs: lut_slots x 5 KB][TabSel x 8][stream staging].
 // The unstuffed stream of the CTA's subsequences is staged (byte-swapped to bit order) with coalesced loads; thread t
 // owns the words [t * W, (t + 1) * W) where W = stream_words is odd, so threads at the same position of their
@@ -78,11 +79,14 @@ __device__ __forceinline__ void stage_cta(const BatchDev& b, const ImageDesc& im
     __syncthreads();
 }
 
+// words_s: shared-window address matching words[0] when the stream is staged in shared memory (32-bit arithmetic, may
+// wrap below the window for the per-thread "virtual base"), 0 otherwise
 __device__ __forceinline__ HuffEnv make_env(const BatchDev& b, const ImageDesc& im, uint32_t clean_len, const uint32_t* words,
-    const uint16_t* lut, const TabSel* tabsel)
+    const uint16_t* lut, const TabSel* tabsel, uint32_t words_s = 0)
 {
     HuffEnv env;
     env.words = words;
+    env.words_s = words_s;
     env.lut = lut;
     env.tabsel = tabsel;
     env.pool = b.huff;
@@ -106,13 +110,15 @@ __device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& en
     s.z = slot & 63u;
     s.blk = slot >> 6;
     s.nblk = 0;
+    s.nrec = 0;
     s.abs = exact;
     const uint32_t z_entry = s.z;
-    decode_span<false, PRESWAPPED>(env, s, (k + 1u) * uint32_t(b.subseq_bits), false, 0, nullptr, nullptr);
+    decode_span<false, PRESWAPPED>(env, s, (k + 1u) * uint32_t(b.subseq_bits), nullptr);
     const unsigned long long X = pack_state(s.p, s.blk * 64u + s.z);
     const bool changed = (X != __ldcg(b.sub_exit + t));
     b.sub_exit[t] = X;
     b.sub_entry[t] = E;
+    b.sub_nrec[t] = s.nrec;
     // slots consumed: absolute (from the image start) once a known state was passed, else relative to the entry
     const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
     b.sub_rec[t] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
@@ -138,11 +144,13 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
     const bool staged = b.stream_words != 0;
     const uint32_t* words = staged ? sm.stream + threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5)
                                    : reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
-    const HuffEnv env = make_env(b, im, clean_len, words, sm.lut, sm.tabsel);
+    const uint32_t words_s = uint32_t(__cvta_generic_to_shared(sm.stream)) + (threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5)) * 4u;
+    const HuffEnv env = make_env(b, im, clean_len, words, sm.lut, sm.tabsel, words_s);
     if (round == 0) {
         if (idle) {
             b.sub_exit[t] = b.sub_entry[t] = pack_state(clean_bits, 0);
             b.sub_rec[t] = 0;
+            b.sub_nrec[t] = 0;
             return;
         }
         b.sub_exit[t] = ~0ull;
@@ -222,7 +230,8 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b)
                 const uint32_t first = k * spw, max_words = (im.raw_len + 16u) >> 2;
                 for (uint32_t j = 0; j < W; ++j)
                     my_words[j] = first + j < max_words ? __byte_perm(gwords[first + j], 0, 0x0123) : 0u;
-                const HuffEnv env = make_env(b, im, clean_len, my_words - first, lut, tabsel);
+                const HuffEnv env = make_env(b, im, clean_len, my_words - first, lut, tabsel,
+                    uint32_t(__cvta_generic_to_shared(my_words)) - first * 4u);
                 changed = sync_decode<true>(b, env, t, k, E, false);
             } else {
                 const HuffEnv env = make_env(b, im, clean_len, gwords, lut, tabsel);
@@ -250,37 +259,59 @@ __global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
     const ImageDesc& im = b.images[img];
     const uint32_t count = im.subseq_cta_count * kSubseqCta;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    __shared__ uint32_t s_w[kScanThreads / 32];
-    __shared__ uint32_t s_carry;
-    if (threadIdx.x == 0)
+    __shared__ uint32_t s_w[kScanThreads / 32], s_r[kScanThreads / 32];
+    __shared__ uint32_t s_carry, s_rcarry;
+    if (threadIdx.x == 0) {
         s_carry = 0x80000000u;
+        s_rcarry = 0;
+    }
     __syncthreads();
     bool bad = false;
     for (uint32_t c0 = 0; c0 < count; c0 += kScanThreads) {
         const uint32_t c = c0 + threadIdx.x;
         uint32_t v = c < count ? b.sub_rec[im.subseq_first + c] : 0u;
+        // coefficient records of the subsequence, rounded up to the store granularity (plain inclusive scan)
+        const uint32_t nr = c < count ? (b.sub_nrec[im.subseq_first + c] + kRecAlign - 1u) & ~(kRecAlign - 1u) : 0u;
+        uint32_t r = nr;
         if (c > 0 && c < count && b.sub_entry[im.subseq_first + c] != b.sub_exit[im.subseq_first + c - 1] &&
             uint64_t(c) * uint32_t(b.subseq_bits) < uint64_t(b.states[img].clean_len) * 8u)
             bad = true; // the chain of entry/exit states is not consistent: synchronisation did not finish
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, v, o);
-            if (lane >= uint32_t(o))
+            const uint32_t rprev = __shfl_up_sync(0xFFFFFFFFu, r, o);
+            if (lane >= uint32_t(o)) {
                 v = seg_combine(tprev, v);
+                r += rprev;
+            }
         }
-        if (lane == 31)
+        if (lane == 31) {
             s_w[warp] = v;
+            s_r[warp] = r;
+        }
         __syncthreads();
-        uint32_t pre = s_carry;
-        for (int i = 0; i < int(warp); ++i)
+        uint32_t pre = s_carry, rpre = s_rcarry;
+        for (int i = 0; i < int(warp); ++i) {
             pre = seg_combine(pre, s_w[i]);
+            rpre += s_r[i];
+        }
         v = seg_combine(pre, v);
-        if (c < count)
+        r += rpre;
+        if (c < count) {
             b.sub_abs[im.subseq_first + c] = v;
+            b.sub_rec_off[im.subseq_first + c] = r - nr;
+        }
         __syncthreads();
-        if (threadIdx.x == kScanThreads - 1)
+        if (threadIdx.x == kScanThreads - 1) {
             s_carry = v;
+            s_rcarry = r;
+        }
         __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        b.states[img].rec_total = s_rcarry;
+        if (s_rcarry > im.rec_cap)
+            atomicOr(&b.states[img].error, kErrRecords);
     }
     if (bad)
         atomicOr(&b.states[img].error, kErrNotConverged);
@@ -299,26 +330,10 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
     const uint32_t clean_len = b.states[img].clean_len;
     const uint32_t clean_bits = clean_len * 8u;
     const uint32_t S = uint32_t(b.subseq_bits);
-
-    // blocks this CTA owns: those that *start* inside its subsequences
-    const uint32_t n_first = k0 == 0 ? 0u : (b.sub_abs[im.subseq_first + k0 - 1] & 0x7FFFFFFFu);
-    const bool last_cta = cta + 1 == im.subseq_cta_count;
-    const uint32_t n_next = b.sub_abs[im.subseq_first + k0 + kSubseqCta - 1] & 0x7FFFFFFFu;
-    const uint32_t first_block = (n_first + 63u) >> 6;
-    uint32_t end_block = last_cta ? im.total_blocks : (n_next + 63u) >> 6;
-    if (end_block > im.total_blocks)
-        end_block = im.total_blocks;
-    int16_t* coef = b.coef + im.coef_off;
-    int16_t* dc = b.dc + im.coef_off / 64;
-    if (end_block > first_block) { // zero the owned coefficient range: the scattered stores below then hit lines in L2
-        uint4* z4 = reinterpret_cast<uint4*>(coef + uint64_t(first_block) * 64);
-        const uint32_t n16 = (end_block - first_block) * 8u;
-        for (uint32_t i = threadIdx.x; i < n16; i += kSubseqCta)
-            z4[i] = make_uint4(0, 0, 0, 0);
-    }
-    __syncthreads();
     if (uint64_t(k) * S >= uint64_t(clean_bits))
         return;
+    if (b.states[img].error & kErrRecords)
+        return; // the records would not fit (flagged by the scan): the image is reported as corrupt
     HuffState s;
     if (k == 0) {
         s.p = 0;
@@ -334,23 +349,29 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
         s.nblk = (b.sub_abs[t - 1] & 0x7FFFFFFFu) >> 6;
     }
     s.abs = true;
-    const bool extend = (threadIdx.x == kSubseqCta - 1) || (uint64_t(k + 1) * S >= uint64_t(clean_bits));
-    const uint32_t* gwords = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
-    const uint32_t end = (k + 1u) * S;
-    uint32_t err = 0;
+    s.nrec = 0;
+    RecOut out;
+    out.rec = b.rec + im.rec_off;
+    out.blk_rec = b.blk_rec + im.coef_off / 64;
+    out.dc = b.dc + im.coef_off / 64;
+    out.cursor = b.sub_rec_off[t];
+    out.limit = out.cursor + ((b.sub_nrec[t] + kRecAlign - 1u) & ~(kRecAlign - 1u));
+    out.qlo = out.qhi = 0;
+    const uint32_t nblk_in = s.nblk;
+    uint32_t err;
     if (b.stream_words) {
-        const HuffEnv env = make_env(b, im, clean_len, sm.stream + threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5), sm.lut, sm.tabsel);
-        err = decode_span<true, true>(env, s, end, false, first_block, coef, dc);
-        if (extend) { // finish the block that straddles into the next CTA's subsequences, reading the stream from global memory
-            const HuffEnv env_g = make_env(b, im, clean_len, gwords, sm.lut, sm.tabsel);
-            err |= decode_span<true, false>(env_g, s, end, true, first_block, coef, dc);
-        }
+        const HuffEnv env = make_env(b, im, clean_len, sm.stream + threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5), sm.lut, sm.tabsel,
+            uint32_t(__cvta_generic_to_shared(sm.stream)) + (threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5)) * 4u);
+        err = decode_span<true, true>(env, s, (k + 1u) * S, &out);
     } else {
-        const HuffEnv env = make_env(b, im, clean_len, gwords, sm.lut, sm.tabsel);
-        err = decode_span<true, false>(env, s, end, extend, first_block, coef, dc);
+        const HuffEnv env = make_env(b, im, clean_len, reinterpret_cast<const uint32_t*>(b.clean + im.clean_off), sm.lut, sm.tabsel);
+        err = decode_span<true, false>(env, s, (k + 1u) * S, &out);
     }
-    if (s.nblk == im.total_blocks && s.z == 0 && extend)
-        b.states[img].done_blocks = s.nblk;
+    if (out.cursor > out.limit)
+        err |= kErrRecords;
+    out.finish();
+    if (s.nblk == im.total_blocks && s.z == 0 && nblk_in < im.total_blocks)
+        b.states[img].done_blocks = s.nblk; // this thread completed the last block
     if (err)
         atomicOr(&b.states[img].error, err);
 }

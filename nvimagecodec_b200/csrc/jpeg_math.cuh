@@ -17,6 +17,47 @@
 namespace b200jpeg {
 
 // ------------------------------------------------------------------------------------------------------------------
+// Coefficient records (device_types.h kRec*) of one block -> dense natural-order coefficients.  blk[] has kRecBlkSlots
+// entries and must be zeroed (entry 64 is a dump for out-of-range indices); c = index of the block's first record,
+// total = records of the image (the reader's hard stop), zzx = kRecZigzagNext.  blk[0] stays 0: the DC travels
+// separately.  A ZRL record is handled like a coefficient of value 0.  Returns true if a coefficient landed past
+// position 63 (corrupt stream).
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int kRecBlkSlots = 72;
+// zzx[n] = natural-order index of zigzag position n - 1 (jpeg_natural_order, ljt/jutils.c:59) for n <= 64, the dump slot after
+#define B2J_ZIGZAG_NEXT_INIT                                                                                                  \
+    {0, 0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, \
+        57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63, 64, 64, 64, 64, 64,  \
+        64, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64}
+constexpr int kRecZigzagNextSize = 81;
+
+B2J_HD bool records_to_block(const uint16_t* rec, uint32_t c, uint32_t total, const uint8_t* zzx, int16_t* blk)
+{
+    uint32_t z = 1, base = c & ~3u, skip = c & 3u;
+    bool done = false, bad = false;
+    while (!done && base < total) { // four records per 8-byte load (ranges are multiples of four records)
+        const uint2 v = *reinterpret_cast<const uint2*>(rec + base);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t r = ((i < 2 ? v.x : v.y) >> (16 * (i & 1))) & 0xFFFFu;
+            if (!done && uint32_t(i) >= skip) {
+                if ((r & 0xF7FFu) == 0) { // kRecEnd or kRecPad
+                    done = r == kRecEnd;
+                } else {
+                    z += (r >> 12) + 1u;               // position after this coefficient, <= 63 + 16
+                    bad = bad || z > 64u;
+                    blk[zzx[z]] = int16_t(int(r << 20) >> 20);
+                    done = z >= 64u;
+                }
+            }
+        }
+        skip = 0;
+        base += 4;
+    }
+    return bad;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
 // Dequantise + 8x8 inverse DCT ("islow") of one block: in[64] natural-order coefficients (in[0] ignored, the DC value is
 // passed separately), q[64] natural-order quant values, out = 8 rows of 8 samples packed little-endian in two uint32
 // each.  int32 arithmetic: exact for every stream an 8-bit encoder can produce (the reference's JLONG is wider only for

@@ -190,9 +190,23 @@ bool is_supported(const ParsedJpeg& p)
         if (!p.adobe && !p.jfif && p.comp_id[0] == 'R' && p.comp_id[1] == 'G' && p.comp_id[2] == 'B')
             return false;
     }
-    for (int c = 0; c < p.ncomp; ++c)
+    for (int c = 0; c < p.ncomp; ++c) {
         if (!p.quant_present[p.tq[c]] || !p.dc[p.td[c]].present || !p.ac[p.ta[c]].present)
             return false;
+        // 8-bit baseline coefficients: DC categories 0..11, AC sizes 0..10 (T.81 F.1.2); tables that list anything larger
+        // cannot come from an 8-bit encoder (the 12-bit value field of a coefficient record relies on this)
+        int ndc = 0, nac = 0;
+        for (int l = 1; l <= 16; ++l) {
+            ndc += p.dc[p.td[c]].bits[l];
+            nac += p.ac[p.ta[c]].bits[l];
+        }
+        for (int i = 0; i < ndc && i < 256; ++i)
+            if (p.dc[p.td[c]].vals[i] > 11)
+                return false;
+        for (int i = 0; i < nac && i < 256; ++i)
+            if ((p.ac[p.ta[c]].vals[i] & 15) > 10)
+                return false;
+    }
     if (size_t(p.width) * size_t(p.height) > (size_t(1) << 28))
         return false;
     return true;

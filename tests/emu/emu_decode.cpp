@@ -48,6 +48,8 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     std::vector<int16_t> coef(plan.coef_elems, 0x5A5A), dcv(plan.coef_elems / 64 + 64, 0x5A5A); // poisoned: the kernels must zero what they own
     std::vector<uint32_t> seg(plan.total_segs + 1, 0), rec(plan.total_subseq, 0), sabs(plan.total_subseq, 0);
     std::vector<unsigned long long> ex(plan.total_subseq, 0), en(plan.total_subseq, 0);
+    std::vector<uint16_t> records(plan.rec_elems + 64, 0x5A5A); // poisoned
+    std::vector<uint32_t> blkrec(plan.coef_elems / 64 + 64, 0xDEADBEEFu), nrec(plan.total_subseq, 0), recoff(plan.total_subseq, 0);
     std::vector<ImageState> states(m);
     std::memset(states.data(), 0, sizeof(ImageState) * m);
     BatchDev b;
@@ -95,6 +97,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         return env;
     };
     // sync_decode of decode_kernels.cu
+    std::vector<uint8_t> clean_sw; // filled after unstuffing
     auto sync_decode = [&](const HuffEnv& env, uint32_t t, uint32_t k, unsigned long long E, bool exact) {
         HuffState s;
         s.p = uint32_t(E);
@@ -102,15 +105,22 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         s.z = slot & 63u;
         s.blk = slot >> 6;
         s.nblk = 0;
+        s.nrec = 0;
         s.abs = exact;
         const uint32_t z_entry = s.z;
-        decode_span<false>(env, s, (k + 1u) * S, false, 0, nullptr, nullptr);
+        if (!clean_sw.empty()) { // the kernels' staged (byte-swapped) stream: exercises the fast synchronisation loop
+            HuffEnv env2 = env;
+            env2.words = reinterpret_cast<const uint32_t*>(clean_sw.data()) + (env.words - reinterpret_cast<const uint32_t*>(clean.data()));
+            decode_span<false, true>(env2, s, (k + 1u) * S, nullptr);
+        } else
+            decode_span<false>(env, s, (k + 1u) * S, nullptr);
         const unsigned long long X = pack_state(s.p, s.blk * 64u + s.z);
         const bool changed = X != ex[t];
         ex[t] = X;
         en[t] = E;
         const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
         rec[t] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
+        nrec[t] = s.nrec;
         return changed;
     };
     // ---- unstuffing + restart marker removal (what k_unstuff_count/scan/write compute) ----
@@ -147,6 +157,14 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
 
     // ---- synchronisation: round 0 (guessed state), round 1 (predecessor's exit), then work-list rounds ----
     (void)jacobi;
+    clean_sw.assign(clean.size() + 64, 0);
+    std::memcpy(clean_sw.data(), clean.data(), clean.size());
+    for (size_t w = 0; w + 4 <= clean_sw.size(); w += 4) {
+        uint32_t v;
+        std::memcpy(&v, clean_sw.data() + w, 4);
+        v = __builtin_bswap32(v);
+        std::memcpy(clean_sw.data() + w, &v, 4);
+    }
     std::vector<uint32_t> wl, wl_next;
     unsigned long long redone = 0;
     for (int round = 0; round < 2; ++round) {
@@ -163,6 +181,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                     if (idle) {
                         ex[t] = en[t] = pack_state(clean_bits, 0);
                         rec[t] = 0;
+                        nrec[t] = 0;
                         continue;
                     }
                     ex[t] = ~0ull;
@@ -213,57 +232,69 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     // ---- segmented scan of slot counts + consistency check (k_subseq_scan) ----
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
-        uint32_t A = 0x80000000u;
+        uint32_t A = 0x80000000u, R = 0;
         for (uint32_t k = 0; k < im.subseq_cta_count * kSubseqCta; ++k) {
             const uint32_t t = im.subseq_first + k;
+            recoff[t] = R;
+            R += (nrec[t] + kRecAlign - 1u) & ~(kRecAlign - 1u);
             if (k > 0 && en[t] != ex[t - 1] && uint64_t(k) * S < uint64_t(states[i].clean_len) * 8u)
                 states[i].error |= kErrNotConverged;
             const uint32_t r = rec[t];
             A = (r & 0x80000000u) ? r : A + r;
             sabs[t] = A;
         }
+        states[i].rec_total = R;
+        if (R > im.rec_cap)
+            states[i].error |= kErrRecords;
     }
-    // ---- write pass (k_huff_write): CTA by CTA, zero the owned range first ----
+    // ---- write pass (k_huff_write): every subsequence emits its coefficient records, in reverse order to show that
+    // the threads do not depend on each other ----
+    std::vector<uint8_t> clean_sw2 = clean_sw;
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
         std::vector<uint16_t> s_lut;
-        const HuffEnv env = make_env(i, true, s_lut);
+        HuffEnv env = make_env(i, true, s_lut);
+        env.words = reinterpret_cast<const uint32_t*>(clean_sw2.data()) + (env.words - reinterpret_cast<const uint32_t*>(clean.data()));
         const uint32_t clean_bits = states[i].clean_len * 8u;
-        int16_t* cf = coef.data() + im.coef_off;
-        int16_t* dcp = dcv.data() + im.coef_off / 64;
-        // CTAs in reverse order: a later CTA zeroing after an earlier CTA stored would lose data if ownership were wrong
-        for (int cta = int(im.subseq_cta_count) - 1; cta >= 0; --cta) {
-            const uint32_t k0 = uint32_t(cta) * kSubseqCta;
-            const uint32_t n_first = k0 == 0 ? 0u : (sabs[im.subseq_first + k0 - 1] & 0x7FFFFFFFu);
-            const bool last_cta = uint32_t(cta) + 1 == im.subseq_cta_count;
-            const uint32_t n_next = sabs[im.subseq_first + k0 + kSubseqCta - 1] & 0x7FFFFFFFu;
-            const uint32_t first_block = (n_first + 63u) >> 6;
-            uint32_t end_block = last_cta ? im.total_blocks : (n_next + 63u) >> 6;
-            if (end_block > im.total_blocks) end_block = im.total_blocks;
-            for (uint32_t bb = first_block; bb < end_block; ++bb)
-                std::memset(cf + uint64_t(bb) * 64, 0, 128);
-            for (uint32_t ti = 0; ti < uint32_t(kSubseqCta); ++ti) {
-                const uint32_t k = k0 + ti, t = im.subseq_first + k;
-                if (uint64_t(k) * S >= uint64_t(clean_bits)) continue;
-                HuffState s;
-                if (k == 0) {
-                    s.p = 0; s.z = 0; s.blk = 0; s.nblk = 0;
-                } else {
-                    const unsigned long long E = ex[t - 1];
-                    const uint32_t slot = uint32_t(E >> 32);
-                    s.p = uint32_t(E); s.z = slot & 63u; s.blk = slot >> 6;
-                    s.nblk = (sabs[t - 1] & 0x7FFFFFFFu) >> 6;
-                }
-                s.abs = true;
-                const bool extend = (ti == uint32_t(kSubseqCta) - 1) || (uint64_t(k + 1) * S >= uint64_t(clean_bits));
-                const uint32_t end = (k + 1u) * S;
-                uint32_t err = 0;
-                if (!(extend && s.p >= end && s.z == 0))
-                    err = decode_span<true>(env, s, end, extend, first_block, cf, dcp);
-                if (s.nblk == im.total_blocks && s.z == 0 && extend) states[i].done_blocks = s.nblk;
-                states[i].error |= err;
+        if (states[i].error & kErrRecords)
+            continue;
+        for (int64_t k64 = int64_t(im.subseq_cta_count) * kSubseqCta - 1; k64 >= 0; --k64) {
+            const uint32_t k = uint32_t(k64), t = im.subseq_first + k;
+            if (uint64_t(k) * S >= uint64_t(clean_bits)) continue;
+            HuffState s;
+            if (k == 0) {
+                s.p = 0; s.z = 0; s.blk = 0; s.nblk = 0;
+            } else {
+                const unsigned long long E = ex[t - 1];
+                const uint32_t slot = uint32_t(E >> 32);
+                s.p = uint32_t(E); s.z = slot & 63u; s.blk = slot >> 6;
+                s.nblk = (sabs[t - 1] & 0x7FFFFFFFu) >> 6;
             }
+            s.abs = true;
+            s.nrec = 0;
+            RecOut out;
+            out.rec = records.data() + im.rec_off;
+            out.blk_rec = blkrec.data() + im.coef_off / 64;
+            out.dc = dcv.data() + im.coef_off / 64;
+            out.cursor = recoff[t];
+            out.limit = out.cursor + ((nrec[t] + kRecAlign - 1u) & ~(kRecAlign - 1u));
+            out.qlo = out.qhi = 0;
+            const uint32_t nblk_in = s.nblk;
+            uint32_t err = decode_span<true, true>(env, s, (k + 1u) * S, &out);
+            if (out.cursor > out.limit) err |= kErrRecords;
+            out.finish();
+            if (s.nblk == im.total_blocks && s.z == 0 && nblk_in < im.total_blocks) states[i].done_blocks = s.nblk;
+            states[i].error |= err;
         }
+        // dense coefficients (what the IDCT kernel rebuilds in shared memory; also the debug tap)
+        static const uint8_t zzx[kRecZigzagNextSize] = B2J_ZIGZAG_NEXT_INIT;
+        if (states[i].done_blocks == im.total_blocks)
+            for (uint32_t bb = 0; bb < im.total_blocks; ++bb) {
+                int16_t blk[kRecBlkSlots] = {};
+                if (records_to_block(records.data() + im.rec_off, blkrec[im.coef_off / 64 + bb], states[i].rec_total, zzx, blk))
+                    states[i].error |= kErrBadCode;
+                std::memcpy(coef.data() + im.coef_off + uint64_t(bb) * 64, blk, 128);
+            }
     }
     // ---- DC prediction (k_dc_scan) ----
     for (int i = 0; i < m; ++i) {

@@ -25,7 +25,7 @@ def refdec():
 
 def gpu_decode(torch, datas, fmt=4, options=":fancy_upsampling=1", pad_stride=0, want_decoder=False):
     from nvimagecodec_b200.decoder import Decoder
-    dec = Decoder(0, options=options)
+    dec = Decoder(0, options=options + " :dump_coef=1")  # keep dense coefficients for the debug tap
     outs, ptrs, strides = [], [], []
     for d in datas:
         i = port.info(d)
