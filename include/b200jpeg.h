@@ -123,12 +123,13 @@ B200JPEG_API int b200jpeg_decode_run(b200jpegDecoder_t decoder, void* user_strea
 
 /* Counters of the last run: [0] kernels launched, [1] Huffman sync rounds (2 full rounds + work-list rounds), [2] entropy-coded
  * bytes, [3] decoded blocks, [4] subsequences, [5] device scratch bytes, [6] subsequences re-decoded in the work-list rounds,
- * [7] output bytes */
-B200JPEG_API int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats8);
+ * [7] output bytes, [8] bytes of coefficient records the Huffman write pass produced, [9..15] reserved (0) */
+B200JPEG_API int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats16);
 
 /* Per-stage device times (ms) of the last run, measured with CUDA events on the decoder's own stream; needs the option
- * "profile=1".  Stages: 0 unstuff (3 kernels + memsets), 1 Huffman sync rounds, 2 slot scan + Huffman write,
- * 3 DC prediction, 4 dequant+IDCT, 5 upsample+colour.  Returns the number of stages or -1. */
+ * "profile=1" (single group).  Stages: 0 unstuff (3 kernels + memsets), 1 Huffman sync rounds 0 and 1 (2 launches of
+ * k_huff_sync), 2 work-list sync rounds (k_huff_sync_tail), 3 slot/record scan + Huffman write (k_subseq_scan, k_huff_write),
+ * 4 DC prediction, 5 records -> dequant + IDCT, 6 upsample + colour.  Returns the number of stages or -1. */
 B200JPEG_API int b200jpeg_decoder_get_stage_times(b200jpegDecoder_t decoder, float* ms, int n);
 
 /* Debug/verification taps on the last prepared+run batch (device -> host copies of intermediates):

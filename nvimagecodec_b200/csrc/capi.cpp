@@ -140,11 +140,11 @@ int b200jpeg_decode_batch(b200jpegDecoder_t decoder, int n, const uint8_t* const
     }
 }
 
-int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats8)
+int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats16)
 {
-    if (!decoder || !stats8)
+    if (!decoder || !stats16)
         return B200JPEG_STATUS_INVALID_PARAMETER;
-    decoder->impl->get_stats(stats8);
+    decoder->impl->get_stats(stats16);
     return B200JPEG_STATUS_SUCCESS;
 }
 

@@ -13,8 +13,10 @@ struct LaunchDims
 
 // each returns the number of kernels it launched
 int launch_unstuff(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
-// rounds 0 and 1 over every subsequence, then the cooperative tail kernel (grid size from tail_grid_size); -1 on launch failure
-int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid);
+// rounds 0 and 1 over every subsequence
+int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
+// the cooperative work-list kernel (grid size from huff_configure); -1 on launch failure
+int launch_huff_tail(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid);
 // set the dynamic shared memory limits for b.lut_slots / b.stream_words and size the cooperative tail grid; -1 on error
 int huff_configure(const BatchDev& b, int device, int* tail_grid);
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
@@ -22,7 +24,7 @@ int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_color(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 
-enum Stage { kStageUnstuff = 0, kStageSync, kStageWrite, kStageDc, kStageIdct, kStageColor, kNumStages };
+enum Stage { kStageUnstuff = 0, kStageSync, kStageTail, kStageWrite, kStageDc, kStageIdct, kStageColor, kNumStages };
 
 
 } // namespace b200jpeg

@@ -4,6 +4,7 @@
 // plugin (extensions/nvjpeg/hw_decoder.cpp:492-680): gather bitstreams, one batched launch sequence, sync, report.
 #include "decoder.h"
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -64,6 +65,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
             o.copy_threads = std::max(1, std::atoi(value.c_str()));
         else if (name == "groups")
             o.groups = std::max(1, std::atoi(value.c_str()));
+        else if (name == "groups_host")
+            o.groups_host = std::max(0, std::atoi(value.c_str()));
         else if (name == "stage_stream")
             o.stage_stream = std::atoi(value.c_str()) != 0;
         else if (name == "dump_coef")
@@ -257,7 +260,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     const size_t off_quant = align_up(off_huff + sizeof(DevHuffTable) * plan_.huff.size(), 256);
     const size_t off_m0 = align_up(off_quant + plan_.quant.size() * sizeof(uint16_t), 256);
     const size_t map_bytes = align_up(sizeof(uint32_t) * (m + 1), 256);
-    const size_t meta_bytes = off_m0 + 4 * map_bytes;
+    const size_t off_cimg = off_m0 + 4 * map_bytes;
+    const size_t meta_bytes = off_cimg + align_up(sizeof(uint32_t) * (plan_.total_subseq / kSubseqCta + 1), 256);
     if ((rc = ensure(d_meta_, meta_bytes)) || (rc = ensure_pinned(h_meta_, meta_bytes)) ||
         (rc = ensure_pinned(h_raw_, plan_.raw_bytes)) ||
         (rc = ensure_pinned(h_states_, sizeof(ImageState) * m + sizeof(SyncCounters) * kMaxGroups)))
@@ -270,6 +274,11 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     std::memcpy(hm + off_m0 + 1 * map_bytes, plan_.map_subseq.data(), sizeof(uint32_t) * (m + 1));
     std::memcpy(hm + off_m0 + 2 * map_bytes, plan_.map_idct.data(), sizeof(uint32_t) * (m + 1));
     std::memcpy(hm + off_m0 + 3 * map_bytes, plan_.map_color.data(), sizeof(uint32_t) * (m + 1));
+    for (int i = 0; i < m; ++i) { // image of every subsequence CTA (the work-list rounds look items up by subsequence index)
+        uint32_t* cimg = reinterpret_cast<uint32_t*>(hm + off_cimg) + plan_.images[i].subseq_first / kSubseqCta;
+        for (uint32_t c = 0; c < plan_.images[i].subseq_cta_count; ++c)
+            cimg[c] = uint32_t(i);
+    }
 
     B2J_CUDA(cudaMemcpyAsync(d_meta_.p, h_meta_.p, meta_bytes, cudaMemcpyHostToDevice, streams_[0]));
     B2J_CUDA(cudaEventRecord(ev_meta_, streams_[0]));
@@ -302,6 +311,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.planes = static_cast<uint8_t*>(d_planes_.p);
     dev_.cta_map_unstuff = reinterpret_cast<const uint32_t*>(dm + off_m0 + 0 * map_bytes);
     dev_.cta_map_subseq = reinterpret_cast<const uint32_t*>(dm + off_m0 + 1 * map_bytes);
+    dev_.subseq_cta_img = reinterpret_cast<const uint32_t*>(dm + off_cimg);
+    dev_.image_base = 0;
     dev_.cta_map_idct = reinterpret_cast<const uint32_t*>(dm + off_m0 + 2 * map_bytes);
     dev_.cta_map_color = reinterpret_cast<const uint32_t*>(dm + off_m0 + 3 * map_bytes);
     dev_.subseq_bits = plan_.subseq_bits;
@@ -323,16 +334,26 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     }
     dev_.total_subseq = plan_.total_subseq;
     // ---- groups of consecutive images, balanced by entropy-coded bytes; each group runs on its own stream ----
+    // With host outputs the device->host copies (9x the compressed bytes) bound the call: the first group is small so that
+    // the copy engine starts early, and every later group is twice as large so that it is ready before the copies of its
+    // predecessors drain.  With device outputs the groups are equal.
     int G = opt_.profile ? 1 : std::max(1, std::min(opt_.groups, kMaxGroups));
+    if (!opt_.profile && !host_outs_.empty() && opt_.groups_host > 0)
+        G = std::min(opt_.groups_host, kMaxGroups);
     G = std::min(G, m);
+    const bool growing = !host_outs_.empty() && G > 1;
+    uint64_t weight_total = 0, weight_sum = 0;
+    for (int g = 0; g < G; ++g)
+        weight_total += growing ? (uint64_t(1) << g) + (g == G - 1 ? 1 : 0) : 1;
     int per_group = std::max(1, std::min(tail_capacity_ / G, sm_count_));
     int first = 0;
     for (int g = 0; g < G; ++g) {
         int last = first;
+        weight_sum += growing ? (uint64_t(1) << g) : 1;
         if (g == G - 1) {
             last = m;
         } else {
-            const uint64_t target = plan_.raw_bytes * uint64_t(g + 1) / uint64_t(G);
+            const uint64_t target = plan_.raw_bytes * weight_sum / weight_total;
             while (last < m - (G - 1 - g) && (last == first || plan_.images[last].raw_off + plan_.images[last].raw_len / 2 <= target))
                 ++last;
         }
@@ -346,6 +367,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
         gr.dev.num_images = gr.count;
         gr.dev.cta_map_unstuff = dev_.cta_map_unstuff + first;
         gr.dev.cta_map_subseq = dev_.cta_map_subseq + first;
+        gr.dev.image_base = first;
         gr.dev.cta_map_idct = dev_.cta_map_idct + first;
         gr.dev.cta_map_color = dev_.cta_map_color + first;
         gr.dev.base_unstuff = plan_.map_unstuff[first];
@@ -424,6 +446,8 @@ int Decoder::launch_group(int g)
         if (prof)
             cudaEventRecord(ev_stage_[i], st);
     };
+    if (trace_)
+        cudaEventRecord(ev_trace_[1 + 3 * g], st);
     if (g != 0)
         B2J_CUDA(cudaStreamWaitEvent(st, ev_meta_, 0)); // descriptors / tables went up on stream 0
     B2J_CUDA(cudaStreamWaitEvent(st, ev_in_, 0));       // and whatever the caller had in flight on the output buffers
@@ -432,7 +456,9 @@ int Decoder::launch_group(int g)
     B2J_CUDA(cudaMemsetAsync(gr.dev.sync, 0, sizeof(SyncCounters), st));
     stat_launches_ += launch_unstuff(gr.dev, gr.dims, st);
     mark(kStageSync);
-    const int ns = launch_huff_sync(gr.dev, gr.dims, st, gr.tail_grid);
+    stat_launches_ += launch_huff_sync(gr.dev, gr.dims, st);
+    mark(kStageTail);
+    const int ns = launch_huff_tail(gr.dev, gr.dims, st, gr.tail_grid);
     if (ns < 0) {
         std::fprintf(stderr, "b200jpeg: cooperative launch failed: %s\n", cudaGetErrorString(cudaGetLastError()));
         return B200JPEG_STATUS_CUDA_ERROR;
@@ -449,6 +475,8 @@ int Decoder::launch_group(int g)
     mark(kNumStages);
     stage_valid_ = prof;
     B2J_CUDA(cudaGetLastError());
+    if (trace_)
+        cudaEventRecord(ev_trace_[2 + 3 * g], st);
     const int m = int(plan_.images.size());
     B2J_CUDA(cudaMemcpyAsync(static_cast<ImageState*>(h_states_.p) + m0, static_cast<ImageState*>(d_states_.p) + m0, sizeof(ImageState) * mc,
         cudaMemcpyDeviceToHost, st));
@@ -457,9 +485,14 @@ int Decoder::launch_group(int g)
     for (int idx : gr.host_outs) { // host-memory outputs: copy back
         const HostOutput& ho = host_outs_[idx];
         const size_t pitch = align_up(ho.row_bytes, 16);
-        B2J_CUDA(cudaMemcpy2DAsync(ho.host, size_t(ho.host_stride), static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch, ho.row_bytes,
-            ho.rows, cudaMemcpyDeviceToHost, st));
+        if (size_t(ho.host_stride) == pitch) // contiguous on both sides: one linear copy runs at the full PCIe rate
+            B2J_CUDA(cudaMemcpyAsync(ho.host, static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch * ho.rows, cudaMemcpyDeviceToHost, st));
+        else
+            B2J_CUDA(cudaMemcpy2DAsync(ho.host, size_t(ho.host_stride), static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch, ho.row_bytes,
+                ho.rows, cudaMemcpyDeviceToHost, st));
     }
+    if (trace_)
+        cudaEventRecord(ev_trace_[3 + 3 * g], st);
     return 0;
 }
 
@@ -473,6 +506,8 @@ int Decoder::begin_run(cudaStream_t user_stream, int32_t* statuses)
     stat_launches_ = 0;
     if (!groups_.empty())
         B2J_CUDA(cudaEventRecord(ev_in_, user_stream));
+    if (trace_)
+        cudaEventRecord(ev_trace_[0], streams_[0]);
     return 0;
 }
 
@@ -491,10 +526,12 @@ int Decoder::finish(int32_t* statuses)
         stat_rounds_ = std::max<uint64_t>(stat_rounds_, 2 + sc[g].rounds);
         stat_redone_ += sc[g].redone;
     }
+    stat_record_bytes_ = 0;
     for (int i = 0; i < m; ++i) {
         const int bi = planned_to_batch_[i];
         if (hs[i].error || hs[i].done_blocks != plan_.images[i].total_blocks)
             statuses[bi] = B200JPEG_STATUS_CORRUPT_STREAM;
+        stat_record_bytes_ += uint64_t(hs[i].rec_total) * sizeof(uint16_t);
     }
     return B200JPEG_STATUS_SUCCESS;
 }
@@ -513,16 +550,48 @@ int Decoder::run(cudaStream_t user_stream, int32_t* statuses)
 // whole decode, pipelined over the groups: while group g is on the GPU the host stages group g+1
 int Decoder::decode(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, cudaStream_t user_stream, int32_t* statuses)
 {
+    static const bool trace = std::getenv("B200JPEG_TRACE") != nullptr; // developer aid: host-side timeline on stderr
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = trace ? now() : 0;
+    if (trace && !ev_trace_[0])
+        for (cudaEvent_t& e : ev_trace_)
+            cudaEventCreate(&e);
+    trace_ = trace;
     int rc = plan_batch(n, data, sizes, outs, statuses);
     if (rc)
         return rc;
     if ((rc = begin_run(user_stream, statuses)))
         return rc;
+    const double t1 = trace ? now() : 0;
+    double t_stage = 0, t_launch = 0;
     for (size_t g = 0; g < groups_.size(); ++g) {
-        if ((rc = stage_group(int(g))) || (rc = launch_group(int(g))))
+        const double a = trace ? now() : 0;
+        if ((rc = stage_group(int(g))))
             return rc;
+        const double b = trace ? now() : 0;
+        if ((rc = launch_group(int(g))))
+            return rc;
+        if (trace) {
+            t_stage += b - a;
+            t_launch += now() - b;
+        }
     }
-    return finish(statuses);
+    const double t2 = trace ? now() : 0;
+    rc = finish(statuses);
+    if (trace) {
+        for (size_t g = 0; g < groups_.size(); ++g) {
+            float a = 0, b = 0, c = 0;
+            cudaEventElapsedTime(&a, ev_trace_[0], ev_trace_[1 + 3 * g]);
+            cudaEventElapsedTime(&b, ev_trace_[0], ev_trace_[2 + 3 * g]);
+            cudaEventElapsedTime(&c, ev_trace_[0], ev_trace_[3 + 3 * g]);
+            std::fprintf(stderr, "b200jpeg trace: group %zu (%d images): input on device %.3f, kernels done %.3f, outputs on host %.3f ms\n", g,
+                groups_[g].count, a, b, c);
+        }
+    }
+    if (trace)
+        std::fprintf(stderr, "b200jpeg trace: plan %.3f ms, stage %.3f ms, launch %.3f ms, wait %.3f ms (%zu groups)\n", t1 - t0, t_stage,
+            t_launch, now() - t2, groups_.size());
+    return rc;
 }
 
 void Decoder::get_stats(uint64_t* s) const
@@ -537,6 +606,9 @@ void Decoder::get_stats(uint64_t* s) const
     s[5] = scratch_bytes_;
     s[6] = stat_redone_;
     s[7] = plan_.out_bytes;
+    s[8] = stat_record_bytes_;
+    for (int i = 9; i < 16; ++i)
+        s[i] = 0;
 }
 
 int Decoder::get_stage_times(float* ms, int n)

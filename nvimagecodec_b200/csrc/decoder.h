@@ -14,6 +14,7 @@ struct DecoderOptions
 {
     bool fancy_upsampling = true; // reference default (libjpeg_turbo_decoder.cpp:250-276)
     int subseq_bytes = 128;
+    int groups_host = 5;  // groups (of doubling size) when outputs go to host memory; 0 = use `groups`
     int copy_threads = 4;
     int groups = 4;           // the batch is cut into this many groups of images that run on separate streams (pipelining)
     bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)
@@ -90,6 +91,8 @@ class Decoder
     DecoderOptions opt_;
     cudaStream_t streams_[kMaxGroups] = {};
     cudaEvent_t ev_in_ = nullptr, ev_meta_ = nullptr;
+    bool trace_ = false;
+    cudaEvent_t ev_trace_[1 + 3 * kMaxGroups] = {}; // B200JPEG_TRACE: start, then per group: staged, kernels done, copied back
     cudaEvent_t ev_stage_[kNumStages + 1] = {};
     bool stage_valid_ = false;
     bool ready_ = false;
@@ -110,7 +113,7 @@ class Decoder
     const uint8_t* const* data_ = nullptr; // caller's bitstreams during decode()/prepare()
     size_t scratch_bytes_ = 0;
 
-    uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_redone_ = 0;
+    uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_record_bytes_ = 0, stat_redone_ = 0;
     int tail_capacity_ = 0, sm_count_ = 0, cfg_lut_slots_ = -1, cfg_stream_words_ = -1;
 };
 

@@ -182,6 +182,8 @@ struct BatchDev // pointers handed to every kernel
     uint8_t* planes;
     const uint32_t* cta_map_unstuff; // prefix arrays: first CTA of each image (+ total at [num_images])
     const uint32_t* cta_map_subseq;
+    const uint32_t* subseq_cta_img;  // batch image index of every subsequence CTA (indexed by global subsequence / kSubseqCta)
+    int32_t image_base;              // batch index of images[0] (a launch may cover a group of consecutive images)
     const uint32_t* cta_map_idct;
     const uint32_t* cta_map_color;
     // a launch may cover only a group of consecutive images: images / states / the CTA maps then point at the group's first

@@ -167,7 +167,10 @@ B2J_HD uint32_t make_record(uint32_t t, uint32_t sz, uint32_t zadv, bool is_ac, 
 // WRITE = true : s.abs must hold.  Every symbol becomes a record in `out` (AC: coefficient / ZRL / end of block, DC:
 //                padding); a DC symbol also stores the DC difference of its block and the index of the block's first
 //                coefficient record.  Returns error flags.
-template <bool WRITE, bool PRESWAPPED = false>
+// DIRECT selects the inner loop used well inside a segment: true = both stream words fetched from shared memory per
+// symbol (fewest instructions: the throughput kernels, whose warps hide the extra latency), false = sliding window in
+// registers (shortest dependency chain: the latency-bound work-list rounds).
+template <bool WRITE, bool PRESWAPPED = false, bool DIRECT = true>
 B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecOut* out)
 {
     if (end > env.clean_bits)
@@ -203,7 +206,7 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
         const uint32_t seg_end = last ? env.total_blocks : uint32_t(g + 1) * env.seg_blocks; // used when s.abs
         TabSel ts = env.tabsel[blk];
         bool cross = false;
-        if (PRESWAPPED && p < lim && lim + 32u <= B && (!WRITE || nblk + (lim - p) / 2u + 16u < seg_end)) {
+        if (PRESWAPPED && DIRECT && p < lim && lim + 32u <= B && (!WRITE || nblk + (lim - p) / 2u + 16u < seg_end)) {
             // Well inside a segment (the common case): no symbol can run over the segment end (and, writing, the blocks
             // of the segment cannot run out: a block takes at least two bits), so the loop carries nothing but the
             // decoder state.  Both stream words are fetched per symbol (shared memory): cheaper than keeping a sliding

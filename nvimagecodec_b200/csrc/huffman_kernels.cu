@@ -101,7 +101,7 @@ __device__ __forceinline__ HuffEnv make_env(const BatchDev& b, const ImageDesc& 
 
 // Decode subsequence k of an image from entry state E in synchronisation mode and publish the result.
 // Returns true if the exit state differs from the one recorded before.
-template <bool PRESWAPPED>
+template <bool PRESWAPPED, bool DIRECT = true>
 __device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& env, uint32_t t, uint32_t k, unsigned long long E, bool exact)
 {
     HuffState s;
@@ -113,7 +113,7 @@ __device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& en
     s.nrec = 0;
     s.abs = exact;
     const uint32_t z_entry = s.z;
-    decode_span<false, PRESWAPPED>(env, s, (k + 1u) * uint32_t(b.subseq_bits), nullptr);
+    decode_span<false, PRESWAPPED, DIRECT>(env, s, (k + 1u) * uint32_t(b.subseq_bits), nullptr);
     const unsigned long long X = pack_state(s.p, s.blk * 64u + s.z);
     const bool changed = (X != __ldcg(b.sub_exit + t));
     b.sub_exit[t] = X;
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b)
         uint32_t* out = b.worklist[(r + 1) & 1];
         for (uint32_t i = tid; i < n; i += nthreads) {
             const uint32_t t = __ldcg(in + i);
-            const int img = find_image_h(b.cta_map_subseq, b.num_images, t / kSubseqCta);
+            const int img = int(__ldg(b.subseq_cta_img + t / kSubseqCta)) - b.image_base;
             const ImageDesc& im = b.images[img];
             const uint32_t k = t - im.subseq_first;
             const unsigned long long E = __ldcg(b.sub_exit + t - 1); // written by other SMs in earlier rounds: bypass L1
@@ -227,12 +227,30 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b)
             }
             bool changed;
             if (W) {
-                const uint32_t first = k * spw, max_words = (im.raw_len + 16u) >> 2;
-                for (uint32_t j = 0; j < W; ++j)
-                    my_words[j] = first + j < max_words ? __byte_perm(gwords[first + j], 0, 0x0123) : 0u;
+                // the subsequence starts on a 16-byte boundary of the image's stream (which is readable 16 bytes past its
+                // end): fetch it with independent 16-byte loads first, then byte-swap into the thread's staging words
+                const uint32_t first = k * spw;
+                const uint4* src = reinterpret_cast<const uint4*>(gwords + first);
+                constexpr int kMaxVec = 17; // (256 B / 4 + 3 | 1) words
+                uint4 v[kMaxVec];
+                const int nvec = int(W + 3u) >> 2;
+                const int avail = int((((im.raw_len + 16u) >> 2) - first + 3u) >> 2); // 16-byte groups inside the stream buffer
+#pragma unroll
+                for (int j = 0; j < kMaxVec; ++j)
+                    if (j < nvec)
+                        v[j] = j < avail ? __ldcg(src + j) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+                for (int j = 0; j < kMaxVec; ++j)
+                    if (j < nvec) {
+                        const uint32_t w4[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            if (uint32_t(4 * j + q) < W)
+                                my_words[4 * j + q] = __byte_perm(w4[q], 0, 0x0123);
+                    }
                 const HuffEnv env = make_env(b, im, clean_len, my_words - first, lut, tabsel,
                     uint32_t(__cvta_generic_to_shared(my_words)) - first * 4u);
-                changed = sync_decode<true>(b, env, t, k, E, false);
+                changed = sync_decode<true, true>(b, env, t, k, E, false);
             } else {
                 const HuffEnv env = make_env(b, im, clean_len, gwords, lut, tabsel);
                 changed = sync_decode<false>(b, env, t, k, E, false);
@@ -401,17 +419,22 @@ int huff_configure(const BatchDev& b, int device, int* tail_grid)
     return 0;
 }
 
-int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid)
+int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
 {
     const size_t ms = main_smem_bytes(b);
     k_huff_sync<<<d.subseq_ctas, kSubseqCta, ms, st>>>(b, 0);
     k_huff_sync<<<d.subseq_ctas, kSubseqCta, ms, st>>>(b, 1);
+    return 2;
+}
+
+int launch_huff_tail(const BatchDev& b, const LaunchDims&, cudaStream_t st, int tail_grid)
+{
     BatchDev bb = b;
     void* args[] = {&bb};
     if (cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_huff_sync_tail), dim3(tail_grid), dim3(kSubseqCta), args, tail_smem_bytes(b), st) !=
         cudaSuccess)
         return -1;
-    return 3;
+    return 1;
 }
 
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st)

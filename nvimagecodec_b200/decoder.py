@@ -131,17 +131,19 @@ class Decoder:
         return self.last_statuses
 
     def stats(self):
-        s = (C.c_uint64 * 8)()
+        s = (C.c_uint64 * 16)()
         _capi.lib().b200jpeg_decoder_get_stats(self._h, s)
         keys = ("launches", "sync_rounds", "scan_bytes", "blocks", "subsequences", "scratch_bytes", "tail_redone", "out_bytes")
-        return dict(zip(keys, [int(v) for v in s]))
+        d = dict(zip(keys, [int(v) for v in s[:8]]))
+        d["record_bytes"] = int(s[8])
+        return d
 
-    STAGES = ("unstuff", "huff_sync", "huff_write", "dc_scan", "idct", "color")
+    STAGES = ("unstuff", "huff_sync", "huff_tail", "huff_write", "dc_scan", "idct", "color")
 
     def stage_times(self):
         """per-stage device ms of the last run (needs option profile=1) or None"""
-        ms = (C.c_float * 6)()
-        if _capi.lib().b200jpeg_decoder_get_stage_times(self._h, ms, 6) < 0:
+        ms = (C.c_float * 7)()
+        if _capi.lib().b200jpeg_decoder_get_stage_times(self._h, ms, 7) < 0:
             return None
         return dict(zip(self.STAGES, [float(v) for v in ms]))
 
