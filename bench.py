@@ -88,6 +88,31 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons}
 
 
+def pin_to_gpu_numa_node(index):
+    """one host thread set per device: run this rank on the cores next to its GPU so that pinned staging
+    buffers are allocated on, and copied from, the local memory node.  Returns a description or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]
+        base = "/sys/bus/pci/devices/" + bus
+        node = int(open(base + "/numa_node").read())
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return {"numa_node": node, "cpus": len(cpus)}
+    except Exception:
+        pass
+    return None
+
+
 def hbm_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -134,6 +159,145 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
+def _synth_one(seed):
+    from nvimagecodec_b200.corpus import synth_image
+    return synth_image(seed, W, H)
+
+
+def run_encode(args, rank, world, local_rank):
+    """BASELINE.json configs[4]: batched JPEG encode, 128x 1920x1080 RGB -> 4:2:0 q90 baseline, bitstream-exact vs
+    libjpeg-turbo.  value: device-resident pixels -> host JPEG bytes; e2e: pinned host pixels -> host JPEG bytes."""
+    from concurrent.futures import ProcessPoolExecutor, ThreadPoolExecutor
+    import multiprocessing as mp
+    n = args.batch
+    distinct = min(n, 16)
+    with ProcessPoolExecutor(max_workers=max(1, min(16, os.cpu_count() or 1)), mp_context=mp.get_context("spawn")) as ex:
+        base = list(ex.map(_synth_one, [2000 + i for i in range(distinct)]))
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the b200jpeg path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
+    from nvimagecodec_b200 import _capi
+    from nvimagecodec_b200.encoder import Encoder
+    from oracle import port, ref
+    host = [torch.from_numpy(base[i % distinct]).pin_memory() for i in range(n)]
+    devt = [h.to(dev) for h in host]
+    enc = Encoder(local_rank, options=":profile=1")
+    cap = W * H * 3 // 2 + 4096
+    caps = [cap] * n
+    out_host = torch.empty(n * cap, dtype=torch.uint8).pin_memory()  # page-locked destination of the JPEG files
+    out_ptrs = [out_host.data_ptr() + i * cap for i in range(n)]
+
+    def inputs(tensors, on_host):
+        return [dict(buffer=t.data_ptr(), row_stride=W * 3, width=W, height=H, format=_capi.FMT_I_RGB, on_host=int(on_host),
+                     subsampling=_capi.CSS_420, quality=QUALITY, restart_interval=0) for t in tensors]
+
+    # ---- parity gate + CPU baseline: libjpeg-turbo jpeg_compress (the reference tree's encoder) on the host cores ----
+    torch.cuda.synchronize(dev)
+    got, st = enc.encode_raw(inputs(devt, False), caps)
+    assert all(x == 0 for x in st), st
+    cpu_baseline = None
+    if rank == 0:
+        lj = (lambda im: ref.ljt_encode(im, QUALITY, (2, 2))) if ref.available() else (lambda im: port.encode(im, QUALITY, (2, 2)))
+        kind = "reference" if ref.available() else "port"
+        cores = os.cpu_count() or 1
+        for i in range(distinct):
+            if got[i] != lj(base[i]):
+                raise SystemExit("PARITY FAILURE: encoded image %d differs from libjpeg-turbo" % i)
+        assert all(got[i] == got[i % distinct] for i in range(n))
+        if not args.skip_cpu_baseline:
+            sample = [base[i % distinct] for i in range(min(n, max(16, 2 * cores)))]
+            with ThreadPoolExecutor(max_workers=cores) as tp:  # ctypes releases the GIL: one jpeg_compress per host thread
+                list(tp.map(lj, sample[:cores]))
+                t0 = time.perf_counter()
+                list(tp.map(lj, sample))
+                dt = time.perf_counter() - t0
+            cpu_baseline = {"value": len(sample) * W * H / 1e6 / dt, "unit": "Mpixel/s", "cores": cores, "kind": kind,
+                            "images_per_s": len(sample) / dt,
+                            "sample": "%d of the %d images, libjpeg-turbo 3.0.3 jpeg_compress (WITH_SIMD=0) on %d host threads" % (len(sample), n, cores)}
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(inp):
+        for _ in range(max(3, args.warmup)):
+            enc.encode_into(inp, out_ptrs, caps)
+        barrier()
+        stage = [0.0, 0.0, 0.0]
+        launches = 0
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            sizes, st = enc.encode_into(inp, out_ptrs, caps)
+            es = enc.stats()
+            launches += es["launches"]
+            stage = [stage[0] + es["dct_us"], stage[1] + es["entropy_us"], stage[2] + es["stuff_us"]]
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        assert all(x == 0 for x in st)
+        if rank == 0:  # the timed path wrote the same files as the parity-checked call
+            for i in (0, n - 1):
+                assert out_host[i * cap:i * cap + sizes[i]].numpy().tobytes() == got[i]
+        return dt, [v / args.steps / 1e3 for v in stage], launches, enc.stats()
+
+    with ClockSampler(local_rank) as clocks:
+        dt_dev, stage_ms, launches, es = timed(inputs(devt, False))
+    dt_host, _, _, _ = timed(inputs(host, True))
+    t = torch.tensor([dt_dev, dt_host], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dt_dev, dt_host = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    mpix = n * W * H / 1e6 * world
+    peak, peak_kind = hbm_peak()
+    blocks, in_b, out_b = es["blocks"], es["in_bytes"], es["out_bytes"]
+    # k_enc_dct: reads the pixels once, writes 128 B of zigzag coefficients + 4 B (DC, AC length) per block
+    alg_dct = in_b + 132 * blocks
+    line = {
+        "metric": "encoded_mpixel_per_s", "value": mpix / (dt_dev / args.steps), "unit": "Mpixel/s", "images_per_s": n * world / (dt_dev / args.steps),
+        "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": 1e3 * dt_dev / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C5: %dx 1920x1080 interleaved RGB u8 -> 4:2:0 q90 baseline JPEG (standard Huffman tables, %.0f KB avg), per GPU"
+                               % (n, out_b / n / 1e3),
+                   "l2": "working set per step %.0f MB (pixels+coefficients) > 126 MB L2, no explicit flush" % ((in_b + 128 * blocks) / 1e6),
+                   "parity": "byte-exact vs libjpeg-turbo jpeg_compress on all distinct images before timing",
+                   "timing": "wall clock around b200jpeg_encode_batch (synchronous; it reads the stream lengths back mid-way), device-resident "
+                             "pixels in, JPEG files in host memory out"},
+        "clocks": clocks.summary(),
+        "e2e": {"value": mpix / (dt_host / args.steps), "unit": "Mpixel/s", "images_per_s": n * world / (dt_host / args.steps),
+                "ms_per_step": 1e3 * dt_host / args.steps, "h2d_bytes_per_step": int(in_b), "d2h_bytes_per_step": int(out_b)},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "k_enc_dct", "achieved": alg_dct / (stage_ms[0] * 1e-3) / 1e9 if stage_ms[0] else None, "peak": peak,
+                     "peak_kind": peak_kind, "unit": "GB/s", "frac": alg_dct / (stage_ms[0] * 1e-3) / 1e9 / peak if stage_ms[0] else None,
+                     "traffic": None, "algorithmic_bytes": alg_dct, "ms": stage_ms[0],
+                     "stage_ms": {"dct (incl. H2D of descriptors)": stage_ms[0], "scan+emit": stage_ms[1], "stuff": stage_ms[2]}},
+        "cpu_baseline": cpu_baseline,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -143,17 +307,27 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--options", default=":fancy_upsampling=1")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="decode", choices=["decode", "encode"],
+                    help="decode = the headline C1 decode batch (default); encode = BASELINE configs[4], 128x 1080p RGB -> JPEG")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "encode":
+        if args.impl == "reference":
+            raise SystemExit("the reference arm is defined for the decode headline; the encode line carries its libjpeg-turbo baseline")
+        if args.batch == 64:
+            args.batch = 128
+        run_encode(args, rank, world, local_rank)
+        return
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
 
     datas = make_corpus(args.batch)  # before CUDA init (spawned workers)
+    numa = pin_to_gpu_numa_node(local_rank) if world > 1 else None
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():
@@ -161,7 +335,19 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL announces its version on stdout at the first collective: keep stdout for the one JSON line
+        os.environ["NCCL_DEBUG"] = "WARN"
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     from nvimagecodec_b200.decoder import Decoder
 
     n = args.batch
@@ -298,7 +484,7 @@ def main():
                                "fancy upsampling, per GPU" % (n, S / n / 1e3),
                    "l2": "working set per step %.0f MB (records+planes+output) > 126 MB L2, no explicit flush" %
                          ((R + 70 * blocks + out_b) / 1e6),
-                   "options": args.options, "sync_rounds": stats["sync_rounds"], "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"],
+                   "host_affinity": numa, "options": args.options, "sync_rounds": stats["sync_rounds"], "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"],
                    "parity": "bit-exact vs reference libjpeg_turbo_ext on all %d images before timing" % n},
         "clocks": clocks.summary(),
         "e2e": {"value": mpix_step / (e2e_ms / args.steps / 1e3), "unit": "Mpixel/s", "images_per_s": n * world / (e2e_ms / args.steps / 1e3),

@@ -5,9 +5,12 @@
 // arithmetic mirrors libjpeg-turbo's jpeg_compress (see enc_math.cuh / enc_plan.cpp for the per-function citations).
 #include "encoder.h"
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 #include "enc_plan.h"
 #include "encode_kernels.h"
@@ -24,6 +27,37 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
             return B200JPEG_STATUS_CUDA_ERROR;                                                                      \
         }                                                                                                           \
     } while (0)
+
+// is this host pointer page-locked memory CUDA knows about (then async copies can use it directly)?
+inline bool is_pinned(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+// run job(i) for i in [0, n) on up to `threads` host threads
+template <class F>
+inline void parallel_for(int n, int threads, const F& job)
+{
+    threads = std::max(1, std::min(threads, n));
+    if (threads == 1) {
+        for (int i = 0; i < n; ++i)
+            job(i);
+        return;
+    }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t)
+        pool.emplace_back([&, t] {
+            for (int i = t; i < n; i += threads)
+                job(i);
+        });
+    for (auto& th : pool)
+        th.join();
+}
 
 struct Buf
 {
@@ -120,6 +154,9 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     cudaStream_t user_stream, int32_t* statuses)
 {
     Impl& s = *impl_;
+    static const bool trace = std::getenv("B200JPEG_TRACE") != nullptr; // developer aid: host-side timeline on stderr
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_begin = now();
     B2J_CUDA(cudaSetDevice(s.device));
     std::memset(s.stats, 0, sizeof(s.stats));
     std::vector<EncImageDesc> images;
@@ -180,6 +217,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     if (m == 0)
         return B200JPEG_STATUS_SUCCESS;
     const uint32_t total_segs = seg_map.back();
+    const double t_plan = now();
 
     // ---- scratch ----
     int rc = 0;
@@ -195,8 +233,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
         (rc = s.ensure(s.d_dc, total_blocks * 2, false)) || (rc = s.ensure(s.d_acbits, total_blocks * 2, false)) ||
         (rc = s.ensure(s.d_blk_off, total_blocks * 4, false)) || (rc = s.ensure(s.d_seg_bits, size_t(total_segs) * 4, false)) ||
         (rc = s.ensure(s.d_seg_off, size_t(total_segs) * 4, false)) || (rc = s.ensure(s.d_img_bytes, size_t(m) * 8, false)) ||
-        (rc = s.ensure(s.h_sizes, size_t(m) * 8, true)) || (host_pix_bytes && ((rc = s.ensure(s.d_pixels, host_pix_bytes, false)) ||
-                                                               (rc = s.ensure(s.h_pixels, host_pix_bytes, true)))))
+        (rc = s.ensure(s.h_sizes, size_t(m) * 8, true)) || (host_pix_bytes && (rc = s.ensure(s.d_pixels, host_pix_bytes, false))))
         return rc;
 
     // ---- host pixels -> pinned staging -> device ----
@@ -205,16 +242,39 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     if (s.profile)
         cudaEventRecord(s.ev[0], s.stream);
     if (host_pix_bytes) {
+        // page-locked inputs go up directly; pageable ones pass through the pinned staging buffer (copied by a few threads)
+        std::vector<int> staged;
         for (int k = 0; k < m; ++k) {
             if (host_pix_off[k] == SIZE_MAX)
                 continue;
             EncImageDesc& im = images[k];
             const size_t planes = im.in_fmt == B200JPEG_FMT_P_RGB ? 3 : 1;
             const size_t bytes = size_t(im.stride) * im.height * planes;
-            std::memcpy(static_cast<uint8_t*>(s.h_pixels.p) + host_pix_off[k], im.pixels, bytes);
-            im.pixels = static_cast<const uint8_t*>(s.d_pixels.p) + host_pix_off[k];
+            uint8_t* dst = static_cast<uint8_t*>(s.d_pixels.p) + host_pix_off[k];
+            if (is_pinned(im.pixels))
+                B2J_CUDA(cudaMemcpyAsync(dst, im.pixels, bytes, cudaMemcpyHostToDevice, s.stream));
+            else
+                staged.push_back(k);
         }
-        B2J_CUDA(cudaMemcpyAsync(s.d_pixels.p, s.h_pixels.p, host_pix_bytes, cudaMemcpyHostToDevice, s.stream));
+        if (!staged.empty()) {
+            if ((rc = s.ensure(s.h_pixels, host_pix_bytes, true)))
+                return rc;
+            parallel_for(int(staged.size()), 8, [&](int j) {
+                const int k = staged[j];
+                const EncImageDesc& im = images[k];
+                const size_t planes = im.in_fmt == B200JPEG_FMT_P_RGB ? 3 : 1;
+                std::memcpy(static_cast<uint8_t*>(s.h_pixels.p) + host_pix_off[k], im.pixels, size_t(im.stride) * im.height * planes);
+            });
+            for (int k : staged) {
+                const EncImageDesc& im = images[k];
+                const size_t planes = im.in_fmt == B200JPEG_FMT_P_RGB ? 3 : 1;
+                B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(s.d_pixels.p) + host_pix_off[k], static_cast<uint8_t*>(s.h_pixels.p) + host_pix_off[k],
+                    size_t(im.stride) * im.height * planes, cudaMemcpyHostToDevice, s.stream));
+            }
+        }
+        for (int k = 0; k < m; ++k)
+            if (host_pix_off[k] != SIZE_MAX)
+                images[k].pixels = static_cast<const uint8_t*>(s.d_pixels.p) + host_pix_off[k];
     }
     uint8_t* hm = static_cast<uint8_t*>(s.h_meta.p);
     std::memcpy(hm + off_img, images.data(), sizeof(EncImageDesc) * m);
@@ -259,6 +319,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     uint32_t* hsizes = static_cast<uint32_t*>(s.h_sizes.p);
     B2J_CUDA(cudaMemcpyAsync(hsizes, b.img_stream_bytes, sizeof(uint32_t) * m, cudaMemcpyDeviceToHost, s.stream));
     B2J_CUDA(cudaStreamSynchronize(s.stream)); // the stream lengths decide the layout of everything that follows
+    const double t_half = now();
 
     // ---- second half: layout of the streams, Huffman emit, stuffing ----
     EncImageDyn* dyn = static_cast<EncImageDyn*>(s.h_dyn.p);
@@ -296,27 +357,55 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     B2J_CUDA(cudaMemcpyAsync(hsizes + m, b.img_out_bytes, sizeof(uint32_t) * m, cudaMemcpyDeviceToHost, s.stream));
     B2J_CUDA(cudaStreamSynchronize(s.stream));
 
+    const double t_dev = now();
     // ---- headers (host) + entropy-coded bytes (device -> caller's buffer) + EOI ----
-    uint64_t total_out = 0;
+    // page-locked destinations receive the bytes directly; pageable ones go through a pinned bounce buffer and a threaded
+    // host copy (an asynchronous copy into pageable memory would be staged by the driver one image at a time)
+    uint64_t total_out = 0, bounce_bytes = 0;
+    std::vector<uint64_t> bounce_off(m, UINT64_MAX);
+    std::vector<char> ok(m, 0);
     for (int k = 0; k < m; ++k) {
         const int bi = batch_index[k];
         const size_t hdr = headers[k].size(), body = hsizes[m + k], need = hdr + body + 2;
+        out_sizes[bi] = need;
         if (need > out_capacity[bi]) {
             statuses[bi] = B200JPEG_STATUS_BUFFER_TOO_SMALL;
-            out_sizes[bi] = need;
             continue;
         }
+        ok[k] = 1;
+        total_out += need;
+        if (!is_pinned(out[bi])) {
+            bounce_off[k] = bounce_bytes;
+            bounce_bytes += align_up(body, 256);
+        }
+    }
+    if (bounce_bytes && (rc = s.ensure(s.h_out, bounce_bytes, true)))
+        return rc;
+    for (int k = 0; k < m; ++k) {
+        if (!ok[k])
+            continue;
+        const int bi = batch_index[k];
+        const size_t hdr = headers[k].size(), body = hsizes[m + k];
+        uint8_t* dst = bounce_off[k] == UINT64_MAX ? out[bi] + hdr : static_cast<uint8_t*>(s.h_out.p) + bounce_off[k];
+        B2J_CUDA(cudaMemcpyAsync(dst, static_cast<uint8_t*>(s.d_out.p) + dyn[k].out_off, body, cudaMemcpyDeviceToHost, s.stream));
         std::memcpy(out[bi], headers[k].data(), hdr);
-        B2J_CUDA(cudaMemcpyAsync(out[bi] + hdr, static_cast<uint8_t*>(s.d_out.p) + dyn[k].out_off, body, cudaMemcpyDeviceToHost, s.stream));
         out[bi][hdr + body] = 0xFF;
         out[bi][hdr + body + 1] = 0xD9;
-        out_sizes[bi] = need;
-        total_out += need;
+    }
+    if (bounce_bytes) {
+        B2J_CUDA(cudaStreamSynchronize(s.stream));
+        parallel_for(m, 8, [&](int k) {
+            if (ok[k] && bounce_off[k] != UINT64_MAX)
+                std::memcpy(out[batch_index[k]] + headers[k].size(), static_cast<uint8_t*>(s.h_out.p) + bounce_off[k], hsizes[m + k]);
+        });
     }
     B2J_CUDA(cudaStreamSynchronize(s.stream));
     if (s.profile)
         for (int i = 0; i < 4; ++i)
             cudaEventElapsedTime(&s.stage_ms[i], s.ev[i], s.ev[i + 1]);
+    if (trace)
+        std::fprintf(stderr, "b200jpeg encode trace: plan %.3f, first half (pixels up, DCT, scan) %.3f, second half (emit, stuff) %.3f, copy out %.3f ms\n",
+            t_plan - t_begin, t_half - t_plan, t_dev - t_half, now() - t_dev);
     s.stats[0] = launches;
     s.stats[1] = total_blocks;
     s.stats[2] = in_bytes;

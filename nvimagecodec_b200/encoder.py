@@ -70,6 +70,23 @@ class Encoder:
         self.last_statuses = list(st)
         return [bufs[i][:sizes[i]].tobytes() if st[i] == 0 else None for i in range(n)], self.last_statuses
 
+    def encode_into(self, inputs, out_ptrs, capacities, cuda_stream=0):
+        """lowest level: caller-owned output buffers (host pointers; page-locked ones are filled without a bounce copy)
+        -> (sizes, statuses)"""
+        n = len(inputs)
+        arr = (_capi.EncodeInput * n)()
+        for i, d in enumerate(inputs):
+            for k, v in d.items():
+                setattr(arr[i], k, v)
+        sizes = (C.c_size_t * n)()
+        st = (C.c_int32 * n)()
+        rc = _capi.lib().b200jpeg_encode_batch(self._h, n, arr, (C.c_void_p * n)(*out_ptrs), (C.c_size_t * n)(*capacities), sizes,
+                                               C.c_void_p(cuda_stream), st)
+        if rc != 0:
+            raise RuntimeError("b200jpeg_encode_batch: %s" % _capi.status_string(rc))
+        self.last_statuses = list(st)
+        return list(sizes), self.last_statuses
+
     def stats(self):
         s = (C.c_uint64 * 8)()
         _capi.lib().b200jpeg_encoder_get_stats(self._h, s)
