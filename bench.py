@@ -415,7 +415,8 @@ def main():
     barrier()
 
     # ---- e2e: host JPEG bytes -> host RGB through the C ABI ----
-    houts = [torch.empty((H, W * 3), dtype=torch.uint8).pin_memory() for _ in range(n)]
+    hbatch = torch.empty((n, H, W * 3), dtype=torch.uint8).pin_memory()  # the batch tensor a data loader would hand over
+    houts = [hbatch[i] for i in range(n)]
     hptrs = [o.data_ptr() for o in houts]
     for _ in range(2):
         dec.decode_into(datas, hptrs, strides, fmts, True, stream)
@@ -489,7 +490,7 @@ def main():
         "clocks": clocks.summary(),
         "e2e": {"value": mpix_step / (e2e_ms / args.steps / 1e3), "unit": "Mpixel/s", "images_per_s": n * world / (e2e_ms / args.steps / 1e3),
                 "ms_per_step": e2e_ms / args.steps, "h2d_bytes_per_step": int(S), "d2h_bytes_per_step": int(out_b), "timing": "wall clock around "
-                "b200jpeg_decode_batch (synchronous), pinned host output buffers"},
+                "b200jpeg_decode_batch (synchronous), pageable host JPEG bytes in, one pinned host batch tensor (N x H x W x 3) out"},
         "gpu_launches": int(launches),
         "roofline": roof,
         "cpu_baseline": cpu_baseline,

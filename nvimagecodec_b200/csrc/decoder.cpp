@@ -9,6 +9,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <thread>
+#if defined(__x86_64__) || defined(_M_X64)
+#include <emmintrin.h>
+#endif
 #include "../../include/b200jpeg.h"
 
 namespace b200jpeg {
@@ -396,29 +399,160 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
 }
 
 // entropy-coded bytes of one group -> pinned staging -> device (asynchronous on the group's stream)
+// ---- staging pool ----
+// Copy into the pinned staging buffer with streaming stores: the bytes are read next by the GPU's DMA engine, not by a
+// CPU, and an upload that has to pull freshly written lines out of the cores' caches runs at half the PCIe rate.
+static void stage_copy(uint8_t* dst, const uint8_t* src, size_t len)
+{
+#if defined(__x86_64__) || defined(_M_X64)
+    if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0 && len >= 64) {
+        size_t i = 0;
+        for (; i + 64 <= len; i += 64) {
+            const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i));
+            const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 16));
+            const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 32));
+            const __m128i d = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 48));
+            _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i), a);
+            _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 16), b);
+            _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 32), c);
+            _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 48), d);
+        }
+        if (i < len)
+            std::memcpy(dst + i, src + i, len - i);
+        _mm_sfence();
+        return;
+    }
+#endif
+    std::memcpy(dst, src, len);
+}
+
+StagePool::StagePool(int workers)
+{
+    for (int i = 0; i < workers; ++i)
+        th_.emplace_back([this] { worker(); });
+}
+
+StagePool::~StagePool()
+{
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        stop_ = true;
+    }
+    cv_.notify_all();
+    for (auto& t : th_)
+        t.join();
+}
+
+bool StagePool::claim_one()
+{
+    const size_t n = items_->size();
+    if (next_.load(std::memory_order_relaxed) >= n)
+        return false;
+    const size_t i = next_.fetch_add(1, std::memory_order_relaxed);
+    if (i >= n)
+        return false;
+    const Item& it = (*items_)[i];
+    stage_copy(it.dst, it.src, it.len);
+    done_[i].store(1, std::memory_order_release);
+    return true;
+}
+
+void StagePool::worker()
+{
+    uint64_t seen = 0;
+    for (;;) {
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            cv_.wait(lk, [&] { return stop_ || epoch_ != seen; });
+            if (stop_)
+                return;
+            seen = epoch_;
+        }
+        while (claim_one()) {
+        }
+        acks_.fetch_add(1, std::memory_order_acq_rel); // every worker passes through every job, however late it wakes up
+    }
+}
+
+void StagePool::quiesce()
+{
+    while (acks_.load(std::memory_order_acquire) != epoch_ * th_.size())
+        std::this_thread::yield();
+}
+
+void StagePool::start(const std::vector<Item>* items)
+{
+    quiesce();
+    if (items->size() > done_cap_) {
+        done_cap_ = items->size() * 2;
+        done_.reset(new std::atomic<uint8_t>[done_cap_]);
+    }
+    for (size_t i = 0; i < items->size(); ++i)
+        done_[i].store(0, std::memory_order_relaxed);
+    checked_ = 0;
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        items_ = items;
+        next_.store(0, std::memory_order_release);
+        ++epoch_;
+    }
+    cv_.notify_all();
+}
+
+void StagePool::wait_prefix(size_t upto)
+{
+    for (;;) {
+        while (checked_ < upto && done_[checked_].load(std::memory_order_acquire))
+            ++checked_;
+        if (checked_ >= upto)
+            return;
+        if (!claim_one())
+            std::this_thread::yield();
+    }
+}
+
+namespace {
+struct StageGuard
+{
+    StagePool* pool;
+    size_t n;
+    ~StageGuard() { pool->wait_prefix(n); }
+};
+} // namespace
+
+// The entropy-coded bytes of every planned image, cut into pieces of at most 256 KB, in group order.
+void Decoder::stage_start()
+{
+    constexpr size_t kPiece = 256 << 10;
+    uint8_t* hr = static_cast<uint8_t*>(h_raw_.p);
+    if (!pool_) {
+        const int hw = int(std::thread::hardware_concurrency());
+        pool_.reset(new StagePool(std::max(0, std::min(opt_.copy_threads, hw > 0 ? hw : 1) - 1)));
+    }
+    pool_->quiesce(); // no worker of the previous job looks at the item list any more
+    stage_items_.clear();
+    stage_group_end_.assign(groups_.size(), 0);
+    for (size_t g = 0; g < groups_.size(); ++g) {
+        const Group& gr = groups_[g];
+        for (int i = gr.first; i < gr.first + gr.count; ++i) {
+            const ImageDesc& im = plan_.images[i];
+            const int bi = planned_to_batch_[i];
+            const uint8_t* src = data_[bi] + parsed_[bi].scan_offset;
+            for (size_t off = 0; off < im.raw_len; off += kPiece)
+                stage_items_.push_back({src + off, hr + im.raw_off + off, std::min(kPiece, size_t(im.raw_len) - off)});
+        }
+        stage_group_end_[g] = stage_items_.size();
+    }
+    pool_->start(&stage_items_);
+}
+
 int Decoder::stage_group(int g)
 {
     Group& gr = groups_[g];
-    uint8_t* hr = static_cast<uint8_t*>(h_raw_.p);
-    auto copy_range = [&](int lo, int hi) {
-        for (int i = lo; i < hi; ++i) {
-            const ImageDesc& im = plan_.images[i];
-            const int bi = planned_to_batch_[i];
-            std::memcpy(hr + im.raw_off, data_[bi] + parsed_[bi].scan_offset, im.raw_len);
-        }
-    };
+    pool_->wait_prefix(stage_group_end_[g]);
     const size_t bytes = gr.raw_hi - gr.raw_lo;
-    const int nthreads = std::min(std::min(opt_.copy_threads, gr.count), std::max(1, int(bytes >> 20)));
-    if (nthreads <= 1) {
-        copy_range(gr.first, gr.first + gr.count);
-    } else {
-        std::vector<std::thread> th;
-        for (int t = 0; t < nthreads; ++t)
-            th.emplace_back(copy_range, gr.first + gr.count * t / nthreads, gr.first + gr.count * (t + 1) / nthreads);
-        for (auto& x : th)
-            x.join();
-    }
-    B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(d_raw_.p) + gr.raw_lo, hr + gr.raw_lo, bytes, cudaMemcpyHostToDevice, streams_[g]));
+    B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(d_raw_.p) + gr.raw_lo, static_cast<uint8_t*>(h_raw_.p) + gr.raw_lo, bytes, cudaMemcpyHostToDevice,
+        streams_[g]));
     return 0;
 }
 
@@ -427,6 +561,8 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
     const int rc = plan_batch(n, data, sizes, outs, statuses);
     if (rc)
         return rc;
+    stage_start();
+    StageGuard guard{pool_.get(), stage_items_.size()}; // the caller's bytes are read by other threads until every item is done
     for (size_t g = 0; g < groups_.size(); ++g)
         if (const int r = stage_group(int(g)))
             return r;
@@ -482,14 +618,28 @@ int Decoder::launch_group(int g)
         cudaMemcpyDeviceToHost, st));
     B2J_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(h_states_.p) + sizeof(ImageState) * m + sizeof(SyncCounters) * g, gr.dev.sync,
         sizeof(SyncCounters), cudaMemcpyDeviceToHost, st));
-    for (int idx : gr.host_outs) { // host-memory outputs: copy back
-        const HostOutput& ho = host_outs_[idx];
+    // host-memory outputs: copy back.  Outputs that are contiguous on both sides (rows, and then whole images of a batch
+    // tensor) travel as one linear copy: every copy costs a few microseconds of PCIe idle time.
+    for (size_t k = 0; k < gr.host_outs.size();) {
+        const HostOutput& ho = host_outs_[gr.host_outs[k]];
         const size_t pitch = align_up(ho.row_bytes, 16);
-        if (size_t(ho.host_stride) == pitch) // contiguous on both sides: one linear copy runs at the full PCIe rate
-            B2J_CUDA(cudaMemcpyAsync(ho.host, static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch * ho.rows, cudaMemcpyDeviceToHost, st));
-        else
+        if (size_t(ho.host_stride) != pitch) {
             B2J_CUDA(cudaMemcpy2DAsync(ho.host, size_t(ho.host_stride), static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch, ho.row_bytes,
                 ho.rows, cudaMemcpyDeviceToHost, st));
+            ++k;
+            continue;
+        }
+        size_t len = pitch * ho.rows;
+        size_t k2 = k + 1;
+        for (; k2 < gr.host_outs.size(); ++k2) {
+            const HostOutput& nx = host_outs_[gr.host_outs[k2]];
+            const size_t np = align_up(nx.row_bytes, 16);
+            if (size_t(nx.host_stride) != np || nx.dev_off != ho.dev_off + len || static_cast<uint8_t*>(nx.host) != static_cast<uint8_t*>(ho.host) + len)
+                break;
+            len += np * nx.rows;
+        }
+        B2J_CUDA(cudaMemcpyAsync(ho.host, static_cast<uint8_t*>(d_out_.p) + ho.dev_off, len, cudaMemcpyDeviceToHost, st));
+        k = k2;
     }
     if (trace_)
         cudaEventRecord(ev_trace_[3 + 3 * g], st);
@@ -564,6 +714,8 @@ int Decoder::decode(int n, const uint8_t* const* data, const size_t* sizes, cons
         return rc;
     const double t1 = trace ? now() : 0;
     double t_stage = 0, t_launch = 0;
+    stage_start();
+    StageGuard guard{pool_.get(), stage_items_.size()};
     for (size_t g = 0; g < groups_.size(); ++g) {
         const double a = trace ? now() : 0;
         if ((rc = stage_group(int(g))))

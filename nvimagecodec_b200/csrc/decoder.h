@@ -1,9 +1,14 @@
 // decoder.h -- batch decoder object behind b200jpeg_decode_* (host scheduling, staging, launches).
 #pragma once
 #include <cuda_runtime_api.h>
+#include <atomic>
+#include <condition_variable>
 #include <cstddef>
 #include <cstdint>
+#include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 #include "batch_plan.h"
 #include "decode_kernels.h"
@@ -15,7 +20,7 @@ struct DecoderOptions
     bool fancy_upsampling = true; // reference default (libjpeg_turbo_decoder.cpp:250-276)
     int subseq_bytes = 128;
     int groups_host = 5;  // groups (of doubling size) when outputs go to host memory; 0 = use `groups`
-    int copy_threads = 4;
+    int copy_threads = 8; // host threads (the caller's included) that copy entropy-coded bytes into pinned staging
     int groups = 4;           // the batch is cut into this many groups of images that run on separate streams (pipelining)
     bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)
     bool dump_coef = false; // debug: keep dense DCT coefficients for b200jpeg_debug_fetch(what = 0)
@@ -43,6 +48,39 @@ struct HostOutput // an output the caller wants in host memory
 };
 
 constexpr int kMaxGroups = 8;
+
+// Persistent host threads that fill the pinned staging buffer.  The items of a job are claimed in order; the calling
+// thread helps until the prefix it needs (one group of images) is complete, issues that group's upload and launches, and
+// comes back for the next prefix while the workers keep copying.
+class StagePool
+{
+  public:
+    struct Item
+    {
+        const uint8_t* src;
+        uint8_t* dst;
+        size_t len;
+    };
+    explicit StagePool(int workers);
+    ~StagePool();
+    void start(const std::vector<Item>* items); // the vector must stay alive until wait_prefix(items->size()) returned
+    void wait_prefix(size_t upto);
+    void quiesce(); // every worker is done with the previous job
+
+  private:
+    bool claim_one();
+    void worker();
+    std::vector<std::thread> th_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    uint64_t epoch_ = 0;
+    bool stop_ = false;
+    const std::vector<Item>* items_ = nullptr;
+    std::atomic<size_t> next_{0};
+    std::unique_ptr<std::atomic<uint8_t>[]> done_;
+    size_t done_cap_ = 0, checked_ = 0;
+    std::atomic<uint64_t> acks_{0};
+};
 
 struct Group // consecutive planned images that are launched together on one stream
 {
@@ -82,6 +120,7 @@ class Decoder
     int ensure(DevBuf& b, size_t bytes);
     int ensure_pinned(DevBuf& b, size_t bytes);
     int plan_batch(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses);
+    void stage_start();
     int stage_group(int g);
     int launch_group(int g);
     int begin_run(cudaStream_t user_stream, int32_t* statuses);
@@ -111,6 +150,9 @@ class Decoder
     LaunchDims dims_{};
     std::vector<Group> groups_;
     const uint8_t* const* data_ = nullptr; // caller's bitstreams during decode()/prepare()
+    std::unique_ptr<StagePool> pool_;
+    std::vector<StagePool::Item> stage_items_;
+    std::vector<size_t> stage_group_end_; // per group: end of its items
     size_t scratch_bytes_ = 0;
 
     uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_record_bytes_ = 0, stat_redone_ = 0;
