@@ -259,18 +259,20 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
             const uint32_t win = funnel_left(w0, w1, p);
             const uint32_t base = z ? ts.ac_off : ts.dc_off;
             uint32_t e = env.lut[base + (win >> (32 - kLutBits))];
+            bool bad = false;
             if ((e & 31u) == 0) { // code longer than kLutBits
                 bool ok = true;
                 e = huff_long_entry(env.lut, base, e, env.pool + (z ? ts.ac_idx : ts.dc_idx), win, ok);
-                if (WRITE && !ok)
-                    err |= kErrBadCode;
+                bad = !ok;
             }
             const uint32_t tot = e & 31u, sz = (e >> 5) & 15u, zadv = e >> 9;
             const uint32_t newp = p + tot;
-            if (newp > B) { // the "symbol" runs over the segment end: it was padding
-                cross = true;
+            if (newp > B) { // the "symbol" runs over the segment end: it was padding (a thread may well start inside
+                cross = true; // the pad bits of a segment whose blocks are complete; they never form a whole code)
                 break;
             }
+            if (WRITE && bad)
+                err |= kErrBadCode;
             if (WRITE) {
                 int val;
                 const uint32_t r = make_record(win << (tot - sz), sz, zadv, z != 0, val);

@@ -5,6 +5,8 @@
 // Lets the "not gpu" tests check parser, planner, Huffman self-synchronisation, IDCT, upsampling and colour logic
 // bit-for-bit against the oracle without a GPU.  Never linked into the product.
 #include <cstdio>
+#include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <vector>
 #include "../../nvimagecodec_b200/csrc/batch_plan.h"
@@ -284,6 +286,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             if (out.cursor > out.limit) err |= kErrRecords;
             out.finish();
             if (s.nblk == im.total_blocks && s.z == 0 && nblk_in < im.total_blocks) states[i].done_blocks = s.nblk;
+            if (err && std::getenv("EMU_DEBUG")) std::fprintf(stderr, "emu: write pass err %u at subseq %u (p0 %u) nblk_in %u -> %u z %u\n", err, k, k * S, nblk_in, s.nblk, s.z);
             states[i].error |= err;
         }
         // dense coefficients (what the IDCT kernel rebuilds in shared memory; also the debug tap)
@@ -291,8 +294,10 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         if (states[i].done_blocks == im.total_blocks)
             for (uint32_t bb = 0; bb < im.total_blocks; ++bb) {
                 int16_t blk[kRecBlkSlots] = {};
-                if (records_to_block(records.data() + im.rec_off, blkrec[im.coef_off / 64 + bb], states[i].rec_total, zzx, blk))
+                if (records_to_block(records.data() + im.rec_off, blkrec[im.coef_off / 64 + bb], states[i].rec_total, zzx, blk)) {
+                    if (std::getenv("EMU_DEBUG") && !(states[i].error & kErrBadCode)) std::fprintf(stderr, "emu: records_to_block bad at block %u first rec %u\n", bb, blkrec[im.coef_off / 64 + bb]);
                     states[i].error |= kErrBadCode;
+                }
                 std::memcpy(coef.data() + im.coef_off + uint64_t(bb) * 64, blk, 128);
             }
     }
@@ -343,6 +348,8 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                 else { color_unit<1, 1>(b, im, q, x0, px, yrow); store_unit_simple<1>(im, x0, px, yrow); }
             }
         }
+        if (std::getenv("EMU_DEBUG"))
+            std::fprintf(stderr, "emu: image %d error flags %u, done_blocks %u of %u, rec_total %u cap %u\n", i, states[i].error, states[i].done_blocks, im.total_blocks, states[i].rec_total, unsigned(im.rec_cap));
         if (states[i].error) statuses[idx[i]] = 4;
         else if (states[i].done_blocks != im.total_blocks) statuses[idx[i]] = 4;
     }

@@ -84,3 +84,17 @@ def test_golden_fixtures_through_emulation():
         d = open(os.path.join(GOLDEN, name), "rb").read()
         outs, st, _, _ = emu.decode_batch([d], [(227, 149)], 4)
         assert st == [0] and np.array_equal(outs[0], port.decode(d, port.FMT_I_RGB, True)), name
+
+
+def test_emulated_many_short_restart_segments():
+    """Thousands of short restart segments: subsequences begin in every possible place relative to a segment end, in
+    particular inside the pad bits of a segment whose blocks are already complete (the bits there plus the start of the
+    next segment may look like an invalid code; that is padding, not corruption)."""
+    datas = [make_jpeg(3020, 1536, 1024, (1, 1), 90, restart_interval=1), make_jpeg(3021, 1280, 960, (2, 2), 92, restart_interval=2),
+             make_jpeg(3022, 1024, 1024, (1, 1), 97, restart_interval=3)]
+    dims = [(1536, 1024), (1280, 960), (1024, 1024)]
+    for subseq in (32, 128):
+        outs, st, rounds, _ = emu.decode_batch(datas, dims, 4, 1, subseq)
+        assert st == [0, 0, 0]
+        for d, o in zip(datas, outs):
+            assert np.array_equal(o, port.decode(d, port.FMT_I_RGB, True))
