@@ -4,8 +4,9 @@
 //                         reference's edge replication, chroma box downsampling, then one 8x8 block per thread: level
 //                         shift + islow FDCT + reciprocal quantisation -> zigzag int16 coefficients (coalesced through a
 //                         shared-memory staging area), the block's DC and the entropy-coded length of its AC part
-//   E2 k_enc_scan         one warp per restart segment: DC category lengths + AC lengths -> bit offset of every block
-//   E3 k_enc_segscan      one warp per image: byte offsets of the segments, unstuffed stream length
+//   E2 k_enc_bits         bits of every block (DC category code + value bits + AC part), exclusive scan inside each tile of
+//                         kEncCta blocks; k_enc_tilescan: one warp per image scans the tile totals
+//   E3 k_enc_segscan      one CTA per image: bytes of every restart segment, byte offsets of the segments, stream length
 //   E4 k_enc_emit         one block per thread: Huffman-codes its coefficients into the CTA's shared-memory window of the
 //                         stream (OR-ed words), pads segment ends with 1-bits; window -> global, shared edge words by atomicOr
 //   E5 k_enc_stuff_count / k_enc_stuff_scan / k_enc_stuff_write
@@ -262,52 +263,108 @@ __device__ __forceinline__ int enc_dc_diff(const EncBatchDev& b, const EncImageD
     return p < 0 ? cur : cur - int(b.dc[im.blk_first + uint64_t(p)]);
 }
 
-constexpr int kEncScanWarps = 4;
-__global__ void __launch_bounds__(kEncScanWarps * 32) k_enc_scan(EncBatchDev b, uint32_t total_segments)
+// Bit position of block k in the image's entropy-coded data if restart segments were not byte aligned: a plain prefix
+// sum over all blocks of the image, kept as a per-tile base (tile = the kEncCta blocks of one emit CTA) plus the offset
+// inside the tile.  k == total_blocks gives the image's total.  Arithmetic is modulo 2^32 (differences are what is used).
+__device__ __forceinline__ uint32_t enc_prefix_bits(const EncBatchDev& b, const EncImageDesc& im, int img, uint32_t k)
 {
-    const uint32_t seg_abs = blockIdx.x * kEncScanWarps + (threadIdx.x >> 5);
-    if (seg_abs >= total_segments)
-        return;
-    const uint32_t lane = threadIdx.x & 31;
-    const int img = enc_find_image(b.seg_map, b.num_images, seg_abs);
+    if (k >= im.total_blocks)
+        return b.img_bits[img];
+    return b.tile_off[im.emit_cta_first + k / kEncCta] + b.blk_off[im.blk_first + k];
+}
+
+// absolute bit position of block k inside the image's unstuffed stream (segments start on byte boundaries)
+__device__ __forceinline__ uint64_t enc_block_bitpos(const EncBatchDev& b, const EncImageDesc& im, int img, uint32_t k)
+{
+    const uint32_t seg = k / im.seg_blocks;
+    const uint32_t rel = enc_prefix_bits(b, im, img, k) - enc_prefix_bits(b, im, img, seg * im.seg_blocks);
+    return uint64_t(b.seg_byte_off[im.seg_first + seg]) * 8u + rel;
+}
+
+// E2a: bits of every block (DC category code + value bits + AC part) and their exclusive scan inside the tile
+__global__ void __launch_bounds__(kEncCta) k_enc_bits(EncBatchDev b)
+{
+    __shared__ uint32_t s_warp[kEncCta / 32];
+    const int img = enc_find_image(b.cta_map_emit, b.num_images, blockIdx.x);
     const EncImageDesc& im = b.images[img];
-    const uint32_t seg = seg_abs - im.seg_first;
-    const uint32_t first = seg * im.seg_blocks, last = min(first + im.seg_blocks, im.total_blocks);
+    const uint32_t blk = (blockIdx.x - b.cta_map_emit[img]) * kEncCta + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t bits = 0;
+    if (blk < im.total_blocks) {
+        const int j = int(blk % uint32_t(im.bpm));
+        int comp, first_j, count;
+        enc_block_comp(im, j, comp, first_j, count);
+        const int n = enc_category(enc_dc_diff(b, im, blk));
+        bits = uint32_t(b.acbits[im.blk_first + blk]) + (b.huff->dc[comp ? 1 : 0][n] & 255u) + uint32_t(n);
+    }
+    uint32_t incl = bits;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= uint32_t(o))
+            incl += v;
+    }
+    if (lane == 31)
+        s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t pre = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kEncCta / 32; ++w) {
+        const uint32_t v = s_warp[w];
+        pre += uint32_t(w) < warp ? v : 0u;
+        total += v;
+    }
+    if (blk < im.total_blocks)
+        b.blk_off[im.blk_first + blk] = pre + incl - bits;
+    if (threadIdx.x == 0)
+        b.tile_off[blockIdx.x] = total;
+}
+
+// E2b: one warp per image: exclusive scan of the tile totals
+__global__ void __launch_bounds__(32) k_enc_tilescan(EncBatchDev b)
+{
+    const int img = blockIdx.x;
+    const uint32_t first = b.cta_map_emit[img], ntiles = b.cta_map_emit[img + 1] - first;
+    const uint32_t lane = threadIdx.x;
     uint32_t carry = 0;
-    for (uint32_t base = first; base < last; base += 32) {
-        const uint32_t blk = base + lane;
-        uint32_t bits = 0;
-        if (blk < last) {
-            const int j = int(blk % uint32_t(im.bpm));
-            int comp, first_j, count;
-            enc_block_comp(im, j, comp, first_j, count);
-            const int n = enc_category(enc_dc_diff(b, im, blk));
-            bits = uint32_t(b.acbits[im.blk_first + blk]) + (b.huff->dc[comp ? 1 : 0][n] & 255u) + uint32_t(n);
-        }
-        uint32_t incl = bits;
+    for (uint32_t base = 0; base < ntiles; base += 32) {
+        const uint32_t t = base + lane;
+        const uint32_t v = t < ntiles ? b.tile_off[first + t] : 0u;
+        uint32_t incl = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            const uint32_t u = __shfl_up_sync(0xFFFFFFFFu, incl, o);
             if (lane >= uint32_t(o))
-                incl += v;
+                incl += u;
         }
-        if (blk < last)
-            b.blk_off[im.blk_first + blk] = carry + incl - bits;
+        if (t < ntiles)
+            b.tile_off[first + t] = carry + incl - v;
         carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
     }
     if (lane == 0)
-        b.seg_bits[seg_abs] = carry;
+        b.img_bits[img] = carry;
 }
 
-__global__ void __launch_bounds__(32) k_enc_segscan(EncBatchDev b)
+// E3: one CTA per image: byte length of every restart segment -> byte offsets of the segments, unstuffed stream length
+constexpr int kEncSegScanThreads = 256;
+__global__ void __launch_bounds__(kEncSegScanThreads) k_enc_segscan(EncBatchDev b)
 {
+    __shared__ uint32_t s_warp[kEncSegScanThreads / 32];
+    __shared__ uint32_t s_carry;
     const int img = blockIdx.x;
     const EncImageDesc& im = b.images[img];
-    const uint32_t lane = threadIdx.x;
-    uint32_t carry = 0;
-    for (uint32_t base = 0; base < im.num_segments; base += 32) {
-        const uint32_t s = base + lane;
-        const uint32_t bytes = s < im.num_segments ? (b.seg_bits[im.seg_first + s] + 7u) >> 3 : 0u;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0)
+        s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < im.num_segments; base += kEncSegScanThreads) {
+        const uint32_t s = base + threadIdx.x;
+        uint32_t bytes = 0;
+        if (s < im.num_segments) {
+            const uint32_t lo = s * im.seg_blocks;
+            const uint32_t bits = enc_prefix_bits(b, im, img, lo + im.seg_blocks) - enc_prefix_bits(b, im, img, lo);
+            bytes = (bits + 7u) >> 3;
+        }
         uint32_t incl = bytes;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -315,12 +372,25 @@ __global__ void __launch_bounds__(32) k_enc_segscan(EncBatchDev b)
             if (lane >= uint32_t(o))
                 incl += v;
         }
+        if (lane == 31)
+            s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t pre = s_carry, total = 0;
+#pragma unroll
+        for (int w = 0; w < kEncSegScanThreads / 32; ++w) {
+            const uint32_t v = s_warp[w];
+            pre += uint32_t(w) < warp ? v : 0u;
+            total += v;
+        }
         if (s < im.num_segments)
-            b.seg_byte_off[im.seg_first + s] = carry + incl - bytes;
-        carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
+            b.seg_byte_off[im.seg_first + s] = pre + incl - bytes;
+        __syncthreads();
+        if (threadIdx.x == 0)
+            s_carry += total;
+        __syncthreads();
     }
-    if (lane == 0)
-        b.img_stream_bytes[img] = carry;
+    if (threadIdx.x == 0)
+        b.img_stream_bytes[img] = s_carry;
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -350,10 +420,7 @@ __global__ void __launch_bounds__(kEncCta) k_enc_emit(EncBatchDev b)
     if (threadIdx.x < 32)
         s_dc[threadIdx.x >> 4][threadIdx.x & 15] = b.huff->dc[threadIdx.x >> 4][threadIdx.x & 15];
     // absolute bit position of a block inside the image's unstuffed stream
-    auto bitpos = [&](uint32_t k) -> uint64_t {
-        const uint32_t seg = k / im.seg_blocks;
-        return uint64_t(b.seg_byte_off[im.seg_first + seg]) * 8u + b.blk_off[im.blk_first + k];
-    };
+    auto bitpos = [&](uint32_t k) -> uint64_t { return enc_block_bitpos(b, im, img, k); };
     const uint64_t win_lo_bit = bitpos(blk0) & ~uint64_t(31);
     const uint64_t win_hi_bit = blk_end == im.total_blocks ? uint64_t(dy.stream_bytes) * 8u : bitpos(blk_end);
     const uint32_t win_words = uint32_t((win_hi_bit - win_lo_bit + 31u) >> 5);
@@ -409,8 +476,7 @@ __global__ void k_enc_zero_edges(EncBatchDev b, uint32_t total_ctas)
     const EncImageDesc& im = b.images[img];
     const EncImageDyn& dy = b.dyn[img];
     const uint32_t blk0 = (c - b.cta_map_emit[img]) * kEncCta;
-    const uint32_t seg = blk0 / im.seg_blocks;
-    const uint64_t pos = uint64_t(b.seg_byte_off[im.seg_first + seg]) * 8u + b.blk_off[im.blk_first + blk0];
+    const uint64_t pos = enc_block_bitpos(b, im, img, blk0);
     uint32_t* gw = reinterpret_cast<uint32_t*>(b.stream + dy.stream_off);
     gw[pos >> 5] = 0;
     if (blk0 == 0) { // and the image's last word(s)
@@ -580,9 +646,10 @@ int launch_enc_dct(const EncBatchDev& b, const EncLaunchDims& d, cudaStream_t st
 
 int launch_enc_scan(const EncBatchDev& b, const EncLaunchDims& d, cudaStream_t st)
 {
-    k_enc_scan<<<(d.total_segments + kEncScanWarps - 1) / kEncScanWarps, kEncScanWarps * 32, 0, st>>>(b, d.total_segments);
-    k_enc_segscan<<<d.num_images, 32, 0, st>>>(b);
-    return 2;
+    k_enc_bits<<<d.emit_ctas, kEncCta, 0, st>>>(b);
+    k_enc_tilescan<<<d.num_images, 32, 0, st>>>(b);
+    k_enc_segscan<<<d.num_images, kEncSegScanThreads, 0, st>>>(b);
+    return 3;
 }
 
 int launch_enc_emit(const EncBatchDev& b, const EncLaunchDims& d, cudaStream_t st)

@@ -231,7 +231,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     if ((rc = s.ensure(s.d_meta, meta_bytes, false)) || (rc = s.ensure(s.h_meta, meta_bytes, true)) || (rc = s.ensure(s.d_dyn, dyn_bytes, false)) ||
         (rc = s.ensure(s.h_dyn, dyn_bytes, true)) || (rc = s.ensure(s.d_coef, total_blocks * 128, false)) ||
         (rc = s.ensure(s.d_dc, total_blocks * 2, false)) || (rc = s.ensure(s.d_acbits, total_blocks * 2, false)) ||
-        (rc = s.ensure(s.d_blk_off, total_blocks * 4, false)) || (rc = s.ensure(s.d_seg_bits, size_t(total_segs) * 4, false)) ||
+        (rc = s.ensure(s.d_blk_off, total_blocks * 4, false)) || (rc = s.ensure(s.d_seg_bits, size_t(map_emit.back()) * 4 + size_t(m) * 4, false)) ||
         (rc = s.ensure(s.d_seg_off, size_t(total_segs) * 4, false)) || (rc = s.ensure(s.d_img_bytes, size_t(m) * 8, false)) ||
         (rc = s.ensure(s.h_sizes, size_t(m) * 8, true)) || (host_pix_bytes && (rc = s.ensure(s.d_pixels, host_pix_bytes, false))))
         return rc;
@@ -296,7 +296,8 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     b.dc = static_cast<int16_t*>(s.d_dc.p);
     b.acbits = static_cast<uint16_t*>(s.d_acbits.p);
     b.blk_off = static_cast<uint32_t*>(s.d_blk_off.p);
-    b.seg_bits = static_cast<uint32_t*>(s.d_seg_bits.p);
+    b.tile_off = static_cast<uint32_t*>(s.d_seg_bits.p);
+    b.img_bits = b.tile_off + map_emit.back();
     b.seg_byte_off = static_cast<uint32_t*>(s.d_seg_off.p);
     b.img_stream_bytes = static_cast<uint32_t*>(s.d_img_bytes.p);
     b.img_out_bytes = static_cast<uint32_t*>(s.d_img_bytes.p) + m;
