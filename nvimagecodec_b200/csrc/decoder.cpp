@@ -64,6 +64,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
             int v = std::atoi(value.c_str());
             if (v >= 32 && v <= 4096 && (v % 4) == 0)
                 o.subseq_bytes = v;
+        } else if (name == "stream_priority") {
+            o.stream_priority = std::atoi(value.c_str()) != 0;
         } else if (name == "copy_threads")
             o.copy_threads = std::max(1, std::atoi(value.c_str()));
         else if (name == "groups")
@@ -120,8 +122,14 @@ int Decoder::init()
         std::fprintf(stderr, "b200jpeg: device %d is sm_%d%d; this library only carries sm_100a code\n", device_, prop.major, prop.minor);
         return B200JPEG_STATUS_ARCH_MISMATCH;
     }
-    for (cudaStream_t& st : streams_)
-        B2J_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    // option stream_priority=1: earlier groups run at higher priority, i.e. the block scheduler finishes group g's kernels
+    // before it spends SMs on group g + 1 (equal priorities interleave the groups' CTAs)
+    int prio_lo = 0, prio_hi = 0;
+    B2J_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    for (int g = 0; g < kMaxGroups; ++g) {
+        const int prio = opt_.stream_priority ? std::max(prio_hi, prio_lo - (kMaxGroups - 1 - g)) : prio_lo;
+        B2J_CUDA(cudaStreamCreateWithPriority(&streams_[g], cudaStreamNonBlocking, prio));
+    }
     B2J_CUDA(cudaEventCreateWithFlags(&ev_in_, cudaEventDisableTiming));
     B2J_CUDA(cudaEventCreateWithFlags(&ev_meta_, cudaEventDisableTiming));
     B2J_CUDA(cudaDeviceGetAttribute(&sm_count_, cudaDevAttrMultiProcessorCount, device_));

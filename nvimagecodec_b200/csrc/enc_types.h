@@ -81,10 +81,12 @@ struct EncBatchDev
     uint32_t* chunk_out;      // per stuffing chunk: output bytes, then exclusive prefix inside the image
     uint32_t* img_out_bytes;  // per image: stuffed length
     uint8_t* out;             // stuffed streams
+    // A launch covers a group of consecutive images: images / dyn / the per-image arrays point at the group's first image,
+    // the CTA maps hold batch-wide prefixes and the launch's first CTA is cta_base_* (stuffing chunks: group-local).
     const uint32_t* cta_map_dct;   // prefix arrays [num_images + 1]
     const uint32_t* cta_map_emit;
     const uint32_t* cta_map_stuff;
-    const uint32_t* seg_map;       // first segment of each image [num_images + 1]
+    uint32_t cta_base_dct, cta_base_emit;
 };
 
 // component of block j inside the MCU, its first block index in the MCU and its block count

@@ -44,9 +44,10 @@ __global__ void __launch_bounds__(kEncCta) k_enc_dct(EncBatchDev b)
     __shared__ EncQuantTable s_q[2];
     __shared__ uint8_t s_aclen[2][256];
     // ... colour: full-resolution chroma lives in the second half of s_y's 8 KB while it waits to be downsampled
-    const int img = enc_find_image(b.cta_map_dct, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.cta_base_dct;
+    const int img = enc_find_image(b.cta_map_dct, b.num_images, cta_abs);
     const EncImageDesc& im = b.images[img];
-    const uint32_t cta = blockIdx.x - b.cta_map_dct[img];
+    const uint32_t cta = cta_abs - b.cta_map_dct[img];
     const int my = int(cta / uint32_t(im.tiles_per_row)), tile = int(cta - uint32_t(my) * uint32_t(im.tiles_per_row));
     const int mx0 = tile * im.mcus_per_tile;
     const int nm = min(im.mcus_per_tile, im.mcus_x - mx0); // MCUs in this tile
@@ -285,9 +286,10 @@ __device__ __forceinline__ uint64_t enc_block_bitpos(const EncBatchDev& b, const
 __global__ void __launch_bounds__(kEncCta) k_enc_bits(EncBatchDev b)
 {
     __shared__ uint32_t s_warp[kEncCta / 32];
-    const int img = enc_find_image(b.cta_map_emit, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.cta_base_emit;
+    const int img = enc_find_image(b.cta_map_emit, b.num_images, cta_abs);
     const EncImageDesc& im = b.images[img];
-    const uint32_t blk = (blockIdx.x - b.cta_map_emit[img]) * kEncCta + threadIdx.x;
+    const uint32_t blk = (cta_abs - b.cta_map_emit[img]) * kEncCta + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t bits = 0;
     if (blk < im.total_blocks) {
@@ -317,7 +319,7 @@ __global__ void __launch_bounds__(kEncCta) k_enc_bits(EncBatchDev b)
     if (blk < im.total_blocks)
         b.blk_off[im.blk_first + blk] = pre + incl - bits;
     if (threadIdx.x == 0)
-        b.tile_off[blockIdx.x] = total;
+        b.tile_off[cta_abs] = total;
 }
 
 // E2b: one warp per image: exclusive scan of the tile totals
@@ -409,10 +411,11 @@ __global__ void __launch_bounds__(kEncCta) k_enc_emit(EncBatchDev b)
     __shared__ uint32_t s_win[kEncWindowWords];
     __shared__ uint32_t s_ac[2][256];
     __shared__ uint32_t s_dc[2][16];
-    const int img = enc_find_image(b.cta_map_emit, b.num_images, blockIdx.x);
+    const uint32_t cta_abs = blockIdx.x + b.cta_base_emit;
+    const int img = enc_find_image(b.cta_map_emit, b.num_images, cta_abs);
     const EncImageDesc& im = b.images[img];
     const EncImageDyn& dy = b.dyn[img];
-    const uint32_t cta = blockIdx.x - b.cta_map_emit[img];
+    const uint32_t cta = cta_abs - b.cta_map_emit[img];
     const uint32_t blk0 = cta * kEncCta, blk = blk0 + threadIdx.x;
     const uint32_t blk_end = min(blk0 + kEncCta, im.total_blocks);
     for (int i = threadIdx.x; i < 512; i += kEncCta)
@@ -469,9 +472,9 @@ __global__ void __launch_bounds__(kEncCta) k_enc_emit(EncBatchDev b)
 // clears the stream words two emit CTAs may both write (the first and last word of every CTA's window)
 __global__ void k_enc_zero_edges(EncBatchDev b, uint32_t total_ctas)
 {
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= total_ctas)
+    if (blockIdx.x * blockDim.x + threadIdx.x >= total_ctas)
         return;
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x + b.cta_base_emit;
     const int img = enc_find_image(b.cta_map_emit, b.num_images, c);
     const EncImageDesc& im = b.images[img];
     const EncImageDyn& dy = b.dyn[img];
