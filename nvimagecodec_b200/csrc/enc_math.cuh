@@ -13,8 +13,21 @@
 //   entropy coding      ljt/jchuff.c encode_one_block:558-655
 #pragma once
 #include "enc_types.h"
+#if !defined(__CUDACC__)
+#include "host_shim.h"
+#endif
 
 namespace b200jpeg {
+
+// the same three numbers per coefficient in one 8-byte word (one shared-memory load in the kernel): x = recip, y = corr | shift << 16
+struct EncQuantPacked
+{
+    const uint2* q;
+    B2J_HD uint32_t get_recip(int n) const { return q[n].x; }
+    B2J_HD uint32_t get_corr(int n) const { return q[n].y & 0xFFFFu; }
+    B2J_HD uint32_t get_shift(int n) const { return q[n].y >> 16; }
+};
+
 
 B2J_HD constexpr int enc_zigzag(int k) // natural-order index of zigzag position k (ljt/jutils.c jpeg_natural_order)
 {
@@ -70,7 +83,8 @@ B2J_HD int enc_quantise(int v, uint32_t recip, uint32_t corr, uint32_t shift)
 
 // Level shift, 2-D DCT and quantisation of one block.  rows[2 * r], rows[2 * r + 1]: the 8 samples of row r packed
 // little-endian; zz[k]: quantised coefficient at zigzag position k.
-B2J_HD void enc_fdct_quant(const uint32_t* rows, const EncQuantTable& qt, int16_t* zz)
+template <class Quant>
+B2J_HD void enc_fdct_quant(const uint32_t* rows, const Quant& qt, int16_t* zz)
 {
     int ws[64];
 #pragma unroll
@@ -88,7 +102,7 @@ B2J_HD void enc_fdct_quant(const uint32_t* rows, const EncQuantTable& qt, int16_
 #pragma unroll
     for (int k = 0; k < 64; ++k) {
         const int n = enc_zigzag(k);
-        zz[k] = int16_t(enc_quantise(ws[n], qt.recip[n], qt.corr[n], qt.shift[n]));
+        zz[k] = int16_t(enc_quantise(ws[n], qt.get_recip(n), qt.get_corr(n), qt.get_shift(n)));
     }
 }
 

@@ -175,7 +175,14 @@ bool enc_plan_image(int width, int height, int format, int subsampling, int rest
         im.seg_blocks = im.total_blocks;
         im.num_segments = 1;
     }
-    // one DCT CTA handles a run of MCUs of one MCU row: as many as give at most kEncCta blocks, at most 1024 pixels wide
+    // component planes between the colour-conversion and the FDCT kernels: whole MCUs, rows of a multiple of 16 bytes
+    {
+        const int pc = (im.mcus_x * 8 + 15) / 16 * 16;
+        im.plane_pitch[0] = (ncomp == 3 && hs == 2) ? 2 * pc : pc;
+        im.plane_pitch[1] = im.plane_pitch[2] = ncomp == 3 ? pc : 0;
+        im.plane_off[0] = im.plane_off[1] = im.plane_off[2] = 0; // assigned by the encoder when it lays out the batch
+    }
+    // (CPU emulation of the tests) a run of MCUs of one MCU row handled together: as many as give at most kEncCta blocks, at most 1024 pixels wide
     int mpt = kEncCta / im.bpm;
     if (ncomp == 3 && hs * vs == 4)
         mpt = 16;

@@ -5,7 +5,8 @@
 
 namespace b200jpeg {
 
-constexpr int kEncCta = 128;            // threads per CTA in the DCT and emit kernels: one 8x8 block per thread
+constexpr int kEncCta = 128;            // threads per CTA in the FDCT, bit-count and emit kernels: one 8x8 block per thread
+constexpr int kEncColorCta = 256;       // colour-conversion kernel: 4 pixels x vs rows per thread
 constexpr int kEncCoefPitch = 33;       // words per block in the shared-memory coefficient staging (32 + 1: conflict-free)
 constexpr int kEncMaxBlockBytes = 208;  // upper bound of one block's entropy-coded bits (64 x (16 + 10) bits) in bytes
 constexpr int kEncStuffThreads = 256;   // stuffing kernels: 16 stream bytes per thread
@@ -19,6 +20,9 @@ struct EncQuantTable
     uint16_t corr[64];
     uint8_t shift[64];
     uint8_t qval[64]; // the 8-bit quant values, natural order (for the DQT segment / debugging)
+    B2J_HD uint32_t get_recip(int n) const { return recip[n]; }
+    B2J_HD uint32_t get_corr(int n) const { return corr[n]; }
+    B2J_HD uint32_t get_shift(int n) const { return shift[n]; }
 };
 
 // Standard Huffman tables in encoder form (reference: ljt/jchuff.c jpeg_make_c_derived_tbl:232-312 applied to the T.81
@@ -45,9 +49,11 @@ struct EncImageDesc
     const uint8_t* pixels;  // device memory
     int64_t stride;         // bytes per row; planar: plane p at pixels + p * stride * height
     int32_t qt;             // index of the luma table in the quant pool (chroma = qt + 1)
-    int32_t mcus_per_tile;  // MCUs one DCT CTA handles (a run inside one MCU row)
+    int32_t mcus_per_tile;  // (CPU emulation of the tests: MCUs handled together, a run inside one MCU row)
     int32_t tiles_per_row;
-    uint32_t dct_cta_first; // CTA prefix of this image in the DCT grid (tiles_per_row * mcus_y CTAs)
+    uint32_t color_cta_first; // CTA prefix of this image in the colour-conversion grid
+    int32_t plane_pitch[3];   // Y / Cb / Cr planes after colour conversion + downsampling, padded to whole MCUs:
+    uint64_t plane_off[3];    // bytes per row (multiple of 16) and offset from the plane buffer base
     uint32_t emit_cta_first; // CTA prefix in the emit grid (ceil(total_blocks / kEncCta) CTAs)
     uint64_t blk_first;     // first block of this image in the batch-wide block arrays (coef = blk * 64 int16)
     uint32_t seg_first;     // first segment in the batch-wide segment arrays
@@ -69,6 +75,7 @@ struct EncBatchDev
     int32_t num_images;
     const EncQuantTable* quant;
     const EncHuffTables* huff;
+    uint8_t* planes;          // component planes (EncImageDesc::plane_off / plane_pitch)
     int16_t* coef;            // quantised coefficients, zigzag order, 64 per block, MCU scan order
     int16_t* dc;              // per block: quantised DC
     uint16_t* acbits;         // per block: entropy-coded bits of the AC part
@@ -83,10 +90,10 @@ struct EncBatchDev
     uint8_t* out;             // stuffed streams
     // A launch covers a group of consecutive images: images / dyn / the per-image arrays point at the group's first image,
     // the CTA maps hold batch-wide prefixes and the launch's first CTA is cta_base_* (stuffing chunks: group-local).
-    const uint32_t* cta_map_dct;   // prefix arrays [num_images + 1]
-    const uint32_t* cta_map_emit;
+    const uint32_t* cta_map_color; // prefix arrays [num_images + 1]
+    const uint32_t* cta_map_emit;  // tiles of kEncCta blocks: the FDCT, bit-count and emit kernels
     const uint32_t* cta_map_stuff;
-    uint32_t cta_base_dct, cta_base_emit;
+    uint32_t cta_base_color, cta_base_emit;
 };
 
 // component of block j inside the MCU, its first block index in the MCU and its block count

@@ -1,9 +1,10 @@
 // encode_kernels.cu -- sm_100a kernels of the b200jpeg encode path.
 //
-//   E1 k_enc_dct          per CTA a run of MCUs of one MCU row: RGB -> YCbCr (or gray) into shared memory with the
-//                         reference's edge replication, chroma box downsampling, then one 8x8 block per thread: level
-//                         shift + islow FDCT + reciprocal quantisation -> zigzag int16 coefficients (coalesced through a
-//                         shared-memory staging area), the block's DC and the entropy-coded length of its AC part
+//   E1a k_enc_color       4 pixels x vs rows per thread: RGB -> YCbCr (or gray) with the reference's edge replication and
+//                         chroma box downsampling -> component planes padded to whole MCUs
+//   E1b k_enc_fdct        one 8x8 block per thread (tiles of kEncCta blocks in MCU scan order): level shift + islow FDCT +
+//                         reciprocal quantisation -> zigzag int16 coefficients, the block's DC and the entropy-coded length
+//                         of its AC part; dummy edge blocks take the DC of their source block
 //   E2 k_enc_bits         bits of every block (DC category code + value bits + AC part), exclusive scan inside each tile of
 //                         kEncCta blocks; k_enc_tilescan: one warp per image scans the tile totals
 //   E3 k_enc_segscan      one CTA per image: bytes of every restart segment, byte offsets of the segments, stream length
@@ -32,226 +33,238 @@ __device__ __forceinline__ int enc_find_image(const uint32_t* __restrict__ map, 
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// E1: colour conversion + downsampling + FDCT + quantisation
+// E1a: colour conversion + downsampling -> component planes padded to whole MCUs
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kEncTilePixels = 8192; // gray: 128 MCUs x 8 x 8; colour tiles have at most 4096 pixels
-
-__global__ void __launch_bounds__(kEncCta) k_enc_dct(EncBatchDev b)
+// Four pixels of one source row (x clamped to the last column: expand_right_edge; the caller clamps the row).
+__device__ __forceinline__ void enc_load_rgb4(const EncImageDesc& im, int y, int sx, bool aligned4, uint32_t* r, uint32_t* g, uint32_t* bl)
 {
-    __shared__ __align__(16) uint8_t s_y[kEncTilePixels];  // luma tile; for colour only the first 4096 bytes are used ...
-    __shared__ __align__(16) uint8_t s_c[2][2048];          // downsampled (or 4:4:4) chroma, pitch = tile width / hs
-    __shared__ __align__(16) uint32_t s_coef[kEncCta * kEncCoefPitch];
-    __shared__ EncQuantTable s_q[2];
-    __shared__ uint8_t s_aclen[2][256];
-    // ... colour: full-resolution chroma lives in the second half of s_y's 8 KB while it waits to be downsampled
-    const uint32_t cta_abs = blockIdx.x + b.cta_base_dct;
-    const int img = enc_find_image(b.cta_map_dct, b.num_images, cta_abs);
-    const EncImageDesc& im = b.images[img];
-    const uint32_t cta = cta_abs - b.cta_map_dct[img];
-    const int my = int(cta / uint32_t(im.tiles_per_row)), tile = int(cta - uint32_t(my) * uint32_t(im.tiles_per_row));
-    const int mx0 = tile * im.mcus_per_tile;
-    const int nm = min(im.mcus_per_tile, im.mcus_x - mx0); // MCUs in this tile
-    const int hs = im.hs, vs = im.vs, ncomp = im.ncomp;
-    const int mcu_w = 8 * hs, mcu_h = 8 * vs;
-    const int tw = im.mcus_per_tile * mcu_w, th = mcu_h; // tile size in pixels (tw is a multiple of 64)
-    const int W = im.width, H = im.height;
-    uint8_t* s_cfull0 = s_y + 4096; // [th x tw] full-resolution Cb (<= 2048 ... 4096 bytes), Cr follows in s_coef's space
-    uint8_t* s_cfull1 = reinterpret_cast<uint8_t*>(s_coef);
+    const int W = im.width;
+    const uint8_t* row = im.pixels + int64_t(y) * im.stride;
+    if (im.in_fmt == 4) { // B200JPEG_FMT_I_RGB
+        if (sx + 3 < W && aligned4) {
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(row + sx * 3);
+            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+            r[0] = w0 & 255u; g[0] = (w0 >> 8) & 255u; bl[0] = (w0 >> 16) & 255u;
+            r[1] = w0 >> 24; g[1] = w1 & 255u; bl[1] = (w1 >> 8) & 255u;
+            r[2] = (w1 >> 16) & 255u; g[2] = w1 >> 24; bl[2] = w2 & 255u;
+            r[3] = (w2 >> 8) & 255u; g[3] = (w2 >> 16) & 255u; bl[3] = w2 >> 24;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint8_t* p = row + min(sx + i, W - 1) * 3;
+                r[i] = p[0]; g[i] = p[1]; bl[i] = p[2];
+            }
+        }
+    } else { // planar RGB
+        const int64_t plane_stride = im.stride * int64_t(im.height);
+        if (sx + 3 < W && aligned4) {
+            const uint32_t wr = *reinterpret_cast<const uint32_t*>(row + sx);
+            const uint32_t wg = *reinterpret_cast<const uint32_t*>(row + plane_stride + sx);
+            const uint32_t wb = *reinterpret_cast<const uint32_t*>(row + 2 * plane_stride + sx);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                r[i] = (wr >> (8 * i)) & 255u; g[i] = (wg >> (8 * i)) & 255u; bl[i] = (wb >> (8 * i)) & 255u;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int x = min(sx + i, W - 1);
+                r[i] = row[x]; g[i] = row[plane_stride + x]; bl[i] = row[2 * plane_stride + x];
+            }
+        }
+    }
+}
 
-    { // tables
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(b.quant + im.qt);
-        uint32_t* dst = reinterpret_cast<uint32_t*>(s_q);
-        for (int i = threadIdx.x; i < int(2 * sizeof(EncQuantTable) / 4); i += kEncCta)
-            dst[i] = src[i];
+// One thread: 4 pixels x vs source rows -> 4 x vs luma samples and 4 / hs chroma samples per chroma component.
+// Rows past the image repeat the last row (expand_bottom_edge before downsampling); chroma rows past the last row group
+// repeat that group's result (expand_bottom_edge after downsampling), so their source rows differ from the luma rows.
+template <int HS, int VS>
+__device__ __forceinline__ void enc_color_unit(const EncBatchDev& b, const EncImageDesc& im, int ux, int uy)
+{
+    const int W = im.width, H = im.height, sx = ux * 4;
+    const bool aligned4 = ((reinterpret_cast<uintptr_t>(im.pixels) | uint64_t(im.stride)) & 3u) == 0;
+    uint8_t* yp = b.planes + im.plane_off[0];
+    if (im.ncomp == 1) {
+        const uint8_t* row = im.pixels + int64_t(min(uy, H - 1)) * im.stride;
+        uint32_t yv = 0;
+        if (sx + 3 < W && aligned4)
+            yv = *reinterpret_cast<const uint32_t*>(row + sx);
+        else
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                yv |= uint32_t(row[min(sx + i, W - 1)]) << (8 * i);
+        *reinterpret_cast<uint32_t*>(yp + int64_t(uy) * im.plane_pitch[0] + sx) = yv;
+        return;
+    }
+    const int rows_ds = (H + VS - 1) / VS;
+    const int cgrp = min(uy, rows_ds - 1);
+    uint32_t cb[VS][4], cr[VS][4];
+#pragma unroll
+    for (int dy = 0; dy < VS; ++dy) {
+        const int ly = min(uy * VS + dy, H - 1), cy = min(cgrp * VS + dy, H - 1);
+        uint32_t r[4], g[4], bl[4];
+        enc_load_rgb4(im, ly, sx, aligned4, r, g, bl);
+        uint32_t yv = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            yv |= enc_luma(r[i], g[i], bl[i]) << (8 * i);
+        *reinterpret_cast<uint32_t*>(yp + int64_t(uy * VS + dy) * im.plane_pitch[0] + sx) = yv;
+        if (cy != ly)
+            enc_load_rgb4(im, cy, sx, aligned4, r, g, bl);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            cb[dy][i] = enc_cb(int(r[i]), int(g[i]), int(bl[i]));
+            cr[dy][i] = enc_cr(int(r[i]), int(g[i]), int(bl[i]));
+        }
+    }
+    uint8_t* cbp = b.planes + im.plane_off[1] + int64_t(uy) * im.plane_pitch[1];
+    uint8_t* crp = b.planes + im.plane_off[2] + int64_t(uy) * im.plane_pitch[2];
+    if (HS == 2) { // two outputs at even / odd chroma columns: biases 1, 2 (h2v2) or 0, 1 (h2v1)
+        uint32_t ob, orr;
+        if (VS == 2) {
+            ob = ((cb[0][0] + cb[0][1] + cb[VS - 1][0] + cb[VS - 1][1] + 1u) >> 2) | (((cb[0][2] + cb[0][3] + cb[VS - 1][2] + cb[VS - 1][3] + 2u) >> 2) << 8);
+            orr = ((cr[0][0] + cr[0][1] + cr[VS - 1][0] + cr[VS - 1][1] + 1u) >> 2) | (((cr[0][2] + cr[0][3] + cr[VS - 1][2] + cr[VS - 1][3] + 2u) >> 2) << 8);
+        } else {
+            ob = ((cb[0][0] + cb[0][1]) >> 1) | (((cb[0][2] + cb[0][3] + 1u) >> 1) << 8);
+            orr = ((cr[0][0] + cr[0][1]) >> 1) | (((cr[0][2] + cr[0][3] + 1u) >> 1) << 8);
+        }
+        *reinterpret_cast<uint16_t*>(cbp + ux * 2) = uint16_t(ob);
+        *reinterpret_cast<uint16_t*>(crp + ux * 2) = uint16_t(orr);
+    } else {
+        uint32_t ob = 0, orr = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t vb = VS == 2 ? (cb[0][i] + cb[VS - 1][i] + 1u) >> 1 : cb[0][i];
+            const uint32_t vr = VS == 2 ? (cr[0][i] + cr[VS - 1][i] + 1u) >> 1 : cr[0][i];
+            ob |= vb << (8 * i);
+            orr |= vr << (8 * i);
+        }
+        *reinterpret_cast<uint32_t*>(cbp + sx) = ob;
+        *reinterpret_cast<uint32_t*>(crp + sx) = orr;
+    }
+}
+
+__global__ void __launch_bounds__(kEncColorCta) k_enc_color(EncBatchDev b)
+{
+    const uint32_t cta_abs = blockIdx.x + b.cta_base_color;
+    const int img = enc_find_image(b.cta_map_color, b.num_images, cta_abs);
+    const EncImageDesc& im = b.images[img];
+    const uint32_t u = (cta_abs - b.cta_map_color[img]) * kEncColorCta + threadIdx.x;
+    const uint32_t units_x = uint32_t(im.plane_pitch[0]) >> 2;
+    const uint32_t uy = u / units_x, ux = u - uy * units_x;
+    const int hs = im.ncomp == 1 ? 1 : im.hs, vs = im.ncomp == 1 ? 1 : im.vs;
+    if (uy >= uint32_t(im.mcus_y) * 8u) // one unit row per chroma row (gray: hs = vs = 1)
+        return;
+    if (hs == 2 && vs == 2)
+        enc_color_unit<2, 2>(b, im, int(ux), int(uy));
+    else if (hs == 2)
+        enc_color_unit<2, 1>(b, im, int(ux), int(uy));
+    else if (vs == 2)
+        enc_color_unit<1, 2>(b, im, int(ux), int(uy));
+    else
+        enc_color_unit<1, 1>(b, im, int(ux), int(uy));
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// E1b: level shift + islow FDCT + quantisation, one block per thread (tiles of kEncCta blocks in MCU scan order)
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kEncCta, 4) k_enc_fdct(EncBatchDev b)
+{
+    __shared__ uint2 s_q[2][64];
+    __shared__ uint8_t s_aclen[2][256];
+    const uint32_t cta_abs = blockIdx.x + b.cta_base_emit;
+    const int img = enc_find_image(b.cta_map_emit, b.num_images, cta_abs);
+    const EncImageDesc& im = b.images[img];
+    {
+        const EncQuantTable* q = b.quant + im.qt;
+        for (int i = threadIdx.x; i < 128; i += kEncCta) {
+            const EncQuantTable& t = q[i >> 6];
+            s_q[i >> 6][i & 63] = make_uint2(t.recip[i & 63], uint32_t(t.corr[i & 63]) | (uint32_t(t.shift[i & 63]) << 16));
+        }
         for (int i = threadIdx.x; i < 512; i += kEncCta)
             s_aclen[i >> 8][i & 255] = uint8_t(b.huff->ac[i >> 8][i & 255] & 255u);
     }
-
-    // ---- phase 1: pixels -> Y (and full-resolution Cb, Cr), 4 pixels per thread and step ----
-    const int x0 = mx0 * mcu_w, y0 = my * mcu_h;
-    const int used_w = nm * mcu_w; // columns of the tile that belong to MCUs of the image
-    const int groups_x = used_w >> 2;
-    const bool interleaved = im.in_fmt == 4; // B200JPEG_FMT_I_RGB
-    const int64_t plane_stride = im.stride * int64_t(H);
-    const bool aligned4 = ((reinterpret_cast<uintptr_t>(im.pixels) | uint64_t(im.stride)) & 3u) == 0;
-    for (int g = threadIdx.x; g < groups_x * th; g += kEncCta) {
-        const int ty = g / groups_x, tx = (g - ty * groups_x) << 2;
-        const int sy = min(y0 + ty, H - 1);
-        const int sx = x0 + tx;
-        uint32_t yv = 0, cbv = 0, crv = 0;
-        if (ncomp == 1) {
-            const uint8_t* row = im.pixels + int64_t(sy) * im.stride;
-            if (sx + 3 < W && aligned4)
-                yv = *reinterpret_cast<const uint32_t*>(row + sx);
-            else
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    yv |= uint32_t(row[min(sx + i, W - 1)]) << (8 * i);
-        } else {
-            uint32_t r[4], gg[4], bb[4];
-            if (interleaved) {
-                const uint8_t* row = im.pixels + int64_t(sy) * im.stride;
-                if (sx + 3 < W && aligned4) {
-                    const uint32_t* p = reinterpret_cast<const uint32_t*>(row + sx * 3);
-                    const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
-                    r[0] = w0 & 255u; gg[0] = (w0 >> 8) & 255u; bb[0] = (w0 >> 16) & 255u;
-                    r[1] = w0 >> 24; gg[1] = w1 & 255u; bb[1] = (w1 >> 8) & 255u;
-                    r[2] = (w1 >> 16) & 255u; gg[2] = w1 >> 24; bb[2] = w2 & 255u;
-                    r[3] = (w2 >> 8) & 255u; gg[3] = (w2 >> 16) & 255u; bb[3] = w2 >> 24;
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const uint8_t* p = row + min(sx + i, W - 1) * 3;
-                        r[i] = p[0]; gg[i] = p[1]; bb[i] = p[2];
-                    }
-                }
-            } else {
-                const uint8_t* row = im.pixels + int64_t(sy) * im.stride;
-                if (sx + 3 < W && aligned4) {
-                    const uint32_t wr = *reinterpret_cast<const uint32_t*>(row + sx);
-                    const uint32_t wg = *reinterpret_cast<const uint32_t*>(row + plane_stride + sx);
-                    const uint32_t wb = *reinterpret_cast<const uint32_t*>(row + 2 * plane_stride + sx);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        r[i] = (wr >> (8 * i)) & 255u; gg[i] = (wg >> (8 * i)) & 255u; bb[i] = (wb >> (8 * i)) & 255u;
-                    }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int x = min(sx + i, W - 1);
-                        r[i] = row[x]; gg[i] = row[plane_stride + x]; bb[i] = row[2 * plane_stride + x];
-                    }
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                yv |= enc_luma(r[i], gg[i], bb[i]) << (8 * i);
-                cbv |= enc_cb(int(r[i]), int(gg[i]), int(bb[i])) << (8 * i);
-                crv |= enc_cr(int(r[i]), int(gg[i]), int(bb[i])) << (8 * i);
-            }
-        }
-        *reinterpret_cast<uint32_t*>(s_y + ty * tw + tx) = yv;
-        if (ncomp == 3) {
-            if (hs * vs == 1) {
-                *reinterpret_cast<uint32_t*>(s_c[0] + ty * tw + tx) = cbv;
-                *reinterpret_cast<uint32_t*>(s_c[1] + ty * tw + tx) = crv;
-            } else {
-                *reinterpret_cast<uint32_t*>(s_cfull0 + ty * tw + tx) = cbv;
-                *reinterpret_cast<uint32_t*>(s_cfull1 + ty * tw + tx) = crv;
-            }
-        }
-    }
     __syncthreads();
-
-    // ---- phase 2: chroma box filter (4 outputs per thread and step) ----
-    const int cw = tw / hs; // chroma pitch
-    if (ncomp == 3 && hs * vs > 1) {
-        // chroma rows past the last real row group repeat that group's result (expand_bottom_edge after downsampling)
-        const int rows_ds = (H + vs - 1) / vs;
-        const int cgroups_x = (used_w / hs) >> 2;
-        for (int g = threadIdx.x; g < cgroups_x * 8 * 2; g += kEncCta) {
-            const int c = g / (cgroups_x * 8), gi = g - c * (cgroups_x * 8);
-            const int ry = gi / cgroups_x, cx = (gi - ry * cgroups_x) << 2;
-            const int ryl = min(my * 8 + ry, rows_ds - 1) - my * 8; // source row group inside this tile
-            const uint8_t* full = c ? s_cfull1 : s_cfull0;
-            uint32_t out = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int x = cx + i;
-                uint32_t v;
-                if (hs == 2 && vs == 2) {
-                    const uint8_t* p = full + (2 * ryl) * tw + 2 * x;
-                    v = (uint32_t(p[0]) + p[1] + p[tw] + p[tw + 1] + ((x & 1) ? 2u : 1u)) >> 2;
-                } else if (hs == 2) {
-                    const uint8_t* p = full + ryl * tw + 2 * x;
-                    v = (uint32_t(p[0]) + p[1] + uint32_t(x & 1)) >> 1;
-                } else {
-                    const uint8_t* p = full + (2 * ryl) * tw + x;
-                    v = (uint32_t(p[0]) + p[tw] + 1u) >> 1;
-                }
-                out |= v << (8 * i);
-            }
-            *reinterpret_cast<uint32_t*>(s_c[c] + ry * cw + cx) = out;
-        }
-    }
-    __syncthreads(); // s_coef (which held the full-resolution Cr) is free from here on
-
-    // ---- phase 3: one block per thread ----
-    const int t = threadIdx.x;
-    const int nblocks = nm * im.bpm;
-    const int m = t / im.bpm, j = t - m * im.bpm;
+    const uint32_t blk = (cta_abs - b.cta_map_emit[img]) * kEncCta + threadIdx.x;
+    if (blk >= im.total_blocks)
+        return;
+    const int ncomp = im.ncomp, hs = im.hs, vs = im.vs;
+    const uint32_t mcu = blk / uint32_t(im.bpm);
+    const int j = int(blk - mcu * uint32_t(im.bpm));
+    const int my = int(mcu / uint32_t(im.mcus_x)), mx = int(mcu - uint32_t(my) * uint32_t(im.mcus_x));
     int comp = 0, first_j = 0, count = 1;
     enc_block_comp(im, j, comp, first_j, count);
     const int mw = comp == 0 && ncomp == 3 ? hs : 1, mh = comp == 0 && ncomp == 3 ? vs : 1;
-    const int jj = j - first_j, by = jj / mw, bx = jj - by * mw;
-    const bool active = t < nblocks;
-    const bool real = active && (mx0 + m) * mw + bx < im.wib[comp] && my * mh + by < im.hib[comp];
-    uint32_t* my_coef = s_coef + t * kEncCoefPitch;
+    int jj = j - first_j;
+    // dummy block (ljt/jccoefct.c:176-196): no AC, the DC of the block before it in the MCU; a whole dummy row copies the
+    // block before the row.  The source may itself be a dummy of the first kind; blocks at (0, 0) of a component are real.
+    bool real = true;
+    for (;;) {
+        const int sby = jj / mw, sbx = jj - sby * mw;
+        const bool row_dummy = my * mh + sby >= im.hib[comp];
+        const bool col_dummy = mx * mw + sbx >= im.wib[comp];
+        if (!row_dummy && !col_dummy)
+            break;
+        real = false;
+        jj = row_dummy ? sby * mw - 1 : jj - 1;
+    }
+    const int by = jj / mw, bx = jj - by * mw;
+    const int pitch = im.plane_pitch[comp];
+    const uint8_t* src = b.planes + im.plane_off[comp] + int64_t((my * mh + by) * 8) * pitch + (mx * mw + bx) * 8;
+    uint32_t rows[16];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const uint2 v = *reinterpret_cast<const uint2*>(src + r * pitch);
+        rows[2 * r] = v.x;
+        rows[2 * r + 1] = v.y;
+    }
+    const EncQuantPacked qt{s_q[comp ? 1 : 0]};
+    uint4* dst = reinterpret_cast<uint4*>(b.coef + (im.blk_first + blk) * 64);
+    if (!real) {
+        // the DC term of the islow FDCT is the plain sum of the level-shifted samples: (4 * sum + 2) >> 2
+        uint32_t sum = 0;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            sum = __dp4a(rows[i], 0x01010101u, sum);
+        const int dcq = enc_quantise(int(sum) - 128 * 64, qt.get_recip(0), qt.get_corr(0), qt.get_shift(0));
+        dst[0] = make_uint4(uint32_t(uint16_t(dcq)), 0, 0, 0);
+#pragma unroll
+        for (int i = 1; i < 8; ++i)
+            dst[i] = make_uint4(0, 0, 0, 0);
+        b.dc[im.blk_first + blk] = int16_t(dcq);
+        b.acbits[im.blk_first + blk] = uint16_t(s_aclen[comp ? 1 : 0][0]); // EOB only
+        return;
+    }
+    int16_t zz[64];
+    enc_fdct_quant(rows, qt, zz);
+    // entropy-coded length of the AC part (same walk as the emit kernel, lengths only)
+    const uint8_t* aclen = s_aclen[comp ? 1 : 0];
     uint32_t acbits = 0;
-    if (real) {
-        uint32_t rows[16];
-        const uint8_t* src = comp == 0 ? s_y + (by * 8) * tw + (m * mw + bx) * 8 : s_c[comp - 1] + m * 8;
-        const int pitch = comp == 0 ? tw : cw;
+    int run = 0;
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const uint2 v = *reinterpret_cast<const uint2*>(src + r * pitch);
-            rows[2 * r] = v.x;
-            rows[2 * r + 1] = v.y;
+    for (int k = 1; k < 64; ++k) {
+        const int v = zz[k];
+        if (v == 0) {
+            ++run;
+        } else {
+            acbits += uint32_t(run >> 4) * aclen[0xF0];
+            const int n = enc_category(v);
+            acbits += uint32_t(aclen[(run & 15) * 16 + n]) + uint32_t(n);
+            run = 0;
         }
-        int16_t zz[64];
-        enc_fdct_quant(rows, s_q[comp ? 1 : 0], zz);
-        // entropy-coded length of the AC part (same walk as the emit kernel, lengths only)
-        const uint8_t* aclen = s_aclen[comp ? 1 : 0];
-        int run = 0;
-#pragma unroll
-        for (int k = 1; k < 64; ++k) {
-            const int v = zz[k];
-            if (v == 0) {
-                ++run;
-            } else {
-                acbits += uint32_t(run >> 4) * aclen[0xF0];
-                const int n = enc_category(v);
-                acbits += uint32_t(aclen[(run & 15) * 16 + n]) + uint32_t(n);
-                run = 0;
-            }
-        }
-        if (run)
-            acbits += aclen[0];
-#pragma unroll
-        for (int k = 0; k < 32; ++k)
-            my_coef[k] = uint32_t(uint16_t(zz[2 * k])) | (uint32_t(uint16_t(zz[2 * k + 1])) << 16);
-    } else if (active) {
-#pragma unroll
-        for (int k = 0; k < 32; ++k)
-            my_coef[k] = 0;
-        acbits = s_aclen[comp ? 1 : 0][0]; // EOB only
     }
-    __syncthreads();
-    if (active && !real) {
-        // dummy block (ljt/jccoefct.c:176-196): DC of the block before it in the MCU; a whole dummy row copies the block
-        // before the row.  The source may itself be a dummy of the first kind; blocks at (0, 0) of a component are real.
-        int sj = jj;
-        for (;;) {
-            const int sby = sj / mw, sbx = sj - sby * mw;
-            const bool row_dummy = my * mh + sby >= im.hib[comp];
-            const bool col_dummy = (mx0 + m) * mw + sbx >= im.wib[comp];
-            if (!row_dummy && !col_dummy)
-                break;
-            sj = row_dummy ? sby * mw - 1 : sj - 1;
-        }
-        const uint32_t dcv = s_coef[(m * im.bpm + first_j + sj) * kEncCoefPitch] & 0xFFFFu;
-        my_coef[0] = dcv;
+    if (run)
+        acbits += aclen[0];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        uint32_t w[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            w[k] = uint32_t(uint16_t(zz[8 * i + 2 * k])) | (uint32_t(uint16_t(zz[8 * i + 2 * k + 1])) << 16);
+        dst[i] = make_uint4(w[0], w[1], w[2], w[3]);
     }
-    __syncthreads();
-    // ---- coalesced copy-out ----
-    const uint64_t blk0 = im.blk_first + (uint64_t(my) * uint64_t(im.mcus_x) + uint64_t(mx0)) * uint64_t(im.bpm);
-    uint32_t* gcoef = reinterpret_cast<uint32_t*>(b.coef + blk0 * 64);
-    for (int i = threadIdx.x; i < nblocks * 32; i += kEncCta)
-        gcoef[i] = s_coef[(i >> 5) * kEncCoefPitch + (i & 31)];
-    if (active) {
-        b.dc[blk0 + t] = int16_t(my_coef[0] & 0xFFFFu);
-        b.acbits[blk0 + t] = uint16_t(acbits);
-    }
+    b.dc[im.blk_first + blk] = zz[0];
+    b.acbits[im.blk_first + blk] = uint16_t(acbits);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -643,8 +656,9 @@ __global__ void __launch_bounds__(kEncStuffThreads) k_enc_stuff_write(EncBatchDe
 // ------------------------------------------------------------------------------------------------------------------
 int launch_enc_dct(const EncBatchDev& b, const EncLaunchDims& d, cudaStream_t st)
 {
-    k_enc_dct<<<d.dct_ctas, kEncCta, 0, st>>>(b);
-    return 1;
+    k_enc_color<<<d.color_ctas, kEncColorCta, 0, st>>>(b);
+    k_enc_fdct<<<d.emit_ctas, kEncCta, 0, st>>>(b);
+    return 2;
 }
 
 int launch_enc_scan(const EncBatchDev& b, const EncLaunchDims& d, cudaStream_t st)

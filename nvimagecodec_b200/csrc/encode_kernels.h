@@ -8,7 +8,7 @@ namespace b200jpeg {
 struct EncLaunchDims
 {
     int num_images = 0;
-    uint32_t dct_ctas = 0, emit_ctas = 0, stuff_ctas = 0, total_segments = 0;
+    uint32_t color_ctas = 0, emit_ctas = 0, stuff_ctas = 0, total_segments = 0;
 };
 
 // each returns the number of kernels it launched

@@ -77,7 +77,7 @@ struct Encoder::Impl
     cudaEvent_t ev_in = nullptr, ev_meta = nullptr;
     cudaEvent_t ev_half[kEncGroups] = {}, ev_sizes[kEncGroups] = {}, ev_done[kEncGroups] = {};
     cudaEvent_t ev[8] = {};
-    Buf d_pixels, d_meta, d_dyn, d_coef, d_dc, d_acbits, d_blk_off, d_seg_bits, d_seg_off, d_img_bytes;
+    Buf d_pixels, d_planes, d_meta, d_dyn, d_coef, d_dc, d_acbits, d_blk_off, d_seg_bits, d_seg_off, d_img_bytes;
     Buf d_stream[kEncGroups], d_chunks[kEncGroups], d_out[kEncGroups]; // per group: they grow while other groups are in flight
     Buf h_pixels, h_meta, h_dyn, h_sizes, h_out;
     uint64_t stats[8] = {};
@@ -119,7 +119,7 @@ Encoder::~Encoder()
 {
     Impl& s = *impl_;
     cudaSetDevice(s.device);
-    Buf* dev[] = {&s.d_pixels, &s.d_meta, &s.d_dyn, &s.d_coef, &s.d_dc, &s.d_acbits, &s.d_blk_off, &s.d_seg_bits, &s.d_seg_off, &s.d_img_bytes};
+    Buf* dev[] = {&s.d_pixels, &s.d_planes, &s.d_meta, &s.d_dyn, &s.d_coef, &s.d_dc, &s.d_acbits, &s.d_blk_off, &s.d_seg_bits, &s.d_seg_off, &s.d_img_bytes};
     for (Buf* b : dev)
         if (b->p)
             cudaFree(b->p);
@@ -197,6 +197,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     std::vector<size_t> host_pix_off; // staging offset of host inputs (SIZE_MAX for device inputs)
     size_t host_pix_bytes = 0;
     uint64_t total_blocks = 0, in_bytes = 0;
+    size_t plane_bytes = 0;
     for (int i = 0; i < n; ++i) {
         out_sizes[i] = 0;
         statuses[i] = B200JPEG_STATUS_SUCCESS;
@@ -232,11 +233,19 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
         enc_build_quant(in[i].quality, 1, quant.back());
         headers.emplace_back();
         enc_write_headers(im, quant[im.qt], quant[im.qt + 1], headers.back());
-        im.dct_cta_first = map_dct.back();
+        im.color_cta_first = map_dct.back();
+        {
+            const size_t ybytes = size_t(im.plane_pitch[0]) * size_t(im.mcus_y) * 8 * (im.ncomp == 3 ? im.vs : 1);
+            const size_t cbytes = size_t(im.plane_pitch[1]) * size_t(im.mcus_y) * 8;
+            im.plane_off[0] = plane_bytes;
+            im.plane_off[1] = im.plane_off[0] + align_up(ybytes, 256);
+            im.plane_off[2] = im.plane_off[1] + align_up(cbytes, 256);
+            plane_bytes = im.plane_off[2] + align_up(cbytes, 256);
+        }
         im.emit_cta_first = map_emit.back();
         im.blk_first = total_blocks;
         im.seg_first = total_segs;
-        map_dct.push_back(map_dct.back() + uint32_t(im.tiles_per_row) * uint32_t(im.mcus_y));
+        map_dct.push_back(map_dct.back() + uint32_t((uint64_t(im.plane_pitch[0] / 4) * uint64_t(im.mcus_y) * 8 + kEncColorCta - 1) / kEncColorCta));
         map_emit.push_back(map_emit.back() + (im.total_blocks + kEncCta - 1) / kEncCta);
         total_segs += im.num_segments;
         total_blocks += im.total_blocks;
@@ -275,7 +284,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     const size_t dyn_arr_bytes = align_up(sizeof(EncImageDyn) * m, 256);
     const size_t dyn_bytes = dyn_arr_bytes + sizeof(uint32_t) * (m + G); // per group a chunk map of (images + 1) entries
     if ((rc = s.ensure(s.d_meta, meta_bytes, false)) || (rc = s.ensure(s.h_meta, meta_bytes, true)) || (rc = s.ensure(s.d_dyn, dyn_bytes, false)) ||
-        (rc = s.ensure(s.h_dyn, dyn_bytes, true)) || (rc = s.ensure(s.d_coef, total_blocks * 128, false)) ||
+        (rc = s.ensure(s.h_dyn, dyn_bytes, true)) || (rc = s.ensure(s.d_coef, total_blocks * 128, false)) || (rc = s.ensure(s.d_planes, plane_bytes, false)) ||
         (rc = s.ensure(s.d_dc, total_blocks * 2, false)) || (rc = s.ensure(s.d_acbits, total_blocks * 2, false)) ||
         (rc = s.ensure(s.d_blk_off, total_blocks * 4, false)) ||
         (rc = s.ensure(s.d_seg_bits, size_t(map_emit.back()) * 4 + size_t(m) * 4, false)) ||
@@ -320,6 +329,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
         b.num_images = cnt;
         b.quant = reinterpret_cast<const EncQuantTable*>(dm + off_quant);
         b.huff = reinterpret_cast<const EncHuffTables*>(dm + off_huff);
+        b.planes = static_cast<uint8_t*>(s.d_planes.p);
         b.coef = static_cast<int16_t*>(s.d_coef.p);
         b.dc = static_cast<int16_t*>(s.d_dc.p);
         b.acbits = static_cast<uint16_t*>(s.d_acbits.p);
@@ -329,17 +339,17 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
         b.seg_byte_off = static_cast<uint32_t*>(s.d_seg_off.p);
         b.img_stream_bytes = static_cast<uint32_t*>(s.d_img_bytes.p) + k0;
         b.img_out_bytes = static_cast<uint32_t*>(s.d_img_bytes.p) + m + k0;
-        b.cta_map_dct = reinterpret_cast<const uint32_t*>(dm + off_maps) + k0;
+        b.cta_map_color = reinterpret_cast<const uint32_t*>(dm + off_maps) + k0;
         b.cta_map_emit = reinterpret_cast<const uint32_t*>(dm + off_maps + map_bytes) + k0;
         b.cta_map_stuff = reinterpret_cast<const uint32_t*>(static_cast<uint8_t*>(s.d_dyn.p) + dyn_arr_bytes) + k0 + g;
-        b.cta_base_dct = map_dct[k0];
+        b.cta_base_color = map_dct[k0];
         b.cta_base_emit = map_emit[k0];
         b.stream = static_cast<uint8_t*>(s.d_stream[g].p);
         b.out = static_cast<uint8_t*>(s.d_out[g].p);
         b.chunk_out = static_cast<uint32_t*>(s.d_chunks[g].p);
         d = EncLaunchDims{};
         d.num_images = cnt;
-        d.dct_ctas = map_dct[k0 + cnt] - map_dct[k0];
+        d.color_ctas = map_dct[k0 + cnt] - map_dct[k0];
         d.emit_ctas = map_emit[k0 + cnt] - map_emit[k0];
     };
 
