@@ -157,6 +157,43 @@ B2J_HD void enc_put_ac(const Get& get, const uint32_t* ac_tab, Sink& sink)
     }
 }
 
+// The same AC part driven by the block's non-zero mask (bit k = coefficient at zigzag position k is non-zero): one loop
+// iteration per non-zero coefficient instead of a test of all 63 positions.
+B2J_HD int enc_lowest_bit(uint64_t m) // index of the lowest set bit, m != 0
+{
+#if defined(__CUDA_ARCH__)
+    return __ffsll((long long)m) - 1;
+#else
+    return __builtin_ctzll(m);
+#endif
+}
+
+template <class Sink, class Get>
+B2J_HD void enc_put_ac_sparse(uint64_t mask, const Get& get, const uint32_t* ac_tab, Sink& sink)
+{
+    int prev = 0;
+    mask &= ~uint64_t(1);
+    while (mask) {
+        const int k = enc_lowest_bit(mask);
+        mask &= mask - 1;
+        int run = k - prev - 1;
+        prev = k;
+        for (; run > 15; run -= 16) {
+            const uint32_t z = ac_tab[0xF0];
+            sink.put(z >> 8, int(z & 255u));
+        }
+        const int v = get(k);
+        const int n = enc_category(v);
+        const uint32_t e = ac_tab[run * 16 + n];
+        const uint32_t vbits = uint32_t(v < 0 ? v - 1 : v) & ((1u << n) - 1u);
+        sink.put(((e >> 8) << n) | vbits, int(e & 255u) + n);
+    }
+    if (prev != 63) {
+        const uint32_t e = ac_tab[0];
+        sink.put(e >> 8, int(e & 255u));
+    }
+}
+
 struct EncBitCounter
 {
     uint32_t bits = 0;
@@ -171,12 +208,19 @@ struct EncWordSink
     uint32_t widx;
     uint64_t acc; // bits left-aligned
     int n;        // valid bits in acc
+    bool first;   // the next word written is the first one: its leading bits may belong to the previous block
     B2J_HD void start(uint32_t* w, uint32_t bitpos)
     {
         words = w;
         widx = bitpos >> 5;
         acc = 0;
         n = int(bitpos & 31u);
+        first = true;
+    }
+    B2J_HD void set_word(uint32_t v) // a word in the middle of the block's bits: nobody else writes it
+    {
+        words[widx] = v;
+        ++widx;
     }
     B2J_HD void or_word(uint32_t v)
     {
@@ -194,7 +238,11 @@ struct EncWordSink
         acc |= uint64_t(code) << (64 - n - len);
         n += len;
         if (n >= 32) {
-            or_word(uint32_t(acc >> 32));
+            if (first)
+                or_word(uint32_t(acc >> 32));
+            else
+                set_word(uint32_t(acc >> 32));
+            first = false;
             acc <<= 32;
             n -= 32;
         }

@@ -79,6 +79,7 @@ struct EncBatchDev
     int16_t* coef;            // quantised coefficients, zigzag order, 64 per block, MCU scan order
     int16_t* dc;              // per block: quantised DC
     uint16_t* acbits;         // per block: entropy-coded bits of the AC part
+    uint64_t* nzmask;         // per block: bit k = the coefficient at zigzag position k is non-zero
     uint32_t* blk_off;        // per block: bit offset inside its tile (the kEncCta blocks of one emit CTA)
     uint32_t* tile_off;       // per emit CTA: bits of the image's blocks before the tile
     uint32_t* img_bits;       // per image: bits of all blocks

@@ -233,13 +233,14 @@ __global__ void __launch_bounds__(kEncCta, 4) k_enc_fdct(EncBatchDev b)
             dst[i] = make_uint4(0, 0, 0, 0);
         b.dc[im.blk_first + blk] = int16_t(dcq);
         b.acbits[im.blk_first + blk] = uint16_t(s_aclen[comp ? 1 : 0][0]); // EOB only
+        b.nzmask[im.blk_first + blk] = 0;
         return;
     }
     int16_t zz[64];
     enc_fdct_quant(rows, qt, zz);
     // entropy-coded length of the AC part (same walk as the emit kernel, lengths only)
     const uint8_t* aclen = s_aclen[comp ? 1 : 0];
-    uint32_t acbits = 0;
+    uint32_t acbits = 0, mlo = 0, mhi = 0;
     int run = 0;
 #pragma unroll
     for (int k = 1; k < 64; ++k) {
@@ -251,10 +252,15 @@ __global__ void __launch_bounds__(kEncCta, 4) k_enc_fdct(EncBatchDev b)
             const int n = enc_category(v);
             acbits += uint32_t(aclen[(run & 15) * 16 + n]) + uint32_t(n);
             run = 0;
+            if (k < 32)
+                mlo |= 1u << k;
+            else
+                mhi |= 1u << (k - 32);
         }
     }
     if (run)
         acbits += aclen[0];
+    b.nzmask[im.blk_first + blk] = uint64_t(mlo) | (uint64_t(mhi) << 32);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         uint32_t w[4];
@@ -411,13 +417,68 @@ __global__ void __launch_bounds__(kEncSegScanThreads) k_enc_segscan(EncBatchDev 
 // ------------------------------------------------------------------------------------------------------------------
 // E4: Huffman emit
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int kEncWindowWords = (kEncCta * kEncMaxBlockBytes) / 4 + 8;
+// The CTA's window of the stream in shared memory: 64 bytes per block on average, i.e. any tile whose blocks average no more
+// than 512 bits (anything but near-lossless qualities).  A tile that needs more ORs its bits straight into global memory.
+constexpr int kEncWindowWords = kEncCta * 16 + 8;
 
-struct CoefRegs
+// Same interface as EncWordSink; the words go to the (zeroed) global stream in stream byte order, all by atomicOr.
+struct EncGlobalSink
 {
-    uint32_t w[32];
-    __device__ __forceinline__ int operator()(int k) const { return int(int16_t((k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xFFFFu))); }
+    uint32_t* words;
+    uint32_t widx;
+    uint64_t acc;
+    int n;
+    __device__ __forceinline__ void start(uint32_t* w, uint32_t bitpos)
+    {
+        words = w;
+        widx = bitpos >> 5;
+        acc = 0;
+        n = int(bitpos & 31u);
+    }
+    __device__ __forceinline__ void or_word(uint32_t v)
+    {
+        if (v)
+            atomicOr(words + widx, __byte_perm(v, 0, 0x0123));
+        ++widx;
+    }
+    __device__ __forceinline__ void put(uint32_t code, int len)
+    {
+        acc |= uint64_t(code) << (64 - n - len);
+        n += len;
+        if (n >= 32) {
+            or_word(uint32_t(acc >> 32));
+            acc <<= 32;
+            n -= 32;
+        }
+    }
+    __device__ __forceinline__ void finish()
+    {
+        if (n)
+            or_word(uint32_t(acc >> 32));
+    }
 };
+
+template <class Sink>
+__device__ __forceinline__ void enc_emit_block(const EncBatchDev& b, const EncImageDesc& im, uint32_t blk, const uint32_t (*s_dc)[16],
+    const uint32_t (*s_ac)[256], Sink& sink)
+{
+    const int16_t* cf = b.coef + (im.blk_first + blk) * 64; // one 128-byte line: read through L1, non-zero positions only
+    const uint64_t mask = b.nzmask[im.blk_first + blk];
+    const int j = int(blk % uint32_t(im.bpm));
+    int comp, first_j, count;
+    enc_block_comp(im, j, comp, first_j, count);
+    const int tsel = comp ? 1 : 0;
+    enc_put_dc(enc_dc_diff(b, im, blk), s_dc[tsel], sink);
+    enc_put_ac_sparse(mask, [cf](int k) { return int(__ldg(cf + k)); }, s_ac[tsel], sink);
+    // last block of a restart segment (or of the image): fill the byte with 1-bits (ljt/jchuff.c flush_bits:480)
+    const bool seg_last = (blk + 1 == im.total_blocks) || ((blk + 1) % im.seg_blocks == 0);
+    if (seg_last) {
+        const int used = sink.n & 7; // the window starts on a 32-bit boundary of a byte-aligned stream
+        if (used)
+            sink.put((1u << (8 - used)) - 1u, 8 - used);
+    }
+    sink.finish();
+}
 
 __global__ void __launch_bounds__(kEncCta) k_enc_emit(EncBatchDev b)
 {
@@ -431,6 +492,8 @@ __global__ void __launch_bounds__(kEncCta) k_enc_emit(EncBatchDev b)
     const uint32_t cta = cta_abs - b.cta_map_emit[img];
     const uint32_t blk0 = cta * kEncCta, blk = blk0 + threadIdx.x;
     const uint32_t blk_end = min(blk0 + kEncCta, im.total_blocks);
+    if (blk < blk_end) // start fetching the block's coefficient line; it is first needed after the set-up below
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(b.coef + (im.blk_first + blk) * 64));
     for (int i = threadIdx.x; i < 512; i += kEncCta)
         s_ac[i >> 8][i & 255] = b.huff->ac[i >> 8][i & 255];
     if (threadIdx.x < 32)
@@ -440,42 +503,38 @@ __global__ void __launch_bounds__(kEncCta) k_enc_emit(EncBatchDev b)
     const uint64_t win_lo_bit = bitpos(blk0) & ~uint64_t(31);
     const uint64_t win_hi_bit = blk_end == im.total_blocks ? uint64_t(dy.stream_bytes) * 8u : bitpos(blk_end);
     const uint32_t win_words = uint32_t((win_hi_bit - win_lo_bit + 31u) >> 5);
-    for (uint32_t i = threadIdx.x; i < win_words; i += kEncCta)
-        s_win[i] = 0;
+    const bool in_smem = win_words <= uint32_t(kEncWindowWords);
+    const bool last_shared = (win_hi_bit & 31u) != 0; // the last word continues in the next tile (or is the image's last)
+    uint32_t* gw = reinterpret_cast<uint32_t*>(b.stream + dy.stream_off) + (win_lo_bit >> 5);
+    if (in_smem) {
+        for (uint32_t i = threadIdx.x; i < win_words; i += kEncCta)
+            s_win[i] = 0;
+    } else { // the words only this tile writes; k_enc_zero_edges cleared the shared ones
+        for (uint32_t i = 1 + threadIdx.x; i < win_words; i += kEncCta)
+            if (!(i + 1 == win_words && last_shared))
+                gw[i] = 0;
+    }
     __syncthreads();
     if (blk < blk_end) {
-        CoefRegs c;
-        const uint4* src = reinterpret_cast<const uint4*>(b.coef + (im.blk_first + blk) * 64);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const uint4 v = src[i];
-            c.w[4 * i] = v.x; c.w[4 * i + 1] = v.y; c.w[4 * i + 2] = v.z; c.w[4 * i + 3] = v.w;
+        const uint32_t rel = uint32_t(bitpos(blk) - win_lo_bit);
+        if (in_smem) {
+            EncWordSink sink;
+            sink.start(s_win, rel);
+            enc_emit_block(b, im, blk, s_dc, s_ac, sink);
+        } else {
+            EncGlobalSink sink;
+            sink.start(gw, rel);
+            enc_emit_block(b, im, blk, s_dc, s_ac, sink);
         }
-        const int j = int(blk % uint32_t(im.bpm));
-        int comp, first_j, count;
-        enc_block_comp(im, j, comp, first_j, count);
-        const int tsel = comp ? 1 : 0;
-        EncWordSink sink;
-        const uint64_t pos = bitpos(blk);
-        sink.start(s_win, uint32_t(pos - win_lo_bit));
-        enc_put_dc(enc_dc_diff(b, im, blk), s_dc[tsel], sink);
-        enc_put_ac(c, s_ac[tsel], sink);
-        // last block of a restart segment (or of the image): fill the byte with 1-bits (ljt/jchuff.c flush_bits:480)
-        const bool seg_last = (blk + 1 == im.total_blocks) || ((blk + 1) % im.seg_blocks == 0);
-        if (seg_last) {
-            const int used = sink.n & 7; // the window starts on a 32-bit boundary of a byte-aligned stream
-            if (used)
-                sink.put((1u << (8 - used)) - 1u, 8 - used);
-        }
-        sink.finish();
     }
+    if (!in_smem)
+        return;
     __syncthreads();
     // window -> global stream (bytes in stream order): interior words plain, the two edge words may be shared with the
     // neighbouring CTAs' windows -> atomicOr on memory the zeroing kernel cleared
-    uint32_t* gw = reinterpret_cast<uint32_t*>(b.stream + dy.stream_off) + (win_lo_bit >> 5);
     for (uint32_t i = threadIdx.x; i < win_words; i += kEncCta) {
         const uint32_t v = __byte_perm(s_win[i], 0, 0x0123);
-        if (i == 0 || (i + 1 == win_words && (win_hi_bit & 31u)))
+        if (i == 0 || (i + 1 == win_words && last_shared))
             atomicOr(gw + i, v);
         else
             gw[i] = v;

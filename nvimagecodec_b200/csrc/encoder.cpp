@@ -77,7 +77,7 @@ struct Encoder::Impl
     cudaEvent_t ev_in = nullptr, ev_meta = nullptr;
     cudaEvent_t ev_half[kEncGroups] = {}, ev_sizes[kEncGroups] = {}, ev_done[kEncGroups] = {};
     cudaEvent_t ev[8] = {};
-    Buf d_pixels, d_planes, d_meta, d_dyn, d_coef, d_dc, d_acbits, d_blk_off, d_seg_bits, d_seg_off, d_img_bytes;
+    Buf d_nzmask, d_pixels, d_planes, d_meta, d_dyn, d_coef, d_dc, d_acbits, d_blk_off, d_seg_bits, d_seg_off, d_img_bytes;
     Buf d_stream[kEncGroups], d_chunks[kEncGroups], d_out[kEncGroups]; // per group: they grow while other groups are in flight
     Buf h_pixels, h_meta, h_dyn, h_sizes, h_out;
     uint64_t stats[8] = {};
@@ -119,7 +119,7 @@ Encoder::~Encoder()
 {
     Impl& s = *impl_;
     cudaSetDevice(s.device);
-    Buf* dev[] = {&s.d_pixels, &s.d_planes, &s.d_meta, &s.d_dyn, &s.d_coef, &s.d_dc, &s.d_acbits, &s.d_blk_off, &s.d_seg_bits, &s.d_seg_off, &s.d_img_bytes};
+    Buf* dev[] = {&s.d_nzmask, &s.d_pixels, &s.d_planes, &s.d_meta, &s.d_dyn, &s.d_coef, &s.d_dc, &s.d_acbits, &s.d_blk_off, &s.d_seg_bits, &s.d_seg_off, &s.d_img_bytes};
     for (Buf* b : dev)
         if (b->p)
             cudaFree(b->p);
@@ -198,6 +198,9 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     size_t host_pix_bytes = 0;
     uint64_t total_blocks = 0, in_bytes = 0;
     size_t plane_bytes = 0;
+    int prev_quality = -1;
+    images.reserve(n);
+    headers.reserve(n);
     for (int i = 0; i < n; ++i) {
         out_sizes[i] = 0;
         statuses[i] = B200JPEG_STATUS_SUCCESS;
@@ -226,13 +229,23 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
         } else {
             host_pix_off.push_back(SIZE_MAX);
         }
-        im.qt = int32_t(quant.size());
-        quant.emplace_back();
-        enc_build_quant(in[i].quality, 0, quant.back());
-        quant.emplace_back();
-        enc_build_quant(in[i].quality, 1, quant.back());
-        headers.emplace_back();
-        enc_write_headers(im, quant[im.qt], quant[im.qt + 1], headers.back());
+        // tables and header bytes depend on (quality, geometry) only: a run of equal images shares them
+        const bool same = !images.empty() && prev_quality == in[i].quality && images.back().width == im.width && images.back().height == im.height &&
+            images.back().ncomp == im.ncomp && images.back().hs == im.hs && images.back().vs == im.vs &&
+            images.back().restart_interval == im.restart_interval;
+        if (same) {
+            im.qt = images.back().qt;
+            headers.push_back(headers.back());
+        } else {
+            im.qt = int32_t(quant.size());
+            quant.emplace_back();
+            enc_build_quant(in[i].quality, 0, quant.back());
+            quant.emplace_back();
+            enc_build_quant(in[i].quality, 1, quant.back());
+            headers.emplace_back();
+            enc_write_headers(im, quant[im.qt], quant[im.qt + 1], headers.back());
+        }
+        prev_quality = in[i].quality;
         im.color_cta_first = map_dct.back();
         {
             const size_t ybytes = size_t(im.plane_pitch[0]) * size_t(im.mcus_y) * 8 * (im.ncomp == 3 ? im.vs : 1);
@@ -260,13 +273,17 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     // ---- groups of consecutive images, balanced by blocks; each runs on its own stream so that the uploads, the two
     // host round trips (stream sizes, stuffed sizes) and the copy-out of one group overlap the kernels of the others ----
     const int G = s.profile ? 1 : std::max(1, std::min(s.groups, m));
+    // The groups shrink (weights G+1, G, .., 2): what is left when the GPU is done is the last group's copy-out.
     std::vector<int> gfirst(G + 1, m);
     gfirst[0] = 0;
     {
         int k = 0;
-        uint64_t acc = 0;
+        uint64_t acc = 0, wsum = 0, wtot = 0;
+        for (int g = 0; g < G; ++g)
+            wtot += uint64_t(G + 1 - g);
         for (int g = 1; g < G; ++g) {
-            const uint64_t target = total_blocks * uint64_t(g) / uint64_t(G);
+            wsum += uint64_t(G + 2 - g);
+            const uint64_t target = total_blocks * wsum / wtot;
             while (k < m - (G - g) && (k < gfirst[g - 1] + 1 || acc + images[k].total_blocks / 2 <= target))
                 acc += images[k++].total_blocks;
             gfirst[g] = k;
@@ -285,7 +302,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     const size_t dyn_bytes = dyn_arr_bytes + sizeof(uint32_t) * (m + G); // per group a chunk map of (images + 1) entries
     if ((rc = s.ensure(s.d_meta, meta_bytes, false)) || (rc = s.ensure(s.h_meta, meta_bytes, true)) || (rc = s.ensure(s.d_dyn, dyn_bytes, false)) ||
         (rc = s.ensure(s.h_dyn, dyn_bytes, true)) || (rc = s.ensure(s.d_coef, total_blocks * 128, false)) || (rc = s.ensure(s.d_planes, plane_bytes, false)) ||
-        (rc = s.ensure(s.d_dc, total_blocks * 2, false)) || (rc = s.ensure(s.d_acbits, total_blocks * 2, false)) ||
+        (rc = s.ensure(s.d_dc, total_blocks * 2, false)) || (rc = s.ensure(s.d_acbits, total_blocks * 2, false)) || (rc = s.ensure(s.d_nzmask, total_blocks * 8, false)) ||
         (rc = s.ensure(s.d_blk_off, total_blocks * 4, false)) ||
         (rc = s.ensure(s.d_seg_bits, size_t(map_emit.back()) * 4 + size_t(m) * 4, false)) ||
         (rc = s.ensure(s.d_seg_off, size_t(total_segs) * 4, false)) || (rc = s.ensure(s.d_img_bytes, size_t(m) * 8, false)) ||
@@ -333,6 +350,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
         b.coef = static_cast<int16_t*>(s.d_coef.p);
         b.dc = static_cast<int16_t*>(s.d_dc.p);
         b.acbits = static_cast<uint16_t*>(s.d_acbits.p);
+        b.nzmask = static_cast<uint64_t*>(s.d_nzmask.p);
         b.blk_off = static_cast<uint32_t*>(s.d_blk_off.p);
         b.tile_off = static_cast<uint32_t*>(s.d_seg_bits.p);
         b.img_bits = b.tile_off + map_emit.back() + k0;

@@ -151,7 +151,17 @@ extern "C" long emu_encode(const uint8_t* pixels, int width, int height, int for
             EncWordSink sink;
             sink.start(win.data(), uint32_t(bitpos(blk) - lo));
             enc_put_dc(dc_diff(blk), huff.dc[comp ? 1 : 0], sink);
-            enc_put_ac(Coef64{coef.data() + size_t(blk) * 64}, huff.ac[comp ? 1 : 0], sink);
+            {
+                const Coef64 get{coef.data() + size_t(blk) * 64};
+                uint64_t mask = 0;
+                for (int k = 1; k < 64; ++k)
+                    if (get(k))
+                        mask |= uint64_t(1) << k;
+                if (blk & 1) // both statements of the AC walk: the one that tests every position and the mask-driven one
+                    enc_put_ac(get, huff.ac[comp ? 1 : 0], sink);
+                else
+                    enc_put_ac_sparse(mask, get, huff.ac[comp ? 1 : 0], sink);
+            }
             if (blk + 1 == nb || (blk + 1) % im.seg_blocks == 0) {
                 const int used = sink.n & 7;
                 if (used)

@@ -54,6 +54,8 @@ def test_encode_gray_noise_and_golden_md5(enc):
     noise = np.random.default_rng(1).integers(0, 256, (95, 130, 3), dtype=np.uint8)
     for samp, name in CSS.items():
         assert enc.encode(noise, ".jpg", EncodeParams(quality=100, chroma_subsampling=name)) == want(noise, 100, samp, 0)
+        # > 512 bits per block: the emit kernel's tiles do not fit their shared-memory window and write to global memory
+        assert enc.encode(noise, ".jpg", EncodeParams(quality=98, chroma_subsampling=name, restart_interval=2)) == want(noise, 98, samp, 2)
     md5 = json.load(open(os.path.join(GOLDEN, "golden.json")))["ljt_md5"]
     raw = open(os.path.join(GOLDEN, "testorig.ppm"), "rb").read()
     t = np.frombuffer(raw.split(b"\n", 3)[3], dtype=np.uint8).reshape(149, 227, 3)
