@@ -36,31 +36,41 @@ __device__ __forceinline__ int enc_find_image(const uint32_t* __restrict__ map, 
 // E1a: colour conversion + downsampling -> component planes padded to whole MCUs
 // ------------------------------------------------------------------------------------------------------------------
 // Four pixels of one source row (x clamped to the last column: expand_right_edge; the caller clamps the row).
-__device__ __forceinline__ void enc_load_rgb4(const EncImageDesc& im, int y, int sx, bool aligned4, uint32_t* r, uint32_t* g, uint32_t* bl)
+// The source image as the colour kernel needs it, copied out of the descriptor once (the kernel's stores could alias the
+// descriptor as far as the compiler knows, and it would re-read it after every store).
+struct EncSrc
+{
+    const uint8_t* __restrict__ pixels;
+    int64_t stride;
+    int width, height, in_fmt;
+    bool aligned4;
+};
+
+__device__ __forceinline__ void enc_load_rgb4(const EncSrc& im, int y, int sx, bool aligned4, uint32_t* r, uint32_t* g, uint32_t* bl)
 {
     const int W = im.width;
     const uint8_t* row = im.pixels + int64_t(y) * im.stride;
     if (im.in_fmt == 4) { // B200JPEG_FMT_I_RGB
         if (sx + 3 < W && aligned4) {
             const uint32_t* p = reinterpret_cast<const uint32_t*>(row + sx * 3);
-            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
-            r[0] = w0 & 255u; g[0] = (w0 >> 8) & 255u; bl[0] = (w0 >> 16) & 255u;
-            r[1] = w0 >> 24; g[1] = w1 & 255u; bl[1] = (w1 >> 8) & 255u;
-            r[2] = (w1 >> 16) & 255u; g[2] = w1 >> 24; bl[2] = w2 & 255u;
-            r[3] = (w2 >> 8) & 255u; g[3] = (w2 >> 16) & 255u; bl[3] = w2 >> 24;
+            const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+            r[0] = __byte_perm(w0, 0, 0x4440); g[0] = __byte_perm(w0, 0, 0x4441); bl[0] = __byte_perm(w0, 0, 0x4442);
+            r[1] = __byte_perm(w0, 0, 0x4443); g[1] = __byte_perm(w1, 0, 0x4440); bl[1] = __byte_perm(w1, 0, 0x4441);
+            r[2] = __byte_perm(w1, 0, 0x4442); g[2] = __byte_perm(w1, 0, 0x4443); bl[2] = __byte_perm(w2, 0, 0x4440);
+            r[3] = __byte_perm(w2, 0, 0x4441); g[3] = __byte_perm(w2, 0, 0x4442); bl[3] = __byte_perm(w2, 0, 0x4443);
         } else {
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const uint8_t* p = row + min(sx + i, W - 1) * 3;
-                r[i] = p[0]; g[i] = p[1]; bl[i] = p[2];
+                r[i] = __ldg(p); g[i] = __ldg(p + 1); bl[i] = __ldg(p + 2);
             }
         }
     } else { // planar RGB
         const int64_t plane_stride = im.stride * int64_t(im.height);
         if (sx + 3 < W && aligned4) {
-            const uint32_t wr = *reinterpret_cast<const uint32_t*>(row + sx);
-            const uint32_t wg = *reinterpret_cast<const uint32_t*>(row + plane_stride + sx);
-            const uint32_t wb = *reinterpret_cast<const uint32_t*>(row + 2 * plane_stride + sx);
+            const uint32_t wr = __ldg(reinterpret_cast<const uint32_t*>(row + sx));
+            const uint32_t wg = __ldg(reinterpret_cast<const uint32_t*>(row + plane_stride + sx));
+            const uint32_t wb = __ldg(reinterpret_cast<const uint32_t*>(row + 2 * plane_stride + sx));
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 r[i] = (wr >> (8 * i)) & 255u; g[i] = (wg >> (8 * i)) & 255u; bl[i] = (wb >> (8 * i)) & 255u;
@@ -69,7 +79,7 @@ __device__ __forceinline__ void enc_load_rgb4(const EncImageDesc& im, int y, int
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int x = min(sx + i, W - 1);
-                r[i] = row[x]; g[i] = row[plane_stride + x]; bl[i] = row[2 * plane_stride + x];
+                r[i] = __ldg(row + x); g[i] = __ldg(row + plane_stride + x); bl[i] = __ldg(row + 2 * plane_stride + x);
             }
         }
     }
@@ -79,12 +89,21 @@ __device__ __forceinline__ void enc_load_rgb4(const EncImageDesc& im, int y, int
 // Rows past the image repeat the last row (expand_bottom_edge before downsampling); chroma rows past the last row group
 // repeat that group's result (expand_bottom_edge after downsampling), so their source rows differ from the luma rows.
 template <int HS, int VS>
-__device__ __forceinline__ void enc_color_unit(const EncBatchDev& b, const EncImageDesc& im, int ux, int uy)
+__device__ __forceinline__ void enc_color_unit(const EncBatchDev& b, const EncImageDesc& desc, int ux, int uy)
 {
+    EncSrc im;
+    im.pixels = desc.pixels;
+    im.stride = desc.stride;
+    im.width = desc.width;
+    im.height = desc.height;
+    im.in_fmt = desc.in_fmt;
+    const int ncomp = desc.ncomp, pitch_y = desc.plane_pitch[0], pitch_c = desc.plane_pitch[1];
+    uint8_t* const yp = b.planes + desc.plane_off[0];
+    uint8_t* const cbp = b.planes + desc.plane_off[1] + int64_t(uy) * pitch_c;
+    uint8_t* const crp = b.planes + desc.plane_off[2] + int64_t(uy) * pitch_c;
     const int W = im.width, H = im.height, sx = ux * 4;
     const bool aligned4 = ((reinterpret_cast<uintptr_t>(im.pixels) | uint64_t(im.stride)) & 3u) == 0;
-    uint8_t* yp = b.planes + im.plane_off[0];
-    if (im.ncomp == 1) {
+    if (ncomp == 1) {
         const uint8_t* row = im.pixels + int64_t(min(uy, H - 1)) * im.stride;
         uint32_t yv = 0;
         if (sx + 3 < W && aligned4)
@@ -93,7 +112,7 @@ __device__ __forceinline__ void enc_color_unit(const EncBatchDev& b, const EncIm
 #pragma unroll
             for (int i = 0; i < 4; ++i)
                 yv |= uint32_t(row[min(sx + i, W - 1)]) << (8 * i);
-        *reinterpret_cast<uint32_t*>(yp + int64_t(uy) * im.plane_pitch[0] + sx) = yv;
+        *reinterpret_cast<uint32_t*>(yp + int64_t(uy) * pitch_y + sx) = yv;
         return;
     }
     const int rows_ds = (H + VS - 1) / VS;
@@ -108,7 +127,7 @@ __device__ __forceinline__ void enc_color_unit(const EncBatchDev& b, const EncIm
 #pragma unroll
         for (int i = 0; i < 4; ++i)
             yv |= enc_luma(r[i], g[i], bl[i]) << (8 * i);
-        *reinterpret_cast<uint32_t*>(yp + int64_t(uy * VS + dy) * im.plane_pitch[0] + sx) = yv;
+        *reinterpret_cast<uint32_t*>(yp + int64_t(uy * VS + dy) * pitch_y + sx) = yv;
         if (cy != ly)
             enc_load_rgb4(im, cy, sx, aligned4, r, g, bl);
 #pragma unroll
@@ -117,8 +136,6 @@ __device__ __forceinline__ void enc_color_unit(const EncBatchDev& b, const EncIm
             cr[dy][i] = enc_cr(int(r[i]), int(g[i]), int(bl[i]));
         }
     }
-    uint8_t* cbp = b.planes + im.plane_off[1] + int64_t(uy) * im.plane_pitch[1];
-    uint8_t* crp = b.planes + im.plane_off[2] + int64_t(uy) * im.plane_pitch[2];
     if (HS == 2) { // two outputs at even / odd chroma columns: biases 1, 2 (h2v2) or 0, 1 (h2v1)
         uint32_t ob, orr;
         if (VS == 2) {
