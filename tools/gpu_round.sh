@@ -13,11 +13,16 @@ tail -c 600 $out/${tag}_bench.json
 python bench.py --impl reference --steps 3 --warmup 1 > $out/${tag}_bench_ref.json 2> $out/${tag}_bench_ref.err; echo "ref rc=$?"
 python tools/quick_bench.py 64 8 > $out/${tag}_quick.log 2>&1; echo "quick rc=$?"
 grep "run 5" $out/${tag}_quick.log
+python bench.py --workload encode --steps 10 --warmup 3 > $out/${tag}_bench_encode.json 2> $out/${tag}_bench_encode.err; echo "encode bench rc=$?"
+tail -c 400 $out/${tag}_bench_encode.json
 if [ "${SKIP_NCU:-0}" != "1" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --skip-cpu-baseline > $out/${tag}_ncu_list.log 2>&1; echo "ncu list rc=$?"
 # one full step of the single-stream (profile) decoder after 3 warm runs: quick_bench launches 11 kernels per run
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_' --launch-skip ${NCU_SKIP:-33} --launch-count ${NCU_COUNT:-11} \
     -o $out/${tag}_full python tools/quick_bench.py 64 8 > $out/${tag}_ncu_full.log 2>&1; echo "ncu full rc=$?"
+# every encoder kernel of one warm encode call on a single stream (the profile encoder of the bench: last call of the run)
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_enc' --launch-skip ${NCU_ENC_SKIP:-390} --launch-count 10 \
+    -o $out/${tag}_enc_full python bench.py --workload encode --steps 1 --warmup 3 --skip-cpu-baseline > $out/${tag}_ncu_enc_full.log 2>&1; echo "ncu enc rc=$?"
 fi
 ls -la $out
