@@ -92,6 +92,12 @@ typedef struct
     int64_t row_stride;  /* bytes */
     int32_t format;      /* b200jpegFormat_t */
     int32_t on_host;     /* 0: buffer is device memory (plugin case); 1: host memory, the library stages + copies back */
+    /* Region of interest = nvimgcodecImageInfo_t::region (reference include/nvimgcodec.h:446-457, consumed by
+     * extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:355-369 and jpeg_mem.cpp:206-240): the buffer receives pixels
+     * [roi_x, roi_x + roi_width) x [roi_y, roi_y + roi_height) of the image, bit-identical to the same pixels of a full
+     * decode (what the reference produces).  roi_width == roi_height == 0: the whole image.  Planar formats: plane p
+     * starts at buffer + p * row_stride * roi_height. */
+    int32_t roi_x, roi_y, roi_width, roi_height;
 } b200jpegOutput_t;
 
 /* ---- library ---- */

@@ -21,7 +21,8 @@ class StreamInfo(C.Structure):
 
 
 class Output(C.Structure):
-    _fields_ = [("buffer", C.c_void_p), ("row_stride", C.c_int64), ("format", C.c_int32), ("on_host", C.c_int32)]
+    _fields_ = [("buffer", C.c_void_p), ("row_stride", C.c_int64), ("format", C.c_int32), ("on_host", C.c_int32),
+                ("roi_x", C.c_int32), ("roi_y", C.c_int32), ("roi_width", C.c_int32), ("roi_height", C.c_int32)]
 
 
 class EncodeInput(C.Structure):

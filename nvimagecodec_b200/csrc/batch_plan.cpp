@@ -247,11 +247,16 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     im.out = static_cast<uint8_t*>(out.buffer);
     im.out_stride = out.row_stride;
     im.fancy = opt.fancy_upsampling ? 1 : 0;
+    const bool whole = out.roi_w <= 0 || out.roi_h <= 0;
+    im.roi_x = whole ? 0 : out.roi_x;
+    im.roi_y = whole ? 0 : out.roi_y;
+    im.roi_w = whole ? pj.width : out.roi_w;
+    im.roi_h = whole ? pj.height : out.roi_h;
 
     plan.total_blocks += uint64_t(mcus) * im.bpm;
     plan.total_pixels += uint64_t(pj.width) * pj.height;
     const int planes = (im.out_fmt == 7) ? 1 : 3;
-    plan.out_bytes += uint64_t(pj.width) * pj.height * planes;
+    plan.out_bytes += uint64_t(im.roi_w) * im.roi_h * planes;
     plan.images.push_back(im);
 }
 

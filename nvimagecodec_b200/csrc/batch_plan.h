@@ -15,6 +15,7 @@ struct OutputSpec
     void* buffer = nullptr; // device pointer the colour kernel writes to
     int64_t row_stride = 0;
     int format = 4;
+    int roi_x = 0, roi_y = 0, roi_w = 0, roi_h = 0; // region of interest inside the image; roi_w == 0: the whole image
 };
 
 struct PlanOptions

@@ -103,7 +103,8 @@ int b200jpeg_decode_prepare(b200jpegDecoder_t decoder, int n, const uint8_t* con
     try {
         std::vector<Decoder::OutputDesc> outs(n);
         for (int i = 0; i < n; ++i)
-            outs[i] = Decoder::OutputDesc{outputs[i].buffer, outputs[i].row_stride, outputs[i].format, outputs[i].on_host};
+            outs[i] = Decoder::OutputDesc{outputs[i].buffer, outputs[i].row_stride, outputs[i].format, outputs[i].on_host, outputs[i].roi_x,
+                outputs[i].roi_y, outputs[i].roi_width, outputs[i].roi_height};
         return decoder->impl->prepare(n, data, sizes, outs.data(), statuses);
     } catch (const std::bad_alloc&) {
         return B200JPEG_STATUS_ALLOC_FAILED;
@@ -131,7 +132,8 @@ int b200jpeg_decode_batch(b200jpegDecoder_t decoder, int n, const uint8_t* const
     try {
         std::vector<Decoder::OutputDesc> outs(n);
         for (int i = 0; i < n; ++i)
-            outs[i] = Decoder::OutputDesc{outputs[i].buffer, outputs[i].row_stride, outputs[i].format, outputs[i].on_host};
+            outs[i] = Decoder::OutputDesc{outputs[i].buffer, outputs[i].row_stride, outputs[i].format, outputs[i].on_host, outputs[i].roi_x,
+                outputs[i].roi_y, outputs[i].roi_width, outputs[i].roi_height};
         return decoder->impl->decode(n, data, sizes, outs.data(), static_cast<cudaStream_t>(user_stream), statuses);
     } catch (const std::bad_alloc&) {
         return B200JPEG_STATUS_ALLOC_FAILED;

@@ -36,10 +36,30 @@ constexpr int kRowWords = kColorTilePx * 3 / 4; // interleaved RGB row of a tile
 constexpr int kRowStride = kRowWords + 4;       // spare word for the unaligned copy, keeps 16-byte alignment
 constexpr int kPlaneStride = kColorTilePx / 4 + 4;
 
-// copy nbytes from shared memory (word aligned, one spare word readable past the end) to dst (any alignment)
-__device__ __forceinline__ void warp_store_row(uint8_t* dst, const uint32_t* s_row, int nbytes, uint32_t lane)
+// copy nbytes from shared memory (s_row is word aligned, one spare word readable past the end of the row; the copy starts
+// sofs bytes into it) to dst (any alignment)
+__device__ __forceinline__ void warp_store_row(uint8_t* dst, const uint32_t* s_row, int nbytes, uint32_t lane, int sofs = 0)
 {
     const uint32_t m = uint32_t(reinterpret_cast<uintptr_t>(dst) & 3u);
+    if (sofs) { // region of interest that starts inside the tile: source and destination are both unaligned
+        const uint8_t* sb = reinterpret_cast<const uint8_t*>(s_row) + sofs;
+        int head = int((4u - m) & 3u);
+        if (head > nbytes)
+            head = nbytes;
+        if (int(lane) < head)
+            dst[lane] = sb[lane];
+        const int nw = (nbytes - head) >> 2;
+        uint32_t* d32 = reinterpret_cast<uint32_t*>(dst + head);
+        const int s0 = sofs + head;
+        const uint32_t* sw = s_row + (s0 >> 2);
+        const uint32_t sh = uint32_t(s0 & 3) * 8u;
+        for (int w = int(lane); w < nw; w += 32)
+            d32[w] = __funnelshift_r(sw[w], sw[w + 1], sh);
+        const int done = head + (nw << 2);
+        if (int(lane) < nbytes - done)
+            dst[done + lane] = sb[done + lane];
+        return;
+    }
     const uint8_t* sb = reinterpret_cast<const uint8_t*>(s_row);
     if (m == 0) {
         const int nw = nbytes >> 2;
@@ -216,10 +236,15 @@ __device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& i
     } else {
         yrow[0] = q;
     }
-    bool valid[VY];
+    bool valid[VY]; // rows of the image that are inside the region of interest
 #pragma unroll
     for (int r = 0; r < VY; ++r)
-        valid[r] = yrow[r] >= 0 && yrow[r] < im.height;
+        valid[r] = yrow[r] >= im.roi_y && yrow[r] < im.roi_y + im.roi_h;
+    // the part of the tile inside the region of interest
+    const int tile_end = im.width - xbase < kColorTilePx ? im.width : xbase + kColorTilePx;
+    const int xa = xbase > im.roi_x ? xbase : im.roi_x, xb = tile_end < im.roi_x + im.roi_w ? tile_end : im.roi_x + im.roi_w;
+    if (xb <= xa || !(valid[0] || valid[VY - 1]))
+        return;
 
     // ---- loads: everything the lane needs is requested before anything is used ----
     uint32_t yw[VY][4];
@@ -227,7 +252,7 @@ __device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& i
     if (active) {
 #pragma unroll
         for (int r = 0; r < VY; ++r) {
-            const int yy = valid[r] ? yrow[r] : (yrow[r] < 0 ? 0 : im.height - 1);
+            const int yy = yrow[r] < 0 ? 0 : (yrow[r] > im.height - 1 ? im.height - 1 : yrow[r]);
             const uint8_t* p = b.planes + im.plane_off[0] + uint64_t(yy) * im.plane_pitch[0] + x0;
             const uint2 v = *reinterpret_cast<const uint2*>(p), u = *reinterpret_cast<const uint2*>(p + 8);
             yw[r][0] = v.x;
@@ -286,18 +311,18 @@ __device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& i
     }
     __syncwarp();
     // ---- coalesced copy-out ----
-    const int tile_px = im.width - xbase < kColorTilePx ? im.width - xbase : kColorTilePx;
 #pragma unroll
     for (int r = 0; r < VY; ++r) {
         if (!valid[r])
             continue;
         const uint32_t* s_buf = s_warp + r * row_stride_words;
+        const int oy = yrow[r] - im.roi_y, ox = xa - im.roi_x, npx = xb - xa, skip = xa - xbase;
         if (interleaved) {
-            warp_store_row(im.out + int64_t(yrow[r]) * im.out_stride + int64_t(xbase) * 3, s_buf, tile_px * 3, lane);
+            warp_store_row(im.out + int64_t(oy) * im.out_stride + int64_t(ox) * 3, s_buf, npx * 3, lane, skip * 3);
         } else {
             const int nplanes = fmt == 7 ? 1 : 3;
             for (int pl = 0; pl < nplanes; ++pl)
-                warp_store_row(im.out + (int64_t(pl) * im.height + yrow[r]) * im.out_stride + xbase, s_buf + pl * kPlaneStride, tile_px, lane);
+                warp_store_row(im.out + (int64_t(pl) * im.roi_h + oy) * im.out_stride + ox, s_buf + pl * kPlaneStride, npx, lane, skip);
         }
     }
     __syncwarp();

@@ -219,6 +219,18 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
         os.buffer = outs[i].buffer;
         os.row_stride = outs[i].row_stride;
         os.format = outs[i].format;
+        int out_w = parsed_[i].width, out_h = parsed_[i].height;
+        if (outs[i].roi_w > 0 || outs[i].roi_h > 0) { // same validity rule as the reference (jpeg_mem.cpp IsCropWindowValid:94-100)
+            if (outs[i].roi_w <= 0 || outs[i].roi_h <= 0 || outs[i].roi_x < 0 || outs[i].roi_y < 0 ||
+                int64_t(outs[i].roi_x) + outs[i].roi_w > parsed_[i].width || int64_t(outs[i].roi_y) + outs[i].roi_h > parsed_[i].height) {
+                pre_status_[i] = B200JPEG_STATUS_INVALID_PARAMETER;
+                continue;
+            }
+            os.roi_x = outs[i].roi_x;
+            os.roi_y = outs[i].roi_y;
+            os.roi_w = out_w = outs[i].roi_w;
+            os.roi_h = out_h = outs[i].roi_h;
+        }
         if (outs[i].on_host) {
             const int fmt = resolve_format(outs[i].format, parsed_[i].ncomp);
             const bool interleaved = (fmt == 4 || fmt == 6);
@@ -226,8 +238,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
             ho.image = int(plan_.images.size());
             ho.host = outs[i].buffer;
             ho.host_stride = outs[i].row_stride;
-            ho.row_bytes = size_t(parsed_[i].width) * (interleaved ? 3 : 1);
-            ho.rows = size_t(parsed_[i].height) * (interleaved ? 1 : (fmt == 7 ? 1 : 3));
+            ho.row_bytes = size_t(out_w) * (interleaved ? 3 : 1);
+            ho.rows = size_t(out_h) * (interleaved ? 1 : (fmt == 7 ? 1 : 3));
             ho.dev_off = dev_out_bytes;
             const size_t pitch = align_up(ho.row_bytes, 16);
             dev_out_bytes += align_up(pitch * ho.rows, 256);
@@ -631,7 +643,7 @@ int Decoder::launch_group(int g)
     for (size_t k = 0; k < gr.host_outs.size();) {
         const HostOutput& ho = host_outs_[gr.host_outs[k]];
         const size_t pitch = align_up(ho.row_bytes, 16);
-        if (size_t(ho.host_stride) != pitch) {
+        if (size_t(ho.host_stride) != pitch || ho.row_bytes != pitch) { // rows with slack: never write the caller's slack bytes
             B2J_CUDA(cudaMemcpy2DAsync(ho.host, size_t(ho.host_stride), static_cast<uint8_t*>(d_out_.p) + ho.dev_off, pitch, ho.row_bytes,
                 ho.rows, cudaMemcpyDeviceToHost, st));
             ++k;
@@ -642,7 +654,7 @@ int Decoder::launch_group(int g)
         for (; k2 < gr.host_outs.size(); ++k2) {
             const HostOutput& nx = host_outs_[gr.host_outs[k2]];
             const size_t np = align_up(nx.row_bytes, 16);
-            if (size_t(nx.host_stride) != np || nx.dev_off != ho.dev_off + len || static_cast<uint8_t*>(nx.host) != static_cast<uint8_t*>(ho.host) + len)
+            if (size_t(nx.host_stride) != np || nx.row_bytes != np || nx.dev_off != ho.dev_off + len || static_cast<uint8_t*>(nx.host) != static_cast<uint8_t*>(ho.host) + len)
                 break;
             len += np * nx.rows;
         }

@@ -106,6 +106,7 @@ class Decoder
         int64_t row_stride;
         int format;
         int on_host;
+        int roi_x = 0, roi_y = 0, roi_w = 0, roi_h = 0; // region of interest; roi_w == 0: the whole image
     };
 
     // two-phase: prepare = parse + plan + H2D of the bitstreams; run = all device work of the prepared batch

@@ -114,6 +114,11 @@ struct ImageDesc
     int64_t out_stride;
     int32_t out_fmt;      // b200jpegFormat_t resolved: P_RGB/I_RGB/P_BGR/I_BGR/P_Y
     int32_t fancy;
+    // region of interest: the output buffer holds pixels [roi_x, roi_x + roi_w) x [roi_y, roi_y + roi_h) of the image (the
+    // whole image by default).  The reference decodes a region to exactly the pixels the full decode has there
+    // (extensions/libjpeg_turbo/jpeg_mem.cpp:206-240 asks libjpeg for one spare pixel left and right so that the upsampling
+    // filter at the region's edge sees its real neighbours).
+    int32_t roi_x, roi_y, roi_w, roi_h;
 };
 
 // Per-image state written by the device.

@@ -356,21 +356,22 @@ B2J_HD void store_unit_simple(const ImageDesc& im, int x0, const uint32_t* px, c
     const int fmt = im.out_fmt;
     const int npx = im.width - x0 < 16 ? im.width - x0 : 16;
     for (int r = 0; r < VY; ++r) {
-        if (yrow[r] < 0)
+        const int oy = yrow[r] - im.roi_y; // row inside the region of interest
+        if (yrow[r] < 0 || oy < 0 || oy >= im.roi_h)
             continue;
-        if (fmt == 4 || fmt == 6) {
-            uint8_t* dst = im.out + int64_t(yrow[r]) * im.out_stride + int64_t(x0) * 3;
-            for (int i = 0; i < npx; ++i) {
-                dst[3 * i] = uint8_t(px[r * 16 + i]);
-                dst[3 * i + 1] = uint8_t(px[r * 16 + i] >> 8);
-                dst[3 * i + 2] = uint8_t(px[r * 16 + i] >> 16);
-            }
-        } else {
-            const int nplanes = fmt == 7 ? 1 : 3;
-            for (int pl = 0; pl < nplanes; ++pl) {
-                uint8_t* dst = im.out + (int64_t(pl) * im.height + yrow[r]) * im.out_stride + x0;
-                for (int i = 0; i < npx; ++i)
-                    dst[i] = uint8_t(px[r * 16 + i] >> (8 * pl));
+        for (int i = 0; i < npx; ++i) {
+            const int ox = x0 + i - im.roi_x;
+            if (ox < 0 || ox >= im.roi_w)
+                continue;
+            if (fmt == 4 || fmt == 6) {
+                uint8_t* dst = im.out + int64_t(oy) * im.out_stride + int64_t(ox) * 3;
+                dst[0] = uint8_t(px[r * 16 + i]);
+                dst[1] = uint8_t(px[r * 16 + i] >> 8);
+                dst[2] = uint8_t(px[r * 16 + i] >> 16);
+            } else {
+                const int nplanes = fmt == 7 ? 1 : 3;
+                for (int pl = 0; pl < nplanes; ++pl)
+                    im.out[(int64_t(pl) * im.roi_h + oy) * im.out_stride + ox] = uint8_t(px[r * 16 + i] >> (8 * pl));
             }
         }
     }

@@ -101,12 +101,22 @@ nvimgcodecProcessingStatus_t check_target(const nvimgcodecImageInfo_t& info, con
     }
     if (info.plane_info[0].sample_type != NVIMGCODEC_SAMPLE_DATA_TYPE_UINT8)
         st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_TYPE_UNSUPPORTED;
-    if (params->enable_roi && info.region.ndim > 0)
+    // region of interest: the reference's rule (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:355-369) -- two
+    // dimensions, inside the image, and the target image has the region's size
+    int want_w = si.width, want_h = si.height;
+    if (info.region.ndim != 0 && info.region.ndim != 2) {
         st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED;
+    } else if (info.region.ndim == 2) {
+        const int x = info.region.start[1], y = info.region.start[0];
+        want_w = info.region.end[1] - x;
+        want_h = info.region.end[0] - y;
+        if (x < 0 || y < 0 || want_w <= 0 || want_h <= 0 || x + want_w > si.width || y + want_h > si.height)
+            st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED;
+    }
     if (params->apply_exif_orientation && (info.orientation.flip_x || info.orientation.flip_y || info.orientation.rotated != 0))
         st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
-    if (int(info.plane_info[0].width) != si.width || int(info.plane_info[0].height) != si.height)
-        st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED; // a cropped / resized target is not ours
+    if (int(info.plane_info[0].width) != want_w || int(info.plane_info[0].height) != want_h)
+        st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED; // a resized target is not ours
     if (info.buffer_kind != NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_DEVICE)
         st |= NVIMGCODEC_PROCESSING_STATUS_BACKEND_UNSUPPORTED;
     return st;
@@ -179,6 +189,13 @@ nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, nvimgcodecCodeStreamD
             outs[i].row_stride = int64_t(info.plane_info[0].row_stride);
             outs[i].format = int32_t(info.sample_format);
             outs[i].on_host = info.buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST ? 1 : 0;
+            outs[i].roi_x = outs[i].roi_y = outs[i].roi_width = outs[i].roi_height = 0;
+            if (info.region.ndim == 2) {
+                outs[i].roi_x = info.region.start[1];
+                outs[i].roi_y = info.region.start[0];
+                outs[i].roi_width = info.region.end[1] - info.region.start[1];
+                outs[i].roi_height = info.region.end[0] - info.region.start[0];
+            }
             if (i == 0)
                 user_stream = info.cuda_stream;
             if (!data[i]) {

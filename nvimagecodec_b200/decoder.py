@@ -90,7 +90,7 @@ class Decoder:
             pass
 
     # ---- low level: caller-provided buffers -------------------------------------------------------------------
-    def _outputs(self, buffers, strides, formats, on_host):
+    def _outputs(self, buffers, strides, formats, on_host, rois=None):
         n = len(buffers)
         outs = (_capi.Output * n)()
         for i in range(n):
@@ -98,14 +98,17 @@ class Decoder:
             outs[i].row_stride = strides[i]
             outs[i].format = formats[i]
             outs[i].on_host = int(on_host)
+            if rois is not None and rois[i]:
+                outs[i].roi_x, outs[i].roi_y, outs[i].roi_width, outs[i].roi_height = rois[i]
         return outs
 
-    def decode_into(self, datas, buffers, strides, formats, on_host=False, cuda_stream=0):
-        """decode a batch into raw pointers (device pointers, or host pointers with on_host=True) -> status list"""
+    def decode_into(self, datas, buffers, strides, formats, on_host=False, cuda_stream=0, rois=None):
+        """decode a batch into raw pointers (device pointers, or host pointers with on_host=True) -> status list.
+        rois: per image None or (x, y, width, height): the buffer receives that region of the image only"""
         n = len(datas)
         st = (C.c_int32 * n)()
         rc = _capi.lib().b200jpeg_decode_batch(self._h, n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
-                                               self._outputs(buffers, strides, formats, on_host), C.c_void_p(cuda_stream), st)
+                                               self._outputs(buffers, strides, formats, on_host, rois), C.c_void_p(cuda_stream), st)
         if rc != 0:
             raise RuntimeError("b200jpeg_decode_batch: %s" % _capi.status_string(rc))
         self.last_statuses = list(st)

@@ -221,9 +221,9 @@ REFH_API int refh_get_info(void* h, const unsigned char* data, size_t size, int*
 //   reps        : the decode call is repeated `reps` times on the same streams/images; seconds[r] gets the
 //                 wall time of Decode + FutureWaitForAll (+ cudaStreamSynchronize for device buffers)
 //   status_out  : per-sample nvimgcodecProcessingStatus_t of the last repetition
-REFH_API int refh_decode(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers, const int* widths,
+static int decode_impl(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers, const int* widths,
     const int* heights, const int* sample_formats, const int64_t* row_strides, int buffer_kind, void* cuda_stream, int reps,
-    unsigned int* status_out, double* seconds)
+    unsigned int* status_out, double* seconds, const int* rois)
 {
     auto* d = (Decoder*)hd;
     auto inst = d->s->instance;
@@ -243,12 +243,21 @@ REFH_API int refh_decode(void* hd, int n, const unsigned char** data, const size
         nvimgcodecImageInfo_t info;
         fill_image_info(info, widths[i], heights[i], sample_formats[i], row_strides[i], buffer_kind, buffers[i], cuda_stream,
             unchanged_channels);
+        if (rois && rois[4 * i + 2] > 0) { // region of interest: x, y, width, height; widths / heights are the region's
+            info.region.struct_type = NVIMGCODEC_STRUCTURE_TYPE_REGION;
+            info.region.struct_size = sizeof(nvimgcodecRegion_t);
+            info.region.ndim = 2;
+            info.region.start[0] = rois[4 * i + 1];
+            info.region.start[1] = rois[4 * i];
+            info.region.end[0] = rois[4 * i + 1] + rois[4 * i + 3];
+            info.region.end[1] = rois[4 * i] + rois[4 * i + 2];
+        }
         if (nvimgcodecImageCreate(inst, &img[i], &info) != NVIMGCODEC_STATUS_SUCCESS)
             rc = -2;
     }
     nvimgcodecDecodeParams_t params{NVIMGCODEC_STRUCTURE_TYPE_DECODE_PARAMS, sizeof(nvimgcodecDecodeParams_t), 0};
     params.apply_exif_orientation = 0;
-    params.enable_roi = 0;
+    params.enable_roi = rois ? 1 : 0;
     for (int r = 0; r < reps && rc == 0; ++r) {
         double t0 = now_s();
         nvimgcodecFuture_t fut = nullptr;
@@ -277,6 +286,24 @@ REFH_API int refh_decode(void* hd, int n, const unsigned char** data, const size
             nvimgcodecCodeStreamDestroy(cs[i]);
     }
     return rc;
+}
+
+REFH_API int refh_decode(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers, const int* widths,
+    const int* heights, const int* sample_formats, const int64_t* row_strides, int buffer_kind, void* cuda_stream, int reps,
+    unsigned int* status_out, double* seconds)
+{
+    return decode_impl(hd, n, data, sizes, buffers, widths, heights, sample_formats, row_strides, buffer_kind, cuda_stream, reps, status_out,
+        seconds, nullptr);
+}
+
+// The same with a region of interest per image (rois: x, y, width, height; width 0 = whole image); widths / heights
+// describe the target buffers, i.e. the regions (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:355-369).
+REFH_API int refh_decode_roi(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers, const int* widths,
+    const int* heights, const int* sample_formats, const int64_t* row_strides, int buffer_kind, void* cuda_stream, int reps,
+    unsigned int* status_out, double* seconds, const int* rois)
+{
+    return decode_impl(hd, n, data, sizes, buffers, widths, heights, sample_formats, row_strides, buffer_kind, cuda_stream, reps, status_out,
+        seconds, rois);
 }
 
 // nvimgcodecDecoderCanDecode for a batch (src/image_generic_decoder.cpp:84-131)

@@ -47,6 +47,7 @@ def lib():
         L.refh_decode.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p),
                                   C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64), C.c_int,
                                   C.c_void_p, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_double)]
+        L.refh_decode_roi.argtypes = L.refh_decode.argtypes + [C.POINTER(C.c_int)]
         L.refh_can_decode.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_int),
                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(C.c_uint)]
         L.refh_encode.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int),
@@ -170,10 +171,12 @@ class Decoder:
             raise RuntimeError("refh_can_decode rc=%d" % rc)
         return list(st)
 
-    def decode_host(self, datas, fmt=I_RGB, reps=1, dims=None, row_strides=None):
+    def decode_host(self, datas, fmt=I_RGB, reps=1, dims=None, row_strides=None, rois=None):
         """Decode to host numpy buffers. Returns (list of arrays, status list, seconds list).
-        Interleaved -> (H, W, C); planar -> (C, H, W)."""
+        Interleaved -> (H, W, C); planar -> (C, H, W).  rois: per image (x, y, w, h) or None: decode that region only."""
         n = len(datas)
+        if rois is not None:
+            dims = [(r[2], r[3]) if r else self.session.get_info(d)[:2] for d, r in zip(datas, rois)]
         if dims is None:
             dims = [self.session.get_info(d)[:2] for d in datas]
         fmts = fmt if isinstance(fmt, (list, tuple)) else [fmt] * n
@@ -186,10 +189,14 @@ class Decoder:
             strides.append(stride)
         st = (C.c_uint * n)()
         secs = (C.c_double * reps)()
-        rc = lib().refh_decode(self.h, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
-                               _arr(C.c_void_p, [o.ctypes.data for o in outs]), _arr(C.c_int, [d[0] for d in dims]),
-                               _arr(C.c_int, [d[1] for d in dims]), _arr(C.c_int, fmts), _arr(C.c_int64, strides), BUFFER_HOST,
-                               None, reps, st, secs)
+        args = (self.h, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
+                _arr(C.c_void_p, [o.ctypes.data for o in outs]), _arr(C.c_int, [d[0] for d in dims]),
+                _arr(C.c_int, [d[1] for d in dims]), _arr(C.c_int, fmts), _arr(C.c_int64, strides), BUFFER_HOST, None, reps, st, secs)
+        if rois is None:
+            rc = lib().refh_decode(*args)
+        else:
+            flat = [v for r in rois for v in (r if r else (0, 0, 0, 0))]
+            rc = lib().refh_decode_roi(*args, _arr(C.c_int, flat))
         if rc != 0:
             raise RuntimeError("refh_decode rc=%d" % rc)
         res = []
@@ -201,14 +208,19 @@ class Decoder:
                 res.append(o.reshape(h, s)[:, :w * ch].reshape(h, w, ch))
         return res, list(st), list(secs)
 
-    def decode_raw(self, datas, buffers, dims, fmts, strides, buffer_kind, stream=None, reps=1):
-        """Decode into caller-provided raw pointers (ints); used with device buffers for the b200jpeg plugin."""
+    def decode_raw(self, datas, buffers, dims, fmts, strides, buffer_kind, stream=None, reps=1, rois=None):
+        """Decode into caller-provided raw pointers (ints); used with device buffers for the b200jpeg plugin.
+        rois: per image (x, y, w, h) or None; dims are then the regions' sizes."""
         n = len(datas)
         st = (C.c_uint * n)()
         secs = (C.c_double * reps)()
-        rc = lib().refh_decode(self.h, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
-                               _arr(C.c_void_p, buffers), _arr(C.c_int, [d[0] for d in dims]), _arr(C.c_int, [d[1] for d in dims]),
-                               _arr(C.c_int, fmts), _arr(C.c_int64, strides), buffer_kind, stream, reps, st, secs)
+        args = (self.h, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
+                _arr(C.c_void_p, buffers), _arr(C.c_int, [d[0] for d in dims]), _arr(C.c_int, [d[1] for d in dims]),
+                _arr(C.c_int, fmts), _arr(C.c_int64, strides), buffer_kind, stream, reps, st, secs)
+        if rois is None:
+            rc = lib().refh_decode(*args)
+        else:
+            rc = lib().refh_decode_roi(*args, _arr(C.c_int, [v for r in rois for v in (r if r else (0, 0, 0, 0))]))
         if rc != 0:
             raise RuntimeError("refh_decode rc=%d" % rc)
         return list(st), list(secs)

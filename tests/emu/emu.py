@@ -52,9 +52,12 @@ def encode(pixels, quality=90, subsampling=3, restart_interval=0, planar=False):
     return out[:n].tobytes()
 
 
-def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=64, jacobi=True, want_coef=False, slots=None):
-    """dims: list of (w, h).  Returns (outputs, statuses, rounds, coefs)"""
+def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=64, jacobi=True, want_coef=False, slots=None, rois=None):
+    """dims: list of (w, h).  Returns (outputs, statuses, rounds, coefs).  rois: per image None or (x, y, w, h): the output
+    holds that region only"""
     n = len(datas)
+    if rois is not None:
+        dims = [(r[2], r[3]) if r else d for d, r in zip(dims, rois)]
     fmts = fmt if isinstance(fmt, (list, tuple)) else [fmt] * n
     outs, strides = [], []
     for (w, h), f in zip(dims, fmts):
@@ -71,6 +74,7 @@ def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=64
     lib().emu_decode_batch(n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
                            (C.c_void_p * n)(*[o.ctypes.data for o in outs]), (C.c_int64 * n)(*strides), (C.c_int * n)(*fmts),
                            int(fancy), subseq_bytes, max_rounds, int(jacobi), st, C.byref(rounds),
-                           (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None, stats)
+                           (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None, stats,
+                           (C.c_int * (4 * n))(*[v for r in rois for v in (r if r else (0, 0, 0, 0))]) if rois is not None else None)
     decode_batch.last_stats = {"rounds": int(stats[0]), "redone": int(stats[1]), "subsequences": int(stats[2])}
     return outs, list(st), rounds.value, coefs

@@ -98,3 +98,26 @@ def test_emulated_many_short_restart_segments():
         assert st == [0, 0, 0]
         for d, o in zip(datas, outs):
             assert np.array_equal(o, port.decode(d, port.FMT_I_RGB, True))
+
+
+def test_emulated_region_of_interest():
+    """Region-of-interest decode: the output is exactly the same pixels of the reference's ROI decode (which equals the
+    crop of its full decode), for every sampling mode, fancy and plain upsampling, interleaved and planar outputs."""
+    rng = np.random.default_rng(11)
+    sess = ref.Session.shared()
+    for fancy in (1, 0):
+        rdec = sess.decoder(options=":fancy_upsampling=%d" % fancy)
+        for (w, h, samp, gray) in [(227, 149, (2, 2), False), (131, 77, (2, 1), False), (131, 77, (1, 2), False), (100, 100, (1, 1), False),
+                                   (201, 99, (1, 1), True), (640, 426, (2, 2), False)]:
+            d = make_jpeg(77, w, h, samp, 85, gray=gray)
+            rois = [(0, 0, w, h), (0, 0, 1, 1), (w - 1, h - 1, 1, 1), (1, 1, w - 2, h - 2), (16, 16, 32, 32), (15, 17, 33, 31)]
+            for _ in range(6):
+                x, y = int(rng.integers(0, w - 1)), int(rng.integers(0, h - 1))
+                rois.append((x, y, int(rng.integers(1, w - x + 1)), int(rng.integers(1, h - y + 1))))
+            for fmt, rfmt in ((4, ref.I_RGB), (3, ref.P_RGB)):
+                want, rst, _ = rdec.decode_host([d] * len(rois), fmt=rfmt, rois=rois)
+                assert all(s == ref.STATUS_SUCCESS for s in rst)
+                outs, st, _, _ = emu.decode_batch([d] * len(rois), [(w, h)] * len(rois), fmt, fancy, 128, rois=rois)
+                assert st == [0] * len(rois)
+                for r, o, wv in zip(rois, outs, want):
+                    assert np.array_equal(o, wv), (fancy, w, h, samp, gray, fmt, r)

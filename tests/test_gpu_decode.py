@@ -196,3 +196,47 @@ def test_python_mirror_api(torch_mod, refdec):
     one = dec.decode(datas[0])
     assert np.array_equal(one.cpu(), want[0])
     assert dec.decode(b"garbage") is None
+
+
+def test_region_of_interest(torch_mod, refdec):
+    """ROI decode through the C ABI: device and host outputs, interleaved / planar / Y, regions that start and end inside
+    the 512-pixel tiles of the colour kernel; bit-exact against the reference's ROI decode; invalid regions are refused."""
+    torch = torch_mod
+    from nvimagecodec_b200.decoder import Decoder
+    rng = np.random.default_rng(12)
+    dec = Decoder(0, options=":fancy_upsampling=1")
+    for (w, h, samp, gray) in [(1300, 420, (2, 2), False), (1111, 333, (2, 1), False), (700, 300, (1, 2), False), (1030, 200, (1, 1), False),
+                               (900, 260, (1, 1), True)]:
+        d = make_jpeg(99, w, h, samp, 88, gray=gray)
+        rois = [(0, 0, w, h), (w - 1, h - 1, 1, 1), (511, 0, 2, h), (512, 7, 513, 100), (1, 1, w - 2, h - 2), (3, 5, 1021, 17)]
+        for _ in range(6):
+            x, y = int(rng.integers(0, w - 1)), int(rng.integers(0, h - 1))
+            rois.append((x, y, int(rng.integers(1, w - x + 1)), int(rng.integers(1, h - y + 1))))
+        rois = [(x, y, min(rw, w - x), min(rh, h - y)) for (x, y, rw, rh) in rois]
+        n = len(rois)
+        for fmt in (4, 3, 7):
+            want, rst, _ = refdec[1].decode_host([d] * n, fmt=FMT_REF[fmt], rois=rois)
+            assert all(s == ref.STATUS_SUCCESS for s in rst)
+            for on_host in (False, True):
+                outs, ptrs, strides = [], [], []
+                for (x, y, rw, rh) in rois:
+                    stride = rw * 3 + 5 if fmt == 4 else rw + 3
+                    rows = rh if fmt in (4, 7) else 3 * rh
+                    t = torch.zeros((rows, stride), dtype=torch.uint8, device="cpu" if on_host else "cuda")
+                    outs.append(t.pin_memory() if on_host else t)
+                    ptrs.append(outs[-1].data_ptr())
+                    strides.append(stride)
+                st = dec.decode_into([d] * n, ptrs, strides, [fmt] * n, on_host, rois=rois)
+                torch.cuda.synchronize()
+                assert st == [0] * n
+                for (x, y, rw, rh), t, wv in zip(rois, outs, want):
+                    a = t.cpu().numpy()
+                    got = a[:, :rw * 3].reshape(rh, rw, 3) if fmt == 4 else a[:, :rw].reshape(1 if fmt == 7 else 3, rh, rw)
+                    assert np.array_equal(got, wv), (w, h, samp, gray, fmt, on_host, (x, y, rw, rh))
+                    assert not a[:, (rw * 3 if fmt == 4 else rw):].any(), ("wrote past the region's row", fmt, on_host, (x, y, rw, rh))
+    d = make_jpeg(5, 64, 48, (2, 2), 90)
+    t = torch.zeros((48, 64 * 3), dtype=torch.uint8, device="cuda")
+    bad = [(60, 0, 8, 8), (0, 40, 8, 16), (-1, 0, 4, 4), (0, 0, 0, 5)]
+    st = dec.decode_into([d] * len(bad), [t.data_ptr()] * len(bad), [64 * 3] * len(bad), [4] * len(bad), False, rois=bad)
+    assert all(s != 0 for s in st[:3]), st
+    dec.close()

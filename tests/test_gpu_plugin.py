@@ -38,6 +38,26 @@ def test_decode_through_reference_framework(sess):
     dec.close()
 
 
+def test_region_of_interest_through_reference_framework(sess):
+    """nvimgcodecImageInfo_t::region with the GPU_ONLY backend list: only our plugin can have produced the pixels, and they
+    equal the region decoded by libjpeg_turbo_ext"""
+    import torch
+    cases = [(640, 426, (2, 2)), (333, 211, (2, 1)), (227, 149, (1, 1))]
+    datas = [make_jpeg(600 + i, w, h, samp, 88) for i, (w, h, samp) in enumerate(cases)]
+    rois = [(100, 50, 333, 200), (1, 0, 332, 211), (226, 148, 1, 1)]
+    dims = [(r[2], r[3]) for r in rois]
+    dec = sess.decoder(device_id=0, backends=ref.BACKEND_GPU_ONLY, options=":fancy_upsampling=1")
+    outs = [torch.zeros((h, w * 3), dtype=torch.uint8, device="cuda") for (w, h) in dims]
+    torch.cuda.synchronize()
+    st, _ = dec.decode_raw(datas, [o.data_ptr() for o in outs], dims, [ref.I_RGB] * 3, [w * 3 for (w, h) in dims], ref.BUFFER_DEVICE, rois=rois)
+    torch.cuda.synchronize()
+    assert st == [ref.STATUS_SUCCESS] * 3, st
+    want, wst, _ = ref.Session.shared().decoder(options=":fancy_upsampling=1").decode_host(datas, rois=rois)
+    for o, w in zip(outs, want):
+        assert np.array_equal(o.cpu().numpy().reshape(w.shape), w)
+    dec.close()
+
+
 def test_gpu_only_backend_selects_b200jpeg(sess):
     """backends=[GPU_ONLY]: libjpeg_turbo_ext (CPU_ONLY) is filtered out by the framework (src/decoder_worker.cpp:63-93), so a
     successful decode can only have come from our plugin"""
