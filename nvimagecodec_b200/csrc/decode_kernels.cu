@@ -361,6 +361,15 @@ __global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
     __syncthreads();
     if (ref.comp < 0)
         return;
+    { // region of interest: blocks none of whose samples can reach a pixel of the region (8 pixels of margin cover the
+      // neighbours the upsampling filters look at) are not needed
+        const uint64_t rel = ref.dst - im.plane_off[ref.comp];
+        const int by = int(rel / uint64_t(ref.pitch)) >> 3, bx = int(rel % uint64_t(ref.pitch)) >> 3;
+        const int sx = 8 * (im.hmax / im.hs[ref.comp]), sy = 8 * (im.vmax / im.vs[ref.comp]); // block size in image pixels
+        if ((bx + 1) * sx <= im.roi_x - 8 || bx * sx >= im.roi_x + im.roi_w + 8 || (by + 1) * sy <= im.roi_y - 8 ||
+            by * sy >= im.roi_y + im.roi_h + 8)
+            return;
+    }
     // the thread's own slot: zero it, scatter the block's coefficient records into it, read it back as a dense block
     uint8_t* slot = s_blk + threadIdx.x * kIdctPitch;
 #pragma unroll

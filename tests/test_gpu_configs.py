@@ -48,8 +48,9 @@ def _run_config(name, distinct, fmts_distinct, batch, options=":fancy_upsampling
     assert all(s == 0 for s in st), (name, [i for i, s in enumerate(st) if s])
     # reference decode of the distinct images (CPU thread pool)
     rdec = ref.Session.shared().decoder(options=options)
-    want, rst, _ = rdec.decode_host(distinct, fmt=[FMT_REF[f] for f in fmts_distinct])
+    want, rst, rsecs = rdec.decode_host(distinct, fmt=[FMT_REF[f] for f in fmts_distinct], reps=2)
     assert all(s == ref.STATUS_SUCCESS for s in rst)
+    cpu_mpix = sum(d["width"] * d["height"] for d in dims) / 1e6 / min(rsecs)
     for i in range(n0):
         got = outs[i].cpu().numpy()
         w, h = dims[i]["width"], dims[i]["height"]
@@ -87,7 +88,9 @@ def _run_config(name, distinct, fmts_distinct, batch, options=":fancy_upsampling
     line = {"config": name, "images": batch, "distinct": n0, "mpixel": pixels / 1e6, "jpeg_mb": sum(len(d) for d in datas) / 1e6,
             "ms_per_batch_device_inputs": ms, "mpixel_per_s": pixels / 1e6 / (ms / 1e3), "images_per_s": batch / (ms / 1e3),
             "e2e_ms_host_to_host": e2e_ms, "e2e_mpixel_per_s": pixels / 1e6 / (e2e_ms / 1e3), "sync_rounds": stats["sync_rounds"],
-            "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"], "parity": "bit-exact vs libjpeg_turbo_ext"}
+            "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"], "parity": "bit-exact vs libjpeg_turbo_ext",
+            "cpu_reference_mpixel_per_s": cpu_mpix, "cpu_sample": "the %d distinct images, libjpeg_turbo_ext on %d host threads (WITH_SIMD=0)"
+                                                                  % (n0, os.cpu_count() or 1)}
     out_dir = os.path.join(util.ROOT, "gpurun_out")
     if os.path.isdir(out_dir):
         with open(os.path.join(out_dir, "configs_bench.jsonl"), "a") as f:
