@@ -114,6 +114,26 @@ B200JPEG_API int b200jpeg_parse_header(const uint8_t* data, size_t size, b200jpe
 B200JPEG_API int b200jpeg_decoder_create(b200jpegDecoder_t* decoder, int device_id, const char* options);
 B200JPEG_API int b200jpeg_decoder_destroy(b200jpegDecoder_t decoder);
 
+/* Memory callbacks: every device / page-locked host allocation of the decoder (encoder) made after this call goes through
+ * them; call it right after create.  Same signatures and meaning as nvimgcodecDeviceAllocator_t / nvimgcodecPinnedAllocator_t
+ * of nvimgcodecExecutionParams_t (reference include/nvimgcodec.h:232-302): stream-ordered (ctx, &ptr, size, stream) /
+ * (ctx, ptr, size, stream), 0 = success, sizes padded to a multiple of *_padding.  A NULL pair keeps cudaMalloc /
+ * cudaHostAlloc for that kind of memory. */
+typedef int (*b200jpegMalloc_t)(void* ctx, void** ptr, size_t size, void* cuda_stream);
+typedef int (*b200jpegFree_t)(void* ctx, void* ptr, size_t size, void* cuda_stream);
+typedef struct
+{
+    b200jpegMalloc_t device_malloc;
+    b200jpegFree_t device_free;
+    void* device_ctx;
+    size_t device_padding;
+    b200jpegMalloc_t pinned_malloc;
+    b200jpegFree_t pinned_free;
+    void* pinned_ctx;
+    size_t pinned_padding;
+} b200jpegAllocators_t;
+B200JPEG_API int b200jpeg_decoder_set_allocators(b200jpegDecoder_t decoder, const b200jpegAllocators_t* allocators);
+
 /* Decode a batch.  data[i]/sizes[i]: whole JPEG files in host memory.  outputs[i]: where the pixels go.
  * user_stream: CUDA stream (cudaStream_t as void*) the outputs are ordered on -- on return the work has been enqueued and
  * synchronised enough that statuses[i] is final (B200JPEG_STATUS_*) and device outputs are complete.
@@ -162,6 +182,7 @@ typedef struct
 
 B200JPEG_API int b200jpeg_encoder_create(b200jpegEncoder_t* encoder, int device_id, const char* options);
 B200JPEG_API int b200jpeg_encoder_destroy(b200jpegEncoder_t encoder);
+B200JPEG_API int b200jpeg_encoder_set_allocators(b200jpegEncoder_t encoder, const b200jpegAllocators_t* allocators);
 /* out[i] (host memory, capacity out_capacity[i]) receives a complete JFIF file; out_sizes[i] its length. */
 B200JPEG_API int b200jpeg_encode_batch(b200jpegEncoder_t encoder, int batch_size, const b200jpegEncodeInput_t* inputs, uint8_t* const* out,
     const size_t* out_capacity, size_t* out_sizes, void* user_stream, int32_t* statuses);

@@ -25,6 +25,15 @@ class Output(C.Structure):
                 ("roi_x", C.c_int32), ("roi_y", C.c_int32), ("roi_width", C.c_int32), ("roi_height", C.c_int32)]
 
 
+MALLOC_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t, C.c_void_p)
+FREE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
+
+
+class Allocators(C.Structure):
+    _fields_ = [("device_malloc", MALLOC_FN), ("device_free", FREE_FN), ("device_ctx", C.c_void_p), ("device_padding", C.c_size_t),
+                ("pinned_malloc", MALLOC_FN), ("pinned_free", FREE_FN), ("pinned_ctx", C.c_void_p), ("pinned_padding", C.c_size_t)]
+
+
 class EncodeInput(C.Structure):
     _fields_ = [("buffer", C.c_void_p), ("row_stride", C.c_int64), ("width", C.c_int32), ("height", C.c_int32), ("format", C.c_int32),
                 ("on_host", C.c_int32), ("subsampling", C.c_int32), ("quality", C.c_int32), ("restart_interval", C.c_int32)]
@@ -32,7 +41,8 @@ class EncodeInput(C.Structure):
 
 EXPORTS = ["b200jpeg_version", "b200jpeg_status_string", "b200jpeg_parse_header", "b200jpeg_decoder_create", "b200jpeg_decoder_destroy",
            "b200jpeg_decode_batch", "b200jpeg_decode_prepare", "b200jpeg_decode_run", "b200jpeg_decoder_get_stats", "b200jpeg_decoder_get_stage_times", "b200jpeg_debug_fetch",
-           "b200jpeg_encoder_create", "b200jpeg_encoder_destroy", "b200jpeg_encode_batch", "b200jpeg_encoder_get_stats"]
+           "b200jpeg_encoder_create", "b200jpeg_encoder_destroy", "b200jpeg_encode_batch", "b200jpeg_encoder_get_stats",
+           "b200jpeg_decoder_set_allocators", "b200jpeg_encoder_set_allocators"]
 
 _lib = None
 
@@ -64,6 +74,8 @@ def lib():
         L.b200jpeg_encode_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(EncodeInput), C.POINTER(C.c_void_p), C.POINTER(C.c_size_t),
                                             C.POINTER(C.c_size_t), C.c_void_p, C.POINTER(C.c_int32)]
         L.b200jpeg_encoder_get_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        L.b200jpeg_decoder_set_allocators.argtypes = [C.c_void_p, C.POINTER(Allocators)]
+        L.b200jpeg_encoder_set_allocators.argtypes = [C.c_void_p, C.POINTER(Allocators)]
         _lib = L
     return _lib
 

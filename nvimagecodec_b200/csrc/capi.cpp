@@ -86,6 +86,36 @@ int b200jpeg_decoder_create(b200jpegDecoder_t* decoder, int device_id, const cha
     return B200JPEG_STATUS_SUCCESS;
 }
 
+static Allocators to_allocators(const b200jpegAllocators_t* a)
+{
+    Allocators r;
+    if (a) {
+        r.device_malloc = reinterpret_cast<AllocFn>(a->device_malloc);
+        r.device_free = reinterpret_cast<FreeFn>(a->device_free);
+        r.device_ctx = a->device_ctx;
+        r.device_padding = a->device_padding;
+        r.pinned_malloc = reinterpret_cast<AllocFn>(a->pinned_malloc);
+        r.pinned_free = reinterpret_cast<FreeFn>(a->pinned_free);
+        r.pinned_ctx = a->pinned_ctx;
+        r.pinned_padding = a->pinned_padding;
+    }
+    return r;
+}
+
+int b200jpeg_decoder_set_allocators(b200jpegDecoder_t decoder, const b200jpegAllocators_t* allocators)
+{
+    if (!decoder)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    return decoder->impl->set_allocators(to_allocators(allocators));
+}
+
+int b200jpeg_encoder_set_allocators(b200jpegEncoder_t encoder, const b200jpegAllocators_t* allocators)
+{
+    if (!encoder)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    return encoder->impl->set_allocators(to_allocators(allocators));
+}
+
 int b200jpeg_decoder_destroy(b200jpegDecoder_t decoder)
 {
     if (!decoder)

@@ -90,13 +90,16 @@ Decoder::~Decoder()
         cudaSetDevice(device_);
     DevBuf* dbufs[] = {&d_records_, &d_blkrec_, &d_nrec_, &d_recoff_, &d_raw_, &d_clean_, &d_coef_, &d_dc_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
         &d_rec_, &d_abs_, &d_wl0_, &d_wl1_, &d_sync_, &d_out_};
+    for (cudaStream_t st : streams_)
+        if (st)
+            cudaStreamSynchronize(st);
     for (DevBuf* b : dbufs)
-        if (b->p)
-            cudaFree(b->p);
+        alloc_.release(false, b->p, b->cap, streams_[0]);
     DevBuf* hbufs[] = {&h_raw_, &h_meta_, &h_states_};
     for (DevBuf* b : hbufs)
-        if (b->p)
-            cudaFreeHost(b->p);
+        alloc_.release(true, b->p, b->cap, streams_[0]);
+    if (streams_[0])
+        cudaStreamSynchronize(streams_[0]); // stream-ordered frees
     if (ev_in_)
         cudaEventDestroy(ev_in_);
     for (cudaEvent_t e : ev_stage_)
@@ -146,19 +149,26 @@ int Decoder::ensure(DevBuf& b, size_t bytes)
     if (b.p) {
         for (cudaStream_t st : streams_)
             B2J_CUDA(cudaStreamSynchronize(st));
-        B2J_CUDA(cudaFree(b.p));
+        alloc_.release(false, b.p, b.cap, streams_[0]);
         scratch_bytes_ -= b.cap;
         b.p = nullptr;
         b.cap = 0;
     }
-    const size_t want = align_up(bytes + bytes / 8, 1 << 20);
-    if (cudaMalloc(&b.p, want) != cudaSuccess) {
-        cudaGetLastError();
+    size_t want = align_up(bytes + bytes / 8, 1 << 20);
+    if (!alloc_.alloc(false, &b.p, &want, streams_[0]))
         return B200JPEG_STATUS_ALLOC_FAILED;
-    }
+    B2J_CUDA(cudaStreamSynchronize(streams_[0])); // a stream-ordered allocation is used on every group's stream
     b.cap = want;
     scratch_bytes_ += want;
     return 0;
+}
+
+int Decoder::set_allocators(const Allocators& a)
+{
+    if (scratch_bytes_ != 0 || h_raw_.p || h_meta_.p || h_states_.p)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    alloc_ = a;
+    return B200JPEG_STATUS_SUCCESS;
 }
 
 int Decoder::ensure_pinned(DevBuf& b, size_t bytes)
@@ -168,15 +178,14 @@ int Decoder::ensure_pinned(DevBuf& b, size_t bytes)
     if (b.p) {
         for (cudaStream_t st : streams_)
             B2J_CUDA(cudaStreamSynchronize(st));
-        B2J_CUDA(cudaFreeHost(b.p));
+        alloc_.release(true, b.p, b.cap, streams_[0]);
         b.p = nullptr;
         b.cap = 0;
     }
-    const size_t want = align_up(bytes + bytes / 8, 1 << 20);
-    if (cudaHostAlloc(&b.p, want, cudaHostAllocDefault) != cudaSuccess) {
-        cudaGetLastError();
+    size_t want = align_up(bytes + bytes / 8, 1 << 20);
+    if (!alloc_.alloc(true, &b.p, &want, streams_[0]))
         return B200JPEG_STATUS_ALLOC_FAILED;
-    }
+    B2J_CUDA(cudaStreamSynchronize(streams_[0]));
     b.cap = want;
     return 0;
 }

@@ -10,6 +10,7 @@
 #include <string>
 #include <thread>
 #include <vector>
+#include "alloc.h"
 #include "batch_plan.h"
 #include "decode_kernels.h"
 
@@ -118,6 +119,8 @@ class Decoder
     int get_stage_times(float* ms, int n); // per Stage, last run
     int64_t debug_fetch(int what, int image, int comp, void* dst, size_t cap);
     int device() const { return device_; }
+    // memory callbacks for every later allocation; only before the first decode (buffers are returned to where they came from)
+    int set_allocators(const Allocators& a);
 
   private:
     int ensure(DevBuf& b, size_t bytes);
@@ -131,6 +134,7 @@ class Decoder
 
     int device_;
     DecoderOptions opt_;
+    Allocators alloc_;
     cudaStream_t streams_[kMaxGroups] = {};
     cudaEvent_t ev_in_ = nullptr, ev_meta_ = nullptr;
     bool trace_ = false;

@@ -83,23 +83,26 @@ struct Encoder::Impl
     uint64_t stats[8] = {};
     float stage_ms[4] = {};
 
+    Allocators alloc;
+    bool allocated = false;
+
     int ensure(Buf& b, size_t bytes, bool pinned)
     {
         if (bytes <= b.cap)
             return 0;
-        if (b.p) { // cudaFree waits for the device; nothing in flight uses this buffer (whole-batch buffers are sized before the
-            // first launch of a call, per-group ones are only used by their own group)
-            B2J_CUDA(pinned ? cudaFreeHost(b.p) : cudaFree(b.p));
+        if (b.p) { // nothing in flight may still use the buffer: whole-batch buffers are sized before the first launch of a call,
+            // per-group ones are only used by their own group, whose stream has drained when it gets here again
+            B2J_CUDA(cudaDeviceSynchronize());
+            alloc.release(pinned, b.p, b.cap, stream);
             b.p = nullptr;
             b.cap = 0;
         }
-        const size_t want = align_up(bytes + bytes / 8 + 256, 1 << 16);
-        const cudaError_t e = pinned ? cudaHostAlloc(&b.p, want, cudaHostAllocDefault) : cudaMalloc(&b.p, want);
-        if (e != cudaSuccess) {
-            cudaGetLastError();
+        size_t want = align_up(bytes + bytes / 8 + 256, 1 << 16);
+        if (!alloc.alloc(pinned, &b.p, &want, stream))
             return B200JPEG_STATUS_ALLOC_FAILED;
-        }
+        B2J_CUDA(cudaStreamSynchronize(stream)); // a stream-ordered allocation is used on every group's stream
         b.cap = want;
+        allocated = true;
         return 0;
     }
 };
@@ -120,17 +123,17 @@ Encoder::~Encoder()
     Impl& s = *impl_;
     cudaSetDevice(s.device);
     Buf* dev[] = {&s.d_nzmask, &s.d_pixels, &s.d_planes, &s.d_meta, &s.d_dyn, &s.d_coef, &s.d_dc, &s.d_acbits, &s.d_blk_off, &s.d_seg_bits, &s.d_seg_off, &s.d_img_bytes};
+    cudaDeviceSynchronize();
     for (Buf* b : dev)
-        if (b->p)
-            cudaFree(b->p);
+        s.alloc.release(false, b->p, b->cap, s.stream);
     for (int g = 0; g < kEncGroups; ++g)
         for (Buf* b : {&s.d_stream[g], &s.d_chunks[g], &s.d_out[g]})
-            if (b->p)
-                cudaFree(b->p);
+            s.alloc.release(false, b->p, b->cap, s.stream);
     Buf* host[] = {&s.h_pixels, &s.h_meta, &s.h_dyn, &s.h_sizes, &s.h_out};
     for (Buf* b : host)
-        if (b->p)
-            cudaFreeHost(b->p);
+        s.alloc.release(true, b->p, b->cap, s.stream);
+    if (s.stream)
+        cudaStreamSynchronize(s.stream); // stream-ordered frees
     for (cudaEvent_t e : s.ev)
         if (e)
             cudaEventDestroy(e);
@@ -560,6 +563,14 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
     s.stats[5] = uint64_t(s.stage_ms[0] * 1e3f);
     s.stats[6] = uint64_t((s.stage_ms[1] + s.stage_ms[2]) * 1e3f);
     s.stats[7] = uint64_t(s.stage_ms[3] * 1e3f);
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+int Encoder::set_allocators(const Allocators& a)
+{
+    if (impl_->allocated)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    impl_->alloc = a;
     return B200JPEG_STATUS_SUCCESS;
 }
 

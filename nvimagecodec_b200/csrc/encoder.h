@@ -4,6 +4,7 @@
 #include <cstddef>
 #include <cstdint>
 #include "../../include/b200jpeg.h"
+#include "alloc.h"
 
 namespace b200jpeg {
 
@@ -16,6 +17,7 @@ class Encoder
     int encode(int n, const b200jpegEncodeInput_t* inputs, uint8_t* const* out, const size_t* out_capacity, size_t* out_sizes,
         cudaStream_t user_stream, int32_t* statuses);
     void get_stats(uint64_t* s8) const;
+    int set_allocators(const Allocators& a); // before the first encode
 
   private:
     struct Impl;

@@ -461,6 +461,25 @@ struct Extension
     }
 };
 
+// the framework's allocators (include/nvimgcodec.h:232-302) in the C ABI's form; cudaStream_t and void* are the same at the ABI level
+b200jpegAllocators_t exec_allocators(const nvimgcodecExecutionParams_t* exec)
+{
+    b200jpegAllocators_t a{};
+    if (exec->device_allocator && exec->device_allocator->device_malloc && exec->device_allocator->device_free) {
+        a.device_malloc = reinterpret_cast<b200jpegMalloc_t>(exec->device_allocator->device_malloc);
+        a.device_free = reinterpret_cast<b200jpegFree_t>(exec->device_allocator->device_free);
+        a.device_ctx = exec->device_allocator->device_ctx;
+        a.device_padding = exec->device_allocator->device_mem_padding;
+    }
+    if (exec->pinned_allocator && exec->pinned_allocator->pinned_malloc && exec->pinned_allocator->pinned_free) {
+        a.pinned_malloc = reinterpret_cast<b200jpegMalloc_t>(exec->pinned_allocator->pinned_malloc);
+        a.pinned_free = reinterpret_cast<b200jpegFree_t>(exec->pinned_allocator->pinned_free);
+        a.pinned_ctx = exec->pinned_allocator->pinned_ctx;
+        a.pinned_padding = exec->pinned_allocator->pinned_mem_padding;
+    }
+    return a;
+}
+
 nvimgcodecStatus_t dec_create(void* instance, nvimgcodecDecoder_t* decoder, const nvimgcodecExecutionParams_t* exec, const char* options)
 {
     auto* ext = reinterpret_cast<Extension*>(instance);
@@ -476,6 +495,8 @@ nvimgcodecStatus_t dec_create(void* instance, nvimgcodecDecoder_t* decoder, cons
         log_msg(ext->fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_WARNING, kDecoderId, std::string("decoder unavailable: ") + b200jpeg_status_string(rc));
         return rc == B200JPEG_STATUS_ARCH_MISMATCH ? NVIMGCODEC_STATUS_EXTENSION_ARCH_MISMATCH : NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR;
     }
+    const b200jpegAllocators_t al = exec_allocators(exec);
+    b200jpeg_decoder_set_allocators(st->dec, &al);
     *decoder = reinterpret_cast<nvimgcodecDecoder_t>(st.release());
     return NVIMGCODEC_STATUS_SUCCESS;
 }
@@ -495,6 +516,8 @@ nvimgcodecStatus_t enc_create(void* instance, nvimgcodecEncoder_t* encoder, cons
         log_msg(ext->fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_WARNING, kEncoderId, std::string("encoder unavailable: ") + b200jpeg_status_string(rc));
         return rc == B200JPEG_STATUS_ARCH_MISMATCH ? NVIMGCODEC_STATUS_EXTENSION_ARCH_MISMATCH : NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR;
     }
+    const b200jpegAllocators_t al = exec_allocators(exec);
+    b200jpeg_encoder_set_allocators(st->enc, &al);
     *encoder = reinterpret_cast<nvimgcodecEncoder_t>(st.release());
     return NVIMGCODEC_STATUS_SUCCESS;
 }

@@ -240,3 +240,48 @@ def test_region_of_interest(torch_mod, refdec):
     st = dec.decode_into([d] * len(bad), [t.data_ptr()] * len(bad), [64 * 3] * len(bad), [4] * len(bad), False, rois=bad)
     assert all(s != 0 for s in st[:3]), st
     dec.close()
+
+
+def test_custom_allocators(torch_mod, refdec):
+    """b200jpeg_decoder_set_allocators / b200jpeg_encoder_set_allocators (the framework's device / pinned allocator
+    callbacks): every device allocation goes through the callbacks, frees pass the allocated size back, results unchanged"""
+    import ctypes as C
+    torch = torch_mod
+    from nvimagecodec_b200 import _capi
+    from nvimagecodec_b200.decoder import Decoder
+    from nvimagecodec_b200.encoder import Encoder, EncodeParams
+    live, log = {}, {"malloc": 0, "free": 0, "bad_free": 0}
+
+    def dev_malloc(ctx, out, size, stream):
+        p = torch.cuda.caching_allocator_alloc(size)
+        live[p] = size
+        out[0] = p
+        log["malloc"] += 1
+        return 0
+
+    def dev_free(ctx, p, size, stream):
+        if live.pop(p, None) != size:
+            log["bad_free"] += 1
+        torch.cuda.caching_allocator_delete(p)
+        log["free"] += 1
+        return 0
+
+    al = _capi.Allocators()
+    al.device_malloc, al.device_free, al.device_padding = _capi.MALLOC_FN(dev_malloc), _capi.FREE_FN(dev_free), 512
+    datas = [make_jpeg(31 + i, 320, 200, samp, 90) for i, samp in enumerate([(2, 2), (1, 1)])]
+    dec = Decoder(0, options=":fancy_upsampling=1")
+    assert _capi.lib().b200jpeg_decoder_set_allocators(dec._h, C.byref(al)) == 0
+    imgs = dec.decode(datas)
+    want, _, _ = refdec[1].decode_host(datas)
+    for im, w in zip(imgs, want):
+        assert np.array_equal(im.cpu(), w)
+    assert log["malloc"] > 5 and all(s % 512 == 0 for s in live.values())
+    assert _capi.lib().b200jpeg_decoder_set_allocators(dec._h, C.byref(al)) != 0  # too late: buffers exist
+    dec.close()
+    enc = Encoder(0)
+    assert _capi.lib().b200jpeg_encoder_set_allocators(enc._h, C.byref(al)) == 0
+    px = util.synth_image(3, 200, 120)
+    assert enc.encode(px, ".jpg", EncodeParams(quality=90, chroma_subsampling="4:2:0")) == port.encode(px, 90, (2, 2))
+    enc.close()
+    torch.cuda.synchronize()
+    assert not live and log["free"] == log["malloc"] and log["bad_free"] == 0, (live, log)
