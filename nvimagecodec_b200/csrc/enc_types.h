@@ -7,7 +7,6 @@ namespace b200jpeg {
 
 constexpr int kEncCta = 128;            // threads per CTA in the FDCT, bit-count and emit kernels: one 8x8 block per thread
 constexpr int kEncColorCta = 256;       // colour-conversion kernel: 4 pixels x vs rows per thread
-constexpr int kEncCoefPitch = 33;       // words per block in the shared-memory coefficient staging (32 + 1: conflict-free)
 constexpr int kEncMaxBlockBytes = 208;  // upper bound of one block's entropy-coded bits (64 x (16 + 10) bits) in bytes
 constexpr int kEncStuffThreads = 256;   // stuffing kernels: 16 stream bytes per thread
 constexpr int kEncStuffChunk = kEncStuffThreads * 16;

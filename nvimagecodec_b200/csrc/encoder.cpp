@@ -77,7 +77,7 @@ struct Encoder::Impl
     cudaEvent_t ev_in = nullptr, ev_meta = nullptr;
     cudaEvent_t ev_half[kEncGroups] = {}, ev_sizes[kEncGroups] = {}, ev_done[kEncGroups] = {};
     cudaEvent_t ev[8] = {};
-    Buf d_nzmask, d_pixels, d_planes, d_meta, d_dyn, d_coef, d_dc, d_acbits, d_blk_off, d_seg_bits, d_seg_off, d_img_bytes;
+    Buf d_nzmask, d_pixels, d_planes, d_meta, d_dyn, d_coef, d_dc, d_acbits, d_blk_off, d_tile_off, d_seg_off, d_img_bytes;
     Buf d_stream[kEncGroups], d_chunks[kEncGroups], d_out[kEncGroups]; // per group: they grow while other groups are in flight
     Buf h_pixels, h_meta, h_dyn, h_sizes, h_out;
     uint64_t stats[8] = {};
@@ -122,7 +122,7 @@ Encoder::~Encoder()
 {
     Impl& s = *impl_;
     cudaSetDevice(s.device);
-    Buf* dev[] = {&s.d_nzmask, &s.d_pixels, &s.d_planes, &s.d_meta, &s.d_dyn, &s.d_coef, &s.d_dc, &s.d_acbits, &s.d_blk_off, &s.d_seg_bits, &s.d_seg_off, &s.d_img_bytes};
+    Buf* dev[] = {&s.d_nzmask, &s.d_pixels, &s.d_planes, &s.d_meta, &s.d_dyn, &s.d_coef, &s.d_dc, &s.d_acbits, &s.d_blk_off, &s.d_tile_off, &s.d_seg_off, &s.d_img_bytes};
     cudaDeviceSynchronize();
     for (Buf* b : dev)
         s.alloc.release(false, b->p, b->cap, s.stream);
@@ -307,7 +307,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
         (rc = s.ensure(s.h_dyn, dyn_bytes, true)) || (rc = s.ensure(s.d_coef, total_blocks * 128, false)) || (rc = s.ensure(s.d_planes, plane_bytes, false)) ||
         (rc = s.ensure(s.d_dc, total_blocks * 2, false)) || (rc = s.ensure(s.d_acbits, total_blocks * 2, false)) || (rc = s.ensure(s.d_nzmask, total_blocks * 8, false)) ||
         (rc = s.ensure(s.d_blk_off, total_blocks * 4, false)) ||
-        (rc = s.ensure(s.d_seg_bits, size_t(map_emit.back()) * 4 + size_t(m) * 4, false)) ||
+        (rc = s.ensure(s.d_tile_off, size_t(map_emit.back()) * 4 + size_t(m) * 4, false)) ||
         (rc = s.ensure(s.d_seg_off, size_t(total_segs) * 4, false)) || (rc = s.ensure(s.d_img_bytes, size_t(m) * 8, false)) ||
         (rc = s.ensure(s.h_sizes, size_t(m) * 8, true)) || (host_pix_bytes && (rc = s.ensure(s.d_pixels, host_pix_bytes, false))))
         return rc;
@@ -355,7 +355,7 @@ int Encoder::encode(int n, const b200jpegEncodeInput_t* in, uint8_t* const* out,
         b.acbits = static_cast<uint16_t*>(s.d_acbits.p);
         b.nzmask = static_cast<uint64_t*>(s.d_nzmask.p);
         b.blk_off = static_cast<uint32_t*>(s.d_blk_off.p);
-        b.tile_off = static_cast<uint32_t*>(s.d_seg_bits.p);
+        b.tile_off = static_cast<uint32_t*>(s.d_tile_off.p);
         b.img_bits = b.tile_off + map_emit.back() + k0;
         b.seg_byte_off = static_cast<uint32_t*>(s.d_seg_off.p);
         b.img_stream_bytes = static_cast<uint32_t*>(s.d_img_bytes.p) + k0;

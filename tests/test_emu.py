@@ -121,3 +121,16 @@ def test_emulated_region_of_interest():
                 assert st == [0] * len(rois)
                 for r, o, wv in zip(rois, outs, want):
                     assert np.array_equal(o, wv), (fancy, w, h, samp, gray, fmt, r)
+
+
+def test_emulated_extended_sequential_sof1():
+    """An 8-bit extended-sequential stream (SOF1) is the baseline process with room for four tables per class: same path."""
+    d = bytearray(make_jpeg(55, 211, 133, (2, 2), 85))
+    k = d.find(b"\xff\xc0")
+    assert k > 0
+    d[k + 1] = 0xC1
+    d = bytes(d)
+    want, st, _ = ref.Session.shared().decoder(options=":fancy_upsampling=1").decode_host([d])
+    assert st == [ref.STATUS_SUCCESS]
+    outs, st, _, _ = emu.decode_batch([d], [(211, 133)], 4, 1, 128)
+    assert st == [0] and np.array_equal(outs[0], want[0])
