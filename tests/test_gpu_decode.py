@@ -285,3 +285,54 @@ def test_custom_allocators(torch_mod, refdec):
     enc.close()
     torch.cuda.synchronize()
     assert not live and log["free"] == log["malloc"] and log["bad_free"] == 0, (live, log)
+
+
+def _corruptions(rng, good, hdr):
+    """damaged copies of a good stream: bit flips, byte runs, inserted markers, truncation -- entropy-coded part only"""
+    lo, hi = hdr.scan_offset, hdr.scan_offset + hdr.scan_bytes
+    out = []
+    for k in range(40):
+        d = bytearray(good)
+        kind = k % 5
+        if kind == 0:
+            for _ in range(int(rng.integers(1, 6))):
+                d[int(rng.integers(lo, hi))] ^= 1 << int(rng.integers(0, 8))
+        elif kind == 1:
+            p = int(rng.integers(lo, hi - 40))
+            d[p:p + 32] = bytes(rng.integers(0, 256, 32, dtype=np.uint8))
+        elif kind == 2:
+            p = int(rng.integers(lo, hi - 2))
+            d[p:p + 2] = bytes([0xFF, int(rng.integers(0xC0, 0xFF))])
+        elif kind == 3:
+            d = d[:int(rng.integers(lo + 1, hi))] + b"\xff\xd9"
+        else:
+            p = int(rng.integers(lo, hi - 300))
+            d[p:p + 256] = b"\xff" * 256 if k % 2 else b"\x00" * 256
+        out.append(bytes(d))
+    return out
+
+
+@pytest.mark.timeout(300)
+def test_damaged_streams_are_contained(torch_mod, refdec):
+    """Damaged entropy-coded data must neither hang nor disturb the good images of the same batch; every damaged image
+    comes back as decoded-with-garbage (status 0, like libjpeg's warnings) or CORRUPT_STREAM, never anything else."""
+    torch = torch_mod
+    import nvimagecodec_b200 as nb
+    from nvimagecodec_b200.decoder import Decoder
+    rng = np.random.default_rng(77)
+    dec = Decoder(0, options=":fancy_upsampling=1")
+    for (w, h, samp, ri) in [(320, 240, (2, 2), 0), (333, 211, (1, 1), 4), (640, 200, (2, 1), 0)]:
+        good = make_jpeg(6000 + w, w, h, samp, 88, restart_interval=ri)
+        bad = _corruptions(rng, good, nb.parse_header(good))
+        datas = [good] + bad + [good]
+        outs = [torch.zeros((h + 2, w * 3), dtype=torch.uint8, device="cuda") for _ in datas]  # two guard rows per image
+        st = dec.decode_into(datas, [o.data_ptr() for o in outs], [w * 3] * len(datas), [4] * len(datas))
+        torch.cuda.synchronize()
+        assert st[0] == 0 and st[-1] == 0
+        assert all(s in (0, 2, 4) for s in st), st
+        want = refdec[1].decode_host([good])[0][0]
+        for k in (0, len(datas) - 1):
+            assert np.array_equal(outs[k][:h].cpu().numpy().reshape(h, w, 3), want)
+        for o in outs:
+            assert not o[h:].any(), "wrote past the image"
+    dec.close()
