@@ -37,7 +37,7 @@ typedef enum
     B200JPEG_STATUS_SUCCESS = 0,
     B200JPEG_STATUS_INVALID_PARAMETER = 1,
     B200JPEG_STATUS_BAD_JPEG = 2,         /* marker syntax broken / truncated header */
-    B200JPEG_STATUS_UNSUPPORTED = 3,      /* valid JPEG outside this codec's scope (progressive, arithmetic, 12-bit, CMYK, 4:1:1 ...) */
+    B200JPEG_STATUS_UNSUPPORTED = 3,      /* valid JPEG outside this codec's scope (progressive, arithmetic, 12-bit, CMYK, 4:1:0 ...) */
     B200JPEG_STATUS_CORRUPT_STREAM = 4,   /* entropy-coded data inconsistent with the header (detected on the GPU) */
     B200JPEG_STATUS_CUDA_ERROR = 5,
     B200JPEG_STATUS_ARCH_MISMATCH = 6,    /* device is not sm_100 */

@@ -86,11 +86,11 @@ __device__ __forceinline__ void warp_store_row(uint8_t* dst, const uint32_t* s_r
     }
 }
 
-// one chroma row segment of a lane: HX == 2: 8 samples + left/right neighbour; HX == 1: 16 samples
+// one chroma row segment of a lane: HX == 2: 8 samples + left/right neighbour; HX == 1: 16 samples; HX == 4: 4 samples
 template <int HX>
 struct ChromaSeg
 {
-    uint32_t w[HX == 2 ? 2 : 4];
+    uint32_t w[HX == 2 ? 2 : (HX == 4 ? 1 : 4)];
     int left, right; // HX == 2 only
 };
 
@@ -103,6 +103,9 @@ __device__ __forceinline__ void load_seg(ChromaSeg<HX>& s, const uint8_t* row, i
         s.w[1] = v.y;
         s.left = row[c0 > 0 ? c0 - 1 : 0];
         s.right = row[c0 + 8 < dsw ? c0 + 8 : dsw - 1];
+    } else if constexpr (HX == 4) {
+        s.w[0] = *reinterpret_cast<const uint32_t*>(row + c0);
+        s.left = s.right = 0;
     } else {
         const uint2 v = *reinterpret_cast<const uint2*>(row + c0), u = *reinterpret_cast<const uint2*>(row + c0 + 8);
         s.w[0] = v.x;
@@ -156,6 +159,10 @@ __device__ __forceinline__ void upsample_row(const ChromaSeg<HX>& a, const Chrom
 #pragma unroll
         for (int c = 0; c < 8; ++c)
             up[2 * c] = up[2 * c + 1] = n[c + 1]; // box
+    } else if constexpr (HX == 4) { // 4:1:1: plain replication (jdsample.c int_upsample), whatever fancy_upsampling says
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            up[i] = byte_of(a.w[0], i >> 2);
     } else {
         const ChromaSeg<HX>& nr = (VY == 2 && r == 1) ? bseg : a;
         const ChromaSeg<HX>& fr = (VY == 2 && r == 1) ? a : bseg;
@@ -348,7 +355,9 @@ __global__ void __launch_bounds__(kColorCta) k_color(BatchDev b)
         else
             color_tile<1, 2>(b, im, tile, s_warp, lane);
     } else {
-        if (hx == 2)
+        if (hx == 4)
+            color_tile<4, 1>(b, im, tile, s_warp, lane);
+        else if (hx == 2)
             color_tile<2, 1>(b, im, tile, s_warp, lane);
         else
             color_tile<1, 1>(b, im, tile, s_warp, lane);

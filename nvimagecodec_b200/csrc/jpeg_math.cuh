@@ -246,6 +246,11 @@ B2J_HD void upsample_unit(const uint8_t* P, int pitch, int dsw, int dsh, bool fa
         const uint8_t* row = P + uint64_t(q) * pitch;
         if constexpr (HX == 1) {
             load16(row + c0, up[0]);
+        } else if constexpr (HX == 4) { // 4:1:1: each chroma sample covers four pixels (jdsample.c int_upsample:161-203)
+            const uint32_t w = *reinterpret_cast<const uint32_t*>(row + c0);
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                up[0][i] = int((w >> (8 * (i >> 2))) & 255u);
         } else {
             int a[NC + 2];
             load_chroma_row<NC>(row, c0, dsw, a);

@@ -181,7 +181,7 @@ bool is_supported(const ParsedJpeg& p)
         return false;
     if (p.ncomp == 3) {
         const int css = subsampling_of(p);
-        if (css != 0 && css != 2 && css != 3 && css != 4)
+        if (css != 0 && css != 2 && css != 3 && css != 4 && css != 5) // 4:4:4, 4:2:2, 4:2:0, 4:4:0, 4:1:1
             return false;
         // colour space decision of jdapimin.c default_decompress_parms:117-196: JFIF => YCbCr; Adobe transform 0 => RGB;
         // no marker: ids 'R','G','B' => RGB, else YCbCr.  RGB-coded JPEGs are out of scope.

@@ -146,7 +146,7 @@ nvimgcodecStatus_t dec_can_decode(nvimgcodecDecoder_t decoder, nvimgcodecProcess
                 continue;
             }
             if (!si.supported) {
-                // progressive / arithmetic / lossless => ENCODING_UNSUPPORTED, everything else (CMYK, 4:1:1, 12-bit,
+                // progressive / arithmetic / lossless => ENCODING_UNSUPPORTED, everything else (CMYK, 4:1:0, 12-bit,
                 // multi-scan ...) => CODESTREAM_UNSUPPORTED; both send the sample to the next decoder
                 status[i] = (si.sof_marker != 0xC0 && si.sof_marker != 0xC1) ? NVIMGCODEC_PROCESSING_STATUS_ENCODING_UNSUPPORTED
                                                                              : NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED;

@@ -441,9 +441,11 @@ static int upsampled(const jo_image* im, int c, int x, int y, int fancy)
     const jo_comp* k = &im->comp[c];
     int pitch = k->wib * 8;
     const uint8_t* P = k->plane;
-    int hx = im->hmax / k->hs, vy = im->vmax / k->vs; /* expansion factors 1 or 2 */
+    int hx = im->hmax / k->hs, vy = im->vmax / k->vs; /* expansion factors 1 or 2 (4:1:1: 4 x 1) */
     if (hx == 1 && vy == 1)
         return P[(size_t)y * pitch + x];
+    if (hx == 4 && vy == 1) /* neither a 2:1 case nor merged: int_upsample (jdsample.c:161-203, chosen at :501-520) replicates */
+        return P[(size_t)y * pitch + (x >> 2)];
     if (hx == 2 && vy == 1) {
         const uint8_t* in = P + (size_t)y * pitch;
         int cx = x >> 1;

@@ -351,6 +351,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                 int yrow[2] = {-1, -1};
                 if (vy == 2 && hx == 2) { color_unit<2, 2>(b, im, q, x0, px, yrow); store_unit_simple<2>(im, x0, px, yrow); }
                 else if (vy == 2) { color_unit<1, 2>(b, im, q, x0, px, yrow); store_unit_simple<2>(im, x0, px, yrow); }
+                else if (hx == 4) { color_unit<4, 1>(b, im, q, x0, px, yrow); store_unit_simple<1>(im, x0, px, yrow); }
                 else if (hx == 2) { color_unit<2, 1>(b, im, q, x0, px, yrow); store_unit_simple<1>(im, x0, px, yrow); }
                 else { color_unit<1, 1>(b, im, q, x0, px, yrow); store_unit_simple<1>(im, x0, px, yrow); }
             }

@@ -18,7 +18,7 @@ pytestmark = pytest.mark.skipif(not util.have_ref(), reason="corpus needs oracle
 CASES = [(227, 149, (2, 2), 75, 0, False), (64, 48, (1, 1), 90, 0, False), (131, 77, (2, 1), 85, 0, False), (131, 77, (1, 2), 85, 0, False),
          (333, 211, (2, 2), 90, 5, False), (17, 9, (2, 2), 90, 0, False), (3, 5, (2, 2), 90, 0, False), (2, 2, (2, 1), 90, 0, False),
          (1, 1, (1, 1), 90, 0, False), (640, 426, (2, 2), 75, 0, False), (100, 100, (1, 1), 95, 7, False), (500, 375, (2, 2), 75, 1, False),
-         (400, 300, (2, 1), 90, 50, False), (201, 99, (1, 1), 85, 0, True)]
+         (400, 300, (2, 1), 90, 50, False), (201, 99, (1, 1), 85, 0, True), (227, 149, (4, 1), 85, 0, False), (330, 77, (4, 1), 90, 3, False)]
 
 
 def corpus():

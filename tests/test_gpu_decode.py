@@ -101,6 +101,8 @@ CASES = [
     (500, 375, (2, 2), 75, 1, False),
     (800, 600, (2, 1), 90, 50, False),
     (201, 99, (1, 1), 85, 0, True),
+    (227, 149, (4, 1), 85, 0, False),
+    (330, 77, (4, 1), 90, 3, False),
     (1920, 1080, (2, 2), 90, 0, False),
     (1280, 720, (2, 2), 50, 0, False),
 ]
