@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libb200jpeg.so")
+LIB_PATH = os.environ.get("B200JPEG_LIB") or os.path.join(HERE, "lib", "libb200jpeg.so")  # override: kernel-variant experiments
 EXT_DIR = os.path.join(HERE, "extensions")
 EXT_PATH = os.path.join(EXT_DIR, "libb200jpeg_ext.so")
 

@@ -14,21 +14,9 @@
 #include <cuda_runtime.h>
 #include "decode_kernels.h"
 #include "jpeg_math.cuh"
+#include "cta_lookup.cuh"
 
 namespace b200jpeg {
-
-__device__ __forceinline__ int find_image_c(const uint32_t* __restrict__ map, int n, uint32_t cta)
-{
-    int lo = 0, hi = n - 1;
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (map[mid] <= cta)
-            lo = mid;
-        else
-            hi = mid - 1;
-    }
-    return lo;
-}
 
 __device__ __forceinline__ int byte_of(uint32_t w, int i) { return int(__byte_perm(w, 0, 0x4440 + i)); }
 
@@ -337,11 +325,14 @@ __device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& i
 
 constexpr int kColorWarpWords = 2 * 3 * kPlaneStride > 2 * kRowStride ? 2 * 3 * kPlaneStride : 2 * kRowStride;
 
-__global__ void __launch_bounds__(kColorCta) k_color(BatchDev b)
+#ifndef B2J_COLOR_MIN_CTAS
+#define B2J_COLOR_MIN_CTAS 8 // resident CTAs per SM the register allocation aims at
+#endif
+__global__ void __launch_bounds__(kColorCta, B2J_COLOR_MIN_CTAS) k_color(BatchDev b)
 {
     __shared__ __align__(16) uint32_t s_stage[(kColorCta / 32) * kColorWarpWords];
     const uint32_t cta_abs = blockIdx.x + b.base_color;
-    const int img = find_image_c(b.cta_map_color, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_color, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tile = (cta_abs - b.cta_map_color[img]) * (kColorCta / 32) + warp;

@@ -20,21 +20,9 @@
 #include <cuda_runtime.h>
 #include "decode_kernels.h"
 #include "jpeg_math.cuh"
+#include "cta_lookup.cuh"
 
 namespace b200jpeg {
-
-__device__ __forceinline__ int find_image(const uint32_t* __restrict__ map, int n, uint32_t cta)
-{
-    int lo = 0, hi = n - 1;
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (map[mid] <= cta)
-            lo = mid;
-        else
-            hi = mid - 1;
-    }
-    return lo;
-}
 
 // ------------------------------------------------------------------------------------------------------------------
 // Unstuffing
@@ -90,7 +78,7 @@ __device__ __forceinline__ ByteClass classify16(const uint8_t* __restrict__ raw,
 __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_count(BatchDev b)
 {
     const uint32_t cta_abs = blockIdx.x + b.base_unstuff;
-    const int img = find_image(b.cta_map_unstuff, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_unstuff, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     const uint32_t chunk = cta_abs - b.cta_map_unstuff[img];
     const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
@@ -159,7 +147,7 @@ __global__ void __launch_bounds__(32) k_unstuff_scan(BatchDev b)
 __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
 {
     const uint32_t cta_abs = blockIdx.x + b.base_unstuff;
-    const int img = find_image(b.cta_map_unstuff, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_unstuff, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     const uint32_t chunk = cta_abs - b.cta_map_unstuff[img];
     const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
@@ -343,31 +331,32 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
 // conflict free for 16-byte accesses) and reads the slot back as the IDCT input.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kIdctPitch = 144;
-__constant__ uint8_t c_zz_next[kRecZigzagNextSize] = B2J_ZIGZAG_NEXT_INIT;
-__global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
+#ifndef B2J_IDCT_MIN_CTAS
+#define B2J_IDCT_MIN_CTAS 8 // resident CTAs per SM the register allocation aims at
+#endif
+__constant__ uint8_t c_zz_next[kRecZigzagInit] = B2J_ZIGZAG_NEXT_INIT;
+__global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b)
 {
     __shared__ __align__(16) uint8_t s_blk[kIdctCta * kIdctPitch];
     __shared__ uint16_t s_q[3 * 64];
-    __shared__ uint8_t s_zz[kRecZigzagNextSize + 3];
+    __shared__ uint8_t s_zz[kRecZigzagNextSize];
     const uint32_t cta_abs = blockIdx.x + b.base_idct;
-    const int img = find_image(b.cta_map_idct, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_idct, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     for (int i = threadIdx.x; i < im.ncomp_out * 64; i += kIdctCta)
         s_q[i] = b.quant[im.qt[i >> 6] * 64 + (i & 63)];
     const uint32_t u = (cta_abs - b.cta_map_idct[img]) * kIdctCta + threadIdx.x;
     const IdctBlockRef ref = idct_locate(im, u);
-    if (threadIdx.x < kRecZigzagNextSize)
-        s_zz[threadIdx.x] = c_zz_next[threadIdx.x];
+    for (int i = threadIdx.x; i < kRecZigzagNextSize; i += kIdctCta)
+        s_zz[i] = zigzag_next_entry(c_zz_next, i);
     __syncthreads();
     if (ref.comp < 0)
         return;
     { // region of interest: blocks none of whose samples can reach a pixel of the region (8 pixels of margin cover the
       // neighbours the upsampling filters look at) are not needed
-        const uint64_t rel = ref.dst - im.plane_off[ref.comp];
-        const int by = int(rel / uint64_t(ref.pitch)) >> 3, bx = int(rel % uint64_t(ref.pitch)) >> 3;
-        const int sx = 8 * (im.hmax / im.hs[ref.comp]), sy = 8 * (im.vmax / im.vs[ref.comp]); // block size in image pixels
-        if ((bx + 1) * sx <= im.roi_x - 8 || bx * sx >= im.roi_x + im.roi_w + 8 || (by + 1) * sy <= im.roi_y - 8 ||
-            by * sy >= im.roi_y + im.roi_h + 8)
+        const int sx = (8 * im.hmax) >> (im.hs[ref.comp] >> 1), sy = (8 * im.vmax) >> (im.vs[ref.comp] >> 1); // block size in image pixels
+        if ((ref.bx + 1) * sx <= im.roi_x - 8 || ref.bx * sx >= im.roi_x + im.roi_w + 8 || (ref.by + 1) * sy <= im.roi_y - 8 ||
+            ref.by * sy >= im.roi_y + im.roi_h + 8)
             return;
     }
     // the thread's own slot: zero it, scatter the block's coefficient records into it, read it back as a dense block
@@ -375,9 +364,14 @@ __global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
 #pragma unroll
     for (int i = 0; i < 8; ++i)
         reinterpret_cast<uint4*>(slot)[i] = make_uint4(0, 0, 0, 0);
-    if (records_to_block(b.rec + im.rec_off, b.blk_rec[im.coef_off / 64 + ref.src_blk], b.states[img].rec_total, s_zz,
-            reinterpret_cast<int16_t*>(slot)))
-        atomicOr(&b.states[img].error, kErrBadCode);
+    {
+        const uint32_t* first_rec = b.blk_rec + im.coef_off / 64 + ref.src_blk;
+        const uint32_t total = min(b.states[img].rec_total, im.rec_cap);
+        const uint32_t c = first_rec[0];
+        const uint32_t e = ref.src_blk + 1u < im.total_blocks ? first_rec[1] - 1u : total; // up to the next block's DC padding
+        if (records_to_block(b.rec + im.rec_off, min(c, total), min(e, total), s_zz, reinterpret_cast<int16_t*>(slot)))
+            atomicOr(&b.states[img].error, kErrBadCode);
+    }
     alignas(16) int16_t blk[64];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
@@ -395,8 +389,7 @@ __global__ void __launch_bounds__(kIdctCta) k_idct(BatchDev b)
     // so when both sit in this block (ds_w % 8 != 0) column ds_w gets a copy of column ds_w - 1.
     const int dsw = im.ds_w[ref.comp];
     if (im.hs[ref.comp] < im.hmax && (dsw & 7) != 0) {
-        const int bx = int((ref.dst - im.plane_off[ref.comp]) % uint64_t(ref.pitch)) >> 3;
-        if (bx == (dsw >> 3)) {
+        if (ref.bx == (dsw >> 3)) {
             const int e = dsw & 7; // 1..7: copy sample e-1 to sample e in every row
 #pragma unroll
             for (int r = 0; r < 8; ++r) {

@@ -16,7 +16,7 @@ int launch_unstuff(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 // rounds 0 and 1 over every subsequence
 int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 // the cooperative work-list kernel (grid size from huff_configure); -1 on launch failure
-int launch_huff_tail(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid);
+int launch_huff_tail(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid, int plain_rounds);
 // set the dynamic shared memory limits for b.lut_slots / b.stream_words and size the cooperative tail grid; -1 on error
 int huff_configure(const BatchDev& b, int device, int* tail_grid);
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st);

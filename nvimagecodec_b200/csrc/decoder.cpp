@@ -64,6 +64,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
             int v = std::atoi(value.c_str());
             if (v >= 32 && v <= 4096 && (v % 4) == 0)
                 o.subseq_bytes = v;
+        } else if (name == "tail_launches") {
+            o.tail_launches = std::max(0, std::min(32, std::atoi(value.c_str())));
         } else if (name == "stream_priority") {
             o.stream_priority = std::atoi(value.c_str()) != 0;
         } else if (name == "copy_threads")
@@ -623,7 +625,7 @@ int Decoder::launch_group(int g)
     mark(kStageSync);
     stat_launches_ += launch_huff_sync(gr.dev, gr.dims, st);
     mark(kStageTail);
-    const int ns = launch_huff_tail(gr.dev, gr.dims, st, gr.tail_grid);
+    const int ns = launch_huff_tail(gr.dev, gr.dims, st, gr.tail_grid, opt_.tail_launches);
     if (ns < 0) {
         std::fprintf(stderr, "b200jpeg: cooperative launch failed: %s\n", cudaGetErrorString(cudaGetLastError()));
         return B200JPEG_STATUS_CUDA_ERROR;

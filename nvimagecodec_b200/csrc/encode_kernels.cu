@@ -16,21 +16,9 @@
 #include <cuda_runtime.h>
 #include "enc_math.cuh"
 #include "encode_kernels.h"
+#include "cta_lookup.cuh"
 
 namespace b200jpeg {
-
-__device__ __forceinline__ int enc_find_image(const uint32_t* __restrict__ map, int n, uint32_t v)
-{
-    int lo = 0, hi = n - 1;
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (map[mid] <= v)
-            lo = mid;
-        else
-            hi = mid - 1;
-    }
-    return lo;
-}
 
 // ------------------------------------------------------------------------------------------------------------------
 // E1a: colour conversion + downsampling -> component planes padded to whole MCUs
@@ -164,7 +152,7 @@ __device__ __forceinline__ void enc_color_unit(const EncBatchDev& b, const EncIm
 __global__ void __launch_bounds__(kEncColorCta) k_enc_color(EncBatchDev b)
 {
     const uint32_t cta_abs = blockIdx.x + b.cta_base_color;
-    const int img = enc_find_image(b.cta_map_color, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_color, b.num_images, cta_abs);
     const EncImageDesc& im = b.images[img];
     const uint32_t u = (cta_abs - b.cta_map_color[img]) * kEncColorCta + threadIdx.x;
     const uint32_t units_x = uint32_t(im.plane_pitch[0]) >> 2;
@@ -190,7 +178,7 @@ __global__ void __launch_bounds__(kEncCta, 4) k_enc_fdct(EncBatchDev b)
     __shared__ uint2 s_q[2][64];
     __shared__ uint8_t s_aclen[2][256];
     const uint32_t cta_abs = blockIdx.x + b.cta_base_emit;
-    const int img = enc_find_image(b.cta_map_emit, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_emit, b.num_images, cta_abs);
     const EncImageDesc& im = b.images[img];
     {
         const EncQuantTable* q = b.quant + im.qt;
@@ -323,7 +311,7 @@ __global__ void __launch_bounds__(kEncCta) k_enc_bits(EncBatchDev b)
 {
     __shared__ uint32_t s_warp[kEncCta / 32];
     const uint32_t cta_abs = blockIdx.x + b.cta_base_emit;
-    const int img = enc_find_image(b.cta_map_emit, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_emit, b.num_images, cta_abs);
     const EncImageDesc& im = b.images[img];
     const uint32_t blk = (cta_abs - b.cta_map_emit[img]) * kEncCta + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -503,7 +491,7 @@ __global__ void __launch_bounds__(kEncCta) k_enc_emit(EncBatchDev b)
     __shared__ uint32_t s_ac[2][256];
     __shared__ uint32_t s_dc[2][16];
     const uint32_t cta_abs = blockIdx.x + b.cta_base_emit;
-    const int img = enc_find_image(b.cta_map_emit, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_emit, b.num_images, cta_abs);
     const EncImageDesc& im = b.images[img];
     const EncImageDyn& dy = b.dyn[img];
     const uint32_t cta = cta_abs - b.cta_map_emit[img];
@@ -564,7 +552,7 @@ __global__ void k_enc_zero_edges(EncBatchDev b, uint32_t total_ctas)
     if (blockIdx.x * blockDim.x + threadIdx.x >= total_ctas)
         return;
     const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x + b.cta_base_emit;
-    const int img = enc_find_image(b.cta_map_emit, b.num_images, c);
+    const int img = find_image_scalar(b.cta_map_emit, b.num_images, c); // one CTA per thread here
     const EncImageDesc& im = b.images[img];
     const EncImageDyn& dy = b.dyn[img];
     const uint32_t blk0 = (c - b.cta_map_emit[img]) * kEncCta;
@@ -608,7 +596,7 @@ __device__ __forceinline__ uint32_t enc_count_ff(const uint4& v)
 
 __global__ void __launch_bounds__(kEncStuffThreads) k_enc_stuff_count(EncBatchDev b)
 {
-    const int img = enc_find_image(b.cta_map_stuff, b.num_images, blockIdx.x);
+    const int img = find_image_warp(b.cta_map_stuff, b.num_images, blockIdx.x);
     const EncImageDesc& im = b.images[img];
     const EncImageDyn& dy = b.dyn[img];
     const uint32_t chunk = blockIdx.x - dy.chunk_first;
@@ -675,7 +663,7 @@ __global__ void __launch_bounds__(32) k_enc_stuff_scan(EncBatchDev b)
 
 __global__ void __launch_bounds__(kEncStuffThreads) k_enc_stuff_write(EncBatchDev b)
 {
-    const int img = enc_find_image(b.cta_map_stuff, b.num_images, blockIdx.x);
+    const int img = find_image_warp(b.cta_map_stuff, b.num_images, blockIdx.x);
     const EncImageDesc& im = b.images[img];
     const EncImageDyn& dy = b.dyn[img];
     const uint32_t chunk = blockIdx.x - dy.chunk_first;

@@ -18,21 +18,9 @@
 #include "huffman.cuh"
 
 namespace cg = cooperative_groups;
+#include "cta_lookup.cuh"
 
 namespace b200jpeg {
-
-__device__ __forceinline__ int find_image_h(const uint32_t* __restrict__ map, int n, uint32_t cta)
-{
-    int lo = 0, hi = n - 1;
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (map[mid] <= cta)
-            lo = mid;
-        else
-            hi = mid - 1;
-    }
-    return lo;
-}
 
 struct HuffSmem
 {
@@ -130,7 +118,7 @@ extern __shared__ __align__(16) unsigned char g_dyn_smem[];
 __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
 {
     const uint32_t cta_abs = blockIdx.x + b.base_subseq;
-    const int img = find_image_h(b.cta_map_subseq, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_subseq, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     const HuffSmem sm = carve_smem(b, g_dyn_smem, 8);
     const uint32_t k0 = (cta_abs - b.cta_map_subseq[img]) * kSubseqCta;
@@ -180,10 +168,79 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
 // These rounds are latency bound (a chain of n unsynchronised subsequences takes n rounds, each as long as one thread
 // needs for one subsequence), so everything the decode loop touches is staged in shared memory first: the whole LUT pool
 // (when it has at most lut_slots tables), and per thread its image's table selectors and its subsequence's words.
-__global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b)
+// One Jacobi round over work list r & 1; returns false when the list was empty (nothing left to do).
+__device__ __forceinline__ bool tail_round(const BatchDev& b, const HuffSmem& sm, bool pool_staged, int r, uint32_t tid, uint32_t nthreads,
+    uint32_t& redone)
 {
-    cg::grid_group grid = cg::this_grid();
-    const HuffSmem sm = carve_smem(b, g_dyn_smem, kSubseqCta * 8);
+    const uint32_t S = uint32_t(b.subseq_bits), spw = S >> 5, W = uint32_t(b.stream_words);
+    TabSel* my_tabsel = sm.tabsel + threadIdx.x * 8;
+    uint32_t* my_words = sm.stream + threadIdx.x * W;
+    const uint32_t n = __ldcg(&b.sync->count[r % 3]);
+    if (n == 0)
+        return false;
+    if (tid == 0)
+        b.sync->count[(r + 2) % 3] = 0;
+    const uint32_t* in = b.worklist[r & 1];
+    uint32_t* out = b.worklist[(r + 1) & 1];
+    for (uint32_t i = tid; i < n; i += nthreads) {
+        const uint32_t t = __ldcg(in + i);
+        const int img = int(__ldg(b.subseq_cta_img + t / kSubseqCta)) - b.image_base;
+        const ImageDesc& im = b.images[img];
+        const uint32_t k = t - im.subseq_first;
+        const unsigned long long E = __ldcg(b.sub_exit + t - 1); // written by other SMs in earlier rounds: bypass L1
+        if (E == __ldcg(b.sub_entry + t))
+            continue;
+        const uint32_t clean_len = b.states[img].clean_len;
+        const uint32_t* gwords = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
+        const uint16_t* lut = reinterpret_cast<const uint16_t*>(b.huff);
+        const TabSel* tabsel = im.tabsel_g;
+        if (pool_staged) { // selectors relative to the staged pool: table i sits at i * kLutEntries
+            for (int j = 0; j < im.bpm; ++j) {
+                const TabSel g = im.tabsel_g[j];
+                my_tabsel[j] = TabSel{g.dc_idx * kLutEntries, g.ac_idx * kLutEntries, g.dc_idx, g.ac_idx};
+            }
+            lut = sm.lut;
+            tabsel = my_tabsel;
+        }
+        bool changed;
+        if (W) {
+            // the subsequence starts on a 16-byte boundary of the image's stream (which is readable 16 bytes past its
+            // end): fetch it with independent 16-byte loads first, then byte-swap into the thread's staging words
+            const uint32_t first = k * spw;
+            const uint4* src = reinterpret_cast<const uint4*>(gwords + first);
+            constexpr int kMaxVec = 17; // (256 B / 4 + 3 | 1) words
+            uint4 v[kMaxVec];
+            const int nvec = int(W + 3u) >> 2;
+            const int avail = int((((im.raw_len + 16u) >> 2) - first + 3u) >> 2); // 16-byte groups inside the stream buffer
+#pragma unroll
+            for (int j = 0; j < kMaxVec; ++j)
+                if (j < nvec)
+                    v[j] = j < avail ? __ldcg(src + j) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int j = 0; j < kMaxVec; ++j)
+                if (j < nvec) {
+                    const uint32_t w4[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (uint32_t(4 * j + q) < W)
+                            my_words[4 * j + q] = __byte_perm(w4[q], 0, 0x0123);
+                }
+            const HuffEnv env = make_env(b, im, clean_len, my_words - first, lut, tabsel,
+                uint32_t(__cvta_generic_to_shared(my_words)) - first * 4u);
+            changed = sync_decode<true, true>(b, env, t, k, E, false);
+        } else {
+            const HuffEnv env = make_env(b, im, clean_len, gwords, lut, tabsel);
+            changed = sync_decode<false>(b, env, t, k, E, false);
+        }
+        ++redone;
+        if (changed && uint64_t(k + 1) * S < uint64_t(clean_len) * 8u)
+            out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
+    }
+    return true;
+}
+
+__device__ __forceinline__ bool tail_stage_pool(const BatchDev& b, const HuffSmem& sm)
+{
     const bool pool_staged = b.num_tables <= b.lut_slots;
     if (pool_staged) {
         for (int s = 0; s < b.num_tables; ++s)
@@ -191,80 +248,45 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b)
                 reinterpret_cast<uint4*>(sm.lut + s * kLutEntries)[i] = reinterpret_cast<const uint4*>(b.huff[s].lut)[i];
     }
     __syncthreads();
+    return pool_staged;
+}
+
+__global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b, int first_round)
+{
+    cg::grid_group grid = cg::this_grid();
+    if (__ldcg(&b.sync->count[first_round % 3]) == 0) // every thread reads the same value: nothing left, no barrier needed
+        return;
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kSubseqCta * 8);
+    const bool pool_staged = tail_stage_pool(b, sm);
     const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t S = uint32_t(b.subseq_bits), spw = S >> 5, W = uint32_t(b.stream_words);
-    TabSel* my_tabsel = sm.tabsel + threadIdx.x * 8;
-    uint32_t* my_words = sm.stream + threadIdx.x * W;
     uint32_t redone = 0;
-    int r = 0;
+    int r = first_round;
     for (; r < kMaxTailRounds; ++r) {
-        const uint32_t n = __ldcg(&b.sync->count[r % 3]);
-        if (n == 0)
+        if (!tail_round(b, sm, pool_staged, r, tid, nthreads, redone))
             break;
-        if (tid == 0)
-            b.sync->count[(r + 2) % 3] = 0;
-        const uint32_t* in = b.worklist[r & 1];
-        uint32_t* out = b.worklist[(r + 1) & 1];
-        for (uint32_t i = tid; i < n; i += nthreads) {
-            const uint32_t t = __ldcg(in + i);
-            const int img = int(__ldg(b.subseq_cta_img + t / kSubseqCta)) - b.image_base;
-            const ImageDesc& im = b.images[img];
-            const uint32_t k = t - im.subseq_first;
-            const unsigned long long E = __ldcg(b.sub_exit + t - 1); // written by other SMs in earlier rounds: bypass L1
-            if (E == __ldcg(b.sub_entry + t))
-                continue;
-            const uint32_t clean_len = b.states[img].clean_len;
-            const uint32_t* gwords = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
-            const uint16_t* lut = reinterpret_cast<const uint16_t*>(b.huff);
-            const TabSel* tabsel = im.tabsel_g;
-            if (pool_staged) { // selectors relative to the staged pool: table i sits at i * kLutEntries
-                for (int j = 0; j < im.bpm; ++j) {
-                    const TabSel g = im.tabsel_g[j];
-                    my_tabsel[j] = TabSel{g.dc_idx * kLutEntries, g.ac_idx * kLutEntries, g.dc_idx, g.ac_idx};
-                }
-                lut = sm.lut;
-                tabsel = my_tabsel;
-            }
-            bool changed;
-            if (W) {
-                // the subsequence starts on a 16-byte boundary of the image's stream (which is readable 16 bytes past its
-                // end): fetch it with independent 16-byte loads first, then byte-swap into the thread's staging words
-                const uint32_t first = k * spw;
-                const uint4* src = reinterpret_cast<const uint4*>(gwords + first);
-                constexpr int kMaxVec = 17; // (256 B / 4 + 3 | 1) words
-                uint4 v[kMaxVec];
-                const int nvec = int(W + 3u) >> 2;
-                const int avail = int((((im.raw_len + 16u) >> 2) - first + 3u) >> 2); // 16-byte groups inside the stream buffer
-#pragma unroll
-                for (int j = 0; j < kMaxVec; ++j)
-                    if (j < nvec)
-                        v[j] = j < avail ? __ldcg(src + j) : make_uint4(0, 0, 0, 0);
-#pragma unroll
-                for (int j = 0; j < kMaxVec; ++j)
-                    if (j < nvec) {
-                        const uint32_t w4[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
-#pragma unroll
-                        for (int q = 0; q < 4; ++q)
-                            if (uint32_t(4 * j + q) < W)
-                                my_words[4 * j + q] = __byte_perm(w4[q], 0, 0x0123);
-                    }
-                const HuffEnv env = make_env(b, im, clean_len, my_words - first, lut, tabsel,
-                    uint32_t(__cvta_generic_to_shared(my_words)) - first * 4u);
-                changed = sync_decode<true, true>(b, env, t, k, E, false);
-            } else {
-                const HuffEnv env = make_env(b, im, clean_len, gwords, lut, tabsel);
-                changed = sync_decode<false>(b, env, t, k, E, false);
-            }
-            ++redone;
-            if (changed && uint64_t(k + 1) * S < uint64_t(clean_len) * 8u)
-                out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
-        }
         grid.sync();
     }
     if (redone)
         atomicAdd(&b.sync->redone, redone);
     if (tid == 0)
         b.sync->rounds = uint32_t(r);
+}
+
+// The same round as an ordinary launch (option tail_launches): no co-residency requirement, so the round's few CTAs
+// interleave freely with the other groups' kernels; the kernel boundary is the barrier between rounds.
+__global__ void __launch_bounds__(kSubseqCta) k_huff_tail_round(BatchDev b, int r)
+{
+    if (__ldcg(&b.sync->count[r % 3]) == 0)
+        return;
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kSubseqCta * 8);
+    const bool pool_staged = tail_stage_pool(b, sm);
+    const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t redone = 0;
+    tail_round(b, sm, pool_staged, r, tid, nthreads, redone);
+    if (redone)
+        atomicAdd(&b.sync->redone, redone);
+    if (tid == 0)
+        b.sync->rounds = uint32_t(r + 1);
 }
 
 // segmented-scan combine: a = earlier prefix, x = later element; bit31 = "absolute" flag
@@ -338,7 +360,7 @@ __global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
 __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
 {
     const uint32_t cta_abs = blockIdx.x + b.base_subseq;
-    const int img = find_image_h(b.cta_map_subseq, b.num_images, cta_abs);
+    const int img = find_image_warp(b.cta_map_subseq, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     const HuffSmem sm = carve_smem(b, g_dyn_smem, 8);
     const uint32_t cta = cta_abs - b.cta_map_subseq[img];
@@ -408,7 +430,8 @@ int huff_configure(const BatchDev& b, int device, int* tail_grid)
     const size_t ms = main_smem_bytes(b), ts = tail_smem_bytes(b);
     if (cudaFuncSetAttribute(k_huff_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ms)) != cudaSuccess ||
         cudaFuncSetAttribute(k_huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ms)) != cudaSuccess ||
-        cudaFuncSetAttribute(k_huff_sync_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ts)) != cudaSuccess)
+        cudaFuncSetAttribute(k_huff_sync_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ts)) != cudaSuccess ||
+        cudaFuncSetAttribute(k_huff_tail_round, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ts)) != cudaSuccess)
         return -1;
     int per_sm = 0, sms = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_huff_sync_tail, kSubseqCta, ts) != cudaSuccess || per_sm < 1)
@@ -427,14 +450,17 @@ int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
     return 2;
 }
 
-int launch_huff_tail(const BatchDev& b, const LaunchDims&, cudaStream_t st, int tail_grid)
+int launch_huff_tail(const BatchDev& b, const LaunchDims&, cudaStream_t st, int tail_grid, int plain_rounds)
 {
+    for (int r = 0; r < plain_rounds; ++r)
+        k_huff_tail_round<<<tail_grid, kSubseqCta, tail_smem_bytes(b), st>>>(b, r);
     BatchDev bb = b;
-    void* args[] = {&bb};
+    int first_round = plain_rounds;
+    void* args[] = {&bb, &first_round};
     if (cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_huff_sync_tail), dim3(tail_grid), dim3(kSubseqCta), args, tail_smem_bytes(b), st) !=
         cudaSuccess)
         return -1;
-    return 1;
+    return 1 + plain_rounds;
 }
 
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st)

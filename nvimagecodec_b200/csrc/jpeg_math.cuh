@@ -18,43 +18,68 @@ namespace b200jpeg {
 
 // ------------------------------------------------------------------------------------------------------------------
 // Coefficient records (device_types.h kRec*) of one block -> dense natural-order coefficients.  blk[] has kRecBlkSlots
-// entries and must be zeroed (entry 64 is a dump for out-of-range indices); c = index of the block's first record,
-// total = records of the image (the reader's hard stop), zzx = kRecZigzagNext.  blk[0] stays 0: the DC travels
-// separately.  A ZRL record is handled like a coefficient of value 0.  Returns true if a coefficient landed past
-// position 63 (corrupt stream).
+// entries and must be zeroed (entry 64 is a dump for out-of-range indices).  [c, e) = the block's records: c is the index
+// the write pass stored for the block, e the index of the next block's DC padding record (or the image's record count for
+// the last block), so the range holds the block's AC records, possibly an end-of-block record, and padding -- nothing of
+// any other block.  zzx = the table fill_zigzag_next makes.  blk[0] stays 0: the DC travels separately.  A ZRL record is
+// handled like a coefficient of value 0.  Returns true if a coefficient landed past position 63 or the range is longer
+// than any block's can be (corrupt stream).
+// The records are fetched 16 bytes (eight records) at a time, two fetches ahead of their use: the trip count is known up
+// front, so nothing about a fetch depends on the records before it.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kRecBlkSlots = 72;
+constexpr uint32_t kRecMaxPerBlock = 256; // 63 coefficients + end of block + the padding of every subsequence boundary inside
 // zzx[n] = natural-order index of zigzag position n - 1 (jpeg_natural_order, ljt/jutils.c:59) for n <= 64, the dump slot after
 #define B2J_ZIGZAG_NEXT_INIT                                                                                                  \
     {0, 0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, \
-        57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63, 64, 64, 64, 64, 64,  \
-        64, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64}
-constexpr int kRecZigzagNextSize = 81;
+        57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63}
+constexpr int kRecZigzagInit = 65;      // entries of B2J_ZIGZAG_NEXT_INIT
+constexpr int kRecZigzagNextSize = 192; // a position is checked once per eight records: it can pass 64 by 8 * 16 - 1
 
-B2J_HD bool records_to_block(const uint16_t* rec, uint32_t c, uint32_t total, const uint8_t* zzx, int16_t* blk)
+B2J_HD uint8_t zigzag_next_entry(const uint8_t* init, int n) { return n < kRecZigzagInit ? init[n] : uint8_t(64); }
+
+B2J_HD uint4 rec_load8(const uint16_t* p) // eight records, p 16-byte aligned
 {
-    uint32_t z = 1, base = c & ~3u, skip = c & 3u;
-    bool done = false, bad = false;
-    while (!done && base < total) { // four records per 8-byte load (ranges are multiples of four records)
-        const uint2 v = *reinterpret_cast<const uint2*>(rec + base);
+#if defined(__CUDA_ARCH__)
+    return __ldg(reinterpret_cast<const uint4*>(p));
+#else
+    return *reinterpret_cast<const uint4*>(p);
+#endif
+}
+
+B2J_HD bool records_to_block(const uint16_t* rec, uint32_t c, uint32_t e, const uint8_t* zzx, int16_t* blk)
+{
+    if (c >= e)
+        return false; // a block the write pass never reached (its image is reported failed anyway)
+    bool bad = false;
+    if (e - c > kRecMaxPerBlock) {
+        e = c + kRecMaxPerBlock;
+        bad = true;
+    }
+    const uint32_t n = e - c, last = (e - 1u) & ~7u;
+    uint32_t base = c & ~7u, z = 1;
+    const uint4 zero = make_uint4(0, 0, 0, 0);
+    uint4 cur = rec_load8(rec + base);
+    uint4 nxt = base < last ? rec_load8(rec + base + 8) : zero;
+    for (;;) {
+        const uint4 ahead = base + 8u < last ? rec_load8(rec + base + 16) : zero;
+        const uint32_t d = base - c; // record i of this fetch is record d + i of the block (wraps for the ones before c)
+        const uint32_t w[4] = {cur.x, cur.y, cur.z, cur.w};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t r = ((i < 2 ? v.x : v.y) >> (16 * (i & 1))) & 0xFFFFu;
-            if (!done && uint32_t(i) >= skip) {
-                if ((r & 0xF7FFu) == 0) { // kRecEnd or kRecPad
-                    done = r == kRecEnd;
-                } else {
-                    z += (r >> 12) + 1u;               // position after this coefficient, <= 63 + 16
-                    bad = bad || z > 64u;
-                    blk[zzx[z]] = int16_t(int(r << 20) >> 20);
-                    done = z >= 64u;
-                }
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t r = (w[i >> 1] >> (16 * (i & 1))) & 0xFFFFu;
+            if (d + uint32_t(i) < n && (r & 0xF7FFu) != 0) { // neither kRecEnd nor kRecPad
+                z += (r >> 12) + 1u;                         // position after this coefficient
+                blk[zzx[z]] = int16_t(int(r << 20) >> 20);
             }
         }
-        skip = 0;
-        base += 4;
+        if (base == last || z >= 64u)
+            break;
+        cur = nxt;
+        nxt = ahead;
+        base += 8;
     }
-    return bad;
+    return bad || z > 64u;
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -150,6 +175,7 @@ struct IdctBlockRef
     uint32_t src_blk;  // block index in MCU scan order (relative to the image)
     uint64_t dst;      // byte offset of the block's top-left sample in the planes buffer
     int pitch;
+    int bx, by;        // block coordinates inside the component plane
 };
 
 B2J_HD IdctBlockRef idct_locate(const ImageDesc& im, uint32_t u)
@@ -159,6 +185,7 @@ B2J_HD IdctBlockRef idct_locate(const ImageDesc& im, uint32_t u)
     r.src_blk = 0;
     r.dst = 0;
     r.pitch = 0;
+    r.bx = r.by = 0;
     int c = 0;
     uint32_t rem = u;
     for (; c < im.ncomp_out; ++c) {
@@ -169,10 +196,13 @@ B2J_HD IdctBlockRef idct_locate(const ImageDesc& im, uint32_t u)
     }
     if (c >= im.ncomp_out)
         return r;
-    const int bx = int(rem % uint32_t(im.wib[c])), by = int(rem / uint32_t(im.wib[c]));
-    const int mcu = (by / im.vs[c]) * im.mcus_x + (bx / im.hs[c]);
-    const int j = im.blk_first[c] + (by % im.vs[c]) * im.hs[c] + (bx % im.hs[c]);
+    const int by = int(rem / uint32_t(im.wib[c])), bx = int(rem - uint32_t(by) * uint32_t(im.wib[c]));
+    const int hs = im.hs[c], vs = im.vs[c], lh = hs >> 1, lv = vs >> 1; // sampling factors are 1, 2 or 4: log2 = f >> 1
+    const int mcu = (by >> lv) * im.mcus_x + (bx >> lh);
+    const int j = im.blk_first[c] + ((by & (vs - 1)) << lh) + (bx & (hs - 1));
     r.comp = c;
+    r.bx = bx;
+    r.by = by;
     r.src_blk = uint32_t(mcu) * uint32_t(im.bpm) + uint32_t(j);
     r.pitch = im.plane_pitch[c];
     r.dst = im.plane_off[c] + uint64_t(by) * 8 * uint64_t(r.pitch) + uint64_t(bx) * 8;

@@ -297,11 +297,16 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             states[i].error |= err;
         }
         // dense coefficients (what the IDCT kernel rebuilds in shared memory; also the debug tap)
-        static const uint8_t zzx[kRecZigzagNextSize] = B2J_ZIGZAG_NEXT_INIT;
+        static const uint8_t zz_init[kRecZigzagInit] = B2J_ZIGZAG_NEXT_INIT;
+        uint8_t zzx[kRecZigzagNextSize];
+        for (int n = 0; n < kRecZigzagNextSize; ++n) zzx[n] = zigzag_next_entry(zz_init, n);
+        const uint32_t rec_total = std::min(states[i].rec_total, im.rec_cap);
         if (states[i].done_blocks == im.total_blocks)
             for (uint32_t bb = 0; bb < im.total_blocks; ++bb) {
                 int16_t blk[kRecBlkSlots] = {};
-                if (records_to_block(records.data() + im.rec_off, blkrec[im.coef_off / 64 + bb], states[i].rec_total, zzx, blk)) {
+                const uint32_t c = blkrec[im.coef_off / 64 + bb];
+                const uint32_t e = bb + 1 < im.total_blocks ? blkrec[im.coef_off / 64 + bb + 1] - 1u : rec_total;
+                if (records_to_block(records.data() + im.rec_off, std::min(c, rec_total), std::min(e, rec_total), zzx, blk)) {
                     if (std::getenv("EMU_DEBUG") && !(states[i].error & kErrBadCode)) std::fprintf(stderr, "emu: records_to_block bad at block %u first rec %u\n", bb, blkrec[im.coef_off / 64 + bb]);
                     states[i].error |= kErrBadCode;
                 }
