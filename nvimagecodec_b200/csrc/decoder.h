@@ -47,6 +47,7 @@ struct HostOutput // an output the caller wants in host memory
     void* host = nullptr;
     int64_t host_stride = 0;
     size_t dev_off = 0;
+    size_t dev_pitch = 0; // row pitch of the device-side copy: the host's own layout when its rows are tight
     size_t row_bytes = 0;
     size_t rows = 0;
 };
