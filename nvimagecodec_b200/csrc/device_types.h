@@ -14,7 +14,11 @@ constexpr int kLutBits = 11;          // first-level Huffman lookup width
 constexpr int kLutSize = 1 << kLutBits;
 constexpr int kLut2Size = 512;        // second-level entries (codes longer than kLutBits)
 constexpr int kLutEntries = kLutSize + kLut2Size;
-constexpr int kSubseqCta = 256;       // threads per CTA in the subsequence kernels (one subsequence per thread)
+#ifndef B2J_SUBSEQ_CTA
+#define B2J_SUBSEQ_CTA 256
+#endif
+constexpr int kSubseqCta = B2J_SUBSEQ_CTA; // threads per CTA in the subsequence kernels (one subsequence per thread)
+constexpr int kTailCta = 256;         // threads per CTA of the work-list rounds (any subsequence, any thread)
 constexpr int kUnstuffThreads = 256;  // threads per CTA in the unstuffing kernels
 constexpr int kUnstuffBytesPerThread = 16;
 constexpr int kChunkBytes = kUnstuffThreads * kUnstuffBytesPerThread; // raw bytes per unstuff CTA

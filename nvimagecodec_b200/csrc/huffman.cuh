@@ -140,8 +140,13 @@ struct RecOut
         qlo = (qlo >> 16) | (qhi << 16);
         qhi = (qhi >> 16) | (r << 16);
         ++cursor;
-        if ((cursor & (kRecAlign - 1u)) == 0 && cursor <= limit)
+        if ((cursor & (kRecAlign - 1u)) == 0 && cursor <= limit) {
+#if defined(__CUDA_ARCH__)
+            asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(rec + cursor - kRecAlign), "r"(qlo), "r"(qhi) : "memory");
+#else
             *reinterpret_cast<uint2*>(rec + cursor - kRecAlign) = make_uint2(qlo, qhi);
+#endif
+        }
     }
     B2J_HD void finish() // fill the range with padding records
     {
@@ -152,14 +157,25 @@ struct RecOut
 
 // value bits -> coefficient (HUFF_EXTEND, ljt/jdhuff.c:483-488) and the record of the symbol, without branches.
 // t = stream window shifted so that the first value bit is bit 31; sz = number of value bits; zadv from the table entry.
-B2J_HD uint32_t make_record(uint32_t t, uint32_t sz, uint32_t zadv, bool is_ac, int& val)
+// A first value bit of 1 means a positive coefficient equal to the sz bits; a 0 means minus the complement of the sz bits.
+// The record of a DC symbol is never read (a block's record range starts after it, jpeg_math.cuh records_to_block): it
+// is whatever the same formula yields.
+B2J_HD uint32_t shr_upto32(uint32_t x, uint32_t n) // x >> n for n in [0, 32]
 {
-    const uint32_t bits = sz ? t >> (32u - sz) : 0u;
-    const int neg = ~(int(t) >> 31); // all ones when the first value bit is 0: a negative coefficient
-    val = int(bits) + (neg & (1 - (1 << sz)));
-    uint32_t r = (((zadv - 1u) << 12) | (uint32_t(val) & 0xFFFu)) & 0xFFFFu; // ZRL (sz 0, zadv 16) comes out as kRecZrl
-    r = zadv == 64u ? kRecEnd : r;
-    return is_ac ? r : kRecPad;
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_rc(x, 0u, n);
+#else
+    return n >= 32u ? 0u : x >> n;
+#endif
+}
+
+B2J_HD uint32_t make_record(uint32_t t, uint32_t sz, uint32_t zadv, int& val)
+{
+    const uint32_t pos = uint32_t(int(t) >> 31);           // all ones for a positive coefficient
+    const uint32_t mag = shr_upto32(t ^ ~pos, 32u - sz);   // magnitude; 0 when there are no value bits
+    val = int((mag ^ ~pos) + pos + 1u);                    // (mag ^ m) - m with m = ~pos: mag or -mag
+    const uint32_t r = (((zadv - 1u) << 12) | (uint32_t(val) & 0xFFFu)) & 0xFFFFu; // ZRL (sz 0, zadv 16) comes out as kRecZrl
+    return zadv == 64u ? kRecEnd : r;
 }
 
 // Decode every symbol that starts in [s.p, end) (segment changes included), beginning in state s.
@@ -226,7 +242,7 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
                 if (WRITE) {
                     const uint32_t sz = (e >> 5) & 15u;
                     int val;
-                    const uint32_t r = make_record(win << (tot - sz), sz, zadv, z != 0, val);
+                    const uint32_t r = make_record(win << (tot - sz), sz, zadv, val);
                     out->push(r);
                     if (z == 0) {
                         out->dc[nblk] = int16_t(val);
@@ -275,7 +291,7 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
                 err |= kErrBadCode;
             if (WRITE) {
                 int val;
-                const uint32_t r = make_record(win << (tot - sz), sz, zadv, z != 0, val);
+                const uint32_t r = make_record(win << (tot - sz), sz, zadv, val);
                 out->push(r);
                 if (z == 0) {
                     out->dc[nblk] = int16_t(val);

@@ -244,19 +244,19 @@ __device__ __forceinline__ bool tail_stage_pool(const BatchDev& b, const HuffSme
     const bool pool_staged = b.num_tables <= b.lut_slots;
     if (pool_staged) {
         for (int s = 0; s < b.num_tables; ++s)
-            for (int i = threadIdx.x; i < kLutEntries / 8; i += kSubseqCta)
+            for (int i = threadIdx.x; i < kLutEntries / 8; i += kTailCta)
                 reinterpret_cast<uint4*>(sm.lut + s * kLutEntries)[i] = reinterpret_cast<const uint4*>(b.huff[s].lut)[i];
     }
     __syncthreads();
     return pool_staged;
 }
 
-__global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b, int first_round)
+__global__ void __launch_bounds__(kTailCta) k_huff_sync_tail(BatchDev b, int first_round)
 {
     cg::grid_group grid = cg::this_grid();
     if (__ldcg(&b.sync->count[first_round % 3]) == 0) // every thread reads the same value: nothing left, no barrier needed
         return;
-    const HuffSmem sm = carve_smem(b, g_dyn_smem, kSubseqCta * 8);
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kTailCta * 8);
     const bool pool_staged = tail_stage_pool(b, sm);
     const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t redone = 0;
@@ -274,11 +274,11 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync_tail(BatchDev b, int f
 
 // The same round as an ordinary launch (option tail_launches): no co-residency requirement, so the round's few CTAs
 // interleave freely with the other groups' kernels; the kernel boundary is the barrier between rounds.
-__global__ void __launch_bounds__(kSubseqCta) k_huff_tail_round(BatchDev b, int r)
+__global__ void __launch_bounds__(kTailCta) k_huff_tail_round(BatchDev b, int r)
 {
     if (__ldcg(&b.sync->count[r % 3]) == 0)
         return;
-    const HuffSmem sm = carve_smem(b, g_dyn_smem, kSubseqCta * 8);
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kTailCta * 8);
     const bool pool_staged = tail_stage_pool(b, sm);
     const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t redone = 0;
@@ -391,7 +391,13 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
     s.abs = true;
     s.nrec = 0;
     RecOut out;
-    out.rec = b.rec + im.rec_off;
+    {
+        // the record pointer as an opaque register pair: one wide multiply-add forms a store address from the cursor
+        // (left to itself the compiler re-derives the pointer from the descriptor at every store)
+        unsigned long long rp = reinterpret_cast<unsigned long long>(b.rec + im.rec_off);
+        asm volatile("mov.u64 %0, %0;" : "+l"(rp));
+        out.rec = reinterpret_cast<uint16_t*>(rp);
+    }
     out.blk_rec = b.blk_rec + im.coef_off / 64;
     out.dc = b.dc + im.coef_off / 64;
     out.cursor = b.sub_rec_off[t];
@@ -422,7 +428,7 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
 static size_t main_smem_bytes(const BatchDev& b) { return size_t(b.lut_slots) * kLutEntries * 2 + 8 * sizeof(TabSel) + size_t(kSubseqCta) * b.stream_words * 4; }
 static size_t tail_smem_bytes(const BatchDev& b)
 {
-    return size_t(b.lut_slots) * kLutEntries * 2 + size_t(kSubseqCta) * 8 * sizeof(TabSel) + size_t(kSubseqCta) * b.stream_words * 4;
+    return size_t(b.lut_slots) * kLutEntries * 2 + size_t(kTailCta) * 8 * sizeof(TabSel) + size_t(kTailCta) * b.stream_words * 4;
 }
 
 int huff_configure(const BatchDev& b, int device, int* tail_grid)
@@ -434,7 +440,7 @@ int huff_configure(const BatchDev& b, int device, int* tail_grid)
         cudaFuncSetAttribute(k_huff_tail_round, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ts)) != cudaSuccess)
         return -1;
     int per_sm = 0, sms = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_huff_sync_tail, kSubseqCta, ts) != cudaSuccess || per_sm < 1)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_huff_sync_tail, kTailCta, ts) != cudaSuccess || per_sm < 1)
         return -1;
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms < 1)
         return -1;
@@ -453,11 +459,11 @@ int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
 int launch_huff_tail(const BatchDev& b, const LaunchDims&, cudaStream_t st, int tail_grid, int plain_rounds)
 {
     for (int r = 0; r < plain_rounds; ++r)
-        k_huff_tail_round<<<tail_grid, kSubseqCta, tail_smem_bytes(b), st>>>(b, r);
+        k_huff_tail_round<<<tail_grid, kTailCta, tail_smem_bytes(b), st>>>(b, r);
     BatchDev bb = b;
     int first_round = plain_rounds;
     void* args[] = {&bb, &first_round};
-    if (cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_huff_sync_tail), dim3(tail_grid), dim3(kSubseqCta), args, tail_smem_bytes(b), st) !=
+    if (cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_huff_sync_tail), dim3(tail_grid), dim3(kTailCta), args, tail_smem_bytes(b), st) !=
         cudaSuccess)
         return -1;
     return 1 + plain_rounds;
