@@ -134,3 +134,23 @@ def test_emulated_extended_sequential_sof1():
     assert st == [ref.STATUS_SUCCESS]
     outs, st, _, _ = emu.decode_batch([d], [(211, 133)], 4, 1, 128)
     assert st == [0] and np.array_equal(outs[0], want[0])
+
+
+def test_emulated_randomized_batch():
+    """random sizes (1..160 log-uniform), samplings, qualities, restart intervals and content through the emulated pipeline
+    in one batch, twice (interleaved RGB with fancy upsampling, planar RGB without): bit-exact against the port"""
+    rng = np.random.default_rng(99)
+    specs = []
+    for _ in range(24):
+        gray = rng.random() < 0.15
+        specs.append(dict(w=int(round(2 ** rng.uniform(0, np.log2(160)))), h=int(round(2 ** rng.uniform(0, np.log2(160)))),
+                          samp=(1, 1) if gray else [(1, 1), (2, 1), (1, 2), (2, 2), (4, 1)][int(rng.integers(0, 5))],
+                          quality=int(rng.integers(25, 101)), restart_interval=int(rng.choice([0, 0, 1, 3, 17])), gray=gray,
+                          kind=["photo", "noise", "flat"][int(rng.integers(0, 3))]))
+    datas = [make_jpeg(7000 + i, **s) for i, s in enumerate(specs)]
+    dims = [(s["w"], s["h"]) for s in specs]
+    for fmt, pfmt, fancy in ((4, port.FMT_I_RGB, 1), (3, port.FMT_P_RGB, 0)):
+        outs, st, rounds, _ = emu.decode_batch(datas, dims, fmt, fancy, 64)
+        assert st == [0] * len(datas), [(i, specs[i]) for i, x in enumerate(st) if x]
+        for i, (d, o) in enumerate(zip(datas, outs)):
+            assert np.array_equal(o, port.decode(d, pfmt, fancy)), (i, specs[i], fmt)

@@ -338,3 +338,54 @@ def test_damaged_streams_are_contained(torch_mod, refdec):
         for o in outs:
             assert not o[h:].any(), "wrote past the image"
     dec.close()
+
+
+def _random_specs(rng, n, max_side):
+    specs = []
+    for _ in range(n):
+        w = int(round(2 ** rng.uniform(0, np.log2(max_side))))
+        h = int(round(2 ** rng.uniform(0, np.log2(max_side))))
+        gray = rng.random() < 0.15
+        samp = [(1, 1), (2, 1), (1, 2), (2, 2), (4, 1)][int(rng.integers(0, 5))]
+        ri = int(rng.choice([0, 0, 0, 1, 2, 5, 11, 64]))
+        specs.append(dict(w=w, h=h, samp=(1, 1) if gray else samp, quality=int(rng.integers(25, 101)), restart_interval=ri, gray=gray,
+                          kind=["photo", "photo", "noise", "flat"][int(rng.integers(0, 4))]))
+    return specs
+
+
+@pytest.mark.parametrize("fancy", [1, 0])
+def test_randomized_batches_bit_exact(torch_mod, refdec, fancy):
+    """Three batches of 64 random images (sizes 1..700 log-uniform, every supported sampling, qualities 25..100, restart
+    intervals, photo / noise / flat content, a random output format and row slack per image) through ONE decoder object,
+    so that every buffer is reused with different contents: every image bit-exact against the reference decoder."""
+    from nvimagecodec_b200.decoder import Decoder
+    torch = torch_mod
+    rng = np.random.default_rng(77 + fancy)
+    dec = Decoder(0, options=":fancy_upsampling=%d" % fancy)
+    for batch in range(3):
+        specs = _random_specs(rng, 64, 700)
+        datas = [make_jpeg(5000 + 100 * batch + i, **s) for i, s in enumerate(specs)]
+        fmts, outs, ptrs, strides = [], [], [], []
+        for s in specs:
+            f = int(rng.choice([7, 4, 6])) if s["gray"] else int(rng.choice([4, 6, 3, 5, 7]))
+            pad = int(rng.choice([0, 0, 1, 13, 64]))
+            row = s["w"] * (3 if f in (4, 6) else 1) + pad
+            rows = s["h"] * (1 if f in (4, 6, 7) else 3)
+            t = torch.full((rows, row), 0xA5, dtype=torch.uint8, device="cuda")
+            fmts.append(f)
+            outs.append(t)
+            ptrs.append(t.data_ptr())
+            strides.append(row)
+        st = dec.decode_into(datas, ptrs, strides, fmts)
+        torch.cuda.synchronize()
+        assert all(x == 0 for x in st), (batch, [(i, specs[i]) for i, x in enumerate(st) if x])
+        want, rst, _ = refdec[fancy].decode_host(datas, fmt=[FMT_REF[f] for f in fmts])
+        assert all(x == ref.STATUS_SUCCESS for x in rst)
+        for i, s in enumerate(specs):
+            a = outs[i].cpu().numpy()
+            f, w, h = fmts[i], s["w"], s["h"]
+            used = w * (3 if f in (4, 6) else 1)
+            got = a[:, :used].reshape(h, w, 3) if f in (4, 6) else a[:, :used].reshape(1 if f == 7 else 3, h, w)
+            assert np.array_equal(got, want[i]), "batch %d image %d %s fmt %d differs from the reference decoder" % (batch, i, s, f)
+            assert (a[:, used:] == 0xA5).all(), "batch %d image %d %s fmt %d: wrote into the row slack" % (batch, i, s, f)
+    dec.close()
