@@ -92,3 +92,24 @@ def test_encode_rejects_out_of_scope(enc):
                                    subsampling=_capi.CSS_420, quality=90, restart_interval=0)], [100000, 100000, 64])
     assert st[0] == 3 and st[1] == 1 and st[2] == 8  # UNSUPPORTED, INVALID_PARAMETER, BUFFER_TOO_SMALL
     assert out == [None, None, None]
+
+
+def test_encode_randomized_batches(enc):
+    """eight calls on one encoder object (buffers reused with different shapes): 40 random images each (sides 1..600
+    log-uniform, photo / noise / flat, a few gray), random quality, sampling and restart interval per call; every file
+    byte-exact against libjpeg-turbo"""
+    import torch
+    from nvimagecodec_b200.encoder import EncodeParams
+    rng = np.random.default_rng(4242)
+    for call in range(8):
+        samp = list(CSS)[int(rng.integers(0, 4))]
+        q, ri = int(rng.integers(1, 101)), int(rng.choice([0, 0, 1, 4, 37]))
+        gray = call % 4 == 3
+        imgs = []
+        for i in range(40):
+            w, h = int(round(2 ** rng.uniform(0, np.log2(600)))), int(round(2 ** rng.uniform(0, np.log2(600))))
+            imgs.append(synth_image(9000 + 100 * call + i, w, h, 1 if gray else 3, ["photo", "photo", "noise", "flat"][int(rng.integers(0, 4))]))
+        p = EncodeParams(quality=q, chroma_subsampling="4:4:4" if gray else CSS[samp], restart_interval=ri)
+        got = enc.encode([torch.from_numpy(i).cuda() for i in imgs] if call % 2 else imgs, ".jpg", p)
+        for i, (im, a) in enumerate(zip(imgs, got)):
+            assert a == want(im, q, (1, 1) if gray else samp, ri), (call, i, im.shape, samp, q, ri)
