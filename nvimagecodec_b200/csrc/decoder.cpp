@@ -66,6 +66,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
                 o.subseq_bytes = v;
         } else if (name == "tail_launches") {
             o.tail_launches = std::max(0, std::min(32, std::atoi(value.c_str())));
+        } else if (name == "tail_spread") {
+            o.tail_spread = std::atoi(value.c_str()) != 0;
         } else if (name == "stream_priority") {
             o.stream_priority = std::atoi(value.c_str()) != 0;
         } else if (name == "copy_threads")
@@ -367,6 +369,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     for (const ImageDesc& im : plan_.images)
         dev_.lut_slots = std::max(dev_.lut_slots, im.ntabs);
     // stream staging in shared memory: per thread its subsequence plus the words a symbol may run over, an odd count
+    dev_.tail_mode = (opt_.tail_spread ? 1 : 0);
     dev_.stream_words = 0;
     if (opt_.stage_stream && opt_.subseq_bytes <= 256)
         dev_.stream_words = (plan_.subseq_bits / 32 + 3) | 1; // a symbol starting in the last word reads two words past it
@@ -391,7 +394,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     uint64_t weight_total = 0, weight_sum = 0;
     for (int g = 0; g < G; ++g)
         weight_total += growing ? (uint64_t(1) << g) + (g == G - 1 ? 1 : 0) : 1;
-    int per_group = std::max(1, std::min(tail_capacity_ / G, sm_count_));
+    int per_group = std::max(1, tail_capacity_ / G); // the groups' cooperative kernels together fill the device exactly
     int first = 0;
     for (int g = 0; g < G; ++g) {
         int last = first;
@@ -719,12 +722,22 @@ int Decoder::finish(int32_t* statuses)
     for (size_t g = 0; g < groups_.size(); ++g) {
         stat_rounds_ = std::max<uint64_t>(stat_rounds_, 2 + sc[g].rounds);
         stat_redone_ += sc[g].redone;
+        if (std::getenv("B200JPEG_TRACE")) {
+            std::fprintf(stderr, "b200jpeg: group %zu work-list rounds (items @ us since the kernel's start):", g);
+            for (uint32_t r = 0; r < sc[g].rounds && r < uint32_t(kTraceRounds); ++r)
+                std::fprintf(stderr, " %u@%.1f", sc[g].round_items[r], sc[g].round_ns[r] * 1e-3);
+            std::fprintf(stderr, "\n");
+        }
     }
     stat_record_bytes_ = 0;
     for (int i = 0; i < m; ++i) {
         const int bi = planned_to_batch_[i];
-        if (hs[i].error || hs[i].done_blocks != plan_.images[i].total_blocks)
+        if (hs[i].error || hs[i].done_blocks != plan_.images[i].total_blocks) {
             statuses[bi] = B200JPEG_STATUS_CORRUPT_STREAM;
+            if (std::getenv("B200JPEG_TRACE"))
+                std::fprintf(stderr, "b200jpeg: image %d: error flags 0x%x, %u of %u blocks\n", bi, hs[i].error, hs[i].done_blocks,
+                    plan_.images[i].total_blocks);
+        }
         stat_record_bytes_ += uint64_t(hs[i].rec_total) * sizeof(uint16_t);
     }
     return B200JPEG_STATUS_SUCCESS;

@@ -25,6 +25,7 @@ struct DecoderOptions
     bool stream_priority = false; // group g's stream outranks group g + 1's (measured: no gain for host outputs, and with
                                   // equal priorities the latency-bound kernels of one group hide behind the others' throughput kernels)
     int tail_launches = 0;  // work-list rounds launched as ordinary kernels before the cooperative kernel takes the rest
+    bool tail_spread = true;  // work-list items dealt lane-major: a short list leaves one decoding lane per warp
     int groups = 4;           // the batch is cut into this many groups of images that run on separate streams (pipelining)
     bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)
     bool dump_coef = false; // debug: keep dense DCT coefficients for b200jpeg_debug_fetch(what = 0)

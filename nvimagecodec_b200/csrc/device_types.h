@@ -156,12 +156,17 @@ B2J_HD unsigned long long pack_state(uint32_t p, uint32_t slot) { return (unsign
 
 constexpr int kMaxTailRounds = 512;
 
+constexpr int kTraceRounds = 16; // work-list rounds whose length and time are kept for B200JPEG_TRACE
+
+
 struct SyncCounters // device-side bookkeeping of the synchronisation rounds
 {
     uint32_t count[3];    // work-list lengths (rotating: round r reads [r % 3], appends to [(r + 1) % 3])
     uint32_t rounds;      // tail rounds executed
     uint32_t redone;      // subsequences re-decoded in tail rounds
     uint32_t pad_[3];
+    uint32_t round_items[kTraceRounds]; // diagnostics (B200JPEG_TRACE): list length of each work-list round ...
+    uint32_t round_ns[kTraceRounds];    // ... and the time from the kernel's start to the end of that round, ns
 };
 
 struct BatchDev // pointers handed to every kernel
@@ -203,6 +208,7 @@ struct BatchDev // pointers handed to every kernel
     int32_t num_tables;    // Huffman tables in the pool
     int32_t lut_slots;     // LUT slots the decoding kernels reserve in shared memory (>= every image's ntabs)
     int32_t stream_words;  // 32-bit words of staged stream per thread (odd, >= subseq_bits / 32 + 3); 0 = read the stream from global memory
+    int32_t tail_mode;     // work-list rounds: bit 0 = items dealt lane-major (few decoding lanes per warp once the list is short)
 };
 
 } // namespace b200jpeg
