@@ -24,7 +24,7 @@ struct DecoderOptions
     int copy_threads = 8; // host threads (the caller's included) that copy entropy-coded bytes into pinned staging
     bool stream_priority = false; // group g's stream outranks group g + 1's (measured: no gain for host outputs, and with
                                   // equal priorities the latency-bound kernels of one group hide behind the others' throughput kernels)
-    int tail_launches = 0;  // work-list rounds launched as ordinary kernels before the cooperative kernel takes the rest
+    int tail_launches = 1;  // work-list rounds launched as ordinary kernels (a thread per subsequence: the long first list in one pass) before the cooperative kernel takes the rest
     bool tail_spread = true;  // work-list items dealt lane-major: a short list leaves one decoding lane per warp
     int groups = 4;           // the batch is cut into this many groups of images that run on separate streams (pipelining)
     bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)

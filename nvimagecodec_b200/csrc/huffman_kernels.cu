@@ -12,6 +12,7 @@
 // owns the words [t * W, (t + 1) * W) where W = stream_words is odd, so threads at the same position of their
 // subsequence hit different banks; the last W - S/32 words of a region duplicate the start of the next one.
 // The per-thread decode loop lives in huffman.cuh (shared with the CPU emulation used by the tests).
+#include <algorithm>
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include "decode_kernels.h"
@@ -296,13 +297,16 @@ __global__ void __launch_bounds__(kTailCta) k_huff_sync_tail(BatchDev b, int fir
 
 // The same round as an ordinary launch (option tail_launches): no co-residency requirement, so the round's few CTAs
 // interleave freely with the other groups' kernels; the kernel boundary is the barrier between rounds.
+// Its grid is not bound by co-residency: it has a thread for every subsequence of the group, dealt thread-major, so a long
+// list (the first one: a quarter of all subsequences) is done in one pass of dense warps instead of two passes of the
+// cooperative grid; CTAs past the end of the list leave at once.
 __global__ void __launch_bounds__(kTailCta) k_huff_tail_round(BatchDev b, int r)
 {
-    if (__ldcg(&b.sync->count[r % 3]) == 0)
+    if (blockIdx.x * blockDim.x >= __ldcg(&b.sync->count[r % 3]))
         return;
     const HuffSmem sm = carve_smem(b, g_dyn_smem, kTailCta * 8);
     const bool pool_staged = tail_stage_pool(b, sm);
-    const uint32_t nthreads = gridDim.x * blockDim.x, tid = tail_slot(b);
+    const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t redone = 0;
     tail_round(b, sm, pool_staged, r, tid, nthreads, redone);
     if (redone)
@@ -478,10 +482,11 @@ int launch_huff_sync(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
     return 2;
 }
 
-int launch_huff_tail(const BatchDev& b, const LaunchDims&, cudaStream_t st, int tail_grid, int plain_rounds)
+int launch_huff_tail(const BatchDev& b, const LaunchDims& d, cudaStream_t st, int tail_grid, int plain_rounds)
 {
+    const int plain_grid = std::max(tail_grid, int((size_t(d.subseq_ctas) * kSubseqCta + kTailCta - 1) / kTailCta));
     for (int r = 0; r < plain_rounds; ++r)
-        k_huff_tail_round<<<tail_grid, kTailCta, tail_smem_bytes(b), st>>>(b, r);
+        k_huff_tail_round<<<plain_grid, kTailCta, tail_smem_bytes(b), st>>>(b, r);
     BatchDev bb = b;
     int first_round = plain_rounds;
     void* args[] = {&bb, &first_round};
