@@ -302,7 +302,10 @@ __global__ void __launch_bounds__(kTailCta) k_huff_sync_tail(BatchDev b, int fir
 // cooperative grid; CTAs past the end of the list leave at once.
 __global__ void __launch_bounds__(kTailCta) k_huff_tail_round(BatchDev b, int r)
 {
-    if (blockIdx.x * blockDim.x >= __ldcg(&b.sync->count[r % 3]))
+    const uint32_t n = __ldcg(&b.sync->count[r % 3]);
+    if (n == 0 && blockIdx.x == 0 && threadIdx.x == 0)
+        b.sync->count[(r + 2) % 3] = 0; // keep the rotation going: a launch after the last round must not find an old length
+    if (blockIdx.x * blockDim.x >= n)
         return;
     const HuffSmem sm = carve_smem(b, g_dyn_smem, kTailCta * 8);
     const bool pool_staged = tail_stage_pool(b, sm);

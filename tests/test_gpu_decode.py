@@ -147,7 +147,11 @@ def test_subsequence_sizes_and_rounds(torch_mod, refdec):
     datas = [make_jpeg(4000 + i, 640, 480, (2, 2), 90) for i in range(4)] + [make_jpeg(4100, 1920, 1080, (2, 2), 90)]
     want, _, _ = refdec[1].decode_host(datas)
     for opts in (":fancy_upsampling=1 :subseq_bytes=64", ":fancy_upsampling=1 :subseq_bytes=32",
-                 ":fancy_upsampling=1 :subseq_bytes=1024", "b200jpeg_decoder:subseq_bytes=512 other_plugin:subseq_bytes=32"):
+                 ":fancy_upsampling=1 :subseq_bytes=1024", "b200jpeg_decoder:subseq_bytes=512 other_plugin:subseq_bytes=32",
+                 # the work-list rounds every way they can run: all in the cooperative kernel / first ones as ordinary
+                 # launches, items dealt thread-major / lane-major, one stream / groups
+                 ":tail_launches=0 :tail_spread=0", ":tail_launches=0 :tail_spread=1 :groups=1", ":tail_launches=3 :tail_spread=1",
+                 ":tail_launches=32 :tail_spread=0 :subseq_bytes=64", ":tail_launches=1 :profile=1"):
         got, st = gpu_decode(torch_mod, datas, 4, opts)
         for i, (g, w) in enumerate(zip(got, want)):
             assert st[i] == 0 and np.array_equal(g, w), (opts, i)

@@ -18,8 +18,8 @@ tail -c 400 $out/${tag}_bench_encode.json
 if [ "${SKIP_NCU:-0}" != "1" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --skip-cpu-baseline > $out/${tag}_ncu_list.log 2>&1; echo "ncu list rc=$?"
-# one full step of the single-stream (profile) decoder after 3 warm runs: quick_bench launches 11 kernels per run
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_' --launch-skip ${NCU_SKIP:-33} --launch-count ${NCU_COUNT:-11} \
+# one full step of the single-stream (profile) decoder after 3 warm runs: quick_bench launches 12 kernels per run
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_' --launch-skip ${NCU_SKIP:-36} --launch-count ${NCU_COUNT:-12} \
     -o $out/${tag}_full python tools/quick_bench.py 64 8 > $out/${tag}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 # every encoder kernel of one warm encode call on a single stream (the profile encoder of the bench: last call of the run)
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_enc' --launch-skip ${NCU_ENC_SKIP:-390} --launch-count 10 \

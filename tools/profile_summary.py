@@ -16,7 +16,7 @@ METRICS = ("dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,sm
            "launch__registers_per_thread,launch__occupancy_limit_registers,launch__occupancy_limit_shared_mem,"
            "launch__shared_mem_per_block_dynamic,launch__shared_mem_per_block_static")
 STAGE_OF = {"k_unstuff_count": "unstuff", "k_unstuff_scan": "unstuff", "k_unstuff_write": "unstuff", "k_huff_sync": "huff_sync",
-            "k_huff_sync_tail": "huff_tail", "k_subseq_scan": "huff_write", "k_huff_write": "huff_write", "k_dc_scan": "dc_scan",
+            "k_huff_sync_tail": "huff_tail", "k_huff_tail_round": "huff_tail", "k_subseq_scan": "huff_write", "k_huff_write": "huff_write", "k_dc_scan": "dc_scan",
             "k_idct": "idct", "k_color": "color"}
 
 
