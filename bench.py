@@ -49,43 +49,81 @@ def make_corpus(n):
 
 
 class ClockSampler:
+    """SM clocks and throttle reasons of the job's GPUs during the timed region.  One sampler for the whole job (rank 0
+    passes every GPU index, the other ranks none): NVML in-process every 10 ms; eight ranks each spawning nvidia-smi --
+    which opens every GPU of the box -- inside a 30 ms timed region is a disturbance of its own.  Falls back to one
+    nvidia-smi process per sample (all GPUs in one query) when pynvml is missing."""
     FIELDS = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    BITS = [0x8, 0x40, 0x20, 0x4]  # nvmlClocksEventReason{HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap}
 
-    def __init__(self, index):
-        self.index = index
-        self.samples = []
+    def __init__(self, indices):
+        self.indices = [indices] if isinstance(indices, int) else list(indices)
+        self.samples = []  # (gpu, sm_mhz, max_mhz, [reason flags])
         self.stop = False
-        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.how = None
+        self.thread = threading.Thread(target=self._run, daemon=True) if self.indices else None
 
-    def _run(self):
+    def _run_nvml(self):
+        import pynvml
+        pynvml.nvmlInit()
+        hs = [pynvml.nvmlDeviceGetHandleByIndex(i) for i in self.indices]
+        mx = [pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM) for h in hs]
+        reasons_of = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+        self.how = "nvml"
+        while not self.stop:
+            for g, h in enumerate(hs):
+                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                r = int(reasons_of(h))
+                self.samples.append((self.indices[g], int(sm), int(mx[g]), [bool(r & b) for b in self.BITS]))
+            time.sleep(0.01)
+
+    def _run_smi(self):
+        self.how = "nvidia-smi"
         while not self.stop:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                out = subprocess.run(["nvidia-smi", "-i", ",".join(str(i) for i in self.indices), "--query-gpu=" + self.FIELDS,
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(",")]
-                if len(parts) >= 6:
-                    self.samples.append(parts)
+                for g, line in enumerate(out.strip().splitlines()):
+                    parts = [p.strip() for p in line.split(",")]
+                    if len(parts) >= 6 and parts[0].isdigit() and parts[1].isdigit() and g < len(self.indices):
+                        self.samples.append((self.indices[g], int(parts[0]), int(parts[1]),
+                                             [parts[2 + i].lower().startswith("active") for i in range(4)]))
             except Exception:
                 pass
             time.sleep(0.1)
 
+    def _run(self):
+        try:
+            self._run_nvml()
+        except Exception:
+            self._run_smi()
+
     def __enter__(self):
-        self.thread.start()
+        if self.thread:
+            self.thread.start()
+            time.sleep(0.05)  # the first sample is in before the timed region starts
         return self
 
     def __exit__(self, *a):
         self.stop = True
-        self.thread.join(timeout=6)
+        if self.thread:
+            self.thread.join(timeout=6)
 
     def summary(self):
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
-        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons}
+        per_gpu = {}
+        for g, sm, _, _ in self.samples:
+            per_gpu.setdefault(g, []).append(sm)
+        med = {g: sorted(v)[len(v) // 2] for g, v in per_gpu.items()}
+        reasons = [n for i, n in enumerate(self.NAMES) if any(s[3][i] for s in self.samples)]
+        out = {"sm_mhz": min(med.values()), "sm_max_mhz": max(s[2] for s in self.samples), "reasons": reasons,
+               "samples": len(self.samples), "how": self.how}
+        if len(med) > 1:
+            out["per_gpu_sm_mhz"] = [med[g] for g in sorted(med)]  # sm_mhz is the lowest of these medians
+        return out
 
 
 def pin_to_gpu_numa_node(index):
@@ -258,7 +296,7 @@ def run_encode(args, rank, world, local_rank):
                 assert out_host[i * cap:i * cap + sizes[i]].numpy().tobytes() == got[i]
         return dt, [v / args.steps / 1e3 for v in stage], launches, enc.stats()
 
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(range(world) if rank == 0 else []) as clocks:
         dt_dev, _, launches, es = timed(inputs(devt, False))
     dt_host, _, _, _ = timed(inputs(host, True))
     _, stage_ms, _, _ = timed(inputs(devt, False), encp)
@@ -393,7 +431,7 @@ def main():
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches = 0
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(range(world) if rank == 0 else []) as clocks:
         e0.record()
         for _ in range(args.steps):
             st = dec.run(stream)
@@ -435,7 +473,11 @@ def main():
 
     # ---- reduce over ranks (max time) ----
     t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    per_rank_ms = [ms_total / args.steps]
     if world > 1:
+        every = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(every, t)
+        per_rank_ms = [float(x[0]) / args.steps for x in every]  # the spread behind the max (reported in config)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, e2e_ms = float(t[0]), float(t[1])
     if rank != 0:
@@ -488,7 +530,7 @@ def main():
                                "fancy upsampling, per GPU" % (n, S / n / 1e3),
                    "l2": "working set per step %.0f MB (records+planes+output) > 126 MB L2, no explicit flush" %
                          ((R + 70 * blocks + out_b) / 1e6),
-                   "host_affinity": numa, "options": args.options, "sync_rounds": stats["sync_rounds"], "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"],
+                   "host_affinity": numa, "per_rank_ms_per_step": [round(x, 4) for x in per_rank_ms], "options": args.options, "sync_rounds": stats["sync_rounds"], "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"],
                    "parity": "bit-exact vs reference libjpeg_turbo_ext on all %d images before timing" % n},
         "clocks": clocks.summary(),
         "e2e": {"value": mpix_step / (e2e_ms / args.steps / 1e3), "unit": "Mpixel/s", "images_per_s": n * world / (e2e_ms / args.steps / 1e3),
