@@ -110,7 +110,11 @@ B200JPEG_API int b200jpeg_parse_header(const uint8_t* data, size_t size, b200jpe
 /* ---- decoder ----
  * options: the reference's option string, "name=value" tokens separated by spaces, optional "b200jpeg_decoder:" or ":"
  * prefix (reference extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:250-276): fancy_upsampling=0|1 (default 1),
- * subseq_bytes=N (bytes of unstuffed stream per Huffman decoding thread, default 128), profile=0|1. */
+ * subseq_bytes=N (bytes of unstuffed stream per Huffman decoding thread, default 128), profile=0|1; tuning knobs, none of
+ * which changes a result: groups=N / groups_host=N (image groups on separate streams), copy_threads=N, tail_launches=N
+ * (work-list rounds run as ordinary launches before the cooperative kernel, default 1), tail_spread=0|1 (work-list
+ * items dealt lane-major, default 1), stream_priority=0|1, stage_stream=0|1, dump_coef=0|1 (debug tap).
+ * B200JPEG_TRACE=1 in the environment prints the host timeline, the work-list rounds and the error flags of failed images. */
 B200JPEG_API int b200jpeg_decoder_create(b200jpegDecoder_t* decoder, int device_id, const char* options);
 B200JPEG_API int b200jpeg_decoder_destroy(b200jpegDecoder_t decoder);
 
