@@ -220,9 +220,11 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     plan.total_subseq += im.subseq_cta_count * kSubseqCta;
     plan.map_subseq.push_back(im.subseq_cta_first + im.subseq_cta_count);
 
-    // coefficient records: one per AC symbol; reserve for 2 bits per symbol plus the per-subsequence rounding
+    // coefficient records: one per entropy-coded symbol (DC, AC, ZRL, end of block).  A symbol takes at least one bit (an
+    // optimised table may give the end-of-block or the zero DC category a 1-bit code, and a flat block is just those two), so
+    // the reservation is one record per bit plus the per-subsequence rounding.  Only the part that is written is ever touched.
     im.rec_off = plan.rec_elems;
-    im.rec_cap = uint32_t(std::min<uint64_t>(uint64_t(im.raw_len) * 4 + uint64_t(im.subseq_cta_count) * kSubseqCta * kRecAlign + 64, 0xFFFFFF00ull));
+    im.rec_cap = uint32_t(std::min<uint64_t>(uint64_t(im.raw_len) * 8 + uint64_t(im.subseq_cta_count) * kSubseqCta * kRecAlign + 64, 0xFFFFFF00ull));
     plan.rec_elems = align_up(plan.rec_elems + im.rec_cap, 64);
     im.coef_off = plan.coef_elems;
     plan.coef_elems = align_up(plan.coef_elems + uint64_t(im.total_blocks) * 64, 64);

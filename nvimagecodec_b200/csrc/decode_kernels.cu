@@ -31,7 +31,7 @@ struct ByteClass
 {
     uint32_t keep;   // bit i: byte i is entropy-coded data
     uint32_t marker; // bit i: byte i is the FF of an RSTn marker
-    uint32_t bad;    // any other marker
+    uint32_t bad;    // bit i: byte i is the FF of any other marker (none may occur inside entropy-coded data)
 };
 
 // byte mask (0xFF / 0x00 per byte) -> 4 bits
@@ -71,7 +71,7 @@ __device__ __forceinline__ ByteClass classify16(const uint8_t* __restrict__ raw,
     c.keep = ~remove & in_mask;
     c.marker = marker & in_mask;
     const uint32_t n_succ = raw_len - base - 1u < 16u ? raw_len - base - 1u : 16u; // bytes that have a successor inside the data
-    c.bad = (bad & ((1u << n_succ) - 1u)) ? 1u : 0u;
+    c.bad = bad & ((1u << n_succ) - 1u);
     return c;
 }
 
@@ -97,8 +97,12 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_count(BatchDev b)
         s_k[threadIdx.x >> 5] = kept;
         s_m[threadIdx.x >> 5] = markers;
     }
+    // A marker other than RSTn ends the entropy-coded data there, as it does for the reference (ljt/jdhuff.c
+    // jpeg_fill_bit_buffer:287-391 stops feeding bytes at the first marker): files that carry more after their first EOI
+    // (MPO / gain-map / motion-photo appendices, embedded thumbnails) decode like everywhere else.  The earliest such
+    // marker wins: the per-image maximum of raw_len - position.
     if (c.bad)
-        atomicOr(&b.states[img].error, kErrBadMarker);
+        atomicMax(&b.states[img].trunc, im.raw_len - (base + uint32_t(__ffs(int(c.bad))) - 1u));
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t k = 0, m = 0;
@@ -117,10 +121,36 @@ __global__ void __launch_bounds__(32) k_unstuff_scan(BatchDev b)
     const int img = blockIdx.x;
     const ImageDesc& im = b.images[img];
     const uint32_t lane = threadIdx.x;
+    // entropy-coded bytes end at the first marker that is not RSTn (k_unstuff_count): chunks behind that point count
+    // nothing, the chunk it falls into is counted again up to it
+    const uint32_t trunc = b.states[img].trunc;
+    const uint32_t eff_len = im.raw_len - trunc;
+    const uint32_t cut = trunc ? eff_len / kChunkBytes : 0xFFFFFFFFu;
+    uint64_t cut_count = 0;
+    if (trunc) {
+        uint32_t kept = 0, markers = 0;
+        for (uint32_t off = lane * 16u; off < uint32_t(kChunkBytes); off += 32u * 16u) {
+            const uint32_t base = cut * kChunkBytes + off;
+            if (base < eff_len) {
+                uint32_t w[4], next;
+                const ByteClass c = classify16(b.raw + im.raw_off, eff_len, base, w, next);
+                kept += __popc(c.keep);
+                markers += __popc(c.marker);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            kept += __shfl_xor_sync(0xFFFFFFFFu, kept, o);
+            markers += __shfl_xor_sync(0xFFFFFFFFu, markers, o);
+        }
+        cut_count = uint64_t(kept) | (uint64_t(markers) << 32);
+    }
     uint64_t carry = 0;
     for (uint32_t c0 = 0; c0 < im.chunk_count; c0 += 32) {
         const uint32_t c = c0 + lane;
-        const uint64_t v = c < im.chunk_count ? b.chunk_counts[im.chunk_first + c] : 0;
+        uint64_t v = c < im.chunk_count ? b.chunk_counts[im.chunk_first + c] : 0;
+        if (c >= cut)
+            v = c == cut ? cut_count : 0;
         uint64_t inc = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -138,6 +168,7 @@ __global__ void __launch_bounds__(32) k_unstuff_scan(BatchDev b)
         S[g] = g == 0 ? 0u : clean_len; // U3 overwrites [1 .. markers]
     if (lane == 0) {
         b.states[img].clean_len = clean_len;
+        b.states[img].raw_eff = eff_len;
         b.states[img].marker_count = markers;
         if (markers != uint32_t(im.num_segments - 1))
             atomicOr(&b.states[img].error, kErrBadMarker);
@@ -153,8 +184,9 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
     const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
     uint32_t w[4] = {0, 0, 0, 0}, next = 0;
     ByteClass c{0, 0, 0};
-    if (base < im.raw_len)
-        c = classify16(b.raw + im.raw_off, im.raw_len, base, w, next);
+    const uint32_t eff_len = b.states[img].raw_eff; // raw_len, or up to the first marker that is not RSTn
+    if (base < eff_len)
+        c = classify16(b.raw + im.raw_off, eff_len, base, w, next);
     // block exclusive scan of (kept | markers << 16)
     const uint32_t mine = uint32_t(__popc(c.keep)) | (uint32_t(__popc(c.marker)) << 16);
     uint32_t inc = mine;

@@ -133,14 +133,16 @@ struct ImageState
     uint32_t error;         // bit flags, see kErr*
     uint32_t done_blocks;   // set by the thread that completes the last block (== total_blocks when the scan is complete)
     uint32_t rec_total;     // coefficient records of the image (after the subsequence scan)
-    uint32_t pad_[3];
+    uint32_t trunc;         // raw_len - position of the first marker other than RSTn inside the scan data (0: none)
+    uint32_t raw_eff;       // entropy-coded bytes actually taken: raw_len - trunc
+    uint32_t pad_[1];
 };
 
-constexpr uint32_t kErrBadMarker = 1;     // unexpected marker inside entropy-coded data / wrong RSTn order / count
+constexpr uint32_t kErrBadMarker = 1;     // wrong RSTn order / count
 constexpr uint32_t kErrBadCode = 2;       // invalid Huffman code on the synchronised path
 constexpr uint32_t kErrNotConverged = 4;  // subsequence synchronisation incomplete
 constexpr uint32_t kErrOverrun = 8;       // decode ran past the end of a segment / image
-constexpr uint32_t kErrRecords = 16;      // more coefficient records than reserved (a stream averaging < 2 bits per AC symbol)
+constexpr uint32_t kErrRecords = 16;      // more coefficient records than reserved (cannot happen for whole symbols: one record per bit is reserved)
 
 // Coefficient records: what the Huffman write pass hands to the IDCT kernel, one uint16 per AC symbol in stream order
 //   run << 12 | (value & 0xFFF)   a coefficient `value` (never 0) after `run` zeros
@@ -154,7 +156,11 @@ constexpr uint32_t kRecAlign = 4;         // records per 8-byte store: every sub
 // State of the Huffman decoder between two symbols, packed in 64 bits: bit position | (block-in-MCU * 64 + zigzag index) << 32
 B2J_HD unsigned long long pack_state(uint32_t p, uint32_t slot) { return (unsigned long long)p | ((unsigned long long)slot << 32); }
 
-constexpr int kMaxTailRounds = 512;
+constexpr int kRunAheadFrom = 4; // work-list rounds from this one on: one thread per run of consecutive listed subsequences
+                                 // walks the run and on into what follows while exit states keep changing (the lists are
+                                 // short by then, so nothing is serialised that would have run in parallel); with the
+                                 // shortcut of huffman.cuh subseq_repeats a periodic stream is walked at memory speed
+                                 // instead of one subsequence per round
 
 constexpr int kTraceRounds = 16; // work-list rounds whose length and time are kept for B200JPEG_TRACE
 
@@ -187,7 +193,10 @@ struct BatchDev // pointers handed to every kernel
     uint32_t* worklist[2];  // subsequences whose entry changed (global subsequence indices)
     SyncCounters* sync;
     uint32_t* sub_nrec;     // per subsequence: AC symbols (= coefficient records) its last decode produced
-    uint32_t* sub_rec_off;  // exclusive scan of sub_nrec rounded up to kRecAlign: first record of the subsequence in the image
+    uint32_t* sub_rec_off;  // exclusive scan of sub_nrec rounded up to kRecAlign: first record of the subsequence in the image.
+                            // Until k_subseq_scan writes it the array holds the work-list stamps of the synchronisation
+                            // rounds: the subsequence is an item of work-list round r iff stamp >= r + 1 (r + 2 once it has
+                            // also been listed for round r + 1)
     uint16_t* rec;          // coefficient records of all images (ImageDesc::rec_off)
     uint32_t* blk_rec;      // per block: index of its first record inside the image's records
     int32_t dump_coef;      // debug: the IDCT kernel also writes the dense coefficients it reconstructed to coef[]

@@ -352,4 +352,18 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
     return err;
 }
 
+// Run-ahead shortcut for periodic streams (flat image areas: every MCU has the same bits, so a decoder that starts at
+// the wrong phase can stay there for ever and the repair travels one subsequence at a time).  If the decode of
+// subsequence k went from state (p, slot) to (p + S, slot) and the stream words of subsequence k + 1 -- including the two
+// words a last symbol or table lookup may reach into -- equal those of subsequence k, the decode of k + 1 from that exit
+// state is the same decode shifted by S bits: nothing needs to be decoded.  `words` = the image's stream (either byte
+// order), first = first word of subsequence k, spw = words per subsequence.
+B2J_HD bool subseq_repeats(const uint32_t* words, uint32_t first, uint32_t spw)
+{
+    for (uint32_t j = 0; j < spw + 2u; ++j)
+        if (words[first + j] != words[first + spw + j])
+            return false;
+    return true;
+}
+
 } // namespace b200jpeg

@@ -91,7 +91,8 @@ __device__ __forceinline__ HuffEnv make_env(const BatchDev& b, const ImageDesc& 
 // Decode subsequence k of an image from entry state E in synchronisation mode and publish the result.
 // Returns true if the exit state differs from the one recorded before.
 template <bool PRESWAPPED, bool DIRECT = true>
-__device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& env, uint32_t t, uint32_t k, unsigned long long E, bool exact)
+__device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& env, uint32_t t, uint32_t k, unsigned long long E, bool exact,
+    unsigned long long* exit_state = nullptr)
 {
     HuffState s;
     s.p = uint32_t(E);
@@ -105,6 +106,8 @@ __device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& en
     decode_span<false, PRESWAPPED, DIRECT>(env, s, (k + 1u) * uint32_t(b.subseq_bits), nullptr);
     const unsigned long long X = pack_state(s.p, s.blk * 64u + s.z);
     const bool changed = (X != __ldcg(b.sub_exit + t));
+    if (exit_state)
+        *exit_state = X;
     b.sub_exit[t] = X;
     b.sub_entry[t] = E;
     b.sub_nrec[t] = s.nrec;
@@ -136,6 +139,7 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
     const uint32_t words_s = uint32_t(__cvta_generic_to_shared(sm.stream)) + (threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5)) * 4u;
     const HuffEnv env = make_env(b, im, clean_len, words, sm.lut, sm.tabsel, words_s);
     if (round == 0) {
+        b.sub_rec_off[t] = 0; // work-list stamp: not an item of any round
         if (idle) {
             b.sub_exit[t] = b.sub_entry[t] = pack_state(clean_bits, 0);
             b.sub_rec[t] = 0;
@@ -159,6 +163,7 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
         if (changed && next_live) {
             const uint32_t i = atomicAdd(&b.sync->count[0], 1u);
             b.worklist[0][i] = t + 1;
+            b.sub_rec_off[t + 1] = 1u; // item of work-list round 0
         }
     }
 }
@@ -183,14 +188,16 @@ __device__ __forceinline__ bool tail_round(const BatchDev& b, const HuffSmem& sm
         b.sync->count[(r + 2) % 3] = 0;
     const uint32_t* in = b.worklist[r & 1];
     uint32_t* out = b.worklist[(r + 1) & 1];
+    const bool run_ahead = r >= kRunAheadFrom;
     for (uint32_t i = tid; i < n; i += nthreads) {
-        const uint32_t t = __ldcg(in + i);
+        uint32_t t = __ldcg(in + i);
+        // Run-ahead rounds: only the head of a run of consecutive listed subsequences is worked on -- by one thread that walks
+        // the whole run (every item of it is due) and on into the subsequences behind it for as long as exit states keep
+        // changing.  The items behind the head are left to that thread.
+        if (run_ahead && __ldcg(b.sub_rec_off + t - 1) >= uint32_t(r) + 1u)
+            continue;
         const int img = int(__ldg(b.subseq_cta_img + t / kSubseqCta)) - b.image_base;
         const ImageDesc& im = b.images[img];
-        const uint32_t k = t - im.subseq_first;
-        const unsigned long long E = __ldcg(b.sub_exit + t - 1); // written by other SMs in earlier rounds: bypass L1
-        if (E == __ldcg(b.sub_entry + t))
-            continue;
         const uint32_t clean_len = b.states[img].clean_len;
         const uint32_t* gwords = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
         const uint16_t* lut = reinterpret_cast<const uint16_t*>(b.huff);
@@ -203,39 +210,82 @@ __device__ __forceinline__ bool tail_round(const BatchDev& b, const HuffSmem& sm
             lut = sm.lut;
             tabsel = my_tabsel;
         }
-        bool changed;
-        if (W) {
-            // the subsequence starts on a 16-byte boundary of the image's stream (which is readable 16 bytes past its
-            // end): fetch it with independent 16-byte loads first, then byte-swap into the thread's staging words
-            const uint32_t first = k * spw;
-            const uint4* src = reinterpret_cast<const uint4*>(gwords + first);
-            constexpr int kMaxVec = 17; // (256 B / 4 + 3 | 1) words
-            uint4 v[kMaxVec];
-            const int nvec = int(W + 3u) >> 2;
-            const int avail = int((((im.raw_len + 16u) >> 2) - first + 3u) >> 2); // 16-byte groups inside the stream buffer
+        unsigned long long E = __ldcg(b.sub_exit + t - 1); // written by other SMs in earlier rounds: bypass L1
+        bool prev_shift = false; // the subsequence before t was done by this thread and moved the state by exactly S bits
+        bool in_run = true;      // t belongs to the run of listed items this thread started with
+        for (;;) {
+            const uint32_t k = t - im.subseq_first;
+            bool changed = false;
+            unsigned long long X;
+            if (E == __ldcg(b.sub_entry + t)) {
+                X = __ldcg(b.sub_exit + t); // already decoded from this state
+            } else if (prev_shift && im.num_segments == 1 && uint64_t(k + 1) * S + 64u <= uint64_t(clean_len) * 8u &&
+                       subseq_repeats(gwords, (k - 1u) * spw, spw)) {
+                // periodic stretch (huffman.cuh subseq_repeats): the same decode as the one before, S bits further on
+                X = E + S;
+                changed = (X != __ldcg(b.sub_exit + t));
+                b.sub_exit[t] = X;
+                b.sub_entry[t] = E;
+                b.sub_nrec[t] = b.sub_nrec[t - 1];
+                b.sub_rec[t] = b.sub_rec[t - 1];
+                ++redone;
+            } else if (W) {
+                // the subsequence starts on a 16-byte boundary of the image's stream (which is readable 16 bytes past its
+                // end): fetch it with independent 16-byte loads first, then byte-swap into the thread's staging words
+                const uint32_t first = k * spw;
+                const uint4* src = reinterpret_cast<const uint4*>(gwords + first);
+                constexpr int kMaxVec = 17; // (256 B / 4 + 3 | 1) words
+                uint4 v[kMaxVec];
+                const int nvec = int(W + 3u) >> 2;
+                const int avail = int((((im.raw_len + 16u) >> 2) - first + 3u) >> 2); // 16-byte groups inside the stream buffer
 #pragma unroll
-            for (int j = 0; j < kMaxVec; ++j)
-                if (j < nvec)
-                    v[j] = j < avail ? __ldcg(src + j) : make_uint4(0, 0, 0, 0);
+                for (int j = 0; j < kMaxVec; ++j)
+                    if (j < nvec)
+                        v[j] = j < avail ? __ldcg(src + j) : make_uint4(0, 0, 0, 0);
 #pragma unroll
-            for (int j = 0; j < kMaxVec; ++j)
-                if (j < nvec) {
-                    const uint32_t w4[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+                for (int j = 0; j < kMaxVec; ++j)
+                    if (j < nvec) {
+                        const uint32_t w4[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
 #pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        if (uint32_t(4 * j + q) < W)
-                            my_words[4 * j + q] = __byte_perm(w4[q], 0, 0x0123);
+                        for (int q = 0; q < 4; ++q)
+                            if (uint32_t(4 * j + q) < W)
+                                my_words[4 * j + q] = __byte_perm(w4[q], 0, 0x0123);
+                    }
+                const HuffEnv env = make_env(b, im, clean_len, my_words - first, lut, tabsel,
+                    uint32_t(__cvta_generic_to_shared(my_words)) - first * 4u);
+                changed = sync_decode<true, true>(b, env, t, k, E, false, &X);
+                ++redone;
+            } else {
+                const HuffEnv env = make_env(b, im, clean_len, gwords, lut, tabsel);
+                changed = sync_decode<false>(b, env, t, k, E, false, &X);
+                ++redone;
+            }
+            if (uint64_t(k + 1) * S >= uint64_t(clean_len) * 8u)
+                break; // no subsequence behind this one
+            if (!run_ahead) { // Jacobi: a changed exit state makes the successor an item of the next round
+                if (changed) {
+                    out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
+                    b.sub_rec_off[t + 1] = uint32_t(r) + 2u;
                 }
-            const HuffEnv env = make_env(b, im, clean_len, my_words - first, lut, tabsel,
-                uint32_t(__cvta_generic_to_shared(my_words)) - first * 4u);
-            changed = sync_decode<true, true>(b, env, t, k, E, false);
-        } else {
-            const HuffEnv env = make_env(b, im, clean_len, gwords, lut, tabsel);
-            changed = sync_decode<false>(b, env, t, k, E, false);
+                break;
+            }
+            const bool next_listed = __ldcg(b.sub_rec_off + t + 1) >= uint32_t(r) + 1u;
+            if (next_listed && !in_run) { // the head of another run: its thread may have read the old exit state
+                if (changed) {
+                    out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
+                    b.sub_rec_off[t + 1] = uint32_t(r) + 2u;
+                }
+                break;
+            }
+            if (!next_listed) {
+                if (!changed)
+                    break;
+                in_run = false;
+            }
+            prev_shift = (X == E + S);
+            E = X;
+            ++t;
         }
-        ++redone;
-        if (changed && uint64_t(k + 1) * S < uint64_t(clean_len) * 8u)
-            out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
     }
     return true;
 }
@@ -277,7 +327,7 @@ __global__ void __launch_bounds__(kTailCta) k_huff_sync_tail(BatchDev b, int fir
     unsigned long long t0 = 0;
     if (tid == 0)
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    for (; r < kMaxTailRounds; ++r) {
+    for (;; ++r) { // until the list is empty: at most one round per subsequence of the longest unsynchronised chain
         if (tid == 0 && r < kTraceRounds)
             b.sync->round_items[r] = __ldcg(&b.sync->count[r % 3]);
         if (!tail_round(b, sm, pool_staged, r, tid, nthreads, redone))

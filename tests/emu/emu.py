@@ -52,7 +52,7 @@ def encode(pixels, quality=90, subsampling=3, restart_interval=0, planar=False):
     return out[:n].tobytes()
 
 
-def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=64, jacobi=True, want_coef=False, slots=None, rois=None):
+def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=1 << 30, jacobi=True, want_coef=False, slots=None, rois=None):
     """dims: list of (w, h).  Returns (outputs, statuses, rounds, coefs).  rois: per image None or (x, y, w, h): the output
     holds that region only"""
     n = len(datas)
@@ -76,5 +76,5 @@ def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=64
                            int(fancy), subseq_bytes, max_rounds, int(jacobi), st, C.byref(rounds),
                            (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None, stats,
                            (C.c_int * (4 * n))(*[v for r in rois for v in (r if r else (0, 0, 0, 0))]) if rois is not None else None)
-    decode_batch.last_stats = {"rounds": int(stats[0]), "redone": int(stats[1]), "subsequences": int(stats[2])}
+    decode_batch.last_stats = {"rounds": int(stats[0]), "redone": int(stats[1]), "subsequences": int(stats[2]), "skipped": int(stats[3])}
     return outs, list(st), rounds.value, coefs

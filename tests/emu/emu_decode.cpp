@@ -154,7 +154,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                     states[i].error |= kErrBadMarker;
                 ++markers;
             } else if (cur >= 0xD0 && cur <= 0xD7 && pv == 0xFF) remove = true;
-            else if (cur == 0xFF && nx != 0 && p + 1 < im.raw_len) states[i].error |= kErrBadMarker;
+            else if (cur == 0xFF && nx != 0 && p + 1 < im.raw_len) break; // any other marker ends the entropy-coded data
             if (!remove) dst[k++] = uint8_t(cur);
         }
         states[i].clean_len = k;
@@ -175,7 +175,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         std::memcpy(clean_sw.data() + w, &v, 4);
     }
     std::vector<uint32_t> wl, wl_next;
-    unsigned long long redone = 0;
+    unsigned long long redone = 0, skipped = 0;
     for (int round = 0; round < 2; ++round) {
         const std::vector<unsigned long long> snap = ex; // worst-case race: every thread sees its predecessor's old exit
         for (int i = 0; i < m; ++i) {
@@ -208,25 +208,78 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             }
         }
     }
+    // work-list rounds (tail_round of huffman_kernels.cu): Jacobi until the list is empty; from round kRunAheadFrom on one
+    // thread per run of listed items walks the run and on into what follows, periodic stretches without decoding
+    std::vector<uint32_t> stamp(plan.total_subseq, 0);
+    for (uint32_t t : wl)
+        stamp[t] = 1;
     int rounds = 2;
     while (!wl.empty() && rounds < max_rounds) {
+        const int r = rounds - 2;
+        const bool run_ahead = r >= kRunAheadFrom;
         const std::vector<unsigned long long> snap = ex;
         wl_next.clear();
-        for (uint32_t t : wl) {
+        for (uint32_t t0 : wl) {
+            uint32_t t = t0;
+            if (run_ahead && stamp[t - 1] >= uint32_t(r) + 1u)
+                continue; // not the head of its run of listed items
             int i = 0;
             while (i + 1 < m && plan.images[i + 1].subseq_first <= t)
                 ++i;
             const ImageDesc& im = plan.images[i];
-            const uint32_t k = t - im.subseq_first;
-            const unsigned long long E = snap[t - 1];
-            if (E == en[t])
-                continue;
             std::vector<uint16_t> unused;
             const HuffEnv env = make_env(i, false, unused); // the tail kernel reads the tables from the global pool
-            const bool changed = sync_decode(env, t, k, E, false);
-            ++redone;
-            if (changed && uint64_t(k + 1) * S < uint64_t(states[i].clean_len) * 8u)
-                wl_next.push_back(t + 1);
+            const uint32_t* gwords = reinterpret_cast<const uint32_t*>(clean.data() + im.clean_off);
+            const uint32_t spw = S >> 5;
+            const uint64_t clean_bits = uint64_t(states[i].clean_len) * 8u;
+            unsigned long long E = snap[t - 1];
+            bool prev_shift = false, in_run = true;
+            for (;;) {
+                const uint32_t k = t - im.subseq_first;
+                bool changed = false;
+                unsigned long long X;
+                if (E == en[t]) {
+                    X = ex[t];
+                } else if (prev_shift && im.num_segments == 1 && uint64_t(k + 1) * S + 64u <= clean_bits && subseq_repeats(gwords, (k - 1u) * spw, spw)) {
+                    X = E + S;
+                    changed = X != ex[t];
+                    ex[t] = X;
+                    en[t] = E;
+                    nrec[t] = nrec[t - 1];
+                    rec[t] = rec[t - 1];
+                    ++skipped;
+                    ++redone;
+                } else {
+                    changed = sync_decode(env, t, k, E, false);
+                    X = ex[t];
+                    ++redone;
+                }
+                if (uint64_t(k + 1) * S >= clean_bits)
+                    break;
+                if (!run_ahead) {
+                    if (changed) {
+                        wl_next.push_back(t + 1);
+                        stamp[t + 1] = uint32_t(r) + 2u;
+                    }
+                    break;
+                }
+                const bool next_listed = stamp[t + 1] >= uint32_t(r) + 1u;
+                if (next_listed && !in_run) {
+                    if (changed) {
+                        wl_next.push_back(t + 1);
+                        stamp[t + 1] = uint32_t(r) + 2u;
+                    }
+                    break;
+                }
+                if (!next_listed) {
+                    if (!changed)
+                        break;
+                    in_run = false;
+                }
+                prev_shift = (X == E + S);
+                E = X;
+                ++t;
+            }
         }
         wl.swap(wl_next);
         ++rounds;
@@ -236,6 +289,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         stats[0] = uint64_t(rounds);
         stats[1] = redone;
         stats[2] = plan.total_subseq;
+        stats[3] = skipped;
     }
 
     // ---- segmented scan of slot counts + consistency check (k_subseq_scan) ----

@@ -154,3 +154,60 @@ def test_emulated_randomized_batch():
         assert st == [0] * len(datas), [(i, specs[i]) for i, x in enumerate(st) if x]
         for i, (d, o) in enumerate(zip(datas, outs)):
             assert np.array_equal(o, port.decode(d, pfmt, fancy)), (i, specs[i], fmt)
+
+
+def test_emulated_flat_images_with_optimised_tables():
+    """Flat and mostly-flat images with optimised Huffman tables: the end-of-block and zero-DC codes are one bit long, so a
+    block is two symbols in two bits -- the record reservation must cover one record per bit (such files came
+    back as CORRUPT_STREAM)."""
+    rng = np.random.default_rng(5)
+    flat = np.full((512, 512, 3), 200, np.uint8)
+    mostly = flat.copy()
+    mostly[:48] = rng.integers(0, 255, (48, 512, 3))
+    gray = np.full((256, 512), 17, np.uint8)
+    datas, dims = [], []
+    for img in (flat, mostly, gray):
+        for samp in ((1, 1), (2, 2)):
+            if img.ndim == 2 and samp != (1, 1):
+                continue
+            datas.append(ref.ljt_encode(img, 90, samp, optimize=True))
+            dims.append((img.shape[1], img.shape[0]))
+    outs, st, rounds, _ = emu.decode_batch(datas, dims, 4, 1, 128)
+    assert st == [0] * len(datas)
+    for d, o in zip(datas, outs):
+        assert np.array_equal(o, port.decode(d, port.FMT_I_RGB, True))
+
+
+def test_emulated_periodic_streams_converge():
+    """A flat image is a periodic bit stream: a decoder that starts at the wrong phase never locks on, so the repair has
+    to travel the whole image.  The run-ahead rounds walk it (without decoding where the period divides the subsequence
+    length) instead of spending one work-list round per subsequence (4096x4096 hit the old cap of 512 rounds)."""
+    flat = np.full((2048, 2048, 3), 200, np.uint8)
+    half = flat.copy()
+    half[:256] = np.random.default_rng(6).integers(0, 255, (256, 2048, 3))
+    for img, samp, opt in ((flat, (2, 2), False), (half, (2, 2), False), (flat, (1, 1), True), (half, (2, 1), True)):
+        d = ref.ljt_encode(img, 90, samp, optimize=opt)
+        outs, st, rounds, _ = emu.decode_batch([d], [(2048, 2048)], 4, 1, 128)
+        assert st == [0] and np.array_equal(outs[0], port.decode(d, port.FMT_I_RGB, True))
+        assert rounds <= 2 + 4 + 8, rounds  # Jacobi rounds, then a few run-ahead rounds
+    d = ref.ljt_encode(flat, 90, (2, 2))
+    emu.decode_batch([d], [(2048, 2048)], 4, 1, 128)
+    assert emu.decode_batch.last_stats["skipped"] > 100  # the periodic stretch was walked without decoding it
+
+
+def test_emulated_data_after_first_eoi():
+    """Files that carry more data after the image's EOI -- a second JPEG (MPO, gain maps, motion photos), a thumbnail, stray
+    bytes with an FFD9 in them: the scan ends at the first marker, like for the reference (the parser took the
+    last EOI of the file and the image came back corrupt)."""
+    a = make_jpeg(91, 320, 200, (2, 2), 85)
+    b2 = make_jpeg(92, 64, 64, (1, 1), 85)
+    c = make_jpeg(93, 211, 97, (2, 1), 90, restart_interval=3)
+    datas = [a + b"\x00" * 37 + b2, a + b2, c + b"\xff\xd9\x12\x34\xff\xd9", a + b"\xff\xe1\x00\x08abcdef\xff\xd9"]
+    dims = [(320, 200), (320, 200), (211, 97), (320, 200)]
+    wants = [port.decode(x, port.FMT_I_RGB, True) for x in (a, a, c, a)]
+    rwant, rst, _ = ref.Session.shared().decoder(options=":fancy_upsampling=1").decode_host(datas)
+    assert all(s == ref.STATUS_SUCCESS for s in rst)
+    outs, st, _, _ = emu.decode_batch(datas, dims, 4, 1, 128)
+    assert st == [0] * len(datas)
+    for o, w, rw in zip(outs, wants, rwant):
+        assert np.array_equal(o, w) and np.array_equal(o, rw)
