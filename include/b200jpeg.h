@@ -98,11 +98,22 @@ typedef struct
      * decode (what the reference produces).  roi_width == roi_height == 0: the whole image.  Planar formats: plane p
      * starts at buffer + p * row_stride * roi_height. */
     int32_t roi_x, roi_y, roi_width, roi_height;
+    /* nvimgcodecImageInfo_t::cuda_stream of this image (reference include/nvimgcodec.h:474-497): with has_cuda_stream != 0 the
+     * decoder waits for what is in flight on that stream before it writes the buffer, and makes the stream wait for the
+     * decode (reference idiom: extensions/nvjpeg/hw_decoder.cpp:649-655, cuda_decoder.cpp:551-556).  Otherwise the
+     * user_stream argument of the call plays that role. */
+    void* cuda_stream;
+    int32_t has_cuda_stream;
+    int32_t reserved;
 } b200jpegOutput_t;
 
 /* ---- library ---- */
 B200JPEG_API const char* b200jpeg_version(void);
 B200JPEG_API const char* b200jpeg_status_string(int status);
+/* Diagnostics (CUDA failures, configuration problems) go to stderr unless a callback is installed; severity 0 info,
+ * 1 warning, 2 error.  The nvImageCodec extension installs one that forwards to nvimgcodecFrameworkDesc_t::log. */
+typedef void (*b200jpegLogFn_t)(void* ctx, int severity, const char* message);
+B200JPEG_API void b200jpeg_set_log_callback(b200jpegLogFn_t fn, void* ctx);
 
 /* ---- stream probe (host only, no CUDA) ---- */
 B200JPEG_API int b200jpeg_parse_header(const uint8_t* data, size_t size, b200jpegStreamInfo_t* info);
@@ -110,6 +121,8 @@ B200JPEG_API int b200jpeg_parse_header(const uint8_t* data, size_t size, b200jpe
 /* ---- decoder ----
  * options: the reference's option string, "name=value" tokens separated by spaces, optional "b200jpeg_decoder:" or ":"
  * prefix (reference extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:250-276): fancy_upsampling=0|1 (default 1),
+ * fast_idct=0|1 (the reference's switch to JDCT_IFAST, libjpeg_turbo_decoder.cpp:272-273: create() answers
+ * B200JPEG_STATUS_UNSUPPORTED for 1, so that the framework keeps its CPU decoder for such a session),
  * subseq_bytes=N (bytes of unstuffed stream per Huffman decoding thread, default 128), profile=0|1; tuning knobs, none of
  * which changes a result: groups=N / groups_host=N (image groups on separate streams), copy_threads=N, tail_launches=N
  * (work-list rounds run as ordinary launches before the cooperative kernel, default 1), tail_spread=0|1 (work-list
@@ -144,6 +157,17 @@ B200JPEG_API int b200jpeg_decoder_set_allocators(b200jpegDecoder_t decoder, cons
  * Replaces DecoderImpl::decodeBatch (reference extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:444-490). */
 B200JPEG_API int b200jpeg_decode_batch(b200jpegDecoder_t decoder, int batch_size, const uint8_t* const* data, const size_t* sizes,
     const b200jpegOutput_t* outputs, void* user_stream, int32_t* statuses);
+
+/* The same call in two halves, so that the host work of batch k + 1 overlaps the device work of batch k (the plugin's
+ * decode() returns after submit and reports imageReady from a completion thread, the way the reference's plugins hand
+ * their work to the executor, extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:444-490).
+ *   submit: parse, plan, copy the entropy-coded bytes to pinned staging, enqueue every copy and kernel, make the outputs'
+ *           streams wait for the result.  On return data[]/sizes[] are not needed any more; statuses[] holds what the
+ *           host already knows (bad / unsupported streams).  Up to two batches may be in flight (each has its own scratch).
+ *   wait:   blocks until the oldest submitted batch is done on the device; statuses[] final (same batch_size entries). */
+B200JPEG_API int b200jpeg_decode_submit(b200jpegDecoder_t decoder, int batch_size, const uint8_t* const* data, const size_t* sizes,
+    const b200jpegOutput_t* outputs, void* user_stream, int32_t* statuses);
+B200JPEG_API int b200jpeg_decode_wait(b200jpegDecoder_t decoder, int32_t* statuses);
 
 /* Two-phase variant used to time the device work with inputs already resident in HBM:
  * prepare = parse + table building + H2D of bitstreams/descriptors; run = every kernel of the decode, nothing else. */

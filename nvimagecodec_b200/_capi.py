@@ -22,7 +22,8 @@ class StreamInfo(C.Structure):
 
 class Output(C.Structure):
     _fields_ = [("buffer", C.c_void_p), ("row_stride", C.c_int64), ("format", C.c_int32), ("on_host", C.c_int32),
-                ("roi_x", C.c_int32), ("roi_y", C.c_int32), ("roi_width", C.c_int32), ("roi_height", C.c_int32)]
+                ("roi_x", C.c_int32), ("roi_y", C.c_int32), ("roi_width", C.c_int32), ("roi_height", C.c_int32),
+                ("cuda_stream", C.c_void_p), ("has_cuda_stream", C.c_int32), ("reserved", C.c_int32)]
 
 
 MALLOC_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t, C.c_void_p)
@@ -39,7 +40,7 @@ class EncodeInput(C.Structure):
                 ("on_host", C.c_int32), ("subsampling", C.c_int32), ("quality", C.c_int32), ("restart_interval", C.c_int32)]
 
 
-EXPORTS = ["b200jpeg_version", "b200jpeg_status_string", "b200jpeg_parse_header", "b200jpeg_decoder_create", "b200jpeg_decoder_destroy",
+EXPORTS = ["b200jpeg_version", "b200jpeg_status_string", "b200jpeg_set_log_callback", "b200jpeg_decode_submit", "b200jpeg_decode_wait", "b200jpeg_parse_header", "b200jpeg_decoder_create", "b200jpeg_decoder_destroy",
            "b200jpeg_decode_batch", "b200jpeg_decode_prepare", "b200jpeg_decode_run", "b200jpeg_decoder_get_stats", "b200jpeg_decoder_get_stage_times", "b200jpeg_debug_fetch",
            "b200jpeg_encoder_create", "b200jpeg_encoder_destroy", "b200jpeg_encode_batch", "b200jpeg_encoder_get_stats",
            "b200jpeg_decoder_set_allocators", "b200jpeg_encoder_set_allocators"]
@@ -62,6 +63,8 @@ def lib():
         L.b200jpeg_decoder_destroy.argtypes = [C.c_void_p]
         L.b200jpeg_decode_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(Output),
                                             C.c_void_p, C.POINTER(C.c_int32)]
+        L.b200jpeg_decode_submit.argtypes = L.b200jpeg_decode_batch.argtypes
+        L.b200jpeg_decode_wait.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
         L.b200jpeg_decode_prepare.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(Output),
                                               C.POINTER(C.c_int32)]
         L.b200jpeg_decode_run.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]

@@ -1,5 +1,6 @@
 // capi.cpp -- extern "C" boundary of libb200jpeg.so (include/b200jpeg.h).
 #include <cuda_runtime_api.h>
+#include <atomic>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -7,13 +8,56 @@
 #include "decoder.h"
 #include "encoder.h"
 #include "jpeg_parse.h"
+#include "log.h"
 
 using namespace b200jpeg;
 
+// Two complete decoder contexts (streams, scratch, pinned staging) so that two batches can be in flight
+// (b200jpeg_decode_submit / _wait); the second one is created when it is first needed.
 struct b200jpegDecoder
 {
-    Decoder* impl;
+    Decoder* slot[2] = {nullptr, nullptr};
+    int device = 0;
+    DecoderOptions opt;
+    Allocators alloc;
+    bool alloc_set = false;
+    std::atomic<uint64_t> submitted{0}, completed{0}; // submit and wait may come from two threads (one each)
+    int last = 0; // slot of the batch whose results get_stats / debug_fetch describe
+    Decoder* impl() { return slot[last]; }
+    ~b200jpegDecoder()
+    {
+        delete slot[0];
+        delete slot[1];
+    }
 };
+
+static int make_slot(b200jpegDecoder* d, int i)
+{
+    if (d->slot[i])
+        return B200JPEG_STATUS_SUCCESS;
+    Decoder* dec = new Decoder(d->device, d->opt);
+    int rc = dec->init();
+    if (rc == B200JPEG_STATUS_SUCCESS && d->alloc_set)
+        rc = dec->set_allocators(d->alloc);
+    if (rc != B200JPEG_STATUS_SUCCESS) {
+        delete dec;
+        return rc;
+    }
+    d->slot[i] = dec;
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+static std::vector<Decoder::OutputDesc> to_outputs(int n, const b200jpegOutput_t* outputs)
+{
+    std::vector<Decoder::OutputDesc> outs(n);
+    for (int i = 0; i < n; ++i) {
+        outs[i] = Decoder::OutputDesc{outputs[i].buffer, outputs[i].row_stride, outputs[i].format, outputs[i].on_host, outputs[i].roi_x,
+            outputs[i].roi_y, outputs[i].roi_width, outputs[i].roi_height};
+        outs[i].stream = static_cast<cudaStream_t>(outputs[i].cuda_stream);
+        outs[i].has_stream = outputs[i].has_cuda_stream != 0;
+    }
+    return outs;
+}
 struct b200jpegEncoder
 {
     Encoder* impl;
@@ -21,7 +65,9 @@ struct b200jpegEncoder
 
 extern "C" {
 
-const char* b200jpeg_version(void) { return "b200jpeg 0.1.0 (sm_100a)"; }
+const char* b200jpeg_version(void) { return "b200jpeg 0.2.0 (sm_100a)"; }
+
+void b200jpeg_set_log_callback(b200jpegLogFn_t fn, void* ctx) { set_log_callback(reinterpret_cast<LogFn>(fn), ctx); }
 
 const char* b200jpeg_status_string(int s)
 {
@@ -71,13 +117,18 @@ int b200jpeg_decoder_create(b200jpegDecoder_t* decoder, int device_id, const cha
         return B200JPEG_STATUS_INVALID_PARAMETER;
     *decoder = nullptr;
     try {
-        Decoder* d = new Decoder(device_id, parse_decoder_options(options, "b200jpeg_decoder"));
-        const int rc = d->init();
+        const DecoderOptions opt = parse_decoder_options(options, "b200jpeg_decoder");
+        if (opt.fast_idct)
+            return B200JPEG_STATUS_UNSUPPORTED; // JDCT_IFAST pixels are not offered (see DecoderOptions::fast_idct)
+        b200jpegDecoder* d = new b200jpegDecoder();
+        d->device = device_id;
+        d->opt = opt;
+        const int rc = make_slot(d, 0);
         if (rc != B200JPEG_STATUS_SUCCESS) {
             delete d;
             return rc;
         }
-        *decoder = new b200jpegDecoder{d};
+        *decoder = d;
     } catch (const std::bad_alloc&) {
         return B200JPEG_STATUS_ALLOC_FAILED;
     } catch (...) {
@@ -104,9 +155,11 @@ static Allocators to_allocators(const b200jpegAllocators_t* a)
 
 int b200jpeg_decoder_set_allocators(b200jpegDecoder_t decoder, const b200jpegAllocators_t* allocators)
 {
-    if (!decoder)
+    if (!decoder || decoder->slot[1])
         return B200JPEG_STATUS_INVALID_PARAMETER;
-    return decoder->impl->set_allocators(to_allocators(allocators));
+    decoder->alloc = to_allocators(allocators);
+    decoder->alloc_set = true;
+    return decoder->slot[0]->set_allocators(decoder->alloc);
 }
 
 int b200jpeg_encoder_set_allocators(b200jpegEncoder_t encoder, const b200jpegAllocators_t* allocators)
@@ -120,7 +173,6 @@ int b200jpeg_decoder_destroy(b200jpegDecoder_t decoder)
 {
     if (!decoder)
         return B200JPEG_STATUS_INVALID_PARAMETER;
-    delete decoder->impl;
     delete decoder;
     return B200JPEG_STATUS_SUCCESS;
 }
@@ -128,14 +180,12 @@ int b200jpeg_decoder_destroy(b200jpegDecoder_t decoder)
 int b200jpeg_decode_prepare(b200jpegDecoder_t decoder, int n, const uint8_t* const* data, const size_t* sizes,
     const b200jpegOutput_t* outputs, int32_t* statuses)
 {
-    if (!decoder || n < 0)
+    if (!decoder || n < 0 || decoder->submitted != decoder->completed)
         return B200JPEG_STATUS_INVALID_PARAMETER;
     try {
-        std::vector<Decoder::OutputDesc> outs(n);
-        for (int i = 0; i < n; ++i)
-            outs[i] = Decoder::OutputDesc{outputs[i].buffer, outputs[i].row_stride, outputs[i].format, outputs[i].on_host, outputs[i].roi_x,
-                outputs[i].roi_y, outputs[i].roi_width, outputs[i].roi_height};
-        return decoder->impl->prepare(n, data, sizes, outs.data(), statuses);
+        const std::vector<Decoder::OutputDesc> outs = to_outputs(n, outputs);
+        decoder->last = 0;
+        return decoder->slot[0]->prepare(n, data, sizes, outs.data(), statuses);
     } catch (const std::bad_alloc&) {
         return B200JPEG_STATUS_ALLOC_FAILED;
     } catch (...) {
@@ -145,10 +195,11 @@ int b200jpeg_decode_prepare(b200jpegDecoder_t decoder, int n, const uint8_t* con
 
 int b200jpeg_decode_run(b200jpegDecoder_t decoder, void* user_stream, int32_t* statuses)
 {
-    if (!decoder || !statuses)
+    if (!decoder || !statuses || decoder->submitted != decoder->completed)
         return B200JPEG_STATUS_INVALID_PARAMETER;
     try {
-        return decoder->impl->run(static_cast<cudaStream_t>(user_stream), statuses);
+        decoder->last = 0;
+        return decoder->slot[0]->run(static_cast<cudaStream_t>(user_stream), statuses);
     } catch (...) {
         return B200JPEG_STATUS_INTERNAL_ERROR;
     }
@@ -157,16 +208,56 @@ int b200jpeg_decode_run(b200jpegDecoder_t decoder, void* user_stream, int32_t* s
 int b200jpeg_decode_batch(b200jpegDecoder_t decoder, int n, const uint8_t* const* data, const size_t* sizes,
     const b200jpegOutput_t* outputs, void* user_stream, int32_t* statuses)
 {
-    if (!decoder || n < 0)
+    if (!decoder || n < 0 || decoder->submitted != decoder->completed)
         return B200JPEG_STATUS_INVALID_PARAMETER;
     try {
-        std::vector<Decoder::OutputDesc> outs(n);
-        for (int i = 0; i < n; ++i)
-            outs[i] = Decoder::OutputDesc{outputs[i].buffer, outputs[i].row_stride, outputs[i].format, outputs[i].on_host, outputs[i].roi_x,
-                outputs[i].roi_y, outputs[i].roi_width, outputs[i].roi_height};
-        return decoder->impl->decode(n, data, sizes, outs.data(), static_cast<cudaStream_t>(user_stream), statuses);
+        const std::vector<Decoder::OutputDesc> outs = to_outputs(n, outputs);
+        decoder->last = 0;
+        return decoder->slot[0]->decode(n, data, sizes, outs.data(), static_cast<cudaStream_t>(user_stream), statuses);
     } catch (const std::bad_alloc&) {
         return B200JPEG_STATUS_ALLOC_FAILED;
+    } catch (...) {
+        return B200JPEG_STATUS_INTERNAL_ERROR;
+    }
+}
+
+int b200jpeg_decode_submit(b200jpegDecoder_t decoder, int n, const uint8_t* const* data, const size_t* sizes,
+    const b200jpegOutput_t* outputs, void* user_stream, int32_t* statuses)
+{
+    if (!decoder || n < 0 || decoder->submitted - decoder->completed >= 2)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    try {
+        const int s = int(decoder->submitted & 1);
+        int rc = make_slot(decoder, s);
+        if (rc != B200JPEG_STATUS_SUCCESS)
+            return rc;
+        const std::vector<Decoder::OutputDesc> outs = to_outputs(n, outputs);
+        rc = decoder->slot[s]->submit(n, data, sizes, outs.data(), static_cast<cudaStream_t>(user_stream), statuses);
+        if (rc != B200JPEG_STATUS_SUCCESS) {
+            if (decoder->slot[s]->in_flight()) { // partly enqueued: drain it, the batch is not counted
+                std::vector<int32_t> tmp(n > 0 ? n : 1);
+                decoder->slot[s]->wait(tmp.data());
+            }
+            return rc;
+        }
+        ++decoder->submitted;
+        return B200JPEG_STATUS_SUCCESS;
+    } catch (const std::bad_alloc&) {
+        return B200JPEG_STATUS_ALLOC_FAILED;
+    } catch (...) {
+        return B200JPEG_STATUS_INTERNAL_ERROR;
+    }
+}
+
+int b200jpeg_decode_wait(b200jpegDecoder_t decoder, int32_t* statuses)
+{
+    if (!decoder || !statuses || decoder->submitted == decoder->completed)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    try {
+        const int s = int(decoder->completed & 1);
+        ++decoder->completed;
+        decoder->last = s;
+        return decoder->slot[s]->wait(statuses);
     } catch (...) {
         return B200JPEG_STATUS_INTERNAL_ERROR;
     }
@@ -176,7 +267,7 @@ int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats16)
 {
     if (!decoder || !stats16)
         return B200JPEG_STATUS_INVALID_PARAMETER;
-    decoder->impl->get_stats(stats16);
+    decoder->impl()->get_stats(stats16);
     return B200JPEG_STATUS_SUCCESS;
 }
 
@@ -184,14 +275,14 @@ int b200jpeg_decoder_get_stage_times(b200jpegDecoder_t decoder, float* ms, int n
 {
     if (!decoder || !ms)
         return -1;
-    return decoder->impl->get_stage_times(ms, n);
+    return decoder->impl()->get_stage_times(ms, n);
 }
 
 int64_t b200jpeg_debug_fetch(b200jpegDecoder_t decoder, int what, int image, int component, void* host_dst, size_t capacity)
 {
     if (!decoder)
         return -1;
-    return decoder->impl->debug_fetch(what, image, component, host_dst, capacity);
+    return decoder->impl()->debug_fetch(what, image, component, host_dst, capacity);
 }
 
 int b200jpeg_encoder_create(b200jpegEncoder_t* encoder, int device_id, const char* options)

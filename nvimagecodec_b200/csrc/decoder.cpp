@@ -13,6 +13,7 @@
 #include <emmintrin.h>
 #endif
 #include "../../include/b200jpeg.h"
+#include "log.h"
 
 namespace b200jpeg {
 
@@ -22,7 +23,7 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
     do {                                                                                                       \
         cudaError_t e__ = (call);                                                                              \
         if (e__ != cudaSuccess) {                                                                              \
-            std::fprintf(stderr, "b200jpeg: CUDA error %s at %s:%d\n", cudaGetErrorString(e__), __FILE__, __LINE__); \
+            log_message(kLogError, "CUDA error %s at %s:%d", cudaGetErrorString(e__), __FILE__, __LINE__); \
             return B200JPEG_STATUS_CUDA_ERROR;                                                                 \
         }                                                                                                      \
     } while (0)
@@ -82,6 +83,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
             o.dump_coef = std::atoi(value.c_str()) != 0;
         else if (name == "profile")
             o.profile = std::atoi(value.c_str()) != 0;
+        else if (name == "fast_idct")
+            o.fast_idct = std::atoi(value.c_str()) != 0;
     }
     return o;
 }
@@ -104,8 +107,11 @@ Decoder::~Decoder()
         alloc_.release(true, b->p, b->cap, streams_[0]);
     if (streams_[0])
         cudaStreamSynchronize(streams_[0]); // stream-ordered frees
-    if (ev_in_)
-        cudaEventDestroy(ev_in_);
+    for (cudaEvent_t e : ev_user_)
+        cudaEventDestroy(e);
+    for (cudaEvent_t e : ev_done_)
+        if (e)
+            cudaEventDestroy(e);
     for (cudaEvent_t e : ev_stage_)
         if (e)
             cudaEventDestroy(e);
@@ -126,7 +132,7 @@ int Decoder::init()
     cudaDeviceProp prop;
     B2J_CUDA(cudaGetDeviceProperties(&prop, device_));
     if (prop.major != 10) {
-        std::fprintf(stderr, "b200jpeg: device %d is sm_%d%d; this library only carries sm_100a code\n", device_, prop.major, prop.minor);
+        log_message(kLogWarning, "device %d is sm_%d%d; this library only carries sm_100a code", device_, prop.major, prop.minor);
         return B200JPEG_STATUS_ARCH_MISMATCH;
     }
     // option stream_priority=1: earlier groups run at higher priority, i.e. the block scheduler finishes group g's kernels
@@ -137,7 +143,8 @@ int Decoder::init()
         const int prio = opt_.stream_priority ? std::max(prio_hi, prio_lo - (kMaxGroups - 1 - g)) : prio_lo;
         B2J_CUDA(cudaStreamCreateWithPriority(&streams_[g], cudaStreamNonBlocking, prio));
     }
-    B2J_CUDA(cudaEventCreateWithFlags(&ev_in_, cudaEventDisableTiming));
+    for (cudaEvent_t& e : ev_done_)
+        B2J_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     B2J_CUDA(cudaEventCreateWithFlags(&ev_meta_, cudaEventDisableTiming));
     B2J_CUDA(cudaDeviceGetAttribute(&sm_count_, cudaDevAttrMultiProcessorCount, device_));
     if (opt_.profile)
@@ -207,6 +214,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     pre_status_.assign(n, B200JPEG_STATUS_SUCCESS);
     planned_to_batch_.clear();
     host_outs_.clear();
+    out_streams_.clear();
+    any_default_stream_ = false;
 
     PlanOptions popt;
     popt.subseq_bytes = opt_.subseq_bytes;
@@ -244,6 +253,19 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
             os.roi_w = out_w = outs[i].roi_w;
             os.roi_h = out_h = outs[i].roi_h;
         }
+        { // rows must not overlap (a short stride would make the colour kernel's stores, or the copy back, run into each other)
+            const int fmt0 = resolve_format(outs[i].format, parsed_[i].ncomp);
+            const int64_t row_bytes = int64_t(out_w) * ((fmt0 == 4 || fmt0 == 6) ? 3 : 1);
+            if (outs[i].row_stride < row_bytes) {
+                pre_status_[i] = B200JPEG_STATUS_INVALID_PARAMETER;
+                continue;
+            }
+        }
+        if (outs[i].has_stream) {
+            if (std::find(out_streams_.begin(), out_streams_.end(), outs[i].stream) == out_streams_.end())
+                out_streams_.push_back(outs[i].stream);
+        } else
+            any_default_stream_ = true;
         if (outs[i].on_host) {
             const int fmt = resolve_format(outs[i].format, parsed_[i].ncomp);
             const bool interleaved = (fmt == 4 || fmt == 6);
@@ -375,7 +397,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
         dev_.stream_words = (plan_.subseq_bits / 32 + 3) | 1; // a symbol starting in the last word reads two words past it
     if (dev_.lut_slots != cfg_lut_slots_ || dev_.stream_words != cfg_stream_words_) {
         if (huff_configure(dev_, device_, &tail_capacity_) != 0 || tail_capacity_ <= 0) {
-            std::fprintf(stderr, "b200jpeg: cannot configure the Huffman kernels: %s\n", cudaGetErrorString(cudaGetLastError()));
+            log_message(kLogError, "cannot configure the Huffman kernels: %s", cudaGetErrorString(cudaGetLastError()));
             return B200JPEG_STATUS_CUDA_ERROR;
         }
         cfg_lut_slots_ = dev_.lut_slots;
@@ -632,7 +654,8 @@ int Decoder::launch_group(int g)
         cudaEventRecord(ev_trace_[1 + 3 * g], st);
     if (g != 0)
         B2J_CUDA(cudaStreamWaitEvent(st, ev_meta_, 0)); // descriptors / tables went up on stream 0
-    B2J_CUDA(cudaStreamWaitEvent(st, ev_in_, 0));       // and whatever the caller had in flight on the output buffers
+    for (size_t u = 0; u < user_streams_.size(); ++u)
+        B2J_CUDA(cudaStreamWaitEvent(st, ev_user_[u], 0)); // and whatever the caller had in flight on the output buffers
     mark(kStageUnstuff);
     B2J_CUDA(cudaMemsetAsync(static_cast<ImageState*>(d_states_.p) + m0, 0, sizeof(ImageState) * mc, st));
     B2J_CUDA(cudaMemsetAsync(gr.dev.sync, 0, sizeof(SyncCounters), st));
@@ -642,7 +665,7 @@ int Decoder::launch_group(int g)
     mark(kStageTail);
     const int ns = launch_huff_tail(gr.dev, gr.dims, st, gr.tail_grid, opt_.tail_launches);
     if (ns < 0) {
-        std::fprintf(stderr, "b200jpeg: cooperative launch failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+        log_message(kLogError, "cooperative launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         return B200JPEG_STATUS_CUDA_ERROR;
     }
     stat_launches_ += ns;
@@ -690,6 +713,10 @@ int Decoder::launch_group(int g)
     }
     if (trace_)
         cudaEventRecord(ev_trace_[3 + 3 * g], st);
+    // the outputs' streams continue after this group (reference idiom: extensions/nvjpeg/hw_decoder.cpp:649-655)
+    B2J_CUDA(cudaEventRecord(ev_done_[g], st));
+    for (cudaStream_t us : user_streams_)
+        B2J_CUDA(cudaStreamWaitEvent(us, ev_done_[g], 0));
     return 0;
 }
 
@@ -701,8 +728,17 @@ int Decoder::begin_run(cudaStream_t user_stream, int32_t* statuses)
     for (int i = 0; i < batch_size_; ++i)
         statuses[i] = pre_status_[i];
     stat_launches_ = 0;
+    user_streams_ = out_streams_;
+    if ((any_default_stream_ || user_streams_.empty()) && std::find(user_streams_.begin(), user_streams_.end(), user_stream) == user_streams_.end())
+        user_streams_.push_back(user_stream);
+    while (ev_user_.size() < user_streams_.size()) {
+        cudaEvent_t e = nullptr;
+        B2J_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ev_user_.push_back(e);
+    }
     if (!groups_.empty())
-        B2J_CUDA(cudaEventRecord(ev_in_, user_stream));
+        for (size_t u = 0; u < user_streams_.size(); ++u)
+            B2J_CUDA(cudaEventRecord(ev_user_[u], user_streams_[u]));
     if (trace_)
         cudaEventRecord(ev_trace_[0], streams_[0]);
     return 0;
@@ -710,7 +746,10 @@ int Decoder::begin_run(cudaStream_t user_stream, int32_t* statuses)
 
 int Decoder::finish(int32_t* statuses)
 {
+    in_flight_ = false;
     const int m = int(plan_.images.size());
+    for (int i = 0; i < batch_size_; ++i)
+        statuses[i] = pre_status_[i];
     for (size_t g = 0; g < groups_.size(); ++g)
         B2J_CUDA(cudaStreamSynchronize(streams_[g]));
     if (m == 0)
@@ -722,7 +761,7 @@ int Decoder::finish(int32_t* statuses)
     for (size_t g = 0; g < groups_.size(); ++g) {
         stat_rounds_ = std::max<uint64_t>(stat_rounds_, 2 + sc[g].rounds);
         stat_redone_ += sc[g].redone;
-        if (std::getenv("B200JPEG_TRACE")) {
+        if (trace_enabled()) {
             std::fprintf(stderr, "b200jpeg: group %zu work-list rounds (items @ us since the kernel's start):", g);
             for (uint32_t r = 0; r < sc[g].rounds && r < uint32_t(kTraceRounds); ++r)
                 std::fprintf(stderr, " %u@%.1f", sc[g].round_items[r], sc[g].round_ns[r] * 1e-3);
@@ -734,7 +773,7 @@ int Decoder::finish(int32_t* statuses)
         const int bi = planned_to_batch_[i];
         if (hs[i].error || hs[i].done_blocks != plan_.images[i].total_blocks) {
             statuses[bi] = B200JPEG_STATUS_CORRUPT_STREAM;
-            if (std::getenv("B200JPEG_TRACE"))
+            if (trace_enabled())
                 std::fprintf(stderr, "b200jpeg: image %d: error flags 0x%x, %u of %u blocks\n", bi, hs[i].error, hs[i].done_blocks,
                     plan_.images[i].total_blocks);
         }
@@ -755,9 +794,11 @@ int Decoder::run(cudaStream_t user_stream, int32_t* statuses)
 }
 
 // whole decode, pipelined over the groups: while group g is on the GPU the host stages group g+1
-int Decoder::decode(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, cudaStream_t user_stream, int32_t* statuses)
+int Decoder::submit(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, cudaStream_t user_stream, int32_t* statuses)
 {
-    static const bool trace = std::getenv("B200JPEG_TRACE") != nullptr; // developer aid: host-side timeline on stderr
+    if (in_flight_)
+        return B200JPEG_STATUS_INVALID_PARAMETER; // the batch before was not waited for
+    const bool trace = trace_enabled(); // developer aid: host-side timeline on stderr
     auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t0 = trace ? now() : 0;
     if (trace && !ev_trace_[0])
@@ -769,6 +810,7 @@ int Decoder::decode(int n, const uint8_t* const* data, const size_t* sizes, cons
         return rc;
     if ((rc = begin_run(user_stream, statuses)))
         return rc;
+    in_flight_ = true;
     const double t1 = trace ? now() : 0;
     double t_stage = 0, t_launch = 0;
     stage_start();
@@ -785,8 +827,21 @@ int Decoder::decode(int n, const uint8_t* const* data, const size_t* sizes, cons
             t_launch += now() - b;
         }
     }
+    if (trace)
+        std::fprintf(stderr, "b200jpeg trace: plan %.3f ms, stage %.3f ms, launch %.3f ms (%zu groups)\n", t1 - t0, t_stage, t_launch,
+            groups_.size());
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+int Decoder::wait(int32_t* statuses)
+{
+    if (!in_flight_)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    cudaSetDevice(device_); // wait may run on a thread of its own
+    const bool trace = trace_;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t2 = trace ? now() : 0;
-    rc = finish(statuses);
+    const int rc = finish(statuses);
     if (trace) {
         for (size_t g = 0; g < groups_.size(); ++g) {
             float a = 0, b = 0, c = 0;
@@ -796,11 +851,23 @@ int Decoder::decode(int n, const uint8_t* const* data, const size_t* sizes, cons
             std::fprintf(stderr, "b200jpeg trace: group %zu (%d images): input on device %.3f, kernels done %.3f, outputs on host %.3f ms\n", g,
                 groups_[g].count, a, b, c);
         }
+        std::fprintf(stderr, "b200jpeg trace: wait %.3f ms\n", now() - t2);
     }
-    if (trace)
-        std::fprintf(stderr, "b200jpeg trace: plan %.3f ms, stage %.3f ms, launch %.3f ms, wait %.3f ms (%zu groups)\n", t1 - t0, t_stage,
-            t_launch, now() - t2, groups_.size());
     return rc;
+}
+
+int Decoder::decode(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, cudaStream_t user_stream, int32_t* statuses)
+{
+    const int rc = submit(n, data, sizes, outs, user_stream, statuses);
+    if (rc) {
+        if (in_flight_) { // something may be running: drain it before reporting the failure
+            for (cudaStream_t st : streams_)
+                cudaStreamSynchronize(st);
+            in_flight_ = false;
+        }
+        return rc;
+    }
+    return wait(statuses);
 }
 
 void Decoder::get_stats(uint64_t* s) const

@@ -30,6 +30,8 @@ struct DecoderOptions
     bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)
     bool dump_coef = false; // debug: keep dense DCT coefficients for b200jpeg_debug_fetch(what = 0)
     bool profile = false; // record CUDA events between the kernel stages (b200jpeg_decoder_get_stage_times)
+    bool fast_idct = false; // the reference's fast_idct=1 selects JDCT_IFAST (libjpeg_turbo_decoder.cpp:272-273,352), whose
+                            // pixels differ from islow and between libjpeg-turbo builds: not offered, create() refuses it
 };
 
 // Parse "name=value" tokens; tokens may be prefixed "b200jpeg_decoder:" or ":"; tokens addressed to another plugin are
@@ -111,6 +113,8 @@ class Decoder
         int format;
         int on_host;
         int roi_x = 0, roi_y = 0, roi_w = 0, roi_h = 0; // region of interest; roi_w == 0: the whole image
+        cudaStream_t stream = nullptr; // with has_stream: the stream this output is ordered on (else the call's stream)
+        bool has_stream = false;
     };
 
     // two-phase: prepare = parse + plan + H2D of the bitstreams; run = all device work of the prepared batch
@@ -118,6 +122,12 @@ class Decoder
     int run(cudaStream_t user_stream, int32_t* statuses);
     // one-shot, pipelined over the groups (host staging of group g+1 overlaps the device work of group g)
     int decode(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, cudaStream_t user_stream, int32_t* statuses);
+    // the same in two steps: submit returns when the host work is done (headers parsed, entropy-coded bytes in pinned staging,
+    // every copy and kernel enqueued, the outputs' streams made to wait for them); wait blocks until the device is done and
+    // fills in the final statuses.  The caller's bytes are not read after submit returns.
+    int submit(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, cudaStream_t user_stream, int32_t* statuses);
+    int wait(int32_t* statuses);
+    bool in_flight() const { return in_flight_; }
     void get_stats(uint64_t* s8) const;
     int get_stage_times(float* ms, int n); // per Stage, last run
     int64_t debug_fetch(int what, int image, int comp, void* dst, size_t cap);
@@ -139,7 +149,13 @@ class Decoder
     DecoderOptions opt_;
     Allocators alloc_;
     cudaStream_t streams_[kMaxGroups] = {};
-    cudaEvent_t ev_in_ = nullptr, ev_meta_ = nullptr;
+    cudaEvent_t ev_meta_ = nullptr;
+    std::vector<cudaStream_t> out_streams_;  // distinct streams named by the outputs of the planned batch
+    std::vector<cudaStream_t> user_streams_; // the streams of the running batch: out_streams_ (+ the call's stream)
+    std::vector<cudaEvent_t> ev_user_;       // one event per user stream: what the caller had in flight on the outputs
+    cudaEvent_t ev_done_[kMaxGroups] = {};   // end of each group's device work
+    bool any_default_stream_ = false;        // some output of the planned batch names no stream of its own
+    bool in_flight_ = false;
     bool trace_ = false;
     cudaEvent_t ev_trace_[1 + 3 * kMaxGroups] = {}; // B200JPEG_TRACE: start, then per group: staged, kernels done, copied back
     cudaEvent_t ev_stage_[kNumStages + 1] = {};

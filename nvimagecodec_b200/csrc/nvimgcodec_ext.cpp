@@ -12,9 +12,13 @@
 // (libjpeg_turbo_ext, priority 300); there is no CPU fallback in here.
 #include <nvimgcodec.h>
 #include <algorithm>
+#include <condition_variable>
 #include <cstring>
+#include <deque>
 #include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 #include "../../include/b200jpeg.h"
 
@@ -59,11 +63,83 @@ const uint8_t* stream_bytes(nvimgcodecIoStreamDesc_t* io, std::vector<uint8_t>& 
 // ---------------------------------------------------------------------------------------------------------------
 // Decoder
 // ---------------------------------------------------------------------------------------------------------------
+nvimgcodecProcessingStatus_t to_processing_status(int rc, int32_t res)
+{
+    if (rc != B200JPEG_STATUS_SUCCESS)
+        return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+    switch (res) {
+    case B200JPEG_STATUS_SUCCESS: return NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+    case B200JPEG_STATUS_UNSUPPORTED: return NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED;
+    case B200JPEG_STATUS_BAD_JPEG:
+    case B200JPEG_STATUS_CORRUPT_STREAM: return NVIMGCODEC_PROCESSING_STATUS_IMAGE_CORRUPTED;
+    default: return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+    }
+}
+
+// decode() hands a batch to the library (b200jpeg_decode_submit: host work done, device work enqueued and ordered onto
+// the images' streams) and returns; the statuses -- corrupt entropy-coded data is found on the device -- are collected by
+// this thread, which then reports imageReady for every sample of the batch.  Reporting from another thread after decode()
+// has returned is what the reference's own plugins do (their executor tasks call imageReady,
+// extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:444-490).  Two batches can be in flight, so the host work of batch
+// k + 1 (canDecode, header parse, staging) overlaps the kernels of batch k.
 struct DecoderState
 {
     const nvimgcodecFrameworkDesc_t* fw = nullptr;
     const nvimgcodecExecutionParams_t* exec = nullptr;
     b200jpegDecoder_t dec = nullptr;
+    bool async = true;
+
+    struct Pending
+    {
+        std::vector<nvimgcodecImageDesc_t*> imgs;
+    };
+    std::mutex mu;
+    std::condition_variable cv;
+    std::deque<Pending> queue; // batches submitted and not yet reported (at most two)
+    bool stop = false;
+    std::thread completer;
+
+    void complete_one(Pending& p)
+    {
+        const int n = int(p.imgs.size());
+        std::vector<int32_t> res(n > 0 ? n : 1, B200JPEG_STATUS_INTERNAL_ERROR);
+        const int rc = b200jpeg_decode_wait(dec, res.data());
+        if (rc != B200JPEG_STATUS_SUCCESS)
+            log_msg(fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR, kDecoderId, std::string("decode batch failed: ") + b200jpeg_status_string(rc));
+        for (int i = 0; i < n; ++i)
+            p.imgs[i]->imageReady(p.imgs[i]->instance, to_processing_status(rc, res[i]));
+    }
+    void run()
+    {
+        if (exec)
+            cudaSetDevice(exec->device_id);
+        for (;;) {
+            Pending* p = nullptr;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return stop || !queue.empty(); });
+                if (queue.empty())
+                    return; // stop requested and nothing left
+                p = &queue.front(); // stays in the queue until it is reported: the queue's length is what is in flight
+            }
+            complete_one(*p);
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                queue.pop_front();
+            }
+            cv.notify_all();
+        }
+    }
+    void shutdown()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            stop = true;
+        }
+        cv.notify_all();
+        if (completer.joinable())
+            completer.join();
+    }
 };
 
 nvimgcodecProcessingStatus_t check_target(const nvimgcodecImageInfo_t& info, const b200jpegStreamInfo_t& si,
@@ -130,6 +206,7 @@ nvimgcodecStatus_t dec_can_decode(nvimgcodecDecoder_t decoder, nvimgcodecProcess
     try {
         std::vector<uint8_t> storage;
         for (int i = 0; i < n; ++i) {
+            storage.clear();
             status[i] = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
             nvimgcodecJpegImageInfo_t jinfo{NVIMGCODEC_STRUCTURE_TYPE_JPEG_IMAGE_INFO, sizeof(nvimgcodecJpegImageInfo_t), nullptr};
             nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), &jinfo};
@@ -141,7 +218,10 @@ nvimgcodecStatus_t dec_can_decode(nvimgcodecDecoder_t decoder, nvimgcodecProcess
             size_t size = 0;
             const uint8_t* data = stream_bytes(css[i]->io_stream, storage, size);
             b200jpegStreamInfo_t si;
-            if (!data || b200jpeg_parse_header(data, size, &si) != B200JPEG_STATUS_SUCCESS) {
+            const bool parsed = data && b200jpeg_parse_header(data, size, &si) == B200JPEG_STATUS_SUCCESS;
+            if (data && storage.empty() && css[i]->io_stream->unmap) // a mapping is handed back as soon as the header is read
+                css[i]->io_stream->unmap(css[i]->io_stream->instance, const_cast<uint8_t*>(data), size);
+            if (!parsed) {
                 status[i] = NVIMGCODEC_PROCESSING_STATUS_FAIL;
                 continue;
             }
@@ -180,48 +260,62 @@ nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, nvimgcodecCodeStreamD
         std::vector<const uint8_t*> data(n, nullptr);
         std::vector<size_t> sizes(n, 0);
         std::vector<b200jpegOutput_t> outs(n);
-        cudaStream_t user_stream = nullptr;
         for (int i = 0; i < n; ++i) {
             data[i] = stream_bytes(css[i]->io_stream, storage[i], sizes[i]);
             nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
             imgs[i]->getImageInfo(imgs[i]->instance, &info);
+            outs[i] = b200jpegOutput_t{};
             outs[i].buffer = info.buffer;
             outs[i].row_stride = int64_t(info.plane_info[0].row_stride);
             outs[i].format = int32_t(info.sample_format);
             outs[i].on_host = info.buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST ? 1 : 0;
-            outs[i].roi_x = outs[i].roi_y = outs[i].roi_width = outs[i].roi_height = 0;
             if (info.region.ndim == 2) {
                 outs[i].roi_x = info.region.start[1];
                 outs[i].roi_y = info.region.start[0];
                 outs[i].roi_width = info.region.end[1] - info.region.start[1];
                 outs[i].roi_height = info.region.end[0] - info.region.start[0];
             }
-            if (i == 0)
-                user_stream = info.cuda_stream;
+            outs[i].cuda_stream = info.cuda_stream; // every distinct stream is waited for, and made to wait for the decode
+            outs[i].has_cuda_stream = 1;
             if (!data[i]) {
                 static const uint8_t empty[2] = {0, 0};
                 data[i] = empty;
                 sizes[i] = 0;
             }
         }
-        std::vector<int32_t> res(n, B200JPEG_STATUS_INTERNAL_ERROR);
-        const int rc = b200jpeg_decode_batch(st->dec, n, data.data(), sizes.data(), outs.data(), user_stream, res.data());
-        // b200jpeg_decode_batch returns with the device work complete, so every user stream may consume the outputs
-        for (int i = 0; i < n; ++i) {
-            nvimgcodecProcessingStatus_t ps = NVIMGCODEC_PROCESSING_STATUS_FAIL;
-            if (rc == B200JPEG_STATUS_SUCCESS) {
-                switch (res[i]) {
-                case B200JPEG_STATUS_SUCCESS: ps = NVIMGCODEC_PROCESSING_STATUS_SUCCESS; break;
-                case B200JPEG_STATUS_UNSUPPORTED: ps = NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED; break;
-                case B200JPEG_STATUS_BAD_JPEG:
-                case B200JPEG_STATUS_CORRUPT_STREAM: ps = NVIMGCODEC_PROCESSING_STATUS_IMAGE_CORRUPTED; break;
-                default: ps = NVIMGCODEC_PROCESSING_STATUS_FAIL; break;
-                }
+        auto unmap_all = [&] { // after submit the bytes sit in the library's pinned staging
+            for (int i = 0; i < n; ++i)
+                if (css[i]->io_stream && css[i]->io_stream->unmap && storage[i].empty() && sizes[i])
+                    css[i]->io_stream->unmap(css[i]->io_stream->instance, const_cast<uint8_t*>(data[i]), sizes[i]);
+        };
+        std::vector<int32_t> res(n > 0 ? n : 1, B200JPEG_STATUS_INTERNAL_ERROR);
+        int rc;
+        if (st->async) {
+            {
+                std::unique_lock<std::mutex> lk(st->mu);
+                st->cv.wait(lk, [&] { return st->queue.size() < 2; }); // the library takes two batches in flight
             }
-            if (css[i]->io_stream && css[i]->io_stream->unmap && storage[i].empty() && sizes[i])
-                css[i]->io_stream->unmap(css[i]->io_stream->instance, const_cast<uint8_t*>(data[i]), sizes[i]);
-            report(i, ps);
+            rc = b200jpeg_decode_submit(st->dec, n, data.data(), sizes.data(), outs.data(), nullptr, res.data());
+            unmap_all();
+            if (rc == B200JPEG_STATUS_SUCCESS) {
+                DecoderState::Pending p;
+                p.imgs.assign(imgs, imgs + n);
+                for (int i = 0; i < n; ++i)
+                    reported[i] = 1; // from here on the completion thread reports
+                {
+                    std::lock_guard<std::mutex> lk(st->mu);
+                    st->queue.push_back(std::move(p));
+                }
+                st->cv.notify_all();
+                return NVIMGCODEC_STATUS_SUCCESS;
+            }
+        } else {
+            rc = b200jpeg_decode_batch(st->dec, n, data.data(), sizes.data(), outs.data(), nullptr, res.data());
+            unmap_all();
+            // b200jpeg_decode_batch returns with the device work complete
         }
+        for (int i = 0; i < n; ++i)
+            report(i, to_processing_status(rc, res[i]));
         if (rc != B200JPEG_STATUS_SUCCESS) {
             log_msg(st->fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR, kDecoderId, std::string("decode batch failed: ") + b200jpeg_status_string(rc));
             return rc == B200JPEG_STATUS_CUDA_ERROR ? NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR : NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
@@ -240,6 +334,7 @@ nvimgcodecStatus_t dec_destroy(nvimgcodecDecoder_t decoder)
     auto* st = reinterpret_cast<DecoderState*>(decoder);
     if (!st)
         return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    st->shutdown(); // reports whatever is still in flight
     if (st->dec)
         b200jpeg_decoder_destroy(st->dec);
     delete st;
@@ -441,8 +536,17 @@ struct Extension
     nvimgcodecEncoderDesc_t enc_desc;
     bool dec_registered = false, enc_registered = false;
 
+    static void lib_log(void* ctx, int severity, const char* message)
+    {
+        auto* fw = static_cast<const nvimgcodecFrameworkDesc_t*>(ctx);
+        log_msg(fw, severity >= 2 ? NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR : severity == 1 ? NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_WARNING
+                                                                                             : NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_INFO,
+            "b200jpeg", message);
+    }
+
     explicit Extension(const nvimgcodecFrameworkDesc_t* f) : fw(f)
     {
+        b200jpeg_set_log_callback(&Extension::lib_log, const_cast<nvimgcodecFrameworkDesc_t*>(fw));
         dec_desc = nvimgcodecDecoderDesc_t{NVIMGCODEC_STRUCTURE_TYPE_DECODER_DESC, sizeof(nvimgcodecDecoderDesc_t), nullptr, this, kDecoderId,
             "jpeg", NVIMGCODEC_BACKEND_KIND_GPU_ONLY, dec_create, dec_destroy, dec_can_decode, dec_decode};
         if (fw->registerDecoder(fw->instance, &dec_desc, kPriority) == NVIMGCODEC_STATUS_SUCCESS)
@@ -454,6 +558,7 @@ struct Extension
     }
     ~Extension()
     {
+        b200jpeg_set_log_callback(nullptr, nullptr);
         if (enc_registered)
             fw->unregisterEncoder(fw->instance, &enc_desc);
         if (dec_registered)
@@ -491,12 +596,18 @@ nvimgcodecStatus_t dec_create(void* instance, nvimgcodecDecoder_t* decoder, cons
     st->fw = ext->fw;
     st->exec = exec;
     const int rc = b200jpeg_decoder_create(&st->dec, exec->device_id, options ? options : "");
-    if (rc != B200JPEG_STATUS_SUCCESS) {
+    if (rc != B200JPEG_STATUS_SUCCESS) { // the framework then treats the decoder as absent and falls back (src/image_decoder.cpp:29-36,62-68)
         log_msg(ext->fw, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_WARNING, kDecoderId, std::string("decoder unavailable: ") + b200jpeg_status_string(rc));
+        if (rc == B200JPEG_STATUS_UNSUPPORTED)
+            return NVIMGCODEC_STATUS_EXTENSION_IMPLEMENTATION_NOT_SUPPORTED; // an option asks for what is not offered (fast_idct=1)
         return rc == B200JPEG_STATUS_ARCH_MISMATCH ? NVIMGCODEC_STATUS_EXTENSION_ARCH_MISMATCH : NVIMGCODEC_STATUS_EXTENSION_CUDA_CALL_ERROR;
     }
     const b200jpegAllocators_t al = exec_allocators(exec);
     b200jpeg_decoder_set_allocators(st->dec, &al);
+    // "async=0" (optionally prefixed like every option): decode() returns only when the device is done
+    st->async = !(options && std::strstr(options, "async=0"));
+    if (st->async)
+        st->completer = std::thread([p = st.get()] { p->run(); });
     *decoder = reinterpret_cast<nvimgcodecDecoder_t>(st.release());
     return NVIMGCODEC_STATUS_SUCCESS;
 }

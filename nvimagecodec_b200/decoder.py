@@ -90,7 +90,7 @@ class Decoder:
             pass
 
     # ---- low level: caller-provided buffers -------------------------------------------------------------------
-    def _outputs(self, buffers, strides, formats, on_host, rois=None):
+    def _outputs(self, buffers, strides, formats, on_host, rois=None, streams=None):
         n = len(buffers)
         outs = (_capi.Output * n)()
         for i in range(n):
@@ -98,20 +98,46 @@ class Decoder:
             outs[i].row_stride = strides[i]
             outs[i].format = formats[i]
             outs[i].on_host = int(on_host)
+            if streams is not None and streams[i] is not None:
+                outs[i].cuda_stream = streams[i]
+                outs[i].has_cuda_stream = 1
             if rois is not None and rois[i]:
                 outs[i].roi_x, outs[i].roi_y, outs[i].roi_width, outs[i].roi_height = rois[i]
         return outs
 
-    def decode_into(self, datas, buffers, strides, formats, on_host=False, cuda_stream=0, rois=None):
+    def decode_into(self, datas, buffers, strides, formats, on_host=False, cuda_stream=0, rois=None, streams=None):
         """decode a batch into raw pointers (device pointers, or host pointers with on_host=True) -> status list.
         rois: per image None or (x, y, width, height): the buffer receives that region of the image only"""
         n = len(datas)
         st = (C.c_int32 * n)()
         rc = _capi.lib().b200jpeg_decode_batch(self._h, n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
-                                               self._outputs(buffers, strides, formats, on_host, rois), C.c_void_p(cuda_stream), st)
+                                               self._outputs(buffers, strides, formats, on_host, rois, streams), C.c_void_p(cuda_stream), st)
         if rc != 0:
             raise RuntimeError("b200jpeg_decode_batch: %s" % _capi.status_string(rc))
         self.last_statuses = list(st)
+        return self.last_statuses
+
+    def submit(self, datas, buffers, strides, formats, on_host=False, cuda_stream=0, rois=None, streams=None):
+        """first half of decode_into: returns when the host work is done and the device work is enqueued (up to two batches
+        in flight); -> the statuses the host already knows"""
+        n = len(datas)
+        st = (C.c_int32 * n)()
+        rc = _capi.lib().b200jpeg_decode_submit(self._h, n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
+                                                self._outputs(buffers, strides, formats, on_host, rois, streams), C.c_void_p(cuda_stream), st)
+        if rc != 0:
+            raise RuntimeError("b200jpeg_decode_submit: %s" % _capi.status_string(rc))
+        self._pending = getattr(self, "_pending", [])
+        self._pending.append(n)
+        return list(st)
+
+    def wait(self):
+        """second half: blocks until the oldest submitted batch is done -> final status list"""
+        n = self._pending.pop(0)
+        st = (C.c_int32 * max(n, 1))()
+        rc = _capi.lib().b200jpeg_decode_wait(self._h, st)
+        if rc != 0:
+            raise RuntimeError("b200jpeg_decode_wait: %s" % _capi.status_string(rc))
+        self.last_statuses = list(st)[:n]
         return self.last_statuses
 
     def prepare(self, datas, buffers, strides, formats, on_host=False):
@@ -169,6 +195,11 @@ class Decoder:
             try:
                 info = _capi.parse_header(d)
             except ValueError:
+                tensors.append(None)
+                continue
+            # nothing is allocated for a stream the decoder will not take (the header is untrusted: a 65535 x 65535 SOF
+            # must not turn into a 12.9 GB allocation)
+            if not info.supported or info.width * info.height > (1 << 28):
                 tensors.append(None)
                 continue
             if fmt in (_capi.FMT_I_RGB, _capi.FMT_I_BGR):
