@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_struct_layouts_match_header():
-    assert C.sizeof(_capi.Output) == 40
+    assert C.sizeof(_capi.Output) == 56
     assert C.sizeof(_capi.StreamInfo) == 72
     assert C.sizeof(_capi.EncodeInput) == 48
 
