@@ -169,6 +169,23 @@ B200JPEG_API int b200jpeg_decode_submit(b200jpegDecoder_t decoder, int batch_siz
     const b200jpegOutput_t* outputs, void* user_stream, int32_t* statuses);
 B200JPEG_API int b200jpeg_decode_wait(b200jpegDecoder_t decoder, int32_t* statuses);
 
+/* ---- one batch over several GPUs of a box (reference hook: nvimgcodecExecutionParams_t::device_id, one decoder per
+ * device, include/nvimgcodec.h:845).  Images are independent, so the batch is dealt to the devices -- greedy
+ * longest-processing-time on an estimated cost of 8 x compressed bytes + pixels, the same deal on every caller without
+ * communication -- and every device decodes its share with its own decoder, host thread, streams and pinned staging.
+ * There is no collective: outputs stay on the GPU that decoded them (or go to host memory with on_host). ---- */
+typedef struct b200jpegMultiDecoder* b200jpegMultiDecoder_t;
+/* device_of_image[i] = index (0 .. num_devices-1) of the device that gets image i.  widths/heights may be NULL (cost =
+ * compressed bytes only).  Pure host function. */
+B200JPEG_API int b200jpeg_shard_batch(int batch_size, const size_t* sizes, const int32_t* widths, const int32_t* heights, int num_devices,
+    int32_t* device_of_image);
+B200JPEG_API int b200jpeg_multi_decoder_create(b200jpegMultiDecoder_t* decoder, int num_devices, const int* device_ids, const char* options);
+B200JPEG_API int b200jpeg_multi_decoder_destroy(b200jpegMultiDecoder_t decoder);
+/* outputs[i].buffer must live on device device_ids[device_of_image[i]] (or in host memory with on_host).  Every device's
+ * share runs concurrently (one host thread each); returns when all are done; statuses[i] as for b200jpeg_decode_batch. */
+B200JPEG_API int b200jpeg_multi_decode_batch(b200jpegMultiDecoder_t decoder, int batch_size, const uint8_t* const* data, const size_t* sizes,
+    const b200jpegOutput_t* outputs, const int32_t* device_of_image, int32_t* statuses);
+
 /* Two-phase variant used to time the device work with inputs already resident in HBM:
  * prepare = parse + table building + H2D of bitstreams/descriptors; run = every kernel of the decode, nothing else. */
 B200JPEG_API int b200jpeg_decode_prepare(b200jpegDecoder_t decoder, int batch_size, const uint8_t* const* data, const size_t* sizes,

@@ -10,7 +10,7 @@ from ._capi import EXT_DIR, EXT_PATH, LIB_PATH, parse_header, status_string  # n
 
 
 def __getattr__(name):
-    if name in ("Decoder", "Image"):
+    if name in ("Decoder", "Image", "MultiDeviceDecoder"):
         from . import decoder
         return getattr(decoder, name)
     if name == "Encoder":

@@ -40,7 +40,8 @@ class EncodeInput(C.Structure):
                 ("on_host", C.c_int32), ("subsampling", C.c_int32), ("quality", C.c_int32), ("restart_interval", C.c_int32)]
 
 
-EXPORTS = ["b200jpeg_version", "b200jpeg_status_string", "b200jpeg_set_log_callback", "b200jpeg_decode_submit", "b200jpeg_decode_wait", "b200jpeg_parse_header", "b200jpeg_decoder_create", "b200jpeg_decoder_destroy",
+EXPORTS = ["b200jpeg_version", "b200jpeg_status_string", "b200jpeg_set_log_callback", "b200jpeg_decode_submit", "b200jpeg_decode_wait", "b200jpeg_shard_batch",
+           "b200jpeg_multi_decoder_create", "b200jpeg_multi_decoder_destroy", "b200jpeg_multi_decode_batch", "b200jpeg_parse_header", "b200jpeg_decoder_create", "b200jpeg_decoder_destroy",
            "b200jpeg_decode_batch", "b200jpeg_decode_prepare", "b200jpeg_decode_run", "b200jpeg_decoder_get_stats", "b200jpeg_decoder_get_stage_times", "b200jpeg_debug_fetch",
            "b200jpeg_encoder_create", "b200jpeg_encoder_destroy", "b200jpeg_encode_batch", "b200jpeg_encoder_get_stats",
            "b200jpeg_decoder_set_allocators", "b200jpeg_encoder_set_allocators"]
@@ -65,6 +66,11 @@ def lib():
                                             C.c_void_p, C.POINTER(C.c_int32)]
         L.b200jpeg_decode_submit.argtypes = L.b200jpeg_decode_batch.argtypes
         L.b200jpeg_decode_wait.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+        L.b200jpeg_shard_batch.argtypes = [C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, C.POINTER(C.c_int32)]
+        L.b200jpeg_multi_decoder_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_int), C.c_char_p]
+        L.b200jpeg_multi_decoder_destroy.argtypes = [C.c_void_p]
+        L.b200jpeg_multi_decode_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(Output),
+                                                  C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.b200jpeg_decode_prepare.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(Output),
                                               C.POINTER(C.c_int32)]
         L.b200jpeg_decode_run.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]

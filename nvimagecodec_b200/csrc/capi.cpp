@@ -1,7 +1,13 @@
 // capi.cpp -- extern "C" boundary of libb200jpeg.so (include/b200jpeg.h).
 #include <cuda_runtime_api.h>
+#include <algorithm>
 #include <atomic>
+#include <condition_variable>
+#include <mutex>
+#include <numeric>
+#include <thread>
 #include <cstring>
+#include <memory>
 #include <new>
 #include <vector>
 #include "../../include/b200jpeg.h"
@@ -29,6 +35,28 @@ struct b200jpegDecoder
         delete slot[0];
         delete slot[1];
     }
+};
+
+// One decoder and one persistent host thread per device; a call hands every thread its share of the batch and waits.
+struct b200jpegMultiDecoder
+{
+    struct Worker
+    {
+        b200jpegDecoder* dec = nullptr;
+        std::thread th;
+        std::vector<const uint8_t*> data;
+        std::vector<size_t> sizes;
+        std::vector<b200jpegOutput_t> outs;
+        std::vector<int32_t> statuses;
+        std::vector<int> index; // position in the caller's batch
+        int rc = 0;
+    };
+    std::vector<Worker> workers;
+    std::mutex mu;
+    std::condition_variable cv;
+    uint64_t epoch = 0;
+    int pending = 0;
+    bool stop = false;
 };
 
 static int make_slot(b200jpegDecoder* d, int i)
@@ -263,6 +291,27 @@ int b200jpeg_decode_wait(b200jpegDecoder_t decoder, int32_t* statuses)
     }
 }
 
+// ---- multi-device ----
+int b200jpeg_shard_batch(int n, const size_t* sizes, const int32_t* widths, const int32_t* heights, int num_devices, int32_t* device_of_image)
+{
+    if (n < 0 || num_devices < 1 || (n > 0 && (!sizes || !device_of_image)))
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    // Huffman work scales with the compressed bytes (about 8 symbols per byte-pixel), reconstruction with the pixels
+    std::vector<uint64_t> cost(n);
+    for (int i = 0; i < n; ++i)
+        cost[i] = 8ull * sizes[i] + (widths && heights ? uint64_t(widths[i]) * uint64_t(heights[i]) : 0ull);
+    std::vector<int> order(n);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cost[a] > cost[b]; });
+    std::vector<uint64_t> load(num_devices, 0);
+    for (int i : order) {
+        const int r = int(std::min_element(load.begin(), load.end()) - load.begin());
+        device_of_image[i] = r;
+        load[r] += cost[i];
+    }
+    return B200JPEG_STATUS_SUCCESS;
+}
+
 int b200jpeg_decoder_get_stats(b200jpegDecoder_t decoder, uint64_t* stats16)
 {
     if (!decoder || !stats16)
@@ -283,6 +332,123 @@ int64_t b200jpeg_debug_fetch(b200jpegDecoder_t decoder, int what, int image, int
     if (!decoder)
         return -1;
     return decoder->impl()->debug_fetch(what, image, component, host_dst, capacity);
+}
+
+int b200jpeg_multi_decoder_create(b200jpegMultiDecoder_t* out, int num_devices, const int* device_ids, const char* options)
+{
+    if (!out || num_devices < 1 || !device_ids)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    *out = nullptr;
+    try {
+        std::unique_ptr<b200jpegMultiDecoder> md(new b200jpegMultiDecoder());
+        md->workers.resize(num_devices);
+        for (int w = 0; w < num_devices; ++w) {
+            const int rc = b200jpeg_decoder_create(&md->workers[w].dec, device_ids[w], options);
+            if (rc != B200JPEG_STATUS_SUCCESS) {
+                for (auto& wk : md->workers)
+                    if (wk.dec)
+                        b200jpeg_decoder_destroy(wk.dec);
+                return rc;
+            }
+        }
+        b200jpegMultiDecoder* m = md.get();
+        for (int w = 0; w < num_devices; ++w)
+            m->workers[w].th = std::thread([m, w] {
+                uint64_t seen = 0;
+                b200jpegMultiDecoder::Worker& me = m->workers[w];
+                for (;;) {
+                    {
+                        std::unique_lock<std::mutex> lk(m->mu);
+                        m->cv.wait(lk, [&] { return m->stop || m->epoch != seen; });
+                        if (m->stop)
+                            return;
+                        seen = m->epoch;
+                    }
+                    const int n = int(me.index.size());
+                    me.rc = n ? b200jpeg_decode_batch(me.dec, n, me.data.data(), me.sizes.data(), me.outs.data(), nullptr, me.statuses.data())
+                              : B200JPEG_STATUS_SUCCESS;
+                    {
+                        std::lock_guard<std::mutex> lk(m->mu);
+                        --m->pending;
+                    }
+                    m->cv.notify_all();
+                }
+            });
+        *out = md.release();
+    } catch (const std::bad_alloc&) {
+        return B200JPEG_STATUS_ALLOC_FAILED;
+    } catch (...) {
+        return B200JPEG_STATUS_INTERNAL_ERROR;
+    }
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+int b200jpeg_multi_decoder_destroy(b200jpegMultiDecoder_t md)
+{
+    if (!md)
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    {
+        std::lock_guard<std::mutex> lk(md->mu);
+        md->stop = true;
+    }
+    md->cv.notify_all();
+    for (auto& w : md->workers) {
+        if (w.th.joinable())
+            w.th.join();
+        if (w.dec)
+            b200jpeg_decoder_destroy(w.dec);
+    }
+    delete md;
+    return B200JPEG_STATUS_SUCCESS;
+}
+
+int b200jpeg_multi_decode_batch(b200jpegMultiDecoder_t md, int n, const uint8_t* const* data, const size_t* sizes, const b200jpegOutput_t* outputs,
+    const int32_t* device_of_image, int32_t* statuses)
+{
+    if (!md || n < 0 || (n > 0 && (!data || !sizes || !outputs || !device_of_image || !statuses)))
+        return B200JPEG_STATUS_INVALID_PARAMETER;
+    try {
+        const int nd = int(md->workers.size());
+        for (auto& w : md->workers) {
+            w.data.clear();
+            w.sizes.clear();
+            w.outs.clear();
+            w.index.clear();
+        }
+        for (int i = 0; i < n; ++i) {
+            if (device_of_image[i] < 0 || device_of_image[i] >= nd)
+                return B200JPEG_STATUS_INVALID_PARAMETER;
+            auto& w = md->workers[device_of_image[i]];
+            w.data.push_back(data[i]);
+            w.sizes.push_back(sizes[i]);
+            w.outs.push_back(outputs[i]);
+            w.index.push_back(i);
+        }
+        for (auto& w : md->workers)
+            w.statuses.assign(std::max<size_t>(1, w.index.size()), B200JPEG_STATUS_INTERNAL_ERROR);
+        {
+            std::lock_guard<std::mutex> lk(md->mu);
+            md->pending = nd;
+            ++md->epoch;
+        }
+        md->cv.notify_all();
+        {
+            std::unique_lock<std::mutex> lk(md->mu);
+            md->cv.wait(lk, [&] { return md->pending == 0; });
+        }
+        int rc = B200JPEG_STATUS_SUCCESS;
+        for (auto& w : md->workers) {
+            if (w.rc != B200JPEG_STATUS_SUCCESS)
+                rc = w.rc;
+            for (size_t k = 0; k < w.index.size(); ++k)
+                statuses[w.index[k]] = w.rc == B200JPEG_STATUS_SUCCESS ? w.statuses[k] : w.rc;
+        }
+        return rc;
+    } catch (const std::bad_alloc&) {
+        return B200JPEG_STATUS_ALLOC_FAILED;
+    } catch (...) {
+        return B200JPEG_STATUS_INTERNAL_ERROR;
+    }
 }
 
 int b200jpeg_encoder_create(b200jpegEncoder_t* encoder, int device_id, const char* options)

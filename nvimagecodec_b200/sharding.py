@@ -22,3 +22,17 @@ def shard_batch(costs, world_size):
 
 def my_shard(costs, world_size, rank):
     return shard_batch(costs, world_size)[rank]
+
+
+def shard_batch_native(jpeg_sizes, widths, heights, num_devices):
+    """the library's deal (b200jpeg_shard_batch, the one b200jpeg_multi_decode_batch callers use) -> device index per image;
+    the same greedy partition as shard_batch"""
+    import ctypes as C
+    from . import _capi
+    n = len(jpeg_sizes)
+    out = (C.c_int32 * max(n, 1))()
+    rc = _capi.lib().b200jpeg_shard_batch(n, (C.c_size_t * max(n, 1))(*jpeg_sizes), (C.c_int32 * max(n, 1))(*widths),
+                                          (C.c_int32 * max(n, 1))(*heights), num_devices, out)
+    if rc != 0:
+        raise RuntimeError("b200jpeg_shard_batch: %s" % _capi.status_string(rc))
+    return list(out)[:n]

@@ -223,7 +223,7 @@ REFH_API int refh_get_info(void* h, const unsigned char* data, size_t size, int*
 //   status_out  : per-sample nvimgcodecProcessingStatus_t of the last repetition
 static int decode_impl(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers, const int* widths,
     const int* heights, const int* sample_formats, const int64_t* row_strides, int buffer_kind, void* cuda_stream, int reps,
-    unsigned int* status_out, double* seconds, const int* rois)
+    unsigned int* status_out, double* seconds, const int* rois, const int* orient = nullptr, int apply_exif = 0)
 {
     auto* d = (Decoder*)hd;
     auto inst = d->s->instance;
@@ -252,11 +252,18 @@ static int decode_impl(void* hd, int n, const unsigned char** data, const size_t
             info.region.end[0] = rois[4 * i + 1] + rois[4 * i + 3];
             info.region.end[1] = rois[4 * i] + rois[4 * i + 2];
         }
+        if (orient) { // what the Python layer does: the code stream's EXIF orientation goes into the target's info (python/decoder.cpp:190-205)
+            info.orientation.struct_type = NVIMGCODEC_STRUCTURE_TYPE_ORIENTATION;
+            info.orientation.struct_size = sizeof(nvimgcodecOrientation_t);
+            info.orientation.rotated = orient[3 * i];
+            info.orientation.flip_x = orient[3 * i + 1];
+            info.orientation.flip_y = orient[3 * i + 2];
+        }
         if (nvimgcodecImageCreate(inst, &img[i], &info) != NVIMGCODEC_STATUS_SUCCESS)
             rc = -2;
     }
     nvimgcodecDecodeParams_t params{NVIMGCODEC_STRUCTURE_TYPE_DECODE_PARAMS, sizeof(nvimgcodecDecodeParams_t), 0};
-    params.apply_exif_orientation = 0;
+    params.apply_exif_orientation = apply_exif;
     params.enable_roi = rois ? 1 : 0;
     for (int r = 0; r < reps && rc == 0; ++r) {
         double t0 = now_s();
@@ -304,6 +311,147 @@ REFH_API int refh_decode_roi(void* hd, int n, const unsigned char** data, const 
 {
     return decode_impl(hd, n, data, sizes, buffers, widths, heights, sample_formats, row_strides, buffer_kind, cuda_stream, reps, status_out,
         seconds, rois);
+}
+
+// The same with an EXIF orientation per image (orient: rotated degrees counter-clockwise, flip_x, flip_y) and
+// nvimgcodecDecodeParams_t::apply_exif_orientation; widths / heights describe the target buffers (swapped for 90 / 270).
+REFH_API int refh_decode_ex(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers, const int* widths,
+    const int* heights, const int* sample_formats, const int64_t* row_strides, int buffer_kind, void* cuda_stream, int reps,
+    unsigned int* status_out, double* seconds, const int* rois, const int* orient, int apply_exif)
+{
+    return decode_impl(hd, n, data, sizes, buffers, widths, heights, sample_formats, row_strides, buffer_kind, cuda_stream, reps, status_out,
+        seconds, rois, orient, apply_exif);
+}
+
+// Two decode calls in flight: batch A and batch B (same decoder) are submitted back to back, then both futures are waited
+// for -- the pattern of a loader that keeps one batch ahead.  seconds[0] = wall time of submit A .. both ready.
+REFH_API int refh_decode_pipelined(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers_a, void** buffers_b,
+    const int* widths, const int* heights, const int* sample_formats, const int64_t* row_strides, int buffer_kind, void* cuda_stream,
+    int rounds, unsigned int* status_out, double* seconds)
+{
+    auto* d = (Decoder*)hd;
+    auto inst = d->s->instance;
+    std::vector<nvimgcodecCodeStream_t> cs(n, nullptr);
+    std::vector<nvimgcodecImage_t> img[2];
+    img[0].assign(n, nullptr);
+    img[1].assign(n, nullptr);
+    int rc = 0;
+    for (int i = 0; i < n && rc == 0; ++i) {
+        if (nvimgcodecCodeStreamCreateFromHostMem(inst, &cs[i], data[i], sizes[i]) != NVIMGCODEC_STATUS_SUCCESS) {
+            rc = -1;
+            break;
+        }
+        for (int k = 0; k < 2; ++k) {
+            nvimgcodecImageInfo_t info;
+            fill_image_info(info, widths[i], heights[i], sample_formats[i], row_strides[i], buffer_kind, (k ? buffers_b : buffers_a)[i], cuda_stream, 3);
+            if (nvimgcodecImageCreate(inst, &img[k][i], &info) != NVIMGCODEC_STATUS_SUCCESS)
+                rc = -2;
+        }
+    }
+    nvimgcodecDecodeParams_t params{NVIMGCODEC_STRUCTURE_TYPE_DECODE_PARAMS, sizeof(nvimgcodecDecodeParams_t), 0};
+    if (rc == 0) {
+        // steady state: the future of batch r is waited for after batch r + 1 has been handed in
+        double t0 = now_s();
+        nvimgcodecFuture_t fut[2] = {nullptr, nullptr};
+        for (int r = 0; r < rounds && rc == 0; ++r) {
+            const int k = r & 1;
+            if (nvimgcodecDecoderDecode(d->dec, cs.data(), img[k].data(), n, &params, &fut[k]) != NVIMGCODEC_STATUS_SUCCESS) {
+                rc = -3;
+                break;
+            }
+            if (r > 0) {
+                nvimgcodecFutureWaitForAll(fut[k ^ 1]);
+                size_t sz = 0;
+                std::vector<nvimgcodecProcessingStatus_t> st(n, 0);
+                nvimgcodecFutureGetProcessingStatus(fut[k ^ 1], st.data(), &sz);
+                for (int i = 0; i < n; ++i)
+                    if (status_out && (r == 1 || st[i] != NVIMGCODEC_PROCESSING_STATUS_SUCCESS))
+                        status_out[i] = st[i];
+                nvimgcodecFutureDestroy(fut[k ^ 1]);
+                fut[k ^ 1] = nullptr;
+            }
+        }
+        const int last = (rounds - 1) & 1;
+        if (fut[last]) {
+            nvimgcodecFutureWaitForAll(fut[last]);
+            size_t sz = 0;
+            std::vector<nvimgcodecProcessingStatus_t> st(n, 0);
+            nvimgcodecFutureGetProcessingStatus(fut[last], st.data(), &sz);
+            for (int i = 0; i < n; ++i)
+                if (status_out && (rounds == 1 || st[i] != NVIMGCODEC_PROCESSING_STATUS_SUCCESS))
+                    status_out[i] = st[i];
+            nvimgcodecFutureDestroy(fut[last]);
+        }
+        if (buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_DEVICE)
+            cudaStreamSynchronize((cudaStream_t)cuda_stream);
+        if (seconds)
+            seconds[0] = now_s() - t0;
+    }
+    for (int i = 0; i < n; ++i) {
+        for (int k = 0; k < 2; ++k)
+            if (img[k][i])
+                nvimgcodecImageDestroy(img[k][i]);
+        if (cs[i])
+            nvimgcodecCodeStreamDestroy(cs[i]);
+    }
+    return rc;
+}
+
+// nvimgcodecDecoderCanDecode with every field of the target's image info spelled out: the rejection matrix of a plugin's
+// canDecode (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:118-173).  orient: 3 ints per image or NULL.
+REFH_API int refh_can_decode_ex(void* hd, int n, const unsigned char** data, const size_t* sizes, const int* widths, const int* heights,
+    const int* sample_formats, const int* num_planes, const int* num_channels, const int* sample_types, const int* orient, int apply_exif,
+    int buffer_kind, int force_format, unsigned int* status_out)
+{
+    auto* d = (Decoder*)hd;
+    auto inst = d->s->instance;
+    std::vector<nvimgcodecCodeStream_t> cs(n, nullptr);
+    std::vector<nvimgcodecImage_t> img(n, nullptr);
+    int rc = 0;
+    static unsigned char dummy[16];
+    for (int i = 0; i < n && rc == 0; ++i) {
+        if (nvimgcodecCodeStreamCreateFromHostMem(inst, &cs[i], data[i], sizes[i]) != NVIMGCODEC_STATUS_SUCCESS) {
+            rc = -1;
+            break;
+        }
+        nvimgcodecImageInfo_t info;
+        fill_image_info(info, widths[i], heights[i], sample_formats[i], (int64_t)widths[i] * num_channels[i], buffer_kind, dummy, nullptr, 3);
+        info.num_planes = num_planes[i];
+        for (int p = 0; p < num_planes[i] && p < NVIMGCODEC_MAX_NUM_PLANES; ++p) {
+            info.plane_info[p].struct_type = NVIMGCODEC_STRUCTURE_TYPE_IMAGE_PLANE_INFO;
+            info.plane_info[p].struct_size = sizeof(nvimgcodecImagePlaneInfo_t);
+            info.plane_info[p].width = widths[i];
+            info.plane_info[p].height = heights[i];
+            info.plane_info[p].num_channels = num_channels[i];
+            info.plane_info[p].row_stride = (size_t)widths[i] * num_channels[i];
+            info.plane_info[p].sample_type = (nvimgcodecSampleDataType_t)sample_types[i];
+        }
+        if (orient) {
+            info.orientation.struct_type = NVIMGCODEC_STRUCTURE_TYPE_ORIENTATION;
+            info.orientation.struct_size = sizeof(nvimgcodecOrientation_t);
+            info.orientation.rotated = orient[3 * i];
+            info.orientation.flip_x = orient[3 * i + 1];
+            info.orientation.flip_y = orient[3 * i + 2];
+        }
+        if (nvimgcodecImageCreate(inst, &img[i], &info) != NVIMGCODEC_STATUS_SUCCESS)
+            rc = -2;
+    }
+    nvimgcodecDecodeParams_t params{NVIMGCODEC_STRUCTURE_TYPE_DECODE_PARAMS, sizeof(nvimgcodecDecodeParams_t), 0};
+    params.apply_exif_orientation = apply_exif;
+    if (rc == 0) {
+        std::vector<nvimgcodecProcessingStatus_t> st(n, 0);
+        if (nvimgcodecDecoderCanDecode(d->dec, cs.data(), img.data(), n, &params, st.data(), force_format) != NVIMGCODEC_STATUS_SUCCESS)
+            rc = -3;
+        for (int i = 0; i < n; ++i)
+            status_out[i] = st[i];
+    }
+    for (int i = 0; i < n; ++i) {
+        if (img[i])
+            nvimgcodecImageDestroy(img[i]);
+        if (cs[i])
+            nvimgcodecCodeStreamDestroy(cs[i]);
+    }
+    return rc;
 }
 
 // nvimgcodecDecoderCanDecode for a batch (src/image_generic_decoder.cpp:84-131)

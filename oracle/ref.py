@@ -22,6 +22,11 @@ BUFFER_DEVICE, BUFFER_HOST = 1, 2
 # nvimgcodecChromaSubsampling_t (include/nvimgcodec.h:360-372)
 SAMPLING_444, SAMPLING_422, SAMPLING_420, SAMPLING_440, SAMPLING_411, SAMPLING_410, SAMPLING_GRAY = 0, 2, 3, 4, 5, 6, 7
 STATUS_SUCCESS = 1
+# nvimgcodecProcessingStatus_t (include/nvimgcodec.h:583-612) and nvimgcodecSampleDataType_t (:340-356)
+PS_FAIL, PS_IMAGE_CORRUPTED, PS_CODEC_UNSUPPORTED, PS_BACKEND_UNSUPPORTED, PS_ENCODING_UNSUPPORTED = 0x3, 0x7, 0xB, 0x13, 0x23
+PS_ORIENTATION_UNSUPPORTED, PS_ROI_UNSUPPORTED, PS_SAMPLE_TYPE_UNSUPPORTED, PS_SAMPLE_FORMAT_UNSUPPORTED = 0x9, 0x11, 0x41, 0x81
+PS_NUM_PLANES_UNSUPPORTED, PS_NUM_CHANNELS_UNSUPPORTED = 0x101, 0x201
+TYPE_UINT8, TYPE_UINT16 = 0x0802, 0x1004
 
 _lib = None
 
@@ -48,6 +53,13 @@ def lib():
                                   C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64), C.c_int,
                                   C.c_void_p, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_double)]
         L.refh_decode_roi.argtypes = L.refh_decode.argtypes + [C.POINTER(C.c_int)]
+        L.refh_decode_ex.argtypes = L.refh_decode_roi.argtypes + [C.POINTER(C.c_int), C.c_int]
+        L.refh_decode_pipelined.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p),
+                                            C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                            C.POINTER(C.c_int64), C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_double)]
+        L.refh_can_decode_ex.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_int),
+                                         C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                         C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint)]
         L.refh_can_decode.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_int),
                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(C.c_uint)]
         L.refh_encode.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int),
@@ -171,6 +183,35 @@ class Decoder:
             raise RuntimeError("refh_can_decode rc=%d" % rc)
         return list(st)
 
+    def can_decode_ex(self, datas, dims, fmts, planes, channels, types=None, orient=None, apply_exif=0, buffer_kind=BUFFER_HOST,
+                      force_format=1):
+        """nvimgcodecDecoderCanDecode with the target's image info spelled out per image -> status list"""
+        n = len(datas)
+        types = types or [TYPE_UINT8] * n
+        st = (C.c_uint * n)()
+        flat = _arr(C.c_int, [v for o in orient for v in o]) if orient else None
+        rc = lib().refh_can_decode_ex(self.h, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
+                                      _arr(C.c_int, [d[0] for d in dims]), _arr(C.c_int, [d[1] for d in dims]), _arr(C.c_int, fmts),
+                                      _arr(C.c_int, planes), _arr(C.c_int, channels), _arr(C.c_int, types), flat, apply_exif,
+                                      buffer_kind, force_format, st)
+        if rc != 0:
+            raise RuntimeError("refh_can_decode_ex rc=%d" % rc)
+        return list(st)
+
+    def decode_pipelined(self, datas, buffers_a, buffers_b, dims, fmts, strides, buffer_kind, stream=None, rounds=2):
+        """`rounds` decode calls with two in flight (batch r + 1 is handed in before the future of batch r is waited for),
+        alternating between the two buffer sets -> (statuses, seconds for all rounds)"""
+        n = len(datas)
+        st = (C.c_uint * n)()
+        secs = (C.c_double * 1)()
+        rc = lib().refh_decode_pipelined(self.h, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
+                                         _arr(C.c_void_p, buffers_a), _arr(C.c_void_p, buffers_b), _arr(C.c_int, [d[0] for d in dims]),
+                                         _arr(C.c_int, [d[1] for d in dims]), _arr(C.c_int, fmts), _arr(C.c_int64, strides), buffer_kind,
+                                         stream, rounds, st, secs)
+        if rc != 0:
+            raise RuntimeError("refh_decode_pipelined rc=%d" % rc)
+        return list(st), secs[0]
+
     def decode_host(self, datas, fmt=I_RGB, reps=1, dims=None, row_strides=None, rois=None):
         """Decode to host numpy buffers. Returns (list of arrays, status list, seconds list).
         Interleaved -> (H, W, C); planar -> (C, H, W).  rois: per image (x, y, w, h) or None: decode that region only."""
@@ -208,19 +249,23 @@ class Decoder:
                 res.append(o.reshape(h, s)[:, :w * ch].reshape(h, w, ch))
         return res, list(st), list(secs)
 
-    def decode_raw(self, datas, buffers, dims, fmts, strides, buffer_kind, stream=None, reps=1, rois=None):
+    def decode_raw(self, datas, buffers, dims, fmts, strides, buffer_kind, stream=None, reps=1, rois=None, orient=None, apply_exif=0):
         """Decode into caller-provided raw pointers (ints); used with device buffers for the b200jpeg plugin.
-        rois: per image (x, y, w, h) or None; dims are then the regions' sizes."""
+        rois: per image (x, y, w, h) or None; dims are then the regions' sizes.  orient: per image (rotated, flip_x, flip_y)
+        with apply_exif=1: dims are the oriented sizes."""
         n = len(datas)
         st = (C.c_uint * n)()
         secs = (C.c_double * reps)()
         args = (self.h, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
                 _arr(C.c_void_p, buffers), _arr(C.c_int, [d[0] for d in dims]), _arr(C.c_int, [d[1] for d in dims]),
                 _arr(C.c_int, fmts), _arr(C.c_int64, strides), buffer_kind, stream, reps, st, secs)
-        if rois is None:
+        roi_arr = _arr(C.c_int, [v for r in rois for v in (r if r else (0, 0, 0, 0))]) if rois is not None else None
+        if orient is not None or apply_exif:
+            rc = lib().refh_decode_ex(*args, roi_arr, _arr(C.c_int, [v for o in orient for v in o]) if orient else None, apply_exif)
+        elif rois is None:
             rc = lib().refh_decode(*args)
         else:
-            rc = lib().refh_decode_roi(*args, _arr(C.c_int, [v for r in rois for v in (r if r else (0, 0, 0, 0))]))
+            rc = lib().refh_decode_roi(*args, roi_arr)
         if rc != 0:
             raise RuntimeError("refh_decode rc=%d" % rc)
         return list(st), list(secs)
