@@ -323,11 +323,16 @@ REFH_API int refh_decode_ex(void* hd, int n, const unsigned char** data, const s
         seconds, rois, orient, apply_exif);
 }
 
-// Two decode calls in flight: batch A and batch B (same decoder) are submitted back to back, then both futures are waited
-// for -- the pattern of a loader that keeps one batch ahead.  seconds[0] = wall time of submit A .. both ready.
+// Steady-state decode loop for the benchmark and the pipelining tests: `rounds` decode calls of the same n code streams,
+// alternating between two sets of target buffers, with `depth` calls in flight (1: Decode -> FutureWaitForAll -> next;
+// 2: batch r + 1 is handed in before the future of batch r is waited for -- a loader that keeps one batch ahead).
+// With d2h_bytes != 0 every finished batch is followed by one cudaMemcpyAsync(device -> host) of that many bytes on
+// cuda_stream (what a user of the Python layer does with Image.cpu(); the targets of a set then sit back to back in one
+// allocation starting at d2h_src_*).  seconds[0] = wall time from the first Decode to everything done (stream synchronised).
 REFH_API int refh_decode_pipelined(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers_a, void** buffers_b,
     const int* widths, const int* heights, const int* sample_formats, const int64_t* row_strides, int buffer_kind, void* cuda_stream,
-    int rounds, unsigned int* status_out, double* seconds)
+    int rounds, int depth, void* d2h_dst_a, void* d2h_dst_b, const void* d2h_src_a, const void* d2h_src_b, size_t d2h_bytes,
+    unsigned int* status_out, double* seconds)
 {
     auto* d = (Decoder*)hd;
     auto inst = d->s->instance;
@@ -349,8 +354,22 @@ REFH_API int refh_decode_pipelined(void* hd, int n, const unsigned char** data, 
         }
     }
     nvimgcodecDecodeParams_t params{NVIMGCODEC_STRUCTURE_TYPE_DECODE_PARAMS, sizeof(nvimgcodecDecodeParams_t), 0};
+    if (status_out)
+        for (int i = 0; i < n; ++i)
+            status_out[i] = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+    auto finish = [&](nvimgcodecFuture_t fut, int k) {
+        nvimgcodecFutureWaitForAll(fut);
+        size_t sz = 0;
+        std::vector<nvimgcodecProcessingStatus_t> st(n, 0);
+        nvimgcodecFutureGetProcessingStatus(fut, st.data(), &sz);
+        for (int i = 0; i < n; ++i)
+            if (status_out && st[i] != NVIMGCODEC_PROCESSING_STATUS_SUCCESS)
+                status_out[i] = st[i];
+        nvimgcodecFutureDestroy(fut);
+        if (d2h_bytes) // ordered behind the decode on the images' stream by the plugin's event
+            cudaMemcpyAsync(k ? d2h_dst_b : d2h_dst_a, k ? d2h_src_b : d2h_src_a, d2h_bytes, cudaMemcpyDeviceToHost, (cudaStream_t)cuda_stream);
+    };
     if (rc == 0) {
-        // steady state: the future of batch r is waited for after batch r + 1 has been handed in
         double t0 = now_s();
         nvimgcodecFuture_t fut[2] = {nullptr, nullptr};
         for (int r = 0; r < rounds && rc == 0; ++r) {
@@ -359,31 +378,21 @@ REFH_API int refh_decode_pipelined(void* hd, int n, const unsigned char** data, 
                 rc = -3;
                 break;
             }
-            if (r > 0) {
-                nvimgcodecFutureWaitForAll(fut[k ^ 1]);
-                size_t sz = 0;
-                std::vector<nvimgcodecProcessingStatus_t> st(n, 0);
-                nvimgcodecFutureGetProcessingStatus(fut[k ^ 1], st.data(), &sz);
-                for (int i = 0; i < n; ++i)
-                    if (status_out && (r == 1 || st[i] != NVIMGCODEC_PROCESSING_STATUS_SUCCESS))
-                        status_out[i] = st[i];
-                nvimgcodecFutureDestroy(fut[k ^ 1]);
+            if (depth <= 1) {
+                finish(fut[k], k);
+                fut[k] = nullptr;
+            } else if (r > 0) {
+                finish(fut[k ^ 1], k ^ 1);
                 fut[k ^ 1] = nullptr;
             }
         }
-        const int last = (rounds - 1) & 1;
-        if (fut[last]) {
-            nvimgcodecFutureWaitForAll(fut[last]);
-            size_t sz = 0;
-            std::vector<nvimgcodecProcessingStatus_t> st(n, 0);
-            nvimgcodecFutureGetProcessingStatus(fut[last], st.data(), &sz);
-            for (int i = 0; i < n; ++i)
-                if (status_out && (rounds == 1 || st[i] != NVIMGCODEC_PROCESSING_STATUS_SUCCESS))
-                    status_out[i] = st[i];
-            nvimgcodecFutureDestroy(fut[last]);
+        for (int k = 0; k < 2; ++k) {
+            const int kk = (rounds & 1) ? (k ^ 1) : k; // the older one first
+            if (fut[kk])
+                finish(fut[kk], kk);
+            fut[kk] = nullptr;
         }
-        if (buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_DEVICE)
-            cudaStreamSynchronize((cudaStream_t)cuda_stream);
+        cudaStreamSynchronize((cudaStream_t)cuda_stream);
         if (seconds)
             seconds[0] = now_s() - t0;
     }
