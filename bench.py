@@ -159,38 +159,105 @@ def hbm_peak():
         return 6650.0, "fallback"
 
 
-def reference_decode_all(datas, reps, threads=0):
+def workload_string(args):
+    if args.workload == "c2":
+        return "C2: %dx variable-size ~500x375 4:2:0 q75 baseline JPEG -> interleaved RGB u8, fancy upsampling" % args.batch
+    return "C1: %dx 1920x1080 4:2:0 q90 baseline JPEG, no restart markers -> interleaved RGB u8, fancy upsampling" % args.batch
+
+
+def workload_config(args):
+    """identical in both arms (the driver compares them)"""
+    return {"workload": workload_string(args), "batch": args.batch, "options": ":fancy_upsampling=1"}
+
+
+def _encode_c2(spec):
+    from PIL import Image
+    from nvimagecodec_b200.corpus import synth_image
+    seed, w, h = spec
+    b = io.BytesIO()
+    Image.fromarray(synth_image(seed, w, h)).save(b, "JPEG", quality=75, subsampling="4:2:0", optimize=False)
+    return b.getvalue()
+
+
+def make_workload(args):
+    """-> (list of JPEG bytes, list of (w, h)); C2 repeats 64 distinct images up to the batch size"""
+    if args.workload != "c2":
+        return make_corpus(args.batch), [(W, H)] * args.batch
+    from concurrent.futures import ProcessPoolExecutor
+    import multiprocessing as mp
+    rng = np.random.default_rng(2)
+    distinct = min(args.batch, 64)
+    specs = [(2000 + i, int(rng.integers(320, 641)), int(rng.integers(240, 501))) for i in range(distinct)]
+    with ProcessPoolExecutor(max_workers=max(1, min(16, os.cpu_count() or 1)), mp_context=mp.get_context("spawn")) as ex:
+        base = list(ex.map(_encode_c2, specs))
+    return [base[i % distinct] for i in range(args.batch)], [(specs[i % distinct][1], specs[i % distinct][2]) for i in range(args.batch)]
+
+
+def reference_decode_all(datas, dims, reps, threads=0):
     """reference CPU path: nvimgcodecDecoderDecode -> libjpeg_turbo_ext on the thread-pool executor, host RGB out"""
     from oracle import ref
     sess = ref.Session.shared()
     dec = sess.decoder(device_id=ref.DEVICE_CPU_ONLY, backends=ref.BACKEND_CPU_ONLY, num_threads=threads, options=":fancy_upsampling=1")
-    outs, st, secs = dec.decode_host(datas, fmt=ref.I_RGB, reps=reps, dims=[(W, H)] * len(datas))
+    outs, st, secs = dec.decode_host(datas, fmt=ref.I_RGB, reps=reps, dims=dims)
     assert all(s == ref.STATUS_SUCCESS for s in st)
     return outs, secs
+
+
+def simd_context(datas, dims, cores):
+    """What WITH_SIMD=0 costs the reference arm: the same bytes through a stock SIMD build of libjpeg-turbo (the one PIL bundles;
+    islow IDCT and fancy upsampling are its defaults too) on every host thread.  Context only -- not the reference's code path."""
+    try:
+        import PIL
+        from PIL import Image
+        from concurrent.futures import ThreadPoolExecutor
+
+        def one(d):
+            im = Image.open(io.BytesIO(d))
+            im.load()  # releases the GIL while libjpeg runs
+            return im.size
+
+        with ThreadPoolExecutor(max_workers=cores) as tp:
+            list(tp.map(one, datas[:cores]))
+            best = None
+            for _ in range(3):
+                t0 = time.perf_counter()
+                list(tp.map(one, datas))
+                dt = time.perf_counter() - t0
+                best = dt if best is None else min(best, dt)
+        feats = ""
+        try:
+            from PIL import features
+            feats = " libjpeg-turbo %s" % features.version_feature("libjpeg_turbo") if features.check_feature("libjpeg_turbo") else ""
+        except Exception:
+            pass
+        return {"value": sum(w * h for w, h in dims) / 1e6 / best, "unit": "Mpixel/s", "cores": cores,
+                "how": "PIL %s%s (stock SIMD build), Image.load() of the same %d files on %d threads, best of 3; context only" %
+                       (PIL.__version__, feats, len(datas), cores)}
+    except Exception as e:  # no PIL on the box: say so
+        return {"value": None, "how": "unavailable: %s" % e}
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
     n = args.batch
-    datas = make_corpus(n)
+    datas, dims = make_workload(args)
     cores = os.cpu_count() or 1
-    sample = min(n, max(8, cores * 2)) if cores < 32 else n  # bounded sample of the same workload per step
-    sub = datas[:sample]
-    _, warm = reference_decode_all(sub, max(1, min(args.warmup, 2)))
-    _, secs = reference_decode_all(sub, args.steps)
+    mpix = sum(w * h for w, h in dims) / 1e6
+    _, warm = reference_decode_all(datas, dims, max(1, min(args.warmup, 2)))
+    _, secs = reference_decode_all(datas, dims, args.steps)
     total = float(sum(secs))
-    mpix = sample * W * H / 1e6
     value = mpix * args.steps / total
     line = {
-        "impl": "reference", "metric": "decoded_mpixel_per_s", "value": value, "unit": "Mpixel/s", "images_per_s": sample * args.steps / total,
+        "impl": "reference", "metric": "decoded_mpixel_per_s", "value": value, "unit": "Mpixel/s", "images_per_s": n * args.steps / total,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C1: %dx 1920x1080 4:2:0 q90 baseline JPEG, no restart markers -> interleaved RGB u8" % n,
-                   "reference_path": "nvimgcodecDecoderDecode -> libjpeg_turbo_ext (libjpeg-turbo 3.0.3, WITH_SIMD=0: no nasm in image) "
-                                     "on the default thread-pool executor, host buffers"},
+        "scaling": "strong" if args.workload == "c2" else "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(args),
+        "reference_path": "nvimgcodecDecoderDecode -> libjpeg_turbo_ext (libjpeg-turbo 3.0.3, WITH_SIMD=0: no nasm in the image) on the "
+                          "default thread-pool executor, host buffers; rank 0 only, every image of the batch in every step",
         "cpu_baseline": {"value": value, "unit": "Mpixel/s", "cores": cores, "kind": "reference",
-                         "sample": "%d of the %d images per step, %d steps, all %d host threads" % (sample, n, args.steps, cores)},
+                         "sample": "all %d images per step, %d steps, all %d host threads" % (n, args.steps, cores),
+                         "simd_context": simd_context(datas, dims, cores)},
         "e2e": {"value": value, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -348,8 +415,9 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--options", default=":fancy_upsampling=1")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="decode", choices=["decode", "encode"],
-                    help="decode = the headline C1 decode batch (default); encode = BASELINE configs[4], 128x 1080p RGB -> JPEG")
+    ap.add_argument("--workload", default="decode", choices=["decode", "c2", "encode"],
+                    help="decode = the headline C1 decode batch (default); c2 = BASELINE configs[1], 256 ImageNet-shaped JPEGs dealt over the "
+                         "GPUs (strong scaling); encode = BASELINE configs[4], 128x 1080p RGB -> JPEG")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -363,11 +431,17 @@ def main():
             args.batch = 128
         run_encode(args, rank, world, local_rank)
         return
+    if args.workload == "c2" and args.batch == 64:
+        args.batch = 256
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
 
-    datas = make_corpus(args.batch)  # before CUDA init (spawned workers)
+    run_decode(args, rank, world, local_rank)
+
+
+def run_decode(args, rank, world, local_rank):
+    datas_all, dims_all = make_workload(args)  # before CUDA init (spawned workers)
     numa = pin_to_gpu_numa_node(local_rank) if world > 1 else None
     import torch
     import torch.distributed as dist
@@ -389,33 +463,55 @@ def main():
             sys.stdout.flush()
             os.dup2(saved, 1)
             os.close(saved)
+    import nvimagecodec_b200 as nb
     from nvimagecodec_b200.decoder import Decoder
+    from nvimagecodec_b200.sharding import estimate_cost, shard_batch
+    from oracle import ref  # the unmodified reference FRAMEWORK is the caller of the plugin in the e2e legs (and the checker)
 
-    n = args.batch
-    dec = Decoder(local_rank, options=args.options)
-    outs = [torch.empty((H, W * 3), dtype=torch.uint8, device=dev) for _ in range(n)]
-    ptrs = [o.data_ptr() for o in outs]
-    strides = [W * 3] * n
-    fmts = [4] * n
+    # C1: every rank decodes the whole batch (weak scaling); C2: the batch is dealt over the ranks (strong scaling, fixed N)
+    sharded = args.workload == "c2"
+    if sharded and world > 1:
+        mine = shard_batch([estimate_cost(len(d), w, h) for d, (w, h) in zip(datas_all, dims_all)], world)[rank]
+    else:
+        mine = list(range(len(datas_all)))
+    datas = [datas_all[i] for i in mine]
+    dims = [dims_all[i] for i in mine]
+    n = len(datas)
+    pixels = sum(w * h for w, h in dims)
+    out_bytes = 3 * pixels
+    opts = args.options
     stream = torch.cuda.current_stream(dev).cuda_stream
 
-    # ---- parity gate + CPU baseline (rank 0): the same bytes through the reference's CPU path ----
-    st = dec.decode_into(datas, ptrs, strides, fmts, False, stream)
+    # device outputs: the images of a set back to back in one allocation (a batch tensor), two sets for the two batches in flight
+    offs = np.concatenate([[0], np.cumsum([3 * w * h for w, h in dims])]).astype(np.int64)
+    dev_sets = [torch.empty(out_bytes + 64, dtype=torch.uint8, device=dev) for _ in range(2)]
+    host_sets = [torch.empty(out_bytes + 64, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    ptrs = [[t.data_ptr() + int(offs[i]) for i in range(n)] for t in dev_sets]
+    hptrs = [[t.data_ptr() + int(offs[i]) for i in range(n)] for t in host_sets]
+    strides = [3 * w for w, h in dims]
+    fmts = [4] * n
+
+    dec = Decoder(local_rank, options=opts)
+    st = dec.decode_into(datas, ptrs[0], strides, fmts, False, stream)
     assert all(s == 0 for s in st), st
+    torch.cuda.synchronize(dev)
+
+    # ---- parity gate + CPU baseline (rank 0): the same bytes through the reference's CPU path ----
     cpu_baseline = None
+    want = None
     if rank == 0 and not args.skip_cpu_baseline:
         cores = os.cpu_count() or 1
         reps = 3 if cores >= 16 else 1
-        want, secs = reference_decode_all(datas, reps)
-        for i in range(n):
-            got = outs[i].cpu().numpy().reshape(H, W, 3)
-            if not np.array_equal(got, want[i]):
+        want, secs = reference_decode_all(datas, dims, reps)
+        got = dev_sets[0].cpu().numpy()
+        for i, (w, h) in enumerate(dims):
+            if not np.array_equal(got[offs[i]:offs[i + 1]].reshape(h, w, 3), want[i]):
                 raise SystemExit("PARITY FAILURE on image %d: GPU output differs from the reference decoder" % i)
         best = min(secs)
-        cpu_baseline = {"value": n * W * H / 1e6 / best, "unit": "Mpixel/s", "cores": cores, "kind": "reference",
-                        "images_per_s": n / best,
-                        "sample": "all %d images of the batch, best of %d passes, nvimgcodec default executor with %d threads, "
-                                  "libjpeg-turbo 3.0.3 WITH_SIMD=0" % (n, reps, cores)}
+        cpu_baseline = {"value": pixels / 1e6 / best, "unit": "Mpixel/s", "cores": cores, "kind": "reference", "images_per_s": n / best,
+                        "sample": "all %d images of this rank's batch, best of %d passes, nvimgcodec default executor with %d threads, "
+                                  "libjpeg-turbo 3.0.3 WITH_SIMD=0" % (n, reps, cores),
+                        "simd_context": simd_context(datas, dims, cores)}
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -424,7 +520,7 @@ def main():
         torch.cuda.synchronize(dev)
 
     # ---- value: device-resident inputs, kernels only ----
-    st = dec.prepare(datas, ptrs, strides, fmts, False)
+    st = dec.prepare(datas, ptrs[0], strides, fmts, False)
     assert all(s == 0 for s in st)
     for _ in range(args.warmup):
         dec.run(stream)
@@ -444,8 +540,8 @@ def main():
 
     # ---- per-stage device times: same batch, same steps, single stream with CUDA events between the stages ----
     stage_acc = {}
-    decp = Decoder(local_rank, options=args.options + " :profile=1")
-    st = decp.prepare(datas, ptrs, strides, fmts, False)
+    decp = Decoder(local_rank, options=opts + " :profile=1")
+    st = decp.prepare(datas, ptrs[0], strides, fmts, False)
     for _ in range(args.warmup):
         decp.run(stream)
     for _ in range(args.steps):
@@ -455,87 +551,158 @@ def main():
     decp.close()
     barrier()
 
-    # ---- e2e: host JPEG bytes -> host RGB through the C ABI ----
-    hbatch = torch.empty((n, H, W * 3), dtype=torch.uint8).pin_memory()  # the batch tensor a data loader would hand over
-    houts = [hbatch[i] for i in range(n)]
-    hptrs = [o.data_ptr() for o in houts]
+    # ---- C ABI, host JPEG bytes -> host RGB (b200jpeg_decode_batch) ----
     for _ in range(2):
-        dec.decode_into(datas, hptrs, strides, fmts, True, stream)
+        dec.decode_into(datas, hptrs[0], strides, fmts, True, stream)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        st = dec.decode_into(datas, hptrs, strides, fmts, True, stream)
+        st = dec.decode_into(datas, hptrs[0], strides, fmts, True, stream)
     torch.cuda.synchronize(dev)
-    e2e_s = time.perf_counter() - t0
+    cabi_s = time.perf_counter() - t0
     assert all(s == 0 for s in st)
     if rank == 0:
-        assert torch.equal(houts[0], outs[0].cpu()), "host-output path differs from device-output path"
+        assert torch.equal(host_sets[0][:out_bytes], dev_sets[0][:out_bytes].cpu()), "host-output path differs from device-output path"
+    dec.close()
+
+    # ---- through the unchanged nvimgcodec API: the reference framework dlopen()s libb200jpeg_ext.so from the extensions
+    # directory (src/plugin_framework.cpp:281-351); GPU_ONLY backends, so only the plugin can have decoded ----
+    sess = ref.Session(ext_dir=nb.EXT_DIR, with_ljt=False)
+    fdec = [sess.decoder(device_id=local_rank, backends=ref.BACKEND_GPU_ONLY, options=opts) for _ in range(2)]
+    fdims, ffmts = dims, [ref.I_RGB] * n
+    for t in dev_sets:
+        t.zero_()
+    torch.cuda.synchronize(dev)
+
+    def through_api(rounds, depth, d2h, kind=ref.BUFFER_DEVICE, bufs=None):
+        a, b = bufs or (ptrs[0], ptrs[1])
+        copy = (host_sets[0].data_ptr(), host_sets[1].data_ptr(), dev_sets[0].data_ptr(), dev_sets[1].data_ptr(), out_bytes) if d2h else None
+        st, secs = fdec[0].decode_pipelined(datas, a, b, fdims, ffmts, strides, kind, stream, rounds=rounds, depth=depth, d2h=copy,
+                                            other=fdec[1] if depth > 1 else None)
+        assert all(x == ref.STATUS_SUCCESS for x in st), st
+        return secs
+
+    through_api(2, 2, True)
+    torch.cuda.synchronize(dev)
+    if want is not None:  # what nvimgcodecDecoderDecode delivered, on the device and after the copy to the host
+        for t in (dev_sets[0].cpu().numpy(), dev_sets[1].cpu().numpy(), host_sets[0].numpy(), host_sets[1].numpy()):
+            for i in (0, n // 2, n - 1):
+                w, h = dims[i]
+                if not np.array_equal(t[offs[i]:offs[i + 1]].reshape(h, w, 3), want[i]):
+                    raise SystemExit("PARITY FAILURE through nvimgcodecDecoderDecode (image %d)" % i)
+    api = {}
+    steps = max(2, args.steps)
+    for key, depth, d2h in (("dev_serial", 1, False), ("dev_pipelined", 2, False), ("host_serial", 1, True), ("host_pipelined", 2, True)):
+        through_api(2, depth, d2h)
+        barrier()
+        api[key] = through_api(steps, depth, d2h) / steps
+    # the user hands HOST buffers to the GPU decoder: the framework stages every image in a temporary device buffer it
+    # allocates per call and copies back on the image's stream (src/work.h:120-190)
+    through_api(1, 1, False, ref.BUFFER_HOST, (hptrs[0], hptrs[1]))
+    barrier()
+    hb_steps = max(2, min(5, args.steps))
+    api["framework_host_buffers"] = through_api(hb_steps, 1, False, ref.BUFFER_HOST, (hptrs[0], hptrs[1])) / hb_steps
+    for x in fdec:
+        x.close()
+    sess.close()
 
     # ---- reduce over ranks (max time) ----
-    t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    keys = ["dev_serial", "dev_pipelined", "host_serial", "host_pipelined", "framework_host_buffers"]
+    t = torch.tensor([ms_total, cabi_s * 1e3 / args.steps] + [api[k] * 1e3 for k in keys] + [float(pixels), float(out_bytes), float(n),
+                     float(stats["scan_bytes"])], dtype=torch.float64, device=dev)
     per_rank_ms = [ms_total / args.steps]
+    tot = t.clone()
     if world > 1:
         every = [torch.zeros_like(t) for _ in range(world)]
         dist.all_gather(every, t)
         per_rank_ms = [float(x[0]) / args.steps for x in every]  # the spread behind the max (reported in config)
+        tot = torch.stack(every).sum(0)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms = float(t[0]), float(t[1])
+    ms_total, cabi_ms = float(t[0]), float(t[1])
+    api_ms = {k: float(t[2 + i]) for i, k in enumerate(keys)}
+    job_pixels, job_out_bytes, job_images, job_scan = float(tot[7]), float(tot[8]), float(tot[9]), float(tot[10])
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    mpix_step = n * W * H / 1e6 * world
+    mpix_step = job_pixels / 1e6
     ms_step = ms_total / args.steps
     value = mpix_step / (ms_step / 1e3)
     peak, peak_kind = hbm_peak()
-    # algorithmic bytes per stage for this batch: compressed bytes S, coefficient records 2 B per
+    # algorithmic bytes per stage for this rank's batch: compressed bytes S, coefficient records 2 B per
     # entropy-coded symbol (R bytes in all, measured by the decoder), per block 2 B DC + 4 B record index, planes 64 B/block,
     # output bytes
     S, blocks, out_b, R = stats["scan_bytes"], stats["blocks"], stats["out_bytes"], stats["record_bytes"]
     alg = {"unstuff": 2 * S, "huff_sync": 2 * S, "huff_tail": S * stats["tail_redone"] // max(1, stats["subsequences"]),
            "huff_write": S + R + 6 * blocks, "dc_scan": 4 * blocks, "idct": R + 6 * blocks + 64 * blocks, "color": 64 * blocks + out_b}
     kernels = {"unstuff": "k_unstuff_count + k_unstuff_scan + k_unstuff_write", "huff_sync": "k_huff_sync x2 (rounds 0 and 1)",
-               "huff_tail": "k_huff_sync_tail (cooperative, work-list rounds)", "huff_write": "k_subseq_scan + k_huff_write",
+               "huff_tail": "k_huff_tail_round + k_huff_sync_tail (work-list rounds)", "huff_write": "k_subseq_scan + k_huff_write",
                "dc_scan": "k_dc_scan", "idct": "k_idct", "color": "k_color"}
     traffic = {}
     try:  # DRAM bytes per stage from the committed ncu --set full capture of the same 64-image workload
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             tj = json.load(f)
-        if tj.get("workload_images") == n:
+        if tj.get("workload_images") == n and args.workload == "decode":
             traffic = {k: v["dram_bytes"] for k, v in tj["stages"].items()}
     except Exception:
         pass
     stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
-    # the dominant kernel among the bandwidth-type stages (the work-list rounds are latency bound: a chain of dependent
-    # single-thread decodes; they are reported in stage_ms / huffman_gbit_per_s, not as a bandwidth fraction)
-    cand = {k: v for k, v in stage_ms.items() if k != "huff_tail"}
-    dom = max(cand, key=cand.get) if cand else None
+    stages = []
+    for k in Decoder.STAGES:
+        if k in stage_ms and stage_ms[k] > 0:
+            ach = alg[k] / (stage_ms[k] * 1e-3) / 1e9
+            stages.append({"stage": k, "kernel": kernels[k], "ms": stage_ms[k], "algorithmic_bytes": alg[k], "achieved": ach, "frac": ach / peak,
+                           "traffic": traffic.get(k), "traffic_over_algorithmic": (traffic[k] / alg[k]) if traffic.get(k) and alg[k] else None})
     roof = None
-    if dom:
-        achieved = alg[dom] / (stage_ms[dom] * 1e-3) / 1e9
+    if stages:
+        dom = max(stages, key=lambda x: x["ms"])  # the stage with the largest CUDA-event time, no exclusions
         huff_ms = stage_ms.get("huff_sync", 0) + stage_ms.get("huff_tail", 0) + stage_ms.get("huff_write", 0)
-        roof = {"bound": "hbm", "kernel": kernels[dom], "stage": dom, "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic.get(dom), "algorithmic_bytes": alg[dom], "ms": stage_ms[dom],
+        roof = {"bound": "hbm", "kernel": dom["kernel"], "stage": dom["stage"], "achieved": dom["achieved"], "peak": peak, "peak_kind": peak_kind,
+                "unit": "GB/s", "frac": dom["frac"], "traffic": dom["traffic"], "algorithmic_bytes": dom["algorithmic_bytes"], "ms": dom["ms"],
                 "pipeline": {"algorithmic_bytes": S + out_b, "achieved": (S + out_b) / (ms_step * 1e-3) / 1e9,
-                             "frac": (S + out_b) / (ms_step * 1e-3) / 1e9 / peak},
-                "stage_ms": stage_ms, "stage_frac": {k: alg[k] / (v * 1e-3) / 1e9 / peak for k, v in stage_ms.items() if v > 0},
-                "stage_traffic": traffic or None,
+                             "frac": (S + out_b) / (ms_step * 1e-3) / 1e9 / peak,
+                             "single_stream_ms": sum(x["ms"] for x in stages)},
+                "stages": stages,
+                "huffman_stage": {"ms": huff_ms, "algorithmic_bytes": S + R + 6 * blocks,
+                                  "frac": (S + R + 6 * blocks) / (huff_ms * 1e-3) / 1e9 / peak if huff_ms else None},
                 "huffman_gbit_per_s": S * 8 / (huff_ms * 1e-3) / 1e9 if huff_ms else None}
+
+    def rate(ms):
+        return {"value": mpix_step / (ms / 1e3), "unit": "Mpixel/s", "images_per_s": job_images / (ms / 1e3), "ms_per_step": ms}
+
+    e2e = rate(api_ms["host_pipelined"])
+    e2e.update({"h2d_bytes_per_step": int(job_scan), "d2h_bytes_per_step": int(job_out_bytes),
+                "path": "nvimgcodecDecoderDecode + nvimgcodecFutureWaitForAll of the unmodified framework with libb200jpeg_ext.so found in its "
+                        "extensions directory (GPU_ONLY backends), pageable host JPEG bytes in, device batch tensor out, one cudaMemcpyAsync "
+                        "to a pinned host batch tensor per batch on the images' stream; steady state with two batches in flight (two "
+                        "decoders, ping-pong -- the framework promises one batch per decoder); wall clock, stream synchronised at the end",
+                "serial": rate(api_ms["host_serial"]),
+                "framework_host_buffers": rate(api_ms["framework_host_buffers"]),
+                "c_abi": rate(cabi_ms)})
+    e2e["serial"]["path"] = "the same with one batch at a time: Decode -> WaitForAll -> copy -> synchronise -> next"
+    e2e["framework_host_buffers"]["path"] = ("STRIDED_HOST (pinned) target buffers handed to the GPU decoder: the framework allocates a temporary "
+                                             "device buffer per image per call and copies back itself (src/work.h:120-190)")
+    e2e["c_abi"]["path"] = "b200jpeg_decode_batch with on_host outputs (no framework): pageable JPEG bytes in, pinned host batch tensor out"
+    e2e_dev = rate(api_ms["dev_pipelined"])
+    e2e_dev.update({"h2d_bytes_per_step": int(job_scan), "d2h_bytes_per_step": 0, "serial": rate(api_ms["dev_serial"]),
+                    "path": "as e2e without the copy back: host JPEG bytes -> device pixels, what python/decoder.cpp:148-225 hands its users"})
     line = {
-        "metric": "decoded_mpixel_per_s", "value": value, "unit": "Mpixel/s", "images_per_s": n * world / (ms_step / 1e3),
+        "metric": "decoded_mpixel_per_s", "value": value, "unit": "Mpixel/s", "images_per_s": job_images / (ms_step / 1e3),
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C1: %dx 1920x1080 4:2:0 q90 baseline JPEG (%.0f KB avg), no restart markers -> interleaved RGB u8, "
-                               "fancy upsampling, per GPU" % (n, S / n / 1e3),
-                   "l2": "working set per step %.0f MB (records+planes+output) > 126 MB L2, no explicit flush" %
-                         ((R + 70 * blocks + out_b) / 1e6),
-                   "host_affinity": numa, "per_rank_ms_per_step": [round(x, 4) for x in per_rank_ms], "options": args.options, "sync_rounds": stats["sync_rounds"], "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"],
-                   "parity": "bit-exact vs reference libjpeg_turbo_ext on all %d images before timing" % n},
+        "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(args),
+        "details": {"jpeg_kb_avg": S / n / 1e3, "per_gpu_images": n,
+                    "l2": "working set per step %.0f MB (records+planes+output) > 126 MB L2, no explicit flush" % ((R + 70 * blocks + out_b) / 1e6),
+                    "host_affinity": numa, "per_rank_ms_per_step": [round(x, 4) for x in per_rank_ms], "sync_rounds": stats["sync_rounds"],
+                    "subsequences": stats["subsequences"], "tail_redone": stats["tail_redone"],
+                    "sharding": "batch dealt over the ranks by shard_batch (cost = 8 x bytes + pixels), no collective" if sharded
+                                else "every rank decodes its own copy of the batch",
+                    "parity": "bit-exact vs reference libjpeg_turbo_ext on all %d images before timing (C ABI), and on samples of what "
+                              "nvimgcodecDecoderDecode delivered" % n},
         "clocks": clocks.summary(),
-        "e2e": {"value": mpix_step / (e2e_ms / args.steps / 1e3), "unit": "Mpixel/s", "images_per_s": n * world / (e2e_ms / args.steps / 1e3),
-                "ms_per_step": e2e_ms / args.steps, "h2d_bytes_per_step": int(S), "d2h_bytes_per_step": int(out_b), "timing": "wall clock around "
-                "b200jpeg_decode_batch (synchronous), pageable host JPEG bytes in, one pinned host batch tensor (N x H x W x 3) out"},
+        "e2e": e2e,
+        "e2e_device_out": e2e_dev,
         "gpu_launches": int(launches),
         "roofline": roof,
         "cpu_baseline": cpu_baseline,

@@ -329,12 +329,16 @@ REFH_API int refh_decode_ex(void* hd, int n, const unsigned char** data, const s
 // With d2h_bytes != 0 every finished batch is followed by one cudaMemcpyAsync(device -> host) of that many bytes on
 // cuda_stream (what a user of the Python layer does with Image.cpu(); the targets of a set then sit back to back in one
 // allocation starting at d2h_src_*).  seconds[0] = wall time from the first Decode to everything done (stream synchronised).
-REFH_API int refh_decode_pipelined(void* hd, int n, const unsigned char** data, const size_t* sizes, void** buffers_a, void** buffers_b,
+// hd_b: the decoder that takes the odd rounds.  The reference's own plugins keep per-decoder batch state
+// (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp decodeBatch refills decode_state_batch_->samples_), so two batches in
+// flight on ONE nvimgcodecDecoder_t are outside what the framework promises; two decoders, one batch each, are not.
+REFH_API int refh_decode_pipelined(void* hd, void* hd_b, int n, const unsigned char** data, const size_t* sizes, void** buffers_a, void** buffers_b,
     const int* widths, const int* heights, const int* sample_formats, const int64_t* row_strides, int buffer_kind, void* cuda_stream,
     int rounds, int depth, void* d2h_dst_a, void* d2h_dst_b, const void* d2h_src_a, const void* d2h_src_b, size_t d2h_bytes,
     unsigned int* status_out, double* seconds)
 {
     auto* d = (Decoder*)hd;
+    auto* d2 = hd_b ? (Decoder*)hd_b : d;
     auto inst = d->s->instance;
     std::vector<nvimgcodecCodeStream_t> cs(n, nullptr);
     std::vector<nvimgcodecImage_t> img[2];
@@ -374,7 +378,7 @@ REFH_API int refh_decode_pipelined(void* hd, int n, const unsigned char** data, 
         nvimgcodecFuture_t fut[2] = {nullptr, nullptr};
         for (int r = 0; r < rounds && rc == 0; ++r) {
             const int k = r & 1;
-            if (nvimgcodecDecoderDecode(d->dec, cs.data(), img[k].data(), n, &params, &fut[k]) != NVIMGCODEC_STATUS_SUCCESS) {
+            if (nvimgcodecDecoderDecode((k ? d2 : d)->dec, cs.data(), img[k].data(), n, &params, &fut[k]) != NVIMGCODEC_STATUS_SUCCESS) {
                 rc = -3;
                 break;
             }

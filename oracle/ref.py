@@ -54,7 +54,7 @@ def lib():
                                   C.c_void_p, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_double)]
         L.refh_decode_roi.argtypes = L.refh_decode.argtypes + [C.POINTER(C.c_int)]
         L.refh_decode_ex.argtypes = L.refh_decode_roi.argtypes + [C.POINTER(C.c_int), C.c_int]
-        L.refh_decode_pipelined.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p),
+        L.refh_decode_pipelined.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p),
                                             C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
                                             C.POINTER(C.c_int64), C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_size_t, C.POINTER(C.c_uint), C.POINTER(C.c_double)]
@@ -199,14 +199,15 @@ class Decoder:
             raise RuntimeError("refh_can_decode_ex rc=%d" % rc)
         return list(st)
 
-    def decode_pipelined(self, datas, buffers_a, buffers_b, dims, fmts, strides, buffer_kind, stream=None, rounds=2, depth=2, d2h=None):
+    def decode_pipelined(self, datas, buffers_a, buffers_b, dims, fmts, strides, buffer_kind, stream=None, rounds=2, depth=2, d2h=None, other=None):
         """`rounds` decode calls with `depth` in flight (2: batch r + 1 is handed in before the future of batch r is waited
         for), alternating between the two buffer sets; d2h = (host_a, host_b, dev_a, dev_b, nbytes): one device -> host copy
-        per finished batch on the stream -> (statuses, seconds for all rounds)"""
+        per finished batch on the stream; other = a second Decoder that takes the odd rounds (two batches in flight need two
+        decoders with the reference's own plugins) -> (statuses, seconds for all rounds)"""
         n = len(datas)
         st = (C.c_uint * n)()
         secs = (C.c_double * 1)()
-        rc = lib().refh_decode_pipelined(self.h, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
+        rc = lib().refh_decode_pipelined(self.h, other.h if other else None, n, _arr(C.c_char_p, datas), _arr(C.c_size_t, [len(d) for d in datas]),
                                          _arr(C.c_void_p, buffers_a), _arr(C.c_void_p, buffers_b), _arr(C.c_int, [d[0] for d in dims]),
                                          _arr(C.c_int, [d[1] for d in dims]), _arr(C.c_int, fmts), _arr(C.c_int64, strides), buffer_kind,
                                          stream, rounds, depth, *(d2h if d2h else (None, None, None, None, 0)), st, secs)

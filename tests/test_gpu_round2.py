@@ -267,8 +267,8 @@ def test_images_on_two_user_streams(cpu):
 
 
 def test_two_batches_in_flight(sess, cpu):
-    """b200jpeg_decode_submit / _wait with two batches in flight (each has its own scratch), and the same through the
-    framework: nvimgcodecDecoderDecode of batch r + 1 before the future of batch r is waited for"""
+    """b200jpeg_decode_submit / _wait with two batches in flight (each has its own scratch), and two batches in flight
+    through the framework"""
     import torch
     from nvimagecodec_b200.decoder import Decoder
     a = [make_jpeg(60 + i, 640, 480, (2, 2), 85) for i in range(6)]
@@ -290,16 +290,19 @@ def test_two_batches_in_flight(sess, cpu):
             assert np.array_equal(o.cpu().numpy().reshape(w.shape), w)
             o.zero_()
     dec.close()
-    fdec = sess.decoder(device_id=0, backends=ref.BACKEND_GPU_ONLY, options=":fancy_upsampling=1")
+    # through the framework: two decoders (one batch in flight each, which is what the framework promises), batch r + 1 handed
+    # to the other decoder before the future of batch r is waited for; decode() of the plugin returns with the device busy
+    fdec = [sess.decoder(device_id=0, backends=ref.BACKEND_GPU_ONLY, options=":fancy_upsampling=1") for _ in range(2)]
     oa2 = [torch.zeros_like(o) for o in oa]
     torch.cuda.synchronize()
-    st, secs = fdec.decode_pipelined(a, [o.data_ptr() for o in oa], [o.data_ptr() for o in oa2], [(640, 480)] * 6, [ref.I_RGB] * 6, [1920] * 6,
-                                     ref.BUFFER_DEVICE, rounds=6)
+    st, secs = fdec[0].decode_pipelined(a, [o.data_ptr() for o in oa], [o.data_ptr() for o in oa2], [(640, 480)] * 6, [ref.I_RGB] * 6,
+                                        [1920] * 6, ref.BUFFER_DEVICE, rounds=6, other=fdec[1])
     torch.cuda.synchronize()
     assert st == [ref.STATUS_SUCCESS] * 6
     for o, o2, w in zip(oa, oa2, wa):
         assert np.array_equal(o.cpu().numpy().reshape(w.shape), w) and torch.equal(o, o2)
-    fdec.close()
+    for x in fdec:
+        x.close()
 
 
 def test_flat_optimised_periodic_and_appended_files(cpu):
