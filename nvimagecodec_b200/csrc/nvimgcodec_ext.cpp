@@ -193,8 +193,8 @@ nvimgcodecProcessingStatus_t check_target(const nvimgcodecImageInfo_t& info, con
         st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
     if (int(info.plane_info[0].width) != want_w || int(info.plane_info[0].height) != want_h)
         st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED; // a resized target is not ours
-    if (info.buffer_kind != NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_DEVICE)
-        st |= NVIMGCODEC_PROCESSING_STATUS_BACKEND_UNSUPPORTED;
+    // the buffer kind is not looked at: a host buffer handed to a GPU backend is staged by the framework after canDecode
+    // (src/decoder_worker.cpp:298-302, src/work.h:144-190), and decode() takes either kind anyway
     return st;
 }
 

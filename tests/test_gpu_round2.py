@@ -131,12 +131,17 @@ def _exif_app1(orientation):
 
 def test_can_decode_matrix_matches_the_cpu_plugin_and_falls_back(sess):
     """Every rejection of the plugin's canDecode (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:118-173 is the model):
-    same nvimgcodecProcessingStatus_t as the CPU plugin for the same target description; what only b200jpeg declines
-    (a target that is not the image's size, a host buffer) is decoded by the fallback chain all the same."""
+    same nvimgcodecProcessingStatus_t as the CPU plugin for the same target description; what b200jpeg declines goes
+    down the framework's fallback chain and is decoded all the same."""
     import torch
+    import nvimagecodec_b200 as nb
     d = make_jpeg(1, 64, 48)
-    gpu = sess.decoder(device_id=0, backends=ref.BACKEND_GPU_ONLY, options=":fancy_upsampling=1")
-    cpu_only = sess.decoder(device_id=0, backends=ref.BACKEND_CPU_ONLY, options=":fancy_upsampling=1")
+    # b200jpeg alone in a session of its own: nvimgcodecDecoderCanDecode walks the fallback chain, and the reference
+    # dereferences a null decoder when the last worker of the chain has no allowed backend (src/image_generic_decoder.cpp:110
+    # after src/decoder_worker.cpp:63-93) -- so the plugin is asked where it is the only JPEG decoder there is
+    only = ref.Session(ext_dir=nb.EXT_DIR, with_ljt=False)
+    gpu = only.decoder(device_id=0, backends=0, options=":fancy_upsampling=1")
+    cpu_only = ref.Session.shared().decoder(options=":fancy_upsampling=1")
     # (format, planes, channels, sample type, orientation, expected status)
     rows = [(ref.P_YUV, 3, 1, ref.TYPE_UINT8, (0, 0, 0), ref.PS_SAMPLE_FORMAT_UNSUPPORTED),
             (ref.I_RGB, 1, 3, ref.TYPE_UINT16, (0, 0, 0), ref.PS_SAMPLE_TYPE_UNSUPPORTED),
@@ -153,12 +158,11 @@ def test_can_decode_matrix_matches_the_cpu_plugin_and_falls_back(sess):
     st_cpu = cpu_only.can_decode_ex([d] * n, buffer_kind=ref.BUFFER_HOST, **args)
     assert st_cpu == [r[5] for r in rows], [hex(x) for x in st_cpu]
     assert st_gpu == st_cpu, ([hex(x) for x in st_gpu], [hex(x) for x in st_cpu])
+    # host buffers are the framework's business (it stages them for GPU backends after canDecode, src/work.h:144-190)
+    assert gpu.can_decode_ex([d], [(64, 48)], [ref.I_RGB], [1], [3], buffer_kind=ref.BUFFER_HOST) == [ref.STATUS_SUCCESS]
     # a target that is not the image's size: the CPU plugin does not look, b200jpeg declines (it never resizes)
     st = gpu.can_decode_ex([d], [(32, 24)], [ref.I_RGB], [1], [3], buffer_kind=ref.BUFFER_DEVICE)
     assert st == [ref.PS_ROI_UNSUPPORTED]
-    # a host buffer handed to the plugin itself: declined (the framework stages host buffers for GPU backends, see below)
-    st = gpu.can_decode_ex([d], [(64, 48)], [ref.I_RGB], [1], [3], buffer_kind=ref.BUFFER_HOST)
-    assert st[0] != ref.STATUS_SUCCESS
     # progressive / arithmetic streams: ENCODING_UNSUPPORTED from b200jpeg, decoded by libjpeg_turbo_ext through the chain
     prog, arith = make_jpeg(2, 64, 48, progressive=True), make_jpeg(3, 64, 48, arith=True)
     st = gpu.can_decode_ex([prog, arith], [(64, 48)] * 2, [ref.I_RGB] * 2, [1] * 2, [3] * 2, buffer_kind=ref.BUFFER_DEVICE)
@@ -169,11 +173,12 @@ def test_can_decode_matrix_matches_the_cpu_plugin_and_falls_back(sess):
     fst, _ = both.decode_raw([d, prog, arith], [o.data_ptr() for o in outs], [(64, 48)] * 3, [ref.I_RGB] * 3, [192] * 3, ref.BUFFER_DEVICE)
     torch.cuda.synchronize()
     want, _, _ = ref.Session.shared().decoder(options=":fancy_upsampling=1").decode_host([d, prog, arith])
-    assert fst[0] == ref.STATUS_SUCCESS and fst[2] == ref.STATUS_SUCCESS
-    for k in (0, 2):
+    assert fst[0] == ref.STATUS_SUCCESS and fst[1] == ref.STATUS_SUCCESS, fst
+    for k in (0, 1):
         assert np.array_equal(outs[k].cpu().numpy().reshape(48, 64, 3), want[k])
     for x in (gpu, cpu_only, both):
         x.close()
+    only.close()
 
 
 def test_framework_with_host_user_buffers(sess, cpu):
