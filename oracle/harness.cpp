@@ -361,6 +361,15 @@ REFH_API int refh_decode_pipelined(void* hd, void* hd_b, int n, const unsigned c
     if (status_out)
         for (int i = 0; i < n; ++i)
             status_out[i] = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+    // The copies run on a stream of their own: on the images' stream the copy of batch r would queue up behind the wait for
+    // batch r + 1 (a GPU plugin makes the images' stream wait for the decode when the call is made).
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t decoded[2] = {nullptr, nullptr};
+    if (d2h_bytes) {
+        cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking);
+        cudaEventCreateWithFlags(&decoded[0], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&decoded[1], cudaEventDisableTiming);
+    }
     auto finish = [&](nvimgcodecFuture_t fut, int k) {
         nvimgcodecFutureWaitForAll(fut);
         size_t sz = 0;
@@ -370,8 +379,10 @@ REFH_API int refh_decode_pipelined(void* hd, void* hd_b, int n, const unsigned c
             if (status_out && st[i] != NVIMGCODEC_PROCESSING_STATUS_SUCCESS)
                 status_out[i] = st[i];
         nvimgcodecFutureDestroy(fut);
-        if (d2h_bytes) // ordered behind the decode on the images' stream by the plugin's event
-            cudaMemcpyAsync(k ? d2h_dst_b : d2h_dst_a, k ? d2h_src_b : d2h_src_a, d2h_bytes, cudaMemcpyDeviceToHost, (cudaStream_t)cuda_stream);
+        if (d2h_bytes) { // behind the decode of THIS batch only: the event was recorded on the images' stream right after Decode returned
+            cudaStreamWaitEvent(copy_stream, decoded[k], 0);
+            cudaMemcpyAsync(k ? d2h_dst_b : d2h_dst_a, k ? d2h_src_b : d2h_src_a, d2h_bytes, cudaMemcpyDeviceToHost, copy_stream);
+        }
     };
     if (rc == 0) {
         double t0 = now_s();
@@ -382,6 +393,8 @@ REFH_API int refh_decode_pipelined(void* hd, void* hd_b, int n, const unsigned c
                 rc = -3;
                 break;
             }
+            if (d2h_bytes)
+                cudaEventRecord(decoded[k], (cudaStream_t)cuda_stream);
             if (depth <= 1) {
                 finish(fut[k], k);
                 fut[k] = nullptr;
@@ -397,8 +410,15 @@ REFH_API int refh_decode_pipelined(void* hd, void* hd_b, int n, const unsigned c
             fut[kk] = nullptr;
         }
         cudaStreamSynchronize((cudaStream_t)cuda_stream);
+        if (copy_stream)
+            cudaStreamSynchronize(copy_stream);
         if (seconds)
             seconds[0] = now_s() - t0;
+    }
+    if (copy_stream) {
+        cudaStreamDestroy(copy_stream);
+        cudaEventDestroy(decoded[0]);
+        cudaEventDestroy(decoded[1]);
     }
     for (int i = 0; i < n; ++i) {
         for (int k = 0; k < 2; ++k)
