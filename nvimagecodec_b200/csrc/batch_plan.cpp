@@ -186,6 +186,17 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
         im.tabsel_s[b] = TabSel{uint32_t(slot_of(dc_tab[c])) * kLutEntries, uint32_t(slot_of(ac_tab[c])) * kLutEntries, uint32_t(dc_tab[c]),
             uint32_t(ac_tab[c])};
     }
+    // the reconstruction kernel stages the image's distinct AC tables only
+    im.nac = 0;
+    for (int c = 0; c < pj.ncomp; ++c) {
+        int s = 0;
+        for (; s < im.nac; ++s)
+            if (im.ac_pool[s] == ac_tab[c])
+                break;
+        if (s == im.nac)
+            im.ac_pool[im.nac++] = ac_tab[c];
+        im.ac_slot[c] = s;
+    }
     const uint32_t mcus = uint32_t(im.mcus_x) * uint32_t(im.mcus_y);
     im.total_blocks = mcus * uint32_t(im.bpm);
     im.restart_interval = pj.restart_interval;
@@ -220,12 +231,6 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     plan.total_subseq += im.subseq_cta_count * kSubseqCta;
     plan.map_subseq.push_back(im.subseq_cta_first + im.subseq_cta_count);
 
-    // coefficient records: one per entropy-coded symbol (DC, AC, ZRL, end of block).  A symbol takes at least one bit (an
-    // optimised table may give the end-of-block or the zero DC category a 1-bit code, and a flat block is just those two), so
-    // the reservation is one record per bit plus the per-subsequence rounding.  Only the part that is written is ever touched.
-    im.rec_off = plan.rec_elems;
-    im.rec_cap = uint32_t(std::min<uint64_t>(uint64_t(im.raw_len) * 8 + uint64_t(im.subseq_cta_count) * kSubseqCta * kRecAlign + 64, 0xFFFFFF00ull));
-    plan.rec_elems = align_up(plan.rec_elems + im.rec_cap, 64);
     im.coef_off = plan.coef_elems;
     plan.coef_elems = align_up(plan.coef_elems + uint64_t(im.total_blocks) * 64, 64);
     uint64_t blocks_out = 0;
@@ -267,7 +272,6 @@ void plan_finish(BatchPlan& plan)
     plan.raw_bytes = align_up(plan.raw_bytes + 64, 256);
     plan.clean_bytes = align_up(plan.clean_bytes + 64, 256);
     plan.coef_elems = align_up(plan.coef_elems + 64, 128);
-    plan.rec_elems = align_up(plan.rec_elems + 64, 128);
     plan.plane_bytes = align_up(plan.plane_bytes + 64, 256);
 }
 

@@ -8,17 +8,18 @@
 //   H1 k_huff_sync x 2   self-synchronising subsequence decode (no output): round 0 from a guessed state, round 1 from the
 //                        predecessor's exit state; subsequences whose exit state changed feed a work list
 //   H2 k_huff_sync_tail  cooperative kernel: Jacobi rounds over the (compacted) work list until it is empty
-//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute write position per subsequence
-//   H4 k_huff_write      final decode pass: every AC symbol becomes a 16-bit coefficient record (8-byte stores from a
-//                        register queue), every DC symbol stores the block's DC difference and first record index
+//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute block position per subsequence
+//   H4 k_huff_write      block pass: per block the DC difference and the bit position of its first AC symbol
 //   D1 k_dc_scan         per image: DC prediction = segmented (restart interval) prefix sum per component over dc[]
-//   I1 k_idct            coefficient records -> dense block in shared memory, dequantise + islow IDCT, one 8x8 block per
-//                        thread, writes component planes
+//   I1 k_idct            one 8x8 block per thread: Huffman-decode the block's AC symbols from the stream into a dense block
+//                        in shared memory, dequantise + islow IDCT, write the component planes -- coefficients never leave
+//                        the SM
 //   C1 k_color           upsample (fancy / box) + YCbCr->RGB; a warp produces 512 pixels x (1|2) rows, staged in shared
 //                        memory and written with fully coalesced 128-byte store instructions at any alignment
 // The per-thread arithmetic lives in huffman.cuh / jpeg_math.cuh (shared with the CPU emulation used by the tests).
 #include <cuda_runtime.h>
 #include "decode_kernels.h"
+#include "huffman.cuh"
 #include "jpeg_math.cuh"
 #include "cta_lookup.cuh"
 
@@ -358,29 +359,34 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// IDCT: one block per thread.  Each thread expands its block's coefficient records (sequential uint16 reads from the
-// record stream the Huffman write pass produced) into its own dense 8x8 slot in shared memory (row pitch 144 bytes:
-// conflict free for 16-byte accesses) and reads the slot back as the IDCT input.
+// IDCT: one block per thread.  The block pass left, per block, the bit position of its first AC symbol; the thread decodes
+// those symbols itself (huffman.cuh decode_block_ac: the image's AC tables staged in shared memory, the stream read through
+// L1) straight into its own dense 8x8 slot in shared memory (row pitch 144 bytes: conflict free for 16-byte accesses) and
+// reads the slot back as the IDCT input.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kIdctPitch = 144;
 #ifndef B2J_IDCT_MIN_CTAS
-#define B2J_IDCT_MIN_CTAS 8 // resident CTAs per SM the register allocation aims at
+#define B2J_IDCT_MIN_CTAS 4 // resident CTAs per SM the register allocation aims at
 #endif
-__constant__ uint8_t c_zz_next[kRecZigzagInit] = B2J_ZIGZAG_NEXT_INIT;
 __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b)
 {
-    __shared__ __align__(16) uint8_t s_blk[kIdctCta * kIdctPitch];
-    __shared__ uint16_t s_q[3 * 64];
-    __shared__ uint8_t s_zz[kRecZigzagNextSize];
+    extern __shared__ __align__(16) uint8_t s_dyn[];
+    uint8_t* s_blk = s_dyn;                                                                // kIdctCta * kIdctPitch
+    uint16_t* s_q = reinterpret_cast<uint16_t*>(s_dyn + kIdctCta * kIdctPitch);            // 3 * 64
+    uint16_t* s_lut = s_q + 3 * 64;                                                        // up to 3 AC tables
     const uint32_t cta_abs = blockIdx.x + b.base_idct;
     const int img = find_image_warp(b.cta_map_idct, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     for (int i = threadIdx.x; i < im.ncomp_out * 64; i += kIdctCta)
         s_q[i] = b.quant[im.qt[i >> 6] * 64 + (i & 63)];
+    if (!b.dense_coef)
+        for (int s = 0; s < im.nac; ++s) {
+            const uint4* src = reinterpret_cast<const uint4*>(b.huff[im.ac_pool[s]].lut);
+            for (int i = threadIdx.x; i < kLutEntries / 8; i += kIdctCta)
+                reinterpret_cast<uint4*>(s_lut + s * kLutEntries)[i] = __ldg(src + i);
+        }
     const uint32_t u = (cta_abs - b.cta_map_idct[img]) * kIdctCta + threadIdx.x;
     const IdctBlockRef ref = idct_locate(im, u);
-    for (int i = threadIdx.x; i < kRecZigzagNextSize; i += kIdctCta)
-        s_zz[i] = zigzag_next_entry(c_zz_next, i);
     __syncthreads();
     if (ref.comp < 0)
         return;
@@ -391,24 +397,30 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
             ref.by * sy >= im.roi_y + im.roi_h + 8)
             return;
     }
-    // the thread's own slot: zero it, scatter the block's coefficient records into it, read it back as a dense block
     uint8_t* slot = s_blk + threadIdx.x * kIdctPitch;
+    if (b.dense_coef) { // multi-scan streams: the scans were accumulated into dense coefficients
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
-        reinterpret_cast<uint4*>(slot)[i] = make_uint4(0, 0, 0, 0);
-    {
-        const uint32_t* first_rec = b.blk_rec + im.coef_off / 64 + ref.src_blk;
-        const uint32_t total = min(b.states[img].rec_total, im.rec_cap);
-        const uint32_t c = first_rec[0];
-        const uint32_t e = ref.src_blk + 1u < im.total_blocks ? first_rec[1] - 1u : total; // up to the next block's DC padding
-        if (records_to_block(b.rec + im.rec_off, min(c, total), min(e, total), s_zz, reinterpret_cast<int16_t*>(slot)))
-            atomicOr(&b.states[img].error, kErrBadCode);
+        for (int i = 0; i < 8; ++i)
+            reinterpret_cast<uint4*>(slot)[i] = reinterpret_cast<const uint4*>(b.coef + im.coef_off + uint64_t(ref.src_blk) * 64)[i];
+    } else {
+        // the thread's own slot: zero it, decode the block's AC symbols into it, read it back as a dense block
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            reinterpret_cast<uint4*>(slot)[i] = make_uint4(0, 0, 0, 0);
+        const uint32_t clean_len = b.states[img].clean_len;
+        const uint32_t p = b.blk_pos[im.coef_off / 64 + ref.src_blk];
+        uint32_t err = kErrOverrun; // a block the block pass never reached has no position: its image is reported failed
+        if (ref.src_blk < b.states[img].done_blocks && p < clean_len * 8u)
+            err = decode_block_ac(reinterpret_cast<const uint32_t*>(b.clean + im.clean_off), (im.raw_len + 12u) >> 2, p, s_lut,
+                uint32_t(im.ac_slot[ref.comp]) * kLutEntries, b.huff + im.ac_pool[im.ac_slot[ref.comp]], reinterpret_cast<int16_t*>(slot));
+        if (err)
+            atomicOr(&b.states[img].error, err);
     }
     alignas(16) int16_t blk[64];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
         reinterpret_cast<uint4*>(blk)[i] = reinterpret_cast<const uint4*>(slot)[i];
-    if (b.dump_coef) { // debug tap: the dense coefficients as the reference holds them (DC slot unused)
+    if (b.dump_coef && !b.dense_coef) { // debug tap: the dense coefficients as the reference holds them (DC slot unused)
 #pragma unroll
         for (int i = 0; i < 8; ++i)
             reinterpret_cast<uint4*>(b.coef + im.coef_off + uint64_t(ref.src_blk) * 64)[i] = reinterpret_cast<const uint4*>(blk)[i];
@@ -456,9 +468,16 @@ int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
     return 1;
 }
 
+static size_t idct_smem_bytes() { return size_t(kIdctCta) * kIdctPitch + 3 * 64 * 2 + 3 * size_t(kLutEntries) * 2; }
+
+int idct_configure()
+{
+    return cudaFuncSetAttribute(k_idct, cudaFuncAttributeMaxDynamicSharedMemorySize, int(idct_smem_bytes())) == cudaSuccess ? 0 : -1;
+}
+
 int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
 {
-    k_idct<<<d.idct_ctas, kIdctCta, 0, st>>>(b);
+    k_idct<<<d.idct_ctas, kIdctCta, idct_smem_bytes(), st>>>(b);
     return 1;
 }
 

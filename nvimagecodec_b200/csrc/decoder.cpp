@@ -95,7 +95,7 @@ Decoder::~Decoder()
 {
     if (device_ >= 0)
         cudaSetDevice(device_);
-    DevBuf* dbufs[] = {&d_records_, &d_blkrec_, &d_nrec_, &d_recoff_, &d_raw_, &d_clean_, &d_coef_, &d_dc_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
+    DevBuf* dbufs[] = {&d_blkpos_, &d_stamp_, &d_raw_, &d_clean_, &d_coef_, &d_dc_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
         &d_rec_, &d_abs_, &d_wl0_, &d_wl1_, &d_sync_, &d_out_};
     for (cudaStream_t st : streams_)
         if (st)
@@ -147,6 +147,10 @@ int Decoder::init()
         B2J_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     B2J_CUDA(cudaEventCreateWithFlags(&ev_meta_, cudaEventDisableTiming));
     B2J_CUDA(cudaDeviceGetAttribute(&sm_count_, cudaDevAttrMultiProcessorCount, device_));
+    if (idct_configure() != 0) {
+        log_message(kLogError, "cannot configure the IDCT kernel: %s", cudaGetErrorString(cudaGetLastError()));
+        return B200JPEG_STATUS_CUDA_ERROR;
+    }
     if (opt_.profile)
         for (cudaEvent_t& e : ev_stage_)
             B2J_CUDA(cudaEventCreate(&e));
@@ -310,9 +314,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     int rc = 0;
     if ((rc = ensure(d_raw_, plan_.raw_bytes)) || (rc = ensure(d_clean_, plan_.clean_bytes)) ||
         (opt_.dump_coef && (rc = ensure(d_coef_, plan_.coef_elems * sizeof(int16_t)))) ||
-        (rc = ensure(d_dc_, plan_.coef_elems / 64 * sizeof(int16_t) + 64)) || (rc = ensure(d_records_, plan_.rec_elems * sizeof(uint16_t))) ||
-        (rc = ensure(d_blkrec_, plan_.coef_elems / 64 * sizeof(uint32_t) + 64)) || (rc = ensure(d_nrec_, 4 * size_t(plan_.total_subseq))) ||
-        (rc = ensure(d_recoff_, 4 * size_t(plan_.total_subseq))) ||
+        (rc = ensure(d_dc_, plan_.coef_elems / 64 * sizeof(int16_t) + 64)) ||
+        (rc = ensure(d_blkpos_, plan_.coef_elems / 64 * sizeof(uint32_t) + 64)) || (rc = ensure(d_stamp_, 4 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_planes_, plan_.plane_bytes)) ||
         (rc = ensure(d_states_, sizeof(ImageState) * m)) || (rc = ensure(d_seg_, sizeof(uint32_t) * (plan_.total_segs + 1))) ||
         (rc = ensure(d_chunks_, sizeof(uint64_t) * plan_.total_chunks)) || (rc = ensure(d_exit_, 8 * size_t(plan_.total_subseq))) ||
@@ -373,10 +376,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.sync = static_cast<SyncCounters*>(d_sync_.p);
     dev_.coef = static_cast<int16_t*>(d_coef_.p);
     dev_.dump_coef = opt_.dump_coef ? 1 : 0;
-    dev_.rec = static_cast<uint16_t*>(d_records_.p);
-    dev_.blk_rec = static_cast<uint32_t*>(d_blkrec_.p);
-    dev_.sub_nrec = static_cast<uint32_t*>(d_nrec_.p);
-    dev_.sub_rec_off = static_cast<uint32_t*>(d_recoff_.p);
+    dev_.blk_pos = static_cast<uint32_t*>(d_blkpos_.p);
+    dev_.sub_stamp = static_cast<uint32_t*>(d_stamp_.p);
     dev_.dc = static_cast<int16_t*>(d_dc_.p);
     dev_.planes = static_cast<uint8_t*>(d_planes_.p);
     dev_.cta_map_unstuff = reinterpret_cast<const uint32_t*>(dm + off_m0 + 0 * map_bytes);
@@ -768,7 +769,6 @@ int Decoder::finish(int32_t* statuses)
             std::fprintf(stderr, "\n");
         }
     }
-    stat_record_bytes_ = 0;
     for (int i = 0; i < m; ++i) {
         const int bi = planned_to_batch_[i];
         if (hs[i].error || hs[i].done_blocks != plan_.images[i].total_blocks) {
@@ -777,7 +777,6 @@ int Decoder::finish(int32_t* statuses)
                 std::fprintf(stderr, "b200jpeg: image %d: error flags 0x%x, %u of %u blocks\n", bi, hs[i].error, hs[i].done_blocks,
                     plan_.images[i].total_blocks);
         }
-        stat_record_bytes_ += uint64_t(hs[i].rec_total) * sizeof(uint16_t);
     }
     return B200JPEG_STATUS_SUCCESS;
 }
@@ -882,7 +881,7 @@ void Decoder::get_stats(uint64_t* s) const
     s[5] = scratch_bytes_;
     s[6] = stat_redone_;
     s[7] = plan_.out_bytes;
-    s[8] = stat_record_bytes_;
+    s[8] = 0;
     for (int i = 9; i < 16; ++i)
         s[i] = 0;
 }

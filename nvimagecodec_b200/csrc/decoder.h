@@ -169,7 +169,7 @@ class Decoder
     int batch_size_ = 0;
     std::vector<HostOutput> host_outs_;
 
-    DevBuf d_records_, d_blkrec_, d_nrec_, d_recoff_, d_raw_, d_clean_, d_coef_, d_dc_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_wl0_,
+    DevBuf d_blkpos_, d_stamp_, d_raw_, d_clean_, d_coef_, d_dc_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_wl0_,
         d_wl1_, d_sync_, d_out_;
     DevBuf h_raw_, h_meta_, h_states_;
     BatchDev dev_{};
@@ -181,7 +181,7 @@ class Decoder
     std::vector<size_t> stage_group_end_; // per group: end of its items
     size_t scratch_bytes_ = 0;
 
-    uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_record_bytes_ = 0, stat_redone_ = 0;
+    uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_redone_ = 0;
     int tail_capacity_ = 0, sm_count_ = 0, cfg_lut_slots_ = -1, cfg_stream_words_ = -1;
 };
 

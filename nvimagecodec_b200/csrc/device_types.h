@@ -22,7 +22,7 @@ constexpr int kTailCta = 256;         // threads per CTA of the work-list rounds
 constexpr int kUnstuffThreads = 256;  // threads per CTA in the unstuffing kernels
 constexpr int kUnstuffBytesPerThread = 16;
 constexpr int kChunkBytes = kUnstuffThreads * kUnstuffBytesPerThread; // raw bytes per unstuff CTA
-constexpr int kIdctCta = 128;        // threads per CTA, one 8x8 block per thread
+constexpr int kIdctCta = 256;        // threads per CTA, one 8x8 block per thread
 constexpr int kColorCta = 128;       // threads per CTA: 4 warps, each warp one tile of 512 pixels x (1|2) rows
 constexpr int kColorTilePx = 512;    // pixels per warp tile (16 per lane)
 constexpr int kDcCta = 512;          // threads per CTA, one MCU per thread per iteration
@@ -102,10 +102,13 @@ struct ImageDesc
     uint32_t subseq_cta_first, subseq_cta_count;
     uint32_t seg_first;   // index into the segment-start pool; entries [seg_first, seg_first + num_segments]
 
+    // Huffman tables of the reconstruction kernel: it decodes the AC symbols of a block itself and stages only AC tables
+    int32_t nac;              // distinct AC tables of the image
+    int32_t ac_pool[3];       // their pool indices; slot s sits at s * kLutEntries of the kernel's staged LUTs
+    int32_t ac_slot[3];       // per component: slot of its AC table
+
     // intermediates
-    uint64_t rec_off;         // first coefficient record of this image in the record buffer (uint16 units, multiple of 8)
-    uint32_t rec_cap;         // records reserved for the image
-    uint64_t coef_off;        // int16 units, blocks in MCU scan order (coef_off / 64 = first block in the DC / block-record arrays)
+    uint64_t coef_off;        // int16 units, blocks in MCU scan order (coef_off / 64 = first block in the DC / block-position arrays)
     uint64_t plane_off[3];    // bytes
     int32_t plane_pitch[3];
     uint32_t idct_cta_first, idct_cta_count;
@@ -132,7 +135,7 @@ struct ImageState
     uint32_t marker_count;  // RSTn markers seen
     uint32_t error;         // bit flags, see kErr*
     uint32_t done_blocks;   // set by the thread that completes the last block (== total_blocks when the scan is complete)
-    uint32_t rec_total;     // coefficient records of the image (after the subsequence scan)
+    uint32_t reserved0;
     uint32_t trunc;         // raw_len - position of the first marker other than RSTn inside the scan data (0: none)
     uint32_t raw_eff;       // entropy-coded bytes actually taken: raw_len - trunc
     uint32_t pad_[1];
@@ -142,16 +145,6 @@ constexpr uint32_t kErrBadMarker = 1;     // wrong RSTn order / count
 constexpr uint32_t kErrBadCode = 2;       // invalid Huffman code on the synchronised path
 constexpr uint32_t kErrNotConverged = 4;  // subsequence synchronisation incomplete
 constexpr uint32_t kErrOverrun = 8;       // decode ran past the end of a segment / image
-constexpr uint32_t kErrRecords = 16;      // more coefficient records than reserved (cannot happen for whole symbols: one record per bit is reserved)
-
-// Coefficient records: what the Huffman write pass hands to the IDCT kernel, one uint16 per AC symbol in stream order
-//   run << 12 | (value & 0xFFF)   a coefficient `value` (never 0) after `run` zeros
-//   kRecZrl                       sixteen zeros
-//   kRecEnd                       end of block (the EOB symbol)
-//   kRecPad                       filler at the end of a subsequence's record range, skipped by the reader
-// A block whose last coefficient sits at zigzag position 63 has no kRecEnd: the reader stops at position 64.
-constexpr uint32_t kRecZrl = 0xF000u, kRecEnd = 0x0000u, kRecPad = 0x0800u;
-constexpr uint32_t kRecAlign = 4;         // records per 8-byte store: every subsequence's range is a multiple of this
 
 // State of the Huffman decoder between two symbols, packed in 64 bits: bit position | (block-in-MCU * 64 + zigzag index) << 32
 B2J_HD unsigned long long pack_state(uint32_t p, uint32_t slot) { return (unsigned long long)p | ((unsigned long long)slot << 32); }
@@ -188,20 +181,17 @@ struct BatchDev // pointers handed to every kernel
     uint64_t* chunk_counts; // per unstuff chunk: kept bytes | markers << 32  (then exclusive-scanned in place)
     unsigned long long* sub_exit;   // per subsequence: decoder state after its last symbol
     unsigned long long* sub_entry;  // state the last decode of that subsequence started from
-    uint32_t* sub_rec;      // coefficient slots consumed by that decode; bit31: absolute (a restart boundary was crossed)
+    uint32_t* sub_rec;      // coefficient slots (64 per block) consumed by that decode; bit31: absolute (a restart boundary was crossed)
     uint32_t* sub_abs;      // inclusive scan of sub_rec: absolute slot count at the subsequence's exit
     uint32_t* worklist[2];  // subsequences whose entry changed (global subsequence indices)
     SyncCounters* sync;
-    uint32_t* sub_nrec;     // per subsequence: AC symbols (= coefficient records) its last decode produced
-    uint32_t* sub_rec_off;  // exclusive scan of sub_nrec rounded up to kRecAlign: first record of the subsequence in the image.
-                            // Until k_subseq_scan writes it the array holds the work-list stamps of the synchronisation
-                            // rounds: the subsequence is an item of work-list round r iff stamp >= r + 1 (r + 2 once it has
-                            // also been listed for round r + 1)
-    uint16_t* rec;          // coefficient records of all images (ImageDesc::rec_off)
-    uint32_t* blk_rec;      // per block: index of its first record inside the image's records
+    uint32_t* sub_stamp;    // work-list stamps of the synchronisation rounds: the subsequence is an item of work-list round r
+                            // iff stamp >= r + 1 (r + 2 once it has also been listed for round r + 1)
+    uint32_t* blk_pos;      // per block: bit position of its first AC symbol in the image's unstuffed stream (block pass)
+    int32_t dense_coef;     // the IDCT kernel takes dense coefficients from coef[] (multi-scan streams) instead of decoding AC symbols
     int32_t dump_coef;      // debug: the IDCT kernel also writes the dense coefficients it reconstructed to coef[]
     int16_t* coef;          // debug tap (dump_coef): AC coefficients, natural order, 64 per block (slot 0 unused: the DC lives in dc[])
-    int16_t* dc;            // per block: DC difference after the write pass, DC value after the DC scan
+    int16_t* dc;            // per block: DC difference after the block pass, DC value after the DC scan
     uint8_t* planes;
     const uint32_t* cta_map_unstuff; // prefix arrays: first CTA of each image (+ total at [num_images])
     const uint32_t* cta_map_subseq;

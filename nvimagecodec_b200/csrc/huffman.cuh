@@ -119,47 +119,18 @@ struct HuffState
     uint32_t z;      // zigzag index inside the current block (0 = the DC symbol is next)
     uint32_t blk;    // block inside the MCU
     uint32_t nblk;   // blocks completed: absolute block index of the current block if abs, else relative to the entry
-    uint32_t nrec;   // symbols decoded = records the write pass emits for the same span
     bool abs;
 };
 
-// Where the write pass puts what it decodes (all pointers are per image).  Every symbol pushes exactly one record (a DC
-// symbol pushes padding) so the loop has no data-dependent branch around the queue; records go out eight bytes at a time
-// from a 64-bit register queue: the stores of a warp's lanes hit 32 different lines whatever we do, so there should be few.
-struct RecOut
+// Where the block pass puts what it finds (pointers are per image): for every block the DC difference and the bit position
+// of its first AC symbol.  The AC symbols themselves are decoded by the thread that reconstructs the block
+// (decode_block_ac below, called from the IDCT kernel): coefficients never travel through memory.
+struct BlkOut
 {
-    uint16_t* rec;      // the image's records
-    uint32_t* blk_rec;  // per block: index of its first record
     int16_t* dc;        // per block: DC difference
-    uint32_t cursor;    // next record index; starts at the subsequence's offset (a multiple of kRecAlign)
-    uint32_t limit;     // end of the subsequence's range: records past it are dropped (only a corrupt stream gets there)
-    uint32_t qlo, qhi;  // the last records, oldest in the low half of qlo
-
-    B2J_HD void push(uint32_t r)
-    {
-        qlo = (qlo >> 16) | (qhi << 16);
-        qhi = (qhi >> 16) | (r << 16);
-        ++cursor;
-        if ((cursor & (kRecAlign - 1u)) == 0 && cursor <= limit) {
-#if defined(__CUDA_ARCH__)
-            asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(rec + cursor - kRecAlign), "r"(qlo), "r"(qhi) : "memory");
-#else
-            *reinterpret_cast<uint2*>(rec + cursor - kRecAlign) = make_uint2(qlo, qhi);
-#endif
-        }
-    }
-    B2J_HD void finish() // fill the range with padding records
-    {
-        while (cursor < limit)
-            push(kRecPad);
-    }
+    uint32_t* pos;      // per block: bit position (in the image's unstuffed stream) right behind the DC symbol
 };
 
-// value bits -> coefficient (HUFF_EXTEND, ljt/jdhuff.c:483-488) and the record of the symbol, without branches.
-// t = stream window shifted so that the first value bit is bit 31; sz = number of value bits; zadv from the table entry.
-// A first value bit of 1 means a positive coefficient equal to the sz bits; a 0 means minus the complement of the sz bits.
-// The record of a DC symbol is never read (a block's record range starts after it, jpeg_math.cuh records_to_block): it
-// is whatever the same formula yields.
 B2J_HD uint32_t shr_upto32(uint32_t x, uint32_t n) // x >> n for n in [0, 32]
 {
 #if defined(__CUDA_ARCH__)
@@ -169,25 +140,25 @@ B2J_HD uint32_t shr_upto32(uint32_t x, uint32_t n) // x >> n for n in [0, 32]
 #endif
 }
 
-B2J_HD uint32_t make_record(uint32_t t, uint32_t sz, uint32_t zadv, int& val)
+// value bits -> coefficient (HUFF_EXTEND, ljt/jdhuff.c:483-488) without branches.  t = stream window shifted so that the
+// first value bit is bit 31; sz = number of value bits.  A first value bit of 1 means a positive coefficient equal to the sz
+// bits; a 0 means the sz bits minus (2^sz - 1).  sz == 0 yields 0.
+B2J_HD int huff_extend(uint32_t t, uint32_t sz)
 {
-    const uint32_t pos = uint32_t(int(t) >> 31);           // all ones for a positive coefficient
-    const uint32_t mag = shr_upto32(t ^ ~pos, 32u - sz);   // magnitude; 0 when there are no value bits
-    val = int((mag ^ ~pos) + pos + 1u);                    // (mag ^ m) - m with m = ~pos: mag or -mag
-    const uint32_t r = (((zadv - 1u) << 12) | (uint32_t(val) & 0xFFFu)) & 0xFFFFu; // ZRL (sz 0, zadv 16) comes out as kRecZrl
-    return zadv == 64u ? kRecEnd : r;
+    const uint32_t v = shr_upto32(t, 32u - sz);
+    const uint32_t neg = ~uint32_t(int(t) >> 31); // all ones when the first value bit is 0
+    return int(v) - int(neg & ((1u << sz) - 1u));
 }
 
 // Decode every symbol that starts in [s.p, end) (segment changes included), beginning in state s.
-// WRITE = false: synchronisation pass, nothing is stored; s.nrec counts the symbols.
-// WRITE = true : s.abs must hold.  Every symbol becomes a record in `out` (AC: coefficient / ZRL / end of block, DC:
-//                padding); a DC symbol also stores the DC difference of its block and the index of the block's first
-//                coefficient record.  Returns error flags.
+// WRITE = false: synchronisation pass, nothing is stored.
+// WRITE = true : block pass, s.abs must hold.  Every DC symbol stores the DC difference of its block and the bit position
+//                behind it (where the block's AC symbols start).  Returns error flags.
 // DIRECT selects the inner loop used well inside a segment: true = both stream words fetched from shared memory per
 // symbol (fewest instructions: the throughput kernels, whose warps hide the extra latency), false = sliding window in
 // registers (shortest dependency chain: the latency-bound work-list rounds).
 template <bool WRITE, bool PRESWAPPED = false, bool DIRECT = true>
-B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecOut* out)
+B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, BlkOut* out)
 {
     if (end > env.clean_bits)
         end = env.clean_bits;
@@ -214,7 +185,7 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
             s.blk = 0;
         }
     }
-    uint32_t p = s.p, z = s.z, blk = s.blk, nblk = s.nblk, nrec = s.nrec;
+    uint32_t p = s.p, z = s.z, blk = s.blk, nblk = s.nblk;
     for (;;) {
         const bool last = (g == nseg - 1);
         const uint32_t B = last ? env.clean_bits : env.seg[g + 1] * 8u; // end of this segment's bits
@@ -239,19 +210,12 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
                         err |= kErrBadCode;
                 }
                 const uint32_t tot = e & 31u, zadv = e >> 9;
-                if (WRITE) {
-                    const uint32_t sz = (e >> 5) & 15u;
-                    int val;
-                    const uint32_t r = make_record(win << (tot - sz), sz, zadv, val);
-                    out->push(r);
-                    if (z == 0) {
-                        out->dc[nblk] = int16_t(val);
-                        out->blk_rec[nblk] = out->cursor;
-                    }
-                } else {
-                    ++nrec;
-                }
                 p += tot;
+                if (WRITE && z == 0) {
+                    const uint32_t sz = (e >> 5) & 15u;
+                    out->dc[nblk] = int16_t(huff_extend(win << (tot - sz), sz));
+                    out->pos[nblk] = p;
+                }
                 z += zadv;
                 if (z >= 64u) {
                     z = 0;
@@ -289,16 +253,9 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
             }
             if (WRITE && bad)
                 err |= kErrBadCode;
-            if (WRITE) {
-                int val;
-                const uint32_t r = make_record(win << (tot - sz), sz, zadv, val);
-                out->push(r);
-                if (z == 0) {
-                    out->dc[nblk] = int16_t(val);
-                    out->blk_rec[nblk] = out->cursor;
-                }
-            } else {
-                ++nrec;
+            if (WRITE && z == 0) {
+                out->dc[nblk] = int16_t(huff_extend(win << (tot - sz), sz));
+                out->pos[nblk] = newp;
             }
             z += zadv;
             p = newp;
@@ -348,7 +305,58 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, RecO
     s.z = z;
     s.blk = blk;
     s.nblk = nblk;
-    s.nrec = nrec;
+    return err;
+}
+
+// AC coefficients of one block straight from the stream (ljt/jdhuff.c decode_mcu_slow:598-640): p = bit position of the
+// block's first AC symbol (BlkOut::pos).  words = the image's unstuffed stream as stored (byte order of the file), readable
+// up to word index max_word; lut / ac_off / tab = the block's AC table as staged by the caller.  blk = 64 natural-order
+// coefficients, zeroed by the caller (entry 0 is not touched: the DC value travels separately).  Returns error flags
+// (an invalid code, or a coefficient behind position 63: corrupt data).  At most 63 symbols are read whatever the bits say.
+B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32_t p, const uint16_t* lut, uint32_t ac_off,
+    const DevHuffTable* tab, int16_t* blk)
+{
+    uint32_t widx = p >> 5;
+    if (widx > max_word)
+        return kErrOverrun;
+    auto load = [&](uint32_t i) {
+        i = i > max_word ? max_word : i;
+#if defined(__CUDA_ARCH__)
+        return bswap32(__ldg(words + i));
+#else
+        return bswap32(words[i]);
+#endif
+    };
+    uint32_t w0 = load(widx), w1 = load(widx + 1), w2 = load(widx + 2);
+    uint32_t z = 1, err = 0;
+    while (z < 64u) {
+        const uint32_t win = funnel_left(w0, w1, p);
+        uint32_t e = lut[ac_off + (win >> (32 - kLutBits))];
+        if ((e & 31u) == 0) { // code longer than kLutBits
+            bool ok = true;
+            e = huff_long_entry(lut, ac_off, e, tab, win, ok);
+            if (!ok)
+                err |= kErrBadCode;
+        }
+        const uint32_t tot = e & 31u, sz = (e >> 5) & 15u, zadv = e >> 9;
+        if (zadv == 64u)
+            break; // end of block
+        if (sz) { // a coefficient after zadv - 1 zeros (a ZRL symbol has no value bits and just moves on by 16)
+            const uint32_t k = z + zadv - 1u;
+            if (k < 64u)
+                blk[B2J_ZZ(k)] = int16_t(huff_extend(win << (tot - sz), sz));
+            else
+                err |= kErrBadCode;
+        }
+        z += zadv;
+        p += tot;
+        if ((p >> 5) != widx) {
+            ++widx;
+            w0 = w1;
+            w1 = w2;
+            w2 = load(widx + 2);
+        }
+    }
     return err;
 }
 

@@ -3,10 +3,10 @@
 //   H1 k_huff_sync x 2   self-synchronising subsequence decode (no output): round 0 from a guessed state, round 1 from the
 //                        predecessor's exit state; subsequences whose exit state changed feed a work list
 //   H2 k_huff_sync_tail  cooperative kernel: Jacobi rounds over the (compacted) work list until it is empty
-//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute block position per subsequence,
-//                        scan of record counts -> record offset per subsequence
-//   H4 k_huff_write      final decode pass: every AC symbol becomes a 16-bit coefficient record (8-byte stores from a
-//                        register queue), every DC symbol stores the block's DC difference and first record index
+//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute block position per subsequence
+//   H4 k_huff_write      block pass: a last decode from the agreed entry states that stores, for every block, the DC
+//                        difference and the bit position of its first AC symbol (the AC symbols are decoded by the thread
+//                        that reconstructs the block, decode_kernels.cu k_idct)
 // Shared memory layout of the decoding kernels (dynamic): [LUTs: lut_slots x 5 KB][TabSel x 8][stream staging].
 // The unstuffed stream of the CTA's subsequences is staged (byte-swapped to bit order) with coalesced loads; thread t
 // owns the words [t * W, (t + 1) * W) where W = stream_words is odd, so threads at the same position of their
@@ -100,7 +100,6 @@ __device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& en
     s.z = slot & 63u;
     s.blk = slot >> 6;
     s.nblk = 0;
-    s.nrec = 0;
     s.abs = exact;
     const uint32_t z_entry = s.z;
     decode_span<false, PRESWAPPED, DIRECT>(env, s, (k + 1u) * uint32_t(b.subseq_bits), nullptr);
@@ -110,7 +109,6 @@ __device__ __forceinline__ bool sync_decode(const BatchDev& b, const HuffEnv& en
         *exit_state = X;
     b.sub_exit[t] = X;
     b.sub_entry[t] = E;
-    b.sub_nrec[t] = s.nrec;
     // slots consumed: absolute (from the image start) once a known state was passed, else relative to the entry
     const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
     b.sub_rec[t] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
@@ -139,11 +137,10 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
     const uint32_t words_s = uint32_t(__cvta_generic_to_shared(sm.stream)) + (threadIdx.x * uint32_t(b.stream_words) - k * (S >> 5)) * 4u;
     const HuffEnv env = make_env(b, im, clean_len, words, sm.lut, sm.tabsel, words_s);
     if (round == 0) {
-        b.sub_rec_off[t] = 0; // work-list stamp: not an item of any round
+        b.sub_stamp[t] = 0; // not an item of any work-list round
         if (idle) {
             b.sub_exit[t] = b.sub_entry[t] = pack_state(clean_bits, 0);
             b.sub_rec[t] = 0;
-            b.sub_nrec[t] = 0;
             return;
         }
         b.sub_exit[t] = ~0ull;
@@ -163,7 +160,7 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
         if (changed && next_live) {
             const uint32_t i = atomicAdd(&b.sync->count[0], 1u);
             b.worklist[0][i] = t + 1;
-            b.sub_rec_off[t + 1] = 1u; // item of work-list round 0
+            b.sub_stamp[t + 1] = 1u; // item of work-list round 0
         }
     }
 }
@@ -194,7 +191,7 @@ __device__ __forceinline__ bool tail_round(const BatchDev& b, const HuffSmem& sm
         // Run-ahead rounds: only the head of a run of consecutive listed subsequences is worked on -- by one thread that walks
         // the whole run (every item of it is due) and on into the subsequences behind it for as long as exit states keep
         // changing.  The items behind the head are left to that thread.
-        if (run_ahead && __ldcg(b.sub_rec_off + t - 1) >= uint32_t(r) + 1u)
+        if (run_ahead && __ldcg(b.sub_stamp + t - 1) >= uint32_t(r) + 1u)
             continue;
         const int img = int(__ldg(b.subseq_cta_img + t / kSubseqCta)) - b.image_base;
         const ImageDesc& im = b.images[img];
@@ -226,7 +223,6 @@ __device__ __forceinline__ bool tail_round(const BatchDev& b, const HuffSmem& sm
                 changed = (X != __ldcg(b.sub_exit + t));
                 b.sub_exit[t] = X;
                 b.sub_entry[t] = E;
-                b.sub_nrec[t] = b.sub_nrec[t - 1];
                 b.sub_rec[t] = b.sub_rec[t - 1];
                 ++redone;
             } else if (W) {
@@ -265,15 +261,15 @@ __device__ __forceinline__ bool tail_round(const BatchDev& b, const HuffSmem& sm
             if (!run_ahead) { // Jacobi: a changed exit state makes the successor an item of the next round
                 if (changed) {
                     out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
-                    b.sub_rec_off[t + 1] = uint32_t(r) + 2u;
+                    b.sub_stamp[t + 1] = uint32_t(r) + 2u;
                 }
                 break;
             }
-            const bool next_listed = __ldcg(b.sub_rec_off + t + 1) >= uint32_t(r) + 1u;
+            const bool next_listed = __ldcg(b.sub_stamp + t + 1) >= uint32_t(r) + 1u;
             if (next_listed && !in_run) { // the head of another run: its thread may have read the old exit state
                 if (changed) {
                     out[atomicAdd(&b.sync->count[(r + 1) % 3], 1u)] = t + 1;
-                    b.sub_rec_off[t + 1] = uint32_t(r) + 2u;
+                    b.sub_stamp[t + 1] = uint32_t(r) + 2u;
                 }
                 break;
             }
@@ -378,59 +374,37 @@ __global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
     const ImageDesc& im = b.images[img];
     const uint32_t count = im.subseq_cta_count * kSubseqCta;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    __shared__ uint32_t s_w[kScanThreads / 32], s_r[kScanThreads / 32];
-    __shared__ uint32_t s_carry, s_rcarry;
-    if (threadIdx.x == 0) {
+    __shared__ uint32_t s_w[kScanThreads / 32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0)
         s_carry = 0x80000000u;
-        s_rcarry = 0;
-    }
     __syncthreads();
     bool bad = false;
     for (uint32_t c0 = 0; c0 < count; c0 += kScanThreads) {
         const uint32_t c = c0 + threadIdx.x;
         uint32_t v = c < count ? b.sub_rec[im.subseq_first + c] : 0u;
-        // coefficient records of the subsequence, rounded up to the store granularity (plain inclusive scan)
-        const uint32_t nr = c < count ? (b.sub_nrec[im.subseq_first + c] + kRecAlign - 1u) & ~(kRecAlign - 1u) : 0u;
-        uint32_t r = nr;
         if (c > 0 && c < count && b.sub_entry[im.subseq_first + c] != b.sub_exit[im.subseq_first + c - 1] &&
             uint64_t(c) * uint32_t(b.subseq_bits) < uint64_t(b.states[img].clean_len) * 8u)
             bad = true; // the chain of entry/exit states is not consistent: synchronisation did not finish
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, v, o);
-            const uint32_t rprev = __shfl_up_sync(0xFFFFFFFFu, r, o);
-            if (lane >= uint32_t(o)) {
+            if (lane >= uint32_t(o))
                 v = seg_combine(tprev, v);
-                r += rprev;
-            }
         }
-        if (lane == 31) {
+        if (lane == 31)
             s_w[warp] = v;
-            s_r[warp] = r;
-        }
         __syncthreads();
-        uint32_t pre = s_carry, rpre = s_rcarry;
-        for (int i = 0; i < int(warp); ++i) {
+        uint32_t pre = s_carry;
+        for (int i = 0; i < int(warp); ++i)
             pre = seg_combine(pre, s_w[i]);
-            rpre += s_r[i];
-        }
         v = seg_combine(pre, v);
-        r += rpre;
-        if (c < count) {
+        if (c < count)
             b.sub_abs[im.subseq_first + c] = v;
-            b.sub_rec_off[im.subseq_first + c] = r - nr;
-        }
         __syncthreads();
-        if (threadIdx.x == kScanThreads - 1) {
+        if (threadIdx.x == kScanThreads - 1)
             s_carry = v;
-            s_rcarry = r;
-        }
         __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        b.states[img].rec_total = s_rcarry;
-        if (s_rcarry > im.rec_cap)
-            atomicOr(&b.states[img].error, kErrRecords);
     }
     if (bad)
         atomicOr(&b.states[img].error, kErrNotConverged);
@@ -451,8 +425,6 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
     const uint32_t S = uint32_t(b.subseq_bits);
     if (uint64_t(k) * S >= uint64_t(clean_bits))
         return;
-    if (b.states[img].error & kErrRecords)
-        return; // the records would not fit (flagged by the scan): the image is reported as corrupt
     HuffState s;
     if (k == 0) {
         s.p = 0;
@@ -468,20 +440,9 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
         s.nblk = (b.sub_abs[t - 1] & 0x7FFFFFFFu) >> 6;
     }
     s.abs = true;
-    s.nrec = 0;
-    RecOut out;
-    {
-        // the record pointer as an opaque register pair: one wide multiply-add forms a store address from the cursor
-        // (left to itself the compiler re-derives the pointer from the descriptor at every store)
-        unsigned long long rp = reinterpret_cast<unsigned long long>(b.rec + im.rec_off);
-        asm volatile("mov.u64 %0, %0;" : "+l"(rp));
-        out.rec = reinterpret_cast<uint16_t*>(rp);
-    }
-    out.blk_rec = b.blk_rec + im.coef_off / 64;
+    BlkOut out;
     out.dc = b.dc + im.coef_off / 64;
-    out.cursor = b.sub_rec_off[t];
-    out.limit = out.cursor + ((b.sub_nrec[t] + kRecAlign - 1u) & ~(kRecAlign - 1u));
-    out.qlo = out.qhi = 0;
+    out.pos = b.blk_pos + im.coef_off / 64;
     const uint32_t nblk_in = s.nblk;
     uint32_t err;
     if (b.stream_words) {
@@ -492,9 +453,6 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
         const HuffEnv env = make_env(b, im, clean_len, reinterpret_cast<const uint32_t*>(b.clean + im.clean_off), sm.lut, sm.tabsel);
         err = decode_span<true, false>(env, s, (k + 1u) * S, &out);
     }
-    if (out.cursor > out.limit)
-        err |= kErrRecords;
-    out.finish();
     if (s.nblk == im.total_blocks && s.z == 0 && nblk_in < im.total_blocks)
         b.states[img].done_blocks = s.nblk; // this thread completed the last block
     if (err)

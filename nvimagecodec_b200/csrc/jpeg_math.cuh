@@ -17,89 +17,6 @@
 namespace b200jpeg {
 
 // ------------------------------------------------------------------------------------------------------------------
-// Coefficient records (device_types.h kRec*) of one block -> dense natural-order coefficients.  blk[] has kRecBlkSlots
-// entries and must be zeroed (entry 64 is a dump for out-of-range indices).  [c, e) = the block's records: c is the index
-// the write pass stored for the block, e the index of the next block's DC padding record (or the image's record count for
-// the last block), so the range holds the block's AC records, possibly an end-of-block record, and padding -- nothing of
-// any other block.  zzx = the table fill_zigzag_next makes.  blk[0] stays 0: the DC travels separately.  A ZRL record is
-// handled like a coefficient of value 0.  Returns true if a coefficient landed past position 63 or the range is longer
-// than any block's can be (corrupt stream).
-// The records are fetched 16 bytes (eight records) at a time, two fetches ahead of their use: the trip count is known up
-// front, so nothing about a fetch depends on the records before it.
-// ------------------------------------------------------------------------------------------------------------------
-constexpr int kRecBlkSlots = 72;
-constexpr uint32_t kRecMaxPerBlock = 256; // 63 coefficients + end of block + the padding of every subsequence boundary inside
-// zzx[n] = natural-order index of zigzag position n - 1 (jpeg_natural_order, ljt/jutils.c:59) for n <= 64, the dump slot after
-#define B2J_ZIGZAG_NEXT_INIT                                                                                                  \
-    {0, 0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, \
-        57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63}
-constexpr int kRecZigzagInit = 65;      // entries of B2J_ZIGZAG_NEXT_INIT
-constexpr int kRecZigzagNextSize = 208; // a position is checked once per eight records: it can pass 64 by 8 * 16 - 1, and the
-                                        // table is also read for the position a non-coefficient record would lead to (+ 16)
-
-B2J_HD uint8_t zigzag_next_entry(const uint8_t* init, int n) { return n < kRecZigzagInit ? init[n] : uint8_t(64); }
-
-B2J_HD uint4 rec_load8(const uint16_t* p) // eight records, p 16-byte aligned
-{
-#if defined(__CUDA_ARCH__)
-    return __ldg(reinterpret_cast<const uint4*>(p));
-#else
-    return *reinterpret_cast<const uint4*>(p);
-#endif
-}
-
-B2J_HD bool records_to_block(const uint16_t* rec, uint32_t c, uint32_t e, const uint8_t* zzx, int16_t* blk)
-{
-    if (c >= e)
-        return false; // a block the write pass never reached (its image is reported failed anyway)
-    bool bad = false;
-    if (e - c > kRecMaxPerBlock) {
-        e = c + kRecMaxPerBlock;
-        bad = true;
-    }
-    const uint32_t n = e - c, last = (e - 1u) & ~7u;
-    uint32_t base = c & ~7u, z = 1;
-    const uint4 zero = make_uint4(0, 0, 0, 0);
-#if defined(__CUDA_ARCH__)
-    // device: zzx and blk are in shared memory; their window addresses are taken once (left generic, the compiler
-    // re-derives the shared window for every access)
-    const uint32_t zz_s = uint32_t(__cvta_generic_to_shared(zzx)), blk_s = uint32_t(__cvta_generic_to_shared(blk));
-#endif
-    uint4 cur = rec_load8(rec + base);
-    uint4 nxt = base < last ? rec_load8(rec + base + 8) : zero;
-    for (;;) {
-        const uint4 ahead = base + 8u < last ? rec_load8(rec + base + 16) : zero;
-        const uint32_t d = base - c; // record i of this fetch is record d + i of the block (wraps for the ones before c)
-        const uint32_t w[4] = {cur.x, cur.y, cur.z, cur.w};
-        // Branch-free per record: a record that is no coefficient (padding, end of block, outside [c, e)) leaves z alone
-        // and stores into the dump slot.
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const uint32_t ww = w[i >> 1];
-            const uint32_t r = (i & 1) ? ww >> 16 : ww & 0xFFFFu;
-            const bool ok = d + uint32_t(i) < n && (r & 0xF7FFu) != 0; // neither kRecEnd nor kRecPad
-            const uint32_t zn = z + (r >> 12) + 1u;                    // position after this coefficient
-            const int val = (i & 1) ? int(ww << 4) >> 20 : int(ww << 20) >> 20;
-#if defined(__CUDA_ARCH__)
-            uint32_t nat;
-            asm("ld.shared.u8 %0, [%1];" : "=r"(nat) : "r"(zz_s + zn));
-            nat = ok ? nat : 64u;
-            asm volatile("st.shared.u16 [%0], %1;" ::"r"(blk_s + nat * 2u), "h"(uint16_t(val)) : "memory");
-#else
-            blk[ok ? zzx[zn] : 64] = int16_t(val);
-#endif
-            z = ok ? zn : z;
-        }
-        if (base == last || z >= 64u)
-            break;
-        cur = nxt;
-        nxt = ahead;
-        base += 8;
-    }
-    return bad || z > 64u;
-}
-
-// ------------------------------------------------------------------------------------------------------------------
 // Dequantise + 8x8 inverse DCT ("islow") of one block: in[64] natural-order coefficients (in[0] ignored, the DC value is
 // passed separately), q[64] natural-order quant values, out = 8 rows of 8 samples packed little-endian in two uint32
 // each.  int32 arithmetic: exact for every stream an 8-bit encoder can produce (the reference's JLONG is wider only for

@@ -57,8 +57,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     std::vector<int16_t> coef(plan.coef_elems, 0x5A5A), dcv(plan.coef_elems / 64 + 64, 0x5A5A); // poisoned: the kernels must zero what they own
     std::vector<uint32_t> seg(plan.total_segs + 1, 0), rec(plan.total_subseq, 0), sabs(plan.total_subseq, 0);
     std::vector<unsigned long long> ex(plan.total_subseq, 0), en(plan.total_subseq, 0);
-    std::vector<uint16_t> records(plan.rec_elems + 64, 0x5A5A); // poisoned
-    std::vector<uint32_t> blkrec(plan.coef_elems / 64 + 64, 0xDEADBEEFu), nrec(plan.total_subseq, 0), recoff(plan.total_subseq, 0);
+    std::vector<uint32_t> blkpos(plan.coef_elems / 64 + 64, 0xDEADBEEFu); // poisoned
     std::vector<ImageState> states(m);
     std::memset(states.data(), 0, sizeof(ImageState) * m);
     BatchDev b;
@@ -114,7 +113,6 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         s.z = slot & 63u;
         s.blk = slot >> 6;
         s.nblk = 0;
-        s.nrec = 0;
         s.abs = exact;
         const uint32_t z_entry = s.z;
         if (!clean_sw.empty()) { // the kernels' staged (byte-swapped) stream: exercises the fast synchronisation loop
@@ -129,7 +127,6 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         en[t] = E;
         const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
         rec[t] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
-        nrec[t] = s.nrec;
         return changed;
     };
     // ---- unstuffing + restart marker removal (what k_unstuff_count/scan/write compute) ----
@@ -190,7 +187,6 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                     if (idle) {
                         ex[t] = en[t] = pack_state(clean_bits, 0);
                         rec[t] = 0;
-                        nrec[t] = 0;
                         continue;
                     }
                     ex[t] = ~0ull;
@@ -245,7 +241,6 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                     changed = X != ex[t];
                     ex[t] = X;
                     en[t] = E;
-                    nrec[t] = nrec[t - 1];
                     rec[t] = rec[t - 1];
                     ++skipped;
                     ++redone;
@@ -295,23 +290,18 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     // ---- segmented scan of slot counts + consistency check (k_subseq_scan) ----
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
-        uint32_t A = 0x80000000u, R = 0;
+        uint32_t A = 0x80000000u;
         for (uint32_t k = 0; k < im.subseq_cta_count * kSubseqCta; ++k) {
             const uint32_t t = im.subseq_first + k;
-            recoff[t] = R;
-            R += (nrec[t] + kRecAlign - 1u) & ~(kRecAlign - 1u);
             if (k > 0 && en[t] != ex[t - 1] && uint64_t(k) * S < uint64_t(states[i].clean_len) * 8u)
                 states[i].error |= kErrNotConverged;
             const uint32_t r = rec[t];
             A = (r & 0x80000000u) ? r : A + r;
             sabs[t] = A;
         }
-        states[i].rec_total = R;
-        if (R > im.rec_cap)
-            states[i].error |= kErrRecords;
     }
-    // ---- write pass (k_huff_write): every subsequence emits its coefficient records, in reverse order to show that
-    // the threads do not depend on each other ----
+    // ---- block pass (k_huff_write): per block the DC difference and the position of its first AC symbol; the
+    // subsequences in reverse order to show that the threads do not depend on each other ----
     std::vector<uint8_t> clean_sw2 = clean_sw;
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
@@ -319,8 +309,6 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         HuffEnv env = make_env(i, true, s_lut);
         env.words = reinterpret_cast<const uint32_t*>(clean_sw2.data()) + (env.words - reinterpret_cast<const uint32_t*>(clean.data()));
         const uint32_t clean_bits = states[i].clean_len * 8u;
-        if (states[i].error & kErrRecords)
-            continue;
         for (int64_t k64 = int64_t(im.subseq_cta_count) * kSubseqCta - 1; k64 >= 0; --k64) {
             const uint32_t k = uint32_t(k64), t = im.subseq_first + k;
             if (uint64_t(k) * S >= uint64_t(clean_bits)) continue;
@@ -334,38 +322,33 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                 s.nblk = (sabs[t - 1] & 0x7FFFFFFFu) >> 6;
             }
             s.abs = true;
-            s.nrec = 0;
-            RecOut out;
-            out.rec = records.data() + im.rec_off;
-            out.blk_rec = blkrec.data() + im.coef_off / 64;
+            BlkOut out;
             out.dc = dcv.data() + im.coef_off / 64;
-            out.cursor = recoff[t];
-            out.limit = out.cursor + ((nrec[t] + kRecAlign - 1u) & ~(kRecAlign - 1u));
-            out.qlo = out.qhi = 0;
+            out.pos = blkpos.data() + im.coef_off / 64;
             const uint32_t nblk_in = s.nblk;
             uint32_t err = decode_span<true, true>(env, s, (k + 1u) * S, &out);
-            if (out.cursor > out.limit) err |= kErrRecords;
-            out.finish();
             if (s.nblk == im.total_blocks && s.z == 0 && nblk_in < im.total_blocks) states[i].done_blocks = s.nblk;
-            if (err && std::getenv("EMU_DEBUG")) std::fprintf(stderr, "emu: write pass err %u at subseq %u (p0 %u) nblk_in %u -> %u z %u\n", err, k, k * S, nblk_in, s.nblk, s.z);
+            if (err && std::getenv("EMU_DEBUG")) std::fprintf(stderr, "emu: block pass err %u at subseq %u (p0 %u) nblk_in %u -> %u z %u\n", err, k, k * S, nblk_in, s.nblk, s.z);
             states[i].error |= err;
         }
-        // dense coefficients (what the IDCT kernel rebuilds in shared memory; also the debug tap)
-        static const uint8_t zz_init[kRecZigzagInit] = B2J_ZIGZAG_NEXT_INIT;
-        uint8_t zzx[kRecZigzagNextSize];
-        for (int n = 0; n < kRecZigzagNextSize; ++n) zzx[n] = zigzag_next_entry(zz_init, n);
-        const uint32_t rec_total = std::min(states[i].rec_total, im.rec_cap);
-        if (states[i].done_blocks == im.total_blocks)
+        // dense coefficients: what every IDCT thread decodes into its shared-memory slot (also the debug tap)
+        if (states[i].done_blocks == im.total_blocks) {
+            std::vector<uint16_t> lut(size_t(3) * kLutEntries, 0);
+            for (int sidx = 0; sidx < im.nac; ++sidx)
+                std::memcpy(&lut[size_t(sidx) * kLutEntries], plan.huff[im.ac_pool[sidx]].lut, kLutEntries * 2);
             for (uint32_t bb = 0; bb < im.total_blocks; ++bb) {
-                int16_t blk[kRecBlkSlots] = {};
-                const uint32_t c = blkrec[im.coef_off / 64 + bb];
-                const uint32_t e = bb + 1 < im.total_blocks ? blkrec[im.coef_off / 64 + bb + 1] - 1u : rec_total;
-                if (records_to_block(records.data() + im.rec_off, std::min(c, rec_total), std::min(e, rec_total), zzx, blk)) {
-                    if (std::getenv("EMU_DEBUG") && !(states[i].error & kErrBadCode)) std::fprintf(stderr, "emu: records_to_block bad at block %u first rec %u\n", bb, blkrec[im.coef_off / 64 + bb]);
-                    states[i].error |= kErrBadCode;
-                }
+                int16_t blk[64] = {};
+                const int c = im.blk_comp[bb % uint32_t(im.bpm)];
+                const uint32_t p = blkpos[im.coef_off / 64 + bb];
+                uint32_t err = kErrOverrun;
+                if (p < clean_bits)
+                    err = decode_block_ac(reinterpret_cast<const uint32_t*>(clean.data() + im.clean_off), (im.raw_len + 12u) >> 2, p, lut.data(),
+                        uint32_t(im.ac_slot[c]) * kLutEntries, plan.huff.data() + im.ac_pool[im.ac_slot[c]], blk);
+                if (err && std::getenv("EMU_DEBUG") && !(states[i].error & err)) std::fprintf(stderr, "emu: block %u decode err %u (pos %u)\n", bb, err, p);
+                states[i].error |= err;
                 std::memcpy(coef.data() + im.coef_off + uint64_t(bb) * 64, blk, 128);
             }
+        }
     }
     // ---- DC prediction (k_dc_scan) ----
     for (int i = 0; i < m; ++i) {
@@ -416,7 +399,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             }
         }
         if (std::getenv("EMU_DEBUG"))
-            std::fprintf(stderr, "emu: image %d error flags %u, done_blocks %u of %u, rec_total %u cap %u\n", i, states[i].error, states[i].done_blocks, im.total_blocks, states[i].rec_total, unsigned(im.rec_cap));
+            std::fprintf(stderr, "emu: image %d error flags %u, done_blocks %u of %u\n", i, states[i].error, states[i].done_blocks, im.total_blocks);
         if (states[i].error) statuses[idx[i]] = 4;
         else if (states[i].done_blocks != im.total_blocks) statuses[idx[i]] = 4;
     }
