@@ -373,12 +373,22 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
     extern __shared__ __align__(16) uint8_t s_dyn[];
     uint8_t* s_blk = s_dyn;                                                                // kIdctCta * kIdctPitch
     uint16_t* s_q = reinterpret_cast<uint16_t*>(s_dyn + kIdctCta * kIdctPitch);            // 3 * 64
-    uint16_t* s_lut = s_q + 3 * 64;                                                        // up to 3 AC tables
+    uint8_t* s_zz = reinterpret_cast<uint8_t*>(s_q + 3 * 64);                              // kZigzagDump
+    uint16_t* s_order = reinterpret_cast<uint16_t*>(s_zz + kZigzagDump);                   // kIdctCta: decode order
+    uint32_t* s_job = reinterpret_cast<uint32_t*>(s_order + kIdctCta);                     // kIdctCta x {bit position, table}
+    uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_job + 2 * kIdctCta);                   // up to 3 AC tables
+    __shared__ uint32_t s_cnt[8], s_err;
     const uint32_t cta_abs = blockIdx.x + b.base_idct;
     const int img = find_image_warp(b.cta_map_idct, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
     for (int i = threadIdx.x; i < im.ncomp_out * 64; i += kIdctCta)
         s_q[i] = b.quant[im.qt[i >> 6] * 64 + (i & 63)];
+    if (threadIdx.x < kZigzagDump)
+        s_zz[threadIdx.x] = zigzag_dump_entry(c_zigzag, threadIdx.x);
+    if (threadIdx.x < 8)
+        s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 8)
+        s_err = 0;
     if (!b.dense_coef)
         for (int s = 0; s < im.nac; ++s) {
             const uint4* src = reinterpret_cast<const uint4*>(b.huff[im.ac_pool[s]].lut);
@@ -387,35 +397,78 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
         }
     const uint32_t u = (cta_abs - b.cta_map_idct[img]) * kIdctCta + threadIdx.x;
     const IdctBlockRef ref = idct_locate(im, u);
-    __syncthreads();
-    if (ref.comp < 0)
-        return;
-    { // region of interest: blocks none of whose samples can reach a pixel of the region (8 pixels of margin cover the
-      // neighbours the upsampling filters look at) are not needed
+    bool wanted = ref.comp >= 0;
+    if (wanted) { // region of interest: blocks none of whose samples can reach a pixel of the region (8 pixels of margin cover
+                  // the neighbours the upsampling filters look at) are not needed
         const int sx = (8 * im.hmax) >> (im.hs[ref.comp] >> 1), sy = (8 * im.vmax) >> (im.vs[ref.comp] >> 1); // block size in image pixels
         if ((ref.bx + 1) * sx <= im.roi_x - 8 || ref.bx * sx >= im.roi_x + im.roi_w + 8 || (ref.by + 1) * sy <= im.roi_y - 8 ||
             ref.by * sy >= im.roi_y + im.roi_h + 8)
-            return;
+            wanted = false;
     }
     uint8_t* slot = s_blk + threadIdx.x * kIdctPitch;
+    __syncthreads();
     if (b.dense_coef) { // multi-scan streams: the scans were accumulated into dense coefficients
+        if (wanted) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-            reinterpret_cast<uint4*>(slot)[i] = reinterpret_cast<const uint4*>(b.coef + im.coef_off + uint64_t(ref.src_blk) * 64)[i];
+            for (int i = 0; i < 8; ++i)
+                reinterpret_cast<uint4*>(slot)[i] = reinterpret_cast<const uint4*>(b.coef + im.coef_off + uint64_t(ref.src_blk) * 64)[i];
+        }
     } else {
-        // the thread's own slot: zero it, decode the block's AC symbols into it, read it back as a dense block
+        // Every thread zeroes the slot of its own block and posts the block as a job: where its AC symbols start and which
+        // table they use.  The jobs are then dealt out again by length (a counting sort over eight classes of the block's
+        // bit count, longest first): the lanes of a warp decode blocks of similar length instead of waiting for the longest
+        // of 32 arbitrary ones.  Afterwards every thread reads its own block's slot back, so the IDCT and the plane stores
+        // stay in plane order.
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < 9; ++i)
             reinterpret_cast<uint4*>(slot)[i] = make_uint4(0, 0, 0, 0);
-        const uint32_t clean_len = b.states[img].clean_len;
-        const uint32_t p = b.blk_pos[im.coef_off / 64 + ref.src_blk];
-        uint32_t err = kErrOverrun; // a block the block pass never reached has no position: its image is reported failed
-        if (ref.src_blk < b.states[img].done_blocks && p < clean_len * 8u)
-            err = decode_block_ac(reinterpret_cast<const uint32_t*>(b.clean + im.clean_off), (im.raw_len + 12u) >> 2, p, s_lut,
-                uint32_t(im.ac_slot[ref.comp]) * kLutEntries, b.huff + im.ac_pool[im.ac_slot[ref.comp]], reinterpret_cast<int16_t*>(slot));
-        if (err)
-            atomicOr(&b.states[img].error, err);
+        const uint32_t clean_bits = b.states[img].clean_len * 8u;
+        uint32_t cls = 0, rank = 0;
+        if (wanted) {
+            const uint32_t* pos = b.blk_pos + im.coef_off / 64 + ref.src_blk;
+            const uint32_t p = pos[0];
+            if (ref.src_blk < b.states[img].done_blocks && p < clean_bits) {
+                const uint32_t nxt = ref.src_blk + 1u < im.total_blocks ? pos[1] : clean_bits;
+                const uint32_t bits = nxt > p ? nxt - p : 0u;
+                cls = 7u - min(7u, uint32_t(32 - __clz(bits >> 4))); // 0: 1024 bits and more ... 7: under 16 bits
+                rank = atomicAdd(&s_cnt[cls], 1u);
+                s_job[2 * threadIdx.x] = p;
+                s_job[2 * threadIdx.x + 1] = uint32_t(im.ac_slot[ref.comp]);
+            } else {
+                wanted = false; // a block the block pass never reached: its image is reported failed
+                atomicOr(&s_err, kErrOverrun);
+            }
+        }
+        __syncthreads();
+        uint32_t total = 0;
+        if (wanted) {
+            uint32_t before = 0;
+#pragma unroll
+            for (uint32_t c = 0; c < 8; ++c) {
+                before += c < cls ? s_cnt[c] : 0u;
+                total += s_cnt[c];
+            }
+            s_order[before + rank] = uint16_t(threadIdx.x);
+        } else {
+#pragma unroll
+            for (uint32_t c = 0; c < 8; ++c)
+                total += s_cnt[c];
+        }
+        __syncthreads();
+        if (threadIdx.x < total) {
+            const uint32_t j = s_order[threadIdx.x];
+            const uint32_t sl = s_job[2 * j + 1];
+            const uint32_t err = decode_block_ac(reinterpret_cast<const uint32_t*>(b.clean + im.clean_off), (im.raw_len + 12u) >> 2, s_job[2 * j],
+                s_lut, sl * kLutEntries, b.huff + im.ac_pool[sl], s_zz, reinterpret_cast<int16_t*>(s_blk + j * kIdctPitch));
+            if (err)
+                atomicOr(&s_err, err);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0 && s_err)
+            atomicOr(&b.states[img].error, s_err);
     }
+    if (!wanted)
+        return;
     alignas(16) int16_t blk[64];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
@@ -468,7 +521,7 @@ int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
     return 1;
 }
 
-static size_t idct_smem_bytes() { return size_t(kIdctCta) * kIdctPitch + 3 * 64 * 2 + 3 * size_t(kLutEntries) * 2; }
+static size_t idct_smem_bytes() { return size_t(kIdctCta) * kIdctPitch + 3 * 64 * 2 + kZigzagDump + size_t(kIdctCta) * (2 + 8) + 3 * size_t(kLutEntries) * 2; }
 
 int idct_configure()
 {

@@ -310,11 +310,19 @@ B2J_HD uint32_t decode_span(const HuffEnv& env, HuffState& s, uint32_t end, BlkO
 
 // AC coefficients of one block straight from the stream (ljt/jdhuff.c decode_mcu_slow:598-640): p = bit position of the
 // block's first AC symbol (BlkOut::pos).  words = the image's unstuffed stream as stored (byte order of the file), readable
-// up to word index max_word; lut / ac_off / tab = the block's AC table as staged by the caller.  blk = 64 natural-order
-// coefficients, zeroed by the caller (entry 0 is not touched: the DC value travels separately).  Returns error flags
-// (an invalid code, or a coefficient behind position 63: corrupt data).  At most 63 symbols are read whatever the bits say.
+// up to word index max_word; lut / ac_off / tab = the block's AC table as staged by the caller.  blk = kBlkSlots
+// natural-order coefficients, zeroed by the caller (entry 0 is not touched: the DC value travels separately; entry 64 is a
+// dump).  zzd = kZigzagDump entries: zigzag position -> natural index, 64 (the dump) for positions behind the block; on the
+// device a shared-memory copy (the lanes of a warp look up different positions, which constant memory would serialise).
+// Every symbol stores: a ZRL or end-of-block symbol writes a zero to a position that is zero anyway, or to the dump -- no
+// branch in the loop but the one for codes longer than the first-level table and the one that refills the window.
+// Returns error flags (invalid code, a run that leaves the block: corrupt data).  At most 63 symbols are read.
+constexpr int kBlkSlots = 72;     // 64 coefficients + dump, padded to a 16-byte multiple
+constexpr int kZigzagDump = 128;  // positions 1 .. 63 + 63 can be asked for
+B2J_HD uint8_t zigzag_dump_entry(const uint8_t* zigzag64, int k) { return k < 64 ? zigzag64[k] : uint8_t(64); }
+
 B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32_t p, const uint16_t* lut, uint32_t ac_off,
-    const DevHuffTable* tab, int16_t* blk)
+    const DevHuffTable* tab, const uint8_t* zzd, int16_t* blk)
 {
     uint32_t widx = p >> 5;
     if (widx > max_word)
@@ -328,8 +336,8 @@ B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32
 #endif
     };
     uint32_t w0 = load(widx), w1 = load(widx + 1), w2 = load(widx + 2);
-    uint32_t z = 1, err = 0;
-    while (z < 64u) {
+    uint32_t z = 1, err = 0, zadv;
+    do {
         const uint32_t win = funnel_left(w0, w1, p);
         uint32_t e = lut[ac_off + (win >> (32 - kLutBits))];
         if ((e & 31u) == 0) { // code longer than kLutBits
@@ -338,16 +346,9 @@ B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32
             if (!ok)
                 err |= kErrBadCode;
         }
-        const uint32_t tot = e & 31u, sz = (e >> 5) & 15u, zadv = e >> 9;
-        if (zadv == 64u)
-            break; // end of block
-        if (sz) { // a coefficient after zadv - 1 zeros (a ZRL symbol has no value bits and just moves on by 16)
-            const uint32_t k = z + zadv - 1u;
-            if (k < 64u)
-                blk[B2J_ZZ(k)] = int16_t(huff_extend(win << (tot - sz), sz));
-            else
-                err |= kErrBadCode;
-        }
+        const uint32_t tot = e & 31u, sz = (e >> 5) & 15u;
+        zadv = e >> 9;
+        blk[zzd[z + zadv - 1u]] = int16_t(huff_extend(win << (tot - sz), sz)); // position of the coefficient: after zadv - 1 zeros
         z += zadv;
         p += tot;
         if ((p >> 5) != widx) {
@@ -356,7 +357,10 @@ B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32
             w1 = w2;
             w2 = load(widx + 2);
         }
-    }
+    } while (z < 64u);
+    // z == 64: the last coefficient sat at position 63; z >= 65 with zadv == 64: end of block; anything else ran over the block
+    if (z > 64u && zadv != 64u)
+        err |= kErrBadCode;
     return err;
 }
 

@@ -336,14 +336,16 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             std::vector<uint16_t> lut(size_t(3) * kLutEntries, 0);
             for (int sidx = 0; sidx < im.nac; ++sidx)
                 std::memcpy(&lut[size_t(sidx) * kLutEntries], plan.huff[im.ac_pool[sidx]].lut, kLutEntries * 2);
+            uint8_t zzd[kZigzagDump];
+            for (int k = 0; k < kZigzagDump; ++k) zzd[k] = zigzag_dump_entry(h_zigzag, k);
             for (uint32_t bb = 0; bb < im.total_blocks; ++bb) {
-                int16_t blk[64] = {};
+                int16_t blk[kBlkSlots] = {};
                 const int c = im.blk_comp[bb % uint32_t(im.bpm)];
                 const uint32_t p = blkpos[im.coef_off / 64 + bb];
                 uint32_t err = kErrOverrun;
                 if (p < clean_bits)
                     err = decode_block_ac(reinterpret_cast<const uint32_t*>(clean.data() + im.clean_off), (im.raw_len + 12u) >> 2, p, lut.data(),
-                        uint32_t(im.ac_slot[c]) * kLutEntries, plan.huff.data() + im.ac_pool[im.ac_slot[c]], blk);
+                        uint32_t(im.ac_slot[c]) * kLutEntries, plan.huff.data() + im.ac_pool[im.ac_slot[c]], zzd, blk);
                 if (err && std::getenv("EMU_DEBUG") && !(states[i].error & err)) std::fprintf(stderr, "emu: block %u decode err %u (pos %u)\n", bb, err, p);
                 states[i].error |= err;
                 std::memcpy(coef.data() + im.coef_off + uint64_t(bb) * 64, blk, 128);
