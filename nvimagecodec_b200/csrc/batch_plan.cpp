@@ -242,7 +242,8 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
             blocks_out += uint64_t(im.wib[c]) * im.hib[c];
     }
     im.idct_cta_first = plan.map_idct.back();
-    im.idct_cta_count = cdiv(blocks_out, kIdctCta);
+    (void)blocks_out;
+    im.idct_cta_count = cdiv(im.total_blocks, kIdctCta); // blocks in MCU scan order, the order of the stream
     plan.map_idct.push_back(im.idct_cta_first + im.idct_cta_count);
     const int vy = pj.ncomp == 1 ? 1 : im.vmax / im.vs[1];
     im.color_rows = vy == 2 ? im.ds_h[1] + 1 : pj.height; // row pairs (2q+1, 2q+2), q = -1 .. ds_h-1, when chroma is v-subsampled

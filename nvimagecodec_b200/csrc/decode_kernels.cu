@@ -359,14 +359,16 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// IDCT: one block per thread.  The block pass left, per block, the bit position of its first AC symbol; the thread decodes
-// those symbols itself (huffman.cuh decode_block_ac: the image's AC tables staged in shared memory, the stream read through
-// L1) straight into its own dense 8x8 slot in shared memory (row pitch 144 bytes: conflict free for 16-byte accesses) and
-// reads the slot back as the IDCT input.
+// IDCT: one block per thread, a CTA takes kIdctCta consecutive blocks of the stream (MCU scan order).  The block pass left,
+// per block, the bit position of its first AC symbol; the CTA stages the piece of the stream its blocks occupy (a few KB,
+// contiguous) in shared memory in bit order, and every thread decodes the AC symbols of one block (huffman.cuh
+// decode_block_ac: the image's AC tables staged in shared memory too) straight into that block's dense 8x8 slot (row pitch
+// 144 bytes: conflict free for 16-byte accesses).  The slots are then read back as the IDCT input.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kIdctPitch = 144;
+constexpr int kIdctStreamWords = 4096; // staged stream per CTA: 16 KB = 64 bytes per block; longer pieces are read from global memory
 #ifndef B2J_IDCT_MIN_CTAS
-#define B2J_IDCT_MIN_CTAS 4 // resident CTAs per SM the register allocation aims at
+#define B2J_IDCT_MIN_CTAS 3 // resident CTAs per SM the register allocation aims at
 #endif
 __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b)
 {
@@ -376,7 +378,8 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
     uint8_t* s_zz = reinterpret_cast<uint8_t*>(s_q + 3 * 64);                              // kZigzagDump
     uint16_t* s_order = reinterpret_cast<uint16_t*>(s_zz + kZigzagDump);                   // kIdctCta: decode order
     uint32_t* s_job = reinterpret_cast<uint32_t*>(s_order + kIdctCta);                     // kIdctCta x {bit position, table}
-    uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_job + 2 * kIdctCta);                   // up to 3 AC tables
+    uint32_t* s_stream = s_job + 2 * kIdctCta;                                             // kIdctStreamWords
+    uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_stream + kIdctStreamWords);            // the image's AC tables (b.lut_ac_slots)
     __shared__ uint32_t s_cnt[8], s_err;
     const uint32_t cta_abs = blockIdx.x + b.base_idct;
     const int img = find_image_warp(b.cta_map_idct, b.num_images, cta_abs);
@@ -389,13 +392,28 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
         s_cnt[threadIdx.x] = 0;
     if (threadIdx.x == 8)
         s_err = 0;
-    if (!b.dense_coef)
+    const uint32_t u0 = (cta_abs - b.cta_map_idct[img]) * kIdctCta, u = u0 + threadIdx.x;
+    const uint32_t* words = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
+    const uint32_t max_word = (im.raw_len + 12u) >> 2;
+    const uint32_t clean_bits = b.states[img].clean_len * 8u;
+    const bool complete = b.states[img].done_blocks == im.total_blocks; // else the image is reported failed: nothing is decoded
+    uint32_t w_first = 0, n_words = 0;
+    if (!b.dense_coef && complete) {
         for (int s = 0; s < im.nac; ++s) {
             const uint4* src = reinterpret_cast<const uint4*>(b.huff[im.ac_pool[s]].lut);
             for (int i = threadIdx.x; i < kLutEntries / 8; i += kIdctCta)
                 reinterpret_cast<uint4*>(s_lut + s * kLutEntries)[i] = __ldg(src + i);
         }
-    const uint32_t u = (cta_abs - b.cta_map_idct[img]) * kIdctCta + threadIdx.x;
+        // the piece of the stream between the first block's AC symbols and the block after the CTA's last one
+        const uint32_t* pos = b.blk_pos + im.coef_off / 64;
+        const uint32_t e = min(u0 + uint32_t(kIdctCta), im.total_blocks);
+        const uint32_t p_first = min(pos[u0], clean_bits), p_end = e < im.total_blocks ? min(pos[e], clean_bits) : clean_bits;
+        w_first = p_first >> 5;
+        n_words = p_end >= p_first ? ((p_end + 31u) >> 5) - w_first + 3u : 0u; // a window may look two words past its symbol
+        if (n_words <= uint32_t(kIdctStreamWords))
+            for (uint32_t i = threadIdx.x; i < n_words; i += kIdctCta)
+                s_stream[i] = __byte_perm(__ldg(words + min(w_first + i, max_word)), 0, 0x0123);
+    }
     const IdctBlockRef ref = idct_locate(im, u);
     bool wanted = ref.comp >= 0;
     if (wanted) { // region of interest: blocks none of whose samples can reach a pixel of the region (8 pixels of margin cover
@@ -417,17 +435,15 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
         // Every thread zeroes the slot of its own block and posts the block as a job: where its AC symbols start and which
         // table they use.  The jobs are then dealt out again by length (a counting sort over eight classes of the block's
         // bit count, longest first): the lanes of a warp decode blocks of similar length instead of waiting for the longest
-        // of 32 arbitrary ones.  Afterwards every thread reads its own block's slot back, so the IDCT and the plane stores
-        // stay in plane order.
+        // of 32 arbitrary ones.  Afterwards every thread reads its own block's slot back.
 #pragma unroll
         for (int i = 0; i < 9; ++i)
             reinterpret_cast<uint4*>(slot)[i] = make_uint4(0, 0, 0, 0);
-        const uint32_t clean_bits = b.states[img].clean_len * 8u;
         uint32_t cls = 0, rank = 0;
         if (wanted) {
             const uint32_t* pos = b.blk_pos + im.coef_off / 64 + ref.src_blk;
             const uint32_t p = pos[0];
-            if (ref.src_blk < b.states[img].done_blocks && p < clean_bits) {
+            if (complete && p < clean_bits) {
                 const uint32_t nxt = ref.src_blk + 1u < im.total_blocks ? pos[1] : clean_bits;
                 const uint32_t bits = nxt > p ? nxt - p : 0u;
                 cls = 7u - min(7u, uint32_t(32 - __clz(bits >> 4))); // 0: 1024 bits and more ... 7: under 16 bits
@@ -458,8 +474,13 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
         if (threadIdx.x < total) {
             const uint32_t j = s_order[threadIdx.x];
             const uint32_t sl = s_job[2 * j + 1];
-            const uint32_t err = decode_block_ac(reinterpret_cast<const uint32_t*>(b.clean + im.clean_off), (im.raw_len + 12u) >> 2, s_job[2 * j],
-                s_lut, sl * kLutEntries, b.huff + im.ac_pool[sl], s_zz, reinterpret_cast<int16_t*>(s_blk + j * kIdctPitch));
+            int16_t* dst = reinterpret_cast<int16_t*>(s_blk + j * kIdctPitch);
+            uint32_t err;
+            if (n_words <= uint32_t(kIdctStreamWords))
+                err = decode_block_ac<true>(s_stream - w_first, w_first + n_words - 1u, s_job[2 * j], s_lut, sl * kLutEntries, b.huff + im.ac_pool[sl],
+                    s_zz, dst);
+            else
+                err = decode_block_ac<false>(words, max_word, s_job[2 * j], s_lut, sl * kLutEntries, b.huff + im.ac_pool[sl], s_zz, dst);
             if (err)
                 atomicOr(&s_err, err);
         }
@@ -521,16 +542,20 @@ int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
     return 1;
 }
 
-static size_t idct_smem_bytes() { return size_t(kIdctCta) * kIdctPitch + 3 * 64 * 2 + kZigzagDump + size_t(kIdctCta) * (2 + 8) + 3 * size_t(kLutEntries) * 2; }
+static size_t idct_smem_bytes(int lut_ac_slots)
+{
+    return size_t(kIdctCta) * kIdctPitch + 3 * 64 * 2 + kZigzagDump + size_t(kIdctCta) * (2 + 8) + size_t(kIdctStreamWords) * 4 +
+           size_t(lut_ac_slots) * kLutEntries * 2;
+}
 
 int idct_configure()
 {
-    return cudaFuncSetAttribute(k_idct, cudaFuncAttributeMaxDynamicSharedMemorySize, int(idct_smem_bytes())) == cudaSuccess ? 0 : -1;
+    return cudaFuncSetAttribute(k_idct, cudaFuncAttributeMaxDynamicSharedMemorySize, int(idct_smem_bytes(3))) == cudaSuccess ? 0 : -1;
 }
 
 int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
 {
-    k_idct<<<d.idct_ctas, kIdctCta, idct_smem_bytes(), st>>>(b);
+    k_idct<<<d.idct_ctas, kIdctCta, idct_smem_bytes(b.lut_ac_slots), st>>>(b);
     return 1;
 }
 

@@ -389,8 +389,11 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.subseq_bits = plan_.subseq_bits;
     dev_.num_tables = int(plan_.huff.size());
     dev_.lut_slots = 1;
-    for (const ImageDesc& im : plan_.images)
+    dev_.lut_ac_slots = 1;
+    for (const ImageDesc& im : plan_.images) {
         dev_.lut_slots = std::max(dev_.lut_slots, im.ntabs);
+        dev_.lut_ac_slots = std::max(dev_.lut_ac_slots, im.nac);
+    }
     // stream staging in shared memory: per thread its subsequence plus the words a symbol may run over, an odd count
     dev_.tail_mode = (opt_.tail_spread ? 1 : 0);
     dev_.stream_words = 0;

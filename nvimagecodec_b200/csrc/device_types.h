@@ -206,6 +206,7 @@ struct BatchDev // pointers handed to every kernel
     uint32_t total_subseq;
     int32_t num_tables;    // Huffman tables in the pool
     int32_t lut_slots;     // LUT slots the decoding kernels reserve in shared memory (>= every image's ntabs)
+    int32_t lut_ac_slots;  // AC-table slots the reconstruction kernel reserves (>= every image's nac)
     int32_t stream_words;  // 32-bit words of staged stream per thread (odd, >= subseq_bits / 32 + 3); 0 = read the stream from global memory
     int32_t tail_mode;     // work-list rounds: bit 0 = items dealt lane-major (few decoding lanes per warp once the list is short)
 };

@@ -321,6 +321,10 @@ constexpr int kBlkSlots = 72;     // 64 coefficients + dump, padded to a 16-byte
 constexpr int kZigzagDump = 128;  // positions 1 .. 63 + 63 can be asked for
 B2J_HD uint8_t zigzag_dump_entry(const uint8_t* zigzag64, int k) { return k < 64 ? zigzag64[k] : uint8_t(64); }
 
+// STAGED: words are already in bit order and sit in fast memory (the caller staged the span its blocks need): both words of
+// the window are read per symbol.  Otherwise words are as stored (file byte order) in global memory and a three-word window
+// slides along in registers.
+template <bool STAGED>
 B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32_t p, const uint16_t* lut, uint32_t ac_off,
     const DevHuffTable* tab, const uint8_t* zzd, int16_t* blk)
 {
@@ -330,15 +334,26 @@ B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32
     auto load = [&](uint32_t i) {
         i = i > max_word ? max_word : i;
 #if defined(__CUDA_ARCH__)
-        return bswap32(__ldg(words + i));
+        return STAGED ? words[i] : bswap32(__ldg(words + i));
 #else
-        return bswap32(words[i]);
+        return STAGED ? words[i] : bswap32(words[i]);
 #endif
     };
-    uint32_t w0 = load(widx), w1 = load(widx + 1), w2 = load(widx + 2);
+    uint32_t w0 = 0, w1 = 0, w2 = 0;
+    if (!STAGED) {
+        w0 = load(widx);
+        w1 = load(widx + 1);
+        w2 = load(widx + 2);
+    }
     uint32_t z = 1, err = 0, zadv;
     do {
-        const uint32_t win = funnel_left(w0, w1, p);
+        uint32_t win;
+        if (STAGED) {
+            const uint32_t wi = p >> 5;
+            win = funnel_left(load(wi), load(wi + 1), p);
+        } else {
+            win = funnel_left(w0, w1, p);
+        }
         uint32_t e = lut[ac_off + (win >> (32 - kLutBits))];
         if ((e & 31u) == 0) { // code longer than kLutBits
             bool ok = true;
@@ -351,7 +366,7 @@ B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32
         blk[zzd[z + zadv - 1u]] = int16_t(huff_extend(win << (tot - sz), sz)); // position of the coefficient: after zadv - 1 zeros
         z += zadv;
         p += tot;
-        if ((p >> 5) != widx) {
+        if (!STAGED && (p >> 5) != widx) {
             ++widx;
             w0 = w1;
             w1 = w2;

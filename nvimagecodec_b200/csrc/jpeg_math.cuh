@@ -102,11 +102,11 @@ B2J_HD void idct_block(const int16_t* in, int dcval, const uint16_t* q, uint32_t
     }
 }
 
-// Where block u (plane order: component, block row, block column) of image im comes from and goes to.
+// Where block u (MCU scan order, the order of the stream: ljt/jdcoefct.c decompress_onepass:86-169) of image im goes to.
 struct IdctBlockRef
 {
-    int comp;          // -1: no such block
-    uint32_t src_blk;  // block index in MCU scan order (relative to the image)
+    int comp;          // -1: no such block, or a component the output does not need
+    uint32_t src_blk;  // = u
     uint64_t dst;      // byte offset of the block's top-left sample in the planes buffer
     int pitch;
     int bx, by;        // block coordinates inside the component plane
@@ -116,30 +116,24 @@ B2J_HD IdctBlockRef idct_locate(const ImageDesc& im, uint32_t u)
 {
     IdctBlockRef r;
     r.comp = -1;
-    r.src_blk = 0;
+    r.src_blk = u;
     r.dst = 0;
     r.pitch = 0;
     r.bx = r.by = 0;
-    int c = 0;
-    uint32_t rem = u;
-    for (; c < im.ncomp_out; ++c) {
-        const uint32_t nb = uint32_t(im.wib[c]) * uint32_t(im.hib[c]);
-        if (rem < nb)
-            break;
-        rem -= nb;
-    }
+    if (u >= im.total_blocks)
+        return r;
+    const uint32_t mcu = u / uint32_t(im.bpm), j = u - mcu * uint32_t(im.bpm);
+    const int c = im.blk_comp[j];
     if (c >= im.ncomp_out)
         return r;
-    const int by = int(rem / uint32_t(im.wib[c])), bx = int(rem - uint32_t(by) * uint32_t(im.wib[c]));
-    const int hs = im.hs[c], vs = im.vs[c], lh = hs >> 1, lv = vs >> 1; // sampling factors are 1, 2 or 4: log2 = f >> 1
-    const int mcu = (by >> lv) * im.mcus_x + (bx >> lh);
-    const int j = im.blk_first[c] + ((by & (vs - 1)) << lh) + (bx & (hs - 1));
+    const int my = int(mcu / uint32_t(im.mcus_x)), mx = int(mcu - uint32_t(my) * uint32_t(im.mcus_x));
+    const int jj = int(j) - im.blk_first[c];
+    const int hs = im.hs[c], lh = hs >> 1; // sampling factors are 1, 2 or 4: log2 = f >> 1
     r.comp = c;
-    r.bx = bx;
-    r.by = by;
-    r.src_blk = uint32_t(mcu) * uint32_t(im.bpm) + uint32_t(j);
+    r.bx = mx * hs + (jj & (hs - 1));
+    r.by = my * im.vs[c] + (jj >> lh);
     r.pitch = im.plane_pitch[c];
-    r.dst = im.plane_off[c] + uint64_t(by) * 8 * uint64_t(r.pitch) + uint64_t(bx) * 8;
+    r.dst = im.plane_off[c] + uint64_t(r.by) * 8 * uint64_t(r.pitch) + uint64_t(r.bx) * 8;
     return r;
 }
 

@@ -344,7 +344,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                 const uint32_t p = blkpos[im.coef_off / 64 + bb];
                 uint32_t err = kErrOverrun;
                 if (p < clean_bits)
-                    err = decode_block_ac(reinterpret_cast<const uint32_t*>(clean.data() + im.clean_off), (im.raw_len + 12u) >> 2, p, lut.data(),
+                    err = decode_block_ac<false>(reinterpret_cast<const uint32_t*>(clean.data() + im.clean_off), (im.raw_len + 12u) >> 2, p, lut.data(),
                         uint32_t(im.ac_slot[c]) * kLutEntries, plan.huff.data() + im.ac_pool[im.ac_slot[c]], zzd, blk);
                 if (err && std::getenv("EMU_DEBUG") && !(states[i].error & err)) std::fprintf(stderr, "emu: block %u decode err %u (pos %u)\n", bb, err, p);
                 states[i].error |= err;
