@@ -104,7 +104,12 @@ typedef struct
      * user_stream argument of the call plays that role. */
     void* cuda_stream;
     int32_t has_cuda_stream;
-    int32_t reserved;
+    /* EXIF orientation applied to the output = nvimgcodecImageInfo_t::orientation with nvimgcodecDecodeParams_t::
+     * apply_exif_orientation (reference include/nvimgcodec.h; the CPU plugin declines it, libjpeg_turbo_decoder.cpp:164-165;
+     * the GPU precedent is extensions/nvjpeg/cuda_decoder.cpp:443-460): rotated / 90 (counter-clockwise quarter turns, 0..3)
+     * | flip_x << 2 | flip_y << 3.  The buffer has the oriented size (width and height swapped for odd quarter turns).
+     * Not combined with a region of interest. */
+    int32_t orientation;
 } b200jpegOutput_t;
 
 /* ---- library ---- */

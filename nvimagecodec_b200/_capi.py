@@ -23,7 +23,7 @@ class StreamInfo(C.Structure):
 class Output(C.Structure):
     _fields_ = [("buffer", C.c_void_p), ("row_stride", C.c_int64), ("format", C.c_int32), ("on_host", C.c_int32),
                 ("roi_x", C.c_int32), ("roi_y", C.c_int32), ("roi_width", C.c_int32), ("roi_height", C.c_int32),
-                ("cuda_stream", C.c_void_p), ("has_cuda_stream", C.c_int32), ("reserved", C.c_int32)]
+                ("cuda_stream", C.c_void_p), ("has_cuda_stream", C.c_int32), ("orientation", C.c_int32)]
 
 
 MALLOC_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t, C.c_void_p)

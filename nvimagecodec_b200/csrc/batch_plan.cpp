@@ -260,6 +260,7 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     im.roi_y = whole ? 0 : out.roi_y;
     im.roi_w = whole ? pj.width : out.roi_w;
     im.roi_h = whole ? pj.height : out.roi_h;
+    im.orient = out.orient & 15;
 
     plan.total_blocks += uint64_t(mcus) * im.bpm;
     plan.total_pixels += uint64_t(pj.width) * pj.height;

@@ -16,6 +16,7 @@ struct OutputSpec
     int64_t row_stride = 0;
     int format = 4;
     int roi_x = 0, roi_y = 0, roi_w = 0, roi_h = 0; // region of interest inside the image; roi_w == 0: the whole image
+    int orient = 0; // ImageDesc::orient
 };
 
 struct PlanOptions

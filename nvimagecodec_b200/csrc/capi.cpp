@@ -83,6 +83,7 @@ static std::vector<Decoder::OutputDesc> to_outputs(int n, const b200jpegOutput_t
             outputs[i].roi_y, outputs[i].roi_width, outputs[i].roi_height};
         outs[i].stream = static_cast<cudaStream_t>(outputs[i].cuda_stream);
         outs[i].has_stream = outputs[i].has_cuda_stream != 0;
+        outs[i].orient = outputs[i].orientation & 15;
     }
     return outs;
 }

@@ -214,6 +214,31 @@ __device__ __forceinline__ void stage_row(const uint32_t* px, int fmt, uint32_t*
     }
 }
 
+// Oriented output (ImageDesc::orient): the lane's 16 pixels of one image row go to wherever the rotation / mirroring puts
+// them, one pixel at a time.  A rotated row is a column of the output, so there is nothing to coalesce; oriented files are
+// rare and this path only has to be right.
+__device__ __forceinline__ void store_row_oriented(const ImageDesc& im, const uint32_t* px, int x0, int y, int fmt)
+{
+    const int oy0 = y - im.roi_y, out_h = (im.orient & 1) ? im.roi_w : im.roi_h;
+    for (int i = 0; i < 16; ++i) {
+        const int x = x0 + i - im.roi_x;
+        if (x < 0 || x >= im.roi_w || x0 + i >= im.width)
+            continue;
+        int ox, oy;
+        orient_pixel(im.orient, im.roi_w, im.roi_h, x, oy0, ox, oy);
+        if (fmt == 4 || fmt == 6) {
+            uint8_t* dst = im.out + int64_t(oy) * im.out_stride + int64_t(ox) * 3;
+            dst[0] = uint8_t(px[i]);
+            dst[1] = uint8_t(px[i] >> 8);
+            dst[2] = uint8_t(px[i] >> 16);
+        } else {
+            const int nplanes = fmt == 7 ? 1 : 3;
+            for (int pl = 0; pl < nplanes; ++pl)
+                im.out[(int64_t(pl) * out_h + oy) * im.out_stride + ox] = uint8_t(px[i] >> (8 * pl));
+        }
+    }
+}
+
 template <int HX, int VY>
 __device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& im, uint32_t tile, uint32_t* s_warp, uint32_t lane)
 {
@@ -286,7 +311,7 @@ __device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& i
     for (int r = 0; r < VY; ++r) {
         if (active && valid[r]) {
             uint32_t* s_buf = s_warp + r * row_stride_words;
-            if (fmt == 7) { // Y only: the luma bytes are the output
+            if (fmt == 7 && !im.orient) { // Y only: the luma bytes are the output
                 *reinterpret_cast<uint4*>(s_buf + lane * 4) = make_uint4(yw[r][0], yw[r][1], yw[r][2], yw[r][3]);
             } else {
                 uint32_t px[16];
@@ -300,11 +325,16 @@ __device__ __forceinline__ void color_tile(const BatchDev& b, const ImageDesc& i
                     upsample_row<HX, VY>(cra, crb, r, fancy_h, fancy_v, cr);
                     convert16(yw[r], cb, cr, bgr, px);
                 }
-                stage_row(px, fmt, s_buf, lane);
+                if (im.orient)
+                    store_row_oriented(im, px, x0, yrow[r], fmt);
+                else
+                    stage_row(px, fmt, s_buf, lane);
             }
         }
     }
     __syncwarp();
+    if (im.orient)
+        return;
     // ---- coalesced copy-out ----
 #pragma unroll
     for (int r = 0; r < VY; ++r) {

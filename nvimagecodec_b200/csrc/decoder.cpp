@@ -256,7 +256,14 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
             os.roi_y = outs[i].roi_y;
             os.roi_w = out_w = outs[i].roi_w;
             os.roi_h = out_h = outs[i].roi_h;
+            if (outs[i].orient) { // orientation and region together are not offered
+                pre_status_[i] = B200JPEG_STATUS_UNSUPPORTED;
+                continue;
+            }
         }
+        os.orient = outs[i].orient & 15;
+        if (os.orient & 1) // odd quarter turns: the buffer is height x width
+            std::swap(out_w, out_h);
         { // rows must not overlap (a short stride would make the colour kernel's stores, or the copy back, run into each other)
             const int fmt0 = resolve_format(outs[i].format, parsed_[i].ncomp);
             const int64_t row_bytes = int64_t(out_w) * ((fmt0 == 4 || fmt0 == 6) ? 3 : 1);

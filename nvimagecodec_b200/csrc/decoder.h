@@ -115,6 +115,7 @@ class Decoder
         int roi_x = 0, roi_y = 0, roi_w = 0, roi_h = 0; // region of interest; roi_w == 0: the whole image
         cudaStream_t stream = nullptr; // with has_stream: the stream this output is ordered on (else the call's stream)
         bool has_stream = false;
+        int orient = 0; // ImageDesc::orient
     };
 
     // two-phase: prepare = parse + plan + H2D of the bitstreams; run = all device work of the prepared batch

@@ -126,6 +126,10 @@ struct ImageDesc
     // (extensions/libjpeg_turbo/jpeg_mem.cpp:206-240 asks libjpeg for one spare pixel left and right so that the upsampling
     // filter at the region's edge sees its real neighbours).
     int32_t roi_x, roi_y, roi_w, roi_h;
+    // EXIF orientation applied to the output (nvimgcodecOrientation_t, reference include/nvimgcodec.h; meaning fixed by
+    // src/parsers/exif_orientation.h:37-60): the image is rotated counter-clockwise by 90 * (orient & 3) degrees, then mirrored
+    // horizontally (bit 2, flip_x) and vertically (bit 3, flip_y).  The output buffer has the oriented size.  0: as stored.
+    int32_t orient;
 };
 
 // Per-image state written by the device.

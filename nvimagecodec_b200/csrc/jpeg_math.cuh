@@ -312,6 +312,34 @@ B2J_HD void color_unit(const BatchDev& b, const ImageDesc& im, int q, int x0, ui
         }
 }
 
+// Where pixel (x, y) of the w x h image (region) lands in the oriented output, and that output's size (see ImageDesc::orient).
+B2J_HD void orient_pixel(int orient, int w, int h, int x, int y, int& ox, int& oy)
+{
+    const int rot = orient & 3;
+    int ow = w, oh = h;
+    if (rot == 1) { // 90 degrees counter-clockwise
+        ox = y;
+        oy = w - 1 - x;
+        ow = h;
+        oh = w;
+    } else if (rot == 2) {
+        ox = w - 1 - x;
+        oy = h - 1 - y;
+    } else if (rot == 3) { // 270 degrees counter-clockwise = 90 clockwise
+        ox = h - 1 - y;
+        oy = x;
+        ow = h;
+        oh = w;
+    } else {
+        ox = x;
+        oy = y;
+    }
+    if (orient & 4)
+        ox = ow - 1 - ox;
+    if (orient & 8)
+        oy = oh - 1 - oy;
+}
+
 // Plain store of a unit (used by the CPU emulation; the CUDA kernel stages through shared memory instead).
 template <int VY>
 B2J_HD void store_unit_simple(const ImageDesc& im, int x0, const uint32_t* px, const int* yrow)
@@ -323,18 +351,23 @@ B2J_HD void store_unit_simple(const ImageDesc& im, int x0, const uint32_t* px, c
         if (yrow[r] < 0 || oy < 0 || oy >= im.roi_h)
             continue;
         for (int i = 0; i < npx; ++i) {
-            const int ox = x0 + i - im.roi_x;
+            int ox = x0 + i - im.roi_x;
             if (ox < 0 || ox >= im.roi_w)
                 continue;
+            int oyy = oy, out_h = im.roi_h;
+            if (im.orient) {
+                orient_pixel(im.orient, im.roi_w, im.roi_h, ox, oy, ox, oyy);
+                out_h = (im.orient & 1) ? im.roi_w : im.roi_h;
+            }
             if (fmt == 4 || fmt == 6) {
-                uint8_t* dst = im.out + int64_t(oy) * im.out_stride + int64_t(ox) * 3;
+                uint8_t* dst = im.out + int64_t(oyy) * im.out_stride + int64_t(ox) * 3;
                 dst[0] = uint8_t(px[r * 16 + i]);
                 dst[1] = uint8_t(px[r * 16 + i] >> 8);
                 dst[2] = uint8_t(px[r * 16 + i] >> 16);
             } else {
                 const int nplanes = fmt == 7 ? 1 : 3;
                 for (int pl = 0; pl < nplanes; ++pl)
-                    im.out[(int64_t(pl) * im.roi_h + oy) * im.out_stride + ox] = uint8_t(px[r * 16 + i] >> (8 * pl));
+                    im.out[(int64_t(pl) * out_h + oyy) * im.out_stride + ox] = uint8_t(px[r * 16 + i] >> (8 * pl));
             }
         }
     }

@@ -137,8 +137,11 @@ struct DecoderState
             stop = true;
         }
         cv.notify_all();
-        if (completer.joinable())
-            completer.join();
+        try {
+            if (completer.joinable() && completer.get_id() != std::this_thread::get_id())
+                completer.join();
+        } catch (...) { // a process that is being torn down may have taken the thread away already
+        }
     }
 };
 
@@ -189,8 +192,14 @@ nvimgcodecProcessingStatus_t check_target(const nvimgcodecImageInfo_t& info, con
         if (x < 0 || y < 0 || want_w <= 0 || want_h <= 0 || x + want_w > si.width || y + want_h > si.height)
             st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED;
     }
-    if (params->apply_exif_orientation && (info.orientation.flip_x || info.orientation.flip_y || info.orientation.rotated != 0))
-        st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
+    // EXIF orientation is applied by the colour kernel (quarter turns and mirrors; the CPU plugin declines it,
+    // libjpeg_turbo_decoder.cpp:164-165; nvjpeg's plugins apply it, cuda_decoder.cpp:443-460) -- not together with a region
+    if (params->apply_exif_orientation && (info.orientation.flip_x || info.orientation.flip_y || info.orientation.rotated != 0)) {
+        if (info.region.ndim != 0 || info.orientation.rotated % 90 != 0 || info.orientation.rotated < 0 || info.orientation.rotated >= 360)
+            st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
+        else if ((info.orientation.rotated / 90) & 1)
+            std::swap(want_w, want_h);
+    }
     if (int(info.plane_info[0].width) != want_w || int(info.plane_info[0].height) != want_h)
         st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED; // a resized target is not ours
     // the buffer kind is not looked at: a host buffer handed to a GPU backend is staged by the framework after canDecode
@@ -275,6 +284,8 @@ nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, nvimgcodecCodeStreamD
                 outs[i].roi_width = info.region.end[1] - info.region.start[1];
                 outs[i].roi_height = info.region.end[0] - info.region.start[0];
             }
+            if (params && params->apply_exif_orientation)
+                outs[i].orientation = ((info.orientation.rotated / 90) & 3) | (info.orientation.flip_x ? 4 : 0) | (info.orientation.flip_y ? 8 : 0);
             outs[i].cuda_stream = info.cuda_stream; // every distinct stream is waited for, and made to wait for the decode
             outs[i].has_cuda_stream = 1;
             if (!data[i]) {

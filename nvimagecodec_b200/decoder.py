@@ -90,7 +90,7 @@ class Decoder:
             pass
 
     # ---- low level: caller-provided buffers -------------------------------------------------------------------
-    def _outputs(self, buffers, strides, formats, on_host, rois=None, streams=None):
+    def _outputs(self, buffers, strides, formats, on_host, rois=None, streams=None, orientations=None):
         n = len(buffers)
         outs = (_capi.Output * n)()
         for i in range(n):
@@ -101,17 +101,20 @@ class Decoder:
             if streams is not None and streams[i] is not None:
                 outs[i].cuda_stream = streams[i]
                 outs[i].has_cuda_stream = 1
+            if orientations is not None and orientations[i]:
+                rotated, flip_x, flip_y = orientations[i]
+                outs[i].orientation = (rotated // 90) & 3 | (4 if flip_x else 0) | (8 if flip_y else 0)
             if rois is not None and rois[i]:
                 outs[i].roi_x, outs[i].roi_y, outs[i].roi_width, outs[i].roi_height = rois[i]
         return outs
 
-    def decode_into(self, datas, buffers, strides, formats, on_host=False, cuda_stream=0, rois=None, streams=None):
+    def decode_into(self, datas, buffers, strides, formats, on_host=False, cuda_stream=0, rois=None, streams=None, orientations=None):
         """decode a batch into raw pointers (device pointers, or host pointers with on_host=True) -> status list.
         rois: per image None or (x, y, width, height): the buffer receives that region of the image only"""
         n = len(datas)
         st = (C.c_int32 * n)()
         rc = _capi.lib().b200jpeg_decode_batch(self._h, n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
-                                               self._outputs(buffers, strides, formats, on_host, rois, streams), C.c_void_p(cuda_stream), st)
+                                               self._outputs(buffers, strides, formats, on_host, rois, streams, orientations), C.c_void_p(cuda_stream), st)
         if rc != 0:
             raise RuntimeError("b200jpeg_decode_batch: %s" % _capi.status_string(rc))
         self.last_statuses = list(st)

@@ -28,7 +28,7 @@ def lib():
         L = C.CDLL(SO)
         L.emu_decode_batch.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p),
                                        C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int,
-                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.emu_encode.restype = C.c_long
         L.emu_encode.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
         _lib = L
@@ -52,13 +52,15 @@ def encode(pixels, quality=90, subsampling=3, restart_interval=0, planar=False):
     return out[:n].tobytes()
 
 
-def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=1 << 30, jacobi=True, want_coef=False, slots=None, rois=None):
+def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=1 << 30, jacobi=True, want_coef=False, slots=None, rois=None, orients=None):
     """dims: list of (w, h).  Returns (outputs, statuses, rounds, coefs).  rois: per image None or (x, y, w, h): the output
     holds that region only"""
     n = len(datas)
     if rois is not None:
         dims = [(r[2], r[3]) if r else d for d, r in zip(dims, rois)]
     fmts = fmt if isinstance(fmt, (list, tuple)) else [fmt] * n
+    if orients is not None:  # (rotated, flip_x, flip_y) per image: odd quarter turns swap the output's width and height
+        dims = [(d[1], d[0]) if o and (o[0] // 90) & 1 else d for d, o in zip(dims, orients)]
     outs, strides = [], []
     for (w, h), f in zip(dims, fmts):
         if f in (4, 6, 2):
@@ -75,6 +77,8 @@ def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=1 
                            (C.c_void_p * n)(*[o.ctypes.data for o in outs]), (C.c_int64 * n)(*strides), (C.c_int * n)(*fmts),
                            int(fancy), subseq_bytes, max_rounds, int(jacobi), st, C.byref(rounds),
                            (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None, stats,
-                           (C.c_int * (4 * n))(*[v for r in rois for v in (r if r else (0, 0, 0, 0))]) if rois is not None else None)
+                           (C.c_int * (4 * n))(*[v for r in rois for v in (r if r else (0, 0, 0, 0))]) if rois is not None else None,
+                           (C.c_int * n)(*[((o[0] // 90) & 3 | (4 if o[1] else 0) | (8 if o[2] else 0)) if o else 0 for o in orients])
+                           if orients is not None else None)
     decode_batch.last_stats = {"rounds": int(stats[0]), "redone": int(stats[1]), "subsequences": int(stats[2]), "skipped": int(stats[3])}
     return outs, list(st), rounds.value, coefs

@@ -18,7 +18,7 @@ using namespace b200jpeg;
 extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t* sizes, uint8_t* const* outs, const int64_t* strides,
     const int* formats, int fancy, int subseq_bytes, int max_rounds, int jacobi, int* statuses, int* rounds_used,
     int16_t* const* coef_out /* optional per image, MCU order */, unsigned long long* stats /* optional [8] */,
-    const int* rois /* optional: x, y, width, height per image; width 0 = whole image */)
+    const int* rois /* optional: x, y, width, height per image; width 0 = whole image */, const int* orients /* optional: ImageDesc::orient per image */)
 {
     PlanOptions opt;
     opt.subseq_bytes = subseq_bytes;
@@ -48,6 +48,8 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             o.roi_w = rois[4 * i + 2];
             o.roi_h = rois[4 * i + 3];
         }
+        if (orients)
+            o.orient = orients[i];
         plan_add_image(plan, parsed[i], o, opt);
         idx.push_back(i);
     }

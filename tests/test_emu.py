@@ -211,3 +211,20 @@ def test_emulated_data_after_first_eoi():
     assert st == [0] * len(datas)
     for o, w, rw in zip(outs, wants, rwant):
         assert np.array_equal(o, w) and np.array_equal(o, rw)
+
+
+def test_emulated_exif_orientation():
+    """the eight EXIF orientations applied while the pixels are written (f3): equal to the reference's decode rotated /
+    mirrored with numpy; EXIF 5 must come out as the transpose and EXIF 7 as the anti-transpose"""
+    for (w, h, samp, gray) in [(227, 149, (2, 2), False), (131, 77, (2, 1), False), (100, 64, (1, 1), False), (201, 99, (1, 1), True)]:
+        d = make_jpeg(31, w, h, samp, 85, gray=gray)
+        want = port.decode(d, port.FMT_I_RGB, True)
+        n = len(util.EXIF_ORIENTATIONS)
+        outs, st, _, _ = emu.decode_batch([d] * n, [(w, h)] * n, 4, 1, 128, orients=util.EXIF_ORIENTATIONS)
+        assert st == [0] * n
+        for o, got in zip(util.EXIF_ORIENTATIONS, outs):
+            assert np.array_equal(got, util.apply_orientation(want, *o)), (w, h, o)
+        assert np.array_equal(outs[4], want.transpose(1, 0, 2)) and np.array_equal(outs[6], want[::-1, ::-1].transpose(1, 0, 2))
+        pl, st, _, _ = emu.decode_batch([d] * n, [(w, h)] * n, 3, 1, 128, orients=util.EXIF_ORIENTATIONS)
+        for o, got in zip(util.EXIF_ORIENTATIONS, pl):
+            assert np.array_equal(got.transpose(1, 2, 0), util.apply_orientation(want, *o)), ("planar", w, h, o)

@@ -60,3 +60,20 @@ def unstuff_reference(scan):
             continue
         out.append(cur)
     return bytes(out), marks
+
+
+def apply_orientation(img, rotated, flip_x, flip_y):
+    """nvimgcodecOrientation_t applied to an (H, W, C) array: rotate counter-clockwise by `rotated` degrees, then mirror
+    horizontally (flip_x) / vertically (flip_y) -- the meaning src/parsers/exif_orientation.h:37-60 gives the EXIF values
+    (e.g. EXIF 6 "rotate 90 CW" = {270, False, False}, EXIF 5 "transpose" = {90, False, True})"""
+    out = np.rot90(img, k=(rotated // 90) % 4, axes=(0, 1))
+    if flip_x:
+        out = out[:, ::-1]
+    if flip_y:
+        out = out[::-1]
+    return np.ascontiguousarray(out)
+
+
+# the eight EXIF orientations as (rotated, flip_x, flip_y), in the order of the tag's values 1..8
+EXIF_ORIENTATIONS = [(0, False, False), (0, True, False), (180, False, False), (0, False, True), (90, False, True), (270, False, False),
+                     (270, False, True), (90, False, False)]

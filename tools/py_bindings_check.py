@@ -65,10 +65,12 @@ def main():
                     assert np.array_equal(host(one), want[0])
     # only GPU backends allowed: what decodes was decoded by b200jpeg (nvjpeg_ext is not in the extensions directory)
     gpu_only = nvimgcodec.Decoder(backends=[nvimgcodec.Backend(nvimgcodec.GPU_ONLY)], options=opts)
-    imgs = gpu_only.decode(datas)
-    for i, (im, w) in enumerate(zip(imgs[:-1], want)):
+    # (without the progressive file: when the last allowed decoder declines a sample, the reference's fallback worker has no
+    # decoder and fails the whole batch -- src/decoder_worker.cpp:268-272 setAll)
+    imgs = gpu_only.decode(datas[:-1])
+    assert len(imgs) == len(datas) - 1
+    for i, (im, w) in enumerate(zip(imgs, want)):
         assert im is not None and np.array_equal(host(im), w), i
-    assert imgs[-1] is None or not hasattr(imgs[-1], "shape") or True
     # path input (Decoder.read) and DLPack
     d = tempfile.mkdtemp(prefix="nvimgcodec_img_")
     paths = []
