@@ -384,3 +384,43 @@ def test_c2_sharded_over_the_gpus():
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=800)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
         assert "C2 sharded OK" in r.stdout, r.stdout[-2000:]
+
+
+def test_exif_orientation_applied_by_the_colour_kernel(sess, cpu):
+    """f3: the eight EXIF orientations (nvimgcodecImageInfo_t::orientation with apply_exif_orientation, the meaning of
+    src/parsers/exif_orientation.h:37-60) through the C ABI and through nvimgcodecDecoderDecode; oracle = the reference's
+    decode rotated / mirrored with numpy (the CPU plugin itself declines orientation, libjpeg_turbo_decoder.cpp:164-165)"""
+    import torch
+    from nvimagecodec_b200.decoder import Decoder
+    dec = Decoder(0, options=":fancy_upsampling=1")
+    fdec = sess.decoder(device_id=0, backends=ref.BACKEND_GPU_ONLY, options=":fancy_upsampling=1")
+    orients = util.EXIF_ORIENTATIONS
+    n = len(orients)
+    for (w, h, samp, gray) in [(640, 426, (2, 2), False), (333, 211, (2, 1), False), (1030, 200, (1, 1), False), (201, 99, (1, 1), True)]:
+        d = make_jpeg(41, w, h, samp, 88, gray=gray)
+        want = cpu.decode_host([d])[0][0]
+        odims = [(h, w) if (o[0] // 90) & 1 else (w, h) for o in orients]
+        for fmt in (4, 3):
+            outs = [torch.zeros((oh, ow * 3) if fmt == 4 else (3 * oh, ow), dtype=torch.uint8, device="cuda") for (ow, oh) in odims]
+            strides = [ow * 3 if fmt == 4 else ow for (ow, oh) in odims]
+            st = dec.decode_into([d] * n, [o.data_ptr() for o in outs], strides, [fmt] * n, orientations=orients)
+            torch.cuda.synchronize()
+            assert st == [0] * n
+            for o, t, (ow, oh) in zip(orients, outs, odims):
+                a = t.cpu().numpy()
+                got = a.reshape(oh, ow, 3) if fmt == 4 else a.reshape(3, oh, ow).transpose(1, 2, 0)
+                assert np.array_equal(got, util.apply_orientation(want, *o)), (w, h, samp, fmt, o)
+        outs = [torch.zeros((oh, ow * 3), dtype=torch.uint8, device="cuda") for (ow, oh) in odims]
+        torch.cuda.synchronize()
+        fst, _ = fdec.decode_raw([d] * n, [o.data_ptr() for o in outs], odims, [ref.I_RGB] * n, [ow * 3 for (ow, oh) in odims], ref.BUFFER_DEVICE,
+                                 orient=[(o[0], int(o[1]), int(o[2])) for o in orients], apply_exif=1)
+        torch.cuda.synchronize()
+        assert fst == [ref.STATUS_SUCCESS] * n, fst
+        for o, t, (ow, oh) in zip(orients, outs, odims):
+            assert np.array_equal(t.cpu().numpy().reshape(oh, ow, 3), util.apply_orientation(want, *o)), ("framework", w, h, o)
+    # orientation together with a region is not offered
+    t = torch.zeros((10, 30), dtype=torch.uint8, device="cuda")
+    st = dec.decode_into([d], [t.data_ptr()], [30], [4], rois=[(0, 0, 10, 10)], orientations=[(90, False, False)])
+    assert st == [3]
+    dec.close()
+    fdec.close()
