@@ -207,6 +207,7 @@ int Decoder::ensure_pinned(DevBuf& b, size_t bytes)
 
 int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, const OutputDesc* outs, int32_t* statuses)
 {
+    NvtxRange nvtx("b200jpeg plan_batch");
     ready_ = false;
     groups_.clear();
     data_ = data;
@@ -627,6 +628,7 @@ void Decoder::stage_start()
 
 int Decoder::stage_group(int g)
 {
+    NvtxRange nvtx("b200jpeg stage_group");
     Group& gr = groups_[g];
     pool_->wait_prefix(stage_group_end_[g]);
     const size_t bytes = gr.raw_hi - gr.raw_lo;
@@ -653,6 +655,7 @@ int Decoder::prepare(int n, const uint8_t* const* data, const size_t* sizes, con
 // every kernel of one group on the group's stream, then its statuses (and host outputs) back to the host
 int Decoder::launch_group(int g)
 {
+    NvtxRange nvtx("b200jpeg launch_group");
     Group& gr = groups_[g];
     cudaStream_t st = streams_[g];
     const int m0 = gr.first, mc = gr.count;
@@ -757,6 +760,7 @@ int Decoder::begin_run(cudaStream_t user_stream, int32_t* statuses)
 
 int Decoder::finish(int32_t* statuses)
 {
+    NvtxRange nvtx("b200jpeg finish (wait for the device)");
     in_flight_ = false;
     const int m = int(plan_.images.size());
     for (int i = 0; i < batch_size_; ++i)

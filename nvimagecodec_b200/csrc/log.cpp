@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
+#include <nvtx3/nvToolsExt.h>
 
 namespace b200jpeg {
 
@@ -45,5 +46,8 @@ bool trace_enabled()
     static const bool on = std::getenv("B200JPEG_TRACE") != nullptr;
     return on;
 }
+
+NvtxRange::NvtxRange(const char* name) { nvtxRangePushA(name); }
+NvtxRange::~NvtxRange() { nvtxRangePop(); }
 
 } // namespace b200jpeg

@@ -12,4 +12,15 @@ void set_log_callback(LogFn fn, void* ctx);
 void log_message(int severity, const char* fmt, ...) __attribute__((format(printf, 2, 3)));
 bool trace_enabled(); // B200JPEG_TRACE in the environment (read once)
 
+// NVTX range over a host-side stage (plan / stage / launch / wait ...), the way the reference marks its own
+// (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:180,464, extensions/nvjpeg/hw_decoder.cpp:192,639): lines up with the
+// kernels in an nsys timeline; costs nothing when no tool is attached.
+struct NvtxRange
+{
+    explicit NvtxRange(const char* name);
+    ~NvtxRange();
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
+
 } // namespace b200jpeg

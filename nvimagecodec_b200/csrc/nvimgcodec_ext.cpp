@@ -13,6 +13,7 @@
 #include <nvimgcodec.h>
 #include <algorithm>
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <memory>
@@ -21,6 +22,7 @@
 #include <thread>
 #include <vector>
 #include "../../include/b200jpeg.h"
+#include <nvtx3/nvToolsExt.h>
 
 #ifndef NVIMGCODEC_VER
 #include "nvimgcodec_version.h"
@@ -212,6 +214,8 @@ nvimgcodecStatus_t dec_can_decode(nvimgcodecDecoder_t decoder, nvimgcodecProcess
 {
     if (!decoder || !status || !css || !imgs || !params)
         return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    nvtxRangePushA("b200jpeg_can_decode");
+    struct Pop { ~Pop() { nvtxRangePop(); } } pop;
     try {
         std::vector<uint8_t> storage;
         for (int i = 0; i < n; ++i) {
@@ -257,6 +261,8 @@ nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, nvimgcodecCodeStreamD
     auto* st = reinterpret_cast<DecoderState*>(decoder);
     if (!st || !css || !imgs || n < 0)
         return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
+    nvtxRangePushA("b200jpeg_decode_batch");
+    struct Pop { ~Pop() { nvtxRangePop(); } } pop;
     std::vector<char> reported(n, 0);
     auto report = [&](int i, nvimgcodecProcessingStatus_t s) {
         if (!reported[i]) { // imageReady exactly once per sample (src/processing_results.cpp:104-115)
@@ -361,6 +367,40 @@ struct EncoderState
     const nvimgcodecFrameworkDesc_t* fw = nullptr;
     const nvimgcodecExecutionParams_t* exec = nullptr;
     b200jpegEncoder_t enc = nullptr;
+    // where the library puts the files before they are handed to the code streams: one page-locked allocation kept across
+    // calls (the device -> host copies go straight into it), never cleared
+    uint8_t* bounce = nullptr;
+    size_t bounce_cap = 0;
+    bool bounce_pinned = false;
+    uint8_t* ensure_bounce(size_t bytes)
+    {
+        if (bytes <= bounce_cap)
+            return bounce;
+        release_bounce();
+        const size_t want = bytes + bytes / 4;
+        void* p = nullptr;
+        if (cudaHostAlloc(&p, want, cudaHostAllocDefault) == cudaSuccess) {
+            bounce_pinned = true;
+        } else {
+            cudaGetLastError();
+            p = std::malloc(want);
+            bounce_pinned = false;
+        }
+        bounce = static_cast<uint8_t*>(p);
+        bounce_cap = p ? want : 0;
+        return bounce;
+    }
+    void release_bounce()
+    {
+        if (bounce) {
+            if (bounce_pinned)
+                cudaFreeHost(bounce);
+            else
+                std::free(bounce);
+        }
+        bounce = nullptr;
+        bounce_cap = 0;
+    }
 };
 
 // what the caller wants written: baseline only, standard Huffman tables only
@@ -468,8 +508,8 @@ nvimgcodecStatus_t enc_encode(nvimgcodecEncoder_t encoder, nvimgcodecImageDesc_t
     };
     try {
         std::vector<b200jpegEncodeInput_t> in(n);
-        std::vector<std::vector<uint8_t>> bufs(n);
         std::vector<uint8_t*> outs(n);
+        std::vector<size_t> offs(n + 1, 0);
         std::vector<size_t> caps(n), sizes(n, 0);
         std::vector<int32_t> res(n, B200JPEG_STATUS_INTERNAL_ERROR);
         cudaStream_t user_stream = nullptr;
@@ -490,10 +530,19 @@ nvimgcodecStatus_t enc_encode(nvimgcodecEncoder_t encoder, nvimgcodecImageDesc_t
             in[i].restart_interval = 0;
             if (i == 0)
                 user_stream = info.cuda_stream;
+            // a baseline file never needs more than about the raw size (16 bits per coefficient would be 2x; quality 100 noise
+            // stays under 1.3x): twice the samples plus the headers
             caps[i] = size_t(in[i].width) * in[i].height * (in[i].format == B200JPEG_FMT_P_Y ? 1 : 3) * 2 + 4096;
-            bufs[i].resize(caps[i]);
-            outs[i] = bufs[i].data();
+            offs[i + 1] = offs[i] + ((caps[i] + 255) & ~size_t(255));
         }
+        uint8_t* bounce = st->ensure_bounce(offs[n]);
+        if (!bounce && n > 0) {
+            for (int i = 0; i < n; ++i)
+                report(i, NVIMGCODEC_PROCESSING_STATUS_FAIL);
+            return NVIMGCODEC_STATUS_EXTENSION_ALLOCATOR_FAILURE;
+        }
+        for (int i = 0; i < n; ++i)
+            outs[i] = bounce + offs[i];
         const int rc = b200jpeg_encode_batch(st->enc, n, in.data(), outs.data(), caps.data(), sizes.data(), user_stream, res.data());
         for (int i = 0; i < n; ++i) {
             if (rc != B200JPEG_STATUS_SUCCESS || res[i] != B200JPEG_STATUS_SUCCESS) {
@@ -528,6 +577,7 @@ nvimgcodecStatus_t enc_destroy(nvimgcodecEncoder_t encoder)
         return NVIMGCODEC_STATUS_EXTENSION_INVALID_PARAMETER;
     if (st->enc)
         b200jpeg_encoder_destroy(st->enc);
+    st->release_bounce();
     delete st;
     return NVIMGCODEC_STATUS_SUCCESS;
 }
