@@ -606,8 +606,21 @@ def run_decode(args, rank, world, local_rank):
         x.close()
     sess.close()
 
+    # ---- the floor of any host->host number on this box: the raw device -> pinned host copy of one batch of pixels, every rank
+    # at once (at 8 GPUs the box's aggregate device -> host rate, not the decoder, bounds e2e) ----
+    barrier()
+    floor_steps = max(3, min(10, args.steps))
+    for _ in range(2):
+        host_sets[0][:out_bytes].copy_(dev_sets[0][:out_bytes], non_blocking=True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(floor_steps):
+        host_sets[0][:out_bytes].copy_(dev_sets[0][:out_bytes], non_blocking=True)
+    torch.cuda.synchronize(dev)
+    api["copy_floor"] = (time.perf_counter() - t0) / floor_steps
+
     # ---- reduce over ranks (max time) ----
-    keys = ["dev_serial", "dev_pipelined", "host_serial", "host_pipelined", "framework_host_buffers"]
+    keys = ["dev_serial", "dev_pipelined", "host_serial", "host_pipelined", "framework_host_buffers", "copy_floor"]
     t = torch.tensor([ms_total, cabi_s * 1e3 / args.steps] + [api[k] * 1e3 for k in keys] + [float(pixels), float(out_bytes), float(n),
                      float(stats["scan_bytes"])], dtype=torch.float64, device=dev)
     per_rank_ms = [ms_total / args.steps]
@@ -620,7 +633,7 @@ def run_decode(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, cabi_ms = float(t[0]), float(t[1])
     api_ms = {k: float(t[2 + i]) for i, k in enumerate(keys)}
-    job_pixels, job_out_bytes, job_images, job_scan = float(tot[7]), float(tot[8]), float(tot[9]), float(tot[10])
+    job_pixels, job_out_bytes, job_images, job_scan = float(tot[8]), float(tot[9]), float(tot[10]), float(tot[11])
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -679,6 +692,9 @@ def run_decode(args, rank, world, local_rank):
                         "extensions directory (GPU_ONLY backends), pageable host JPEG bytes in, device batch tensor out, one cudaMemcpyAsync "
                         "to a pinned host batch tensor per batch on the images' stream; steady state with two batches in flight (two "
                         "decoders, ping-pong -- the framework promises one batch per decoder); wall clock, stream synchronised at the end",
+                "copy_floor_ms": api_ms["copy_floor"], "frac_of_copy_floor": api_ms["copy_floor"] / api_ms["host_pipelined"],
+                "copy_floor": "one cudaMemcpyAsync of the batch's %d output bytes per rank, device -> pinned host, all ranks at once: %.1f GB/s per rank"
+                              % (int(job_out_bytes / max(1, world)), job_out_bytes / max(1, world) / api_ms["copy_floor"] / 1e6),
                 "serial": rate(api_ms["host_serial"]),
                 "framework_host_buffers": rate(api_ms["framework_host_buffers"]),
                 "c_abi": rate(cabi_ms)})

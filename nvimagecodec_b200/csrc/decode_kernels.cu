@@ -20,6 +20,7 @@
 #include <cuda_runtime.h>
 #include "decode_kernels.h"
 #include "huffman.cuh"
+#include "bulk_copy.cuh"
 #include "jpeg_math.cuh"
 #include "cta_lookup.cuh"
 
@@ -381,6 +382,10 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
     uint32_t* s_stream = s_job + 2 * kIdctCta;                                             // kIdctStreamWords
     uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_stream + kIdctStreamWords);            // the image's AC tables (b.lut_ac_slots)
     __shared__ uint32_t s_cnt[8], s_err;
+    __shared__ __align__(8) uint64_t s_bar;
+    if (threadIdx.x == 0)
+        mbar_init(&s_bar, 1);
+    __syncthreads();
     const uint32_t cta_abs = blockIdx.x + b.base_idct;
     const int img = find_image_warp(b.cta_map_idct, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
@@ -398,11 +403,12 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
     const uint32_t clean_bits = b.states[img].clean_len * 8u;
     const bool complete = b.states[img].done_blocks == im.total_blocks; // else the image is reported failed: nothing is decoded
     uint32_t w_first = 0, n_words = 0;
-    if (!b.dense_coef && complete) {
-        for (int s = 0; s < im.nac; ++s) {
-            const uint4* src = reinterpret_cast<const uint4*>(b.huff[im.ac_pool[s]].lut);
-            for (int i = threadIdx.x; i < kLutEntries / 8; i += kIdctCta)
-                reinterpret_cast<uint4*>(s_lut + s * kLutEntries)[i] = __ldg(src + i);
+    const bool decode = !b.dense_coef && complete;
+    if (decode) {
+        if (threadIdx.x == 0) { // the AC tables arrive as bulk copies while the threads stage the stream
+            mbar_expect_tx(&s_bar, uint32_t(im.nac) * kLutEntries * 2u);
+            for (int s = 0; s < im.nac; ++s)
+                bulk_copy_g2s(s_lut + s * kLutEntries, b.huff[im.ac_pool[s]].lut, kLutEntries * 2u, &s_bar);
         }
         // the piece of the stream between the first block's AC symbols and the block after the CTA's last one
         const uint32_t* pos = b.blk_pos + im.coef_off / 64;
@@ -424,6 +430,8 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
             wanted = false;
     }
     uint8_t* slot = s_blk + threadIdx.x * kIdctPitch;
+    if (decode)
+        mbar_wait(&s_bar, 0);
     __syncthreads();
     if (b.dense_coef) { // multi-scan streams: the scans were accumulated into dense coefficients
         if (wanted) {

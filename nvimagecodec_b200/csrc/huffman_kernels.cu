@@ -17,6 +17,7 @@
 #include <cuda_runtime.h>
 #include "decode_kernels.h"
 #include "huffman.cuh"
+#include "bulk_copy.cuh"
 
 namespace cg = cooperative_groups;
 #include "cta_lookup.cuh"
@@ -43,10 +44,15 @@ __device__ __forceinline__ HuffSmem carve_smem(const BatchDev& b, unsigned char*
 // subsequences in shared memory.
 __device__ __forceinline__ void stage_cta(const BatchDev& b, const ImageDesc& im, const HuffSmem& sm, uint32_t k0)
 {
-    for (int s = 0; s < im.ntabs; ++s) {
-        const uint4* src = reinterpret_cast<const uint4*>(b.huff[im.tab_pool[s]].lut);
-        for (int i = threadIdx.x; i < kLutEntries / 8; i += kSubseqCta)
-            reinterpret_cast<uint4*>(sm.lut + s * kLutEntries)[i] = src[i];
+    // the tables travel as bulk copies (one thread issues them, the TMA engine moves them) while all threads stage the stream
+    __shared__ __align__(8) uint64_t s_bar;
+    if (threadIdx.x == 0)
+        mbar_init(&s_bar, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(&s_bar, uint32_t(im.ntabs) * kLutEntries * 2u);
+        for (int s = 0; s < im.ntabs; ++s)
+            bulk_copy_g2s(sm.lut + s * kLutEntries, b.huff[im.tab_pool[s]].lut, kLutEntries * 2u, &s_bar);
     }
     if (threadIdx.x < kMaxBlocksPerMcu)
         sm.tabsel[threadIdx.x] = im.tabsel_s[threadIdx.x];
@@ -65,6 +71,7 @@ __device__ __forceinline__ void stage_cta(const BatchDev& b, const ImageDesc& im
                 sm.stream[(t - 1) * W + spw + j] = v;
         }
     }
+    mbar_wait(&s_bar, 0);
     __syncthreads();
 }
 
@@ -301,10 +308,17 @@ __device__ __forceinline__ uint32_t tail_slot(const BatchDev& b)
 __device__ __forceinline__ bool tail_stage_pool(const BatchDev& b, const HuffSmem& sm)
 {
     const bool pool_staged = b.num_tables <= b.lut_slots;
+    __shared__ __align__(8) uint64_t s_bar;
+    if (threadIdx.x == 0)
+        mbar_init(&s_bar, 1);
+    __syncthreads();
     if (pool_staged) {
-        for (int s = 0; s < b.num_tables; ++s)
-            for (int i = threadIdx.x; i < kLutEntries / 8; i += kTailCta)
-                reinterpret_cast<uint4*>(sm.lut + s * kLutEntries)[i] = reinterpret_cast<const uint4*>(b.huff[s].lut)[i];
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(&s_bar, uint32_t(b.num_tables) * kLutEntries * 2u);
+            for (int s = 0; s < b.num_tables; ++s)
+                bulk_copy_g2s(sm.lut + s * kLutEntries, b.huff[s].lut, kLutEntries * 2u, &s_bar);
+        }
+        mbar_wait(&s_bar, 0);
     }
     __syncthreads();
     return pool_staged;
