@@ -167,8 +167,36 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
         im.ds_w[c] = (pj.width * im.hs[c] + im.hmax - 1) / im.hmax;
         im.ds_h[c] = (pj.height * im.vs[c] + im.vmax - 1) / im.vmax;
         im.qt[c] = intern_quant(plan, pj.quant[pj.tq[c]]);
-        dc_tab[c] = intern_huff(plan, g_seen, pj.dc[pj.td[c]], true);
-        ac_tab[c] = intern_huff(plan, g_seen, pj.ac[pj.ta[c]], false);
+        if (pj.sof != 0xC2) {
+            dc_tab[c] = intern_huff(plan, g_seen, pj.dc[pj.td[c]], true);
+            ac_tab[c] = intern_huff(plan, g_seen, pj.ac[pj.ta[c]], false);
+        }
+    }
+    im.progressive = pj.sof == 0xC2 ? 1 : 0;
+    if (im.progressive) { // the scans, with the tables each of them uses interned into the pool
+        im.scan_first = uint32_t(plan.scans.size());
+        im.scan_count = uint32_t(pj.scans.size());
+        for (const ScanInfo& si : pj.scans) {
+            ScanDesc sd;
+            std::memset(&sd, 0, sizeof(sd));
+            sd.off = uint32_t(si.offset - pj.scan_offset);
+            sd.len = uint32_t(si.bytes);
+            sd.ncomp = si.ncomp;
+            sd.ss = si.ss;
+            sd.se = si.se;
+            sd.ah = si.ah;
+            sd.al = si.al;
+            sd.restart_interval = si.restart_interval;
+            for (int i = 0; i < si.ncomp; ++i) {
+                sd.comp[i] = si.comp[i];
+                if (si.ss == 0 && si.ah == 0)
+                    sd.dc_tab[i] = intern_huff(plan, g_seen, si.dc[si.td[i]], true);
+            }
+            if (si.ss != 0)
+                sd.ac_tab = intern_huff(plan, g_seen, si.ac[si.ta[0]], false);
+            plan.scans.push_back(sd);
+        }
+        plan.prog_images.push_back(uint32_t(plan.images.size()));
     }
     im.bpm = j;
     // table selectors: distinct pool tables get shared-memory slots in order of first use
@@ -212,8 +240,9 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     plan.total_segs += uint32_t(im.num_segments) + 1;
 
     im.raw_off = plan.raw_bytes;
-    im.raw_len = uint32_t(pj.scan_bytes);
-    plan.raw_bytes = align_up(plan.raw_bytes + im.raw_len + 1, 16);
+    im.stage_len = uint32_t(pj.scan_bytes);
+    im.raw_len = im.progressive ? 0u : im.stage_len; // the baseline Huffman kernels see nothing of a progressive stream
+    plan.raw_bytes = align_up(plan.raw_bytes + im.stage_len + 1, 16);
     im.clean_off = plan.clean_bytes;
     plan.clean_bytes = align_up(plan.clean_bytes + im.raw_len + 16, 16);
 

@@ -147,10 +147,11 @@ __device__ __forceinline__ void upsample_row(const ChromaSeg<HX>& a, const Chrom
 #pragma unroll
         for (int c = 0; c < 8; ++c)
             up[2 * c] = up[2 * c + 1] = n[c + 1]; // box
-    } else if constexpr (HX == 4) { // 4:1:1: plain replication (jdsample.c int_upsample), whatever fancy_upsampling says
+    } else if constexpr (HX == 4) { // 4:1:1 / 4:1:0: plain replication (jdsample.c int_upsample), whatever fancy_upsampling says
+        const ChromaSeg<HX>& nr = (VY == 2 && r == 1) ? bseg : a;
 #pragma unroll
         for (int i = 0; i < 16; ++i)
-            up[i] = byte_of(a.w[0], i >> 2);
+            up[i] = byte_of(nr.w[0], i >> 2);
     } else {
         const ChromaSeg<HX>& nr = (VY == 2 && r == 1) ? bseg : a;
         const ChromaSeg<HX>& fr = (VY == 2 && r == 1) ? a : bseg;
@@ -371,7 +372,9 @@ __global__ void __launch_bounds__(kColorCta, B2J_COLOR_MIN_CTAS) k_color(BatchDe
     uint32_t* s_warp = s_stage + warp * kColorWarpWords;
     const int hx = color_hx(im), vy = color_vy(im);
     if (vy == 2) {
-        if (hx == 2)
+        if (hx == 4)
+            color_tile<4, 2>(b, im, tile, s_warp, lane);
+        else if (hx == 2)
             color_tile<2, 2>(b, im, tile, s_warp, lane);
         else
             color_tile<1, 2>(b, im, tile, s_warp, lane);

@@ -403,7 +403,8 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
     const uint32_t clean_bits = b.states[img].clean_len * 8u;
     const bool complete = b.states[img].done_blocks == im.total_blocks; // else the image is reported failed: nothing is decoded
     uint32_t w_first = 0, n_words = 0;
-    const bool decode = !b.dense_coef && complete;
+    const bool dense = b.dense_coef || im.progressive; // multi-scan streams: the scans were accumulated into dense coefficients
+    const bool decode = !dense && complete;
     if (decode) {
         if (threadIdx.x == 0) { // the AC tables arrive as bulk copies while the threads stage the stream
             mbar_expect_tx(&s_bar, uint32_t(im.nac) * kLutEntries * 2u);
@@ -433,7 +434,9 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
     if (decode)
         mbar_wait(&s_bar, 0);
     __syncthreads();
-    if (b.dense_coef) { // multi-scan streams: the scans were accumulated into dense coefficients
+    if (dense) {
+        if (!complete)
+            wanted = false; // a scan failed: the image is reported failed
         if (wanted) {
 #pragma unroll
             for (int i = 0; i < 8; ++i)
@@ -502,12 +505,12 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
 #pragma unroll
     for (int i = 0; i < 8; ++i)
         reinterpret_cast<uint4*>(blk)[i] = reinterpret_cast<const uint4*>(slot)[i];
-    if (b.dump_coef && !b.dense_coef) { // debug tap: the dense coefficients as the reference holds them (DC slot unused)
+    if (b.dump_coef && !dense) { // debug tap: the dense coefficients as the reference holds them (DC slot unused)
 #pragma unroll
         for (int i = 0; i < 8; ++i)
             reinterpret_cast<uint4*>(b.coef + im.coef_off + uint64_t(ref.src_blk) * 64)[i] = reinterpret_cast<const uint4*>(blk)[i];
     }
-    const int dcval = b.dc[im.coef_off / 64 + ref.src_blk];
+    const int dcval = dense ? int(blk[0]) : int(b.dc[im.coef_off / 64 + ref.src_blk]);
     uint32_t out[16];
     idct_block(blk, dcval, s_q + ref.comp * 64, out);
     // Horizontally subsampled planes: the colour kernel reads column ds_w as the right neighbour of the last real column

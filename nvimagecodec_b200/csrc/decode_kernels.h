@@ -22,6 +22,8 @@ int huff_configure(const BatchDev& b, int device, int* tail_grid);
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
+// the scans of progressive images [first, first + count) of b.prog_images -> dense coefficients
+int launch_progressive(const BatchDev& b, uint32_t first, uint32_t count, cudaStream_t st);
 int idct_configure(); // dynamic shared memory limit of k_idct; -1 on error
 int launch_color(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 

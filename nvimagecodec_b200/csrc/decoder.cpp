@@ -321,7 +321,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     // ---- scratch ----
     int rc = 0;
     if ((rc = ensure(d_raw_, plan_.raw_bytes)) || (rc = ensure(d_clean_, plan_.clean_bytes)) ||
-        (opt_.dump_coef && (rc = ensure(d_coef_, plan_.coef_elems * sizeof(int16_t)))) ||
+        ((opt_.dump_coef || !plan_.prog_images.empty()) && (rc = ensure(d_coef_, plan_.coef_elems * sizeof(int16_t)))) ||
         (rc = ensure(d_dc_, plan_.coef_elems / 64 * sizeof(int16_t) + 64)) ||
         (rc = ensure(d_blkpos_, plan_.coef_elems / 64 * sizeof(uint32_t) + 64)) || (rc = ensure(d_stamp_, 4 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_planes_, plan_.plane_bytes)) ||
@@ -342,7 +342,9 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     const size_t off_m0 = align_up(off_quant + plan_.quant.size() * sizeof(uint16_t), 256);
     const size_t map_bytes = align_up(sizeof(uint32_t) * (m + 1), 256);
     const size_t off_cimg = off_m0 + 4 * map_bytes;
-    const size_t meta_bytes = off_cimg + align_up(sizeof(uint32_t) * (plan_.total_subseq / kSubseqCta + 1), 256);
+    const size_t off_scans = off_cimg + align_up(sizeof(uint32_t) * (plan_.total_subseq / kSubseqCta + 1), 256);
+    const size_t off_prog = off_scans + align_up(sizeof(ScanDesc) * plan_.scans.size(), 256);
+    const size_t meta_bytes = off_prog + align_up(sizeof(uint32_t) * plan_.prog_images.size(), 256);
     if ((rc = ensure(d_meta_, meta_bytes)) || (rc = ensure_pinned(h_meta_, meta_bytes)) ||
         (rc = ensure_pinned(h_raw_, plan_.raw_bytes)) ||
         (rc = ensure_pinned(h_states_, sizeof(ImageState) * m + sizeof(SyncCounters) * kMaxGroups)))
@@ -361,6 +363,10 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
             cimg[c] = uint32_t(i);
     }
 
+    if (!plan_.scans.empty())
+        std::memcpy(hm + off_scans, plan_.scans.data(), sizeof(ScanDesc) * plan_.scans.size());
+    if (!plan_.prog_images.empty())
+        std::memcpy(hm + off_prog, plan_.prog_images.data(), sizeof(uint32_t) * plan_.prog_images.size());
     B2J_CUDA(cudaMemcpyAsync(d_meta_.p, h_meta_.p, meta_bytes, cudaMemcpyHostToDevice, streams_[0]));
     B2J_CUDA(cudaEventRecord(ev_meta_, streams_[0]));
 
@@ -391,6 +397,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.cta_map_unstuff = reinterpret_cast<const uint32_t*>(dm + off_m0 + 0 * map_bytes);
     dev_.cta_map_subseq = reinterpret_cast<const uint32_t*>(dm + off_m0 + 1 * map_bytes);
     dev_.subseq_cta_img = reinterpret_cast<const uint32_t*>(dm + off_cimg);
+    dev_.scans = reinterpret_cast<const ScanDesc*>(dm + off_scans);
+    dev_.prog_images = reinterpret_cast<const uint32_t*>(dm + off_prog);
     dev_.image_base = 0;
     dev_.cta_map_idct = reinterpret_cast<const uint32_t*>(dm + off_m0 + 2 * map_bytes);
     dev_.cta_map_color = reinterpret_cast<const uint32_t*>(dm + off_m0 + 3 * map_bytes);
@@ -437,7 +445,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
             last = m;
         } else {
             const uint64_t target = plan_.raw_bytes * weight_sum / weight_total;
-            while (last < m - (G - 1 - g) && (last == first || plan_.images[last].raw_off + plan_.images[last].raw_len / 2 <= target))
+            while (last < m - (G - 1 - g) && (last == first || plan_.images[last].raw_off + plan_.images[last].stage_len / 2 <= target))
                 ++last;
         }
         Group gr;
@@ -465,6 +473,9 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
         gr.dims.subseq_ctas = plan_.map_subseq[last] - plan_.map_subseq[first];
         gr.dims.idct_ctas = plan_.map_idct[last] - plan_.map_idct[first];
         gr.dims.color_ctas = plan_.map_color[last] - plan_.map_color[first];
+        gr.prog_first = uint32_t(std::lower_bound(plan_.prog_images.begin(), plan_.prog_images.end(), uint32_t(first)) - plan_.prog_images.begin());
+        gr.prog_count = uint32_t(std::lower_bound(plan_.prog_images.begin(), plan_.prog_images.end(), uint32_t(last)) - plan_.prog_images.begin()) -
+                        gr.prog_first;
         gr.raw_lo = plan_.images[first].raw_off;
         gr.raw_hi = last < m ? plan_.images[last].raw_off : plan_.raw_bytes;
         groups_.push_back(gr);
@@ -618,8 +629,8 @@ void Decoder::stage_start()
             const ImageDesc& im = plan_.images[i];
             const int bi = planned_to_batch_[i];
             const uint8_t* src = data_[bi] + parsed_[bi].scan_offset;
-            for (size_t off = 0; off < im.raw_len; off += kPiece)
-                stage_items_.push_back({src + off, hr + im.raw_off + off, std::min(kPiece, size_t(im.raw_len) - off)});
+            for (size_t off = 0; off < im.stage_len; off += kPiece)
+                stage_items_.push_back({src + off, hr + im.raw_off + off, std::min(kPiece, size_t(im.stage_len) - off)});
         }
         stage_group_end_[g] = stage_items_.size();
     }
@@ -687,6 +698,7 @@ int Decoder::launch_group(int g)
     stat_launches_ += launch_huff_write(gr.dev, gr.dims, st);
     mark(kStageDc);
     stat_launches_ += launch_dc(gr.dev, gr.dims, st);
+    stat_launches_ += launch_progressive(gr.dev, gr.prog_first, gr.prog_count, st); // progressive images of the group: scans -> coefficients
     mark(kStageIdct);
     stat_launches_ += launch_idct(gr.dev, gr.dims, st);
     mark(kStageColor);
@@ -889,7 +901,7 @@ void Decoder::get_stats(uint64_t* s) const
     s[1] = stat_rounds_;
     s[2] = 0;
     for (const ImageDesc& im : plan_.images)
-        s[2] += im.raw_len;
+        s[2] += im.stage_len;
     s[3] = plan_.total_blocks;
     s[4] = plan_.total_subseq;
     s[5] = scratch_bytes_;
@@ -922,8 +934,8 @@ int64_t Decoder::debug_fetch(int what, int image, int comp, void* dst, size_t ca
     const void* src = nullptr;
     size_t bytes = 0;
     if (what == 0) { // coefficients: AC from the coefficient array, DC (after prediction) from the DC array
-        if (!opt_.dump_coef)
-            return -4; // needs the decoder option dump_coef=1
+        if (!opt_.dump_coef && !im.progressive)
+            return -4; // needs the decoder option dump_coef=1 (progressive streams keep their coefficients anyway)
         const size_t nb = im.total_blocks;
         bytes = nb * 128;
         if (bytes > cap)
@@ -935,8 +947,9 @@ int64_t Decoder::debug_fetch(int what, int image, int comp, void* dst, size_t ca
         if (cudaMemcpy(dcv.data(), static_cast<int16_t*>(d_dc_.p) + im.coef_off / 64, nb * 2, cudaMemcpyDeviceToHost) != cudaSuccess)
             return -3;
         int16_t* o = static_cast<int16_t*>(dst);
-        for (size_t i = 0; i < nb; ++i)
-            o[i * 64] = dcv[i];
+        if (!im.progressive) // baseline: the DC values live in their own array
+            for (size_t i = 0; i < nb; ++i)
+                o[i * 64] = dcv[i];
         return int64_t(bytes);
     } else if (what == 1) {
         if (comp < 0 || comp >= im.ncomp)

@@ -93,6 +93,7 @@ class StagePool
 struct Group // consecutive planned images that are launched together on one stream
 {
     int first = 0, count = 0, tail_grid = 0;
+    uint32_t prog_first = 0, prog_count = 0; // the group's progressive images: a range of BatchPlan::prog_images
     BatchDev dev{};
     LaunchDims dims{};
     size_t raw_lo = 0, raw_hi = 0;

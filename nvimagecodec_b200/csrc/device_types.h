@@ -26,7 +26,7 @@ constexpr int kIdctCta = 256;        // threads per CTA, one 8x8 block per threa
 constexpr int kColorCta = 128;       // threads per CTA: 4 warps, each warp one tile of 512 pixels x (1|2) rows
 constexpr int kColorTilePx = 512;    // pixels per warp tile (16 per lane)
 constexpr int kDcCta = 512;          // threads per CTA, one MCU per thread per iteration
-constexpr int kMaxBlocksPerMcu = 6;   // luma up to 2x2 + Cb + Cr
+constexpr int kMaxBlocksPerMcu = 10;  // the limit of the JPEG standard: luma 4x2 + Cb + Cr (4:1:0)
 constexpr int kMaxTabSlots = 6;       // distinct Huffman tables one image can reference (3 components x DC/AC)
 
 // Decode table derived from one DHT table (reference: d_derived_tbl, external/libjpeg-turbo/jdhuff.h:27-51 and
@@ -66,6 +66,18 @@ struct alignas(16) TabSel
     uint32_t dc_off, ac_off, dc_idx, ac_idx;
 };
 
+// One scan of a progressive stream (jpeg_parse.h ScanInfo with the tables interned into the batch's pool).
+struct ScanDesc
+{
+    uint32_t off, len;        // entropy-coded bytes (stuffed, RSTn included), relative to the image's bytes in the raw buffer
+    int32_t ncomp;
+    int32_t comp[3];
+    int32_t dc_tab[3];        // pool indices (DC first scans)
+    int32_t ac_tab;           // pool index (AC scans: one component)
+    int32_t ss, se, ah, al;
+    int32_t restart_interval; // MCUs of this scan between RSTn markers, 0 = none
+};
+
 // Per-image descriptor, built on the host, read-only on the device.
 struct ImageDesc
 {
@@ -83,7 +95,7 @@ struct ImageDesc
     int32_t wib[3], hib[3];   // MCU-padded block grid per component
     int32_t ds_w[3], ds_h[3]; // downsampled_width / height (jdinput.c:130-135)
     int32_t blk_first[3];     // first block-in-MCU index of each component
-    uint8_t blk_comp[8];      // component of block j in the MCU
+    uint8_t blk_comp[12];     // component of block j in the MCU
     int32_t qt[3];            // quant table pool index per component
 
     // Huffman tables: per block-in-MCU selectors, relative to the global pool (tail kernel) and to the per-CTA shared
@@ -92,6 +104,12 @@ struct ImageDesc
     TabSel tabsel_s[kMaxBlocksPerMcu];
     int32_t ntabs;
     int32_t tab_pool[kMaxTabSlots];
+
+    // progressive streams (SOF2): the scans are decoded one after the other into dense coefficients (progressive.cuh), the
+    // baseline Huffman kernels see an empty stream (raw_len == 0) and the reconstruction kernel reads the coefficients
+    int32_t progressive;
+    uint32_t scan_first, scan_count; // into BatchDev::scans
+    uint32_t stage_len;   // bytes of the file that are copied to raw_off (== raw_len for baseline streams)
 
     // entropy-coded bytes
     uint64_t raw_off;     // byte offset in the batch raw buffer (16-byte aligned)
@@ -148,6 +166,7 @@ struct ImageState
 constexpr uint32_t kErrBadMarker = 1;     // wrong RSTn order / count
 constexpr uint32_t kErrBadCode = 2;       // invalid Huffman code on the synchronised path
 constexpr uint32_t kErrNotConverged = 4;  // subsequence synchronisation incomplete
+constexpr uint32_t kErrProgressive = 16;  // a progressive scan ran out of data / hit a bad code / a marker is missing
 constexpr uint32_t kErrOverrun = 8;       // decode ran past the end of a segment / image
 
 // State of the Huffman decoder between two symbols, packed in 64 bits: bit position | (block-in-MCU * 64 + zigzag index) << 32
@@ -192,6 +211,8 @@ struct BatchDev // pointers handed to every kernel
     uint32_t* sub_stamp;    // work-list stamps of the synchronisation rounds: the subsequence is an item of work-list round r
                             // iff stamp >= r + 1 (r + 2 once it has also been listed for round r + 1)
     uint32_t* blk_pos;      // per block: bit position of its first AC symbol in the image's unstuffed stream (block pass)
+    const ScanDesc* scans;  // scans of the progressive images of the batch
+    const uint32_t* prog_images; // batch indices of the progressive images (the launch of k_prog_decode covers a range of this list)
     int32_t dense_coef;     // the IDCT kernel takes dense coefficients from coef[] (multi-scan streams) instead of decoding AC symbols
     int32_t dump_coef;      // debug: the IDCT kernel also writes the dense coefficients it reconstructed to coef[]
     int16_t* coef;          // debug tap (dump_coef): AC coefficients, natural order, 64 per block (slot 0 unused: the DC lives in dc[])

@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
     const uint32_t cta_abs = blockIdx.x + b.base_subseq;
     const int img = find_image_warp(b.cta_map_subseq, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
-    const HuffSmem sm = carve_smem(b, g_dyn_smem, 8);
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kMaxBlocksPerMcu);
     const uint32_t k0 = (cta_abs - b.cta_map_subseq[img]) * kSubseqCta;
     stage_cta(b, im, sm, k0);
     const uint32_t k = k0 + threadIdx.x;
@@ -183,7 +183,7 @@ __device__ __forceinline__ bool tail_round(const BatchDev& b, const HuffSmem& sm
     uint32_t& redone)
 {
     const uint32_t S = uint32_t(b.subseq_bits), spw = S >> 5, W = uint32_t(b.stream_words);
-    TabSel* my_tabsel = sm.tabsel + threadIdx.x * 8;
+    TabSel* my_tabsel = sm.tabsel + threadIdx.x * kMaxBlocksPerMcu;
     uint32_t* my_words = sm.stream + threadIdx.x * W;
     const uint32_t n = __ldcg(&b.sync->count[r % 3]);
     if (n == 0)
@@ -329,7 +329,7 @@ __global__ void __launch_bounds__(kTailCta) k_huff_sync_tail(BatchDev b, int fir
     cg::grid_group grid = cg::this_grid();
     if (__ldcg(&b.sync->count[first_round % 3]) == 0) // every thread reads the same value: nothing left, no barrier needed
         return;
-    const HuffSmem sm = carve_smem(b, g_dyn_smem, kTailCta * 8);
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kTailCta * kMaxBlocksPerMcu);
     const bool pool_staged = tail_stage_pool(b, sm);
     const uint32_t nthreads = gridDim.x * blockDim.x, tid = tail_slot(b);
     uint32_t redone = 0;
@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(kTailCta) k_huff_tail_round(BatchDev b, int r)
         b.sync->count[(r + 2) % 3] = 0; // keep the rotation going: a launch after the last round must not find an old length
     if (blockIdx.x * blockDim.x >= n)
         return;
-    const HuffSmem sm = carve_smem(b, g_dyn_smem, kTailCta * 8);
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kTailCta * kMaxBlocksPerMcu);
     const bool pool_staged = tail_stage_pool(b, sm);
     const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t redone = 0;
@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
     const uint32_t cta_abs = blockIdx.x + b.base_subseq;
     const int img = find_image_warp(b.cta_map_subseq, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
-    const HuffSmem sm = carve_smem(b, g_dyn_smem, 8);
+    const HuffSmem sm = carve_smem(b, g_dyn_smem, kMaxBlocksPerMcu);
     const uint32_t cta = cta_abs - b.cta_map_subseq[img];
     const uint32_t k0 = cta * kSubseqCta, k = k0 + threadIdx.x;
     stage_cta(b, im, sm, k0);
@@ -476,10 +476,10 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
 // ------------------------------------------------------------------------------------------------------------------
 // Launchers
 // ------------------------------------------------------------------------------------------------------------------
-static size_t main_smem_bytes(const BatchDev& b) { return size_t(b.lut_slots) * kLutEntries * 2 + 8 * sizeof(TabSel) + size_t(kSubseqCta) * b.stream_words * 4; }
+static size_t main_smem_bytes(const BatchDev& b) { return size_t(b.lut_slots) * kLutEntries * 2 + kMaxBlocksPerMcu * sizeof(TabSel) + size_t(kSubseqCta) * b.stream_words * 4; }
 static size_t tail_smem_bytes(const BatchDev& b)
 {
-    return size_t(b.lut_slots) * kLutEntries * 2 + size_t(kTailCta) * 8 * sizeof(TabSel) + size_t(kTailCta) * b.stream_words * 4;
+    return size_t(b.lut_slots) * kLutEntries * 2 + size_t(kTailCta) * kMaxBlocksPerMcu * sizeof(TabSel) + size_t(kTailCta) * b.stream_words * 4;
 }
 
 int huff_configure(const BatchDev& b, int device, int* tail_grid)

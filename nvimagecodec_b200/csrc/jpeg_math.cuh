@@ -223,7 +223,14 @@ B2J_HD void upsample_unit(const uint8_t* P, int pitch, int dsw, int dsh, bool fa
         int ra = q < 0 ? 0 : (q > dsh - 1 ? dsh - 1 : q), rb = q + 1 > dsh - 1 ? dsh - 1 : q + 1;
         const uint8_t* rowa = P + uint64_t(ra) * pitch;
         const uint8_t* rowb = P + uint64_t(rb) * pitch;
-        if constexpr (HX == 1) {
+        if constexpr (HX == 4) { // 4:1:0: plain replication in both directions (jdsample.c int_upsample:161-203)
+            const uint32_t wa = *reinterpret_cast<const uint32_t*>(rowa + c0), wb = *reinterpret_cast<const uint32_t*>(rowb + c0);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                up[0][i] = int((wa >> (8 * (i >> 2))) & 255u);
+                up[1][i] = int((wb >> (8 * (i >> 2))) & 255u);
+            }
+        } else if constexpr (HX == 1) {
             int a[16], bb[16];
             load16(rowa + c0, a);
             load16(rowb + c0, bb);

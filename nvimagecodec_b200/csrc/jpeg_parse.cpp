@@ -11,6 +11,62 @@ const uint8_t kZigzagToNatural[64 + 16] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32,
 
 namespace {
 inline unsigned be16(const uint8_t* p) { return (unsigned(p[0]) << 8) | p[1]; }
+
+// End of the entropy-coded data that starts at `from`: the position of the FF of the first marker that is neither stuffing
+// (FF00), fill (FF FF) nor RSTn -- what jpeg_fill_bit_buffer stops at (ljt/jdhuff.c:287-391); n if there is none.
+size_t entropy_end(const uint8_t* d, size_t n, size_t from)
+{
+    size_t p = from;
+    while (p + 1 < n) {
+        const uint8_t* q = static_cast<const uint8_t*>(std::memchr(d + p, 0xFF, n - 1 - p));
+        if (!q)
+            return n;
+        p = size_t(q - d);
+        const int x = d[p + 1];
+        if (x == 0x00 || x == 0xFF || (x >= 0xD0 && x <= 0xD7)) {
+            p += (x == 0xFF) ? 1 : 2;
+            continue;
+        }
+        return p;
+    }
+    return n;
+}
+
+// The progression rules of ljt/jdphuff.c start_pass_phuff_decoder:96-211 (taken strictly: what libjpeg only warns about is
+// declined here), and completeness: at the end every coefficient of every component has been sent down to bit 0.
+bool check_progression(const ParsedJpeg& o)
+{
+    int bits[3][64];
+    for (auto& c : bits)
+        for (int& b : c)
+            b = -1;
+    for (const ScanInfo& sc : o.scans) {
+        if (sc.ss < 0 || sc.ss > sc.se || sc.se > 63 || sc.al < 0 || sc.al > 13 || sc.ah < 0 || sc.ah > 13)
+            return false;
+        if (sc.ss == 0 && sc.se != 0)
+            return false; // DC and AC coefficients never share a scan
+        if (sc.ss != 0 && sc.ncomp != 1)
+            return false; // AC scans carry one component
+        if (sc.ah != 0 && sc.al != sc.ah - 1)
+            return false;
+        for (int i = 0; i < sc.ncomp; ++i) {
+            const int c = sc.comp[i];
+            if (sc.ss != 0 && bits[c][0] < 0)
+                return false; // AC before the component's DC
+            for (int k = sc.ss; k <= sc.se; ++k) {
+                const int expected = bits[c][k] < 0 ? 0 : bits[c][k];
+                if (sc.ah != expected || (bits[c][k] < 0 && sc.ah != 0) || (bits[c][k] >= 0 && sc.ah == 0))
+                    return false;
+                bits[c][k] = sc.al;
+            }
+        }
+    }
+    for (int c = 0; c < o.ncomp; ++c)
+        for (int k = 0; k < 64; ++k)
+            if (bits[c][k] != 0)
+                return false;
+    return !o.scans.empty();
+}
 } // namespace
 
 ParseResult parse_jpeg(const uint8_t* d, size_t n, ParsedJpeg& o)
@@ -31,8 +87,12 @@ ParseResult parse_jpeg(const uint8_t* d, size_t n, ParsedJpeg& o)
         const int m = d[p++];
         if (m == 0x01 || (m >= 0xD0 && m <= 0xD8))
             continue; // parameterless
-        if (m == 0xD9)
-            return PARSE_BAD; // EOI before SOS
+        if (m == 0xD9) {
+            if (o.scans.empty())
+                return PARSE_BAD; // EOI before SOS
+            o.progression_ok = check_progression(o);
+            return PARSE_OK;
+        }
         if (p + 2 > n)
             return PARSE_BAD;
         const size_t L = be16(d + p);
@@ -134,6 +194,46 @@ ParseResult parse_jpeg(const uint8_t* d, size_t n, ParsedJpeg& o)
                     return PARSE_BAD;
             }
             const uint8_t* tail = s + 1 + 2 * ns;
+            if (o.sof == 0xC2 && o.ncomp <= 3) { // progressive: note the scan, skip its entropy-coded bytes, go on to the next marker
+                ScanInfo sc;
+                sc.ncomp = ns;
+                if (ns > 3)
+                    return PARSE_BAD;
+                for (int i = 0; i < ns; ++i) {
+                    int c = -1;
+                    for (int k = 0; k < o.ncomp; ++k)
+                        if (o.comp_id[k] == s[1 + 2 * i])
+                            c = k;
+                    if (c < 0 || (i > 0 && c <= sc.comp[i - 1]))
+                        return PARSE_BAD; // unknown component, or not in frame order (ljt/jdmarker.c:336-354)
+                    sc.comp[i] = c;
+                    sc.td[i] = s[2 + 2 * i] >> 4;
+                    sc.ta[i] = s[2 + 2 * i] & 15;
+                    if (sc.td[i] > 3 || sc.ta[i] > 3)
+                        return PARSE_BAD;
+                    sc.dc[sc.td[i]] = o.dc[sc.td[i]];
+                    sc.ac[sc.ta[i]] = o.ac[sc.ta[i]];
+                }
+                sc.ss = tail[0];
+                sc.se = tail[1];
+                sc.ah = tail[2] >> 4;
+                sc.al = tail[2] & 15;
+                sc.restart_interval = o.restart_interval;
+                sc.offset = p + L;
+                const size_t e = entropy_end(d, n, sc.offset);
+                sc.bytes = e - sc.offset;
+                if (o.scans.empty())
+                    o.scan_offset = sc.offset;
+                o.scan_bytes = e - o.scan_offset; // everything from the first scan's data to the end of the last one's
+                o.scans.push_back(sc);
+                o.scan_ncomp = ns;
+                if (e >= n) { // the file ends inside this scan: no EOI
+                    o.progression_ok = false;
+                    return PARSE_OK;
+                }
+                p = e;
+                continue;
+            }
             o.single_interleaved_scan = in_order && tail[0] == 0 && tail[1] == 63 && tail[2] == 0;
             o.scan_offset = p + L;
             // entropy-coded segment ends at the last EOI of the file (search backwards, tolerate trailing bytes)
@@ -171,17 +271,18 @@ int subsampling_of(const ParsedJpeg& p)
 
 bool is_supported(const ParsedJpeg& p)
 {
-    if (p.sof != 0xC0 && p.sof != 0xC1)
-        return false; // progressive, lossless, arithmetic, differential
+    if (p.sof != 0xC0 && p.sof != 0xC1 && p.sof != 0xC2)
+        return false; // lossless, arithmetic, differential
     if (p.precision != 8)
         return false;
     if (p.ncomp != 1 && p.ncomp != 3)
         return false;
-    if (!p.single_interleaved_scan)
-        return false;
+    const bool progressive = p.sof == 0xC2;
+    if (progressive ? !p.progression_ok : !p.single_interleaved_scan)
+        return false; // a progression that is incomplete or irregular is the CPU decoder's business (it smooths what is missing)
     if (p.ncomp == 3) {
         const int css = subsampling_of(p);
-        if (css != 0 && css != 2 && css != 3 && css != 4 && css != 5) // 4:4:4, 4:2:2, 4:2:0, 4:4:0, 4:1:1
+        if (css != 0 && css != 2 && css != 3 && css != 4 && css != 5 && css != 6) // 4:4:4, 4:2:2, 4:2:0, 4:4:0, 4:1:1, 4:1:0
             return false;
         // colour space decision of jdapimin.c default_decompress_parms:117-196: JFIF => YCbCr; Adobe transform 0 => RGB;
         // no marker: ids 'R','G','B' => RGB, else YCbCr.  RGB-coded JPEGs are out of scope.
@@ -189,6 +290,19 @@ bool is_supported(const ParsedJpeg& p)
             return false;
         if (!p.adobe && !p.jfif && p.comp_id[0] == 'R' && p.comp_id[1] == 'G' && p.comp_id[2] == 'B')
             return false;
+    }
+    if (progressive) {
+        for (int c = 0; c < p.ncomp; ++c)
+            if (!p.quant_present[p.tq[c]])
+                return false;
+        for (const ScanInfo& sc : p.scans)
+            for (int i = 0; i < sc.ncomp; ++i) {
+                if (sc.ss == 0 && sc.ah == 0 && !sc.dc[sc.td[i]].present)
+                    return false;
+                if (sc.ss != 0 && !sc.ac[sc.ta[i]].present)
+                    return false;
+            }
+        return size_t(p.width) * size_t(p.height) <= (size_t(1) << 28);
     }
     for (int c = 0; c < p.ncomp; ++c) {
         if (!p.quant_present[p.tq[c]] || !p.dc[p.td[c]].present || !p.ac[p.ta[c]].present)

@@ -6,6 +6,7 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <vector>
 
 namespace b200jpeg {
 
@@ -15,6 +16,19 @@ struct HuffSpec // one DHT table as transmitted
     uint8_t bits[17] = {0}; // bits[1..16]
     uint8_t vals[256] = {0};
     int count = 0;
+};
+
+// One scan of a progressive stream (SOF2): what get_sos reads (ljt/jdmarker.c:308-376) plus the tables and the restart
+// interval in force when the scan starts (DHT / DRI may be sent again between scans) and where its entropy-coded bytes are.
+struct ScanInfo
+{
+    int ncomp = 0;
+    int comp[3] = {0, 0, 0};          // indices into the frame's components
+    int td[3] = {0, 0, 0}, ta[3] = {0, 0, 0};
+    int ss = 0, se = 0, ah = 0, al = 0;
+    int restart_interval = 0;
+    size_t offset = 0, bytes = 0;     // entropy-coded bytes (stuffed, RSTn included) inside the file
+    HuffSpec dc[4], ac[4];            // only the tables the scan refers to are filled in
 };
 
 struct ParsedJpeg
@@ -32,6 +46,8 @@ struct ParsedJpeg
     size_t scan_offset = 0, scan_bytes = 0; // entropy-coded segment [offset, offset+bytes) (EOI stripped)
     int scan_ncomp = 0;
     bool single_interleaved_scan = false; // SOS lists all frame components in frame order, Ss=0 Se=63 Ah=Al=0
+    std::vector<ScanInfo> scans;          // progressive streams only: every scan of the file, in file order
+    bool progression_ok = false;          // progressive: the scans are a valid progression that ends with every coefficient at full precision
 };
 
 enum ParseResult

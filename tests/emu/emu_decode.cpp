@@ -12,6 +12,7 @@
 #include "../../nvimagecodec_b200/csrc/batch_plan.h"
 #include "../../nvimagecodec_b200/csrc/huffman.cuh"
 #include "../../nvimagecodec_b200/csrc/jpeg_math.cuh"
+#include "../../nvimagecodec_b200/csrc/progressive.cuh"
 
 using namespace b200jpeg;
 
@@ -135,7 +136,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
         const uint8_t* src = data[idx[i]] + parsed[idx[i]].scan_offset;
-        std::memcpy(raw.data() + im.raw_off, src, im.raw_len);
+        std::memcpy(raw.data() + im.raw_off, src, im.stage_len);
         uint8_t* dst = clean.data() + im.clean_off;
         uint32_t k = 0, markers = 0;
         uint32_t* S = seg.data() + im.seg_first;
@@ -354,9 +355,29 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             }
         }
     }
+    // ---- progressive images (k_prog_decode): the scans one after the other into the dense coefficients ----
+    for (int i = 0; i < m; ++i) {
+        const ImageDesc& im = plan.images[i];
+        if (!im.progressive)
+            continue;
+        std::memset(coef.data() + im.coef_off, 0, size_t(im.total_blocks) * 128);
+        uint32_t err = 0;
+        for (uint32_t sidx = 0; sidx < im.scan_count && !err; ++sidx)
+            err = prog_decode_scan(im, plan.scans[im.scan_first + sidx], raw.data() + im.raw_off, plan.huff.data(), coef.data() + im.coef_off, h_zigzag);
+        states[i].error = err; // (the baseline passes saw an empty stream)
+        if (!err)
+            states[i].done_blocks = im.total_blocks;
+    }
     // ---- DC prediction (k_dc_scan) ----
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
+        if (im.progressive) { // the DC values are in the coefficients already
+            for (uint32_t bb = 0; bb < im.total_blocks; ++bb)
+                dcv[im.coef_off / 64 + bb] = coef[im.coef_off + uint64_t(bb) * 64];
+            if (coef_out && coef_out[idx[i]])
+                std::memcpy(coef_out[idx[i]], coef.data() + im.coef_off, size_t(im.total_blocks) * 128);
+            continue;
+        }
         int pred[3] = {0, 0, 0};
         const uint32_t mcus = uint32_t(im.mcus_x) * im.mcus_y;
         int16_t* dcp = dcv.data() + im.coef_off / 64;
@@ -395,7 +416,8 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
                 if (x0 >= im.width) continue;
                 uint32_t px[32];
                 int yrow[2] = {-1, -1};
-                if (vy == 2 && hx == 2) { color_unit<2, 2>(b, im, q, x0, px, yrow); store_unit_simple<2>(im, x0, px, yrow); }
+                if (vy == 2 && hx == 4) { color_unit<4, 2>(b, im, q, x0, px, yrow); store_unit_simple<2>(im, x0, px, yrow); }
+                else if (vy == 2 && hx == 2) { color_unit<2, 2>(b, im, q, x0, px, yrow); store_unit_simple<2>(im, x0, px, yrow); }
                 else if (vy == 2) { color_unit<1, 2>(b, im, q, x0, px, yrow); store_unit_simple<2>(im, x0, px, yrow); }
                 else if (hx == 4) { color_unit<4, 1>(b, im, q, x0, px, yrow); store_unit_simple<1>(im, x0, px, yrow); }
                 else if (hx == 2) { color_unit<2, 1>(b, im, q, x0, px, yrow); store_unit_simple<1>(im, x0, px, yrow); }

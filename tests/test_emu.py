@@ -69,7 +69,7 @@ def test_emulated_1080p_converges_with_worklist_rounds():
 
 def test_emulated_corrupt_and_unsupported():
     good = make_jpeg(5000, 320, 240)
-    prog = make_jpeg(5001, 320, 240, progressive=True)
+    prog = make_jpeg(5001, 320, 240, arith=True)  # arithmetic coding: not ours
     truncated = good[:len(good) // 2]
     bad_rst = bytearray(make_jpeg(5002, 320, 240, restart_interval=4))
     i = bad_rst.find(b"\xff\xd1")
@@ -228,3 +228,52 @@ def test_emulated_exif_orientation():
         pl, st, _, _ = emu.decode_batch([d] * n, [(w, h)] * n, 3, 1, 128, orients=util.EXIF_ORIENTATIONS)
         for o, got in zip(util.EXIF_ORIENTATIONS, pl):
             assert np.array_equal(got.transpose(1, 2, 0), util.apply_orientation(want, *o)), ("planar", w, h, o)
+
+
+PROG_CASES = [(64, 48, (2, 2), False, 0), (227, 149, (2, 2), False, 0), (131, 77, (2, 1), False, 0), (131, 77, (1, 2), False, 0), (100, 100, (1, 1), False, 0),
+              (201, 99, (1, 1), True, 0), (333, 211, (2, 2), False, 5), (17, 9, (2, 2), False, 0), (1, 1, (1, 1), False, 0), (330, 77, (4, 1), False, 3),
+              (227, 149, (4, 2), False, 0), (500, 375, (2, 2), False, 0)]
+
+
+def test_emulated_progressive_streams():
+    """f2: progressive streams (SOF2: spectral selection + successive approximation, DC/AC first and refinement scans, EOB
+    runs, restart intervals) and 4:1:0 sampling, decoded by the body of k_prog_decode (progressive.cuh) into dense
+    coefficients and reconstructed by the usual kernels: bit-exact against the compiled reference, pixels and coefficients"""
+    import nvimagecodec_b200 as nb
+    for fancy in (1, 0):
+        rdec = ref.Session.shared().decoder(options=":fancy_upsampling=%d" % fancy)
+        datas = [make_jpeg(70 + i, w, h, samp, 85, gray=g, progressive=True, restart_interval=ri) for i, (w, h, samp, g, ri) in enumerate(PROG_CASES)]
+        datas.append(make_jpeg(99, 227, 149, (4, 2), 90))  # 4:1:0 baseline
+        dims = [(c[0], c[1]) for c in PROG_CASES] + [(227, 149)]
+        assert all(nb.parse_header(d).supported for d in datas)
+        want, rst, _ = rdec.decode_host(datas)
+        assert all(s == ref.STATUS_SUCCESS for s in rst)
+        slots = [util.mcu_order_coefficients(d).size for d in datas]
+        outs, st, _, coefs = emu.decode_batch(datas, dims, 4, fancy, 128, want_coef=True, slots=slots)
+        assert st == [0] * len(datas), st
+        for i, (o, w) in enumerate(zip(outs, want)):
+            assert np.array_equal(o, w), (fancy, i)
+        for d, c in zip(datas, coefs):
+            assert np.array_equal(c, util.mcu_order_coefficients(d))
+
+
+def test_emulated_progressive_damage_is_contained():
+    """a progressive stream cut short or damaged comes back failed (the framework then hands it to the CPU decoder), never
+    hangs or writes outside its coefficients"""
+    good = make_jpeg(5, 160, 120, (2, 2), 85, progressive=True)
+    rng = np.random.default_rng(3)
+    bad = []
+    for k in range(12):
+        d = bytearray(good)
+        lo = d.find(b"\xff\xda") + 14
+        if k % 3 == 0:
+            d[int(rng.integers(lo, len(d) - 2))] ^= 1 << int(rng.integers(0, 8))
+        elif k % 3 == 1:
+            p = int(rng.integers(lo, len(d) - 40))
+            d[p:p + 16] = bytes(rng.integers(0, 256, 16, dtype=np.uint8))
+        else:
+            d = d[:int(rng.integers(lo, len(d) - 2))]
+        bad.append(bytes(d))
+    outs, st, _, _ = emu.decode_batch([good] + bad + [good], [(160, 120)] * (len(bad) + 2), 4, 1, 128)
+    assert st[0] == 0 and st[-1] == 0 and np.array_equal(outs[0], outs[-1])
+    assert all(s in (0, 2, 3, 4) for s in st), st

@@ -169,7 +169,10 @@ def test_bad_and_unsupported_streams(torch_mod):
     outs = [torch_mod.zeros((240, 960), dtype=torch_mod.uint8, device="cuda") for _ in datas]
     st = dec.decode_into(datas, [o.data_ptr() for o in outs], [960] * len(datas), [4] * len(datas))
     assert st[0] == 0 and st[5] == 0
-    assert st[1] == 3 and st[2] == 3      # UNSUPPORTED -> the framework falls back to the CPU decoder
+    assert st[1] == 0                      # complete progressive streams are decoded (f2)
+    want = ref.Session.shared().decoder(options=":fancy_upsampling=1").decode_host([prog])[0][0]
+    assert np.array_equal(outs[1].cpu().numpy().reshape(240, 320, 3), want)
+    assert st[2] == 3                      # UNSUPPORTED -> the framework falls back to the CPU decoder
     assert st[3] == 4                      # CORRUPT_STREAM (entropy data ends early)
     assert st[4] == 2                      # BAD_JPEG
     assert torch_mod.equal(outs[0], outs[5])

@@ -24,7 +24,7 @@ def test_decode_through_reference_framework(sess):
     cases = [(640, 426, (2, 2), 90, 0, False), (333, 211, (2, 1), 85, 5, False), (227, 149, (1, 1), 75, 0, False), (201, 99, (1, 1), 85, 0, True),
              (1920, 1080, (2, 2), 90, 0, False)]
     datas = [make_jpeg(300 + i, w, h, samp, q, restart_interval=ri, gray=g) for i, (w, h, samp, q, ri, g) in enumerate(cases)]
-    datas.append(make_jpeg(399, 320, 240, progressive=True))  # not ours: must come back from libjpeg_turbo_ext via fallback
+    datas.append(make_jpeg(399, 320, 240, progressive=True))  # progressive: decoded by b200jpeg too (f2)
     dims = [(c[0], c[1]) for c in cases] + [(320, 240)]
     dec = sess.decoder(device_id=0, backends=0, options=":fancy_upsampling=1")
     outs = [torch.zeros((h, w * 3), dtype=torch.uint8, device="cuda") for (w, h) in dims]

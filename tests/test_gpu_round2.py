@@ -163,18 +163,18 @@ def test_can_decode_matrix_matches_the_cpu_plugin_and_falls_back(sess):
     # a target that is not the image's size: the CPU plugin does not look, b200jpeg declines (it never resizes)
     st = gpu.can_decode_ex([d], [(32, 24)], [ref.I_RGB], [1], [3], buffer_kind=ref.BUFFER_DEVICE)
     assert st == [ref.PS_ROI_UNSUPPORTED]
-    # progressive / arithmetic streams: ENCODING_UNSUPPORTED from b200jpeg, decoded by libjpeg_turbo_ext through the chain
+    # progressive streams are ours; arithmetic coding: ENCODING_UNSUPPORTED from b200jpeg, decoded by libjpeg_turbo_ext through the chain
     prog, arith = make_jpeg(2, 64, 48, progressive=True), make_jpeg(3, 64, 48, arith=True)
     st = gpu.can_decode_ex([prog, arith], [(64, 48)] * 2, [ref.I_RGB] * 2, [1] * 2, [3] * 2, buffer_kind=ref.BUFFER_DEVICE)
-    assert st == [ref.PS_ENCODING_UNSUPPORTED] * 2
+    assert st == [ref.STATUS_SUCCESS, ref.PS_ENCODING_UNSUPPORTED]
     both = sess.decoder(device_id=0, backends=0, options=":fancy_upsampling=1")
     outs = [torch.zeros((48, 192), dtype=torch.uint8, device="cuda") for _ in range(3)]
     torch.cuda.synchronize()
     fst, _ = both.decode_raw([d, prog, arith], [o.data_ptr() for o in outs], [(64, 48)] * 3, [ref.I_RGB] * 3, [192] * 3, ref.BUFFER_DEVICE)
     torch.cuda.synchronize()
     want, _, _ = ref.Session.shared().decoder(options=":fancy_upsampling=1").decode_host([d, prog, arith])
-    assert fst[0] == ref.STATUS_SUCCESS and fst[1] == ref.STATUS_SUCCESS, fst
-    for k in (0, 1):
+    assert fst == [ref.STATUS_SUCCESS] * 3, fst
+    for k in (0, 1, 2):
         assert np.array_equal(outs[k].cpu().numpy().reshape(48, 64, 3), want[k])
     for x in (gpu, cpu_only, both):
         x.close()
@@ -424,3 +424,56 @@ def test_exif_orientation_applied_by_the_colour_kernel(sess, cpu):
     assert st == [3]
     dec.close()
     fdec.close()
+
+
+def test_progressive_and_410_streams_on_the_gpu(sess, cpu):
+    """f2: progressive streams (k_prog_decode: every scan of every image into dense coefficients, the images side by side) and
+    4:1:0 sampling, mixed with baseline images in one batch: pixels and quantised coefficients bit-exact against the compiled
+    reference; through the C ABI and through the framework with only GPU backends allowed"""
+    import torch
+    import nvimagecodec_b200 as nb
+    from nvimagecodec_b200.decoder import Decoder
+    cases = [(64, 48, (2, 2), False, 0, True), (227, 149, (2, 2), False, 0, True), (131, 77, (2, 1), False, 0, True), (640, 426, (2, 2), False, 0, False),
+             (131, 77, (1, 2), False, 0, True), (100, 100, (1, 1), False, 0, True), (201, 99, (1, 1), True, 0, True), (333, 211, (2, 2), False, 5, True),
+             (17, 9, (2, 2), False, 0, True), (1, 1, (1, 1), False, 0, True), (330, 77, (4, 1), False, 3, True), (227, 149, (4, 2), False, 0, True),
+             (227, 149, (4, 2), False, 0, False), (1920, 1080, (2, 2), False, 0, True), (500, 375, (2, 2), False, 0, True), (800, 600, (2, 2), False, 0, False)]
+    datas = [make_jpeg(70 + i, w, h, samp, 85, gray=g, progressive=p, restart_interval=ri) for i, (w, h, samp, g, ri, p) in enumerate(cases)]
+    dims = [(c[0], c[1]) for c in cases]
+    assert all(nb.parse_header(d).supported for d in datas)
+    want, rst, _ = cpu.decode_host(datas)
+    assert all(s == ref.STATUS_SUCCESS for s in rst)
+    for opts in (":fancy_upsampling=1", ":fancy_upsampling=1 :groups=1 :dump_coef=1"):
+        dec = Decoder(0, options=opts)
+        outs = [torch.zeros((h, w * 3), dtype=torch.uint8, device="cuda") for (w, h) in dims]
+        for rep in range(2):  # twice through one decoder: the coefficient buffer is reused
+            st = dec.decode_into(datas, [o.data_ptr() for o in outs], [w * 3 for (w, h) in dims], [4] * len(datas))
+            torch.cuda.synchronize()
+            assert st == [0] * len(datas), st
+            for i, (o, w) in enumerate(zip(outs, want)):
+                assert np.array_equal(o.cpu().numpy().reshape(w.shape), w), (opts, rep, i, cases[i])
+        for i, d in enumerate(datas):
+            if cases[i][5] or "dump_coef" in opts:
+                wc = util.mcu_order_coefficients(d)
+                assert np.array_equal(dec.debug_fetch(0, i, 0, wc.size * 2, np.int16), wc), (i, cases[i])
+        dec.close()
+    fdec = sess.decoder(device_id=0, backends=ref.BACKEND_GPU_ONLY, options=":fancy_upsampling=1")
+    outs = [torch.zeros((h, w * 3), dtype=torch.uint8, device="cuda") for (w, h) in dims]
+    torch.cuda.synchronize()
+    fst, _ = fdec.decode_raw(datas, [o.data_ptr() for o in outs], dims, [ref.I_RGB] * len(datas), [w * 3 for (w, h) in dims], ref.BUFFER_DEVICE)
+    torch.cuda.synchronize()
+    assert fst == [ref.STATUS_SUCCESS] * len(datas)
+    for o, w in zip(outs, want):
+        assert np.array_equal(o.cpu().numpy().reshape(w.shape), w)
+    fdec.close()
+    # a progression with its last scan missing is declined (the CPU decoder smooths what is missing) and decoded by the chain
+    prog = datas[1]
+    cut = prog[:prog.rfind(b"\xff\xda")] + b"\xff\xd9"
+    assert not nb.parse_header(cut).supported
+    both = sess.decoder(device_id=0, backends=0, options=":fancy_upsampling=1")
+    out = torch.zeros((149, 227 * 3), dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    st, _ = both.decode_raw([cut], [out.data_ptr()], [(227, 149)], [ref.I_RGB], [227 * 3], ref.BUFFER_DEVICE)
+    torch.cuda.synchronize()
+    wcut, wst, _ = cpu.decode_host([cut])
+    assert st == wst == [ref.STATUS_SUCCESS] and np.array_equal(out.cpu().numpy().reshape(149, 227, 3), wcut[0])
+    both.close()

@@ -25,13 +25,14 @@ def make_jpeg(seed, w, h, samp=(2, 2), quality=90, restart_interval=0, restart_i
 
 def mcu_order_coefficients(data):
     """oracle (jpeg_read_coefficients) coefficients re-ordered into the plugin's MCU scan order: int16[blocks*64]"""
-    info = port.info(data)
-    ncomp = info["ncomp"]
-    hs = [info["hs"], 1, 1] if ncomp == 3 else [1]
-    vs = [info["vs"], 1, 1] if ncomp == 3 else [1]
+    import nvimagecodec_b200 as nb
+    info = nb.parse_header(data)  # (the plain-C port's header reader knows baseline streams only)
+    ncomp = info.num_components
+    hs = [info.h_samp[0], 1, 1] if ncomp == 3 else [1]
+    vs = [info.v_samp[0], 1, 1] if ncomp == 3 else [1]
     hmax, vmax = max(hs), max(vs)
-    mx = (info["width"] + 8 * hmax - 1) // (8 * hmax)
-    my = (info["height"] + 8 * vmax - 1) // (8 * vmax)
+    mx = (info.width + 8 * hmax - 1) // (8 * hmax)
+    my = (info.height + 8 * vmax - 1) // (8 * vmax)
     comps = [ref.ljt_coefficients(data, c, mx * hs[c], my * vs[c]) for c in range(ncomp)]
     parts = []
     for c in range(ncomp):

@@ -34,7 +34,8 @@ def main():
     cases = [(640, 426, (2, 2), 75, 0, False), (640, 426, (2, 1), 85, 0, False), (640, 426, (1, 1), 90, 0, False), (640, 426, (1, 2), 90, 0, False),
              (640, 426, (4, 1), 90, 0, False), (640, 426, (1, 1), 85, 0, True), (333, 211, (2, 2), 90, 5, False), (1920, 1080, (2, 2), 90, 0, False)]
     datas = [make_jpeg(100 + i, w, h, samp, q, restart_interval=ri, gray=g) for i, (w, h, samp, q, ri, g) in enumerate(cases)]
-    datas.append(make_jpeg(199, 320, 240, progressive=True))  # whatever b200jpeg declines comes from the CPU plugin through the fallback chain
+    datas.append(make_jpeg(198, 320, 240, progressive=True))
+    datas.append(make_jpeg(199, 320, 240, arith=True))  # whatever b200jpeg declines comes from the CPU plugin through the fallback chain
 
     def host(img):
         return np.asarray(img.cpu())
@@ -65,7 +66,7 @@ def main():
                     assert np.array_equal(host(one), want[0])
     # only GPU backends allowed: what decodes was decoded by b200jpeg (nvjpeg_ext is not in the extensions directory)
     gpu_only = nvimgcodec.Decoder(backends=[nvimgcodec.Backend(nvimgcodec.GPU_ONLY)], options=opts)
-    # (without the progressive file: when the last allowed decoder declines a sample, the reference's fallback worker has no
+    # (without the arithmetic-coded file: when the last allowed decoder declines a sample, the reference's fallback worker has no
     # decoder and fails the whole batch -- src/decoder_worker.cpp:268-272 setAll)
     imgs = gpu_only.decode(datas[:-1])
     assert len(imgs) == len(datas) - 1
