@@ -228,7 +228,7 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     const uint32_t mcus = uint32_t(im.mcus_x) * uint32_t(im.mcus_y);
     im.total_blocks = mcus * uint32_t(im.bpm);
     im.restart_interval = pj.restart_interval;
-    if (pj.restart_interval > 0 && uint32_t(pj.restart_interval) < mcus) {
+    if (!im.progressive && pj.restart_interval > 0 && uint32_t(pj.restart_interval) < mcus) { // (a progressive stream's restart intervals belong to its scans)
         im.num_segments = int(cdiv(mcus, pj.restart_interval));
         im.seg_blocks = uint32_t(pj.restart_interval) * uint32_t(im.bpm);
     } else {

@@ -364,7 +364,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         uint32_t err = 0;
         for (uint32_t sidx = 0; sidx < im.scan_count && !err; ++sidx)
             err = prog_decode_scan(im, plan.scans[im.scan_first + sidx], raw.data() + im.raw_off, plan.huff.data(), coef.data() + im.coef_off, h_zigzag);
-        states[i].error = err; // (the baseline passes saw an empty stream)
+        states[i].error |= err; // (the baseline passes saw an empty stream and must not have flagged anything)
         if (!err)
             states[i].done_blocks = im.total_blocks;
     }

@@ -32,7 +32,8 @@ def _run_config(name, distinct, fmts_distinct, batch, options=":fancy_upsampling
     idx = [i % n0 for i in range(batch)]
     datas = [distinct[i] for i in idx]
     fmts = [fmts_distinct[i] for i in idx]
-    dims = [util.port.info(d) for d in distinct]
+    import nvimagecodec_b200 as nb
+    dims = [dict(width=i.width, height=i.height) for i in (nb.parse_header(d) for d in distinct)]
     outs, ptrs, strides = [], [], []
     for i in idx:
         w, h = dims[i]["width"], dims[i]["height"]
@@ -135,3 +136,13 @@ def test_c4_mixed_batch():
             fmts.append(4 if (i // 3) % 2 == 0 else 3)
     distinct = _encode_all(specs)
     _run_config("C4 256x mixed gray/4:2:0/4:4:4 256-4096 px, planar+interleaved", distinct, fmts, 256)
+
+
+def test_c2_progressive_imagenet_shaped_batch():
+    """C2 as progressive files (the reference corpus is full of progressive ImageNet JPEGs): 256 variable-size
+    ~500x375 4:2:0 q75 progressive JPEGs -> interleaved RGB, every scan decoded on the GPU"""
+    rng = np.random.default_rng(2)
+    specs = [dict(seed=2000 + i, w=int(rng.integers(320, 641)), h=int(rng.integers(240, 501)), samp=(2, 2), quality=75, progressive=True)
+             for i in range(32)]
+    distinct = _encode_all(specs)
+    _run_config("C2p 256x ~500x375 4:2:0 q75 PROGRESSIVE", distinct, [4] * len(distinct), 256)
