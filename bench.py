@@ -686,19 +686,22 @@ def run_decode(args, rank, world, local_rank):
     def rate(ms):
         return {"value": mpix_step / (ms / 1e3), "unit": "Mpixel/s", "images_per_s": job_images / (ms / 1e3), "ms_per_step": ms}
 
-    e2e = rate(api_ms["host_pipelined"])
-    e2e.update({"h2d_bytes_per_step": int(job_scan), "d2h_bytes_per_step": int(job_out_bytes),
+    # the copy of batch k overlaps the decode of batch k + 1 in both call patterns (the copies run on their own stream); the
+    # headline is the faster one, both are reported
+    best = "host_pipelined" if api_ms["host_pipelined"] <= api_ms["host_serial"] else "host_serial"
+    e2e = rate(api_ms[best])
+    e2e.update({"h2d_bytes_per_step": int(job_scan), "d2h_bytes_per_step": int(job_out_bytes), "pattern": "two decode calls in flight" if best == "host_pipelined" else "one decode call at a time",
                 "path": "nvimgcodecDecoderDecode + nvimgcodecFutureWaitForAll of the unmodified framework with libb200jpeg_ext.so found in its "
                         "extensions directory (GPU_ONLY backends), pageable host JPEG bytes in, device batch tensor out, one cudaMemcpyAsync "
                         "to a pinned host batch tensor per batch on the images' stream; steady state with two batches in flight (two "
                         "decoders, ping-pong -- the framework promises one batch per decoder); wall clock, stream synchronised at the end",
-                "copy_floor_ms": api_ms["copy_floor"], "frac_of_copy_floor": api_ms["copy_floor"] / api_ms["host_pipelined"],
                 "copy_floor": "one cudaMemcpyAsync of the batch's %d output bytes per rank, device -> pinned host, all ranks at once: %.1f GB/s per rank"
                               % (int(job_out_bytes / max(1, world)), job_out_bytes / max(1, world) / api_ms["copy_floor"] / 1e6),
                 "serial": rate(api_ms["host_serial"]),
                 "framework_host_buffers": rate(api_ms["framework_host_buffers"]),
                 "c_abi": rate(cabi_ms)})
-    e2e["serial"]["path"] = "the same with one batch at a time: Decode -> WaitForAll -> copy -> synchronise -> next"
+    e2e["serial"]["path"] = "one decode call at a time: Decode -> WaitForAll -> enqueue the copy -> next Decode"
+    e2e["two_calls_in_flight"]["path"] = "two decoders, ping-pong (the framework promises one batch per decoder): Decode(k + 1) before WaitForAll(k)"
     e2e["framework_host_buffers"]["path"] = ("STRIDED_HOST (pinned) target buffers handed to the GPU decoder: the framework allocates a temporary "
                                              "device buffer per image per call and copies back itself (src/work.h:120-190)")
     e2e["c_abi"]["path"] = "b200jpeg_decode_batch with on_host outputs (no framework): pageable JPEG bytes in, pinned host batch tensor out"

@@ -367,7 +367,10 @@ __global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
 // 144 bytes: conflict free for 16-byte accesses).  The slots are then read back as the IDCT input.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kIdctPitch = 144;
-constexpr int kIdctStreamWords = 4096; // staged stream per CTA: 16 KB = 64 bytes per block; longer pieces are read from global memory
+#ifndef B2J_IDCT_STREAM_WORDS
+#define B2J_IDCT_STREAM_WORDS (16 * B2J_IDCT_CTA)
+#endif
+constexpr int kIdctStreamWords = B2J_IDCT_STREAM_WORDS; // staged stream per CTA: 64 bytes per block by default; longer pieces are read from global memory
 #ifndef B2J_IDCT_MIN_CTAS
 #define B2J_IDCT_MIN_CTAS 3 // resident CTAs per SM the register allocation aims at
 #endif

@@ -22,7 +22,10 @@ constexpr int kTailCta = 256;         // threads per CTA of the work-list rounds
 constexpr int kUnstuffThreads = 256;  // threads per CTA in the unstuffing kernels
 constexpr int kUnstuffBytesPerThread = 16;
 constexpr int kChunkBytes = kUnstuffThreads * kUnstuffBytesPerThread; // raw bytes per unstuff CTA
-constexpr int kIdctCta = 256;        // threads per CTA, one 8x8 block per thread
+#ifndef B2J_IDCT_CTA
+#define B2J_IDCT_CTA 256
+#endif
+constexpr int kIdctCta = B2J_IDCT_CTA; // threads per CTA, one 8x8 block per thread
 constexpr int kColorCta = 128;       // threads per CTA: 4 warps, each warp one tile of 512 pixels x (1|2) rows
 constexpr int kColorTilePx = 512;    // pixels per warp tile (16 per lane)
 constexpr int kDcCta = 512;          // threads per CTA, one MCU per thread per iteration
