@@ -9,6 +9,107 @@
 
 namespace b200jpeg {
 
+// An AC scan (one component, its blocks in raster order) by the whole warp: the 32 lanes move the block between global and
+// shared memory (128 bytes, one word per lane, the next block's load in flight while this one is decoded), lane 0 walks
+// the block's symbols on the shared copy (progressive.cuh: the same block functions the CPU emulation runs).  Blocks inside
+// an end-of-band run of a first scan are skipped without touching memory.
+__device__ uint32_t prog_ac_scan_warp(const ImageDesc& im, const ScanDesc& sc, const uint8_t* raw, const DevHuffTable* tab, int16_t* coef,
+    int16_t* s_blk, const uint8_t* zz)
+{
+    const uint32_t lane = threadIdx.x;
+    const int c0 = sc.comp[0];
+    const uint32_t bw = uint32_t(im.ds_w[c0] + 7) / 8, bh = uint32_t(im.ds_h[c0] + 7) / 8, nblocks = bw * bh;
+    ProgBits br;
+    br.init(raw, sc.off, sc.off + sc.len);
+    uint32_t eobrun = 0, to_go = sc.restart_interval ? uint32_t(sc.restart_interval) : 0xFFFFFFFFu;
+    int next_rst = 0;
+    uint32_t* s_w = reinterpret_cast<uint32_t*>(s_blk);
+    auto block_words = [&](uint32_t n) {
+        const uint32_t by = n / bw, bx = n - by * bw;
+        return reinterpret_cast<uint32_t*>(coef + uint64_t(prog_block_index(im, c0, int(bx), int(by))) * 64);
+    };
+    uint32_t v_next = nblocks ? block_words(0)[lane] : 0u;
+    for (uint32_t n = 0; n < nblocks; ++n) {
+        uint32_t* g = block_words(n);
+        const uint32_t v_cur = v_next;
+        if (n + 1 < nblocks)
+            v_next = block_words(n + 1)[lane];
+        int action = 1; // 0: nothing to do for this block, 1: decode it, 2: error
+        if (lane == 0) {
+            if (to_go == 0) { // process_restart
+                if (!br.restart(next_rst))
+                    action = 2;
+                next_rst = (next_rst + 1) & 7;
+                eobrun = 0;
+                to_go = uint32_t(sc.restart_interval);
+            }
+            --to_go;
+            if (action == 1 && sc.ah == 0 && eobrun > 0) {
+                --eobrun;
+                action = 0;
+            }
+        }
+        action = __shfl_sync(0xFFFFFFFFu, action, 0);
+        if (action == 2)
+            return kErrProgressive;
+        if (action == 0)
+            continue;
+        s_w[lane] = v_cur;
+        __syncwarp();
+        int ok = 1;
+        if (lane == 0) {
+            ok = (sc.ah == 0 ? prog_ac_first_block(br, tab, s_blk, sc.ss, sc.se, sc.al, eobrun, zz)
+                             : prog_ac_refine_block(br, tab, s_blk, sc.ss, sc.se, sc.al, eobrun, zz)) &&
+                 !br.starved;
+        }
+        __syncwarp();
+        const uint32_t v_new = s_w[lane];
+        if (v_new != v_cur)
+            g[lane] = v_new;
+        if (!__shfl_sync(0xFFFFFFFFu, ok, 0))
+            return kErrProgressive;
+    }
+    return 0;
+}
+
+// A DC refinement scan without restart markers is one bit per block in block order: lane 0 reads 32 bits, every lane sets the
+// bit in its own block (the read-modify-writes of 32 blocks overlap instead of following each other).
+__device__ uint32_t prog_dc_refine_warp(const ImageDesc& im, const ScanDesc& sc, const uint8_t* raw, int16_t* coef)
+{
+    const uint32_t lane = threadIdx.x;
+    ProgBits br;
+    br.init(raw, sc.off, sc.off + sc.len);
+    const bool single = sc.ncomp == 1;
+    const int c0 = sc.comp[0];
+    const uint32_t bw = uint32_t(im.ds_w[c0] + 7) / 8, bh = uint32_t(im.ds_h[c0] + 7) / 8;
+    const uint32_t nblocks = single ? bw * bh : im.total_blocks; // an interleaved scan of all components visits the blocks in MCU order
+    for (uint32_t n0 = 0; n0 < nblocks; n0 += 32) {
+        const uint32_t cnt = min(32u, nblocks - n0);
+        uint32_t bits = 0;
+        int ok = 1;
+        if (lane == 0) {
+            const uint32_t hi = br.get(int(min(16u, cnt)));
+            const uint32_t lo = cnt > 16 ? br.get(int(cnt - 16)) : 0u;
+            bits = cnt > 16 ? (hi << (cnt - 16)) | lo : hi; // the first block's bit is the most significant of the cnt bits
+            ok = !br.starved;
+        }
+        bits = __shfl_sync(0xFFFFFFFFu, bits, 0);
+        if (!__shfl_sync(0xFFFFFFFFu, ok, 0))
+            return kErrProgressive;
+        if (lane < cnt && ((bits >> (cnt - 1 - lane)) & 1u)) {
+            const uint32_t n = n0 + lane;
+            uint32_t idx = n;
+            if (single) {
+                const uint32_t by = n / bw, bx = n - by * bw;
+                idx = prog_block_index(im, c0, int(bx), int(by));
+            }
+            int16_t* dc = coef + uint64_t(idx) * 64;
+            *dc = int16_t(*dc | (1 << sc.al));
+        }
+    }
+    return 0;
+}
+
 __global__ void __launch_bounds__(32) k_prog_decode(BatchDev b, uint32_t first, uint32_t count)
 {
     const uint32_t j = blockIdx.x;
@@ -23,12 +124,33 @@ __global__ void __launch_bounds__(32) k_prog_decode(BatchDev b, uint32_t first, 
         for (uint64_t i = threadIdx.x; i < n16; i += 32)
             p[i] = make_uint4(0, 0, 0, 0);
     }
+    __shared__ __align__(16) DevHuffTable s_tab; // the AC table of the scan at hand
+    __shared__ __align__(16) int16_t s_blk[64];
+    __shared__ uint8_t s_zz[64];
+    s_zz[threadIdx.x] = c_zigzag[threadIdx.x];
+    s_zz[threadIdx.x + 32] = c_zigzag[threadIdx.x + 32];
     __syncwarp();
+    uint32_t err = 0;
+    for (uint32_t s = 0; s < im.scan_count && !err; ++s) {
+        const ScanDesc& sc = b.scans[im.scan_first + s];
+        const bool interleaved_all = sc.ncomp == im.ncomp; // every component of the frame: the scan's block order is the buffer's
+        if (sc.ss != 0) {
+            const uint4* src = reinterpret_cast<const uint4*>(b.huff + sc.ac_tab);
+            for (uint32_t i = threadIdx.x; i < sizeof(DevHuffTable) / 16; i += 32)
+                reinterpret_cast<uint4*>(&s_tab)[i] = __ldg(src + i);
+            __syncwarp();
+            err = prog_ac_scan_warp(im, sc, b.raw + im.raw_off, &s_tab, coef, s_blk, s_zz);
+        } else if (sc.ah != 0 && sc.restart_interval == 0 && (sc.ncomp == 1 || interleaved_all)) {
+            err = prog_dc_refine_warp(im, sc, b.raw + im.raw_off, coef);
+        } else {
+            if (threadIdx.x == 0) // DC first scans only write; the rest is rare
+                err = prog_decode_scan(im, sc, b.raw + im.raw_off, b.huff, coef, c_zigzag);
+            err = __shfl_sync(0xFFFFFFFFu, err, 0);
+        }
+        __syncwarp();
+    }
     if (threadIdx.x != 0)
         return;
-    uint32_t err = 0;
-    for (uint32_t s = 0; s < im.scan_count && !err; ++s)
-        err = prog_decode_scan(im, b.scans[im.scan_first + s], b.raw + im.raw_off, b.huff, coef, c_zigzag);
     if (err)
         atomicOr(&b.states[img].error, err);
     else
