@@ -693,8 +693,10 @@ def run_decode(args, rank, world, local_rank):
     e2e.update({"h2d_bytes_per_step": int(job_scan), "d2h_bytes_per_step": int(job_out_bytes), "pattern": "two decode calls in flight" if best == "host_pipelined" else "one decode call at a time",
                 "path": "nvimgcodecDecoderDecode + nvimgcodecFutureWaitForAll of the unmodified framework with libb200jpeg_ext.so found in its "
                         "extensions directory (GPU_ONLY backends), pageable host JPEG bytes in, device batch tensor out, one cudaMemcpyAsync "
-                        "to a pinned host batch tensor per batch on the images' stream; steady state with two batches in flight (two "
-                        "decoders, ping-pong -- the framework promises one batch per decoder); wall clock, stream synchronised at the end",
+                        "to a pinned host batch tensor per batch on a copy stream (it overlaps the next batch's decode); steady state over "
+                        "`steps` batches, wall clock, streams synchronised at the end",
+                "copy_floor_ms": api_ms["copy_floor"], "frac_of_copy_floor": api_ms["copy_floor"] / api_ms[best],
+                "two_calls_in_flight": rate(api_ms["host_pipelined"]),
                 "copy_floor": "one cudaMemcpyAsync of the batch's %d output bytes per rank, device -> pinned host, all ranks at once: %.1f GB/s per rank"
                               % (int(job_out_bytes / max(1, world)), job_out_bytes / max(1, world) / api_ms["copy_floor"] / 1e6),
                 "serial": rate(api_ms["host_serial"]),

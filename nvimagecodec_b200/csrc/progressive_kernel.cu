@@ -9,6 +9,69 @@
 
 namespace b200jpeg {
 
+// decode_mcu_AC_refine (ljt/jdphuff.c:506-655) on a block in shared memory, given which positions of the band are non-zero
+// already (nz: bit k = zigzag position k, from a ballot of the lanes): zeros are stepped over with bit operations, so the cost
+// follows the symbols and the non-zero coefficients (each takes one correction bit), not the 63 positions.  Same result as
+// progressive.cuh prog_ac_refine_block, which the CPU emulation runs.
+__device__ __forceinline__ bool prog_ac_refine_block_mask(ProgBits& br, const DevHuffTable* tab, int16_t* blk, unsigned long long nz, int ss,
+    int se, int al, uint32_t& eobrun, const uint8_t* zz)
+{
+    const int p1 = 1 << al, m1 = -(1 << al);
+    auto correct = [&](int k) { // a correction bit for the non-zero coefficient at position k
+        if (br.get(1)) {
+            int16_t* c = blk + zz[k];
+            if ((*c & p1) == 0)
+                *c = int16_t(*c + (*c >= 0 ? p1 : m1));
+        }
+    };
+    int k = ss;
+    if (eobrun == 0) {
+        while (k <= se) {
+            int s = prog_huff_symbol(br, tab);
+            if (s < 0)
+                return false;
+            int r = s >> 4;
+            s &= 15;
+            if (s) {
+                s = br.get(1) ? p1 : m1;
+            } else if (r != 15) {
+                eobrun = 1u << r;
+                if (r)
+                    eobrun += br.get(r);
+                break;
+            }
+            while (k <= se) { // over the non-zero coefficients (a correction bit each) up to the (r + 1)-th zero
+                const unsigned long long rest = nz >> k;
+                const int t = rest ? __ffsll((long long)rest) - 1 : se - k + 1; // zeros in front of the next non-zero one
+                if (r < t) {
+                    k += r;
+                    r = -1;
+                    break;
+                }
+                k += t;
+                r -= t;
+                if (k > se)
+                    break;
+                correct(k);
+                ++k;
+            }
+            if (s && k <= se)
+                blk[zz[k]] = int16_t(s);
+            ++k;
+        }
+    }
+    if (eobrun > 0) {
+        unsigned long long rest = k <= 63 ? (nz >> k) << k : 0ull;
+        while (rest) {
+            const int pos = __ffsll((long long)rest) - 1;
+            rest &= rest - 1;
+            correct(pos);
+        }
+        --eobrun;
+    }
+    return true;
+}
+
 // An AC scan (one component, its blocks in raster order) by the whole warp: the 32 lanes move the block between global and
 // shared memory (128 bytes, one word per lane, the next block's load in flight while this one is decoded), lane 0 walks
 // the block's symbols on the shared copy (progressive.cuh: the same block functions the CPU emulation runs).  Blocks inside
@@ -56,10 +119,17 @@ __device__ uint32_t prog_ac_scan_warp(const ImageDesc& im, const ScanDesc& sc, c
             continue;
         s_w[lane] = v_cur;
         __syncwarp();
+        unsigned long long nz = 0;
+        if (sc.ah != 0) { // which positions of the band are non-zero: a ballot over the block in zigzag order
+            const uint32_t lo = __ballot_sync(0xFFFFFFFFu, s_blk[zz[lane]] != 0), hi = __ballot_sync(0xFFFFFFFFu, s_blk[zz[lane + 32]] != 0);
+            nz = ((unsigned long long)hi << 32) | lo;
+            const unsigned long long band = (sc.se >= 63 ? ~0ull : ((1ull << (sc.se + 1)) - 1ull)) & ~((1ull << sc.ss) - 1ull);
+            nz &= band;
+        }
         int ok = 1;
         if (lane == 0) {
             ok = (sc.ah == 0 ? prog_ac_first_block(br, tab, s_blk, sc.ss, sc.se, sc.al, eobrun, zz)
-                             : prog_ac_refine_block(br, tab, s_blk, sc.ss, sc.se, sc.al, eobrun, zz)) &&
+                             : prog_ac_refine_block_mask(br, tab, s_blk, nz, sc.ss, sc.se, sc.al, eobrun, zz)) &&
                  !br.starved;
         }
         __syncwarp();
