@@ -157,17 +157,44 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_sync(BatchDev b, int round)
         else
             sync_decode<false>(b, env, t, k, E, k == 0);
     } else {
-        if (idle || k == 0)
-            return;
-        const unsigned long long E = b.sub_exit[t - 1];
-        if (E == b.sub_entry[t])
-            return;
-        const bool changed = staged ? sync_decode<true>(b, env, t, k, E, false) : sync_decode<false>(b, env, t, k, E, false);
-        const bool next_live = uint64_t(k + 1) * S < uint64_t(clean_bits);
-        if (changed && next_live) {
+        // Round 1: every subsequence again, from its predecessor's exit state.  Where that changes the exit state, the
+        // successor is due once more: successors inside this CTA (whose stream is staged here already) are collected in
+        // shared memory and done right away by the first threads of the CTA -- a second, compacted round without another
+        // launch and another staging of the stream; only what changes then, and the successors in the next CTA, go to the
+        // global work list.
+        __shared__ uint32_t s_n;
+        __shared__ uint16_t s_list[kSubseqCta];
+        if (threadIdx.x == 0)
+            s_n = 0;
+        __syncthreads();
+        auto push_global = [&](uint32_t tt) {
             const uint32_t i = atomicAdd(&b.sync->count[0], 1u);
-            b.worklist[0][i] = t + 1;
-            b.sub_stamp[t + 1] = 1u; // item of work-list round 0
+            b.worklist[0][i] = tt;
+            b.sub_stamp[tt] = 1u; // item of work-list round 0
+        };
+        if (!idle && k != 0) {
+            const unsigned long long E = b.sub_exit[t - 1];
+            if (E != b.sub_entry[t]) {
+                const bool changed = staged ? sync_decode<true>(b, env, t, k, E, false) : sync_decode<false>(b, env, t, k, E, false);
+                if (changed && uint64_t(k + 1) * S < uint64_t(clean_bits)) {
+                    if (staged && threadIdx.x + 1 < kSubseqCta)
+                        s_list[atomicAdd(&s_n, 1u)] = uint16_t(threadIdx.x + 1);
+                    else
+                        push_global(t + 1);
+                }
+            }
+        }
+        __syncthreads(); // the exit states written above are visible to the whole CTA
+        if (threadIdx.x < s_n) {
+            const uint32_t li = s_list[threadIdx.x], k2 = k0 + li, t2 = im.subseq_first + k2;
+            const unsigned long long E2 = b.sub_exit[t2 - 1];
+            if (E2 != b.sub_entry[t2]) {
+                const uint32_t* w2 = sm.stream + li * uint32_t(b.stream_words) - k2 * (S >> 5);
+                const uint32_t w2_s = uint32_t(__cvta_generic_to_shared(sm.stream)) + (li * uint32_t(b.stream_words) - k2 * (S >> 5)) * 4u;
+                const HuffEnv env2 = make_env(b, im, clean_len, w2, sm.lut, sm.tabsel, w2_s);
+                if (sync_decode<true>(b, env2, t2, k2, E2, false) && uint64_t(k2 + 1) * S < uint64_t(clean_bits))
+                    push_global(t2 + 1);
+            }
         }
     }
 }
