@@ -216,6 +216,27 @@ B200JPEG_API int b200jpeg_decoder_get_stage_times(b200jpegDecoder_t decoder, flo
  * returns bytes written or <0 */
 B200JPEG_API int64_t b200jpeg_debug_fetch(b200jpegDecoder_t decoder, int what, int image, int component, void* host_dst, size_t capacity);
 
+/* ---- allocation-free entry point ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The decoder's unstuffing stage (k_unstuff_count / scan / write, the first stage of b200jpeg_decode_batch) for ONE
+ * entropy-coded segment, with its scratch (per-4-KB-chunk counts) in a fixed __device__ array of the library instead of
+ * allocated memory: the call makes no cudaMalloc / cudaFree / allocating library call, it only enqueues four kernels on
+ * cuda_stream and returns.
+ *   d_raw[raw_bytes]   device: the entropy-coded bytes of a scan (file bytes [scan_offset, scan_offset + scan_bytes) of
+ *                      b200jpeg_parse_header), raw_bytes <= b200jpeg_unstuff_noalloc_max_bytes() = 64 MiB, else
+ *                      B200JPEG_STATUS_INVALID_PARAMETER (and a log line naming the limit)
+ *   d_clean[capacity]  device: receives the bytes without FF00 stuffing, FF fill bytes and RSTn markers, cut at the first
+ *                      other marker -- what b200jpeg_debug_fetch(what = 2) shows of a decode of the same file
+ *   d_result[4]        device uint32: [0] bytes written to d_clean, [1] RSTn markers removed, [2] raw bytes consumed,
+ *                      [3] 1 if capacity was too small (d_clean then incomplete)
+ * Limits: the scratch is 131104 bytes per GPU, held from library load to exit, shared by every call and not cleared
+ * between calls beyond what the call itself resets -- calls that overlap on the GPU (two streams, two threads) race on it
+ * and must be serialised by the caller. */
+B200JPEG_API size_t b200jpeg_unstuff_noalloc_max_bytes(void);
+B200JPEG_API int b200jpeg_unstuff_noalloc(int device_id, const uint8_t* d_raw, size_t raw_bytes, uint8_t* d_clean, size_t clean_capacity,
+    uint32_t* d_result, void* cuda_stream);
+
 /* ---- encoder (baseline, standard Huffman tables, JFIF header; mirrors libjpeg-turbo jpeg_compress with
  * jpeg_set_quality(q, TRUE), JDCT_ISLOW, optimize_coding=FALSE) ---- */
 typedef struct

@@ -44,7 +44,8 @@ EXPORTS = ["b200jpeg_version", "b200jpeg_status_string", "b200jpeg_set_log_callb
            "b200jpeg_multi_decoder_create", "b200jpeg_multi_decoder_destroy", "b200jpeg_multi_decode_batch", "b200jpeg_parse_header", "b200jpeg_decoder_create", "b200jpeg_decoder_destroy",
            "b200jpeg_decode_batch", "b200jpeg_decode_prepare", "b200jpeg_decode_run", "b200jpeg_decoder_get_stats", "b200jpeg_decoder_get_stage_times", "b200jpeg_debug_fetch",
            "b200jpeg_encoder_create", "b200jpeg_encoder_destroy", "b200jpeg_encode_batch", "b200jpeg_encoder_get_stats",
-           "b200jpeg_decoder_set_allocators", "b200jpeg_encoder_set_allocators"]
+           "b200jpeg_decoder_set_allocators", "b200jpeg_encoder_set_allocators",
+           "b200jpeg_unstuff_noalloc", "b200jpeg_unstuff_noalloc_max_bytes"]
 
 _lib = None
 
@@ -85,6 +86,8 @@ def lib():
         L.b200jpeg_encoder_get_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
         L.b200jpeg_decoder_set_allocators.argtypes = [C.c_void_p, C.POINTER(Allocators)]
         L.b200jpeg_encoder_set_allocators.argtypes = [C.c_void_p, C.POINTER(Allocators)]
+        L.b200jpeg_unstuff_noalloc_max_bytes.restype = C.c_size_t
+        L.b200jpeg_unstuff_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
