@@ -100,6 +100,7 @@ void plan_begin(BatchPlan& plan, const PlanOptions& opt)
     plan.subseq_bits = opt.subseq_bytes * 8;
     plan.map_unstuff.push_back(0);
     plan.map_subseq.push_back(0);
+    plan.map_fused.push_back(0);
     plan.map_idct.push_back(0);
     plan.map_color.push_back(0);
 }
@@ -259,6 +260,9 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     im.subseq_cta_first = plan.map_subseq.back();
     plan.total_subseq += im.subseq_cta_count * kSubseqCta;
     plan.map_subseq.push_back(im.subseq_cta_first + im.subseq_cta_count);
+    im.fused_cta_first = plan.map_fused.back();
+    im.fused_cta_count = cdiv(im.subseq_count, kFusedOwn);
+    plan.map_fused.push_back(im.fused_cta_first + im.fused_cta_count);
 
     im.coef_off = plan.coef_elems;
     plan.coef_elems = align_up(plan.coef_elems + uint64_t(im.total_blocks) * 64, 64);

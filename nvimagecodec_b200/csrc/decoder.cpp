@@ -83,6 +83,8 @@ DecoderOptions parse_decoder_options(const char* options, const char* plugin_id)
             o.dump_coef = std::atoi(value.c_str()) != 0;
         else if (name == "profile")
             o.profile = std::atoi(value.c_str()) != 0;
+        else if (name == "fused")
+            o.fused = std::atoi(value.c_str()) != 0;
         else if (name == "fast_idct")
             o.fast_idct = std::atoi(value.c_str()) != 0;
     }
@@ -96,7 +98,7 @@ Decoder::~Decoder()
     if (device_ >= 0)
         cudaSetDevice(device_);
     DevBuf* dbufs[] = {&d_blkpos_, &d_stamp_, &d_raw_, &d_clean_, &d_coef_, &d_dc_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
-        &d_rec_, &d_abs_, &d_wl0_, &d_wl1_, &d_sync_, &d_out_};
+        &d_rec_, &d_abs_, &d_wl0_, &d_wl1_, &d_sync_, &d_out_, &d_fusedrec_};
     for (cudaStream_t st : streams_)
         if (st)
             cudaStreamSynchronize(st);
@@ -330,6 +332,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
         (rc = ensure(d_entry_, 8 * size_t(plan_.total_subseq))) || (rc = ensure(d_rec_, 4 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_abs_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_wl0_, 4 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_wl1_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_sync_, sizeof(SyncCounters) * kMaxGroups)) ||
+        (rc = ensure(d_fusedrec_, 8 * size_t(plan_.map_fused.back()) + 8)) ||
         (dev_out_bytes && (rc = ensure(d_out_, dev_out_bytes))))
         return rc;
     for (const HostOutput& ho : host_outs_)
@@ -341,7 +344,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     const size_t off_quant = align_up(off_huff + sizeof(DevHuffTable) * plan_.huff.size(), 256);
     const size_t off_m0 = align_up(off_quant + plan_.quant.size() * sizeof(uint16_t), 256);
     const size_t map_bytes = align_up(sizeof(uint32_t) * (m + 1), 256);
-    const size_t off_cimg = off_m0 + 4 * map_bytes;
+    const size_t off_cimg = off_m0 + 5 * map_bytes;
     const size_t off_scans = off_cimg + align_up(sizeof(uint32_t) * (plan_.total_subseq / kSubseqCta + 1), 256);
     const size_t off_prog = off_scans + align_up(sizeof(ScanDesc) * plan_.scans.size(), 256);
     const size_t meta_bytes = off_prog + align_up(sizeof(uint32_t) * plan_.prog_images.size(), 256);
@@ -357,6 +360,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     std::memcpy(hm + off_m0 + 1 * map_bytes, plan_.map_subseq.data(), sizeof(uint32_t) * (m + 1));
     std::memcpy(hm + off_m0 + 2 * map_bytes, plan_.map_idct.data(), sizeof(uint32_t) * (m + 1));
     std::memcpy(hm + off_m0 + 3 * map_bytes, plan_.map_color.data(), sizeof(uint32_t) * (m + 1));
+    std::memcpy(hm + off_m0 + 4 * map_bytes, plan_.map_fused.data(), sizeof(uint32_t) * (m + 1));
     for (int i = 0; i < m; ++i) { // image of every subsequence CTA (the work-list rounds look items up by subsequence index)
         uint32_t* cimg = reinterpret_cast<uint32_t*>(hm + off_cimg) + plan_.images[i].subseq_first / kSubseqCta;
         for (uint32_t c = 0; c < plan_.images[i].subseq_cta_count; ++c)
@@ -396,6 +400,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.planes = static_cast<uint8_t*>(d_planes_.p);
     dev_.cta_map_unstuff = reinterpret_cast<const uint32_t*>(dm + off_m0 + 0 * map_bytes);
     dev_.cta_map_subseq = reinterpret_cast<const uint32_t*>(dm + off_m0 + 1 * map_bytes);
+    dev_.cta_map_fused = reinterpret_cast<const uint32_t*>(dm + off_m0 + 4 * map_bytes);
+    dev_.fused_rec = static_cast<unsigned long long*>(d_fusedrec_.p);
     dev_.subseq_cta_img = reinterpret_cast<const uint32_t*>(dm + off_cimg);
     dev_.scans = reinterpret_cast<const ScanDesc*>(dm + off_scans);
     dev_.prog_images = reinterpret_cast<const uint32_t*>(dm + off_prog);
@@ -415,13 +421,15 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.stream_words = 0;
     if (opt_.stage_stream && opt_.subseq_bytes <= 256)
         dev_.stream_words = (plan_.subseq_bits / 32 + 3) | 1; // a symbol starting in the last word reads two words past it
-    if (dev_.lut_slots != cfg_lut_slots_ || dev_.stream_words != cfg_stream_words_) {
-        if (huff_configure(dev_, device_, &tail_capacity_) != 0 || tail_capacity_ <= 0) {
+    use_fused_ = opt_.fused && dev_.stream_words != 0;
+    if (dev_.lut_slots != cfg_lut_slots_ || dev_.stream_words != cfg_stream_words_ || dev_.subseq_bits != cfg_subseq_bits_) {
+        if (huff_configure(dev_, device_, &tail_capacity_) != 0 || tail_capacity_ <= 0 || (use_fused_ && fused_configure(dev_) != 0)) {
             log_message(kLogError, "cannot configure the Huffman kernels: %s", cudaGetErrorString(cudaGetLastError()));
             return B200JPEG_STATUS_CUDA_ERROR;
         }
         cfg_lut_slots_ = dev_.lut_slots;
         cfg_stream_words_ = dev_.stream_words;
+        cfg_subseq_bits_ = dev_.subseq_bits;
     }
     dev_.total_subseq = plan_.total_subseq;
     // ---- groups of consecutive images, balanced by entropy-coded bytes; each group runs on its own stream ----
@@ -463,6 +471,9 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
         gr.dev.cta_map_color = dev_.cta_map_color + first;
         gr.dev.base_unstuff = plan_.map_unstuff[first];
         gr.dev.base_subseq = plan_.map_subseq[first];
+        gr.dev.cta_map_fused = dev_.cta_map_fused + first;
+        gr.dev.base_fused = plan_.map_fused[first];
+        gr.dims.fused_ctas = plan_.map_fused[last] - plan_.map_fused[first];
         gr.dev.base_idct = plan_.map_idct[first];
         gr.dev.base_color = plan_.map_color[first];
         gr.dev.worklist[0] = dev_.worklist[0] + plan_.images[first].subseq_first;
@@ -685,17 +696,25 @@ int Decoder::launch_group(int g)
     B2J_CUDA(cudaMemsetAsync(static_cast<ImageState*>(d_states_.p) + m0, 0, sizeof(ImageState) * mc, st));
     B2J_CUDA(cudaMemsetAsync(gr.dev.sync, 0, sizeof(SyncCounters), st));
     stat_launches_ += launch_unstuff(gr.dev, gr.dims, st);
-    mark(kStageSync);
-    stat_launches_ += launch_huff_sync(gr.dev, gr.dims, st);
-    mark(kStageTail);
-    const int ns = launch_huff_tail(gr.dev, gr.dims, st, gr.tail_grid, opt_.tail_launches);
-    if (ns < 0) {
-        log_message(kLogError, "cooperative launch failed: %s", cudaGetErrorString(cudaGetLastError()));
-        return B200JPEG_STATUS_CUDA_ERROR;
+    if (use_fused_) { // the whole entropy-decode stage in one launch; its CTAs hand each other one word per CTA, zero = not there yet
+        B2J_CUDA(cudaMemsetAsync(gr.dev.fused_rec + gr.dev.base_fused, 0, 8 * size_t(gr.dims.fused_ctas), st));
+        mark(kStageSync);
+        stat_launches_ += launch_huff_fused(gr.dev, gr.dims, st);
+        mark(kStageTail);
+        mark(kStageWrite);
+    } else {
+        mark(kStageSync);
+        stat_launches_ += launch_huff_sync(gr.dev, gr.dims, st);
+        mark(kStageTail);
+        const int ns = launch_huff_tail(gr.dev, gr.dims, st, gr.tail_grid, opt_.tail_launches);
+        if (ns < 0) {
+            log_message(kLogError, "cooperative launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+            return B200JPEG_STATUS_CUDA_ERROR;
+        }
+        stat_launches_ += ns;
+        mark(kStageWrite);
+        stat_launches_ += launch_huff_write(gr.dev, gr.dims, st);
     }
-    stat_launches_ += ns;
-    mark(kStageWrite);
-    stat_launches_ += launch_huff_write(gr.dev, gr.dims, st);
     mark(kStageDc);
     stat_launches_ += launch_dc(gr.dev, gr.dims, st);
     stat_launches_ += launch_progressive(gr.dev, gr.prog_first, gr.prog_count, st); // progressive images of the group: scans -> coefficients
@@ -956,6 +975,9 @@ int64_t Decoder::debug_fetch(int what, int image, int comp, void* dst, size_t ca
             return -1;
         src = static_cast<uint8_t*>(d_planes_.p) + im.plane_off[comp];
         bytes = size_t(im.plane_pitch[comp]) * im.hib[comp] * 8;
+    } else if (what == 3) { // developer builds (B2J_FUSED_TRACE): eight time stamps per CTA of k_huff_fused, all CTAs of the batch
+        src = d_exit_.p;
+        bytes = std::min(cap, size_t(plan_.map_fused.back()) * 64);
     } else if (what == 2) {
         src = static_cast<uint8_t*>(d_clean_.p) + im.clean_off;
         bytes = static_cast<ImageState*>(h_states_.p)[planned].clean_len;

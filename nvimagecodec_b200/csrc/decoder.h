@@ -30,6 +30,11 @@ struct DecoderOptions
     bool stage_stream = true; // stage the unstuffed stream in shared memory in the Huffman kernels (subseq_bytes <= 256)
     bool dump_coef = false; // debug: keep dense DCT coefficients for b200jpeg_debug_fetch(what = 0)
     bool profile = false; // record CUDA events between the kernel stages (b200jpeg_decoder_get_stage_times)
+    bool fused = false;     // the entropy-decode stage as ONE kernel (k_huff_fused: synchronisation rounds inside the CTA over a halo, CTAs chained by
+                            // look-back, block pass at the end) instead of k_huff_sync x2 + work-list rounds + k_subseq_scan + k_huff_write.
+                            // Bit-exact and tested, but slower on B200 (C1: 0.87 ms against 0.74 ms): a CTA holds 57 KB of shared memory through its
+                            // latency-bound rounds and the wait for its predecessor, which the pooled work-list rounds of the separate kernels do not
+                            // (profiles/r02s_fused_trace.log).  Needs stage_stream.
     bool fast_idct = false; // the reference's fast_idct=1 selects JDCT_IFAST (libjpeg_turbo_decoder.cpp:272-273,352), whose
                             // pixels differ from islow and between libjpeg-turbo builds: not offered, create() refuses it
 };
@@ -172,7 +177,7 @@ class Decoder
     std::vector<HostOutput> host_outs_;
 
     DevBuf d_blkpos_, d_stamp_, d_raw_, d_clean_, d_coef_, d_dc_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_wl0_,
-        d_wl1_, d_sync_, d_out_;
+        d_wl1_, d_sync_, d_out_, d_fusedrec_;
     DevBuf h_raw_, h_meta_, h_states_;
     BatchDev dev_{};
     LaunchDims dims_{};
@@ -184,7 +189,8 @@ class Decoder
     size_t scratch_bytes_ = 0;
 
     uint64_t stat_launches_ = 0, stat_rounds_ = 0, stat_redone_ = 0;
-    int tail_capacity_ = 0, sm_count_ = 0, cfg_lut_slots_ = -1, cfg_stream_words_ = -1;
+    int tail_capacity_ = 0, sm_count_ = 0, cfg_lut_slots_ = -1, cfg_stream_words_ = -1, cfg_subseq_bits_ = -1;
+    bool use_fused_ = false;
 };
 
 } // namespace b200jpeg

@@ -19,6 +19,11 @@ constexpr int kLutEntries = kLutSize + kLut2Size;
 #endif
 constexpr int kSubseqCta = B2J_SUBSEQ_CTA; // threads per CTA in the subsequence kernels (one subsequence per thread)
 constexpr int kTailCta = 256;         // threads per CTA of the work-list rounds (any subsequence, any thread)
+constexpr int kFusedHalo = 8;         // fused Huffman kernel: subsequences before a CTA's own range that it decodes as well, so that the
+                                      // decoder state at the start of its own range is (almost always) known without its predecessor
+constexpr int kFusedOwn = kSubseqCta - kFusedHalo; // subsequences a CTA of the fused kernel owns
+constexpr int kFusedRunHeads = 6;     // fused kernel, rounds from this one on: of a run of consecutive listed subsequences only the head is
+                                      // worked on, by one thread that walks the whole run (streams that never lock on, e.g. flat image areas)
 constexpr int kUnstuffThreads = 256;  // threads per CTA in the unstuffing kernels
 constexpr int kUnstuffBytesPerThread = 16;
 constexpr int kChunkBytes = kUnstuffThreads * kUnstuffBytesPerThread; // raw bytes per unstuff CTA
@@ -121,6 +126,7 @@ struct ImageDesc
     uint32_t chunk_first, chunk_count;   // unstuff CTAs of this image
     uint32_t subseq_first, subseq_count; // subsequence slots (multiple of kSubseqCta) / used slots
     uint32_t subseq_cta_first, subseq_cta_count;
+    uint32_t fused_cta_first, fused_cta_count; // CTAs of the fused Huffman kernel (kFusedOwn subsequences each)
     uint32_t seg_first;   // index into the segment-start pool; entries [seg_first, seg_first + num_segments]
 
     // Huffman tables of the reconstruction kernel: it decodes the AC symbols of a block itself and stages only AC tables
@@ -189,7 +195,9 @@ struct SyncCounters // device-side bookkeeping of the synchronisation rounds
     uint32_t count[3];    // work-list lengths (rotating: round r reads [r % 3], appends to [(r + 1) % 3])
     uint32_t rounds;      // tail rounds executed
     uint32_t redone;      // subsequences re-decoded in tail rounds
-    uint32_t pad_[3];
+    uint32_t ticket;      // fused kernel: CTAs take their position in launch order from here (a CTA only ever waits for one that started before it)
+    uint32_t chain_redo;  // fused kernel: CTAs whose halo did not deliver the true entry state (they re-walked their range)
+    uint32_t pad_[1];
     uint32_t round_items[kTraceRounds]; // diagnostics (B200JPEG_TRACE): list length of each work-list round ...
     uint32_t round_ns[kTraceRounds];    // ... and the time from the kernel's start to the end of that round, ns
 };
@@ -223,13 +231,16 @@ struct BatchDev // pointers handed to every kernel
     uint8_t* planes;
     const uint32_t* cta_map_unstuff; // prefix arrays: first CTA of each image (+ total at [num_images])
     const uint32_t* cta_map_subseq;
+    const uint32_t* cta_map_fused;   // fused Huffman kernel
+    unsigned long long* fused_rec;   // fused Huffman kernel, per CTA: exit state of its last subsequence (huffman.cuh pack_rel) | (coefficient slots
+                                     // consumed up to there | 1 << 31) << 32; zero until the CTA has published it
     const uint32_t* subseq_cta_img;  // batch image index of every subsequence CTA (indexed by global subsequence / kSubseqCta)
     int32_t image_base;              // batch index of images[0] (a launch may cover a group of consecutive images)
     const uint32_t* cta_map_idct;
     const uint32_t* cta_map_color;
     // a launch may cover only a group of consecutive images: images / states / the CTA maps then point at the group's first
     // image (map values stay absolute) and the kernels add these bases to blockIdx.x
-    uint32_t base_unstuff, base_subseq, base_idct, base_color;
+    uint32_t base_unstuff, base_subseq, base_idct, base_color, base_fused;
     int32_t subseq_bits;   // bits per subsequence
     uint32_t total_subseq;
     int32_t num_tables;    // Huffman tables in the pool

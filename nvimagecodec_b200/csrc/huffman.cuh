@@ -379,6 +379,12 @@ B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32
     return err;
 }
 
+// Decoder state at a subsequence boundary in 32 bits, as the fused kernel keeps it in shared memory and hands it from CTA to
+// CTA: bit position relative to the start of subsequence k (an exit state lies at most one symbol behind the subsequence's
+// end: S + 63 < 2^16 for subsequences up to 4 KB... the planner allows 256 bytes) | (block-in-MCU * 64 + zigzag index) << 16.
+B2J_HD uint32_t pack_rel(uint32_t p, uint32_t k, uint32_t S, uint32_t slot) { return (p - k * S) | (slot << 16); }
+B2J_HD uint32_t rel_pos(uint32_t packed, uint32_t k, uint32_t S) { return k * S + (packed & 0xFFFFu); }
+
 // Run-ahead shortcut for periodic streams (flat image areas: every MCU has the same bits, so a decoder that starts at
 // the wrong phase can stay there for ever and the repair travels one subsequence at a time).  If the decode of
 // subsequence k went from state (p, slot) to (p + S, slot) and the stream words of subsequence k + 1 -- including the two

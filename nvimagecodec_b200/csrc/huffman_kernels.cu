@@ -501,6 +501,357 @@ __global__ void __launch_bounds__(kSubseqCta) k_huff_write(BatchDev b)
 }
 
 // ------------------------------------------------------------------------------------------------------------------
+// H* k_huff_fused: the whole entropy-decode stage of a group of images in ONE launch (default; the kernels above are the
+// `fused=0` path).  A CTA owns kFusedOwn consecutive subsequences of an image and also decodes the kFusedHalo subsequences
+// before them (its halo).  It stages that piece of the stream once and then runs, entirely in shared memory,
+//   round 0   every subsequence from a guessed state (thread per subsequence)
+//   round 1   every subsequence from its predecessor's exit state
+//   rounds 2+ the subsequences whose predecessor's exit state changed, compacted onto the first threads; a thread walks on
+//             into the following subsequences for as long as exit states keep changing and no other thread of the round
+//             starts there (a stretch whose words repeat the one before is not decoded at all: periodic streams of flat
+//             image areas never lock on, huffman.cuh subseq_repeats), until no exit state changes any more.
+// The halo makes the state at the start of the own range right without any word from the CTA before (an unsynchronised
+// chain dies out geometrically: 8 subsequences leave about 3 of 10^5 CTAs wrong).  "About" is not "always", so the CTAs of an
+// image form a chain: each publishes the exit state of its last own subsequence together with the number of coefficient
+// slots consumed up to there (one 64-bit word, fused_rec), its successor compares that state with what its halo delivered
+// and, if they differ, walks its own range again from the true state before it publishes in turn.  CTAs take their
+// place in the chain from a ticket counter, so a CTA only ever waits for CTAs that were started before it.
+// With the slot count of its predecessor a CTA knows the absolute block index at every subsequence start (segmented scan
+// inside the CTA) and finishes with the block pass (DC difference and bit position of the first AC symbol per block): the
+// per-subsequence arrays, the work lists, the cooperative kernel, k_subseq_scan and k_huff_write are not needed.
+// Shared memory (dynamic): [LUTs][TabSel x 10][stream: 256 x W words][exit state x 256][slot count x 256][2 lists x 256 B].
+// ------------------------------------------------------------------------------------------------------------------
+struct FusedSmem
+{
+    uint16_t* lut;
+    TabSel* tabsel;
+    uint32_t* stream;
+    uint32_t* exit;  // pack_rel per subsequence of the CTA
+    uint32_t* rec;   // coefficient slots consumed by the last decode of that subsequence; bit 31: absolute
+    uint8_t* list[2];
+};
+
+__host__ __device__ inline uint32_t fused_stream_words(int subseq_bits) { return (uint32_t(subseq_bits) / 32u + 1u) | 1u; }
+
+static size_t fused_smem_bytes(const BatchDev& b)
+{
+    return size_t(b.lut_slots) * kLutEntries * 2 + kMaxBlocksPerMcu * sizeof(TabSel) + (size_t(kSubseqCta) * fused_stream_words(b.subseq_bits) + 4) * 4 +
+           size_t(kSubseqCta) * (4 + 4 + 2);
+}
+
+#if defined(B2J_FUSED_TRACE) // developer build (tools/build_variant.sh): %globaltimer stamps of every CTA's phases in the (otherwise unused) sub_exit array
+#define B2J_STAMP(j)                                                          \
+    do {                                                                      \
+        if (threadIdx.x == 0) {                                               \
+            unsigned long long t__;                                           \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));           \
+            b.sub_exit[size_t(trace_cta) * 8 + (j)] = t__;                    \
+        }                                                                     \
+    } while (0)
+#else
+#define B2J_STAMP(j) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(kSubseqCta, 4) k_huff_fused(BatchDev b)
+{
+    __shared__ uint32_t s_ticket, s_cnt[2], s_start[2][kSubseqCta / 32], s_warp[kSubseqCta / 32], s_agg, s_ok;
+    __shared__ unsigned long long s_pred;
+    __shared__ __align__(8) uint64_t s_bar;
+    const uint32_t i = threadIdx.x, lane = i & 31u, warp = i >> 5;
+    if (i == 0) {
+        s_ticket = atomicAdd(&b.sync->ticket, 1u);
+        s_cnt[0] = s_cnt[1] = 0;
+        mbar_init(&s_bar, 1);
+    }
+    if (i < 2 * (kSubseqCta / 32))
+        (&s_start[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t cta_abs = s_ticket + b.base_fused;
+#if defined(B2J_FUSED_TRACE)
+    const uint32_t trace_cta = cta_abs;
+#endif
+    B2J_STAMP(0);
+    const int img = find_image_warp(b.cta_map_fused, b.num_images, cta_abs);
+    const ImageDesc& im = b.images[img];
+    const uint32_t c = cta_abs - b.cta_map_fused[img];
+    const uint32_t h = c ? uint32_t(kFusedHalo) : 0u;
+    const uint32_t k0 = c * uint32_t(kFusedOwn) - h;
+    const uint32_t clean_len = b.states[img].clean_len, clean_bits = clean_len * 8u;
+    const uint32_t S = uint32_t(b.subseq_bits), spw = S >> 5, W = fused_stream_words(b.subseq_bits);
+    const uint32_t live = uint32_t((uint64_t(clean_bits) + S - 1u) / S); // subsequences of the image that hold data
+    const uint32_t nv = live > k0 ? min(uint32_t(kFusedOwn) + h, live - k0) : 0u; // threads of this CTA with a subsequence
+    if (nv <= h)
+        return; // nothing of its own (the plan counts subsequences of the stuffed length); the same holds for every later CTA of the image
+
+    FusedSmem sm;
+    {
+        unsigned char* base = g_dyn_smem;
+        sm.lut = reinterpret_cast<uint16_t*>(base);
+        sm.tabsel = reinterpret_cast<TabSel*>(base + size_t(b.lut_slots) * kLutEntries * 2);
+        sm.stream = reinterpret_cast<uint32_t*>(sm.tabsel + kMaxBlocksPerMcu);
+        sm.exit = sm.stream + size_t(kSubseqCta) * W + 4;
+        sm.rec = sm.exit + kSubseqCta;
+        sm.list[0] = reinterpret_cast<uint8_t*>(sm.rec + kSubseqCta);
+        sm.list[1] = sm.list[0] + kSubseqCta;
+    }
+    // ---- staging: tables by bulk copy, the stream of subsequences [k0, k0 + 256) byte-swapped to bit order; thread t's region
+    // holds its subsequence and the first word(s) of the next (a symbol that starts in the last word reads one word on)
+    if (i == 0) {
+        mbar_expect_tx(&s_bar, uint32_t(im.ntabs) * kLutEntries * 2u);
+        for (int s = 0; s < im.ntabs; ++s)
+            bulk_copy_g2s(sm.lut + s * kLutEntries, b.huff[im.tab_pool[s]].lut, kLutEntries * 2u, &s_bar);
+    }
+    if (i < kMaxBlocksPerMcu)
+        sm.tabsel[i] = im.tabsel_s[i];
+    {
+        const uint32_t extra = W - spw;
+        const uint32_t* words = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
+        const uint32_t first = k0 * spw, max_words = (im.raw_len + 16u) >> 2;
+        const uint32_t total = kSubseqCta * spw + extra;
+        for (uint32_t g = i; g < total; g += kSubseqCta) {
+            const uint32_t a = first + g;
+            const uint32_t v = a < max_words ? __byte_perm(words[a], 0, 0x0123) : 0u;
+            const uint32_t t = g / spw, j = g - t * spw;
+            if (t < kSubseqCta)
+                sm.stream[t * W + j] = v;
+            if (j < extra && t > 0)
+                sm.stream[(t - 1) * W + spw + j] = v;
+        }
+        if (i < 4)
+            sm.stream[size_t(kSubseqCta) * W + i] = 0;
+    }
+    sm.exit[i] = 0xFFFFFFFFu;
+    sm.rec[i] = 0;
+    mbar_wait(&s_bar, 0);
+    __syncthreads();
+    B2J_STAMP(1);
+
+    const uint32_t stream_s = uint32_t(__cvta_generic_to_shared(sm.stream));
+    HuffEnv env = make_env(b, im, clean_len, nullptr, sm.lut, sm.tabsel, 0);
+    auto point_env = [&](uint32_t li) { // the staged region of list index li, addressed as if the whole stream were there
+        const uint32_t off = li * W - (k0 + li) * spw;
+        env.words = sm.stream + off;
+        env.words_s = stream_s + off * 4u;
+    };
+    // word j (0 .. spw + 1) of the subsequence at list index li, li <= 254
+    auto word_of = [&](uint32_t li, uint32_t j) { return j <= spw ? sm.stream[li * W + j] : sm.stream[(li + 1u) * W + j - spw]; };
+
+    // ---- synchronisation rounds ----
+    uint32_t n_cur = 0, cur = 0, redone = 0, round = 0, inc = 0, exc = 0;
+    const bool own = i >= h && i < nv;
+    unsigned long long pred = 0;
+    for (;; ++round) {
+        int li = -1;
+        if (round == 0)
+            li = i < nv ? int(i) : -1;
+        else if (round == 1)
+            li = (i < nv && i > 0) ? int(i) : -1; // i == 0: the image's first subsequence (state known) or the first of the halo (keeps its guess)
+        else if (i < n_cur)
+            li = sm.list[cur][i];
+        uint32_t E = 0;
+        if (li > 0)
+            E = sm.exit[li - 1];
+        if (round >= 2 && li >= 0)
+            atomicOr(&s_start[round & 1][li >> 5], 1u << (li & 31));
+        __syncthreads(); // every entry state is read before any exit state changes: the rounds are deterministic
+        // Late rounds: when a whole run of consecutive subsequences is still listed, decoding its members side by side is
+        // wasted (each will change again when the state from the run's head arrives): only the head's thread works and
+        // walks the run, the others leave their items to it.
+        const bool run_heads = round >= uint32_t(kFusedRunHeads);
+        if (run_heads && li > 0 && ((s_start[round & 1][(li - 1) >> 5] >> ((li - 1) & 31)) & 1u))
+            li = -1;
+        if (li >= 0) {
+            bool prev_shift = false, in_run = true;
+            for (;;) {
+                const uint32_t kk = k0 + uint32_t(li);
+                uint32_t X;
+                if (prev_shift && im.num_segments == 1 && uint32_t(li) + 2u < uint32_t(kSubseqCta) && uint64_t(kk + 1) * S + 64u <= uint64_t(clean_bits)) {
+                    bool same = true;
+                    for (uint32_t j = 0; j < spw + 2u && same; ++j)
+                        same = word_of(uint32_t(li) - 1u, j) == word_of(uint32_t(li), j);
+                    prev_shift = same;
+                }
+                else
+                    prev_shift = false;
+                bool changed;
+                if (prev_shift) { // the same words from the same relative state: the same decode, S bits further on
+                    X = E;
+                    changed = X != sm.exit[li];
+                    sm.exit[li] = X;
+                    sm.rec[li] = sm.rec[li - 1];
+                } else {
+                    HuffState s;
+                    if (round == 0) {
+                        s.p = kk * S;
+                        s.z = 0;
+                        s.blk = 0;
+                        s.abs = kk == 0;
+                    } else {
+                        s.p = rel_pos(E, kk - 1u, S);
+                        s.z = (E >> 16) & 63u;
+                        s.blk = E >> 22;
+                        s.abs = false;
+                    }
+                    s.nblk = 0;
+                    const uint32_t z_entry = s.z;
+                    point_env(uint32_t(li));
+                    if (round < 2) // every lane of every warp decodes: fewest instructions (two stream words fetched per symbol)
+                        decode_span<false, true, true>(env, s, (kk + 1u) * S, nullptr);
+                    else // a few lanes decode and everything else waits for them: shortest dependency chain (sliding window)
+                        decode_span<false, true, false>(env, s, (kk + 1u) * S, nullptr);
+                    X = pack_rel(s.p, kk, S, s.blk * 64u + s.z);
+                    changed = X != sm.exit[li];
+                    sm.exit[li] = X;
+                    const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
+                    sm.rec[li] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
+                }
+                if (round == 0)
+                    break;
+                if (round >= 2)
+                    ++redone;
+                if (uint32_t(li) + 1u >= nv)
+                    break;
+                const bool next_listed = round >= 2 && ((s_start[round & 1][(li + 1) >> 5] >> ((li + 1) & 31)) & 1u);
+                bool push = false, stop;
+                if (round == 1) { // a plain Jacobi round
+                    push = changed;
+                    stop = true;
+                } else if (!run_heads) { // a walk ends where nothing changes any more, or where another thread's item begins
+                    push = changed && next_listed;
+                    stop = !changed || next_listed;
+                } else if (next_listed && !in_run) { // the head of another run: its thread read the old exit state
+                    push = changed;
+                    stop = true;
+                } else {
+                    stop = !next_listed && !changed;
+                    if (!next_listed)
+                        in_run = false;
+                }
+                if (push)
+                    sm.list[cur ^ 1u][atomicAdd(&s_cnt[cur ^ 1u], 1u)] = uint8_t(li + 1); // an item of the next round
+                if (stop)
+                    break;
+                prev_shift = (X == E); // moved by exactly one subsequence length
+                E = X;
+                ++li;
+            }
+        }
+        __syncthreads();
+        if (round < 3)
+            B2J_STAMP(2 + round);
+        const uint32_t n_next = s_cnt[cur ^ 1u];
+        __syncthreads();
+        if (i == 0)
+            s_cnt[cur] = 0;
+        if (i < kSubseqCta / 32)
+            s_start[round & 1][i] = 0;
+        cur ^= 1u;
+        n_cur = n_next;
+        if (round >= 1 && n_cur == 0) {
+            // ---- nothing changes any more.  Slots consumed up to every subsequence start of the own range: segmented
+            // inclusive scan, first without the predecessor's count so that the link to the next CTA is short ----
+            const uint32_t mine = own ? sm.rec[i] : 0u;
+            inc = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+                if (lane >= uint32_t(o))
+                    inc = seg_combine(tprev, inc);
+            }
+            if (lane == 31)
+                s_warp[warp] = inc;
+            __syncthreads();
+            uint32_t pre = 0;
+            for (uint32_t w = 0; w < warp; ++w)
+                pre = seg_combine(pre, s_warp[w]);
+            inc = seg_combine(pre, inc);
+            exc = __shfl_up_sync(0xFFFFFFFFu, inc, 1);
+            if (lane == 0)
+                exc = pre;
+            if (i == nv - 1u)
+                s_agg = inc;
+            __syncthreads();
+            B2J_STAMP(5);
+            // ---- the link: thread 0 waits for the word of the CTA before this one in the image, compares that CTA's last
+            // exit state with what the halo delivered and, if they agree, publishes this CTA's word at once ----
+            if (i == 0) {
+                unsigned long long v = 1ull << 63; // the first CTA of an image starts at an absolute zero
+                bool ok = true;
+                if (c) {
+                    const volatile unsigned long long* src = b.fused_rec + (cta_abs - 1u);
+                    uint32_t spins = 0;
+                    while (((v = *src) >> 63) == 0) {
+                        __nanosleep(32);
+                        if (++spins > (1u << 24)) { // about a second: the predecessor is gone (it cannot be, but never hang a device over it)
+                            atomicOr(&b.states[img].error, kErrNotConverged);
+                            v = (1ull << 63) | sm.exit[h - 1u];
+                            break;
+                        }
+                    }
+                    ok = uint32_t(v) == sm.exit[h - 1u];
+                }
+                if (ok)
+                    b.fused_rec[cta_abs] = (unsigned long long)sm.exit[nv - 1u] | ((unsigned long long)(seg_combine(uint32_t(v >> 32), s_agg) | 0x80000000u) << 32);
+                else { // the halo was too short for this stretch of the stream: walk the own range again from the true state
+                    sm.exit[h - 1u] = uint32_t(v);
+                    sm.list[cur][0] = uint8_t(h);
+                    atomicAdd(&b.sync->chain_redo, 1u);
+                }
+                s_pred = v;
+                s_ok = ok ? 1u : 0u;
+            }
+            __syncthreads();
+            pred = s_pred;
+            if (s_ok)
+                break;
+            n_cur = 1;
+        }
+    }
+    exc = seg_combine(uint32_t(pred >> 32), exc); // bit 31 of a published count is set: absolute
+    B2J_STAMP(6);
+    if (i == 0)
+        atomicMax(&b.sync->rounds, round >= 1u ? round - 1u : 0u);
+    if (redone)
+        atomicAdd(&b.sync->redone, redone);
+    if (!own)
+        return;
+
+    // ---- block pass: per block the DC difference and the bit position of its first AC symbol ----
+    const uint32_t k = k0 + i;
+    HuffState s;
+    if (k == 0) {
+        s.p = 0;
+        s.z = 0;
+        s.blk = 0;
+        s.nblk = 0;
+    } else {
+        const uint32_t E = sm.exit[i - 1u];
+        s.p = rel_pos(E, k - 1u, S);
+        s.z = (E >> 16) & 63u;
+        s.blk = E >> 22;
+        s.nblk = (exc & 0x7FFFFFFFu) >> 6;
+    }
+    s.abs = true;
+    BlkOut out;
+    out.dc = b.dc + im.coef_off / 64;
+    out.pos = b.blk_pos + im.coef_off / 64;
+    const uint32_t nblk_in = s.nblk;
+    point_env(i);
+    const uint32_t err = decode_span<true, true>(env, s, (k + 1u) * S, &out);
+    if (s.nblk == im.total_blocks && s.z == 0 && nblk_in < im.total_blocks)
+        b.states[img].done_blocks = s.nblk; // this thread completed the last block
+    if (err)
+        atomicOr(&b.states[img].error, err);
+#if defined(B2J_FUSED_TRACE)
+    if (i == h) {
+        unsigned long long t__;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));
+        b.sub_exit[size_t(trace_cta) * 8 + 7] = t__;
+    }
+#endif
+}
+
+// ------------------------------------------------------------------------------------------------------------------
 // Launchers
 // ------------------------------------------------------------------------------------------------------------------
 static size_t main_smem_bytes(const BatchDev& b) { return size_t(b.lut_slots) * kLutEntries * 2 + kMaxBlocksPerMcu * sizeof(TabSel) + size_t(kSubseqCta) * b.stream_words * 4; }
@@ -546,6 +897,17 @@ int launch_huff_tail(const BatchDev& b, const LaunchDims& d, cudaStream_t st, in
         cudaSuccess)
         return -1;
     return 1 + plain_rounds;
+}
+
+int fused_configure(const BatchDev& b)
+{
+    return cudaFuncSetAttribute(k_huff_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, int(fused_smem_bytes(b))) == cudaSuccess ? 0 : -1;
+}
+
+int launch_huff_fused(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
+{
+    k_huff_fused<<<d.fused_ctas, kSubseqCta, fused_smem_bytes(b), st>>>(b);
+    return 1;
 }
 
 int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st)

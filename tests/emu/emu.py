@@ -52,9 +52,11 @@ def encode(pixels, quality=90, subsampling=3, restart_interval=0, planar=False):
     return out[:n].tobytes()
 
 
-def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=1 << 30, jacobi=True, want_coef=False, slots=None, rois=None, orients=None):
+def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=1 << 30, jacobi=True, want_coef=False, slots=None, rois=None, orients=None,
+                 fused=False, halo=0):
     """dims: list of (w, h).  Returns (outputs, statuses, rounds, coefs).  rois: per image None or (x, y, w, h): the output
-    holds that region only"""
+    holds that region only.  fused: emulate k_huff_fused (decoder option fused=1) instead of the separate kernels;
+    halo: its halo length (0 = the kernel's kFusedHalo; 1 makes the chain validation between CTAs fail often)"""
     n = len(datas)
     if rois is not None:
         dims = [(r[2], r[3]) if r else d for d, r in zip(dims, rois)]
@@ -75,10 +77,10 @@ def decode_batch(datas, dims, fmt=4, fancy=True, subseq_bytes=128, max_rounds=1 
     stats = (C.c_uint64 * 8)()
     lib().emu_decode_batch(n, (C.c_char_p * n)(*datas), (C.c_size_t * n)(*[len(d) for d in datas]),
                            (C.c_void_p * n)(*[o.ctypes.data for o in outs]), (C.c_int64 * n)(*strides), (C.c_int * n)(*fmts),
-                           int(fancy), subseq_bytes, max_rounds, int(jacobi), st, C.byref(rounds),
+                           int(fancy), subseq_bytes, max_rounds, (2 | (halo << 8)) if fused else 1, st, C.byref(rounds),
                            (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None, stats,
                            (C.c_int * (4 * n))(*[v for r in rois for v in (r if r else (0, 0, 0, 0))]) if rois is not None else None,
                            (C.c_int * n)(*[((o[0] // 90) & 3 | (4 if o[1] else 0) | (8 if o[2] else 0)) if o else 0 for o in orients])
                            if orients is not None else None)
-    decode_batch.last_stats = {"rounds": int(stats[0]), "redone": int(stats[1]), "subsequences": int(stats[2]), "skipped": int(stats[3])}
+    decode_batch.last_stats = {"rounds": int(stats[0]), "redone": int(stats[1]), "subsequences": int(stats[2]), "skipped": int(stats[3]), "chain_redo": int(stats[4])}
     return outs, list(st), rounds.value, coefs

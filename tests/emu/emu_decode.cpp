@@ -165,7 +165,6 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     }
 
     // ---- synchronisation: round 0 (guessed state), round 1 (predecessor's exit), then work-list rounds ----
-    (void)jacobi;
     clean_sw.assign(clean.size() + 64, 0);
     std::memcpy(clean_sw.data(), clean.data(), clean.size());
     for (size_t w = 0; w + 4 <= clean_sw.size(); w += 4) {
@@ -175,7 +174,11 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         std::memcpy(clean_sw.data() + w, &v, 4);
     }
     std::vector<uint32_t> wl, wl_next;
-    unsigned long long redone = 0, skipped = 0;
+    unsigned long long redone = 0, skipped = 0, chain_redo = 0;
+    int rounds = 2;
+    const bool fused = (jacobi & 0xFF) == 2;
+    const uint32_t H = (jacobi >> 8) ? uint32_t(jacobi >> 8) : uint32_t(kFusedHalo), OWN = uint32_t(kSubseqCta) - H;
+    if (!fused) {
     for (int round = 0; round < 2; ++round) {
         const std::vector<unsigned long long> snap = ex; // worst-case race: every thread sees its predecessor's old exit
         for (int i = 0; i < m; ++i) {
@@ -212,7 +215,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
     std::vector<uint32_t> stamp(plan.total_subseq, 0);
     for (uint32_t t : wl)
         stamp[t] = 1;
-    int rounds = 2;
+    rounds = 2;
     while (!wl.empty() && rounds < max_rounds) {
         const int r = rounds - 2;
         const bool run_ahead = r >= kRunAheadFrom;
@@ -282,14 +285,6 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         wl.swap(wl_next);
         ++rounds;
     }
-    if (rounds_used) *rounds_used = rounds;
-    if (stats) {
-        stats[0] = uint64_t(rounds);
-        stats[1] = redone;
-        stats[2] = plan.total_subseq;
-        stats[3] = skipped;
-    }
-
     // ---- segmented scan of slot counts + consistency check (k_subseq_scan) ----
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];
@@ -303,6 +298,7 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             sabs[t] = A;
         }
     }
+    }
     // ---- block pass (k_huff_write): per block the DC difference and the position of its first AC symbol; the
     // subsequences in reverse order to show that the threads do not depend on each other ----
     std::vector<uint8_t> clean_sw2 = clean_sw;
@@ -312,6 +308,126 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
         HuffEnv env = make_env(i, true, s_lut);
         env.words = reinterpret_cast<const uint32_t*>(clean_sw2.data()) + (env.words - reinterpret_cast<const uint32_t*>(clean.data()));
         const uint32_t clean_bits = states[i].clean_len * 8u;
+        if (fused) {
+            // k_huff_fused: per CTA (kFusedOwn own subsequences + halo) rounds in "shared memory", validation against the
+            // predecessor's published state, segmented scan, block pass
+            BlkOut out;
+            out.dc = dcv.data() + im.coef_off / 64;
+            out.pos = blkpos.data() + im.coef_off / 64;
+            const uint32_t live = uint32_t((uint64_t(clean_bits) + S - 1u) / S);
+            const uint32_t spw = S >> 5;
+            const uint32_t* bwords = env.words; // byte-swapped stream of the image
+            uint32_t pred_state = 0, pred_abs = 0x80000000u;
+            const uint32_t nctas = (im.subseq_count + OWN - 1) / OWN;
+            for (uint32_t c = 0; c < nctas; ++c) {
+                const uint32_t h = c ? H : 0u, k0 = c * OWN - h;
+                const uint32_t nv = live > k0 ? std::min(OWN + h, live - k0) : 0u;
+                if (nv <= h)
+                    break;
+                std::vector<uint32_t> xs(kSubseqCta, 0xFFFFFFFFu), rc(kSubseqCta, 0);
+                std::vector<uint32_t> list, next;
+                bool validated = c == 0;
+                for (uint32_t round = 0;; ++round) {
+                    std::vector<int> items;
+                    if (round == 0) for (uint32_t i2 = 0; i2 < nv; ++i2) items.push_back(int(i2));
+                    else if (round == 1) for (uint32_t i2 = 1; i2 < nv; ++i2) items.push_back(int(i2));
+                    else for (uint32_t v : list) items.push_back(int(v));
+                    std::vector<uint32_t> entries(items.size(), 0);
+                    std::vector<uint8_t> start(kSubseqCta + 1, 0);
+                    for (size_t q = 0; q < items.size(); ++q) {
+                        if (items[q] > 0) entries[q] = xs[items[q] - 1];
+                        if (round >= 2) start[items[q]] = 1;
+                    }
+                    next.clear();
+                    const bool run_heads = round >= uint32_t(kFusedRunHeads);
+                    for (size_t q = 0; q < items.size(); ++q) {
+                        int li = items[q];
+                        if (run_heads && li > 0 && start[li - 1])
+                            continue;
+                        uint32_t E = entries[q];
+                        bool prev_shift = false, in_run = true;
+                        for (;;) {
+                            const uint32_t kk = k0 + uint32_t(li);
+                            uint32_t X;
+                            if (prev_shift && im.num_segments == 1 && uint32_t(li) + 2u < uint32_t(kSubseqCta) && uint64_t(kk + 1) * S + 64u <= uint64_t(clean_bits)) {
+                                bool same = true;
+                                for (uint32_t j = 0; j < spw + 2u && same; ++j)
+                                    same = bwords[(kk - 1u) * spw + j] == bwords[kk * spw + j];
+                                prev_shift = same;
+                            } else
+                                prev_shift = false;
+                            bool changed;
+                            if (prev_shift) {
+                                X = E;
+                                changed = X != xs[li];
+                                xs[li] = X;
+                                rc[li] = rc[li - 1];
+                                ++skipped;
+                            } else {
+                                HuffState s;
+                                if (round == 0) { s.p = kk * S; s.z = 0; s.blk = 0; s.abs = kk == 0; }
+                                else { s.p = rel_pos(E, kk - 1u, S); s.z = (E >> 16) & 63u; s.blk = E >> 22; s.abs = false; }
+                                s.nblk = 0;
+                                const uint32_t z_entry = s.z;
+                                decode_span<false, true>(env, s, (kk + 1u) * S, nullptr);
+                                X = pack_rel(s.p, kk, S, s.blk * 64u + s.z);
+                                changed = X != xs[li];
+                                xs[li] = X;
+                                const uint32_t n = s.abs ? s.nblk * 64u + s.z : s.nblk * 64u + s.z - z_entry;
+                                rc[li] = (n & 0x7FFFFFFFu) | (s.abs ? 0x80000000u : 0u);
+                            }
+                            if (round == 0) break;
+                            if (round >= 2) ++redone;
+                            if (uint32_t(li) + 1u >= nv) break;
+                            const bool next_listed = round >= 2 && start[li + 1];
+                            bool push = false, stop;
+                            if (round == 1) { push = changed; stop = true; }
+                            else if (!run_heads) { push = changed && next_listed; stop = !changed || next_listed; }
+                            else if (next_listed && !in_run) { push = changed; stop = true; }
+                            else { stop = !next_listed && !changed; if (!next_listed) in_run = false; }
+                            if (push) next.push_back(uint32_t(li + 1));
+                            if (stop) break;
+                            prev_shift = (X == E);
+                            E = X;
+                            ++li;
+                        }
+                    }
+                    list.swap(next);
+                    if (round >= 1 && list.empty()) {
+                        rounds = std::max(rounds, int(round) + 1);
+                        if (validated) break;
+                        validated = true;
+                        if (pred_state == xs[h - 1]) break;
+                        xs[h - 1] = pred_state;
+                        list.assign(1, h);
+                        ++chain_redo;
+                    }
+                }
+                uint32_t A = pred_abs;
+                std::vector<uint32_t> exc(kSubseqCta, 0);
+                for (uint32_t i2 = h; i2 < nv; ++i2) {
+                    exc[i2] = A;
+                    A = (rc[i2] & 0x80000000u) ? rc[i2] : A + rc[i2];
+                }
+                pred_state = xs[nv - 1];
+                pred_abs = A | 0x80000000u;
+                for (int64_t i64 = int64_t(nv) - 1; i64 >= int64_t(h); --i64) { // reverse order: the threads do not depend on each other
+                    const uint32_t i2 = uint32_t(i64), k = k0 + i2;
+                    HuffState s;
+                    if (k == 0) { s.p = 0; s.z = 0; s.blk = 0; s.nblk = 0; }
+                    else {
+                        const uint32_t E = xs[i2 - 1];
+                        s.p = rel_pos(E, k - 1u, S); s.z = (E >> 16) & 63u; s.blk = E >> 22;
+                        s.nblk = (exc[i2] & 0x7FFFFFFFu) >> 6;
+                    }
+                    s.abs = true;
+                    const uint32_t nblk_in = s.nblk;
+                    uint32_t err = decode_span<true, true>(env, s, (k + 1u) * S, &out);
+                    if (s.nblk == im.total_blocks && s.z == 0 && nblk_in < im.total_blocks) states[i].done_blocks = s.nblk;
+                    states[i].error |= err;
+                }
+            }
+        } else
         for (int64_t k64 = int64_t(im.subseq_cta_count) * kSubseqCta - 1; k64 >= 0; --k64) {
             const uint32_t k = uint32_t(k64), t = im.subseq_first + k;
             if (uint64_t(k) * S >= uint64_t(clean_bits)) continue;
@@ -355,6 +471,15 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             }
         }
     }
+    if (rounds_used) *rounds_used = rounds;
+    if (stats) {
+        stats[0] = uint64_t(rounds);
+        stats[1] = redone;
+        stats[2] = plan.total_subseq;
+        stats[3] = skipped;
+        stats[4] = chain_redo;
+    }
+
     // ---- progressive images (k_prog_decode): the scans one after the other into the dense coefficients ----
     for (int i = 0; i < m; ++i) {
         const ImageDesc& im = plan.images[i];

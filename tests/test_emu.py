@@ -25,16 +25,36 @@ def corpus():
     return [make_jpeg(1000 + i, w, h, samp, q, restart_interval=ri, gray=g) for i, (w, h, samp, q, ri, g) in enumerate(CASES)]
 
 
+@pytest.mark.parametrize("fused", [False, True])
 @pytest.mark.parametrize("fancy", [1, 0])
 @pytest.mark.parametrize("subseq", [32, 128, 512])
-def test_emulated_pipeline_bit_exact(fancy, subseq):
+def test_emulated_pipeline_bit_exact(fancy, subseq, fused):
     datas = corpus()
     dims = [(c[0], c[1]) for c in CASES]
-    outs, st, rounds, _ = emu.decode_batch(datas, dims, 4, fancy, subseq)
+    outs, st, rounds, _ = emu.decode_batch(datas, dims, 4, fancy, subseq, fused=fused)
     assert st == [0] * len(datas)
     for d, o in zip(datas, outs):
         assert np.array_equal(o, port.decode(d, port.FMT_I_RGB, fancy))
     assert rounds < 64
+
+
+def test_emulated_fused_chain_with_short_halo():
+    """k_huff_fused hands the decoder state from CTA to CTA: a CTA whose halo did not deliver the true entry state walks its
+    range again.  With the kernel's halo (8 subsequences) that is rare; a halo of one subsequence makes it the rule, and
+    the result must still be exact -- with and without restart markers, 4:2:0 (slow to lock on) and 4:4:4."""
+    datas = [make_jpeg(7000, 1920, 1080, (2, 2), 90), make_jpeg(7001, 1600, 1200, (1, 1), 85), make_jpeg(7002, 1280, 960, (2, 2), 92, restart_interval=40),
+             make_jpeg(7003, 2048, 1536, (2, 1), 75)]
+    dims = [(1920, 1080), (1600, 1200), (1280, 960), (2048, 1536)]
+    want = [port.decode(d, port.FMT_I_RGB, True) for d in datas]
+    redo = {}
+    for halo in (1, 2, 0):
+        outs, st, rounds, _ = emu.decode_batch(datas, dims, 4, 1, 128, fused=True, halo=halo)
+        assert st == [0] * 4
+        for o, w in zip(outs, want):
+            assert np.array_equal(o, w)
+        redo[halo] = emu.decode_batch.last_stats["chain_redo"]
+    assert redo[1] > 0 and redo[1] >= redo[2] >= redo[0]
+    assert redo[0] <= 1, redo  # the kernel's halo: a mismatch is a once-in-thousands event
 
 
 def test_emulated_coefficients_match_reference():
@@ -187,9 +207,10 @@ def test_emulated_periodic_streams_converge():
     half[:256] = np.random.default_rng(6).integers(0, 255, (256, 2048, 3))
     for img, samp, opt in ((flat, (2, 2), False), (half, (2, 2), False), (flat, (1, 1), True), (half, (2, 1), True)):
         d = ref.ljt_encode(img, 90, samp, optimize=opt)
-        outs, st, rounds, _ = emu.decode_batch([d], [(2048, 2048)], 4, 1, 128)
-        assert st == [0] and np.array_equal(outs[0], port.decode(d, port.FMT_I_RGB, True))
-        assert rounds <= 2 + 4 + 8, rounds  # Jacobi rounds, then a few run-ahead rounds
+        for fused in (False, True):  # k_huff_fused: its rounds from kFusedRunHeads on walk the runs the same way inside the CTA
+            outs, st, rounds, _ = emu.decode_batch([d], [(2048, 2048)], 4, 1, 128, fused=fused)
+            assert st == [0] and np.array_equal(outs[0], port.decode(d, port.FMT_I_RGB, True))
+            assert rounds <= 2 + 4 + 8, rounds  # Jacobi rounds, then a few run-ahead rounds
     d = ref.ljt_encode(flat, 90, (2, 2))
     emu.decode_batch([d], [(2048, 2048)], 4, 1, 128)
     assert emu.decode_batch.last_stats["skipped"] > 100  # the periodic stretch was walked without decoding it

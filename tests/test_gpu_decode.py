@@ -157,6 +157,41 @@ def test_subsequence_sizes_and_rounds(torch_mod, refdec):
             assert st[i] == 0 and np.array_equal(g, w), (opts, i)
 
 
+def test_fused_entropy_kernel(torch_mod, refdec):
+    """fused=1: the whole entropy-decode stage as one kernel (k_huff_fused: rounds inside the CTA over a halo, CTAs chained by
+    look-back, block pass at the end).  Every sampling mode, restart intervals, tiny images, big images whose streams span
+    many CTAs, flat images (periodic streams that never lock on: the chain between CTAs has to repair them) and damaged
+    data -- pixels and coefficients as the reference has them."""
+    datas = [make_jpeg(1000 + i, w, h, samp, q, restart_interval=ri, gray=g) for i, (w, h, samp, q, ri, g) in enumerate(CASES)]
+    flat = np.full((1536, 2048, 3), 131, np.uint8)
+    half = flat.copy()
+    half[:256] = np.random.default_rng(6).integers(0, 255, (256, 2048, 3))
+    datas += [ref.ljt_encode(flat, 90, (1, 1), optimize=True), ref.ljt_encode(half, 90, (2, 2), optimize=False), ref.ljt_encode(half, 90, (2, 1), optimize=True),
+              make_jpeg(4200, 3840, 2160, (1, 1), 90), make_jpeg(4201, 3840, 2160, (2, 2), 90, restart_interval=240)]
+    want, _, _ = refdec[1].decode_host(datas)
+    for opts in (":fancy_upsampling=1 :fused=1", ":fancy_upsampling=1 :fused=1 :groups=1", ":fancy_upsampling=1 :fused=1 :subseq_bytes=64",
+                 ":fancy_upsampling=1 :fused=1 :subseq_bytes=256 :profile=1"):
+        got, st, dec = gpu_decode(torch_mod, datas, 4, opts, want_decoder=True)
+        for i, (g, w) in enumerate(zip(got, want)):
+            assert st[i] == 0 and np.array_equal(g, w), (opts, i, diagnose(dec, datas, i))
+        assert dec.stats()["launches"] < 12 * 8  # one Huffman launch per group instead of six
+        for i in (0, 4, 16):
+            wantc = util.mcu_order_coefficients(datas[i])
+            assert np.array_equal(dec.debug_fetch(0, i, 0, wantc.size * 2, np.int16), wantc), (opts, i)
+        dec.close()
+    # damaged data: contained exactly as by the separate kernels (same statuses, good images untouched)
+    good = make_jpeg(4300, 640, 480, (2, 2), 90)
+    rng = np.random.default_rng(3)
+    bad = bytearray(make_jpeg(4301, 1280, 960, (2, 2), 90))
+    for pos in rng.integers(len(bad) // 2, len(bad) - 4, 40):
+        bad[pos] ^= 1 << int(rng.integers(0, 8))
+    batch = [good, bytes(bad), good[:len(good) // 2], good]
+    a, sa = gpu_decode(torch_mod, batch, 4, ":fancy_upsampling=1 :fused=1")
+    b, sb = gpu_decode(torch_mod, batch, 4, ":fancy_upsampling=1 :fused=0")
+    assert sa[0] == 0 and sa[3] == 0 and list(sa) == list(sb)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[3], b[3])
+
+
 def test_bad_and_unsupported_streams(torch_mod):
     good = make_jpeg(5000, 320, 240)
     prog = make_jpeg(5001, 320, 240, progressive=True)

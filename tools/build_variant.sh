@@ -5,7 +5,7 @@ name=$1; shift
 dst=tools/_variants/$name
 mkdir -p $dst/obj
 C=nvimagecodec_b200/csrc
-for f in decode_kernels huffman_kernels color_kernel encode_kernels progressive_kernel; do
+for f in decode_kernels huffman_kernels color_kernel encode_kernels progressive_kernel noalloc_unstuff; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-fvisibility=hidden "$@" -c $C/$f.cu -o $dst/obj/$f.o &
 done
 for f in enc_plan decoder encoder capi jpeg_parse batch_plan log; do
