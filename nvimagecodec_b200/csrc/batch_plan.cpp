@@ -195,6 +195,22 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
             }
             if (si.ss != 0)
                 sd.ac_tab = intern_huff(plan, g_seen, si.ac[si.ta[0]], false);
+            // which earlier scans this one has to wait for: those that share a component and whose band overlaps (a scan writes
+            // 16-bit coefficients of its own band only, a refinement scan reads nothing outside its band)
+            const size_t idx = plan.scans.size() - im.scan_first;
+            if (pj.scans.size() > 32) {
+                sd.deps = 0xFFFFFFFFu;
+            } else {
+                for (size_t e = 0; e < idx; ++e) {
+                    const ScanDesc& pe = plan.scans[im.scan_first + e];
+                    bool shared = false;
+                    for (int a = 0; a < sd.ncomp; ++a)
+                        for (int b2 = 0; b2 < pe.ncomp; ++b2)
+                            shared = shared || sd.comp[a] == pe.comp[b2];
+                    if (shared && sd.ss <= pe.se && pe.ss <= sd.se)
+                        sd.deps |= 1u << e;
+                }
+            }
             plan.scans.push_back(sd);
         }
         plan.prog_images.push_back(uint32_t(plan.images.size()));

@@ -84,6 +84,9 @@ struct ScanDesc
     int32_t ac_tab;           // pool index (AC scans: one component)
     int32_t ss, se, ah, al;
     int32_t restart_interval; // MCUs of this scan between RSTn markers, 0 = none
+    uint32_t deps;            // bit j: scan j of the image (j < this one) touches coefficients this scan reads or writes (a component in common and
+                              // overlapping bands) and has to be complete before this scan starts; scans without such a link run side by side
+                              // (k_prog_decode).  Images with more than 32 scans: every earlier scan (all ones).
 };
 
 // Per-image descriptor, built on the host, read-only on the device.

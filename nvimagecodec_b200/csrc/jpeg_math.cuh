@@ -34,14 +34,17 @@ B2J_HD uint32_t idct_range_limit(int v)
     return uint32_t(t);
 }
 
-B2J_HD void idct_1d(int i0, int i1, int i2, int i3, int i4, int i5, int i6, int i7, int* o)
+// One 1-D pass (ljt/jidctint.c:197-291 / :303-399).  rnd is added to both even-part sums: every output contains exactly one
+// of them exactly once, so the rounding constant of the descale that follows (1 << (n - 1)) is added here twice instead of
+// eight times after the butterflies -- the same integers mod 2^32.
+B2J_HD void idct_1d(int i0, int i1, int i2, int i3, int i4, int i5, int i6, int i7, int rnd, int* o)
 {
     int z2 = i2, z3 = i6;
     int z1 = (z2 + z3) * 4433;
     int tmp2 = z1 + z3 * -15137;
     int tmp3 = z1 + z2 * 6270;
-    int tmp0 = (i0 + i4) * 8192;
-    int tmp1 = (i0 - i4) * 8192;
+    int tmp0 = (i0 + i4) * 8192 + rnd;
+    int tmp1 = (i0 - i4) * 8192 + rnd;
     const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
     tmp0 = i7;
     tmp1 = i5;
@@ -74,6 +77,19 @@ B2J_HD void idct_1d(int i0, int i1, int i2, int i3, int i4, int i5, int i6, int 
     o[4] = tmp13 - tmp0;
 }
 
+// Sample from a second-pass output that already carries the rounding constant: descale by 18 bits, range_limit.  Bits
+// 18..27 of v, sign-extended, are exactly the table index the reference forms ((x >> 18) & RANGE_MASK read as a signed
+// 10-bit number); + 128 and a clamp to [0, 255] are what the table holds there.
+B2J_HD uint32_t idct_sample(int v)
+{
+    const int t = (int(uint32_t(v) << 4) >> 22) + 128;
+#if defined(__CUDA_ARCH__)
+    return uint32_t(__vimin_s32_relu(t, 255));
+#else
+    return uint32_t(t < 0 ? 0 : (t > 255 ? 255 : t));
+#endif
+}
+
 B2J_HD void idct_block(const int16_t* in, int dcval, const uint16_t* q, uint32_t* out /*[16]*/)
 {
     int ws[64];
@@ -82,23 +98,19 @@ B2J_HD void idct_block(const int16_t* in, int dcval, const uint16_t* q, uint32_t
         int o[8];
         const int i0 = (c == 0 ? dcval : int(in[c])) * q[c];
         idct_1d(i0, in[8 + c] * q[8 + c], in[16 + c] * q[16 + c], in[24 + c] * q[24 + c], in[32 + c] * q[32 + c],
-            in[40 + c] * q[40 + c], in[48 + c] * q[48 + c], in[56 + c] * q[56 + c], o);
+            in[40 + c] * q[40 + c], in[48 + c] * q[48 + c], in[56 + c] * q[56 + c], 1 << 10, o);
 #pragma unroll
         for (int r = 0; r < 8; ++r)
-            ws[r * 8 + c] = idct_descale(o[r], 11);
+            ws[r * 8 + c] = o[r] >> 11;
     }
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         int o[8];
-        idct_1d(ws[r * 8], ws[r * 8 + 1], ws[r * 8 + 2], ws[r * 8 + 3], ws[r * 8 + 4], ws[r * 8 + 5], ws[r * 8 + 6], ws[r * 8 + 7], o);
-        uint32_t lo = 0, hi = 0;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            lo |= idct_range_limit(idct_descale(o[c], 18)) << (8 * c);
-            hi |= idct_range_limit(idct_descale(o[c + 4], 18)) << (8 * c);
-        }
-        out[2 * r] = lo;
-        out[2 * r + 1] = hi;
+        idct_1d(ws[r * 8], ws[r * 8 + 1], ws[r * 8 + 2], ws[r * 8 + 3], ws[r * 8 + 4], ws[r * 8 + 5], ws[r * 8 + 6], ws[r * 8 + 7], 1 << 17, o);
+        const uint32_t a = idct_sample(o[0]) + (idct_sample(o[1]) << 8), b = idct_sample(o[2]) + (idct_sample(o[3]) << 8);
+        const uint32_t c = idct_sample(o[4]) + (idct_sample(o[5]) << 8), d = idct_sample(o[6]) + (idct_sample(o[7]) << 8);
+        out[2 * r] = a + (b << 16);
+        out[2 * r + 1] = c + (d << 16);
     }
 }
 

@@ -43,6 +43,16 @@ struct ProgBits
     }
     B2J_HD void fill()
     {
+        // four bytes at once when none of them is an FF (255 of 256 are not): the loads do not depend on each other, and
+        // no byte has to be looked at twice; anything with an FF in it goes through the byte loop below
+        while (n <= 32 && !at_marker && pos + 4u <= end) {
+            const uint32_t c0 = d[pos], c1 = d[pos + 1], c2 = d[pos + 2], c3 = d[pos + 3];
+            if (c0 == 0xFF || c1 == 0xFF || c2 == 0xFF || c3 == 0xFF)
+                break;
+            buf |= uint64_t((c0 << 24) | (c1 << 16) | (c2 << 8) | c3) << (32 - n);
+            n += 32;
+            pos += 4;
+        }
         while (n <= 56 && !at_marker) {
             if (pos >= end) {
                 at_marker = true;
@@ -109,11 +119,36 @@ struct ProgBits
     }
 };
 
-// One Huffman symbol by the canonical walk (jpeg_huff_decode): -1 for a code that is not in the table.
-B2J_HD int prog_huff_symbol(ProgBits& br, const DevHuffTable* t)
+// Look-ahead table of a Huffman table for codes of up to kProgFastBits bits: entry = length << 8 | symbol, 0 = longer code.
+// The baseline kernels' LUTs (DevHuffTable::lut) do not serve here: they fold the run length of the end-of-band symbols away,
+// which a progressive scan needs (EOBn, ljt/jdphuff.c:395-404).  Entry i is independent of the others, so a warp fills the
+// table of the scan at hand side by side (k_prog_decode); the CPU emulation fills it in a loop.
+constexpr int kProgFastBits = 8;
+B2J_HD uint16_t prog_fast_entry(const DevHuffTable* t, uint32_t prefix /* kProgFastBits bits */)
+{
+    for (int l = 1; l <= kProgFastBits; ++l) {
+        const int code = int(prefix >> (kProgFastBits - l));
+        if (code <= t->maxcode[l])
+            return uint16_t((l << 8) | t->vals[(code + t->valoffset[l]) & 255]);
+    }
+    return 0;
+}
+
+// One Huffman symbol (jpeg_huff_decode, ljt/jdhuff.c:398-450): look-ahead table first (fast may be null), then the
+// canonical walk over the longer lengths.  -1 for a code that is not in the table.
+B2J_HD int prog_huff_symbol(ProgBits& br, const DevHuffTable* t, const uint16_t* fast = nullptr)
 {
     const uint32_t w = br.peek16();
-    for (int l = 1; l <= 16; ++l) {
+    int l = 1;
+    if (fast) {
+        const uint32_t e = fast[w >> (16 - kProgFastBits)];
+        if (e) {
+            br.skip(int(e >> 8));
+            return int(e & 255u);
+        }
+        l = kProgFastBits + 1;
+    }
+    for (; l <= 16; ++l) {
         const int code = int(w >> (16 - l));
         if (code <= t->maxcode[l]) {
             br.skip(l);
@@ -128,20 +163,20 @@ B2J_HD int prog_extend(uint32_t r, int s) { return r < (1u << (s - 1)) ? int(r) 
 // Index (in the image's coefficient array, blocks in MCU scan order) of block (bx, by) of component c.
 B2J_HD uint32_t prog_block_index(const ImageDesc& im, int c, int bx, int by)
 {
-    const int hs = im.hs[c], vs = im.vs[c];
-    const uint32_t mcu = uint32_t(by / vs) * uint32_t(im.mcus_x) + uint32_t(bx / hs);
-    return mcu * uint32_t(im.bpm) + uint32_t(im.blk_first[c] + (by % vs) * hs + (bx % hs));
+    const int hs = im.hs[c], vs = im.vs[c], lh = hs >> 1, lv = vs >> 1; // sampling factors are 1, 2 or 4: log2 = f >> 1
+    const uint32_t mcu = uint32_t(by >> lv) * uint32_t(im.mcus_x) + uint32_t(bx >> lh);
+    return mcu * uint32_t(im.bpm) + uint32_t(im.blk_first[c] + (by & (vs - 1)) * hs + (bx & (hs - 1)));
 }
 
 // The AC part of one block in a refinement scan (decode_mcu_AC_refine).  zz = zigzag position -> natural index.
 B2J_HD bool prog_ac_refine_block(ProgBits& br, const DevHuffTable* tab, int16_t* blk, int ss, int se, int al, uint32_t& eobrun,
-    const uint8_t* zz)
+    const uint8_t* zz, const uint16_t* fast = nullptr)
 {
     const int p1 = 1 << al, m1 = -(1 << al);
     int k = ss;
     if (eobrun == 0) {
         for (; k <= se; ++k) {
-            int s = prog_huff_symbol(br, tab);
+            int s = prog_huff_symbol(br, tab, fast);
             if (s < 0)
                 return false;
             int r = s >> 4;
@@ -181,14 +216,15 @@ B2J_HD bool prog_ac_refine_block(ProgBits& br, const DevHuffTable* tab, int16_t*
 }
 
 // The AC part of one block in a first scan of its band (decode_mcu_AC_first).
-B2J_HD bool prog_ac_first_block(ProgBits& br, const DevHuffTable* tab, int16_t* blk, int ss, int se, int al, uint32_t& eobrun, const uint8_t* zz)
+B2J_HD bool prog_ac_first_block(ProgBits& br, const DevHuffTable* tab, int16_t* blk, int ss, int se, int al, uint32_t& eobrun, const uint8_t* zz,
+    const uint16_t* fast = nullptr)
 {
     if (eobrun > 0) {
         --eobrun;
         return true;
     }
     for (int k = ss; k <= se; ++k) {
-        int s = prog_huff_symbol(br, tab);
+        int s = prog_huff_symbol(br, tab, fast);
         if (s < 0)
             return false;
         const int r = s >> 4;
@@ -214,8 +250,10 @@ B2J_HD bool prog_ac_first_block(ProgBits& br, const DevHuffTable* tab, int16_t* 
 
 // Decode one scan of image im into its coefficients (coef = the image's first block).  raw = the image's bytes in the raw
 // buffer (ScanDesc::off is relative to it).  Returns 0 or kErrProgressive.
+// fast: optional look-ahead tables (prog_fast_entry), 256 entries per table of the scan: its AC table for an AC scan, else
+// one per component of the scan.
 B2J_HD uint32_t prog_decode_scan(const ImageDesc& im, const ScanDesc& sc, const uint8_t* raw, const DevHuffTable* pool, int16_t* coef,
-    const uint8_t* zz)
+    const uint8_t* zz, const uint16_t* fast = nullptr)
 {
     ProgBits br;
     br.init(raw, sc.off, sc.off + sc.len);
@@ -249,7 +287,7 @@ B2J_HD uint32_t prog_decode_scan(const ImageDesc& im, const ScanDesc& sc, const 
                         int16_t* blk = coef + uint64_t(prog_block_index(im, c, bx, by)) * 64;
                         if (dc) {
                             if (sc.ah == 0) { // decode_mcu_DC_first
-                                int s = prog_huff_symbol(br, pool + sc.dc_tab[i]);
+                                int s = prog_huff_symbol(br, pool + sc.dc_tab[i], fast ? fast + (i << kProgFastBits) : nullptr);
                                 if (s < 0 || s > 15)
                                     return kErrProgressive;
                                 if (s)
@@ -260,8 +298,8 @@ B2J_HD uint32_t prog_decode_scan(const ImageDesc& im, const ScanDesc& sc, const 
                                 blk[0] = int16_t(blk[0] | (1 << sc.al));
                             }
                         } else {
-                            const bool ok = sc.ah == 0 ? prog_ac_first_block(br, pool + sc.ac_tab, blk, sc.ss, sc.se, sc.al, eobrun, zz)
-                                                       : prog_ac_refine_block(br, pool + sc.ac_tab, blk, sc.ss, sc.se, sc.al, eobrun, zz);
+                            const bool ok = sc.ah == 0 ? prog_ac_first_block(br, pool + sc.ac_tab, blk, sc.ss, sc.se, sc.al, eobrun, zz, fast)
+                                                       : prog_ac_refine_block(br, pool + sc.ac_tab, blk, sc.ss, sc.se, sc.al, eobrun, zz, fast);
                             if (!ok)
                                 return kErrProgressive;
                         }

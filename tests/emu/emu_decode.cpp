@@ -487,8 +487,32 @@ extern "C" int emu_decode_batch(int n, const uint8_t* const* data, const size_t*
             continue;
         std::memset(coef.data() + im.coef_off, 0, size_t(im.total_blocks) * 128);
         uint32_t err = 0;
-        for (uint32_t sidx = 0; sidx < im.scan_count && !err; ++sidx)
-            err = prog_decode_scan(im, plan.scans[im.scan_first + sidx], raw.data() + im.raw_off, plan.huff.data(), coef.data() + im.coef_off, h_zigzag);
+        // k_prog_decode runs scans side by side when ScanDesc::deps allows: emulate the most adverse legal order (always the
+        // LAST scan of the file whose dependencies are complete), so that a missing dependency shows up as wrong coefficients
+        std::vector<uint8_t> done(im.scan_count, 0);
+        for (uint32_t step = 0; step < im.scan_count && !err; ++step) {
+            int pick = -1;
+            for (int sidx = int(im.scan_count) - 1; sidx >= 0 && pick < 0; --sidx) {
+                if (done[sidx])
+                    continue;
+                const ScanDesc& sc = plan.scans[im.scan_first + sidx];
+                bool ready = true;
+                for (int e = 0; e < sidx; ++e)
+                    if ((im.scan_count > 32 || ((sc.deps >> e) & 1u)) && !done[e])
+                        ready = false;
+                if (ready)
+                    pick = sidx;
+            }
+            const ScanDesc& sc = plan.scans[im.scan_first + pick];
+            // look-ahead tables as the kernel builds them (prog_fast_entry)
+            std::vector<uint16_t> fast(size_t(3) << kProgFastBits, 0);
+            const int ntab = sc.ss != 0 ? 1 : (sc.ah == 0 ? sc.ncomp : 0);
+            for (int t = 0; t < ntab; ++t)
+                for (uint32_t e = 0; e < (1u << kProgFastBits); ++e)
+                    fast[(size_t(t) << kProgFastBits) + e] = prog_fast_entry(plan.huff.data() + (sc.ss != 0 ? sc.ac_tab : sc.dc_tab[t]), e);
+            err = prog_decode_scan(im, sc, raw.data() + im.raw_off, plan.huff.data(), coef.data() + im.coef_off, h_zigzag, ntab ? fast.data() : nullptr);
+            done[pick] = 1;
+        }
         states[i].error |= err; // (the baseline passes saw an empty stream and must not have flagged anything)
         if (!err)
             states[i].done_blocks = im.total_blocks;
