@@ -26,7 +26,7 @@ if [ "${3:-noncu}" = "ncu" ]; then
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_' --launch-skip ${NCU_SKIP:-36} --launch-count ${NCU_COUNT:-12} \
       -o $out/${tag}_full python tools/quick_bench.py 64 8 > $out/${tag}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 fi
-if [ "${4:-nosan}" = "san" ]; then
+if [ "${4:-nosan}" = "san" ]; then # (compute-sanitizer is closed on this pool: profiles/r02t_sanitizer_unavailable.txt)
   timeout 900 compute-sanitizer --tool memcheck --log-file $out/${tag}_sanitizer_memcheck.log python -m pytest tests/test_gpu_decode.py -x -q -k "mixed_batch or bad_and or damaged" > $out/${tag}_sanitizer_memcheck.out 2>&1; echo "memcheck rc=$?"
   tail -3 $out/${tag}_sanitizer_memcheck.log
   timeout 900 compute-sanitizer --tool racecheck --log-file $out/${tag}_sanitizer_racecheck.log python -m pytest tests/test_gpu_decode.py -x -q -k "mixed_batch" > $out/${tag}_sanitizer_racecheck.out 2>&1; echo "racecheck rc=$?"
