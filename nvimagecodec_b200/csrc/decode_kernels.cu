@@ -77,6 +77,82 @@ __device__ __forceinline__ ByteClass classify16(const uint8_t* __restrict__ raw,
     return c;
 }
 
+// Classification of the CTA's chunk: every thread has kUnstuffGranules consecutive 16-byte granules.  Only a granule that
+// holds an FF (or follows one) can have anything removed, and only one byte in 256 is an FF -- but nearly every warp has a
+// lane with such a granule, so a per-lane slow path would run in nearly every warp.  Instead the few granules that need a
+// look are queued in shared memory and classified by the first threads of the CTA (dense warps); everybody else keeps all
+// 16 bytes.  w = the thread's bytes (zero-filled behind the data).  Contains barriers: call with the whole CTA.
+constexpr int kChunkGranules = kUnstuffThreads * kUnstuffGranules;
+struct CtaClassify
+{
+    uint32_t n;
+    uint16_t list[kChunkGranules], keep[kChunkGranules], marker[kChunkGranules], bad[kChunkGranules];
+};
+
+__device__ __forceinline__ void classify_cta(CtaClassify& sh, const uint8_t* __restrict__ raw, uint32_t len, uint32_t base,
+    uint32_t w[kUnstuffGranules][4], ByteClass c[kUnstuffGranules])
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    if (threadIdx.x == 0)
+        sh.n = 0;
+    __syncthreads();
+    uint32_t slow = 0; // bit q: granule q has to be looked at
+#pragma unroll
+    for (int q = 0; q < kUnstuffGranules; ++q) {
+        const uint32_t gb = base + 16u * q;
+        w[q][0] = w[q][1] = w[q][2] = w[q][3] = 0;
+        c[q] = ByteClass{0, 0, 0};
+        if (gb + 16 <= len) {
+            const uint4 v = *reinterpret_cast<const uint4*>(raw + gb);
+            w[q][0] = v.x; w[q][1] = v.y; w[q][2] = v.z; w[q][3] = v.w;
+        } else if (gb < len) { // the last granule of the data
+            for (uint32_t i = 0; gb + i < len; ++i)
+                w[q][i >> 2] |= uint32_t(raw[gb + i]) << (8 * (i & 3));
+            slow |= 1u << q;
+        }
+    }
+    const uint32_t up = __shfl_up_sync(0xFFFFFFFFu, w[kUnstuffGranules - 1][3], 1);
+#pragma unroll
+    for (int q = 0; q < kUnstuffGranules; ++q) {
+        const uint32_t gb = base + 16u * q;
+        if (gb < len && !((slow >> q) & 1u)) {
+            const uint32_t prev = q ? w[q > 0 ? q - 1 : 0][3] >> 24 : (lane ? up >> 24 : (gb ? raw[gb - 1] : 0u));
+            const uint32_t ff = __vcmpeq4(w[q][0], 0xFFFFFFFFu) | __vcmpeq4(w[q][1], 0xFFFFFFFFu) | __vcmpeq4(w[q][2], 0xFFFFFFFFu) |
+                                __vcmpeq4(w[q][3], 0xFFFFFFFFu);
+            if (ff || prev == 0xFFu)
+                slow |= 1u << q;
+            else
+                c[q].keep = 0xFFFFu;
+        }
+    }
+    if (slow) {
+        uint32_t at = atomicAdd(&sh.n, uint32_t(__popc(slow)));
+#pragma unroll
+        for (int q = 0; q < kUnstuffGranules; ++q)
+            if ((slow >> q) & 1u)
+                sh.list[at++] = uint16_t(threadIdx.x * kUnstuffGranules + q);
+    }
+    __syncthreads();
+    const uint32_t n = sh.n, chunk_base = base - threadIdx.x * kUnstuffBytesPerThread;
+    for (uint32_t j = threadIdx.x; j < n; j += kUnstuffThreads) {
+        const uint32_t g = sh.list[j];
+        uint32_t ww[4], nx;
+        const ByteClass cc = classify16(raw, len, chunk_base + g * 16u, ww, nx);
+        sh.keep[g] = uint16_t(cc.keep);
+        sh.marker[g] = uint16_t(cc.marker);
+        sh.bad[g] = uint16_t(cc.bad);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < kUnstuffGranules; ++q)
+        if ((slow >> q) & 1u) {
+            const uint32_t g = threadIdx.x * kUnstuffGranules + q;
+            c[q].keep = sh.keep[g];
+            c[q].marker = sh.marker[g];
+            c[q].bad = sh.bad[g];
+        }
+}
+
 __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_count(BatchDev b)
 {
     const uint32_t cta_abs = blockIdx.x + b.base_unstuff;
@@ -84,11 +160,18 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_count(BatchDev b)
     const ImageDesc& im = b.images[img];
     const uint32_t chunk = cta_abs - b.cta_map_unstuff[img];
     const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
-    uint32_t w[4], next;
-    ByteClass c{0, 0, 0};
-    if (base < im.raw_len)
-        c = classify16(b.raw + im.raw_off, im.raw_len, base, w, next);
-    uint32_t kept = __popc(c.keep), markers = __popc(c.marker);
+    uint32_t w[kUnstuffGranules][4];
+    ByteClass c[kUnstuffGranules];
+    __shared__ CtaClassify s_cls;
+    classify_cta(s_cls, b.raw + im.raw_off, im.raw_len, base, w, c);
+    uint32_t kept = 0, markers = 0, bad_at = 0xFFFFFFFFu;
+#pragma unroll
+    for (int q = kUnstuffGranules - 1; q >= 0; --q) {
+        kept += __popc(c[q].keep);
+        markers += __popc(c[q].marker);
+        if (c[q].bad)
+            bad_at = base + 16u * q + uint32_t(__ffs(int(c[q].bad))) - 1u;
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         kept += __shfl_down_sync(0xFFFFFFFFu, kept, o);
@@ -103,8 +186,8 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_count(BatchDev b)
     // jpeg_fill_bit_buffer:287-391 stops feeding bytes at the first marker): files that carry more after their first EOI
     // (MPO / gain-map / motion-photo appendices, embedded thumbnails) decode like everywhere else.  The earliest such
     // marker wins: the per-image maximum of raw_len - position.
-    if (c.bad)
-        atomicMax(&b.states[img].trunc, im.raw_len - (base + uint32_t(__ffs(int(c.bad))) - 1u));
+    if (bad_at != 0xFFFFFFFFu)
+        atomicMax(&b.states[img].trunc, im.raw_len - bad_at);
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t k = 0, m = 0;
@@ -184,13 +267,20 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
     const ImageDesc& im = b.images[img];
     const uint32_t chunk = cta_abs - b.cta_map_unstuff[img];
     const uint32_t base = chunk * kChunkBytes + threadIdx.x * kUnstuffBytesPerThread;
-    uint32_t w[4] = {0, 0, 0, 0}, next = 0;
-    ByteClass c{0, 0, 0};
     const uint32_t eff_len = b.states[img].raw_eff; // raw_len, or up to the first marker that is not RSTn
-    if (base < eff_len)
-        c = classify16(b.raw + im.raw_off, eff_len, base, w, next);
+    const uint64_t cb = b.chunk_counts[im.chunk_first + chunk]; // (needed after the scan: requested now)
+    uint32_t w[kUnstuffGranules][4];
+    ByteClass c[kUnstuffGranules];
+    __shared__ CtaClassify s_cls;
+    __shared__ uint32_t s_w[kUnstuffThreads / 32];
+    __shared__ __align__(16) uint32_t s_out[kChunkBytes / 4 + 4];
+    __shared__ uint32_t s_total;
+    classify_cta(s_cls, b.raw + im.raw_off, eff_len, base, w, c);
     // block exclusive scan of (kept | markers << 16)
-    const uint32_t mine = uint32_t(__popc(c.keep)) | (uint32_t(__popc(c.marker)) << 16);
+    uint32_t mine = 0;
+#pragma unroll
+    for (int q = 0; q < kUnstuffGranules; ++q)
+        mine += uint32_t(__popc(c[q].keep)) | (uint32_t(__popc(c[q].marker)) << 16);
     uint32_t inc = mine;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -199,7 +289,11 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
         if (lane >= uint32_t(o))
             inc += t;
     }
-    __shared__ uint32_t s_w[kUnstuffThreads / 32];
+#pragma unroll
+    for (int q = 0; q < kUnstuffGranules; ++q) // the compaction below ORs into the output words
+        reinterpret_cast<uint4*>(s_out)[threadIdx.x * kUnstuffGranules + q] = make_uint4(0, 0, 0, 0);
+    if (threadIdx.x == 0)
+        reinterpret_cast<uint4*>(s_out)[kChunkGranules] = make_uint4(0, 0, 0, 0);
     if (lane == 31)
         s_w[warp] = inc;
     __syncthreads();
@@ -209,33 +303,26 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
         if (i < int(warp))
             wpre += s_w[i];
     const uint32_t excl = wpre + inc - mine;
-    const uint64_t cb = b.chunk_counts[im.chunk_first + chunk];
-    // kept bytes are compacted into shared memory first, then copied out with aligned 4-byte stores
-    __shared__ __align__(16) uint32_t s_out[kChunkBytes / 4 + 4];
-    __shared__ uint32_t s_total;
+    // Kept bytes are compacted into shared memory first, then copied out with aligned 16-byte stores.  The compaction
+    // happens in registers: a granule's removed bytes (usually none, or the one zero behind a stuffed FF) are dropped from
+    // its 128-bit value by shifting what lies above them down, and the value, shifted to its byte offset, is ORed into the
+    // (zeroed) output words -- five shared-memory atomics whatever the alignment, instead of a store per byte.
     uint8_t* sb = reinterpret_cast<uint8_t*>(s_out);
     uint32_t lpos = excl & 0xFFFFu;                    // position inside the chunk's output
     const uint32_t gbase = uint32_t(cb);               // position of the chunk's output in the image's clean stream
     uint32_t ord = uint32_t(cb >> 32) + (excl >> 16);
-    uint32_t* S = b.seg_start + im.seg_first;
     uint32_t bad = 0;
-    if (c.keep == 0xFFFFu && (lpos & 3u) == 0) {
-        uint32_t* s32 = s_out + (lpos >> 2);
-        s32[0] = w[0];
-        s32[1] = w[1];
-        s32[2] = w[2];
-        s32[3] = w[3];
-        lpos += 16;
-    } else {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const uint32_t cur = (w[i >> 2] >> (8 * (i & 3))) & 255u;
-            if (c.keep & (1u << i))
-                sb[lpos++] = uint8_t(cur);
-            if (c.marker & (1u << i)) {
-                const uint32_t nx = (i < 15) ? ((w[(i + 1) >> 2] >> (8 * ((i + 1) & 3))) & 255u) : next;
+    for (int q = 0; q < kUnstuffGranules; ++q) {
+        const uint32_t keep = c[q].keep, cnt = uint32_t(__popc(keep));
+        if (c[q].marker) { // restart markers: the next segment starts at the clean position of the marker
+            uint32_t* S = b.seg_start + im.seg_first;
+            for (uint32_t mk = c[q].marker; mk; mk &= mk - 1u) {
+                const int i = __ffs(int(mk)) - 1;
+                const uint32_t at = base + 16u * q + uint32_t(i) + 1u; // the byte behind the FF
+                const uint32_t nx = at < eff_len ? b.raw[im.raw_off + at] : 0u;
                 if (ord + 1 < uint32_t(im.num_segments)) {
-                    S[ord + 1] = gbase + lpos;
+                    S[ord + 1] = gbase + lpos + uint32_t(__popc(keep & ((1u << i) - 1u)));
                     if (nx != 0xD0u + (ord & 7u))
                         bad = 1;
                 } else
@@ -243,26 +330,59 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
                 ++ord;
             }
         }
+        if (cnt) {
+            uint32_t v0 = w[q][0], v1 = w[q][1], v2 = w[q][2], v3 = w[q][3];
+            uint32_t rem = ~keep & ((2u << (31 - __clz(int(keep)))) - 1u); // removed bytes below the last kept one
+            while (rem) {
+                const uint32_t r = uint32_t(__ffs(int(rem))) - 1u, wi = r >> 2;
+                const uint32_t low = (1u << ((r & 3u) * 8u)) - 1u; // the bytes of word wi below byte r stay
+                const uint32_t d0 = __funnelshift_r(v0, v1, 8), d1 = __funnelshift_r(v1, v2, 8), d2 = __funnelshift_r(v2, v3, 8), d3 = v3 >> 8;
+                v0 = wi == 0 ? (v0 & low) | (d0 & ~low) : v0;
+                v1 = wi == 1 ? (v1 & low) | (d1 & ~low) : (wi < 1 ? d1 : v1);
+                v2 = wi == 2 ? (v2 & low) | (d2 & ~low) : (wi < 2 ? d2 : v2);
+                v3 = wi == 3 ? (v3 & low) | (d3 & ~low) : (wi < 3 ? d3 : v3);
+                rem = (rem >> (r + 1u)) << r; // what lay above moved down by one byte
+            }
+            if (cnt < 16u) { // bytes from cnt on must not reach the neighbour's words
+                const uint32_t kw = cnt >> 2, km = (1u << ((cnt & 3u) * 8u)) - 1u;
+                v0 = kw == 0 ? v0 & km : v0;
+                v1 = kw == 1 ? v1 & km : (kw < 1 ? 0u : v1);
+                v2 = kw == 2 ? v2 & km : (kw < 2 ? 0u : v2);
+                v3 = kw == 3 ? v3 & km : (kw < 3 ? 0u : v3);
+            }
+            const uint32_t sh = (lpos & 3u) * 8u;
+            uint32_t* o = s_out + (lpos >> 2);
+            atomicOr(o, v0 << sh);
+            atomicOr(o + 1, __funnelshift_l(v0, v1, sh));
+            atomicOr(o + 2, __funnelshift_l(v1, v2, sh));
+            atomicOr(o + 3, __funnelshift_l(v2, v3, sh));
+            if (sh)
+                atomicOr(o + 4, v3 >> (32u - sh));
+            lpos += cnt;
+        }
     }
     if (threadIdx.x == kUnstuffThreads - 1)
         s_total = lpos;
     if (bad)
         atomicOr(&b.states[img].error, kErrBadMarker);
     __syncthreads();
+    // copy out: bytes up to the first 16-byte boundary of the destination, then 16-byte stores, then the last bytes
     const uint32_t K = s_total;
     uint8_t* d = b.clean + im.clean_off + gbase;
-    const uint32_t m = uint32_t(reinterpret_cast<uintptr_t>(d) & 3u);
-    uint32_t head = m ? 4u - m : 0u;
+    uint32_t head = uint32_t(16u - (reinterpret_cast<uintptr_t>(d) & 15u)) & 15u;
     if (head > K)
         head = K;
     if (threadIdx.x < head)
         d[threadIdx.x] = sb[threadIdx.x];
-    const uint32_t nw = (K - head) >> 2;
-    uint32_t* d32 = reinterpret_cast<uint32_t*>(d + head);
-    const uint32_t sh = head * 8u;
-    for (uint32_t i = threadIdx.x; i < nw; i += kUnstuffThreads)
-        d32[i] = head ? __funnelshift_r(s_out[i], s_out[i + 1], sh) : s_out[i];
-    const uint32_t done = head + (nw << 2);
+    const uint32_t nv = (K - head) >> 4;
+    uint4* d16 = reinterpret_cast<uint4*>(d + head);
+    const uint32_t o0 = head >> 2, sh = (head & 3u) * 8u;
+    for (uint32_t i = threadIdx.x; i < nv; i += kUnstuffThreads) {
+        const uint32_t* sw = s_out + o0 + 4u * i;
+        const uint32_t a0 = sw[0], a1 = sw[1], a2 = sw[2], a3 = sw[3], a4 = sw[4];
+        d16[i] = make_uint4(__funnelshift_r(a0, a1, sh), __funnelshift_r(a1, a2, sh), __funnelshift_r(a2, a3, sh), __funnelshift_r(a3, a4, sh));
+    }
+    const uint32_t done = head + (nv << 4);
     if (threadIdx.x < K - done)
         d[done + threadIdx.x] = sb[done + threadIdx.x];
 }

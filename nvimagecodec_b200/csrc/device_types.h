@@ -25,8 +25,9 @@ constexpr int kFusedOwn = kSubseqCta - kFusedHalo; // subsequences a CTA of the 
 constexpr int kFusedRunHeads = 6;     // fused kernel, rounds from this one on: of a run of consecutive listed subsequences only the head is
                                       // worked on, by one thread that walks the whole run (streams that never lock on, e.g. flat image areas)
 constexpr int kUnstuffThreads = 256;  // threads per CTA in the unstuffing kernels
-constexpr int kUnstuffBytesPerThread = 16;
-constexpr int kChunkBytes = kUnstuffThreads * kUnstuffBytesPerThread; // raw bytes per unstuff CTA
+constexpr int kUnstuffGranules = 4;   // 16-byte granules per thread (consecutive: 64 bytes of the stream per thread)
+constexpr int kUnstuffBytesPerThread = 16 * kUnstuffGranules;
+constexpr int kChunkBytes = kUnstuffThreads * kUnstuffBytesPerThread; // raw bytes per unstuff CTA (16 KB)
 #ifndef B2J_IDCT_CTA
 #define B2J_IDCT_CTA 256
 #endif
