@@ -131,7 +131,8 @@ B200JPEG_API int b200jpeg_parse_header(const uint8_t* data, size_t size, b200jpe
  * subseq_bytes=N (bytes of unstuffed stream per Huffman decoding thread, default 128), profile=0|1; tuning knobs, none of
  * which changes a result: groups=N / groups_host=N (image groups on separate streams), copy_threads=N, tail_launches=N
  * (work-list rounds run as ordinary launches before the cooperative kernel, default 1), tail_spread=0|1 (work-list
- * items dealt lane-major, default 1), stream_priority=0|1, stage_stream=0|1, dump_coef=0|1 (debug tap).
+ * items dealt lane-major, default 1), stream_priority=0|1, stage_stream=0|1, dump_coef=0|1 (debug tap), fused=0|1 (the
+ * entropy-decode stage as one kernel, k_huff_fused, instead of six launches: same results, slower on B200, default 0).
  * B200JPEG_TRACE=1 in the environment prints the host timeline, the work-list rounds and the error flags of failed images. */
 B200JPEG_API int b200jpeg_decoder_create(b200jpegDecoder_t* decoder, int device_id, const char* options);
 B200JPEG_API int b200jpeg_decoder_destroy(b200jpegDecoder_t decoder);
