@@ -126,6 +126,17 @@ class ClockSampler:
         return out
 
 
+def _gpu_local_cpus(pynvml, index):
+    try:
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]
+        return open("/sys/bus/pci/devices/" + bus + "/local_cpulist").read().strip()
+    except Exception:
+        return None
+
+
 def pin_to_gpu_numa_node(index):
     """one host thread set per device: run this rank on the cores next to its GPU so that pinned staging
     buffers are allocated on, and copied from, the local memory node.  Returns a description or None."""
@@ -144,8 +155,16 @@ def pin_to_gpu_numa_node(index):
             cpus.update(range(int(a), int(b or a) + 1))
         cpus &= os.sched_getaffinity(0)
         if cpus:
-            os.sched_setaffinity(0, cpus)
-            return {"numa_node": node, "cpus": len(cpus)}
+            # the ranks whose GPUs share these cores take disjoint slices of them (the decoder sizes its staging threads by
+            # the cores its process may use): without that, N ranks x (copy threads + completion threads) fight for the box
+            world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
+            sharing = [r for r in range(world) if _gpu_local_cpus(pynvml, r) == _gpu_local_cpus(pynvml, index)] or [index]
+            ordered = sorted(cpus)
+            per = max(1, len(ordered) // len(sharing))
+            k = sharing.index(index) if index in sharing else 0
+            mine = set(ordered[k * per:(k + 1) * per]) or cpus
+            os.sched_setaffinity(0, mine)
+            return {"numa_node": node, "cpus": len(mine), "shared_by_ranks": len(sharing)}
     except Exception:
         pass
     return None
@@ -500,7 +519,7 @@ def run_decode(args, rank, world, local_rank):
     cpu_baseline = None
     want = None
     if rank == 0 and not args.skip_cpu_baseline:
-        cores = os.cpu_count() or 1
+        cores = len(os.sched_getaffinity(0)) or 1  # at N > 1 this rank owns a slice of the host's cores (pin_to_gpu_numa_node)
         reps = 3 if cores >= 16 else 1
         want, secs = reference_decode_all(datas, dims, reps)
         got = dev_sets[0].cpu().numpy()
@@ -619,8 +638,41 @@ def run_decode(args, rank, world, local_rank):
     torch.cuda.synchronize(dev)
     api["copy_floor"] = (time.perf_counter() - t0) / floor_steps
 
+    # ---- the floors of the host bytes -> device pixels number, every rank at once: (1) the raw pinned host -> device copy of one
+    # batch of entropy-coded bytes, (2) the pageable -> pinned staging copy of the same bytes on the threads this rank owns
+    # (what the decoder's StagePool does before its upload): at N > 1 the ranks share the box's PCIe root and memory bus ----
+    import ctypes
+    from concurrent.futures import ThreadPoolExecutor
+    scan_total = int(stats["scan_bytes"])
+    pin_in = torch.empty(scan_total + 64, dtype=torch.uint8).pin_memory()
+    dev_in = torch.empty(scan_total + 64, dtype=torch.uint8, device=dev)
+    for _ in range(2):
+        dev_in.copy_(pin_in, non_blocking=True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(floor_steps):
+        dev_in.copy_(pin_in, non_blocking=True)
+    torch.cuda.synchronize(dev)
+    api["h2d_floor"] = (time.perf_counter() - t0) / floor_steps
+    pageable = np.frombuffer(b"".join(datas), dtype=np.uint8)[:scan_total].copy()
+    nthreads = max(1, min(8, len(os.sched_getaffinity(0))))
+    piece = (scan_total + nthreads - 1) // nthreads  # one piece per thread: a python thread pool is too slow for 256 KB pieces
+    jobs = [(o, min(piece, scan_total - o)) for o in range(0, scan_total, piece)]
+    src0, dst0 = pageable.ctypes.data, pin_in.data_ptr()
+
+    def stage_all(pool):
+        list(pool.map(lambda j: ctypes.memmove(dst0 + j[0], src0 + j[0], j[1]), jobs))
+    with ThreadPoolExecutor(nthreads) as pool:
+        stage_all(pool)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(floor_steps):
+            stage_all(pool)
+        api["stage_floor"] = (time.perf_counter() - t0) / floor_steps
+    del pin_in, dev_in
+
     # ---- reduce over ranks (max time) ----
-    keys = ["dev_serial", "dev_pipelined", "host_serial", "host_pipelined", "framework_host_buffers", "copy_floor"]
+    keys = ["dev_serial", "dev_pipelined", "host_serial", "host_pipelined", "framework_host_buffers", "copy_floor", "h2d_floor", "stage_floor"]
     t = torch.tensor([ms_total, cabi_s * 1e3 / args.steps] + [api[k] * 1e3 for k in keys] + [float(pixels), float(out_bytes), float(n),
                      float(stats["scan_bytes"])], dtype=torch.float64, device=dev)
     per_rank_ms = [ms_total / args.steps]
@@ -633,7 +685,7 @@ def run_decode(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, cabi_ms = float(t[0]), float(t[1])
     api_ms = {k: float(t[2 + i]) for i, k in enumerate(keys)}
-    job_pixels, job_out_bytes, job_images, job_scan = float(tot[8]), float(tot[9]), float(tot[10]), float(tot[11])
+    job_pixels, job_out_bytes, job_images, job_scan = float(tot[2 + len(keys)]), float(tot[3 + len(keys)]), float(tot[4 + len(keys)]), float(tot[5 + len(keys)])
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -709,6 +761,11 @@ def run_decode(args, rank, world, local_rank):
     e2e["c_abi"]["path"] = "b200jpeg_decode_batch with on_host outputs (no framework): pageable JPEG bytes in, pinned host batch tensor out"
     e2e_dev = rate(api_ms["dev_pipelined"])
     e2e_dev.update({"h2d_bytes_per_step": int(job_scan), "d2h_bytes_per_step": 0, "serial": rate(api_ms["dev_serial"]),
+                    "h2d_floor_ms": api_ms["h2d_floor"], "stage_floor_ms": api_ms["stage_floor"],
+                    "floors": "per rank, all ranks at once: raw cudaMemcpyAsync of the batch's %d entropy-coded bytes pinned host -> device "
+                              "(h2d_floor_ms), and the pageable -> pinned copy of the same bytes, one piece per thread on up to 8 of the threads "
+                              "this rank may run on (stage_floor_ms); the decoder does the second, then the first, then %.2f ms of kernels"
+                              % (int(job_scan / max(1, world)), ms_step),
                     "path": "as e2e without the copy back: host JPEG bytes -> device pixels, what python/decoder.cpp:148-225 hands its users"})
     line = {
         "metric": "decoded_mpixel_per_s", "value": value, "unit": "Mpixel/s", "images_per_s": job_images / (ms_step / 1e3),
