@@ -408,6 +408,9 @@ __global__ void __launch_bounds__(kTailCta) k_huff_tail_round(BatchDev b, int r)
 // segmented-scan combine: a = earlier prefix, x = later element; bit31 = "absolute" flag
 __device__ __forceinline__ uint32_t seg_combine(uint32_t a, uint32_t x) { return (x & 0x80000000u) ? x : a + x; }
 
+// One CTA per image; every thread takes a run of consecutive subsequences, combines their slot counts, the CTA scans the
+// threads' totals once and the thread walks its run again writing the absolute counts (one scan and two barriers per image
+// instead of one per 256 subsequences: the kernel sits on the critical path of its group).
 constexpr int kScanThreads = 256;
 __global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
 {
@@ -416,36 +419,37 @@ __global__ void __launch_bounds__(kScanThreads) k_subseq_scan(BatchDev b)
     const uint32_t count = im.subseq_cta_count * kSubseqCta;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ uint32_t s_w[kScanThreads / 32];
-    __shared__ uint32_t s_carry;
-    if (threadIdx.x == 0)
-        s_carry = 0x80000000u;
-    __syncthreads();
+    const uint32_t per = (count + kScanThreads - 1) / kScanThreads;
+    const uint32_t lo = min(threadIdx.x * per, count), hi = min(lo + per, count);
+    const uint32_t* rec = b.sub_rec + im.subseq_first;
+    const uint64_t live_bits = uint64_t(b.states[img].clean_len) * 8u;
     bool bad = false;
-    for (uint32_t c0 = 0; c0 < count; c0 += kScanThreads) {
-        const uint32_t c = c0 + threadIdx.x;
-        uint32_t v = c < count ? b.sub_rec[im.subseq_first + c] : 0u;
-        if (c > 0 && c < count && b.sub_entry[im.subseq_first + c] != b.sub_exit[im.subseq_first + c - 1] &&
-            uint64_t(c) * uint32_t(b.subseq_bits) < uint64_t(b.states[img].clean_len) * 8u)
+    uint32_t v = 0; // identity: no absolute flag, nothing consumed
+    for (uint32_t c = lo; c < hi; ++c) {
+        v = seg_combine(v, rec[c]);
+        if (c > 0 && b.sub_entry[im.subseq_first + c] != b.sub_exit[im.subseq_first + c - 1] && uint64_t(c) * uint32_t(b.subseq_bits) < live_bits)
             bad = true; // the chain of entry/exit states is not consistent: synchronisation did not finish
+    }
+    uint32_t inc = v;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, v, o);
-            if (lane >= uint32_t(o))
-                v = seg_combine(tprev, v);
-        }
-        if (lane == 31)
-            s_w[warp] = v;
-        __syncthreads();
-        uint32_t pre = s_carry;
-        for (int i = 0; i < int(warp); ++i)
-            pre = seg_combine(pre, s_w[i]);
-        v = seg_combine(pre, v);
-        if (c < count)
-            b.sub_abs[im.subseq_first + c] = v;
-        __syncthreads();
-        if (threadIdx.x == kScanThreads - 1)
-            s_carry = v;
-        __syncthreads();
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t tprev = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= uint32_t(o))
+            inc = seg_combine(tprev, inc);
+    }
+    if (lane == 31)
+        s_w[warp] = inc;
+    __syncthreads();
+    uint32_t pre = 0x80000000u; // the image starts at an absolute zero
+    for (uint32_t i = 0; i < warp; ++i)
+        pre = seg_combine(pre, s_w[i]);
+    inc = seg_combine(pre, inc);
+    uint32_t run = __shfl_up_sync(0xFFFFFFFFu, inc, 1); // what came before this thread's run
+    if (lane == 0)
+        run = pre;
+    for (uint32_t c = lo; c < hi; ++c) {
+        run = seg_combine(run, rec[c]);
+        b.sub_abs[im.subseq_first + c] = run;
     }
     if (bad)
         atomicOr(&b.states[img].error, kErrNotConverged);
