@@ -197,7 +197,7 @@ __device__ uint32_t prog_dc_refine_warp(const ImageDesc& im, const ScanDesc& sc,
 }
 
 constexpr int kProgWarps = 4;       // warps per image when the batch has few progressive images (latency: 56 -> 41 ms for 64 .. 256 images)
-constexpr int kProgManyImages = 2048; // from this many on one warp per image: the images alone fill the device (4096 images: 93 ms against 158 ms)
+constexpr int kProgManyImages = 512;  // per launch (a group of the batch); from this many on one warp per image: the images alone fill the device (4096 images in four groups: 93 ms against 156 ms)
 struct ProgWarpSmem // what one warp needs for the scan it is decoding
 {
     DevHuffTable tab;                      // the AC table of an AC scan
