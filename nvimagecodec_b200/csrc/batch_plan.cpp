@@ -101,6 +101,8 @@ void plan_begin(BatchPlan& plan, const PlanOptions& opt)
     plan.map_unstuff.push_back(0);
     plan.map_subseq.push_back(0);
     plan.map_fused.push_back(0);
+    plan.map_dc.push_back(0);
+    plan.map_scan.push_back(0);
     plan.map_idct.push_back(0);
     plan.map_color.push_back(0);
 }
@@ -279,6 +281,12 @@ void plan_add_image(BatchPlan& plan, const ParsedJpeg& pj, const OutputSpec& out
     im.fused_cta_first = plan.map_fused.back();
     im.fused_cta_count = cdiv(im.subseq_count, kFusedOwn);
     plan.map_fused.push_back(im.fused_cta_first + im.fused_cta_count);
+    im.dc_cta_first = plan.map_dc.back();
+    im.dc_cta_count = std::max<uint32_t>(1, cdiv(uint64_t(im.mcus_x) * im.mcus_y, kDcChunkMcus));
+    plan.map_dc.push_back(im.dc_cta_first + im.dc_cta_count);
+    im.scan_cta_first = plan.map_scan.back();
+    im.scan_cta_count = cdiv(uint64_t(im.subseq_cta_count) * kSubseqCta, kScanChunk);
+    plan.map_scan.push_back(im.scan_cta_first + im.scan_cta_count);
 
     im.coef_off = plan.coef_elems;
     plan.coef_elems = align_up(plan.coef_elems + uint64_t(im.total_blocks) * 64, 64);

@@ -32,7 +32,7 @@ struct BatchPlan
     std::vector<uint16_t> quant; // 64 per table
     std::vector<ScanDesc> scans;       // scans of the progressive images
     std::vector<uint32_t> prog_images; // planned indices of the progressive images
-    std::vector<uint32_t> map_unstuff, map_subseq, map_idct, map_color, map_fused; // prefix CTA maps, size n+1
+    std::vector<uint32_t> map_unstuff, map_subseq, map_idct, map_color, map_fused, map_dc, map_scan; // prefix CTA maps, size n+1
     uint64_t raw_bytes = 0, clean_bytes = 0, coef_elems = 0, plane_bytes = 0;
     uint32_t total_chunks = 0, total_subseq = 0, total_segs = 0;
     uint64_t total_blocks = 0, total_pixels = 0, out_bytes = 0;

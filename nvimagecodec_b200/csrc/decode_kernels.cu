@@ -390,131 +390,150 @@ __global__ void __launch_bounds__(kUnstuffThreads) k_unstuff_write(BatchDev b)
 // ------------------------------------------------------------------------------------------------------------------
 // DC prediction: per image, segmented (restart interval) inclusive scan of the DC differences per component.
 // ------------------------------------------------------------------------------------------------------------------
-// One CTA per image.  Every warp takes a contiguous range of the image's MCUs and walks it 32 MCUs at a time with a warp-level
-// segmented scan (coalesced loads, no CTA barrier inside the loop), writing DC values relative to the start of its range;
-// after one barrier the warps add what the ranges before them leave behind to the part of their range in front of its first
-// restart boundary.  (A barrier-synchronised scan per 512 MCUs took 45 us per 1080p image on the critical path of its group.)
-__global__ void __launch_bounds__(kDcCta) k_dc_scan(BatchDev b)
+// An image is cut into chunks of kDcChunkMcus MCUs, one CTA each.  Inside the CTA every warp takes a contiguous range of 256
+// MCUs: it issues the loads of all its eight iterations first (the values go back into the array the differences come from,
+// so the compiler cannot move a load across a store), scans 32 MCUs at a time with warp shuffles, carrying the totals along;
+// one barrier combines the warps.  The chunks of an image form a chain: a CTA publishes what the image's MCUs up to its end
+// leave in the three predictors (two 64-bit words, dc_rec), its successor waits for that (CTAs take their place from a ticket
+// counter, so a CTA only waits for CTAs started before it).  (One CTA per image took 45 us for a 1080p image and 0.47 ms for a
+// 4K 4:4:4 one, on 32 .. 64 SMs, on the critical path of its group.)
+struct DcTotals
 {
-    const int img = blockIdx.x;
+    int v0, v1, v2, flag; // sums per component since the last restart boundary; flag: a boundary was passed
+};
+__device__ __forceinline__ DcTotals dc_combine(const DcTotals& a, const DcTotals& x) // a = earlier, x = later
+{
+    return x.flag ? x : DcTotals{a.v0 + x.v0, a.v1 + x.v1, a.v2 + x.v2, a.flag};
+}
+
+__global__ void __launch_bounds__(kDcCta, 2) k_dc_scan(BatchDev b)
+{
+    constexpr int NW = kDcCta / 32;
+    __shared__ DcTotals s_w[NW];
+    __shared__ DcTotals s_pred;
+    __shared__ uint32_t s_ticket;
+    if (threadIdx.x == 0)
+        s_ticket = atomicAdd(&b.sync->ticket_dc, 1u);
+    __syncthreads();
+    const uint32_t cta_abs = s_ticket + b.base_dc;
+    const int img = find_image_warp(b.cta_map_dc, b.num_images, cta_abs);
     const ImageDesc& im = b.images[img];
+    const uint32_t k = cta_abs - b.cta_map_dc[img];
     const uint32_t mcus = uint32_t(im.mcus_x) * uint32_t(im.mcus_y);
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    constexpr int NW = kDcCta / 32;
-    __shared__ int s_v[NW][3];
-    __shared__ int s_f[NW];
     int16_t* dc = b.dc + im.coef_off / 64;
     const uint32_t ri = im.restart_interval ? uint32_t(im.restart_interval) : 0xFFFFFFFFu;
     const uint32_t bpm = uint32_t(im.bpm);
-    const uint32_t per = ((mcus + NW - 1) / NW + 31u) & ~31u; // MCUs per warp, whole iterations of 32
-    const uint32_t w_lo = min(warp * per, mcus), w_hi = min(w_lo + per, mcus);
-    int c0 = 0, c1 = 0, c2 = 0, cflag = 0; // the range's running totals since its last restart boundary (warp-uniform)
-    // kDcBatch iterations of 32 MCUs at a time: all their loads are issued before anything is stored (the values go back into
-    // the array the differences come from, so the compiler cannot move a load across a store: one iteration at a time this
-    // loop paid a full memory latency per 32 MCUs)
-    constexpr int kDcBatch = 8;
+    const uint32_t w_lo = min(k * uint32_t(kDcChunkMcus) + warp * 32u * kDcBatch, mcus), w_hi = min(w_lo + 32u * kDcBatch, mcus);
     uint32_t comp_of = 0; // 2 bits per block of the MCU
     for (uint32_t j = 0; j < bpm; ++j)
         comp_of |= uint32_t(im.blk_comp[j]) << (2 * j);
-    for (uint32_t mb = w_lo; mb < w_hi; mb += 32 * kDcBatch) {
-        int s0[kDcBatch], s1[kDcBatch], s2[kDcBatch];
+    int s0[kDcBatch], s1[kDcBatch], s2[kDcBatch];
 #pragma unroll
-        for (int it = 0; it < kDcBatch; ++it) {
-            const uint32_t m = mb + uint32_t(it) * 32u + lane;
-            s0[it] = s1[it] = s2[it] = 0;
-            if (m < w_hi) {
-                const int16_t* pm = dc + uint64_t(m) * bpm;
-                for (uint32_t j = 0; j < bpm; ++j) {
-                    const int dv = pm[j];
-                    const uint32_t c = (comp_of >> (2 * j)) & 3u;
-                    s0[it] += c == 0 ? dv : 0;
-                    s1[it] += c == 1 ? dv : 0;
-                    s2[it] += c == 2 ? dv : 0;
-                }
-            }
-        }
-        int e0[kDcBatch], e1[kDcBatch], e2[kDcBatch]; // predictors at the start of the lane's MCU of each iteration
-#pragma unroll
-        for (int it = 0; it < kDcBatch; ++it) {
-            const uint32_t m = mb + uint32_t(it) * 32u + lane;
-            int v0 = s0[it], v1 = s1[it], v2 = s2[it];
-            int flag = (m < w_hi && m % ri == 0) ? 1 : 0; // (m == 0 included: the image starts with every predictor at zero)
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t0 = __shfl_up_sync(0xFFFFFFFFu, v0, o), t1 = __shfl_up_sync(0xFFFFFFFFu, v1, o), t2 = __shfl_up_sync(0xFFFFFFFFu, v2, o),
-                          tf = __shfl_up_sync(0xFFFFFFFFu, flag, o);
-                if (lane >= uint32_t(o)) {
-                    if (!flag) {
-                        v0 += t0;
-                        v1 += t1;
-                        v2 += t2;
-                    }
-                    flag |= tf;
-                }
-            }
-            if (!flag) { // nothing started anew in this iteration up to this lane: the range's totals so far carry on
-                v0 += c0;
-                v1 += c1;
-                v2 += c2;
-            }
-            e0[it] = v0 - s0[it];
-            e1[it] = v1 - s1[it];
-            e2[it] = v2 - s2[it];
-            c0 = __shfl_sync(0xFFFFFFFFu, v0, 31);
-            c1 = __shfl_sync(0xFFFFFFFFu, v1, 31);
-            c2 = __shfl_sync(0xFFFFFFFFu, v2, 31);
-            cflag |= __shfl_sync(0xFFFFFFFFu, flag, 31);
-        }
-#pragma unroll
-        for (int it = 0; it < kDcBatch; ++it) {
-            const uint32_t m = mb + uint32_t(it) * 32u + lane;
-            if (m < w_hi) {
-                int16_t* pm = dc + uint64_t(m) * bpm;
-                int p0 = e0[it], p1 = e1[it], p2 = e2[it];
-                for (uint32_t j = 0; j < bpm; ++j) {
-                    const uint32_t c = (comp_of >> (2 * j)) & 3u;
-                    const int val = (c == 0 ? p0 : (c == 1 ? p1 : p2)) + pm[j];
-                    p0 = c == 0 ? val : p0;
-                    p1 = c == 1 ? val : p1;
-                    p2 = c == 2 ? val : p2;
-                    pm[j] = int16_t(val);
-                }
+    for (int it = 0; it < kDcBatch; ++it) {
+        const uint32_t m = w_lo + uint32_t(it) * 32u + lane;
+        s0[it] = s1[it] = s2[it] = 0;
+        if (m < w_hi) {
+            const int16_t* pm = dc + uint64_t(m) * bpm;
+            for (uint32_t j = 0; j < bpm; ++j) {
+                const int dv = pm[j];
+                const uint32_t c = (comp_of >> (2 * j)) & 3u;
+                s0[it] += c == 0 ? dv : 0;
+                s1[it] += c == 1 ? dv : 0;
+                s2[it] += c == 2 ? dv : 0;
             }
         }
     }
-    if (lane == 0) {
-        s_v[warp][0] = c0;
-        s_v[warp][1] = c1;
-        s_v[warp][2] = c2;
-        s_f[warp] = cflag;
+    // inclusive totals through the lane's MCU of each iteration, relative to the start of the warp's range
+    int i0[kDcBatch], i1[kDcBatch], i2[kDcBatch];
+    uint32_t fmask = 0; // bit it: a restart boundary lies between the start of the warp's range and this MCU (inclusive)
+    DcTotals carry{0, 0, 0, 0};
+#pragma unroll
+    for (int it = 0; it < kDcBatch; ++it) {
+        const uint32_t m = w_lo + uint32_t(it) * 32u + lane;
+        int v0 = s0[it], v1 = s1[it], v2 = s2[it];
+        int flag = (m < w_hi && m % ri == 0) ? 1 : 0; // (m == 0 included: the image starts with every predictor at zero)
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t0 = __shfl_up_sync(0xFFFFFFFFu, v0, o), t1 = __shfl_up_sync(0xFFFFFFFFu, v1, o), t2 = __shfl_up_sync(0xFFFFFFFFu, v2, o),
+                      tf = __shfl_up_sync(0xFFFFFFFFu, flag, o);
+            if (lane >= uint32_t(o)) {
+                if (!flag) {
+                    v0 += t0;
+                    v1 += t1;
+                    v2 += t2;
+                }
+                flag |= tf;
+            }
+        }
+        if (!flag) { // nothing started anew in this iteration up to this lane: the range's totals so far carry on
+            v0 += carry.v0;
+            v1 += carry.v1;
+            v2 += carry.v2;
+        }
+        flag |= carry.flag;
+        i0[it] = v0;
+        i1[it] = v1;
+        i2[it] = v2;
+        fmask |= uint32_t(flag) << it;
+        carry.v0 = __shfl_sync(0xFFFFFFFFu, v0, 31);
+        carry.v1 = __shfl_sync(0xFFFFFFFFu, v1, 31);
+        carry.v2 = __shfl_sync(0xFFFFFFFFu, v2, 31);
+        carry.flag = __shfl_sync(0xFFFFFFFFu, flag, 31);
+    }
+    if (lane == 0)
+        s_w[warp] = carry;
+    __syncthreads();
+    // the chain: what the image's MCUs in front of this chunk leave behind
+    if (threadIdx.x == 0) {
+        DcTotals pred{0, 0, 0, 1}; // the image starts with every predictor at zero
+        if (k) {
+            const volatile unsigned long long* src = b.dc_rec + 2 * size_t(cta_abs - 1u);
+            unsigned long long w1;
+            uint32_t spins = 0;
+            while (((w1 = src[1]) >> 63) == 0) {
+                __nanosleep(32);
+                if (++spins > (1u << 24)) { // the predecessor is gone (it cannot be): fail the image rather than hang the device
+                    atomicOr(&b.states[img].error, kErrNotConverged);
+                    break;
+                }
+            }
+            __threadfence();
+            const unsigned long long w0 = src[0];
+            pred = DcTotals{int(uint32_t(w0)), int(uint32_t(w0 >> 32)), int(uint32_t(w1)), int((w1 >> 32) & 1u)};
+        }
+        DcTotals tot = pred;
+        for (int i = 0; i < NW; ++i)
+            tot = dc_combine(tot, s_w[i]);
+        if (k + 1 < im.dc_cta_count) {
+            unsigned long long* dst = b.dc_rec + 2 * size_t(cta_abs);
+            dst[0] = (unsigned long long)uint32_t(tot.v0) | ((unsigned long long)uint32_t(tot.v1) << 32);
+            __threadfence();
+            dst[1] = (unsigned long long)uint32_t(tot.v2) | ((unsigned long long)(0x80000000u | uint32_t(tot.flag ? 1 : 0)) << 32);
+        }
+        s_pred = pred;
     }
     __syncthreads();
-    if (warp == 0 || w_lo >= w_hi)
-        return;
-    int p[3] = {0, 0, 0}; // what the ranges before this one leave behind
-    for (int i = 0; i < int(warp); ++i) {
-        if (s_f[i]) {
-            p[0] = s_v[i][0];
-            p[1] = s_v[i][1];
-            p[2] = s_v[i][2];
-        } else {
-            p[0] += s_v[i][0];
-            p[1] += s_v[i][1];
-            p[2] += s_v[i][2];
+    DcTotals outer = s_pred; // everything in front of this warp's range
+    for (uint32_t i = 0; i < warp; ++i)
+        outer = dc_combine(outer, s_w[i]);
+#pragma unroll
+    for (int it = 0; it < kDcBatch; ++it) {
+        const uint32_t m = w_lo + uint32_t(it) * 32u + lane;
+        if (m < w_hi) {
+            const bool fresh = (fmask >> it) & 1u; // a boundary between the range's start and this MCU: nothing from outside reaches it
+            int p0 = i0[it] - s0[it] + (fresh ? 0 : outer.v0), p1 = i1[it] - s1[it] + (fresh ? 0 : outer.v1), p2 = i2[it] - s2[it] + (fresh ? 0 : outer.v2);
+            int16_t* pm = dc + uint64_t(m) * bpm;
+            for (uint32_t j = 0; j < bpm; ++j) {
+                const uint32_t c = (comp_of >> (2 * j)) & 3u;
+                const int val = (c == 0 ? p0 : (c == 1 ? p1 : p2)) + pm[j];
+                p0 = c == 0 ? val : p0;
+                p1 = c == 1 ? val : p1;
+                p2 = c == 2 ? val : p2;
+                pm[j] = int16_t(val);
+            }
         }
     }
-    if ((p[0] | p[1] | p[2]) == 0)
-        return;
-    // the MCUs of the range in front of its first restart boundary take the offset
-    uint32_t stop = w_hi;
-    if (ri != 0xFFFFFFFFu) {
-        const uint32_t first = ((w_lo + ri - 1) / ri) * ri;
-        stop = min(stop, first);
-    }
-    const uint32_t n = (stop - w_lo) * bpm;
-    int16_t* q = dc + uint64_t(w_lo) * bpm;
-    for (uint32_t i = lane; i < n; i += 32)
-        q[i] = int16_t(int(q[i]) + p[im.blk_comp[i % bpm]]);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -710,7 +729,7 @@ int launch_unstuff(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
 
 int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st)
 {
-    k_dc_scan<<<d.num_images, kDcCta, 0, st>>>(b);
+    k_dc_scan<<<d.dc_ctas, kDcCta, 0, st>>>(b);
     return 1;
 }
 

@@ -8,7 +8,7 @@ namespace b200jpeg {
 struct LaunchDims
 {
     int num_images = 0;
-    uint32_t unstuff_ctas = 0, subseq_ctas = 0, idct_ctas = 0, color_ctas = 0, fused_ctas = 0;
+    uint32_t unstuff_ctas = 0, subseq_ctas = 0, idct_ctas = 0, color_ctas = 0, fused_ctas = 0, dc_ctas = 0, scan_ctas = 0;
 };
 
 // each returns the number of kernels it launched
@@ -24,6 +24,7 @@ int launch_huff_write(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 // b.sync->ticket == 0 and the group's words of b.fused_rec zeroed
 int launch_huff_fused(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int fused_configure(const BatchDev& b); // dynamic shared memory limit of k_huff_fused; -1 on error
+// needs b.sync->ticket_dc == 0 and the group's words of b.dc_rec zeroed
 int launch_dc(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 int launch_idct(const BatchDev& b, const LaunchDims& d, cudaStream_t st);
 // the scans of progressive images [first, first + count) of b.prog_images -> dense coefficients

@@ -99,7 +99,7 @@ Decoder::~Decoder()
     if (device_ >= 0)
         cudaSetDevice(device_);
     DevBuf* dbufs[] = {&d_blkpos_, &d_stamp_, &d_raw_, &d_clean_, &d_coef_, &d_dc_, &d_planes_, &d_meta_, &d_states_, &d_seg_, &d_chunks_, &d_exit_, &d_entry_,
-        &d_rec_, &d_abs_, &d_wl0_, &d_wl1_, &d_sync_, &d_out_, &d_fusedrec_};
+        &d_rec_, &d_abs_, &d_wl0_, &d_wl1_, &d_sync_, &d_out_, &d_fusedrec_, &d_dcrec_, &d_scanrec_};
     for (cudaStream_t st : streams_)
         if (st)
             cudaStreamSynchronize(st);
@@ -333,7 +333,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
         (rc = ensure(d_entry_, 8 * size_t(plan_.total_subseq))) || (rc = ensure(d_rec_, 4 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_abs_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_wl0_, 4 * size_t(plan_.total_subseq))) ||
         (rc = ensure(d_wl1_, 4 * size_t(plan_.total_subseq))) || (rc = ensure(d_sync_, sizeof(SyncCounters) * kMaxGroups)) ||
-        (rc = ensure(d_fusedrec_, 8 * size_t(plan_.map_fused.back()) + 8)) ||
+        (rc = ensure(d_fusedrec_, 8 * size_t(plan_.map_fused.back()) + 8)) || (rc = ensure(d_dcrec_, 16 * size_t(plan_.map_dc.back()) + 16)) ||
+        (rc = ensure(d_scanrec_, 8 * size_t(plan_.map_scan.back()) + 8)) ||
         (dev_out_bytes && (rc = ensure(d_out_, dev_out_bytes))))
         return rc;
     for (const HostOutput& ho : host_outs_)
@@ -345,7 +346,7 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     const size_t off_quant = align_up(off_huff + sizeof(DevHuffTable) * plan_.huff.size(), 256);
     const size_t off_m0 = align_up(off_quant + plan_.quant.size() * sizeof(uint16_t), 256);
     const size_t map_bytes = align_up(sizeof(uint32_t) * (m + 1), 256);
-    const size_t off_cimg = off_m0 + 5 * map_bytes;
+    const size_t off_cimg = off_m0 + 7 * map_bytes;
     const size_t off_scans = off_cimg + align_up(sizeof(uint32_t) * (plan_.total_subseq / kSubseqCta + 1), 256);
     const size_t off_prog = off_scans + align_up(sizeof(ScanDesc) * plan_.scans.size(), 256);
     const size_t meta_bytes = off_prog + align_up(sizeof(uint32_t) * plan_.prog_images.size(), 256);
@@ -362,6 +363,8 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     std::memcpy(hm + off_m0 + 2 * map_bytes, plan_.map_idct.data(), sizeof(uint32_t) * (m + 1));
     std::memcpy(hm + off_m0 + 3 * map_bytes, plan_.map_color.data(), sizeof(uint32_t) * (m + 1));
     std::memcpy(hm + off_m0 + 4 * map_bytes, plan_.map_fused.data(), sizeof(uint32_t) * (m + 1));
+    std::memcpy(hm + off_m0 + 5 * map_bytes, plan_.map_dc.data(), sizeof(uint32_t) * (m + 1));
+    std::memcpy(hm + off_m0 + 6 * map_bytes, plan_.map_scan.data(), sizeof(uint32_t) * (m + 1));
     for (int i = 0; i < m; ++i) { // image of every subsequence CTA (the work-list rounds look items up by subsequence index)
         uint32_t* cimg = reinterpret_cast<uint32_t*>(hm + off_cimg) + plan_.images[i].subseq_first / kSubseqCta;
         for (uint32_t c = 0; c < plan_.images[i].subseq_cta_count; ++c)
@@ -403,6 +406,10 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.cta_map_subseq = reinterpret_cast<const uint32_t*>(dm + off_m0 + 1 * map_bytes);
     dev_.cta_map_fused = reinterpret_cast<const uint32_t*>(dm + off_m0 + 4 * map_bytes);
     dev_.fused_rec = static_cast<unsigned long long*>(d_fusedrec_.p);
+    dev_.cta_map_dc = reinterpret_cast<const uint32_t*>(dm + off_m0 + 5 * map_bytes);
+    dev_.dc_rec = static_cast<unsigned long long*>(d_dcrec_.p);
+    dev_.cta_map_scan = reinterpret_cast<const uint32_t*>(dm + off_m0 + 6 * map_bytes);
+    dev_.scan_rec = static_cast<unsigned long long*>(d_scanrec_.p);
     dev_.subseq_cta_img = reinterpret_cast<const uint32_t*>(dm + off_cimg);
     dev_.scans = reinterpret_cast<const ScanDesc*>(dm + off_scans);
     dev_.prog_images = reinterpret_cast<const uint32_t*>(dm + off_prog);
@@ -475,6 +482,12 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
         gr.dev.cta_map_fused = dev_.cta_map_fused + first;
         gr.dev.base_fused = plan_.map_fused[first];
         gr.dims.fused_ctas = plan_.map_fused[last] - plan_.map_fused[first];
+        gr.dev.cta_map_dc = dev_.cta_map_dc + first;
+        gr.dev.base_dc = plan_.map_dc[first];
+        gr.dims.dc_ctas = plan_.map_dc[last] - plan_.map_dc[first];
+        gr.dev.cta_map_scan = dev_.cta_map_scan + first;
+        gr.dev.base_scan = plan_.map_scan[first];
+        gr.dims.scan_ctas = plan_.map_scan[last] - plan_.map_scan[first];
         gr.dev.base_idct = plan_.map_idct[first];
         gr.dev.base_color = plan_.map_color[first];
         gr.dev.worklist[0] = dev_.worklist[0] + plan_.images[first].subseq_first;
@@ -702,6 +715,8 @@ int Decoder::launch_group(int g)
     mark(kStageUnstuff);
     B2J_CUDA(cudaMemsetAsync(static_cast<ImageState*>(d_states_.p) + m0, 0, sizeof(ImageState) * mc, st));
     B2J_CUDA(cudaMemsetAsync(gr.dev.sync, 0, sizeof(SyncCounters), st));
+    B2J_CUDA(cudaMemsetAsync(gr.dev.dc_rec + 2 * size_t(gr.dev.base_dc), 0, 16 * size_t(gr.dims.dc_ctas), st)); // the chunks of an image hand each other the DC predictors
+    B2J_CUDA(cudaMemsetAsync(gr.dev.scan_rec + gr.dev.base_scan, 0, 8 * size_t(gr.dims.scan_ctas), st));           // ... and the slot counts
     stat_launches_ += launch_unstuff(gr.dev, gr.dims, st);
     if (use_fused_) { // the whole entropy-decode stage in one launch; its CTAs hand each other one word per CTA, zero = not there yet
         B2J_CUDA(cudaMemsetAsync(gr.dev.fused_rec + gr.dev.base_fused, 0, 8 * size_t(gr.dims.fused_ctas), st));

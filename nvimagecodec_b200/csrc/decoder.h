@@ -177,7 +177,7 @@ class Decoder
     std::vector<HostOutput> host_outs_;
 
     DevBuf d_blkpos_, d_stamp_, d_raw_, d_clean_, d_coef_, d_dc_, d_planes_, d_meta_, d_states_, d_seg_, d_chunks_, d_exit_, d_entry_, d_rec_, d_abs_, d_wl0_,
-        d_wl1_, d_sync_, d_out_, d_fusedrec_;
+        d_wl1_, d_sync_, d_out_, d_fusedrec_, d_dcrec_, d_scanrec_;
     DevBuf h_raw_, h_meta_, h_states_;
     BatchDev dev_{};
     LaunchDims dims_{};

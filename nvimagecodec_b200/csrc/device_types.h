@@ -35,6 +35,9 @@ constexpr int kIdctCta = B2J_IDCT_CTA; // threads per CTA, one 8x8 block per thr
 constexpr int kColorCta = 128;       // threads per CTA: 4 warps, each warp one tile of 512 pixels x (1|2) rows
 constexpr int kColorTilePx = 512;    // pixels per warp tile (16 per lane)
 constexpr int kDcCta = 512;          // threads per CTA, one MCU per thread per iteration
+constexpr int kDcBatch = 8;          // iterations a warp of the DC kernel keeps in flight
+constexpr int kScanChunk = 256 * 8;   // subsequences per CTA of k_subseq_scan (256 threads, eight iterations per warp range)
+constexpr int kDcChunkMcus = kDcCta * kDcBatch; // MCUs per CTA of the DC kernel: big images are cut into chunks that hand each other the predictors
 constexpr int kMaxBlocksPerMcu = 10;  // the limit of the JPEG standard: luma 4x2 + Cb + Cr (4:1:0)
 constexpr int kMaxTabSlots = 6;       // distinct Huffman tables one image can reference (3 components x DC/AC)
 
@@ -131,6 +134,8 @@ struct ImageDesc
     uint32_t subseq_first, subseq_count; // subsequence slots (multiple of kSubseqCta) / used slots
     uint32_t subseq_cta_first, subseq_cta_count;
     uint32_t fused_cta_first, fused_cta_count; // CTAs of the fused Huffman kernel (kFusedOwn subsequences each)
+    uint32_t dc_cta_first, dc_cta_count;       // CTAs of the DC kernel (kDcChunkMcus MCUs each)
+    uint32_t scan_cta_first, scan_cta_count;   // CTAs of k_subseq_scan (kScanChunk subsequences each)
     uint32_t seg_first;   // index into the segment-start pool; entries [seg_first, seg_first + num_segments]
 
     // Huffman tables of the reconstruction kernel: it decodes the AC symbols of a block itself and stages only AC tables
@@ -201,7 +206,9 @@ struct SyncCounters // device-side bookkeeping of the synchronisation rounds
     uint32_t redone;      // subsequences re-decoded in tail rounds
     uint32_t ticket;      // fused kernel: CTAs take their position in launch order from here (a CTA only ever waits for one that started before it)
     uint32_t chain_redo;  // fused kernel: CTAs whose halo did not deliver the true entry state (they re-walked their range)
-    uint32_t pad_[1];
+    uint32_t ticket_dc;   // DC kernel: the same for its chain of chunks
+    uint32_t ticket_scan; // k_subseq_scan: likewise
+    uint32_t pad2_[3];
     uint32_t round_items[kTraceRounds]; // diagnostics (B200JPEG_TRACE): list length of each work-list round ...
     uint32_t round_ns[kTraceRounds];    // ... and the time from the kernel's start to the end of that round, ns
 };
@@ -238,13 +245,18 @@ struct BatchDev // pointers handed to every kernel
     const uint32_t* cta_map_fused;   // fused Huffman kernel
     unsigned long long* fused_rec;   // fused Huffman kernel, per CTA: exit state of its last subsequence (huffman.cuh pack_rel) | (coefficient slots
                                      // consumed up to there | 1 << 31) << 32; zero until the CTA has published it
+    const uint32_t* cta_map_dc;      // DC kernel
+    const uint32_t* cta_map_scan;    // k_subseq_scan
+    unsigned long long* scan_rec;    // k_subseq_scan, per chunk: absolute slot count at the chunk's end | 1 << 63; zero until published
+    unsigned long long* dc_rec;      // DC kernel, two words per chunk: what the image's MCUs up to the chunk's end leave in the three predictors
+                                     // (word 0: Y | Cb << 32; word 1: Cr | (1 << 31 there, bit 0: a restart boundary was passed) << 32); zero until published
     const uint32_t* subseq_cta_img;  // batch image index of every subsequence CTA (indexed by global subsequence / kSubseqCta)
     int32_t image_base;              // batch index of images[0] (a launch may cover a group of consecutive images)
     const uint32_t* cta_map_idct;
     const uint32_t* cta_map_color;
     // a launch may cover only a group of consecutive images: images / states / the CTA maps then point at the group's first
     // image (map values stay absolute) and the kernels add these bases to blockIdx.x
-    uint32_t base_unstuff, base_subseq, base_idct, base_color, base_fused;
+    uint32_t base_unstuff, base_subseq, base_idct, base_color, base_fused, base_dc, base_scan;
     int32_t subseq_bits;   // bits per subsequence
     uint32_t total_subseq;
     int32_t num_tables;    // Huffman tables in the pool
