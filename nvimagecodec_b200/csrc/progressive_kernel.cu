@@ -223,8 +223,8 @@ __global__ void __launch_bounds__(32 * NW) k_prog_decode(BatchDev b, uint32_t fi
     __shared__ __align__(16) ProgWarpSmem s_warp[NW];
     __shared__ uint8_t s_zz[64];
     __shared__ uint32_t s_next, s_done, s_ndone, s_err;
-    if (threadIdx.x < 64)
-        s_zz[threadIdx.x] = c_zigzag[threadIdx.x];
+    for (uint32_t i = threadIdx.x; i < 64; i += 32 * NW) // (one warp per image when the batch holds many: NW == 1)
+        s_zz[i] = c_zigzag[i];
     if (threadIdx.x == 0)
         s_next = s_done = s_ndone = s_err = 0;
     __syncthreads();
