@@ -451,6 +451,31 @@ def test_many_progressive_images_one_warp_each(cpu):
         dec.close()
 
 
+def test_many_small_baseline_images_in_one_launch(cpu):
+    """640 small baseline images in one group: every per-kernel CTA map has more than 64 entries (the warp-wide image lookup
+    narrows the range by binary search first), restart intervals and every sampling mode in the mix"""
+    import torch
+    from nvimagecodec_b200.decoder import Decoder
+    base_cases = [(64, 48, (2, 2), False, 0), (97, 61, (2, 1), False, 3), (80, 80, (1, 1), False, 0), (120, 75, (1, 1), True, 0), (131, 77, (1, 2), False, 0),
+                  (75, 50, (4, 1), False, 2), (160, 120, (2, 2), False, 1), (33, 17, (2, 2), False, 0), (1, 1, (1, 1), False, 0), (17, 9, (2, 2), False, 0)]
+    base = [make_jpeg(950 + i, w, h, samp, 85, gray=g, restart_interval=ri) for i, (w, h, samp, g, ri) in enumerate(base_cases)]
+    want, rst, _ = cpu.decode_host(base)
+    assert all(s == ref.STATUS_SUCCESS for s in rst)
+    n = 640
+    datas = [base[i % len(base)] for i in range(n)]
+    dims = [base_cases[i % len(base)][:2] for i in range(n)]
+    for opts in (":fancy_upsampling=1 :groups=1", ":fancy_upsampling=1 :groups=1 :fused=1", ":fancy_upsampling=1 :groups=3"):
+        dec = Decoder(0, options=opts)
+        outs = [torch.zeros((h, w * 3), dtype=torch.uint8, device="cuda") for (w, h) in dims]
+        st = dec.decode_into(datas, [o.data_ptr() for o in outs], [w * 3 for (w, h) in dims], [4] * n)
+        torch.cuda.synchronize()
+        assert st == [0] * n
+        for i, o in enumerate(outs):
+            w = want[i % len(base)]
+            assert np.array_equal(o.cpu().numpy().reshape(w.shape), w), (opts, i)
+        dec.close()
+
+
 def test_progressive_and_410_streams_on_the_gpu(sess, cpu):
     """f2: progressive streams (k_prog_decode: every scan of every image into dense coefficients, the images side by side) and
     4:1:0 sampling, mixed with baseline images in one batch: pixels and quantised coefficients bit-exact against the compiled
