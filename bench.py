@@ -625,6 +625,43 @@ def run_decode(args, rank, world, local_rank):
         x.close()
     sess.close()
 
+    # ---- secondary reference (north star: "the nvjpeg_ext numbers are added as a secondary reference where that extension
+    # installs offline"): the reference's own GPU plugin for this path, built unmodified by `make -C oracle nvjpeg`, through the
+    # same framework call with the same bytes and the same device buffers.  N = 1 only; context, not a parity partner (nvJPEG's
+    # IDCT is not libjpeg-turbo's). ----
+    nvjpeg_ext = None
+    nvj_dir = os.path.join(ROOT, "oracle", "_ref", "nvjpeg")
+    if rank == 0 and world == 1 and not args.skip_cpu_baseline and not sharded:
+        if not os.path.exists(os.path.join(nvj_dir, "libnvjpeg_ext.so")):
+            nvjpeg_ext = {"unavailable": "oracle/_ref/nvjpeg/libnvjpeg_ext.so not built (make -C oracle nvjpeg)"}
+        else:
+            nvjpeg_ext = {"path": "nvimgcodecDecoderDecode -> the reference's nvjpeg_ext (libnvjpeg 12.4 of the CUDA toolkit, static), pageable host "
+                                  "JPEG bytes in, device pixels out: the call pattern of e2e_device_out.serial", "backends": {}}
+            nsess = ref.Session(ext_dir=nvj_dir, with_ljt=False)
+            for name, mask in (("hybrid_cpu_gpu", ref.BACKEND_HYBRID), ("hw_gpu_only", ref.BACKEND_HW)):
+                try:
+                    nd = nsess.decoder(device_id=local_rank, backends=mask, options=":fancy_upsampling=1")
+                    st, _ = nd.decode_pipelined(datas, ptrs[0], ptrs[1], fdims, ffmts, strides, ref.BUFFER_DEVICE, stream, rounds=2, depth=1)
+                    torch.cuda.synchronize(dev)
+                    if not all(x == ref.STATUS_SUCCESS for x in st):
+                        nvjpeg_ext["backends"][name] = {"unavailable": "no decoder of this kind took the images on this device (status 0x%x)" % st[0]}
+                        nd.close()
+                        continue
+                    entry = {}
+                    if want is not None:
+                        got = dev_sets[0].cpu().numpy()
+                        d0 = np.abs(got[offs[0]:offs[1]].astype(np.int16) - want[0].reshape(-1).astype(np.int16))
+                        entry["vs_libjpeg_turbo_pixels"] = {"max_abs_diff": int(d0.max()), "identical_fraction": float((d0 == 0).mean())}
+                    nsteps = max(3, min(10, args.steps))
+                    st, secs = nd.decode_pipelined(datas, ptrs[0], ptrs[1], fdims, ffmts, strides, ref.BUFFER_DEVICE, stream, rounds=nsteps, depth=1)
+                    torch.cuda.synchronize(dev)
+                    entry.update({"value": pixels / 1e6 / (secs / nsteps), "unit": "Mpixel/s", "ms_per_step": secs / nsteps * 1e3, "steps": nsteps})
+                    nvjpeg_ext["backends"][name] = entry
+                    nd.close()
+                except Exception as e:  # noqa: BLE001  (a secondary reference must not take the bench down)
+                    nvjpeg_ext["backends"][name] = {"unavailable": "%s: %s" % (type(e).__name__, e)}
+            nsess.close()
+
     # ---- the floor of any host->host number on this box: the raw device -> pinned host copy of one batch of pixels, every rank
     # at once (at 8 GPUs the box's aggregate device -> host rate, not the decoder, bounds e2e) ----
     barrier()
@@ -787,6 +824,8 @@ def run_decode(args, rank, world, local_rank):
         "roofline": roof,
         "cpu_baseline": cpu_baseline,
     }
+    if nvjpeg_ext is not None:
+        line["nvjpeg_ext"] = nvjpeg_ext
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
