@@ -2,15 +2,15 @@
 //
 // Pipeline for one batch (all kernels are descriptor-driven: one launch covers every image of the batch, a CTA finds its
 // image with a binary search over a per-kernel prefix map):
-//   U1 k_unstuff_count   count kept bytes / RSTn markers per 4 KB chunk of entropy-coded data
+//   U1 k_unstuff_count   count kept bytes / RSTn markers per 16 KB chunk of entropy-coded data
 //   U2 k_unstuff_scan    per image: exclusive scan of the chunk counts, unstuffed length, segment table init
 //   U3 k_unstuff_write   compact: drop FF00 stuffing, FF fill, RSTn markers; record restart-segment starts
 //   H1 k_huff_sync x 2   self-synchronising subsequence decode (no output): round 0 from a guessed state, round 1 from the
 //                        predecessor's exit state; subsequences whose exit state changed feed a work list
 //   H2 k_huff_sync_tail  cooperative kernel: Jacobi rounds over the (compacted) work list until it is empty
-//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute block position per subsequence
+//   H3 k_subseq_scan     segmented scan of coefficient-slot counts -> absolute block position per subsequence (chunks of an image chained)
 //   H4 k_huff_write      block pass: per block the DC difference and the bit position of its first AC symbol
-//   D1 k_dc_scan         per image: DC prediction = segmented (restart interval) prefix sum per component over dc[]
+//   D1 k_dc_scan         DC prediction = segmented (restart interval) prefix sum per component over dc[] (chunks of an image chained)
 //   I1 k_idct            one 8x8 block per thread: Huffman-decode the block's AC symbols from the stream into a dense block
 //                        in shared memory, dequantise + islow IDCT, write the component planes -- coefficients never leave
 //                        the SM

@@ -3,7 +3,9 @@
 //   H1 k_huff_sync x 2   self-synchronising subsequence decode (no output): round 0 from a guessed state, round 1 from the
 //                        predecessor's exit state; subsequences whose exit state changed feed a work list
 //   H2 k_huff_sync_tail  cooperative kernel: Jacobi rounds over the (compacted) work list until it is empty
-//   H3 k_subseq_scan     per image: segmented scan of coefficient-slot counts -> absolute block position per subsequence
+//   H3 k_subseq_scan     segmented scan of coefficient-slot counts -> absolute block position per subsequence (an image's chunks
+//                        of 2048 subsequences hand each other their totals)
+//   H* k_huff_fused      (option fused=1) H1 .. H4 in one launch; see its header below
 //   H4 k_huff_write      block pass: a last decode from the agreed entry states that stores, for every block, the DC
 //                        difference and the bit position of its first AC symbol (the AC symbols are decoded by the thread
 //                        that reconstructs the block, decode_kernels.cu k_idct)
