@@ -428,7 +428,10 @@ int Decoder::plan_batch(int n, const uint8_t* const* data, const size_t* sizes, 
     dev_.tail_mode = (opt_.tail_spread ? 1 : 0);
     dev_.stream_words = 0;
     if (opt_.stage_stream && opt_.subseq_bytes <= 256)
-        dev_.stream_words = (plan_.subseq_bits / 32 + 3) | 1; // a symbol starting in the last word reads two words past it
+#ifndef B2J_STREAM_EXTRA
+#define B2J_STREAM_EXTRA 3
+#endif
+        dev_.stream_words = (plan_.subseq_bits / 32 + B2J_STREAM_EXTRA) | 1; // a symbol starting in the last word reads two words past it
     use_fused_ = opt_.fused && dev_.stream_words != 0;
     if (dev_.lut_slots != cfg_lut_slots_ || dev_.stream_words != cfg_stream_words_ || dev_.subseq_bits != cfg_subseq_bits_) {
         if (huff_configure(dev_, device_, &tail_capacity_) != 0 || tail_capacity_ <= 0 || (use_fused_ && fused_configure(dev_) != 0)) {

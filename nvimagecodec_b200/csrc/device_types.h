@@ -10,7 +10,10 @@
 
 namespace b200jpeg {
 
-constexpr int kLutBits = 11;          // first-level Huffman lookup width
+#ifndef B2J_LUT_BITS
+#define B2J_LUT_BITS 11
+#endif
+constexpr int kLutBits = B2J_LUT_BITS; // first-level Huffman lookup width (build-time: variant builds)
 constexpr int kLutSize = 1 << kLutBits;
 constexpr int kLut2Size = 512;        // second-level entries (codes longer than kLutBits)
 constexpr int kLutEntries = kLutSize + kLut2Size;
