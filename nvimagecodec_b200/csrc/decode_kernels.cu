@@ -561,7 +561,7 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
     uint32_t* s_job = reinterpret_cast<uint32_t*>(s_order + kIdctCta);                     // kIdctCta x {bit position, table}
     uint32_t* s_stream = s_job + 2 * kIdctCta;                                             // kIdctStreamWords
     uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_stream + kIdctStreamWords);            // the image's AC tables (b.lut_ac_slots)
-    __shared__ uint32_t s_cnt[8], s_err;
+    __shared__ uint32_t s_cnt[8];
     __shared__ __align__(8) uint64_t s_bar;
     if (threadIdx.x == 0)
         mbar_init(&s_bar, 1);
@@ -575,8 +575,6 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
         s_zz[threadIdx.x] = zigzag_dump_entry(c_zigzag, threadIdx.x);
     if (threadIdx.x < 8)
         s_cnt[threadIdx.x] = 0;
-    if (threadIdx.x == 8)
-        s_err = 0;
     const uint32_t u0 = (cta_abs - b.cta_map_idct[img]) * kIdctCta, u = u0 + threadIdx.x;
     const uint32_t* words = reinterpret_cast<const uint32_t*>(b.clean + im.clean_off);
     const uint32_t max_word = (im.raw_len + 12u) >> 2;
@@ -601,7 +599,7 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
             for (uint32_t i = threadIdx.x; i < n_words; i += kIdctCta)
                 s_stream[i] = __byte_perm(__ldg(words + min(w_first + i, max_word)), 0, 0x0123);
     }
-    const IdctBlockRef ref = idct_locate(im, u);
+    IdctBlockRef ref = idct_locate(im, u);
     bool wanted = ref.comp >= 0;
     if (wanted) { // region of interest: blocks none of whose samples can reach a pixel of the region (8 pixels of margin cover
                   // the neighbours the upsampling filters look at) are not needed
@@ -626,7 +624,8 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
         // Every thread zeroes the slot of its own block and posts the block as a job: where its AC symbols start and which
         // table they use.  The jobs are then dealt out again by length (a counting sort over eight classes of the block's
         // bit count, longest first): the lanes of a warp decode blocks of similar length instead of waiting for the longest
-        // of 32 arbitrary ones.  Afterwards every thread reads its own block's slot back.
+        // of 32 arbitrary ones.  The thread that decoded a block goes straight on to reconstruct it: no barrier between
+        // the decode and the IDCT (the warps with the short blocks would spend it waiting for the warp with the long ones).
 #pragma unroll
         for (int i = 0; i < 9; ++i)
             reinterpret_cast<uint4*>(slot)[i] = make_uint4(0, 0, 0, 0);
@@ -643,7 +642,7 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
                 s_job[2 * threadIdx.x + 1] = uint32_t(im.ac_slot[ref.comp]);
             } else {
                 wanted = false; // a block the block pass never reached: its image is reported failed
-                atomicOr(&s_err, kErrOverrun);
+                atomicOr(&b.states[img].error, kErrOverrun);
             }
         }
         __syncthreads();
@@ -662,10 +661,12 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
                 total += s_cnt[c];
         }
         __syncthreads();
-        if (threadIdx.x < total) {
+        wanted = threadIdx.x < total;
+        if (wanted) {
             const uint32_t j = s_order[threadIdx.x];
             const uint32_t sl = s_job[2 * j + 1];
-            int16_t* dst = reinterpret_cast<int16_t*>(s_blk + j * kIdctPitch);
+            slot = s_blk + j * kIdctPitch;
+            int16_t* dst = reinterpret_cast<int16_t*>(slot);
             uint32_t err;
             if (n_words <= uint32_t(kIdctStreamWords))
                 err = decode_block_ac<true>(s_stream - w_first, w_first + n_words - 1u, s_job[2 * j], s_lut, sl * kLutEntries, b.huff + im.ac_pool[sl],
@@ -673,11 +674,9 @@ __global__ void __launch_bounds__(kIdctCta, B2J_IDCT_MIN_CTAS) k_idct(BatchDev b
             else
                 err = decode_block_ac<false>(words, max_word, s_job[2 * j], s_lut, sl * kLutEntries, b.huff + im.ac_pool[sl], s_zz, dst);
             if (err)
-                atomicOr(&s_err, err);
+                atomicOr(&b.states[img].error, err);
+            ref = idct_locate(im, u0 + j); // from here on this thread's block is the one it decoded
         }
-        __syncthreads();
-        if (threadIdx.x == 0 && s_err)
-            atomicOr(&b.states[img].error, s_err);
     }
     if (!wanted)
         return;

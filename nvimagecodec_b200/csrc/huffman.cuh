@@ -332,7 +332,11 @@ B2J_HD uint32_t decode_block_ac(const uint32_t* words, uint32_t max_word, uint32
     if (widx > max_word)
         return kErrOverrun;
     auto load = [&](uint32_t i) {
-        i = i > max_word ? max_word : i;
+        // STAGED: no clamp.  A block takes at most 63 symbols of at most 31 bits, so damaged data can carry the window 62 words
+        // past the word its block starts in and no further; the caller keeps that much readable memory behind the staged
+        // words (k_idct: the Huffman tables follow the stream in shared memory), and what is read there is garbage for garbage.
+        if (!STAGED)
+            i = i > max_word ? max_word : i;
 #if defined(__CUDA_ARCH__)
         return STAGED ? words[i] : bswap32(__ldg(words + i));
 #else
